@@ -1,0 +1,267 @@
+"""ctypes binding of libb200_embed.so -- one Python signature per declaration in include/b200_embed.h.
+
+This is the stub a maintainer of the reference would write in Rust (INTEGRATION.md shows that one);
+it is Python here because the image has no Rust toolchain. No torch types cross this boundary:
+only pointers and sizes. Device memory for the `*_device` / `b200_op_*` entry points is passed as
+raw addresses (e.g. `tensor.data_ptr()`).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import re
+import tempfile
+
+import numpy as np
+
+from . import weights as W
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libb200_embed.so")
+HEADER_PATH = os.path.join(HERE, "..", "include", "b200_embed.h")
+
+FLAG_NORMALIZE = 1
+FLAG_FP32 = 2
+ERR_NAMES = {0: "OK", -1: "INVALID_ARG", -2: "CUDA", -3: "OOM", -4: "UNSUPPORTED_SHAPE", -5: "NO_DEVICE", -6: "IO"}
+KIND_NAMES = ["lengths", "embed_ln", "gemm_qkv", "attention", "gemm_attn_out", "gemm_ffn1", "gemm_ffn2", "add_ln",
+              "pool"]
+
+
+class B200EmbedError(RuntimeError):
+    def __init__(self, code: int, message: str):
+        super().__init__(f"b200_embed error {code} ({ERR_NAMES.get(code, '?')}): {message}")
+        self.code = code
+        self.message = message
+
+
+class Config(C.Structure):
+    _fields_ = [("vocab_size", C.c_int32), ("hidden_size", C.c_int32), ("num_hidden_layers", C.c_int32),
+                ("num_attention_heads", C.c_int32), ("intermediate_size", C.c_int32),
+                ("max_position_embeddings", C.c_int32), ("type_vocab_size", C.c_int32), ("hidden_act", C.c_int32),
+                ("layer_norm_eps", C.c_float), ("max_tokens_per_launch", C.c_int32)]
+
+
+class KindStats(C.Structure):
+    _fields_ = [("total_ms", C.c_double), ("launches", C.c_int64)]
+
+
+_P = C.c_void_p
+_SIGNATURES = {
+    "b200_embed_create": (C.c_int32, [C.POINTER(Config), C.c_char_p, C.c_uint64, C.c_int32, C.POINTER(_P)]),
+    "b200_embed_destroy": (None, [_P]),
+    "b200_embed_hidden_size": (C.c_int32, [_P]),
+    "b200_embed_max_positions": (C.c_int32, [_P]),
+    "b200_embed_last_error": (C.c_char_p, []),
+    "b200_embed_forward": (C.c_int32, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_uint32, _P]),
+    "b200_embed_forward_varlen": (C.c_int32, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_uint32, _P]),
+    "b200_embed_submit": (C.c_int32, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_uint32, _P, C.POINTER(C.c_int64)]),
+    "b200_embed_wait": (C.c_int32, [_P, C.c_int64]),
+    "b200_embed_forward_device": (C.c_int32, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_uint32, _P, _P]),
+    "b200_embed_host_alloc": (C.c_int32, [C.c_size_t, C.POINTER(_P)]),
+    "b200_embed_host_free": (None, [_P]),
+    "b200_embed_export_safetensors": (C.c_int32, [_P, C.c_char_p]),
+    "b200_embed_kernel_launches": (C.c_int64, [_P]),
+    "b200_embed_profile_enable": (C.c_int32, [_P, C.c_int32]),
+    "b200_embed_profile_read": (C.c_int32, [_P, C.POINTER(KindStats), C.c_int32]),
+    "b200_op_embed_layernorm": (C.c_int32, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, _P, _P]),
+    "b200_op_linear": (C.c_int32, [_P, C.c_int32, C.c_int32, _P, _P, C.c_int32, C.c_int32, _P, _P]),
+    "b200_op_attention": (C.c_int32, [_P, _P, _P, C.c_int32, C.c_int32, C.c_int32, _P, _P]),
+    "b200_op_add_layernorm": (C.c_int32, [_P, C.c_int32, C.c_int32, _P, C.c_int32, _P, C.c_int32, C.c_int32, _P, _P]),
+    "b200_op_mean_pool": (C.c_int32, [_P, _P, _P, C.c_int32, C.c_int32, C.c_int32, _P, _P]),
+    "b200_op_gemm_bf16": (C.c_int32, [_P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P, _P]),
+}
+
+_lib = None
+
+
+def declared_symbols() -> list:
+    """Every function name include/b200_embed.h declares."""
+    with open(HEADER_PATH) as f:
+        text = f.read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(b200_(?:embed|op)_[a-z0-9_]+)\s*\(", text)))
+
+
+def load_library():
+    """Loads libb200_embed.so; raises if it has not been built. There is no fallback implementation."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(f"{LIB_PATH} is missing: run `python __graft_entry__.py` (build()) first; "
+                              "there is no CPU or PyTorch fallback for this path")
+        lib = C.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = lib
+    return _lib
+
+
+def missing_symbols(lib=None) -> list:
+    lib = lib or load_library()
+    out = [n for n in declared_symbols() if not hasattr(lib, n)]
+    out += [n for n in declared_symbols() if n not in _SIGNATURES]
+    return out
+
+
+def _check(rc: int):
+    if rc != 0:
+        raise B200EmbedError(rc, load_library().b200_embed_last_error().decode(errors="replace"))
+
+
+def _u32(a):
+    a = np.ascontiguousarray(a, dtype=np.uint32)
+    return a, a.ctypes.data
+
+
+def host_alloc(shape, dtype) -> np.ndarray:
+    """A numpy array in pinned host memory (b200_embed_host_alloc); free with host_free(arr)."""
+    lib = load_library()
+    n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+    p = _P()
+    _check(lib.b200_embed_host_alloc(max(n, 1), C.byref(p)))
+    buf = (C.c_char * max(n, 1)).from_address(p.value)
+    arr = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+    _PINNED[arr.ctypes.data] = p.value
+    return arr
+
+
+_PINNED = {}
+
+
+def host_free(arr: np.ndarray) -> None:
+    p = _PINNED.pop(arr.ctypes.data, None)
+    if p is not None:
+        load_library().b200_embed_host_free(p)
+
+
+class Embedder:
+    """Owns one b200_embed handle (one model replica on one GPU)."""
+
+    def __init__(self, shape: W.BertShape, safetensors_path: str | None = None, seed: int = 1234, device: int = 0,
+                 max_tokens_per_launch: int = 0):
+        self.lib = load_library()
+        self.shape = shape
+        cfg = Config(shape.vocab_size, shape.hidden_size, shape.num_hidden_layers, shape.num_attention_heads,
+                     shape.intermediate_size, shape.max_position_embeddings, shape.type_vocab_size,
+                     shape.hidden_act, shape.layer_norm_eps, max_tokens_per_launch)
+        h = _P()
+        path = safetensors_path.encode() if safetensors_path else None
+        _check(self.lib.b200_embed_create(C.byref(cfg), path, seed, device, C.byref(h)))
+        self.h = h
+        self.device = device
+
+    @classmethod
+    def random_init(cls, shape, seed=1234, device=0, **kw):
+        return cls(shape, None, seed, device, **kw)
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.b200_embed_destroy(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def hidden_size(self) -> int:
+        return self.lib.b200_embed_hidden_size(self.h)
+
+    @property
+    def max_positions(self) -> int:
+        return self.lib.b200_embed_max_positions(self.h)
+
+    def kernel_launches(self) -> int:
+        return int(self.lib.b200_embed_kernel_launches(self.h))
+
+    # -- host-buffer entry points ---------------------------------------------------------------
+    def forward(self, ids, mask, type_ids, flags: int = 0, out: np.ndarray | None = None) -> np.ndarray:
+        ids, p_ids = _u32(ids)
+        mask, p_mask = _u32(mask)
+        type_ids, p_tt = _u32(type_ids)
+        if ids.ndim != 2 or ids.shape != mask.shape or ids.shape != type_ids.shape:
+            raise ValueError("ids, mask and type_ids must be [batch, seq_len] arrays of one shape")
+        b, s = ids.shape
+        if out is None:
+            out = np.empty((b, self.shape.hidden_size), dtype=np.float32)
+        _check(self.lib.b200_embed_forward(self.h, p_ids, p_mask, p_tt, b, s, flags, out.ctypes.data))
+        return out
+
+    def forward_varlen(self, ids_packed, type_ids_packed, cu_seqlens, max_seqlen: int, flags: int = 0) -> np.ndarray:
+        ids, p_ids = _u32(ids_packed)
+        tt, p_tt = _u32(type_ids_packed)
+        cu = np.ascontiguousarray(cu_seqlens, dtype=np.int32)
+        b = len(cu) - 1
+        out = np.empty((b, self.shape.hidden_size), dtype=np.float32)
+        _check(self.lib.b200_embed_forward_varlen(self.h, p_ids, p_tt, cu.ctypes.data, b, int(ids.size), max_seqlen,
+                                                  flags, out.ctypes.data))
+        return out
+
+    def submit(self, ids, mask, type_ids, out: np.ndarray, flags: int = 0) -> int:
+        """Buffers must stay alive (and should be pinned) until wait(ticket)."""
+        for a in (ids, mask, type_ids):
+            assert a.dtype == np.uint32 and a.flags.c_contiguous
+        assert out.dtype == np.float32 and out.flags.c_contiguous
+        b, s = ids.shape
+        t = C.c_int64()
+        _check(self.lib.b200_embed_submit(self.h, ids.ctypes.data, mask.ctypes.data, type_ids.ctypes.data, b, s, flags,
+                                          out.ctypes.data, C.byref(t)))
+        return t.value
+
+    def wait(self, ticket: int) -> None:
+        _check(self.lib.b200_embed_wait(self.h, ticket))
+
+    # -- device-buffer entry point --------------------------------------------------------------
+    def forward_device(self, d_ids: int, d_mask: int, d_type_ids: int, batch: int, seq_len: int, d_out: int,
+                       flags: int = 0, stream: int = 0) -> None:
+        _check(self.lib.b200_embed_forward_device(self.h, d_ids, d_mask, d_type_ids, batch, seq_len, flags, d_out,
+                                                  stream or None))
+
+    # -- introspection ----------------------------------------------------------------------------
+    def export_safetensors(self, path: str) -> None:
+        _check(self.lib.b200_embed_export_safetensors(self.h, path.encode()))
+
+    def export_weights(self) -> dict:
+        """The f32 master weights the handle computes with, as {HF name: ndarray}."""
+        with tempfile.TemporaryDirectory() as d:
+            p = os.path.join(d, "model.safetensors")
+            self.export_safetensors(p)
+            return W.load_safetensors(p)
+
+    def profile(self, on: bool) -> None:
+        _check(self.lib.b200_embed_profile_enable(self.h, int(on)))
+
+    def profile_read(self, reset: bool = True) -> dict:
+        arr = (KindStats * len(KIND_NAMES))()
+        _check(self.lib.b200_embed_profile_read(self.h, arr, int(reset)))
+        return {n: {"total_ms": arr[i].total_ms, "launches": int(arr[i].launches)} for i, n in enumerate(KIND_NAMES)}
+
+    # -- single kernels (device pointers) -------------------------------------------------------
+    def op_embed_layernorm(self, d_ids, d_tt, d_cu, batch, total, dtype, d_out, stream=0):
+        _check(self.lib.b200_op_embed_layernorm(self.h, d_ids, d_tt, d_cu, batch, total, dtype, d_out, stream or None))
+
+    def op_linear(self, layer, which, d_x, d_residual, rows, dtype, d_y, stream=0):
+        _check(self.lib.b200_op_linear(self.h, layer, which, d_x, d_residual or None, rows, dtype, d_y, stream or None))
+
+    def op_attention(self, d_qkv, d_cu, batch, max_seqlen, dtype, d_ctx, stream=0):
+        _check(self.lib.b200_op_attention(self.h, d_qkv, d_cu, batch, max_seqlen, dtype, d_ctx, stream or None))
+
+    def op_add_layernorm(self, layer, which, d_y, y_is_f32, d_residual, rows, dtype, d_out, stream=0):
+        _check(self.lib.b200_op_add_layernorm(self.h, layer, which, d_y, int(y_is_f32), d_residual, rows, dtype, d_out,
+                                              stream or None))
+
+    def op_mean_pool(self, d_hidden, d_cu, batch, dtype, normalize, d_out, stream=0):
+        _check(self.lib.b200_op_mean_pool(self.h, d_hidden, d_cu, batch, dtype, int(normalize), d_out, stream or None))
+
+
+def op_gemm_bf16(d_a, d_b, d_bias, m, n, k, act, block_n, d_c, stream=0):
+    _check(load_library().b200_op_gemm_bf16(d_a, d_b, d_bias, m, n, k, act, block_n, d_c, stream or None))

@@ -1,0 +1,308 @@
+// Memory-bound kernels of the embedding path (all HBM-bound; one warp per token row, 8/16-byte
+// vector accesses, fp32 statistics, warp-shuffle reductions):
+//   lengths / cu_seqlens from the tokenizer's attention mask   (embedding_generator.rs:185, :190)
+//   K1 embedding gather + LayerNorm       (candle bert.rs BertEmbeddings::forward)
+//   K4 residual add + LayerNorm           (BertSelfOutput::forward / BertOutput::forward)
+//   K5 masked mean-pool (+ L2 normalise)  (embedding_generator.rs:201-207; L2 is the north_star addition)
+#include "kernels.h"
+
+#include "common.cuh"
+
+namespace b200 {
+
+namespace {
+
+constexpr int MAX_CHUNKS = 8;  // hidden <= 1024: 32 lanes x 4 elements x 8 chunks
+
+// Exact two-pass LayerNorm of one row held across a warp (chunk i of lane l = columns 128 i + 4 l ..+3).
+template <typename T>
+__device__ __forceinline__ void warp_layernorm_store(float4 (&v)[MAX_CHUNKS], int nchunk, int H, int lane,
+                                                     const float* __restrict__ gamma,
+                                                     const float* __restrict__ beta, float eps, T* out_row) {
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < MAX_CHUNKS; ++i)
+        if (i < nchunk) s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+    const float mean = warp_sum(s) / static_cast<float>(H);
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < MAX_CHUNKS; ++i)
+        if (i < nchunk) {
+            const float a = v[i].x - mean, b = v[i].y - mean, c = v[i].z - mean, d = v[i].w - mean;
+            q += (a * a + b * b) + (c * c + d * d);
+        }
+    const float var = warp_sum(q) / static_cast<float>(H);
+    const float rstd = 1.0f / sqrtf(var + eps);
+#pragma unroll
+    for (int i = 0; i < MAX_CHUNKS; ++i)
+        if (i < nchunk) {
+            const int col = i * 128 + lane * 4;
+            const float4 g = __ldg(reinterpret_cast<const float4*>(gamma + col));
+            const float4 b = __ldg(reinterpret_cast<const float4*>(beta + col));
+            float4 y;
+            y.x = (v[i].x - mean) * rstd * g.x + b.x;
+            y.y = (v[i].y - mean) * rstd * g.y + b.y;
+            y.z = (v[i].z - mean) * rstd * g.z + b.z;
+            y.w = (v[i].w - mean) * rstd * g.w + b.w;
+            Vec4<T>::store(out_row + col, y);
+        }
+}
+
+// ---- attention mask -> lengths ------------------------------------------------------------------
+// One warp per sentence. The mask must be a right-padded 0/1 prefix (PaddingDirection::Right,
+// embedding_generator.rs:85); anything else sets status bit 0.
+__global__ void mask_lengths_kernel(const uint32_t* __restrict__ mask, int batch, int seq_len,
+                                    int* __restrict__ lens, int* __restrict__ status) {
+    const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (b >= batch) return;
+    const uint32_t* row = mask + static_cast<size_t>(b) * seq_len;
+    int cnt = 0;
+    bool bad = false;
+    for (int j = lane; j < seq_len; j += 32) {
+        const uint32_t m = row[j];
+        if (m > 1u) bad = true;
+        if (j > 0 && m > row[j - 1]) bad = true;
+        cnt += (m != 0u);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    bad = __any_sync(0xffffffffu, bad);
+    if (lane == 0) {
+        lens[b] = cnt;
+        if (bad) atomicOr(status, 1);
+    }
+}
+
+// Single-block exclusive scan: cu[0] = 0, cu[b+1] = cu[b] + lens[b].
+__global__ void scan_lengths_kernel(const int* __restrict__ lens, int batch, int* __restrict__ cu) {
+    __shared__ int warp_tot[32];
+    __shared__ int carry;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) { carry = 0; cu[0] = 0; }
+    __syncthreads();
+    for (int base = 0; base < batch; base += blockDim.x) {
+        const int i = base + threadIdx.x;
+        const int v = i < batch ? lens[i] : 0;
+        int x = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int y = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= o) x += y;
+        }
+        if (lane == 31) warp_tot[warp] = x;
+        __syncthreads();
+        if (warp == 0) {
+            int w = lane < (blockDim.x >> 5) ? warp_tot[lane] : 0;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int y = __shfl_up_sync(0xffffffffu, w, o);
+                if (lane >= o) w += y;
+            }
+            warp_tot[lane] = w;  // inclusive
+        }
+        __syncthreads();
+        const int prefix = carry + (warp > 0 ? warp_tot[warp - 1] : 0) + x;  // inclusive
+        if (i < batch) cu[i + 1] = prefix;
+        __syncthreads();
+        if (threadIdx.x == blockDim.x - 1) carry = prefix;
+        __syncthreads();
+    }
+}
+
+// ---- K1 -------------------------------------------------------------------------------------------
+// One warp per token. PADDED: grid over [batch, seq_len] positions, pad positions exit, the row is
+// written packed at cu[b] + j. Packed: grid over tokens, sentence found by binary search in cu.
+template <typename T, bool PADDED>
+__global__ void embed_layernorm_kernel(const uint32_t* __restrict__ ids, const uint32_t* __restrict__ type_ids,
+                                       const int* __restrict__ cu, int batch, int seq_len, int total_tokens,
+                                       const T* __restrict__ word, const T* __restrict__ pos,
+                                       const T* __restrict__ type, const float* __restrict__ gamma,
+                                       const float* __restrict__ beta, float eps, int H, int vocab,
+                                       int type_vocab, int max_pos, T* __restrict__ out,
+                                       int* __restrict__ status) {
+    const long long w = static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    long long src, dst;
+    int j;
+    if (PADDED) {
+        if (w >= static_cast<long long>(batch) * seq_len) return;
+        const int b = static_cast<int>(w / seq_len);
+        j = static_cast<int>(w - static_cast<long long>(b) * seq_len);
+        const int start = cu[b];
+        if (j >= cu[b + 1] - start) return;
+        src = w;
+        dst = start + j;
+    } else {
+        if (w >= total_tokens) return;
+        int lo = 0, hi = batch;  // largest b with cu[b] <= w
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (cu[mid] <= w) lo = mid; else hi = mid;
+        }
+        j = static_cast<int>(w - cu[lo]);
+        src = w;
+        dst = w;
+    }
+    uint32_t id = ids[src], tt = type_ids[src];
+    if (id >= static_cast<uint32_t>(vocab) || tt >= static_cast<uint32_t>(type_vocab) || j >= max_pos) {
+        if (lane == 0) atomicOr(status, 2);
+        id = id >= static_cast<uint32_t>(vocab) ? 0u : id;
+        tt = tt >= static_cast<uint32_t>(type_vocab) ? 0u : tt;
+        j = j >= max_pos ? 0 : j;
+    }
+    const T* wr = word + static_cast<size_t>(id) * H;
+    const T* tr = type + static_cast<size_t>(tt) * H;
+    const T* pr = pos + static_cast<size_t>(j) * H;
+    const int nchunk = H >> 7;
+    float4 v[MAX_CHUNKS];
+#pragma unroll
+    for (int i = 0; i < MAX_CHUNKS; ++i)
+        if (i < nchunk) {
+            const int col = i * 128 + lane * 4;
+            const float4 a = Vec4<T>::load(wr + col), t = Vec4<T>::load(tr + col), p = Vec4<T>::load(pr + col);
+            v[i] = make_float4((a.x + t.x) + p.x, (a.y + t.y) + p.y, (a.z + t.z) + p.z, (a.w + t.w) + p.w);
+        }
+    warp_layernorm_store<T>(v, nchunk, H, lane, gamma, beta, eps, out + static_cast<size_t>(dst) * H);
+}
+
+// ---- K4 -------------------------------------------------------------------------------------------
+template <typename TY, typename T>
+__global__ void add_layernorm_kernel(const TY* __restrict__ y, const T* __restrict__ residual, int rows_cap,
+                                     const int* __restrict__ d_rows, const float* __restrict__ gamma,
+                                     const float* __restrict__ beta, float eps, int H, T* __restrict__ out) {
+    const long long r = static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    int rows = rows_cap;
+    if (d_rows != nullptr) rows = min(rows, *d_rows);
+    if (r >= rows) return;
+    const int nchunk = H >> 7;
+    float4 v[MAX_CHUNKS];
+#pragma unroll
+    for (int i = 0; i < MAX_CHUNKS; ++i)
+        if (i < nchunk) {
+            const int col = i * 128 + lane * 4;
+            const float4 a = Vec4<TY>::load(y + r * H + col), b = Vec4<T>::load(residual + r * H + col);
+            v[i] = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+        }
+    warp_layernorm_store<T>(v, nchunk, H, lane, gamma, beta, eps, out + r * H);
+}
+
+// ---- K5 -------------------------------------------------------------------------------------------
+// One block per sentence: thread (g, c) sums rows g, g+G, ... of 4 columns; groups are combined in
+// shared memory; the divisor is len + 1e-9 in fp32 exactly as the reference; optional L2 norm.
+template <typename T>
+__global__ void mean_pool_kernel(const T* __restrict__ hidden, const int* __restrict__ cu, int H, int normalize,
+                                 float* __restrict__ out) {
+    extern __shared__ float4 part[];  // [G][H/4]
+    __shared__ float red[32];
+    const int b = blockIdx.x;
+    const int cols4 = H >> 2;
+    const int G = blockDim.x / cols4;
+    const int g = threadIdx.x / cols4, c = threadIdx.x - g * cols4;
+    const int start = cu[b], len = cu[b + 1] - start;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (g < G) {
+        const T* p = hidden + static_cast<size_t>(start) * H + c * 4;
+        int j = g;
+        for (; j + G < len; j += 2 * G) {  // two rows in flight
+            const float4 a = Vec4<T>::load(p + static_cast<size_t>(j) * H);
+            const float4 d = Vec4<T>::load(p + static_cast<size_t>(j + G) * H);
+            acc.x += a.x + d.x; acc.y += a.y + d.y; acc.z += a.z + d.z; acc.w += a.w + d.w;
+        }
+        if (j < len) {
+            const float4 a = Vec4<T>::load(p + static_cast<size_t>(j) * H);
+            acc.x += a.x; acc.y += a.y; acc.z += a.z; acc.w += a.w;
+        }
+        part[g * cols4 + c] = acc;
+    }
+    __syncthreads();
+    float ss = 0.f;
+    float4 tot = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (threadIdx.x < cols4) {
+        for (int k = 0; k < G; ++k) {
+            const float4 a = part[k * cols4 + threadIdx.x];
+            tot.x += a.x; tot.y += a.y; tot.z += a.z; tot.w += a.w;
+        }
+        const float den = static_cast<float>(len) + 1e-9f;
+        tot.x /= den; tot.y /= den; tot.z /= den; tot.w /= den;
+        ss = (tot.x * tot.x + tot.y * tot.y) + (tot.z * tot.z + tot.w * tot.w);
+    }
+    if (normalize) {
+        ss = warp_sum(ss);
+        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+        __syncthreads();
+        float t = 0.f;
+        for (int k = 0; k < (blockDim.x >> 5); ++k) t += red[k];
+        const float inv = 1.0f / fmaxf(sqrtf(t), 1e-12f);
+        tot.x *= inv; tot.y *= inv; tot.z *= inv; tot.w *= inv;
+    }
+    if (threadIdx.x < cols4) *reinterpret_cast<float4*>(out + static_cast<size_t>(b) * H + threadIdx.x * 4) = tot;
+}
+
+}  // namespace
+
+cudaError_t launch_mask_lengths(const uint32_t* mask, int batch, int seq_len, int* lens, int* cu, int* status,
+                                cudaStream_t s) {
+    if (batch <= 0) return cudaSuccess;
+    mask_lengths_kernel<<<(batch + 7) / 8, 256, 0, s>>>(mask, batch, seq_len, lens, status);
+    scan_lengths_kernel<<<1, 1024, 0, s>>>(lens, batch, cu);
+    return cudaGetLastError();
+}
+
+template <typename T>
+cudaError_t launch_embed_layernorm(const EmbedArgs& a, cudaStream_t s) {
+    const long long warps = a.padded ? static_cast<long long>(a.batch) * a.seq_len : a.total_tokens;
+    if (warps <= 0) return cudaSuccess;
+    const unsigned grid = static_cast<unsigned>((warps + 7) / 8);
+    if (a.padded)
+        embed_layernorm_kernel<T, true><<<grid, 256, 0, s>>>(
+            a.ids, a.type_ids, a.cu, a.batch, a.seq_len, a.total_tokens, static_cast<const T*>(a.word),
+            static_cast<const T*>(a.pos), static_cast<const T*>(a.type), a.gamma, a.beta, a.eps, a.H, a.vocab,
+            a.type_vocab, a.max_pos, static_cast<T*>(a.out), a.status);
+    else
+        embed_layernorm_kernel<T, false><<<grid, 256, 0, s>>>(
+            a.ids, a.type_ids, a.cu, a.batch, a.seq_len, a.total_tokens, static_cast<const T*>(a.word),
+            static_cast<const T*>(a.pos), static_cast<const T*>(a.type), a.gamma, a.beta, a.eps, a.H, a.vocab,
+            a.type_vocab, a.max_pos, static_cast<T*>(a.out), a.status);
+    return cudaGetLastError();
+}
+template cudaError_t launch_embed_layernorm<__nv_bfloat16>(const EmbedArgs&, cudaStream_t);
+template cudaError_t launch_embed_layernorm<float>(const EmbedArgs&, cudaStream_t);
+
+template <typename TY, typename T>
+cudaError_t launch_add_layernorm(const TY* y, const T* residual, int rows_cap, const int* d_rows,
+                                 const float* gamma, const float* beta, float eps, int H, T* out,
+                                 cudaStream_t s) {
+    if (rows_cap <= 0) return cudaSuccess;
+    add_layernorm_kernel<TY, T><<<(rows_cap + 7) / 8, 256, 0, s>>>(y, residual, rows_cap, d_rows, gamma, beta,
+                                                                  eps, H, out);
+    return cudaGetLastError();
+}
+template cudaError_t launch_add_layernorm<__nv_bfloat16, __nv_bfloat16>(const __nv_bfloat16*, const __nv_bfloat16*,
+                                                                        int, const int*, const float*,
+                                                                        const float*, float, int, __nv_bfloat16*,
+                                                                        cudaStream_t);
+template cudaError_t launch_add_layernorm<float, __nv_bfloat16>(const float*, const __nv_bfloat16*, int, const int*,
+                                                                const float*, const float*, float, int,
+                                                                __nv_bfloat16*, cudaStream_t);
+template cudaError_t launch_add_layernorm<float, float>(const float*, const float*, int, const int*, const float*,
+                                                        const float*, float, int, float*, cudaStream_t);
+
+template <typename T>
+cudaError_t launch_mean_pool(const T* hidden, const int* cu, int batch, int H, int normalize, float* out,
+                             cudaStream_t s) {
+    if (batch <= 0) return cudaSuccess;
+    const int cols4 = H / 4;
+    int G = 512 / cols4;
+    if (G < 1) G = 1;
+    if (G > 8) G = 8;
+    const int threads = ((G * cols4 + 31) / 32) * 32;
+    mean_pool_kernel<T><<<batch, threads, G * cols4 * sizeof(float4), s>>>(hidden, cu, H, normalize, out);
+    return cudaGetLastError();
+}
+template cudaError_t launch_mean_pool<__nv_bfloat16>(const __nv_bfloat16*, const int*, int, int, int, float*,
+                                                     cudaStream_t);
+template cudaError_t launch_mean_pool<float>(const float*, const int*, int, int, int, float*, cudaStream_t);
+
+}  // namespace b200

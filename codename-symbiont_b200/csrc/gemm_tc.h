@@ -1,0 +1,35 @@
+// Host interface of the tcgen05 GEMM (gemm_tc.cu).
+#pragma once
+#include <cuda_runtime.h>
+
+namespace b200 {
+
+enum GemmEpilogue {
+    EPI_BIAS = 0,       // y = x.W^T + b
+    EPI_GELU_ERF = 1,   // y = gelu_erf(x.W^T + b)      (candle HiddenAct::Gelu)
+    EPI_GELU_TANH = 2,  // tanh-form GELU               (HiddenAct::GeluApproximate)
+    EPI_RELU = 3,       // relu                         (HiddenAct::Relu)
+    EPI_RES_LN = 4,     // y = LayerNorm(x.W^T + b + residual); needs block_n == n
+};
+
+struct GemmTcArgs {
+    const void* a;         // [m, k] bf16 row-major (activations)
+    const void* b;         // [n, k] bf16 row-major (HF Linear weight)
+    int m, n, k;
+    const int* d_rows;     // optional device int: rows actually present (<= m); tiles beyond are skipped
+    const float* bias;     // [n]
+    const void* residual;  // [m, n] bf16 (EPI_RES_LN)
+    const float* gamma;    // [n]     (EPI_RES_LN)
+    const float* beta;     // [n]     (EPI_RES_LN)
+    float eps;
+    void* out;             // [m, n] bf16, or fp32 when out_f32
+    int out_f32;           // only with EPI_BIAS
+    int epi;               // GemmEpilogue
+    int block_n;           // 128, 192, 256 (EPI_RES_LN: == n, one of 128/256/384)
+};
+
+// Largest supported tile width for this N and epilogue; 0 if none.
+int gemm_tc_pick_block_n(int n, int epi);
+cudaError_t gemm_tc_launch(const GemmTcArgs& args, cudaStream_t stream, int num_sms);
+
+}  // namespace b200

@@ -1,0 +1,50 @@
+// Host-side launchers of the non-GEMM kernels (elementwise.cu, attention.cu, fp32_ref.cu).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b200 {
+
+// attention mask [batch, seq_len] -> lens[batch], cu[batch+1]; status |= 1 if not a 0/1 prefix.
+cudaError_t launch_mask_lengths(const uint32_t* mask, int batch, int seq_len, int* lens, int* cu, int* status,
+                                cudaStream_t s);
+
+struct EmbedArgs {
+    const uint32_t* ids;       // padded [batch, seq_len] or packed [total_tokens]
+    const uint32_t* type_ids;
+    const int* cu;             // device cu_seqlens[batch + 1]
+    int batch, seq_len, total_tokens;
+    int padded;                // 1: ids are [batch, seq_len]; 0: packed
+    const void *word, *pos, *type;  // tables in T
+    const float *gamma, *beta;
+    float eps;
+    int H, vocab, type_vocab, max_pos;
+    void* out;                 // packed [tokens, H] in T
+    int* status;               // |= 2 on id / type id / position out of range
+};
+template <typename T>
+cudaError_t launch_embed_layernorm(const EmbedArgs& a, cudaStream_t s);
+
+template <typename TY, typename T>
+cudaError_t launch_add_layernorm(const TY* y, const T* residual, int rows_cap, const int* d_rows,
+                                 const float* gamma, const float* beta, float eps, int H, T* out, cudaStream_t s);
+
+template <typename T>
+cudaError_t launch_mean_pool(const T* hidden, const int* cu, int batch, int H, int normalize, float* out,
+                             cudaStream_t s);
+
+// K3 (bf16): varlen flash attention over packed qkv [tokens, 3H]; head_dim 32 or 64.
+cudaError_t launch_attention_bf16(const __nv_bfloat16* qkv, const int* cu, int batch, int max_seqlen, int heads,
+                                  int head_dim, __nv_bfloat16* ctx, cudaStream_t s);
+
+// fp32 validation kernels (correctness only).
+cudaError_t launch_attention_f32(const float* qkv, const int* cu, int batch, int max_seqlen, int heads,
+                                 int head_dim, float* ctx, cudaStream_t s);
+// y[M,N] = act(x[M,K] . w[N,K]^T + bias); act: -1 none, else B200_EMBED_ACT_*.
+cudaError_t launch_gemm_f32(const float* x, const float* w, const float* bias, int m_cap, const int* d_rows, int n,
+                            int k, int act, float* y, cudaStream_t s);
+// fp32 -> bf16 (RNE) weight conversion
+cudaError_t launch_f32_to_bf16(const float* src, __nv_bfloat16* dst, size_t n, cudaStream_t s);
+
+}  // namespace b200

@@ -1,0 +1,183 @@
+/*
+ * b200_embed.h -- C ABI of libb200_embed.so: a B200-native (sm_100a) replacement for the one
+ * data-parallel hot path of makkenzo/codename-symbiont, the sentence-embedding forward pass in
+ * `preprocessing_service` (tokenised batch -> BERT encoder -> masked mean-pool [-> L2 norm]).
+ *
+ * Reference interface replaced (paths relative to the reference repository root):
+ *   services/preprocessing_service/src/embedding_generator.rs
+ *     :17   EmbeddingGenerator::new(model_id, revision, force_cpu)      -> b200_embed_create
+ *     :134  generate_sentence_embeddings(&self, &[String])              -> b200_embed_forward*
+ *     :189-191 Tensor::from_vec(ids / mask / type_ids, (b, P))           (the three u32 inputs)
+ *     :198  BertModel::forward(ids, type_ids, Some(mask))               (the encoder)
+ *     :201-207 masked mean-pool                                         (fused epilogue)
+ *     :214  to_vec2::<f32>()                                            (float* out, [batch][hidden])
+ * Everything above that call (NATS handling, tokenizers, sentence split) and below it
+ * (libs/shared_models payloads, the Qdrant upsert) is unchanged; see INTEGRATION.md for the
+ * Rust binding a maintainer would add.
+ *
+ * Conventions: every entry point returns B200_EMBED_OK (0) or a negative B200_EMBED_ERR_* code and
+ * never throws or aborts across the boundary; the message of the last failure on the calling
+ * thread is b200_embed_last_error(). Pointers are plain host pointers unless the name says
+ * `device`. The caller owns all input and output buffers for the duration of the call; the
+ * library owns weights and workspaces. There is NO CPU fallback: without a CUDA device every
+ * compute entry returns B200_EMBED_ERR_NO_DEVICE.
+ */
+#ifndef B200_EMBED_H_
+#define B200_EMBED_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_EMBED_OK 0
+#define B200_EMBED_ERR_INVALID_ARG (-1)       /* bad pointer/size, id >= vocab, mask not a 0/1 prefix */
+#define B200_EMBED_ERR_CUDA (-2)              /* a CUDA call or kernel failed */
+#define B200_EMBED_ERR_OOM (-3)               /* device or pinned allocation failed */
+#define B200_EMBED_ERR_UNSUPPORTED_SHAPE (-4) /* model shape outside what the kernels are built for */
+#define B200_EMBED_ERR_NO_DEVICE (-5)         /* no CUDA device: there is no CPU fallback */
+#define B200_EMBED_ERR_IO (-6)                /* safetensors file unreadable / tensor missing */
+
+/* flags for the forward entry points */
+#define B200_EMBED_FLAG_NORMALIZE 1u /* append v / max(||v||_2, 1e-12). The reference does NOT normalise
+                                        (embedding_generator.rs:201-207), so the drop-in default is 0. */
+#define B200_EMBED_FLAG_FP32 2u      /* fp32 validation mode: fp32 weights, activations and SIMT GEMMs
+                                        (slow; parity gate cosine >= 0.999999). Default is bf16 tensor cores. */
+
+/* hidden_act values: candle HiddenAct::{Gelu, GeluApproximate, Relu} */
+#define B200_EMBED_ACT_GELU_ERF 0
+#define B200_EMBED_ACT_GELU_TANH 1
+#define B200_EMBED_ACT_RELU 2
+
+typedef struct b200_embed b200_embed;
+
+/* The config.json fields candle's bert::Config reads (embedding_generator.rs:70-71). */
+typedef struct b200_embed_config {
+    int32_t vocab_size;
+    int32_t hidden_size;        /* multiple of 128, <= 1024 */
+    int32_t num_hidden_layers;
+    int32_t num_attention_heads; /* head dim must be 32 or 64 */
+    int32_t intermediate_size;  /* multiple of 64 */
+    int32_t max_position_embeddings;
+    int32_t type_vocab_size;
+    int32_t hidden_act;         /* B200_EMBED_ACT_* */
+    float layer_norm_eps;
+    int32_t max_tokens_per_launch; /* workspace capacity in tokens; 0 = default (1 Mi). Larger calls are
+                                      split into sentence chunks internally, order preserved. */
+} b200_embed_config;
+
+/* -- lifetime: replaces EmbeddingGenerator::new (embedding_generator.rs:17-132) ------------------
+ * safetensors_path: a HuggingFace BERT `model.safetensors` (F32/F16/BF16; names as in
+ * BertModel::load, optional `bert.` prefix, legacy gamma/beta LayerNorm names) or NULL for the
+ * seeded random init used by benchmarks (spec in codename-symbiont_b200/weights.py).
+ * Converts weights to bf16 once, packs Q/K/V into one [3H,H] matrix, keeps the f32 master for
+ * the validation mode. The handle is thread-safe: concurrent forward calls each lease a
+ * stream + workspace (the reference shares one Arc<EmbeddingGenerator>, main.rs:314, :373). */
+int32_t b200_embed_create(const b200_embed_config* cfg, const char* safetensors_path, uint64_t seed,
+                          int32_t device, b200_embed** out);
+void b200_embed_destroy(b200_embed* h);
+
+int32_t b200_embed_hidden_size(const b200_embed* h);
+int32_t b200_embed_max_positions(const b200_embed* h);
+/* thread-local, never NULL */
+const char* b200_embed_last_error(void);
+
+/* -- the hot path: replaces embedding_generator.rs:189-214 ---------------------------------------
+ * input_ids / attention_mask / token_type_ids: [batch, seq_len] row-major u32 exactly as
+ * `tokenizers` produced them (embedding_generator.rs:179-187); attention_mask must be a
+ * right-padded 0/1 prefix per row (PaddingDirection::Right, :85). seq_len <=
+ * max_position_embeddings. Padded positions are never computed (they cannot reach the output,
+ * SURVEY.md section 3.4). out: [batch, hidden] f32 row-major. batch == 0 is OK and writes nothing
+ * (empty in => empty out, :135-137). Blocks until `out` is complete. */
+int32_t b200_embed_forward(b200_embed* h, const uint32_t* input_ids, const uint32_t* attention_mask,
+                           const uint32_t* token_type_ids, int32_t batch, int32_t seq_len, uint32_t flags,
+                           float* out);
+
+/* Packed variant for callers that already dropped the padding: ids/type ids of all sentences back
+ * to back, cu_seqlens[batch+1] exclusive prefix sums (cu_seqlens[batch] == total_tokens). */
+int32_t b200_embed_forward_varlen(b200_embed* h, const uint32_t* ids_packed, const uint32_t* type_ids_packed,
+                                  const int32_t* cu_seqlens, int32_t batch, int32_t total_tokens,
+                                  int32_t max_seqlen, uint32_t flags, float* out);
+
+/* Asynchronous pair for the ingest pipeline (main.rs:360-393 spawns one task per message): submit
+ * returns a ticket at once; the buffers must stay valid and (for overlap) pinned until
+ * b200_embed_wait(ticket) returns. Same semantics as b200_embed_forward otherwise. */
+int32_t b200_embed_submit(b200_embed* h, const uint32_t* input_ids, const uint32_t* attention_mask,
+                          const uint32_t* token_type_ids, int32_t batch, int32_t seq_len, uint32_t flags,
+                          float* out, int64_t* ticket);
+int32_t b200_embed_wait(b200_embed* h, int64_t ticket);
+
+/* Same computation with all four buffers already resident in device memory (replaces the
+ * candle-on-CUDA tensors of :189-198 when the caller keeps data on the GPU). Enqueues on `stream`
+ * (a cudaStream_t, NULL = the handle's own stream) and returns after enqueueing when stream is
+ * non-NULL; input errors are reported by the next synchronising call. */
+int32_t b200_embed_forward_device(b200_embed* h, const uint32_t* device_ids, const uint32_t* device_mask,
+                                  const uint32_t* device_type_ids, int32_t batch, int32_t seq_len,
+                                  uint32_t flags, float* device_out, void* stream);
+
+/* Pinned host memory for the submit/wait pipeline (cudaHostAlloc / cudaFreeHost). */
+int32_t b200_embed_host_alloc(size_t bytes, void** out);
+void b200_embed_host_free(void* p);
+
+/* -- introspection ---------------------------------------------------------------------------------
+ * Writes the f32 master weights as safetensors (HF names), so a checker can load exactly the
+ * weights the handle computes with (replaces nothing; VarBuilder is read-only, :111). */
+int32_t b200_embed_export_safetensors(const b200_embed* h, const char* path);
+/* Number of kernels this handle has launched so far. */
+int64_t b200_embed_kernel_launches(const b200_embed* h);
+
+/* Per-kernel device timing. While enabled, each forward records CUDA events around every kernel
+ * on its launching stream and adds them to per-kind totals (kinds below). Off by default. */
+#define B200_EMBED_KIND_LENGTHS 0   /* mask -> lengths -> cu_seqlens */
+#define B200_EMBED_KIND_EMBED_LN 1  /* K1 gather + LayerNorm            (bert.rs BertEmbeddings::forward) */
+#define B200_EMBED_KIND_GEMM_QKV 2  /* K2 fused Q/K/V projection        (BertSelfAttention::forward) */
+#define B200_EMBED_KIND_ATTENTION 3 /* K3 varlen flash attention */
+#define B200_EMBED_KIND_GEMM_AO 4   /* K2 attention.output.dense (+res+LN fused when it fits) (BertSelfOutput) */
+#define B200_EMBED_KIND_GEMM_FFN1 5 /* K2 intermediate.dense + GELU     (BertIntermediate) */
+#define B200_EMBED_KIND_GEMM_FFN2 6 /* K2 output.dense (+res+LN fused)  (BertOutput) */
+#define B200_EMBED_KIND_ADD_LN 7    /* K4 residual + LayerNorm when not fused */
+#define B200_EMBED_KIND_POOL 8      /* K5 masked mean-pool (+L2)        (embedding_generator.rs:201-207) */
+#define B200_EMBED_NUM_KINDS 9
+typedef struct b200_embed_kind_stats {
+    double total_ms;  /* sum of event-timed durations */
+    int64_t launches;
+} b200_embed_kind_stats;
+int32_t b200_embed_profile_enable(b200_embed* h, int32_t on);
+int32_t b200_embed_profile_read(b200_embed* h, b200_embed_kind_stats* out /* [B200_EMBED_NUM_KINDS] */,
+                                int32_t reset);
+
+/* -- single kernels on device pointers (parity tests and roofline runs) ---------------------------
+ * All pointers are device pointers; `stream` is a cudaStream_t (NULL = default stream). dtype:
+ * 0 = bf16 activations / tensor-core GEMM, 1 = fp32 validation kernels. Row counts are tokens. */
+
+/* K1. out[t,:] = LN(word[ids[t]] + type[tt[t]] + pos[position of t]) for the packed tokens of
+ * `batch` sentences; cu_seqlens int32[batch+1] on device. (bert.rs BertEmbeddings::forward) */
+int32_t b200_op_embed_layernorm(b200_embed* h, const uint32_t* ids_packed, const uint32_t* type_ids_packed,
+                                const int32_t* cu_seqlens, int32_t batch, int32_t total_tokens, int32_t dtype,
+                                void* out, void* stream);
+/* K2. y = epilogue(x . W^T + b) with the weights of encoder layer `layer`:
+ * which = 0 QKV (N=3H), 1 attention.output.dense (+ residual + LayerNorm), 2 intermediate.dense (+ act),
+ * 3 output.dense (+ residual + LayerNorm). residual is read only for which = 1, 3. */
+int32_t b200_op_linear(b200_embed* h, int32_t layer, int32_t which, const void* x, const void* residual,
+                       int32_t rows, int32_t dtype, void* y, void* stream);
+/* K3. ctx = softmax(q k^T / sqrt(d)) v per sentence and head over packed qkv [rows, 3H]. */
+int32_t b200_op_attention(b200_embed* h, const void* qkv, const int32_t* cu_seqlens, int32_t batch,
+                          int32_t max_seqlen, int32_t dtype, void* ctx, void* stream);
+/* K4. out = LN(y + residual) * gamma + beta with the LayerNorm of (layer, which = 1 or 3).
+ * y is fp32 when dtype = 0 came from an unfused GEMM (y_is_f32 != 0). */
+int32_t b200_op_add_layernorm(b200_embed* h, int32_t layer, int32_t which, const void* y, int32_t y_is_f32,
+                              const void* residual, int32_t rows, int32_t dtype, void* out, void* stream);
+/* K5. out[b,:] = sum_j hidden[cu[b]+j,:] / (len_b + 1e-9) [then L2 normalise]. out f32 [batch,H]. */
+int32_t b200_op_mean_pool(b200_embed* h, const void* hidden, const int32_t* cu_seqlens, int32_t batch,
+                          int32_t dtype, int32_t normalize, float* out, void* stream);
+/* Generic bf16 tensor-core GEMM used by K2, exposed for shape sweeps: C[M,N] = A[M,K] . B[N,K]^T + bias,
+ * bf16 in, fp32 accumulate, bf16 out. N % 128 == 0, K % 8 == 0. act: -1 none, else B200_EMBED_ACT_*. */
+int32_t b200_op_gemm_bf16(const void* a, const void* b, const float* bias, int32_t m, int32_t n, int32_t k,
+                          int32_t act, int32_t block_n, void* c, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_EMBED_H_ */
