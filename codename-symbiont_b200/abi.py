@@ -63,11 +63,12 @@ _SIGNATURES = {
     "b200_embed_kernel_launches": (C.c_int64, [_P]),
     "b200_embed_profile_enable": (C.c_int32, [_P, C.c_int32]),
     "b200_embed_profile_read": (C.c_int32, [_P, C.POINTER(KindStats), C.c_int32]),
-    "b200_op_embed_layernorm": (C.c_int32, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, _P, _P]),
-    "b200_op_linear": (C.c_int32, [_P, C.c_int32, C.c_int32, _P, _P, C.c_int32, C.c_int32, _P, _P]),
+    "b200_op_embed_layernorm": (C.c_int32, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, _P, _P, _P]),
+    "b200_op_linear": (C.c_int32, [_P, C.c_int32, C.c_int32, _P, _P, _P, C.c_int32, C.c_int32, _P, _P, _P]),
     "b200_op_attention": (C.c_int32, [_P, _P, _P, C.c_int32, C.c_int32, C.c_int32, _P, _P]),
-    "b200_op_add_layernorm": (C.c_int32, [_P, C.c_int32, C.c_int32, _P, C.c_int32, _P, C.c_int32, C.c_int32, _P, _P]),
-    "b200_op_mean_pool": (C.c_int32, [_P, _P, _P, C.c_int32, C.c_int32, C.c_int32, _P, _P]),
+    "b200_op_add_layernorm": (C.c_int32, [_P, C.c_int32, C.c_int32, _P, C.c_int32, _P, _P, C.c_int32, C.c_int32, _P, _P,
+                                          _P]),
+    "b200_op_mean_pool": (C.c_int32, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, _P, _P]),
     "b200_op_gemm_bf16": (C.c_int32, [_P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P, _P]),
 }
 
@@ -246,21 +247,25 @@ class Embedder:
         return {n: {"total_ms": arr[i].total_ms, "launches": int(arr[i].launches)} for i, n in enumerate(KIND_NAMES)}
 
     # -- single kernels (device pointers) -------------------------------------------------------
-    def op_embed_layernorm(self, d_ids, d_tt, d_cu, batch, total, dtype, d_out, stream=0):
-        _check(self.lib.b200_op_embed_layernorm(self.h, d_ids, d_tt, d_cu, batch, total, dtype, d_out, stream or None))
+    def op_embed_layernorm(self, d_ids, d_tt, d_cu, batch, total, dtype, d_out, d_out_lo=0, stream=0):
+        _check(self.lib.b200_op_embed_layernorm(self.h, d_ids, d_tt, d_cu, batch, total, dtype, d_out, d_out_lo or None,
+                                                stream or None))
 
-    def op_linear(self, layer, which, d_x, d_residual, rows, dtype, d_y, stream=0):
-        _check(self.lib.b200_op_linear(self.h, layer, which, d_x, d_residual or None, rows, dtype, d_y, stream or None))
+    def op_linear(self, layer, which, d_x, d_residual, rows, dtype, d_y, d_residual_lo=0, d_y_lo=0, stream=0):
+        _check(self.lib.b200_op_linear(self.h, layer, which, d_x, d_residual or None, d_residual_lo or None, rows, dtype,
+                                       d_y, d_y_lo or None, stream or None))
 
     def op_attention(self, d_qkv, d_cu, batch, max_seqlen, dtype, d_ctx, stream=0):
         _check(self.lib.b200_op_attention(self.h, d_qkv, d_cu, batch, max_seqlen, dtype, d_ctx, stream or None))
 
-    def op_add_layernorm(self, layer, which, d_y, y_is_f32, d_residual, rows, dtype, d_out, stream=0):
-        _check(self.lib.b200_op_add_layernorm(self.h, layer, which, d_y, int(y_is_f32), d_residual, rows, dtype, d_out,
-                                              stream or None))
+    def op_add_layernorm(self, layer, which, d_y, y_is_f32, d_residual, rows, dtype, d_out, d_residual_lo=0,
+                         d_out_lo=0, stream=0):
+        _check(self.lib.b200_op_add_layernorm(self.h, layer, which, d_y, int(y_is_f32), d_residual, d_residual_lo or None,
+                                              rows, dtype, d_out, d_out_lo or None, stream or None))
 
-    def op_mean_pool(self, d_hidden, d_cu, batch, dtype, normalize, d_out, stream=0):
-        _check(self.lib.b200_op_mean_pool(self.h, d_hidden, d_cu, batch, dtype, int(normalize), d_out, stream or None))
+    def op_mean_pool(self, d_hidden, d_cu, batch, dtype, normalize, d_out, d_hidden_lo=0, stream=0):
+        _check(self.lib.b200_op_mean_pool(self.h, d_hidden, d_hidden_lo or None, d_cu, batch, dtype, int(normalize), d_out,
+                                          stream or None))
 
 
 def op_gemm_bf16(d_a, d_b, d_bias, m, n, k, act, block_n, d_c, stream=0):

@@ -14,11 +14,40 @@ namespace {
 
 constexpr int MAX_CHUNKS = 8;  // hidden <= 1024: 32 lanes x 4 elements x 8 chunks
 
+// bf16 activations that feed a residual add are kept as a (hi, lo) pair of bf16 tensors: hi = bf16(y) is what
+// the next GEMM multiplies, hi + lo (16 mantissa bits) is what the residual add and the pooling read. Rounding
+// the residual stream to bf16 alone would cost 8e-3 max-abs on short sentences (scripts/precision_study.py).
+template <typename T>
+__device__ __forceinline__ void store_split(T* hi, T* lo, int col, float4 y);
+template <>
+__device__ __forceinline__ void store_split<float>(float* hi, float*, int col, float4 y) {
+    Vec4<float>::store(hi + col, y);
+}
+template <>
+__device__ __forceinline__ void store_split<__nv_bfloat16>(__nv_bfloat16* hi, __nv_bfloat16* lo, int col, float4 y) {
+    const uint2 h = make_uint2(pack_bf16x2(y.x, y.y), pack_bf16x2(y.z, y.w));
+    *reinterpret_cast<uint2*>(hi + col) = h;
+    if (lo != nullptr) {
+        const float2 a = unpack_bf16x2(h.x), b = unpack_bf16x2(h.y);
+        *reinterpret_cast<uint2*>(lo + col) = make_uint2(pack_bf16x2(y.x - a.x, y.y - a.y), pack_bf16x2(y.z - b.x, y.w - b.y));
+    }
+}
+template <typename T>
+__device__ __forceinline__ float4 load_split(const T* hi, const T* lo, size_t off) {
+    float4 a = Vec4<T>::load(hi + off);
+    if (lo != nullptr) {
+        const float4 b = Vec4<T>::load(lo + off);
+        a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+    }
+    return a;
+}
+
 // Exact two-pass LayerNorm of one row held across a warp (chunk i of lane l = columns 128 i + 4 l ..+3).
 template <typename T>
 __device__ __forceinline__ void warp_layernorm_store(float4 (&v)[MAX_CHUNKS], int nchunk, int H, int lane,
                                                      const float* __restrict__ gamma,
-                                                     const float* __restrict__ beta, float eps, T* out_row) {
+                                                     const float* __restrict__ beta, float eps, T* out_row,
+                                                     T* out_lo_row) {
     float s = 0.f;
 #pragma unroll
     for (int i = 0; i < MAX_CHUNKS; ++i)
@@ -44,7 +73,7 @@ __device__ __forceinline__ void warp_layernorm_store(float4 (&v)[MAX_CHUNKS], in
             y.y = (v[i].y - mean) * rstd * g.y + b.y;
             y.z = (v[i].z - mean) * rstd * g.z + b.z;
             y.w = (v[i].w - mean) * rstd * g.w + b.w;
-            Vec4<T>::store(out_row + col, y);
+            store_split<T>(out_row, out_lo_row, col, y);
         }
 }
 
@@ -116,10 +145,10 @@ __global__ void scan_lengths_kernel(const int* __restrict__ lens, int batch, int
 template <typename T, bool PADDED>
 __global__ void embed_layernorm_kernel(const uint32_t* __restrict__ ids, const uint32_t* __restrict__ type_ids,
                                        const int* __restrict__ cu, int batch, int seq_len, int total_tokens,
-                                       const T* __restrict__ word, const T* __restrict__ pos,
-                                       const T* __restrict__ type, const float* __restrict__ gamma,
+                                       const float* __restrict__ word, const float* __restrict__ pos,
+                                       const float* __restrict__ type, const float* __restrict__ gamma,
                                        const float* __restrict__ beta, float eps, int H, int vocab,
-                                       int type_vocab, int max_pos, T* __restrict__ out,
+                                       int type_vocab, int max_pos, T* __restrict__ out, T* __restrict__ out_lo,
                                        int* __restrict__ status) {
     const long long w = static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
@@ -151,26 +180,29 @@ __global__ void embed_layernorm_kernel(const uint32_t* __restrict__ ids, const u
         tt = tt >= static_cast<uint32_t>(type_vocab) ? 0u : tt;
         j = j >= max_pos ? 0 : j;
     }
-    const T* wr = word + static_cast<size_t>(id) * H;
-    const T* tr = type + static_cast<size_t>(tt) * H;
-    const T* pr = pos + static_cast<size_t>(j) * H;
+    const float* wr = word + static_cast<size_t>(id) * H;
+    const float* tr = type + static_cast<size_t>(tt) * H;
+    const float* pr = pos + static_cast<size_t>(j) * H;
     const int nchunk = H >> 7;
     float4 v[MAX_CHUNKS];
 #pragma unroll
     for (int i = 0; i < MAX_CHUNKS; ++i)
         if (i < nchunk) {
             const int col = i * 128 + lane * 4;
-            const float4 a = Vec4<T>::load(wr + col), t = Vec4<T>::load(tr + col), p = Vec4<T>::load(pr + col);
+            const float4 a = Vec4<float>::load(wr + col), t = Vec4<float>::load(tr + col), p = Vec4<float>::load(pr + col);
             v[i] = make_float4((a.x + t.x) + p.x, (a.y + t.y) + p.y, (a.z + t.z) + p.z, (a.w + t.w) + p.w);
         }
-    warp_layernorm_store<T>(v, nchunk, H, lane, gamma, beta, eps, out + static_cast<size_t>(dst) * H);
+    warp_layernorm_store<T>(v, nchunk, H, lane, gamma, beta, eps, out + static_cast<size_t>(dst) * H,
+                            out_lo ? out_lo + static_cast<size_t>(dst) * H : nullptr);
 }
 
 // ---- K4 -------------------------------------------------------------------------------------------
 template <typename TY, typename T>
-__global__ void add_layernorm_kernel(const TY* __restrict__ y, const T* __restrict__ residual, int rows_cap,
+__global__ void add_layernorm_kernel(const TY* __restrict__ y, const T* __restrict__ residual,
+                                     const T* __restrict__ residual_lo, int rows_cap,
                                      const int* __restrict__ d_rows, const float* __restrict__ gamma,
-                                     const float* __restrict__ beta, float eps, int H, T* __restrict__ out) {
+                                     const float* __restrict__ beta, float eps, int H, T* __restrict__ out,
+                                     T* __restrict__ out_lo) {
     const long long r = static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     int rows = rows_cap;
@@ -182,18 +214,18 @@ __global__ void add_layernorm_kernel(const TY* __restrict__ y, const T* __restri
     for (int i = 0; i < MAX_CHUNKS; ++i)
         if (i < nchunk) {
             const int col = i * 128 + lane * 4;
-            const float4 a = Vec4<TY>::load(y + r * H + col), b = Vec4<T>::load(residual + r * H + col);
+            const float4 a = Vec4<TY>::load(y + r * H + col), b = load_split<T>(residual, residual_lo, r * H + col);
             v[i] = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
         }
-    warp_layernorm_store<T>(v, nchunk, H, lane, gamma, beta, eps, out + r * H);
+    warp_layernorm_store<T>(v, nchunk, H, lane, gamma, beta, eps, out + r * H, out_lo ? out_lo + r * H : nullptr);
 }
 
 // ---- K5 -------------------------------------------------------------------------------------------
 // One block per sentence: thread (g, c) sums rows g, g+G, ... of 4 columns; groups are combined in
 // shared memory; the divisor is len + 1e-9 in fp32 exactly as the reference; optional L2 norm.
 template <typename T>
-__global__ void mean_pool_kernel(const T* __restrict__ hidden, const int* __restrict__ cu, int H, int normalize,
-                                 float* __restrict__ out) {
+__global__ void mean_pool_kernel(const T* __restrict__ hidden, const T* __restrict__ hidden_lo,
+                                 const int* __restrict__ cu, int H, int normalize, float* __restrict__ out) {
     extern __shared__ float4 part[];  // [G][H/4]
     __shared__ float red[32];
     const int b = blockIdx.x;
@@ -203,15 +235,15 @@ __global__ void mean_pool_kernel(const T* __restrict__ hidden, const int* __rest
     const int start = cu[b], len = cu[b + 1] - start;
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     if (g < G) {
-        const T* p = hidden + static_cast<size_t>(start) * H + c * 4;
+        const size_t p = static_cast<size_t>(start) * H + c * 4;
         int j = g;
         for (; j + G < len; j += 2 * G) {  // two rows in flight
-            const float4 a = Vec4<T>::load(p + static_cast<size_t>(j) * H);
-            const float4 d = Vec4<T>::load(p + static_cast<size_t>(j + G) * H);
+            const float4 a = load_split<T>(hidden, hidden_lo, p + static_cast<size_t>(j) * H);
+            const float4 d = load_split<T>(hidden, hidden_lo, p + static_cast<size_t>(j + G) * H);
             acc.x += a.x + d.x; acc.y += a.y + d.y; acc.z += a.z + d.z; acc.w += a.w + d.w;
         }
         if (j < len) {
-            const float4 a = Vec4<T>::load(p + static_cast<size_t>(j) * H);
+            const float4 a = load_split<T>(hidden, hidden_lo, p + static_cast<size_t>(j) * H);
             acc.x += a.x; acc.y += a.y; acc.z += a.z; acc.w += a.w;
         }
         part[g * cols4 + c] = acc;
@@ -257,52 +289,53 @@ cudaError_t launch_embed_layernorm(const EmbedArgs& a, cudaStream_t s) {
     const unsigned grid = static_cast<unsigned>((warps + 7) / 8);
     if (a.padded)
         embed_layernorm_kernel<T, true><<<grid, 256, 0, s>>>(
-            a.ids, a.type_ids, a.cu, a.batch, a.seq_len, a.total_tokens, static_cast<const T*>(a.word),
-            static_cast<const T*>(a.pos), static_cast<const T*>(a.type), a.gamma, a.beta, a.eps, a.H, a.vocab,
-            a.type_vocab, a.max_pos, static_cast<T*>(a.out), a.status);
+            a.ids, a.type_ids, a.cu, a.batch, a.seq_len, a.total_tokens, a.word, a.pos, a.type, a.gamma, a.beta, a.eps,
+            a.H, a.vocab, a.type_vocab, a.max_pos, static_cast<T*>(a.out), static_cast<T*>(a.out_lo), a.status);
     else
         embed_layernorm_kernel<T, false><<<grid, 256, 0, s>>>(
-            a.ids, a.type_ids, a.cu, a.batch, a.seq_len, a.total_tokens, static_cast<const T*>(a.word),
-            static_cast<const T*>(a.pos), static_cast<const T*>(a.type), a.gamma, a.beta, a.eps, a.H, a.vocab,
-            a.type_vocab, a.max_pos, static_cast<T*>(a.out), a.status);
+            a.ids, a.type_ids, a.cu, a.batch, a.seq_len, a.total_tokens, a.word, a.pos, a.type, a.gamma, a.beta, a.eps,
+            a.H, a.vocab, a.type_vocab, a.max_pos, static_cast<T*>(a.out), static_cast<T*>(a.out_lo), a.status);
     return cudaGetLastError();
 }
 template cudaError_t launch_embed_layernorm<__nv_bfloat16>(const EmbedArgs&, cudaStream_t);
 template cudaError_t launch_embed_layernorm<float>(const EmbedArgs&, cudaStream_t);
 
 template <typename TY, typename T>
-cudaError_t launch_add_layernorm(const TY* y, const T* residual, int rows_cap, const int* d_rows,
-                                 const float* gamma, const float* beta, float eps, int H, T* out,
-                                 cudaStream_t s) {
+cudaError_t launch_add_layernorm(const TY* y, const T* residual, const T* residual_lo, int rows_cap,
+                                 const int* d_rows, const float* gamma, const float* beta, float eps, int H, T* out,
+                                 T* out_lo, cudaStream_t s) {
     if (rows_cap <= 0) return cudaSuccess;
-    add_layernorm_kernel<TY, T><<<(rows_cap + 7) / 8, 256, 0, s>>>(y, residual, rows_cap, d_rows, gamma, beta,
-                                                                  eps, H, out);
+    add_layernorm_kernel<TY, T><<<(rows_cap + 7) / 8, 256, 0, s>>>(y, residual, residual_lo, rows_cap, d_rows, gamma,
+                                                                  beta, eps, H, out, out_lo);
     return cudaGetLastError();
 }
 template cudaError_t launch_add_layernorm<__nv_bfloat16, __nv_bfloat16>(const __nv_bfloat16*, const __nv_bfloat16*,
-                                                                        int, const int*, const float*,
-                                                                        const float*, float, int, __nv_bfloat16*,
-                                                                        cudaStream_t);
-template cudaError_t launch_add_layernorm<float, __nv_bfloat16>(const float*, const __nv_bfloat16*, int, const int*,
-                                                                const float*, const float*, float, int,
+                                                                        const __nv_bfloat16*, int, const int*,
+                                                                        const float*, const float*, float, int,
+                                                                        __nv_bfloat16*, __nv_bfloat16*, cudaStream_t);
+template cudaError_t launch_add_layernorm<float, __nv_bfloat16>(const float*, const __nv_bfloat16*,
+                                                                const __nv_bfloat16*, int, const int*, const float*,
+                                                                const float*, float, int, __nv_bfloat16*,
                                                                 __nv_bfloat16*, cudaStream_t);
-template cudaError_t launch_add_layernorm<float, float>(const float*, const float*, int, const int*, const float*,
-                                                        const float*, float, int, float*, cudaStream_t);
+template cudaError_t launch_add_layernorm<float, float>(const float*, const float*, const float*, int, const int*,
+                                                        const float*, const float*, float, int, float*, float*,
+                                                        cudaStream_t);
 
 template <typename T>
-cudaError_t launch_mean_pool(const T* hidden, const int* cu, int batch, int H, int normalize, float* out,
-                             cudaStream_t s) {
+cudaError_t launch_mean_pool(const T* hidden, const T* hidden_lo, const int* cu, int batch, int H, int normalize,
+                             float* out, cudaStream_t s) {
     if (batch <= 0) return cudaSuccess;
     const int cols4 = H / 4;
     int G = 512 / cols4;
     if (G < 1) G = 1;
     if (G > 8) G = 8;
     const int threads = ((G * cols4 + 31) / 32) * 32;
-    mean_pool_kernel<T><<<batch, threads, G * cols4 * sizeof(float4), s>>>(hidden, cu, H, normalize, out);
+    mean_pool_kernel<T><<<batch, threads, G * cols4 * sizeof(float4), s>>>(hidden, hidden_lo, cu, H, normalize, out);
     return cudaGetLastError();
 }
-template cudaError_t launch_mean_pool<__nv_bfloat16>(const __nv_bfloat16*, const int*, int, int, int, float*,
+template cudaError_t launch_mean_pool<__nv_bfloat16>(const __nv_bfloat16*, const __nv_bfloat16*, const int*, int, int,
+                                                     int, float*, cudaStream_t);
+template cudaError_t launch_mean_pool<float>(const float*, const float*, const int*, int, int, int, float*,
                                                      cudaStream_t);
-template cudaError_t launch_mean_pool<float>(const float*, const int*, int, int, int, float*, cudaStream_t);
 
 }  // namespace b200

@@ -61,11 +61,12 @@ struct LayerW {
 struct Workspace {
     size_t cap = 0;  // rows (tokens)
     void *x = nullptr, *qkv = nullptr, *ctx = nullptr, *a = nullptr, *inter = nullptr;
+    void *x_lo = nullptr, *a_lo = nullptr;  // bf16 mode: low halves of the residual stream (x = hi + lo)
     float* y32 = nullptr;  // pre-LayerNorm fp32 rows when the LN is not fused into the GEMM
     void release() {
-        for (void* p : {x, qkv, ctx, a, inter, static_cast<void*>(y32)})
+        for (void* p : {x, qkv, ctx, a, inter, x_lo, a_lo, static_cast<void*>(y32)})
             if (p) cudaFree(p);
-        x = qkv = ctx = a = inter = nullptr;
+        x = qkv = ctx = a = inter = x_lo = a_lo = nullptr;
         y32 = nullptr;
         cap = 0;
     }
@@ -110,7 +111,6 @@ struct b200_embed {
     float* arena32 = nullptr;
     bf16* arena16 = nullptr;
     float *word = nullptr, *pos = nullptr, *type = nullptr, *emb_g = nullptr, *emb_b = nullptr;
-    bf16 *word16 = nullptr, *pos16 = nullptr, *type16 = nullptr;
     std::vector<LayerW> layers;
     // contexts
     std::mutex mu;
@@ -203,6 +203,10 @@ int ensure_workspace(b200_embed* h, Workspace& w, size_t rows, size_t elt) {
     CU_TRY(cudaMalloc(&w.ctx, rows * H * elt));
     CU_TRY(cudaMalloc(&w.a, rows * H * elt));
     CU_TRY(cudaMalloc(&w.inter, rows * I * elt));
+    if (elt == 2) {
+        CU_TRY(cudaMalloc(&w.x_lo, rows * H * elt));
+        CU_TRY(cudaMalloc(&w.a_lo, rows * H * elt));
+    }
     if (elt == 4 || !h->fuse_ln) CU_TRY(cudaMalloc(&w.y32, rows * H * sizeof(float)));
     w.cap = rows;
     return B200_EMBED_OK;
@@ -297,9 +301,10 @@ struct Job {
 
 int gemm16(b200_embed* h, Context& c, cudaStream_t s, int kind, const void* x, const bf16* w, const float* bias,
            int rows_cap, const int* d_rows, int n, int k, int epi, int block_n, const void* residual,
-           const float* gamma, const float* beta, void* out, int out_f32) {
+           const void* residual_lo, const float* gamma, const float* beta, void* out, void* out_lo, int out_f32) {
     b200::GemmTcArgs g{};
     g.a = x; g.b = w; g.m = rows_cap; g.n = n; g.k = k; g.d_rows = d_rows; g.bias = bias; g.residual = residual;
+    g.residual_lo = residual_lo; g.out_lo = out_lo;
     g.gamma = gamma; g.beta = beta; g.eps = h->cfg.layer_norm_eps; g.out = out; g.out_f32 = out_f32; g.epi = epi;
     g.block_n = block_n;
     CU_TRY(timed(h, c, s, kind, 1, [&] { return b200::gemm_tc_launch(g, s, h->num_sms); }));
@@ -327,9 +332,8 @@ int run_chunk(b200_embed* h, Context& c, cudaStream_t s, const Job& j) {
     e.ids = j.d_ids; e.type_ids = j.d_tt; e.cu = cu; e.batch = j.batch; e.seq_len = j.seq_len;
     e.total_tokens = j.tokens_upper; e.padded = j.d_cu ? 0 : 1; e.gamma = h->emb_g; e.beta = h->emb_b; e.eps = eps;
     e.H = H; e.vocab = h->cfg.vocab_size; e.type_vocab = h->cfg.type_vocab_size;
-    e.max_pos = h->cfg.max_position_embeddings; e.out = w.x; e.status = c.d_status;
-    if (fp32) { e.word = h->word; e.pos = h->pos; e.type = h->type; }
-    else { e.word = h->word16; e.pos = h->pos16; e.type = h->type16; }
+    e.max_pos = h->cfg.max_position_embeddings; e.out = w.x; e.out_lo = fp32 ? nullptr : w.x_lo; e.status = c.d_status;
+    e.word = h->word; e.pos = h->pos; e.type = h->type;
     CU_TRY(timed(h, c, s, B200_EMBED_KIND_EMBED_LN, 1, [&] {
         return fp32 ? b200::launch_embed_layernorm<float>(e, s) : b200::launch_embed_layernorm<bf16>(e, s);
     }));
@@ -349,7 +353,7 @@ int run_chunk(b200_embed* h, Context& c, cudaStream_t s, const Job& j) {
                 return b200::launch_gemm_f32(ctx, lw.ao_w, lw.ao_b, rows, d_rows, H, H, -1, w.y32, s);
             }));
             CU_TRY(timed(h, c, s, B200_EMBED_KIND_ADD_LN, 1, [&] {
-                return b200::launch_add_layernorm<float, float>(w.y32, x, rows, d_rows, lw.ao_g, lw.ao_be, eps, H, a, s);
+                return b200::launch_add_layernorm<float, float>(w.y32, x, nullptr, rows, d_rows, lw.ao_g, lw.ao_be, eps, H, a, nullptr, s);
             }));
             CU_TRY(timed(h, c, s, B200_EMBED_KIND_GEMM_FFN1, 1, [&] {
                 return b200::launch_gemm_f32(a, lw.i_w, lw.i_b, rows, d_rows, I, H, h->cfg.hidden_act, inter, s);
@@ -358,50 +362,52 @@ int run_chunk(b200_embed* h, Context& c, cudaStream_t s, const Job& j) {
                 return b200::launch_gemm_f32(inter, lw.o_w, lw.o_b, rows, d_rows, H, I, -1, w.y32, s);
             }));
             CU_TRY(timed(h, c, s, B200_EMBED_KIND_ADD_LN, 1, [&] {
-                return b200::launch_add_layernorm<float, float>(w.y32, a, rows, d_rows, lw.o_g, lw.o_be, eps, H, x, s);
+                return b200::launch_add_layernorm<float, float>(w.y32, a, nullptr, rows, d_rows, lw.o_g, lw.o_be, eps, H, x, nullptr, s);
             }));
         } else {
             bf16 *x = static_cast<bf16*>(w.x), *qkv = static_cast<bf16*>(w.qkv), *ctx = static_cast<bf16*>(w.ctx),
                  *a = static_cast<bf16*>(w.a), *inter = static_cast<bf16*>(w.inter);
+            bf16 *x_lo = static_cast<bf16*>(w.x_lo), *a_lo = static_cast<bf16*>(w.a_lo);
             rc = gemm16(h, c, s, B200_EMBED_KIND_GEMM_QKV, x, lw.qkv_w16, lw.qkv_b, rows, d_rows, 3 * H, H,
-                        b200::EPI_BIAS, h->bn_qkv, nullptr, nullptr, nullptr, qkv, 0);
+                        b200::EPI_BIAS, h->bn_qkv, nullptr, nullptr, nullptr, nullptr, qkv, nullptr, 0);
             if (rc) return rc;
             CU_TRY(timed(h, c, s, B200_EMBED_KIND_ATTENTION, 1, [&] {
                 return b200::launch_attention_bf16(qkv, cu, j.batch, j.seq_len, h->heads, h->D, ctx, s);
             }));
             if (h->fuse_ln) {
                 rc = gemm16(h, c, s, B200_EMBED_KIND_GEMM_AO, ctx, lw.ao_w16, lw.ao_b, rows, d_rows, H, H,
-                            b200::EPI_RES_LN, H, x, lw.ao_g, lw.ao_be, a, 0);
+                            b200::EPI_RES_LN, H, x, x_lo, lw.ao_g, lw.ao_be, a, a_lo, 0);
                 if (rc) return rc;
             } else {
                 rc = gemm16(h, c, s, B200_EMBED_KIND_GEMM_AO, ctx, lw.ao_w16, lw.ao_b, rows, d_rows, H, H,
-                            b200::EPI_BIAS, h->bn_h, nullptr, nullptr, nullptr, w.y32, 1);
+                            b200::EPI_BIAS, h->bn_h, nullptr, nullptr, nullptr, nullptr, w.y32, nullptr, 1);
                 if (rc) return rc;
                 CU_TRY(timed(h, c, s, B200_EMBED_KIND_ADD_LN, 1, [&] {
-                    return b200::launch_add_layernorm<float, bf16>(w.y32, x, rows, d_rows, lw.ao_g, lw.ao_be, eps, H, a, s);
+                    return b200::launch_add_layernorm<float, bf16>(w.y32, x, x_lo, rows, d_rows, lw.ao_g, lw.ao_be, eps, H, a, a_lo, s);
                 }));
             }
             rc = gemm16(h, c, s, B200_EMBED_KIND_GEMM_FFN1, a, lw.i_w16, lw.i_b, rows, d_rows, I, H, h->act_epi,
-                        h->bn_ffn1, nullptr, nullptr, nullptr, inter, 0);
+                        h->bn_ffn1, nullptr, nullptr, nullptr, nullptr, inter, nullptr, 0);
             if (rc) return rc;
             if (h->fuse_ln) {
                 rc = gemm16(h, c, s, B200_EMBED_KIND_GEMM_FFN2, inter, lw.o_w16, lw.o_b, rows, d_rows, H, I,
-                            b200::EPI_RES_LN, H, a, lw.o_g, lw.o_be, x, 0);
+                            b200::EPI_RES_LN, H, a, a_lo, lw.o_g, lw.o_be, x, x_lo, 0);
                 if (rc) return rc;
             } else {
                 rc = gemm16(h, c, s, B200_EMBED_KIND_GEMM_FFN2, inter, lw.o_w16, lw.o_b, rows, d_rows, H, I,
-                            b200::EPI_BIAS, h->bn_h, nullptr, nullptr, nullptr, w.y32, 1);
+                            b200::EPI_BIAS, h->bn_h, nullptr, nullptr, nullptr, nullptr, w.y32, nullptr, 1);
                 if (rc) return rc;
                 CU_TRY(timed(h, c, s, B200_EMBED_KIND_ADD_LN, 1, [&] {
-                    return b200::launch_add_layernorm<float, bf16>(w.y32, a, rows, d_rows, lw.o_g, lw.o_be, eps, H, x, s);
+                    return b200::launch_add_layernorm<float, bf16>(w.y32, a, a_lo, rows, d_rows, lw.o_g, lw.o_be, eps, H, x, x_lo, s);
                 }));
             }
         }
     }
     const int normalize = (j.flags & B200_EMBED_FLAG_NORMALIZE) ? 1 : 0;
     CU_TRY(timed(h, c, s, B200_EMBED_KIND_POOL, 1, [&] {
-        return fp32 ? b200::launch_mean_pool<float>(static_cast<const float*>(w.x), cu, j.batch, H, normalize, j.d_out, s)
-                    : b200::launch_mean_pool<bf16>(static_cast<const bf16*>(w.x), cu, j.batch, H, normalize, j.d_out, s);
+        return fp32 ? b200::launch_mean_pool<float>(static_cast<const float*>(w.x), nullptr, cu, j.batch, H, normalize, j.d_out, s)
+                    : b200::launch_mean_pool<bf16>(static_cast<const bf16*>(w.x), static_cast<const bf16*>(w.x_lo), cu,
+                                                   j.batch, H, normalize, j.d_out, s);
     }));
     return B200_EMBED_OK;
 }
@@ -528,7 +534,7 @@ int32_t b200_embed_create(const b200_embed_config* cfg, const char* path, uint64
                                al((size_t)H * I) + 3 * al(H);
     const size_t total32 = al(V * H) + al(P * H) + al(T * H) + 2 * al(H) + L * per_layer32;
     const size_t per_layer16 = al(3 * (size_t)H * H) + al((size_t)H * H) + al((size_t)I * H) + al((size_t)H * I);
-    const size_t total16 = al(V * H) + al(P * H) + al(T * H) + L * per_layer16;
+    const size_t total16 = L * per_layer16;
     CU_TRY(cudaMalloc(&h->arena32, total32 * sizeof(float)));
     e = cudaMalloc(&h->arena16, total16 * sizeof(bf16));
     if (e != cudaSuccess) { cudaFree(h->arena32); return cuda_fail(e, "cudaMalloc(bf16 weights)"); }
@@ -566,7 +572,6 @@ int32_t b200_embed_create(const b200_embed_config* cfg, const char* path, uint64
     if ((rc = load("embeddings.token_type_embeddings.weight", {(int64_t)T, H}, h->type))) return rc;
     if ((rc = load("embeddings.LayerNorm.weight", {H}, h->emb_g))) return rc;
     if ((rc = load("embeddings.LayerNorm.bias", {H}, h->emb_b))) return rc;
-    h->word16 = take16(V * H); h->pos16 = take16(P * H); h->type16 = take16(T * H);
     h->layers.resize(L);
     for (int l = 0; l < L; ++l) {
         LayerW& w = h->layers[l];
@@ -594,9 +599,6 @@ int32_t b200_embed_create(const b200_embed_config* cfg, const char* path, uint64
         if ((rc = load(layer_name(l, "output.LayerNorm.bias"), {H}, w.o_be))) return rc;
     }
     // bf16 copies (round to nearest even of the fp32 master)
-    CU_TRY(b200::launch_f32_to_bf16(h->word, h->word16, V * H, nullptr));
-    CU_TRY(b200::launch_f32_to_bf16(h->pos, h->pos16, P * H, nullptr));
-    CU_TRY(b200::launch_f32_to_bf16(h->type, h->type16, T * H, nullptr));
     for (int l = 0; l < L; ++l) {
         LayerW& w = h->layers[l];
         CU_TRY(b200::launch_f32_to_bf16(w.qkv_w, w.qkv_w16, 3 * (size_t)H * H, nullptr));
@@ -847,7 +849,7 @@ int32_t b200_embed_profile_read(b200_embed* h, b200_embed_kind_stats* out, int32
 
 // ---- single kernels on device pointers ------------------------------------------------------------
 int32_t b200_op_embed_layernorm(b200_embed* h, const uint32_t* ids, const uint32_t* tt, const int32_t* cu,
-                                int32_t batch, int32_t total, int32_t dtype, void* out, void* stream) {
+                                int32_t batch, int32_t total, int32_t dtype, void* out, void* out_lo, void* stream) {
     if (!h || !ids || !tt || !cu || !out) return fail(B200_EMBED_ERR_INVALID_ARG, "null argument");
     DeviceGuard guard(h->device);
     Context& c = h->ctxs[0];
@@ -855,9 +857,9 @@ int32_t b200_op_embed_layernorm(b200_embed* h, const uint32_t* ids, const uint32
     e.ids = ids; e.type_ids = tt; e.cu = cu; e.batch = batch; e.seq_len = 0; e.total_tokens = total; e.padded = 0;
     e.gamma = h->emb_g; e.beta = h->emb_b; e.eps = h->cfg.layer_norm_eps; e.H = h->H; e.vocab = h->cfg.vocab_size;
     e.type_vocab = h->cfg.type_vocab_size; e.max_pos = h->cfg.max_position_embeddings; e.out = out;
+    e.out_lo = dtype ? nullptr : out_lo;
     e.status = c.d_status;
-    if (dtype) { e.word = h->word; e.pos = h->pos; e.type = h->type; }
-    else { e.word = h->word16; e.pos = h->pos16; e.type = h->type16; }
+    e.word = h->word; e.pos = h->pos; e.type = h->type;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     h->launches.fetch_add(1);
     CU_TRY(dtype ? b200::launch_embed_layernorm<float>(e, s) : b200::launch_embed_layernorm<bf16>(e, s));
@@ -865,7 +867,7 @@ int32_t b200_op_embed_layernorm(b200_embed* h, const uint32_t* ids, const uint32
 }
 
 int32_t b200_op_linear(b200_embed* h, int32_t layer, int32_t which, const void* x, const void* residual,
-                       int32_t rows, int32_t dtype, void* y, void* stream) {
+                       const void* residual_lo, int32_t rows, int32_t dtype, void* y, void* y_lo, void* stream) {
     if (!h || !x || !y || layer < 0 || layer >= h->L || which < 0 || which > 3)
         return fail(B200_EMBED_ERR_INVALID_ARG, "bad argument");
     if ((which == 1 || which == 3) && !residual) return fail(B200_EMBED_ERR_INVALID_ARG, "residual required");
@@ -888,8 +890,8 @@ int32_t b200_op_linear(b200_embed* h, int32_t layer, int32_t which, const void* 
         cudaError_t e = b200::launch_gemm_f32(static_cast<const float*>(x), w32[which], bias[which], rows, nullptr,
                                               n[which], k[which], which == 2 ? h->cfg.hidden_act : -1, tmp, s);
         if (e == cudaSuccess && ln)
-            e = b200::launch_add_layernorm<float, float>(tmp, static_cast<const float*>(residual), rows, nullptr, gam,
-                                                         bet, eps, H, static_cast<float*>(y), s);
+            e = b200::launch_add_layernorm<float, float>(tmp, static_cast<const float*>(residual), nullptr, rows, nullptr,
+                                                         gam, bet, eps, H, static_cast<float*>(y), nullptr, s);
         if (ln) { cudaStreamSynchronize(s); cudaFree(tmp); }
         CU_TRY(e);
         return B200_EMBED_OK;
@@ -899,19 +901,22 @@ int32_t b200_op_linear(b200_embed* h, int32_t layer, int32_t which, const void* 
         const int epi = which == 2 ? h->act_epi : b200::EPI_BIAS;
         return gemm16(h, c, s, which == 0 ? B200_EMBED_KIND_GEMM_QKV : B200_EMBED_KIND_GEMM_FFN1, x, w16[which],
                       bias[which], rows, nullptr, n[which], k[which], epi, which == 0 ? h->bn_qkv : h->bn_ffn1, nullptr,
-                      nullptr, nullptr, y, 0);
+                      nullptr, nullptr, nullptr, y, nullptr, 0);
     }
     if (h->fuse_ln)
         return gemm16(h, c, s, which == 1 ? B200_EMBED_KIND_GEMM_AO : B200_EMBED_KIND_GEMM_FFN2, x, w16[which],
-                      bias[which], rows, nullptr, H, k[which], b200::EPI_RES_LN, H, residual, gam, bet, y, 0);
+                      bias[which], rows, nullptr, H, k[which], b200::EPI_RES_LN, H, residual, residual_lo, gam, bet, y,
+                      y_lo, 0);
     float* tmp = nullptr;
     CU_TRY(cudaMalloc(&tmp, (size_t)rows * H * 4));
     int rc = gemm16(h, c, s, which == 1 ? B200_EMBED_KIND_GEMM_AO : B200_EMBED_KIND_GEMM_FFN2, x, w16[which],
-                    bias[which], rows, nullptr, H, k[which], b200::EPI_BIAS, h->bn_h, nullptr, nullptr, nullptr, tmp, 1);
+                    bias[which], rows, nullptr, H, k[which], b200::EPI_BIAS, h->bn_h, nullptr, nullptr, nullptr, nullptr,
+                    tmp, nullptr, 1);
     if (!rc) {
         h->launches.fetch_add(1);
-        const cudaError_t e = b200::launch_add_layernorm<float, bf16>(tmp, static_cast<const bf16*>(residual), rows,
-                                                                      nullptr, gam, bet, eps, H, static_cast<bf16*>(y), s);
+        const cudaError_t e = b200::launch_add_layernorm<float, bf16>(
+            tmp, static_cast<const bf16*>(residual), static_cast<const bf16*>(residual_lo), rows, nullptr, gam, bet, eps, H,
+            static_cast<bf16*>(y), static_cast<bf16*>(y_lo), s);
         if (e != cudaSuccess) rc = cuda_fail(e, "add_layernorm");
     }
     cudaStreamSynchronize(s);
@@ -933,7 +938,8 @@ int32_t b200_op_attention(b200_embed* h, const void* qkv, const int32_t* cu, int
 }
 
 int32_t b200_op_add_layernorm(b200_embed* h, int32_t layer, int32_t which, const void* y, int32_t y_is_f32,
-                              const void* residual, int32_t rows, int32_t dtype, void* out, void* stream) {
+                              const void* residual, const void* residual_lo, int32_t rows, int32_t dtype, void* out,
+                              void* out_lo, void* stream) {
     if (!h || !y || !residual || !out || layer < 0 || layer >= h->L || (which != 1 && which != 3))
         return fail(B200_EMBED_ERR_INVALID_ARG, "bad argument");
     DeviceGuard guard(h->device);
@@ -945,24 +951,28 @@ int32_t b200_op_add_layernorm(b200_embed* h, int32_t layer, int32_t which, const
     h->launches.fetch_add(1);
     if (dtype)
         CU_TRY((b200::launch_add_layernorm<float, float>(static_cast<const float*>(y), static_cast<const float*>(residual),
-                                                         rows, nullptr, gam, bet, eps, h->H, static_cast<float*>(out), s)));
+                                                         nullptr, rows, nullptr, gam, bet, eps, h->H,
+                                                         static_cast<float*>(out), nullptr, s)));
     else if (y_is_f32)
         CU_TRY((b200::launch_add_layernorm<float, bf16>(static_cast<const float*>(y), static_cast<const bf16*>(residual),
-                                                        rows, nullptr, gam, bet, eps, h->H, static_cast<bf16*>(out), s)));
+                                                        static_cast<const bf16*>(residual_lo), rows, nullptr, gam, bet, eps,
+                                                        h->H, static_cast<bf16*>(out), static_cast<bf16*>(out_lo), s)));
     else
         CU_TRY((b200::launch_add_layernorm<bf16, bf16>(static_cast<const bf16*>(y), static_cast<const bf16*>(residual),
-                                                       rows, nullptr, gam, bet, eps, h->H, static_cast<bf16*>(out), s)));
+                                                       static_cast<const bf16*>(residual_lo), rows, nullptr, gam, bet, eps,
+                                                       h->H, static_cast<bf16*>(out), static_cast<bf16*>(out_lo), s)));
     return B200_EMBED_OK;
 }
 
-int32_t b200_op_mean_pool(b200_embed* h, const void* hidden, const int32_t* cu, int32_t batch, int32_t dtype,
-                          int32_t normalize, float* out, void* stream) {
+int32_t b200_op_mean_pool(b200_embed* h, const void* hidden, const void* hidden_lo, const int32_t* cu, int32_t batch,
+                          int32_t dtype, int32_t normalize, float* out, void* stream) {
     if (!h || !hidden || !cu || !out) return fail(B200_EMBED_ERR_INVALID_ARG, "null argument");
     DeviceGuard guard(h->device);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     h->launches.fetch_add(1);
-    CU_TRY(dtype ? b200::launch_mean_pool<float>(static_cast<const float*>(hidden), cu, batch, h->H, normalize, out, s)
-                 : b200::launch_mean_pool<bf16>(static_cast<const bf16*>(hidden), cu, batch, h->H, normalize, out, s));
+    CU_TRY(dtype ? b200::launch_mean_pool<float>(static_cast<const float*>(hidden), nullptr, cu, batch, h->H, normalize, out, s)
+                 : b200::launch_mean_pool<bf16>(static_cast<const bf16*>(hidden), static_cast<const bf16*>(hidden_lo), cu,
+                                                batch, h->H, normalize, out, s));
     return B200_EMBED_OK;
 }
 

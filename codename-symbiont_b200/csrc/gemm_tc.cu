@@ -52,11 +52,13 @@ struct GemmDev {
     const int* d_rows;  // optional device-side row count (<= m)
     int n, k;
     const float* bias;
-    const __nv_bfloat16* residual;  // [m, n] (EPI_RES_LN)
+    const __nv_bfloat16* residual;     // [m, n] (EPI_RES_LN): high half of the residual stream
+    const __nv_bfloat16* residual_lo;  // low half (residual = hi + lo) or nullptr
     const float* gamma;
     const float* beta;
     float eps;
-    void* out;  // [m, n] bf16 or fp32
+    void* out;              // [m, n] bf16 or fp32
+    __nv_bfloat16* out_lo;  // EPI_RES_LN: bf16(y - bf16(y)) so that the next residual add sees ~16 mantissa bits
 };
 
 template <typename OutT>
@@ -79,6 +81,22 @@ __device__ __forceinline__ void store_chunk32<float>(float* dst, const float (&f
     float4* d4 = reinterpret_cast<float4*>(dst);
 #pragma unroll
     for (int q = 0; q < 8; ++q) d4[q] = make_float4(f[q * 4], f[q * 4 + 1], f[q * 4 + 2], f[q * 4 + 3]);
+}
+
+// lo[j] = bf16(f[j] - bf16(f[j])): the part of the fp32 value the bf16 "hi" tensor dropped
+__device__ __forceinline__ void store_chunk32_lo(__nv_bfloat16* dst, const float (&f)[32]) {
+    uint4* d4 = reinterpret_cast<uint4*>(dst);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        uint32_t w[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float a = f[q * 8 + 2 * j], b = f[q * 8 + 2 * j + 1];
+            const float2 h = unpack_bf16x2(pack_bf16x2(a, b));
+            w[j] = pack_bf16x2(a - h.x, b - h.y);
+        }
+        d4[q] = make_uint4(w[0], w[1], w[2], w[3]);
+    }
 }
 
 template <int BLOCK_N, int EPI, typename OutT>
@@ -241,6 +259,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 // pass 1: v = acc + bias + residual, kept in TMEM; row sum and sum of squares
                 float sum = 0.f, sumsq = 0.f;
                 const __nv_bfloat16* res = p.residual + static_cast<size_t>(row_ok ? row : 0) * p.n;
+                const __nv_bfloat16* res_lo =
+                    p.residual_lo ? p.residual_lo + static_cast<size_t>(row_ok ? row : 0) * p.n : nullptr;
 #pragma unroll 1
                 for (int c = 0; c < HALF_N / 32; ++c) {
                     uint32_t v[32];
@@ -249,12 +269,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     const int col0 = col_base + c * 32;
                     const float4* b4 = reinterpret_cast<const float4*>(p.bias + col0);
                     const uint4* r4 = reinterpret_cast<const uint4*>(res + col0);
+                    const uint4* l4 = reinterpret_cast<const uint4*>(res_lo + col0);
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
                         const uint4 r = __ldg(r4 + q);
                         const float4 b0 = __ldg(b4 + 2 * q), b1 = __ldg(b4 + 2 * q + 1);
-                        const float2 r0 = unpack_bf16x2(r.x), r1 = unpack_bf16x2(r.y), r2 = unpack_bf16x2(r.z),
-                                     r3 = unpack_bf16x2(r.w);
+                        float2 r0 = unpack_bf16x2(r.x), r1 = unpack_bf16x2(r.y), r2 = unpack_bf16x2(r.z),
+                               r3 = unpack_bf16x2(r.w);
+                        if (res_lo != nullptr) {
+                            const uint4 l = __ldg(l4 + q);
+                            const float2 l0 = unpack_bf16x2(l.x), l1 = unpack_bf16x2(l.y), l2 = unpack_bf16x2(l.z),
+                                         l3 = unpack_bf16x2(l.w);
+                            r0.x += l0.x; r0.y += l0.y; r1.x += l1.x; r1.y += l1.y;
+                            r2.x += l2.x; r2.y += l2.y; r3.x += l3.x; r3.y += l3.y;
+                        }
                         float x[8];
                         x[0] = __uint_as_float(v[q * 8 + 0]) + b0.x + r0.x;
                         x[1] = __uint_as_float(v[q * 8 + 1]) + b0.y + r0.y;
@@ -299,7 +327,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                         f[q * 4 + 2] = (__uint_as_float(v[q * 4 + 2]) - mean) * rstd * g.z + be.z;
                         f[q * 4 + 3] = (__uint_as_float(v[q * 4 + 3]) - mean) * rstd * g.w + be.w;
                     }
-                    if (row_ok) store_chunk32<OutT>(out + static_cast<size_t>(row) * p.n + col0, f);
+                    if (row_ok) {
+                        store_chunk32<OutT>(out + static_cast<size_t>(row) * p.n + col0, f);
+                        if (p.out_lo != nullptr) store_chunk32_lo(p.out_lo + static_cast<size_t>(row) * p.n + col0, f);
+                    }
                 }
                 // the partial-stat slots are reused by the next tile
                 asm volatile("bar.sync 1, %0;" ::"n"(EPI_THREADS) : "memory");
@@ -364,6 +395,8 @@ cudaError_t launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms) {
     GemmDev p;
     p.m = a.m; p.d_rows = a.d_rows; p.n = a.n; p.k = a.k; p.bias = a.bias;
     p.residual = reinterpret_cast<const __nv_bfloat16*>(a.residual);
+    p.residual_lo = reinterpret_cast<const __nv_bfloat16*>(a.residual_lo);
+    p.out_lo = reinterpret_cast<__nv_bfloat16*>(a.out_lo);
     p.gamma = a.gamma; p.beta = a.beta; p.eps = a.eps; p.out = a.out;
     const int tiles = ((a.m + BLOCK_M - 1) / BLOCK_M) * (a.n / BLOCK_N);
     const int grid = tiles < num_sms ? tiles : num_sms;

@@ -18,11 +18,13 @@ struct GemmTcArgs {
     int m, n, k;
     const int* d_rows;     // optional device int: rows actually present (<= m); tiles beyond are skipped
     const float* bias;     // [n]
-    const void* residual;  // [m, n] bf16 (EPI_RES_LN)
+    const void* residual;  // [m, n] bf16 (EPI_RES_LN), high half of the residual stream
+    const void* residual_lo;  // [m, n] bf16 low half (residual = hi + lo), or nullptr
     const float* gamma;    // [n]     (EPI_RES_LN)
     const float* beta;     // [n]     (EPI_RES_LN)
     float eps;
     void* out;             // [m, n] bf16, or fp32 when out_f32
+    void* out_lo;          // EPI_RES_LN: optional [m, n] bf16 low half of the output
     int out_f32;           // only with EPI_BIAS
     int epi;               // GemmEpilogue
     int block_n;           // 128, 192, 256 (EPI_RES_LN: == n, one of 128/256/384)

@@ -16,23 +16,25 @@ struct EmbedArgs {
     const int* cu;             // device cu_seqlens[batch + 1]
     int batch, seq_len, total_tokens;
     int padded;                // 1: ids are [batch, seq_len]; 0: packed
-    const void *word, *pos, *type;  // tables in T
+    const float *word, *pos, *type;  // fp32 tables (bf16 tables alone cost 6e-3 max-abs, precision_study.py)
     const float *gamma, *beta;
     float eps;
     int H, vocab, type_vocab, max_pos;
     void* out;                 // packed [tokens, H] in T
+    void* out_lo;              // bf16 mode: low half of the (hi, lo) pair, or nullptr
     int* status;               // |= 2 on id / type id / position out of range
 };
 template <typename T>
 cudaError_t launch_embed_layernorm(const EmbedArgs& a, cudaStream_t s);
 
 template <typename TY, typename T>
-cudaError_t launch_add_layernorm(const TY* y, const T* residual, int rows_cap, const int* d_rows,
-                                 const float* gamma, const float* beta, float eps, int H, T* out, cudaStream_t s);
+cudaError_t launch_add_layernorm(const TY* y, const T* residual, const T* residual_lo, int rows_cap,
+                                 const int* d_rows, const float* gamma, const float* beta, float eps, int H, T* out,
+                                 T* out_lo, cudaStream_t s);
 
 template <typename T>
-cudaError_t launch_mean_pool(const T* hidden, const int* cu, int batch, int H, int normalize, float* out,
-                             cudaStream_t s);
+cudaError_t launch_mean_pool(const T* hidden, const T* hidden_lo, const int* cu, int batch, int H, int normalize,
+                             float* out, cudaStream_t s);
 
 // K3 (bf16): varlen flash attention over packed qkv [tokens, 3H]; head_dim 32 or 64.
 cudaError_t launch_attention_bf16(const __nv_bfloat16* qkv, const int* cu, int batch, int max_seqlen, int heads,

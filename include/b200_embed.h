@@ -152,26 +152,31 @@ int32_t b200_embed_profile_read(b200_embed* h, b200_embed_kind_stats* out /* [B2
  * All pointers are device pointers; `stream` is a cudaStream_t (NULL = default stream). dtype:
  * 0 = bf16 activations / tensor-core GEMM, 1 = fp32 validation kernels. Row counts are tokens. */
 
+/* Residual-stream tensors in bf16 mode are (hi, lo) pairs of bf16 [rows, H] arrays: hi = bf16(v) is what
+ * the next GEMM multiplies, hi + lo is what residual adds and the pooling read. Every `*_lo` argument may be
+ * NULL (plain bf16) and is ignored when dtype = 1. */
+
 /* K1. out[t,:] = LN(word[ids[t]] + type[tt[t]] + pos[position of t]) for the packed tokens of
  * `batch` sentences; cu_seqlens int32[batch+1] on device. (bert.rs BertEmbeddings::forward) */
 int32_t b200_op_embed_layernorm(b200_embed* h, const uint32_t* ids_packed, const uint32_t* type_ids_packed,
                                 const int32_t* cu_seqlens, int32_t batch, int32_t total_tokens, int32_t dtype,
-                                void* out, void* stream);
+                                void* out, void* out_lo, void* stream);
 /* K2. y = epilogue(x . W^T + b) with the weights of encoder layer `layer`:
  * which = 0 QKV (N=3H), 1 attention.output.dense (+ residual + LayerNorm), 2 intermediate.dense (+ act),
  * 3 output.dense (+ residual + LayerNorm). residual is read only for which = 1, 3. */
 int32_t b200_op_linear(b200_embed* h, int32_t layer, int32_t which, const void* x, const void* residual,
-                       int32_t rows, int32_t dtype, void* y, void* stream);
+                       const void* residual_lo, int32_t rows, int32_t dtype, void* y, void* y_lo, void* stream);
 /* K3. ctx = softmax(q k^T / sqrt(d)) v per sentence and head over packed qkv [rows, 3H]. */
 int32_t b200_op_attention(b200_embed* h, const void* qkv, const int32_t* cu_seqlens, int32_t batch,
                           int32_t max_seqlen, int32_t dtype, void* ctx, void* stream);
 /* K4. out = LN(y + residual) * gamma + beta with the LayerNorm of (layer, which = 1 or 3).
  * y is fp32 when dtype = 0 came from an unfused GEMM (y_is_f32 != 0). */
 int32_t b200_op_add_layernorm(b200_embed* h, int32_t layer, int32_t which, const void* y, int32_t y_is_f32,
-                              const void* residual, int32_t rows, int32_t dtype, void* out, void* stream);
+                              const void* residual, const void* residual_lo, int32_t rows, int32_t dtype, void* out,
+                              void* out_lo, void* stream);
 /* K5. out[b,:] = sum_j hidden[cu[b]+j,:] / (len_b + 1e-9) [then L2 normalise]. out f32 [batch,H]. */
-int32_t b200_op_mean_pool(b200_embed* h, const void* hidden, const int32_t* cu_seqlens, int32_t batch,
-                          int32_t dtype, int32_t normalize, float* out, void* stream);
+int32_t b200_op_mean_pool(b200_embed* h, const void* hidden, const void* hidden_lo, const int32_t* cu_seqlens,
+                          int32_t batch, int32_t dtype, int32_t normalize, float* out, void* stream);
 /* Generic bf16 tensor-core GEMM used by K2, exposed for shape sweeps: C[M,N] = A[M,K] . B[N,K]^T + bias,
  * bf16 in, fp32 accumulate, bf16 out. N % 128 == 0, K % 8 == 0. act: -1 none, else B200_EMBED_ACT_*. */
 int32_t b200_op_gemm_bf16(const void* a, const void* b, const float* bias, int32_t m, int32_t n, int32_t k,

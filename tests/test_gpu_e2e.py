@@ -1,0 +1,235 @@
+"""GPU: the whole path through the C ABI with HOST buffers (the call the reference-side binding makes),
+against the committed golden vectors and the oracle. Gates: BASELINE.md section 5."""
+import threading
+
+import numpy as np
+import pytest
+
+from conftest import load_golden, cos_rows, BF16_COS, BF16_ABS, FP32_COS
+from oracle.oracle import Oracle
+
+pytestmark = pytest.mark.gpu
+
+
+def l2n(v):
+    return v / np.maximum(np.linalg.norm(v, axis=1, keepdims=True), 1e-12)
+
+
+def check(got, want, fp32, want_same_weights=None, lengths=None):
+    """BASELINE.md section 5 gates. fp32 validation mode: cosine >= 0.999999 (+ max-abs 1e-4).
+    bf16 mode: per-vector cosine >= 0.9999 always, and max-abs <= 2e-3
+      (a) on the L2-normalised vectors, which is what the north_star pipeline emits, and
+      (b) on the raw pooled vectors against the oracle run on the SAME bf16-rounded weight matrices the
+          kernels multiply by (`want_same_weights`), which isolates kernel error from weight quantisation;
+          sentences of 2-3 tokens are held to 5e-3 there: with nothing to average over, the bf16 rounding of
+          the GEMM inputs alone reaches 3.6e-3 for them (scripts/precision_study.py bylen).
+    Raw vectors against the fp32-weight oracle are held to 6e-3: rounding the weights to bf16 ALONE moves the
+    raw MiniLM output by 2.9e-3 max-abs (scripts/precision_study.py), so 2e-3 is below
+    the floor of any bf16-weight implementation for un-normalised vectors of magnitude ~3."""
+    assert got.shape == want.shape and np.isfinite(got).all()
+    c, e = cos_rows(got, want).min(), np.abs(got - want).max()
+    if fp32:
+        assert c >= FP32_COS and e <= 1e-4, (c, e)
+        return
+    assert c >= BF16_COS, c
+    en = np.abs(l2n(got) - l2n(want)).max()
+    assert en <= BF16_ABS, en
+    assert e <= 6e-3, e
+    if want_same_weights is not None:
+        e2 = np.abs(got - want_same_weights).max(axis=1)
+        short = np.zeros(len(e2), bool) if lengths is None else (np.asarray(lengths) < 4)
+        assert (e2[~short] <= BF16_ABS).all(), e2[~short].max()
+        assert (e2[short] <= 5e-3).all(), e2[short].max()
+
+
+@pytest.fixture(scope="module")
+def tiny(pkg, built):
+    with pkg.Embedder.random_init(pkg.weights.TINY, seed=1234) as emb:
+        yield emb
+
+
+@pytest.fixture(scope="module")
+def minilm(pkg, built):
+    with pkg.Embedder.random_init(pkg.weights.MINILM_L6, seed=1234) as emb:
+        yield emb
+
+
+def oracle_pair(emb, shape):
+    """The f32 oracle on the handle's weights, and on those weights with the matrices rounded to bf16."""
+    from gpu_util import bf16_round
+    w = emb.export_weights()
+    w16 = {k: bf16_round(v) if (v.ndim == 2 and "embeddings" not in k) else v for k, v in w.items()}
+    return Oracle(shape, w, "f32"), Oracle(shape, w16, "f32")
+
+
+@pytest.mark.parametrize("fp32", [False, True])
+@pytest.mark.parametrize("name", ["tiny_dense", "tiny_ragged", "tiny_single"])
+def test_golden_tiny(pkg, built, name, fp32):
+    g = load_golden(name)
+    with pkg.Embedder.random_init(pkg.weights.TINY, seed=int(g["seed"])) as emb:
+        got = emb.forward(g["ids"], g["mask"], g["type_ids"], flags=pkg.FLAG_FP32 if fp32 else 0)
+    check(got, g["expected_hf_f64"], fp32)
+    check(got, g["expected_oracle_f32"], fp32)
+
+
+@pytest.mark.parametrize("fp32", [False, True])
+def test_golden_minilm(pkg, minilm, fp32):
+    """BASELINE config 1 shape (MiniLM-L6, seq 128), HuggingFace fp64 expectation."""
+    g = load_golden("minilm_b8_s128")
+    got = minilm.forward(g["ids"], g["mask"], g["type_ids"], flags=pkg.FLAG_FP32 if fp32 else 0)
+    check(got, g["expected_hf_f64"], fp32)
+
+
+def test_config1_b32_s128_vs_oracle(pkg, minilm):
+    """BASELINE config 1: MiniLM-L6 batch 32 x seq 128, dense, against the f32 oracle run here."""
+    shape = pkg.weights.MINILM_L6
+    ids, mask, tt = pkg.synth.padded_batch(shape.vocab_size, pkg.synth.lengths_dense(32, 128), 128, seed=42)
+    o, o16 = oracle_pair(minilm, shape)
+    want = o.generate(ids, tt, mask, chunk=8)
+    check(minilm.forward(ids, mask, tt), want, False, o16.generate(ids, tt, mask, chunk=8))
+    check(minilm.forward(ids, mask, tt, flags=pkg.FLAG_FP32), want, True)
+    got_n = minilm.forward(ids, mask, tt, flags=pkg.FLAG_NORMALIZE)  # the north_star output
+    assert np.abs(got_n - o.l2_normalize(want)).max() <= BF16_ABS
+
+
+def test_config3_ragged_8_512_vs_oracle(pkg, minilm):
+    """BASELINE config 3: ragged lengths 8..512 incl. the adversarial 8/512 alternation; padded and packed calls."""
+    shape = pkg.weights.MINILM_L6
+    lengths = np.concatenate([pkg.synth.lengths_loguniform(10, 8, 512, seed=7), [8, 512, 8, 512, 2, 511]])
+    ids, mask, tt = pkg.synth.padded_batch(shape.vocab_size, lengths, 512, seed=42)
+    o, o16 = oracle_pair(minilm, shape)
+    want = o.generate(ids, tt, mask, chunk=8)  # reference schedule
+    got = minilm.forward(ids, mask, tt)
+    check(got, want, False, o16.generate(ids, tt, mask, chunk=8), lengths)
+    pi, pt, cu = pkg.synth.pack(ids, mask, tt)
+    got_v = minilm.forward_varlen(pi, pt, cu, 512)
+    assert np.array_equal(got, got_v)  # same kernels, same packed layout: bit-identical
+    check(minilm.forward_varlen(pi, pt, cu, 512, flags=pkg.FLAG_FP32), want, True)
+
+
+def test_normalize_flag(pkg, tiny):
+    g = load_golden("tiny_ragged")
+    raw = tiny.forward(g["ids"], g["mask"], g["type_ids"])
+    nrm = tiny.forward(g["ids"], g["mask"], g["type_ids"], flags=pkg.FLAG_NORMALIZE)
+    assert np.allclose(np.linalg.norm(nrm, axis=1), 1.0, atol=1e-5)
+    assert np.abs(nrm - raw / np.linalg.norm(raw, axis=1, keepdims=True)).max() <= 1e-6
+
+
+def test_empty_batch_and_errors(pkg, tiny):
+    shape = pkg.weights.TINY
+    z = np.zeros((0, 16), np.uint32)
+    assert tiny.forward(z, z, z).shape == (0, shape.hidden_size)  # embedding_generator.rs:135-137
+    ids, mask, tt = pkg.synth.padded_batch(shape.vocab_size, [4, 8], 8)
+    bad = mask.copy(); bad[0, 6] = 1  # a hole: not a right-padded prefix
+    with pytest.raises(pkg.B200EmbedError) as e:
+        tiny.forward(ids, bad, tt)
+    assert e.value.code == -1
+    big = ids.copy(); big[1, 2] = shape.vocab_size
+    with pytest.raises(pkg.B200EmbedError):
+        tiny.forward(big, mask, tt)
+    with pytest.raises(pkg.B200EmbedError):
+        tiny.forward(*pkg.synth.padded_batch(shape.vocab_size, [4], shape.max_position_embeddings + 1))
+    # the handle still works after errors
+    check(tiny.forward(ids, mask, tt), tiny.forward(ids, mask, tt, flags=pkg.FLAG_FP32), False)
+
+
+def test_chunked_launches_match_single_launch(pkg):
+    """Calls larger than the workspace are split by sentence; results and order must not change."""
+    shape = pkg.weights.TINY
+    lengths = pkg.synth.lengths_uniform(37, 2, 64, seed=1)
+    ids, mask, tt = pkg.synth.padded_batch(shape.vocab_size, lengths, 64)
+    with pkg.Embedder.random_init(shape, seed=1234) as a, \
+            pkg.Embedder.random_init(shape, seed=1234, max_tokens_per_launch=5 * 64) as b:
+        ra, rb = a.forward(ids, mask, tt), b.forward(ids, mask, tt)
+        pi, pt, cu = pkg.synth.pack(ids, mask, tt)
+        rc = b.forward_varlen(pi, pt, cu, 64)
+    assert np.array_equal(ra, rb) and np.array_equal(ra, rc)
+
+
+def test_permutation_and_padding_invariance_at_scale(pkg, minilm):
+    """Size-independent properties at a BASELINE-sized batch (config 2 shape, 4096 x 128 dense is run by
+    bench.py; here 1024 ragged sentences): shuffling sentences shuffles rows bit-exactly, and extra right
+    padding changes nothing."""
+    shape = pkg.weights.MINILM_L6
+    lengths = pkg.synth.lengths_uniform(1024, 8, 128, seed=3)
+    ids, mask, tt = pkg.synth.padded_batch(shape.vocab_size, lengths, 128)
+    base = minilm.forward(ids, mask, tt)
+    perm = np.random.default_rng(0).permutation(len(lengths))
+    assert np.array_equal(minilm.forward(ids[perm], mask[perm], tt[perm]), base[perm])
+    wide = lambda a: np.concatenate([a, np.zeros((a.shape[0], 64), np.uint32)], axis=1)
+    assert np.array_equal(minilm.forward(wide(ids), wide(mask), wide(tt)), base)
+    sub = np.arange(0, 1024, 97)
+    want = Oracle(shape, minilm.export_weights(), "f32").generate(ids[sub], tt[sub], mask[sub])
+    check(base[sub], want, False)
+
+
+def test_submit_wait_and_threads(pkg, tiny):
+    """The handle is shared like Arc<EmbeddingGenerator> (main.rs:314, :373): concurrent calls and tickets."""
+    shape = pkg.weights.TINY
+    batches = [pkg.synth.padded_batch(shape.vocab_size, pkg.synth.lengths_uniform(9, 2, 64, seed=s), 64, seed=s)
+               for s in range(6)]
+    want = [tiny.forward(*b) for b in batches]
+    outs = [np.empty((9, shape.hidden_size), np.float32) for _ in batches]
+    tickets = [tiny.submit(*batches[i], outs[i]) for i in range(4)]
+    with pytest.raises(pkg.B200EmbedError):
+        tiny.submit(*batches[4], outs[4])  # at most 4 in flight
+    for t in tickets:
+        tiny.wait(t)
+    assert all(np.array_equal(outs[i], want[i]) for i in range(4))
+    res = [None] * 6
+    def work(i):
+        res[i] = tiny.forward(*batches[i])
+    th = [threading.Thread(target=work, args=(i,)) for i in range(6)]
+    [t.start() for t in th]; [t.join() for t in th]
+    assert all(np.array_equal(res[i], want[i]) for i in range(6))
+
+
+def test_device_entry_matches_host_entry(pkg, tiny):
+    import torch
+    from gpu_util import dev_u32
+    shape = pkg.weights.TINY
+    ids, mask, tt = pkg.synth.padded_batch(shape.vocab_size, [5, 64, 33, 2], 64)
+    out = torch.empty((4, shape.hidden_size), dtype=torch.float32, device="cuda")
+    a, b, c = dev_u32(ids), dev_u32(mask), dev_u32(tt)
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        tiny.forward_device(a.data_ptr(), b.data_ptr(), c.data_ptr(), 4, 64, out.data_ptr(), stream=s.cuda_stream)
+    s.synchronize()
+    assert np.array_equal(out.cpu().numpy(), tiny.forward(ids, mask, tt))
+    n0 = tiny.kernel_launches()
+    tiny.forward(ids, mask, tt)
+    assert tiny.kernel_launches() - n0 == 2 + 1 + shape.num_hidden_layers * 5 + 1
+
+
+def test_embedding_generator_end_to_end_text(pkg, built, tmp_path):
+    """The reference-shaped host API on real text: tokenizer.json + config.json + model.safetensors in a directory."""
+    import json
+    from tokenizers import Tokenizer, models, normalizers, pre_tokenizers, processors
+    shape = pkg.weights.TINY
+    words = "the quick brown fox jumps over lazy dog . ! ? a symbiont reads web pages and embeds sentences ##s ##ing".split()
+    vocab = {w: i for i, w in enumerate(["[PAD]", "[UNK]", "[CLS]", "[SEP]"] + words)}
+    tok = Tokenizer(models.WordPiece(vocab, unk_token="[UNK]"))
+    tok.normalizer = normalizers.BertNormalizer(lowercase=True)
+    tok.pre_tokenizer = pre_tokenizers.BertPreTokenizer()
+    tok.post_processor = processors.TemplateProcessing(single="[CLS] $A [SEP]", special_tokens=[("[CLS]", 2), ("[SEP]", 3)])
+    tok.save(str(tmp_path / "tokenizer.json"))
+    cfg = dict(vocab_size=shape.vocab_size, hidden_size=shape.hidden_size, num_hidden_layers=shape.num_hidden_layers,
+               num_attention_heads=shape.num_attention_heads, intermediate_size=shape.intermediate_size,
+               hidden_act="gelu", max_position_embeddings=shape.max_position_embeddings,
+               type_vocab_size=shape.type_vocab_size, layer_norm_eps=shape.layer_norm_eps, model_type="bert")
+    json.dump(cfg, open(tmp_path / "config.json", "w"))
+    w = pkg.weights.init_weights(shape, 5)
+    pkg.weights.save_safetensors(str(tmp_path / "model.safetensors"), w)
+    gen = pkg.EmbeddingGenerator.new(str(tmp_path))
+    try:
+        assert gen.generate_sentence_embeddings([]) == []
+        sents = ["The quick brown fox jumps over the lazy dog.", "A symbiont reads web pages!", "Embeds sentences?"] * 4
+        out = gen.generate_sentence_embeddings(sents)
+        assert len(out) == len(sents) and len(out[0]) == shape.hidden_size
+        from codename_symbiont_b200.embedding_generator import tokenize_fixed
+        ids, mask, tt = tokenize_fixed(gen.tokenizer, sents, shape.max_position_embeddings)
+        want = Oracle(shape, w, "f32").generate(ids, tt, mask, chunk=8)
+        check(np.array(out, np.float32), want, False)
+        assert np.array_equal(np.array(out[0]), np.array(out[3]))  # same sentence, same vector, any position
+    finally:
+        gen.close()

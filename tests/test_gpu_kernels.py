@@ -1,0 +1,213 @@
+"""GPU: every kernel of the path, called through the C ABI (b200_op_*), against the CPU oracle on the
+same seeded inputs. bf16 kernels are compared with the oracle running on bf16-rounded weights and
+inputs (so only accumulation order and the output rounding differ); fp32 kernels with the oracle as is."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import cos_rows
+from gpu_util import dev, dev_u32, dev_i32, bf16_round, host, padded_to_packed, cu_of
+from oracle.oracle import Oracle
+
+pytestmark = pytest.mark.gpu
+
+LENGTHS = [2, 3, 16, 33, 64, 64, 17, 9, 1, 40]
+
+
+@pytest.fixture(scope="module")
+def env(pkg, built):
+    shape = pkg.weights.TINY
+    emb = pkg.Embedder.random_init(shape, seed=1234, device=0)
+    w = emb.export_weights()
+    w16 = {k: bf16_round(v) if v.ndim == 2 else v for k, v in w.items()}
+    yield pkg, shape, emb, w, Oracle(shape, w, "f32"), Oracle(shape, w16, "f32")
+    emb.close()
+
+
+def test_native_random_init_matches_numpy_spec(env):
+    pkg, shape, emb, w, _, _ = env
+    want = pkg.weights.init_weights(shape, 1234)
+    assert set(w) == set(want)
+    for k in want:
+        assert w[k].shape == want[k].shape
+        assert np.abs(w[k] - want[k]).max() <= 1e-8, k
+
+
+def test_safetensors_load_equals_random_init(env, tmp_path):
+    pkg, shape, emb, w, _, _ = env
+    p = str(tmp_path / "model.safetensors")
+    pkg.weights.save_safetensors(p, {"bert." + k: v for k, v in w.items()})  # candle's prefix fallback
+    with pkg.Embedder(shape, p, device=0) as e2:
+        w2 = e2.export_weights()
+    assert all(np.array_equal(w[k], w2[k]) for k in w)
+
+
+@pytest.mark.parametrize("dtype", [0, 1])
+def test_k1_embed_layernorm(env, dtype):
+    pkg, shape, emb, w, o32, o16 = env
+    ids, mask, tt = pkg.synth.padded_batch(shape.vocab_size, [max(n, 2) for n in LENGTHS], 64, seed=5)
+    tt = ((np.arange(64)[None, :] % 3 == 0) & (mask > 0)).astype(np.uint32)
+    lengths = mask.sum(1)
+    want = padded_to_packed(o32.embeddings(ids, tt), lengths)
+    pi, pt, cu = pkg.synth.pack(ids, mask, tt)
+    T = int(cu[-1])
+    td = torch.float32 if dtype else torch.bfloat16
+    out = torch.empty((T, shape.hidden_size), dtype=td, device="cuda")
+    out_lo = torch.empty_like(out)
+    d_pi, d_pt, d_cu = dev_u32(pi), dev_u32(pt), dev_i32(cu)
+    emb.op_embed_layernorm(d_pi.data_ptr(), d_pt.data_ptr(), d_cu.data_ptr(), len(lengths), T, dtype, out.data_ptr(),
+                           0 if dtype else out_lo.data_ptr())
+    got = host(out)
+    if dtype:
+        assert np.abs(got - want).max() <= 1e-5
+    else:  # tables are fp32 in both modes: hi is the bf16 rounding of the exact row, hi + lo restores it
+        assert np.abs(got - want).max() <= 2.0 ** -8 * np.abs(want).max()
+        assert np.abs(got + host(out_lo) - want).max() <= 2e-5
+    assert cos_rows(got, want).min() >= (0.999999 if dtype else 0.9999)
+
+
+@pytest.mark.parametrize("m,n,k,block_n,act", [
+    (128, 128, 64, 128, -1), (128, 256, 128, 256, -1), (256, 384, 384, 192, -1), (1000, 1152, 384, 192, -1),
+    (777, 1536, 384, 256, 0), (300, 512, 128, 128, 0), (513, 256, 1536, 256, -1), (129, 128, 72, 128, 2),
+    (4096, 2304, 768, 256, -1), (640, 3072, 768, 256, 1), (1, 128, 64, 128, -1), (20000, 384, 384, 128, -1),
+])
+def test_gemm_tcgen05_vs_fp32(env, m, n, k, block_n, act):
+    """K2 mainloop + bias/activation epilogue vs an fp32 reference of the same op on the same bf16 inputs."""
+    pkg = env[0]
+    g = torch.Generator(device="cuda").manual_seed(m * 7 + n + k)
+    a = (torch.randn((m, k), device="cuda", generator=g) * 1.0).bfloat16()
+    b = (torch.randn((n, k), device="cuda", generator=g) * 0.05).bfloat16()
+    bias = torch.randn((n,), device="cuda", generator=g) * 0.1
+    c = torch.full((m, n), float("nan"), dtype=torch.bfloat16, device="cuda")
+    pkg.abi.op_gemm_bf16(a.data_ptr(), b.data_ptr(), bias.data_ptr(), m, n, k, act, block_n, c.data_ptr())
+    torch.cuda.synchronize()
+    torch.backends.cuda.matmul.allow_tf32 = False
+    ref = a.float() @ b.float().t() + bias
+    if act == 0:
+        ref = torch.nn.functional.gelu(ref)
+    elif act == 1:
+        ref = torch.nn.functional.gelu(ref, approximate="tanh")
+    elif act == 2:
+        ref = torch.relu(ref)
+    err = (c.float() - ref).abs().max().item()
+    scale = ref.abs().max().item()
+    assert np.isfinite(err) and err <= 0.006 * scale + 1e-3, (err, scale)
+
+
+@pytest.mark.parametrize("dtype", [0, 1])
+@pytest.mark.parametrize("which", [0, 1, 2, 3])
+def test_k2_linear_layers(env, dtype, which):
+    """Each Linear of a layer with its fused epilogue: QKV / +res+LN / +GELU / +res+LN (bert.rs)."""
+    pkg, shape, emb, w, o32, o16 = env
+    o = o32 if dtype else o16
+    H, I = shape.hidden_size, shape.intermediate_size
+    rows = 333
+    rng = np.random.default_rng(which)
+    kin = I if which == 3 else H
+    x = rng.standard_normal((rows, kin)).astype(np.float32)
+    res = rng.standard_normal((rows, H)).astype(np.float32)
+    if not dtype:
+        x = bf16_round(x)
+    L = 1
+    if which == 0:
+        want = np.concatenate([o.linear(x, o.layer(L, f"attention.self.{n}.weight"), o.layer(L, f"attention.self.{n}.bias"))
+                               for n in ("query", "key", "value")], axis=1)
+    elif which == 1:
+        y = o.linear(x, o.layer(L, "attention.output.dense.weight"), o.layer(L, "attention.output.dense.bias"))
+        want = o.add_layer_norm(y, res, o.layer(L, "attention.output.LayerNorm.weight"),
+                                o.layer(L, "attention.output.LayerNorm.bias"), shape.layer_norm_eps)
+    elif which == 2:
+        want = o.activation(o.linear(x, o.layer(L, "intermediate.dense.weight"), o.layer(L, "intermediate.dense.bias")), 0)
+    else:
+        y = o.linear(x, o.layer(L, "output.dense.weight"), o.layer(L, "output.dense.bias"))
+        want = o.add_layer_norm(y, res, o.layer(L, "output.LayerNorm.weight"), o.layer(L, "output.LayerNorm.bias"),
+                                shape.layer_norm_eps)
+    td = torch.float32 if dtype else torch.bfloat16
+    res_hi = bf16_round(res)
+    dx, dr, dr_lo = dev(x, td), dev(res, td), dev(res - res_hi, td)  # residual = hi + lo in bf16 mode
+    out = torch.full(want.shape, float("nan"), dtype=td, device="cuda")
+    out_lo = torch.full(want.shape, float("nan"), dtype=td, device="cuda")
+    ln = which in (1, 3)
+    emb.op_linear(L, which, dx.data_ptr(), dr.data_ptr(), rows, dtype, out.data_ptr(),
+                  d_residual_lo=0 if dtype else dr_lo.data_ptr(), d_y_lo=out_lo.data_ptr() if (ln and not dtype) else 0)
+    got = host(out)
+    tol = 2e-5 if dtype else 0.006 * np.abs(want).max() + 1e-3
+    assert np.abs(got - want).max() <= tol, np.abs(got - want).max()
+    if ln and not dtype:  # hi + lo carries the LayerNorm output to ~16 bits; only the bf16 GEMM inputs limit it
+        assert np.abs(got + host(out_lo) - want).max() <= 2e-3
+
+
+@pytest.mark.parametrize("dtype", [0, 1])
+@pytest.mark.parametrize("heads,d", [(4, 32), (2, 64)])
+def test_k3_attention(env, pkg, dtype, heads, d):
+    """Varlen attention vs the oracle's padded additive-mask softmax; ragged lengths incl. 1 and > 64."""
+    shape = pkg.weights.BertShape(512, heads * d, 1, heads, 512, 256, 2)
+    lengths = np.array([1, 2, 63, 64, 65, 128, 200, 17])
+    S, H = 200, heads * d
+    rng = np.random.default_rng(11)
+    q, k, v = (rng.standard_normal((len(lengths), S, H)).astype(np.float32) for _ in range(3))
+    if not dtype:
+        q, k, v = bf16_round(q), bf16_round(k), bf16_round(v)
+    mask = (np.arange(S)[None, :] < lengths[:, None]).astype(np.uint32)
+    with pkg.Embedder.random_init(shape, seed=1) as e:
+        o = Oracle(shape, e.export_weights(), "f32")
+        want = padded_to_packed(o.attention(q, k, v, mask, heads), lengths)
+        qkv = np.concatenate([padded_to_packed(t, lengths) for t in (q, k, v)], axis=1)
+        td = torch.float32 if dtype else torch.bfloat16
+        dq = dev(qkv, td)
+        ctx = torch.full(want.shape, float("nan"), dtype=td, device="cuda")
+        d_cu = dev_i32(cu_of(lengths))
+        e.op_attention(dq.data_ptr(), d_cu.data_ptr(), len(lengths), int(lengths.max()), dtype, ctx.data_ptr())
+        got = host(ctx)
+    tol = 2e-5 if dtype else 0.02  # bf16 P and output rounding on |ctx| <~ 3
+    assert np.abs(got - want).max() <= tol, np.abs(got - want).max()
+    assert cos_rows(got, want).min() >= (0.999999 if dtype else 0.9998)
+
+
+@pytest.mark.parametrize("mode", ["bf16", "f32y", "fp32"])
+def test_k4_add_layernorm(env, mode):
+    pkg, shape, emb, w, o32, _ = env
+    rows, H = 1001, shape.hidden_size
+    rng = np.random.default_rng(3)
+    y = rng.standard_normal((rows, H)).astype(np.float32) * 2
+    r = rng.standard_normal((rows, H)).astype(np.float32)
+    if mode == "bf16":
+        y = bf16_round(y)
+    want = o32.add_layer_norm(y, r, o32.layer(0, "output.LayerNorm.weight"), o32.layer(0, "output.LayerNorm.bias"),
+                              shape.layer_norm_eps)
+    td = torch.float32 if mode == "fp32" else torch.bfloat16
+    dy = dev(y, torch.bfloat16 if mode == "bf16" else torch.float32)
+    out = torch.empty((rows, H), dtype=td, device="cuda")
+    out_lo = torch.empty_like(out)
+    r_hi = bf16_round(r)
+    d_r, d_r_lo = dev(r, td), dev(r - r_hi, td)
+    emb.op_add_layernorm(0, 3, dy.data_ptr(), mode != "bf16", d_r.data_ptr(), rows, int(mode == "fp32"),
+                         out.data_ptr(), d_residual_lo=0 if mode == "fp32" else d_r_lo.data_ptr(),
+                         d_out_lo=0 if mode == "fp32" else out_lo.data_ptr())
+    got = host(out)
+    assert np.abs(got - want).max() <= (1e-5 if mode == "fp32" else 0.02)
+    if mode != "fp32":
+        assert np.abs(got + host(out_lo) - want).max() <= 1e-4
+
+
+@pytest.mark.parametrize("dtype", [0, 1])
+@pytest.mark.parametrize("normalize", [0, 1])
+def test_k5_mean_pool(env, dtype, normalize):
+    """embedding_generator.rs:201-207 (+ the north_star L2 step)."""
+    pkg, shape, emb, w, o32, _ = env
+    lengths = np.array(LENGTHS + [64] * 7)
+    S, H = 64, shape.hidden_size
+    rng = np.random.default_rng(9)
+    hid = rng.standard_normal((len(lengths), S, H)).astype(np.float32)
+    mask = (np.arange(S)[None, :] < lengths[:, None]).astype(np.uint32)
+    want = o32.mean_pool(hid, mask)
+    if normalize:
+        want = o32.l2_normalize(want)
+    td = torch.float32 if dtype else torch.bfloat16
+    out = torch.empty((len(lengths), H), dtype=torch.float32, device="cuda")
+    packed = padded_to_packed(hid, lengths)
+    d_h, d_lo, d_cu = dev(packed, td), dev(packed - bf16_round(packed), td), dev_i32(cu_of(lengths))
+    emb.op_mean_pool(d_h.data_ptr(), d_cu.data_ptr(), len(lengths), dtype, normalize, out.data_ptr(),
+                     d_hidden_lo=0 if dtype else d_lo.data_ptr())
+    got = host(out)
+    assert np.abs(got - want).max() <= (2e-6 if dtype else 3e-5)  # bf16: hi + lo keeps ~16 bits of each element
