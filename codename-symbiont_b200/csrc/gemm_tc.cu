@@ -10,10 +10,16 @@
 //   warp 0      TMA producer: A tile 128x64 and W tile BLOCK_Nx64 (bf16, 128B swizzle) per stage
 //   warp 1      one thread issues tcgen05.mma (128 x UMMA_N x 16, fp32 accumulators in TMEM)
 //   warp 2      TMEM allocator
-//   warps 4-11  epilogue: tcgen05.ld -> bias / activation / residual + LayerNorm -> global
+//   warps 4-11  epilogue. Warp w owns TMEM lane quadrant w%4 (32 rows) and one half of the tile's
+//               columns, and walks them in 32-column chunks: tcgen05.ld -> math in registers ->
+//               swizzled shared-memory staging -> one TMA store per chunk. A thread holds one row,
+//               so writing global memory directly would touch 32 rows x 16 B per instruction
+//               (ncu r01a: 32 sectors per request); the TMA store writes full 64 B row segments.
 // Accumulators are double-buffered in TMEM when 2*BLOCK_N <= 512 columns so the epilogue of tile i
 // overlaps the MMAs of tile i+1. With BLOCK_N == N (<= 384) a CTA owns whole output rows and the
-// residual add + LayerNorm run in the epilogue (EPI_RES_LN), so the pre-LN activations never
+// residual add + LayerNorm run in the epilogue (EPI_RES_LN): pass 1 adds bias and the residual
+// (TMA-loaded per chunk into a per-warp ring, prefetched one tile ahead), parks the sum back in TMEM
+// and accumulates the row statistics; pass 2 normalises and stores. The pre-LN activations never
 // reach HBM. Both operands are K-major ("TN"): activations [M,K] and HF weights [N,K] as stored.
 #include "gemm_tc.h"
 
@@ -33,59 +39,84 @@ constexpr int BLOCK_K = 64;  // 64 bf16 = one 128-byte swizzle row
 constexpr int UMMA_K = 16;
 constexpr int NUM_THREADS = 384;
 constexpr int EPI_WARP0 = 4;
-constexpr int EPI_THREADS = 256;
+constexpr int EPI_WARPS = 8;
+constexpr int EPI_THREADS = EPI_WARPS * 32;
 constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;
+constexpr int CHUNK = 32;                   // epilogue chunk: 32 rows x 32 columns per warp
+constexpr int CHUNK_BF16 = 32 * CHUNK * 2;  // 2 KB, 64-byte rows (SWIZZLE_64B)
+constexpr int CHUNK_F32 = 32 * CHUNK * 4;   // 4 KB, 128-byte rows (SWIZZLE_128B)
+constexpr int SMEM_LIMIT = 232448;          // 227 KB per CTA on sm_100
 
 __host__ __device__ constexpr int b_stage_bytes(int block_n) { return block_n * BLOCK_K * 2; }
-__host__ __device__ constexpr int num_stages(int block_n) {
-    int s = (196 * 1024) / (A_STAGE_BYTES + b_stage_bytes(block_n));
+// per-warp epilogue shared memory: 2 output staging buffers (+ a 2-stage (hi, lo) residual ring for LN)
+__host__ __device__ constexpr int epi_warp_bytes(int epi, bool out_f32) {
+    return (epi == EPI_RES_LN ? 2 * 2 * CHUNK_BF16 : 0) + 2 * (out_f32 ? CHUNK_F32 : CHUNK_BF16);
+}
+// mbarriers (<= 8 + 8 stage, 4 TMEM, 16 residual) + TMEM pointer + LayerNorm partial statistics
+constexpr int AUX_BYTES = 512 + 2 * BLOCK_M * 8;
+__host__ __device__ constexpr int num_stages(int block_n, int epi, bool out_f32) {
+    int s = (SMEM_LIMIT - AUX_BYTES - EPI_WARPS * epi_warp_bytes(epi, out_f32)) /
+            (A_STAGE_BYTES + b_stage_bytes(block_n));
     return s > 8 ? 8 : s;
 }
-// barriers + tmem pointer + LayerNorm partial statistics
-constexpr int AUX_BYTES = 256 + 2 * BLOCK_M * 8;
-__host__ __device__ constexpr int smem_bytes(int block_n) {
-    return 1024 + num_stages(block_n) * (A_STAGE_BYTES + b_stage_bytes(block_n)) + AUX_BYTES;
+__host__ __device__ constexpr int smem_bytes(int block_n, int epi, bool out_f32) {
+    return num_stages(block_n, epi, out_f32) * (A_STAGE_BYTES + b_stage_bytes(block_n)) +
+           EPI_WARPS * epi_warp_bytes(epi, out_f32) + AUX_BYTES;
 }
 
 struct GemmDev {
-    int m;              // rows covered by the tensor map
+    int m;              // rows covered by the tensor maps
     const int* d_rows;  // optional device-side row count (<= m)
     int n, k;
     const float* bias;
-    const __nv_bfloat16* residual;     // [m, n] (EPI_RES_LN): high half of the residual stream
-    const __nv_bfloat16* residual_lo;  // low half (residual = hi + lo) or nullptr
     const float* gamma;
     const float* beta;
     float eps;
-    void* out;              // [m, n] bf16 or fp32
-    __nv_bfloat16* out_lo;  // EPI_RES_LN: bf16(y - bf16(y)) so that the next residual add sees ~16 mantissa bits
+    int has_res_lo, has_out_lo;
 };
 
-template <typename OutT>
-__device__ __forceinline__ void store_chunk32(OutT* dst, const float (&f)[32]);
-template <>
-__device__ __forceinline__ void store_chunk32<__nv_bfloat16>(__nv_bfloat16* dst, const float (&f)[32]) {
-    uint4* d4 = reinterpret_cast<uint4*>(dst);
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        uint4 u;
-        u.x = pack_bf16x2(f[q * 8 + 0], f[q * 8 + 1]);
-        u.y = pack_bf16x2(f[q * 8 + 2], f[q * 8 + 3]);
-        u.z = pack_bf16x2(f[q * 8 + 4], f[q * 8 + 5]);
-        u.w = pack_bf16x2(f[q * 8 + 6], f[q * 8 + 7]);
-        d4[q] = u;
-    }
-}
-template <>
-__device__ __forceinline__ void store_chunk32<float>(float* dst, const float (&f)[32]) {
-    float4* d4 = reinterpret_cast<float4*>(dst);
-#pragma unroll
-    for (int q = 0; q < 8; ++q) d4[q] = make_float4(f[q * 4], f[q * 4 + 1], f[q * 4 + 2], f[q * 4 + 3]);
+// gelu_erf(x) = 0.5 x (1 + erf(x / sqrt 2)) with erf(x / sqrt 2) ~= tanh(x (c1 + c3 x^2 + c5 x^4 + c7 x^6)) on
+// |x| <= 5 (clamped; beyond that both sides are 1 to 1e-6). Coefficients from scripts/fit_gelu.py: max abs error
+// 1.2e-5 (2.5e-5 |x|), 40x tighter than the usual tanh-GELU and far below the bf16 rounding of the output.
+// One MUFU.TANH + 8 FMA-pipe ops instead of ~25 for erff().
+__device__ __forceinline__ float gelu_erf_fast(float x) {
+    const float xc = fminf(fmaxf(x, -5.0f), 5.0f);
+    const float x2 = xc * xc;
+    float p = fmaf(x2, -8.645902750674527e-06f, -2.546073342664881e-04f);
+    p = fmaf(x2, p, 3.672949335123125e-02f);
+    p = fmaf(x2, p, 7.976898743684135e-01f);
+    float t;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(xc * p));
+    const float hx = 0.5f * x;
+    return fmaf(hx, t, hx);
 }
 
+template <int EPI>
+__device__ __forceinline__ float epi_act(float x) {
+    if constexpr (EPI == EPI_GELU_ERF) return gelu_erf_fast(x);
+    else if constexpr (EPI == EPI_GELU_TANH) return activate(x, 1);
+    else if constexpr (EPI == EPI_RELU) return fmaxf(x, 0.f);
+    else return x;
+}
+
+// Writes this thread's row of a 32x32 chunk into a staging buffer laid out as the TMA box expects.
+// bf16: 64-byte rows, SWIZZLE_64B (16-byte piece q of row r lands at piece q ^ ((r >> 1) & 3)).
+__device__ __forceinline__ void stage_row_bf16(uint32_t buf, int r, const float (&f)[32]) {
+    const uint32_t row = buf + r * 64;
+    const int sw = (r >> 1) & 3;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const uint32_t a = row + ((q ^ sw) << 4);
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(pack_bf16x2(f[q * 8 + 0], f[q * 8 + 1])),
+                     "r"(pack_bf16x2(f[q * 8 + 2], f[q * 8 + 3])), "r"(pack_bf16x2(f[q * 8 + 4], f[q * 8 + 5])),
+                     "r"(pack_bf16x2(f[q * 8 + 6], f[q * 8 + 7]))
+                     : "memory");
+    }
+}
 // lo[j] = bf16(f[j] - bf16(f[j])): the part of the fp32 value the bf16 "hi" tensor dropped
-__device__ __forceinline__ void store_chunk32_lo(__nv_bfloat16* dst, const float (&f)[32]) {
-    uint4* d4 = reinterpret_cast<uint4*>(dst);
+__device__ __forceinline__ void stage_row_bf16_lo(uint32_t buf, int r, const float (&f)[32]) {
+    const uint32_t row = buf + r * 64;
+    const int sw = (r >> 1) & 3;
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
         uint32_t w[4];
@@ -95,38 +126,66 @@ __device__ __forceinline__ void store_chunk32_lo(__nv_bfloat16* dst, const float
             const float2 h = unpack_bf16x2(pack_bf16x2(a, b));
             w[j] = pack_bf16x2(a - h.x, b - h.y);
         }
-        d4[q] = make_uint4(w[0], w[1], w[2], w[3]);
+        const uint32_t a = row + ((q ^ sw) << 4);
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3])
+                     : "memory");
     }
+}
+// fp32: 128-byte rows, SWIZZLE_128B (piece q of row r lands at piece q ^ (r & 7)).
+__device__ __forceinline__ void stage_row_f32(uint32_t buf, int r, const float (&f)[32]) {
+    const uint32_t row = buf + r * 128;
+    const int sw = r & 7;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+        const uint32_t a = row + ((q ^ sw) << 4);
+        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(f[q * 4 + 0]), "f"(f[q * 4 + 1]),
+                     "f"(f[q * 4 + 2]), "f"(f[q * 4 + 3])
+                     : "memory");
+    }
+}
+__device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+    return v;
 }
 
 template <int BLOCK_N, int EPI, typename OutT>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+               const __grid_constant__ CUtensorMap tmap_c, const __grid_constant__ CUtensorMap tmap_c_lo,
+               const __grid_constant__ CUtensorMap tmap_r, const __grid_constant__ CUtensorMap tmap_r_lo,
                const GemmDev p) {
+    constexpr bool OUT_F32 = sizeof(OutT) == 4;
     constexpr int NSPLIT = BLOCK_N > 256 ? 2 : 1;
     constexpr int UMMA_N = BLOCK_N / NSPLIT;
     constexpr int ACC_STAGES = (2 * BLOCK_N <= 512) ? 2 : 1;
     constexpr int B_STAGE_BYTES = b_stage_bytes(BLOCK_N);
-    constexpr int STAGES = num_stages(BLOCK_N);
+    constexpr int STAGES = num_stages(BLOCK_N, EPI, OUT_F32);
     constexpr int HALF_N = BLOCK_N / 2;  // columns per epilogue warp group
+    constexpr int NCH = HALF_N / CHUNK;  // chunks per warp per tile
+    constexpr int EPI_WARP_BYTES = epi_warp_bytes(EPI, OUT_F32);
+    constexpr int OUT_CHUNK_BYTES = OUT_F32 ? CHUNK_F32 : CHUNK_BF16;
     static_assert(UMMA_N % 16 == 0 && UMMA_N <= 256, "invalid UMMA N");
-    static_assert(HALF_N % 32 == 0, "epilogue works in 32-column chunks");
+    static_assert(HALF_N % CHUNK == 0, "epilogue works in 32-column chunks");
+    static_assert(STAGES >= 2, "not enough shared memory for a pipeline");
+    static_assert(EPI != EPI_RES_LN || !OUT_F32, "LayerNorm epilogue writes bf16 (hi, lo)");
 
-    extern __shared__ uint8_t smem_raw[];
-    const uint32_t raw_addr = smem_u32(smem_raw);
-    const uint32_t base = (raw_addr + 1023u) & ~1023u;
-    uint8_t* base_ptr = smem_raw + (base - raw_addr);
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    const uint32_t base = smem_u32(smem_raw);
+    if ((base & 1023u) != 0) __trap();  // swizzled TMA / UMMA tiles need 1024-byte alignment
     const uint32_t smem_a = base;
     const uint32_t smem_b = base + STAGES * A_STAGE_BYTES;
-    const uint32_t aux = base + STAGES * (A_STAGE_BYTES + B_STAGE_BYTES);
-    uint8_t* aux_ptr = base_ptr + STAGES * (A_STAGE_BYTES + B_STAGE_BYTES);
-    const uint32_t bar_full = aux;                // STAGES x 8 B
-    const uint32_t bar_empty = aux + 64;          // STAGES x 8 B
-    const uint32_t bar_tfull = aux + 128;         // 2 x 8 B
-    const uint32_t bar_tempty = aux + 144;        // 2 x 8 B
-    const uint32_t tmem_slot = aux + 160;         // 4 B
-    volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(aux_ptr + 160);
-    float2* ln_part = reinterpret_cast<float2*>(aux_ptr + 256);  // [2][BLOCK_M]
+    const uint32_t smem_epi = base + STAGES * (A_STAGE_BYTES + B_STAGE_BYTES);
+    const uint32_t aux = smem_epi + EPI_WARPS * EPI_WARP_BYTES;
+    uint8_t* aux_ptr = smem_raw + (aux - base);
+    const uint32_t bar_full = aux;          // STAGES x 8 B
+    const uint32_t bar_empty = aux + 64;    // STAGES x 8 B
+    const uint32_t bar_tfull = aux + 128;   // 2 x 8 B
+    const uint32_t bar_tempty = aux + 144;  // 2 x 8 B
+    const uint32_t bar_res = aux + 192;     // EPI_WARPS x 2 x 8 B (residual ring, one pair per epilogue warp)
+    const uint32_t tmem_slot = aux + 320;   // 4 B
+    volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(aux_ptr + 320);
+    float2* ln_part = reinterpret_cast<float2*>(aux_ptr + 512);  // [2][BLOCK_M]
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -144,6 +203,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     if (threadIdx.x == 0) {
         prefetch_tmap(&tmap_a);
         prefetch_tmap(&tmap_b);
+        prefetch_tmap(&tmap_c);
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(bar_full + 8 * s, 1);
             mbar_init(bar_empty + 8 * s, 1);
@@ -152,6 +212,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             mbar_init(bar_tfull + 8 * s, 1);
             mbar_init(bar_tempty + 8 * s, EPI_THREADS);
         }
+        for (int s = 0; s < 2 * EPI_WARPS; ++s) mbar_init(bar_res + 8 * s, 1);
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc(tmem_slot, 512);
@@ -216,68 +277,110 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         }
     } else if (warp >= EPI_WARP0) {
         // ------------------------------ epilogue ----------------------------------
-        const int quad = warp & 3;               // TMEM lane quadrant this warp may access
-        const int half = (warp - EPI_WARP0) >> 2;  // which half of the tile's columns
+        const int ew = warp - EPI_WARP0;
+        const int quad = warp & 3;  // TMEM lane quadrant this warp may access
+        const int half = ew >> 2;   // which half of the tile's columns
         const int row_in_tile = quad * 32 + lane;
-        OutT* out = reinterpret_cast<OutT*>(p.out);
+        const uint32_t my_smem = smem_epi + ew * EPI_WARP_BYTES;
+        const uint32_t out_buf = my_smem + (EPI == EPI_RES_LN ? 4 * CHUNK_BF16 : 0);  // 2 x OUT_CHUNK_BYTES
+        uint32_t st_it = 0;  // output staging buffers used so far (alternating)
+
+        // stages one chunk and hands it to the TMA store engine; at most one older store may still be reading
+        auto store_chunk = [&](const CUtensorMap* map, int col0, int row0, const float (&f)[32], bool lo) {
+            const uint32_t buf = out_buf + (st_it & 1) * OUT_CHUNK_BYTES;
+            if (lane == 0) tma_store_wait_read<1>();
+            __syncwarp();
+            if constexpr (OUT_F32) stage_row_f32(buf, lane, f);
+            else if (lo) stage_row_bf16_lo(buf, lane, f);
+            else stage_row_bf16(buf, lane, f);
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+                tma_store_2d(map, buf, col0, row0);
+                tma_store_commit();
+            }
+            ++st_it;
+        };
+
+        // residual ring (EPI_RES_LN): stage s of this warp = my_smem + s * 4 KB: [hi 2 KB][lo 2 KB]
+        uint32_t ld_issued = 0, ld_used = 0;
+        auto issue_residual = [&](int tile, int c) {
+            if (lane == 0) {
+                const int m_tile = tile / num_n_tiles, n_tile = tile % num_n_tiles;
+                const uint32_t s = ld_issued & 1;
+                const uint32_t bar = bar_res + 8 * (2 * ew + s);
+                const uint32_t dst = my_smem + s * (2 * CHUNK_BF16);
+                const int col0 = n_tile * BLOCK_N + half * HALF_N + c * CHUNK, row0 = m_tile * BLOCK_M + quad * 32;
+                mbar_arrive_expect_tx(bar, p.has_res_lo ? 2 * CHUNK_BF16 : CHUNK_BF16);
+                tma_load_2d(dst, &tmap_r, col0, row0, bar);
+                if (p.has_res_lo) tma_load_2d(dst + CHUNK_BF16, &tmap_r_lo, col0, row0, bar);
+            }
+            ++ld_issued;
+        };
+        if constexpr (EPI == EPI_RES_LN) {
+            if (static_cast<int>(blockIdx.x) < num_tiles) {
+                issue_residual(blockIdx.x, 0);
+                if (NCH > 1) issue_residual(blockIdx.x, 1);
+            }
+        }
+
         int it = 0;
         for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
             const int m_tile = t / num_n_tiles, n_tile = t % num_n_tiles;
             const int acc = it % ACC_STAGES;
             const uint32_t acc_phase = (it / ACC_STAGES) & 1;
-            const int row = m_tile * BLOCK_M + row_in_tile;
-            const bool row_ok = row < rows;
+            const int row0 = m_tile * BLOCK_M + quad * 32;
             const int col_base = n_tile * BLOCK_N + half * HALF_N;
-            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * BLOCK_N + half * HALF_N;
+            const uint32_t taddr =
+                tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * BLOCK_N + half * HALF_N;
             mbar_wait(bar_tfull + 8 * acc, acc_phase);
             tc_fence_after_sync();
 
             if constexpr (EPI != EPI_RES_LN) {
 #pragma unroll 1
-                for (int c = 0; c < HALF_N / 32; ++c) {
+                for (int c = 0; c < NCH; ++c) {
                     uint32_t v[32];
-                    tmem_ld_32x32(taddr + c * 32, v);
+                    tmem_ld_32x32(taddr + c * CHUNK, v);
                     tmem_ld_wait();
-                    const int col0 = col_base + c * 32;
+                    if (c == NCH - 1) {  // accumulator drained: the MMA warp may start the tile after next
+                        tc_fence_before_sync();
+                        mbar_arrive(bar_tempty + 8 * acc);
+                    }
+                    const int col0 = col_base + c * CHUNK;
                     float f[32];
                     const float4* b4 = reinterpret_cast<const float4*>(p.bias + col0);
 #pragma unroll
                     for (int q = 0; q < 8; ++q) {
                         const float4 b = __ldg(b4 + q);
-                        f[q * 4 + 0] = __uint_as_float(v[q * 4 + 0]) + b.x;
-                        f[q * 4 + 1] = __uint_as_float(v[q * 4 + 1]) + b.y;
-                        f[q * 4 + 2] = __uint_as_float(v[q * 4 + 2]) + b.z;
-                        f[q * 4 + 3] = __uint_as_float(v[q * 4 + 3]) + b.w;
+                        f[q * 4 + 0] = epi_act<EPI>(__uint_as_float(v[q * 4 + 0]) + b.x);
+                        f[q * 4 + 1] = epi_act<EPI>(__uint_as_float(v[q * 4 + 1]) + b.y);
+                        f[q * 4 + 2] = epi_act<EPI>(__uint_as_float(v[q * 4 + 2]) + b.z);
+                        f[q * 4 + 3] = epi_act<EPI>(__uint_as_float(v[q * 4 + 3]) + b.w);
                     }
-                    if constexpr (EPI == EPI_GELU_ERF || EPI == EPI_GELU_TANH || EPI == EPI_RELU) {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) f[j] = activate(f[j], EPI - EPI_GELU_ERF);
-                    }
-                    if (row_ok) store_chunk32<OutT>(out + static_cast<size_t>(row) * p.n + col0, f);
+                    store_chunk(&tmap_c, col0, row0, f, false);
                 }
             } else {
-                // pass 1: v = acc + bias + residual, kept in TMEM; row sum and sum of squares
+                // pass 1: v = acc + bias + residual, parked in TMEM; row sum and sum of squares
                 float sum = 0.f, sumsq = 0.f;
-                const __nv_bfloat16* res = p.residual + static_cast<size_t>(row_ok ? row : 0) * p.n;
-                const __nv_bfloat16* res_lo =
-                    p.residual_lo ? p.residual_lo + static_cast<size_t>(row_ok ? row : 0) * p.n : nullptr;
 #pragma unroll 1
-                for (int c = 0; c < HALF_N / 32; ++c) {
+                for (int c = 0; c < NCH; ++c) {
                     uint32_t v[32];
-                    tmem_ld_32x32(taddr + c * 32, v);
+                    tmem_ld_32x32(taddr + c * CHUNK, v);
+                    const uint32_t s = ld_used & 1;
+                    mbar_wait(bar_res + 8 * (2 * ew + s), (ld_used >> 1) & 1);
+                    ++ld_used;
+                    const uint32_t rbuf = my_smem + s * (2 * CHUNK_BF16) + lane * 64;
+                    const int sw = (lane >> 1) & 3;
                     tmem_ld_wait();
-                    const int col0 = col_base + c * 32;
-                    const float4* b4 = reinterpret_cast<const float4*>(p.bias + col0);
-                    const uint4* r4 = reinterpret_cast<const uint4*>(res + col0);
-                    const uint4* l4 = reinterpret_cast<const uint4*>(res_lo + col0);
+                    const float4* b4 = reinterpret_cast<const float4*>(p.bias + col_base + c * CHUNK);
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
-                        const uint4 r = __ldg(r4 + q);
+                        const uint4 r = lds_v4(rbuf + ((q ^ sw) << 4));
                         const float4 b0 = __ldg(b4 + 2 * q), b1 = __ldg(b4 + 2 * q + 1);
                         float2 r0 = unpack_bf16x2(r.x), r1 = unpack_bf16x2(r.y), r2 = unpack_bf16x2(r.z),
                                r3 = unpack_bf16x2(r.w);
-                        if (res_lo != nullptr) {
-                            const uint4 l = __ldg(l4 + q);
+                        if (p.has_res_lo) {
+                            const uint4 l = lds_v4(rbuf + CHUNK_BF16 + ((q ^ sw) << 4));
                             const float2 l0 = unpack_bf16x2(l.x), l1 = unpack_bf16x2(l.y), l2 = unpack_bf16x2(l.z),
                                          l3 = unpack_bf16x2(l.w);
                             r0.x += l0.x; r0.y += l0.y; r1.x += l1.x; r1.y += l1.y;
@@ -299,7 +402,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                             v[q * 8 + j] = __float_as_uint(x[j]);
                         }
                     }
-                    tmem_st_32x32(taddr + c * 32, v);
+                    tmem_st_32x32(taddr + c * CHUNK, v);
+                    __syncwarp();  // every lane has read this ring stage: refill it
+                    if (c + 2 < NCH) issue_residual(t, c + 2);
+                    else if (t + static_cast<int>(gridDim.x) < num_tiles && c + 2 - NCH < NCH)
+                        issue_residual(t + gridDim.x, c + 2 - NCH);  // prefetch the next tile's first chunks
                 }
                 tmem_st_wait();
                 ln_part[half * BLOCK_M + row_in_tile] = make_float2(sum, sumsq);
@@ -309,35 +416,36 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 const float mean = (sum + other.x) * inv_n;
                 const float var = fmaxf((sumsq + other.y) * inv_n - mean * mean, 0.f);
                 const float rstd = rsqrtf(var + p.eps);
-                // pass 2: normalise, scale, shift, store
+                // pass 2: normalise, scale, shift, store (hi, lo)
 #pragma unroll 1
-                for (int c = 0; c < HALF_N / 32; ++c) {
+                for (int c = 0; c < NCH; ++c) {
                     uint32_t v[32];
-                    tmem_ld_32x32(taddr + c * 32, v);
+                    tmem_ld_32x32(taddr + c * CHUNK, v);
                     tmem_ld_wait();
-                    const int col0 = col_base + c * 32;
+                    if (c == NCH - 1) {
+                        tc_fence_before_sync();
+                        mbar_arrive(bar_tempty + 8 * acc);
+                    }
+                    const int col0 = col_base + c * CHUNK;
                     const float4* g4 = reinterpret_cast<const float4*>(p.gamma + col0);
                     const float4* be4 = reinterpret_cast<const float4*>(p.beta + col0);
                     float f[32];
 #pragma unroll
                     for (int q = 0; q < 8; ++q) {
                         const float4 g = __ldg(g4 + q), be = __ldg(be4 + q);
-                        f[q * 4 + 0] = (__uint_as_float(v[q * 4 + 0]) - mean) * rstd * g.x + be.x;
-                        f[q * 4 + 1] = (__uint_as_float(v[q * 4 + 1]) - mean) * rstd * g.y + be.y;
-                        f[q * 4 + 2] = (__uint_as_float(v[q * 4 + 2]) - mean) * rstd * g.z + be.z;
-                        f[q * 4 + 3] = (__uint_as_float(v[q * 4 + 3]) - mean) * rstd * g.w + be.w;
+                        f[q * 4 + 0] = fmaf((__uint_as_float(v[q * 4 + 0]) - mean) * rstd, g.x, be.x);
+                        f[q * 4 + 1] = fmaf((__uint_as_float(v[q * 4 + 1]) - mean) * rstd, g.y, be.y);
+                        f[q * 4 + 2] = fmaf((__uint_as_float(v[q * 4 + 2]) - mean) * rstd, g.z, be.z);
+                        f[q * 4 + 3] = fmaf((__uint_as_float(v[q * 4 + 3]) - mean) * rstd, g.w, be.w);
                     }
-                    if (row_ok) {
-                        store_chunk32<OutT>(out + static_cast<size_t>(row) * p.n + col0, f);
-                        if (p.out_lo != nullptr) store_chunk32_lo(p.out_lo + static_cast<size_t>(row) * p.n + col0, f);
-                    }
+                    store_chunk(&tmap_c, col0, row0, f, false);
+                    if (p.has_out_lo) store_chunk(&tmap_c_lo, col0, row0, f, true);
                 }
                 // the partial-stat slots are reused by the next tile
                 asm volatile("bar.sync 1, %0;" ::"n"(EPI_THREADS) : "memory");
             }
-            tc_fence_before_sync();
-            mbar_arrive(bar_tempty + 8 * acc);
         }
+        if (lane == 0) tma_store_wait<0>();  // all stores of this warp are complete before the CTA exits
     }
 
     tc_fence_before_sync();
@@ -364,28 +472,45 @@ PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
     return fn;
 }
 
-// bf16 row-major [rows, cols] matrix, box = 64 columns x box_rows rows, 128-byte swizzle.
-bool make_tmap(CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t cols, uint32_t box_rows) {
+// Row-major [rows, cols] matrix of 2- or 4-byte elements; box = box_cols x box_rows.
+bool make_tmap(CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t cols, uint32_t box_cols, uint32_t box_rows,
+               bool f32, CUtensorMapSwizzle swizzle) {
     auto fn = get_encode_fn();
     if (!fn) return false;
+    const uint64_t es = f32 ? 4 : 2;
     cuuint64_t dims[2] = {cols, rows};
-    cuuint64_t strides[1] = {cols * 2};
-    cuuint32_t box[2] = {BLOCK_K, box_rows};
+    cuuint64_t strides[1] = {cols * es};
+    cuuint32_t box[2] = {box_cols, box_rows};
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
-                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    CUresult r = fn(map, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                    const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     return r == CUDA_SUCCESS;
 }
 
 template <int BLOCK_N, int EPI, typename OutT>
 cudaError_t launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms) {
     constexpr int NSPLIT = BLOCK_N > 256 ? 2 : 1;
-    alignas(64) CUtensorMap ta, tb;
-    if (!make_tmap(&ta, a.a, a.m, a.k, BLOCK_M)) return cudaErrorInvalidValue;
-    if (!make_tmap(&tb, a.b, a.n, a.k, BLOCK_N / NSPLIT)) return cudaErrorInvalidValue;
+    constexpr bool OUT_F32 = sizeof(OutT) == 4;
+    alignas(64) CUtensorMap ta, tb, tc, tcl, tr, trl;
+    if (!make_tmap(&ta, a.a, a.m, a.k, BLOCK_K, BLOCK_M, false, CU_TENSOR_MAP_SWIZZLE_128B))
+        return cudaErrorInvalidValue;
+    if (!make_tmap(&tb, a.b, a.n, a.k, BLOCK_K, BLOCK_N / NSPLIT, false, CU_TENSOR_MAP_SWIZZLE_128B))
+        return cudaErrorInvalidValue;
+    const CUtensorMapSwizzle csw = OUT_F32 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+    if (!make_tmap(&tc, a.out, a.m, a.n, CHUNK, 32, OUT_F32, csw)) return cudaErrorInvalidValue;
+    tcl = tc; tr = tc; trl = tc;
+    if (a.out_lo && !make_tmap(&tcl, a.out_lo, a.m, a.n, CHUNK, 32, false, csw)) return cudaErrorInvalidValue;
+    if (EPI == EPI_RES_LN) {
+        if (!a.residual) return cudaErrorInvalidValue;
+        if (!make_tmap(&tr, a.residual, a.m, a.n, CHUNK, 32, false, csw)) return cudaErrorInvalidValue;
+        trl = tr;
+        if (a.residual_lo && !make_tmap(&trl, a.residual_lo, a.m, a.n, CHUNK, 32, false, csw))
+            return cudaErrorInvalidValue;
+    }
     auto kern = gemm_tc_kernel<BLOCK_N, EPI, OutT>;
-    constexpr int smem = smem_bytes(BLOCK_N);
+    constexpr int smem = smem_bytes(BLOCK_N, EPI, OUT_F32);
+    static_assert(smem <= SMEM_LIMIT, "shared memory budget exceeded");
     static bool attr_set = false;  // per instantiation; benign race (idempotent)
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
@@ -394,14 +519,12 @@ cudaError_t launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms) {
     }
     GemmDev p;
     p.m = a.m; p.d_rows = a.d_rows; p.n = a.n; p.k = a.k; p.bias = a.bias;
-    p.residual = reinterpret_cast<const __nv_bfloat16*>(a.residual);
-    p.residual_lo = reinterpret_cast<const __nv_bfloat16*>(a.residual_lo);
-    p.out_lo = reinterpret_cast<__nv_bfloat16*>(a.out_lo);
-    p.gamma = a.gamma; p.beta = a.beta; p.eps = a.eps; p.out = a.out;
+    p.gamma = a.gamma; p.beta = a.beta; p.eps = a.eps;
+    p.has_res_lo = a.residual_lo != nullptr; p.has_out_lo = a.out_lo != nullptr;
     const int tiles = ((a.m + BLOCK_M - 1) / BLOCK_M) * (a.n / BLOCK_N);
     const int grid = tiles < num_sms ? tiles : num_sms;
     if (grid <= 0) return cudaSuccess;
-    kern<<<grid, NUM_THREADS, smem, stream>>>(ta, tb, p);
+    kern<<<grid, NUM_THREADS, smem, stream>>>(ta, tb, tc, tcl, tr, trl, p);
     return cudaGetLastError();
 }
 
@@ -417,6 +540,7 @@ int gemm_tc_pick_block_n(int n, int epi) {
 
 cudaError_t gemm_tc_launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms) {
     if (a.m <= 0) return cudaSuccess;
+    // TMA needs 16-byte row pitches: k % 8 (bf16 operands) and n % 8 (bf16 output rows)
     if (a.k % 8 != 0 || a.n % a.block_n != 0) return cudaErrorInvalidValue;
 #define B200_CASE(BN, EP, T) \
     if (a.block_n == BN && a.epi == EP && a.out_f32 == (sizeof(T) == 4)) return launch<BN, EP, T>(a, stream, num_sms);
