@@ -65,7 +65,7 @@ _SIGNATURES = {
     "b200_embed_profile_read": (C.c_int32, [_P, C.POINTER(KindStats), C.c_int32]),
     "b200_op_embed_layernorm": (C.c_int32, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, _P, _P, _P]),
     "b200_op_linear": (C.c_int32, [_P, C.c_int32, C.c_int32, _P, _P, _P, C.c_int32, C.c_int32, _P, _P, _P]),
-    "b200_op_attention": (C.c_int32, [_P, _P, _P, C.c_int32, C.c_int32, C.c_int32, _P, _P]),
+    "b200_op_attention": (C.c_int32, [_P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P, _P]),
     "b200_op_add_layernorm": (C.c_int32, [_P, C.c_int32, C.c_int32, _P, C.c_int32, _P, _P, C.c_int32, C.c_int32, _P, _P,
                                           _P]),
     "b200_op_mean_pool": (C.c_int32, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, _P, _P]),
@@ -255,8 +255,8 @@ class Embedder:
         _check(self.lib.b200_op_linear(self.h, layer, which, d_x, d_residual or None, d_residual_lo or None, rows, dtype,
                                        d_y, d_y_lo or None, stream or None))
 
-    def op_attention(self, d_qkv, d_cu, batch, max_seqlen, dtype, d_ctx, stream=0):
-        _check(self.lib.b200_op_attention(self.h, d_qkv, d_cu, batch, max_seqlen, dtype, d_ctx, stream or None))
+    def op_attention(self, d_qkv, d_cu, batch, rows, max_seqlen, dtype, d_ctx, stream=0):
+        _check(self.lib.b200_op_attention(self.h, d_qkv, d_cu, batch, rows, max_seqlen, dtype, d_ctx, stream or None))
 
     def op_add_layernorm(self, layer, which, d_y, y_is_f32, d_residual, rows, dtype, d_out, d_residual_lo=0,
                          d_out_lo=0, stream=0):

@@ -1,0 +1,383 @@
+// K3 (tcgen05): varlen self-attention on the 5th-generation tensor cores.
+//
+// Replaces candle bert.rs BertSelfAttention::forward after the Q/K/V projections (scores = q.k^T/sqrt(d)
+// + (1-mask)*f32::MIN, softmax, .v, head merge; called from embedding_generator.rs:198). See attention.cu
+// for the mma.sync variant of the same math; this kernel is the one the forward uses.
+//
+// Work item = (sentence, head, block of 128 query rows). A persistent CTA walks items; per item it walks the
+// sentence's keys in blocks of 128:
+//   warp 0     TMA producer: Q tile once per item, K and V tiles per key block (2-stage rings), straight from
+//              the packed qkv [tokens, 3H] activations (box D x 128 rows; D*2-byte swizzle)
+//   warp 1     one thread issues tcgen05.mma: S = Q.K^T (128 x 128, fp32 in TMEM), then O_blk = P.V (128 x D)
+//   warp 2     TMEM allocator (256 columns: S 128 + O_blk D)
+//   warps 4-7  softmax: thread r owns query row r (TMEM lane r): two passes over S with tcgen05.ld (row max,
+//              then p = exp2(s*scale - max)), P written as bf16 into a 128B-swizzled K-major smem tile (the A
+//              operand of the second MMA), running max / sum / output kept in registers (online softmax, fp32)
+// Keys past the sentence end get p = 0, which is exactly what the reference's additive f32::MIN mask yields.
+// Rows of the 128-row tiles that lie past the sentence end belong to the next sentence (or are zero-filled
+// by TMA past the last token); they are computed and never stored.
+#include "kernels.h"
+
+#include <cuda.h>
+#include <cudaTypedefs.h>
+
+#include <mutex>
+
+#include "common.cuh"
+
+namespace b200 {
+
+namespace {
+
+constexpr int BLK = 128;  // query rows per item and keys per block
+constexpr int ATT_THREADS = 256;
+constexpr int SM_WARP0 = 4;
+constexpr int SM_THREADS = 128;
+
+// K-major operand, rows of 64 bytes (D = 32): SWIZZLE_64B, 8-row groups 512 B apart.
+__device__ __forceinline__ uint64_t umma_desc_k_sw64(uint32_t a) {
+    return static_cast<uint64_t>((a & 0x3FFFFu) >> 4) | (1ull << 16) | (32ull << 32) | (1ull << 46) | (4ull << 61);
+}
+// MN-major operand (V as stored: [key, d], d contiguous). The swizzle atom is one row of D*2 bytes (MN) by 8 keys
+// (K); SBO = distance between 8-key groups; LBO (between MN atoms) is unused because N = D fits one atom.
+template <int D>
+__device__ __forceinline__ uint64_t umma_desc_mn(uint32_t a) {
+    constexpr uint64_t sbo = (8 * D * 2) >> 4;
+    constexpr uint64_t layout = D == 32 ? 4 : 2;  // SWIZZLE_64B : SWIZZLE_128B
+    return static_cast<uint64_t>((a & 0x3FFFFu) >> 4) | (1ull << 16) | (sbo << 32) | (1ull << 46) | (layout << 61);
+}
+template <int D>
+__device__ __forceinline__ uint64_t umma_desc_k(uint32_t a) {
+    return D == 32 ? umma_desc_k_sw64(a) : umma_desc_sw128(a);
+}
+
+__device__ __forceinline__ float ex2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+struct AttnDev {
+    const int* cu;
+    int batch, heads, H, q_blocks;
+    float scale_log2;
+    __nv_bfloat16* ctx;
+};
+
+template <int D>
+struct AttnSmem {
+    static constexpr int TILE = BLK * D * 2;      // one Q / K / V tile
+    static constexpr int P_BYTES = BLK * BLK * 2;  // two K-major 128 x 64 bf16 tiles
+    static constexpr int OFF_Q = 0;                // 2 stages
+    static constexpr int OFF_KV = 2 * TILE;        // 2 stages x (K, V)
+    static constexpr int OFF_P = OFF_KV + 4 * TILE;
+    static constexpr int OFF_AUX = OFF_P + P_BYTES;
+    static constexpr int BYTES = OFF_AUX + 256;
+};
+
+template <int D>
+__global__ void __launch_bounds__(ATT_THREADS, D == 32 ? 2 : 1)
+attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev p) {
+    using L = AttnSmem<D>;
+    constexpr int TILE = L::TILE;
+    constexpr uint32_t TMEM_COLS = 256;
+    constexpr int O_COL = BLK;  // O_blk columns start after the 128 S columns
+
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    const uint32_t base = smem_u32(smem_raw);
+    if ((base & 1023u) != 0) __trap();
+    const uint32_t smem_q = base + L::OFF_Q, smem_kv = base + L::OFF_KV, smem_p = base + L::OFF_P;
+    const uint32_t aux = base + L::OFF_AUX;
+    const uint32_t bar_q_full = aux, bar_q_empty = aux + 16, bar_kv_full = aux + 32, bar_kv_empty = aux + 48;
+    const uint32_t bar_s_full = aux + 64, bar_s_empty = aux + 72, bar_p_full = aux + 80, bar_o_full = aux + 88,
+                   bar_o_empty = aux + 96;
+    const uint32_t tmem_slot = aux + 128;
+    volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + L::OFF_AUX + 128);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int items = p.batch * p.heads * p.q_blocks;
+
+    if (threadIdx.x == 0) {
+        prefetch_tmap(&tmap_qkv);
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(bar_q_full + 8 * s, 1);
+            mbar_init(bar_q_empty + 8 * s, 1);
+            mbar_init(bar_kv_full + 8 * s, 1);
+            mbar_init(bar_kv_empty + 8 * s, 1);
+        }
+        mbar_init(bar_s_full, 1);
+        mbar_init(bar_s_empty, SM_THREADS);
+        mbar_init(bar_p_full, SM_THREADS);
+        mbar_init(bar_o_full, 1);
+        mbar_init(bar_o_empty, SM_THREADS);
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc(tmem_slot, TMEM_COLS);
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = *tmem_slot_ptr;
+
+    // item i -> (sentence b, query block qb, head h); items whose query block lies past the sentence end are empty
+    auto decode = [&](int i, int& b, int& qb, int& h, int& start, int& len) {
+        const int per_b = p.heads * p.q_blocks;
+        b = i / per_b;
+        const int r = i - b * per_b;
+        qb = r / p.heads;
+        h = r - qb * p.heads;
+        start = p.cu[b];
+        len = p.cu[b + 1] - start;
+        return qb * BLK < len;
+    };
+
+    if (warp == 0) {
+        if (lane == 0) {
+            uint32_t q_it = 0, kv_it = 0;
+            for (int i = blockIdx.x; i < items; i += gridDim.x) {
+                int b, qb, h, start, len;
+                if (!decode(i, b, qb, h, start, len)) continue;
+                const uint32_t qs = q_it & 1;
+                mbar_wait(bar_q_empty + 8 * qs, ((q_it >> 1) & 1) ^ 1);
+                mbar_arrive_expect_tx(bar_q_full + 8 * qs, TILE);
+                tma_load_2d(smem_q + qs * TILE, &tmap_qkv, h * D, start + qb * BLK, bar_q_full + 8 * qs);
+                ++q_it;
+                const int nkb = (len + BLK - 1) / BLK;
+                for (int kb = 0; kb < nkb; ++kb, ++kv_it) {
+                    const uint32_t s = kv_it & 1;
+                    mbar_wait(bar_kv_empty + 8 * s, ((kv_it >> 1) & 1) ^ 1);
+                    mbar_arrive_expect_tx(bar_kv_full + 8 * s, 2 * TILE);
+                    tma_load_2d(smem_kv + s * 2 * TILE, &tmap_qkv, p.H + h * D, start + kb * BLK, bar_kv_full + 8 * s);
+                    tma_load_2d(smem_kv + s * 2 * TILE + TILE, &tmap_qkv, 2 * p.H + h * D, start + kb * BLK,
+                                bar_kv_full + 8 * s);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc_s = umma_idesc_bf16(BLK, BLK);
+            constexpr uint32_t idesc_o = umma_idesc_bf16(BLK, D) | (1u << 16);  // B (= V) is MN-major
+            uint32_t q_it = 0, kv_it = 0, blk_it = 0;
+            for (int i = blockIdx.x; i < items; i += gridDim.x) {
+                int b, qb, h, start, len;
+                if (!decode(i, b, qb, h, start, len)) continue;
+                const uint32_t qs = q_it & 1;
+                mbar_wait(bar_q_full + 8 * qs, (q_it >> 1) & 1);
+                const int nkb = (len + BLK - 1) / BLK;
+                for (int kb = 0; kb < nkb; ++kb, ++kv_it, ++blk_it) {
+                    const uint32_t s = kv_it & 1;
+                    const uint32_t k_smem = smem_kv + s * 2 * TILE, v_smem = k_smem + TILE;
+                    mbar_wait(bar_kv_full + 8 * s, (kv_it >> 1) & 1);
+                    mbar_wait(bar_s_empty, (blk_it & 1) ^ 1);  // softmax has drained the previous S
+                    tc_fence_after_sync();
+                    const uint64_t dq = umma_desc_k<D>(smem_q + qs * TILE), dk = umma_desc_k<D>(k_smem);
+#pragma unroll
+                    for (int k = 0; k < D / 16; ++k)
+                        umma_bf16(tmem_base, dq + 2 * k, dk + 2 * k, idesc_s, k > 0 ? 1u : 0u);
+                    umma_commit(bar_s_full);
+                    mbar_wait(bar_p_full, blk_it & 1);           // P is in shared memory
+                    mbar_wait(bar_o_empty, (blk_it & 1) ^ 1);    // previous O_blk has been read
+                    tc_fence_after_sync();
+#pragma unroll
+                    for (int k = 0; k < BLK / 16; ++k) {
+                        // P: two K-major 128x64 tiles (16 KB each), 32 B per 16-key step inside a tile
+                        const uint64_t dp = umma_desc_sw128(smem_p + (k >> 2) * (BLK * 128)) + 2 * (k & 3);
+                        // V: 16 keys per step = 16 rows of D*2 bytes
+                        const uint64_t dv = umma_desc_mn<D>(v_smem + k * 16 * D * 2);
+                        umma_bf16(tmem_base + O_COL, dp, dv, idesc_o, k > 0 ? 1u : 0u);
+                    }
+                    umma_commit(bar_o_full);
+                    umma_commit(bar_kv_empty + 8 * s);
+                }
+                umma_commit(bar_q_empty + 8 * qs);
+                ++q_it;
+            }
+        }
+    } else if (warp >= SM_WARP0) {
+        const int quad = warp & 3;
+        const int row = quad * 32 + lane;  // query row inside the item = TMEM lane
+        const uint32_t t_s = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
+        const uint32_t t_o = t_s + O_COL;
+        uint32_t blk_it = 0;
+        for (int i = blockIdx.x; i < items; i += gridDim.x) {
+            int b, qb, h, start, len;
+            if (!decode(i, b, qb, h, start, len)) continue;
+            float m = -INFINITY, l = 0.f;
+            float o[D];
+#pragma unroll
+            for (int j = 0; j < D; ++j) o[j] = 0.f;
+            const int nkb = (len + BLK - 1) / BLK;
+            for (int kb = 0; kb < nkb; ++kb, ++blk_it) {
+                const int nvalid = min(BLK, len - kb * BLK);  // keys of this block inside the sentence
+                mbar_wait(bar_s_full, blk_it & 1);
+                tc_fence_after_sync();
+                // pass 1: row maximum over the valid keys
+                float mx = -INFINITY;
+#pragma unroll 1
+                for (int c = 0; c < BLK / 32; ++c) {
+                    uint32_t v[32];
+                    tmem_ld_32x32(t_s + c * 32, v);
+                    tmem_ld_wait();
+                    if (c * 32 + 32 <= nvalid) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(v[j]));
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)
+                            if (c * 32 + j < nvalid) mx = fmaxf(mx, __uint_as_float(v[j]));
+                    }
+                }
+                const float m_new = fmaxf(m, mx * p.scale_log2);
+                const float corr = ex2(m - m_new);
+                m = m_new;
+                // pass 2: p = exp2(s*scale - m); bf16 P into the swizzled K-major tiles; row sum
+                float lb = 0.f;
+#pragma unroll 1
+                for (int c = 0; c < BLK / 32; ++c) {
+                    uint32_t v[32];
+                    tmem_ld_32x32(t_s + c * 32, v);
+                    tmem_ld_wait();
+                    if (c == BLK / 32 - 1) {  // S fully read: the next Q.K^T may overwrite it
+                        tc_fence_before_sync();
+                        mbar_arrive(bar_s_empty);
+                    }
+                    float pj[32];
+                    if (c * 32 + 32 <= nvalid) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) pj[j] = ex2(fmaf(__uint_as_float(v[j]), p.scale_log2, -m_new));
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)
+                            pj[j] = (c * 32 + j < nvalid) ? ex2(fmaf(__uint_as_float(v[j]), p.scale_log2, -m_new)) : 0.f;
+                    }
+                    // tile (c >> 1), row `row`, 16-byte pieces (c & 1) * 4 .. +3, swizzled by row & 7
+                    const uint32_t prow = smem_p + (c >> 1) * (BLK * 128) + row * 128;
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const uint32_t w0 = pack_bf16x2(pj[q * 8 + 0], pj[q * 8 + 1]), w1 = pack_bf16x2(pj[q * 8 + 2], pj[q * 8 + 3]),
+                                       w2 = pack_bf16x2(pj[q * 8 + 4], pj[q * 8 + 5]), w3 = pack_bf16x2(pj[q * 8 + 6], pj[q * 8 + 7]);
+                        // the row sum uses the rounded values the tensor core will multiply
+                        const float2 a0 = unpack_bf16x2(w0), a1 = unpack_bf16x2(w1), a2 = unpack_bf16x2(w2), a3 = unpack_bf16x2(w3);
+                        lb += ((a0.x + a0.y) + (a1.x + a1.y)) + ((a2.x + a2.y) + (a3.x + a3.y));
+                        const uint32_t piece = ((c & 1) * 4 + q) ^ (row & 7);
+                        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(prow + (piece << 4)), "r"(w0), "r"(w1),
+                                     "r"(w2), "r"(w3)
+                                     : "memory");
+                    }
+                }
+                fence_proxy_async_smem();
+                mbar_arrive(bar_p_full);
+                l = fmaf(l, corr, lb);
+                // O = O * corr + P.V
+                mbar_wait(bar_o_full, blk_it & 1);
+                tc_fence_after_sync();
+#pragma unroll
+                for (int c = 0; c < D / 32; ++c) {
+                    uint32_t v[32];
+                    tmem_ld_32x32(t_o + c * 32, v);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) o[c * 32 + j] = fmaf(o[c * 32 + j], corr, __uint_as_float(v[j]));
+                }
+                tc_fence_before_sync();
+                mbar_arrive(bar_o_empty);
+            }
+            // finalise: O / l, staged through the (now idle) P buffer so that global stores are row-contiguous
+            const float inv = 1.0f / l;
+            constexpr int PITCH = D * 2 + 16;  // bytes; the pad spreads rows over banks
+            const uint32_t orow = smem_p + row * PITCH;
+#pragma unroll
+            for (int q = 0; q < D / 8; ++q)
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(orow + q * 16),
+                             "r"(pack_bf16x2(o[q * 8 + 0] * inv, o[q * 8 + 1] * inv)),
+                             "r"(pack_bf16x2(o[q * 8 + 2] * inv, o[q * 8 + 3] * inv)),
+                             "r"(pack_bf16x2(o[q * 8 + 4] * inv, o[q * 8 + 5] * inv)),
+                             "r"(pack_bf16x2(o[q * 8 + 6] * inv, o[q * 8 + 7] * inv))
+                             : "memory");
+            asm volatile("bar.sync 1, %0;" ::"n"(SM_THREADS) : "memory");
+            constexpr int PPR = D / 8;  // 16-byte pieces per row
+            const int t = threadIdx.x - SM_WARP0 * 32;
+            const int q0 = qb * BLK;
+#pragma unroll
+            for (int k = 0; k < PPR; ++k) {
+                const int idx = k * SM_THREADS + t;
+                const int r = idx / PPR, pc = idx % PPR;
+                if (q0 + r < len) {
+                    uint4 val;
+                    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                                 : "=r"(val.x), "=r"(val.y), "=r"(val.z), "=r"(val.w)
+                                 : "r"(smem_p + r * PITCH + pc * 16));
+                    *reinterpret_cast<uint4*>(p.ctx + static_cast<size_t>(start + q0 + r) * p.H + h * D + pc * 8) = val;
+                }
+            }
+            asm volatile("bar.sync 1, %0;" ::"n"(SM_THREADS) : "memory");  // staging reads done before the next P writes
+        }
+    }
+
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after_sync();
+        tmem_dealloc(tmem_base, TMEM_COLS);
+    }
+}
+
+PFN_cuTensorMapEncodeTiled_v12000 encode_fn() {
+    static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* ptr = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(ptr);
+    });
+    return fn;
+}
+
+template <int D>
+cudaError_t launch(const __nv_bfloat16* qkv, const int* cu, int rows_cap, int batch, int max_seqlen, int heads,
+                   __nv_bfloat16* ctx, int num_sms, cudaStream_t s) {
+    auto fn = encode_fn();
+    if (!fn) return cudaErrorInvalidValue;
+    const int H = heads * D;
+    alignas(64) CUtensorMap map;
+    cuuint64_t dims[2] = {static_cast<cuuint64_t>(3 * H), static_cast<cuuint64_t>(rows_cap)};
+    cuuint64_t strides[1] = {static_cast<cuuint64_t>(3 * H) * 2};
+    cuuint32_t box[2] = {D, BLK};
+    cuuint32_t estr[2] = {1, 1};
+    if (fn(&map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<__nv_bfloat16*>(qkv), dims, strides, box, estr,
+           CU_TENSOR_MAP_INTERLEAVE_NONE, D == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
+           CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+        return cudaErrorInvalidValue;
+    auto kern = attention_tc_kernel<D>;
+    constexpr int smem = AttnSmem<D>::BYTES;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    AttnDev p;
+    p.cu = cu; p.batch = batch; p.heads = heads; p.H = H; p.q_blocks = (max_seqlen + BLK - 1) / BLK;
+    p.scale_log2 = 1.4426950408889634f / sqrtf(static_cast<float>(D));
+    p.ctx = ctx;
+    const long long items = static_cast<long long>(batch) * heads * p.q_blocks;
+    if (items <= 0) return cudaSuccess;
+    const int ctas = num_sms * (D == 32 ? 2 : 1);
+    const int grid = static_cast<int>(items < ctas ? items : ctas);
+    kern<<<grid, ATT_THREADS, smem, s>>>(map, p);
+    return cudaGetLastError();
+}
+
+}  // namespace
+
+cudaError_t launch_attention_tc(const __nv_bfloat16* qkv, const int* cu, int rows_cap, int batch, int max_seqlen,
+                                int heads, int head_dim, __nv_bfloat16* ctx, int num_sms, cudaStream_t s) {
+    if (batch <= 0 || max_seqlen <= 0) return cudaSuccess;
+    if (static_cast<long long>(batch) * heads * ((max_seqlen + BLK - 1) / BLK) > 0x7fffffffLL) return cudaErrorInvalidValue;
+    if (head_dim == 32) return launch<32>(qkv, cu, rows_cap, batch, max_seqlen, heads, ctx, num_sms, s);
+    if (head_dim == 64) return launch<64>(qkv, cu, rows_cap, batch, max_seqlen, heads, ctx, num_sms, s);
+    return cudaErrorInvalidValue;
+}
+
+}  // namespace b200

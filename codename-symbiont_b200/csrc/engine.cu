@@ -15,6 +15,7 @@
 #include <atomic>
 #include <condition_variable>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <mutex>
@@ -107,6 +108,7 @@ struct b200_embed {
     bool fuse_ln = false;
     int bn_qkv = 0, bn_ffn1 = 0, bn_h = 0;
     int act_epi = b200::EPI_GELU_ERF;
+    bool attn_mma = false;  // B200_EMBED_ATTENTION=mma selects the mma.sync attention kernel (A/B checks)
     // weights
     float* arena32 = nullptr;
     bf16* arena16 = nullptr;
@@ -193,7 +195,7 @@ void release(b200_embed* h, Context* c) {
     h->cv.notify_one();
 }
 
-int ensure_workspace(b200_embed* h, Workspace& w, size_t rows, size_t elt) {
+int ensure_workspace(b200_embed* h, Workspace& w, size_t rows, size_t elt, cudaStream_t s) {
     rows = round_up(rows, 128);
     if (rows <= w.cap) return B200_EMBED_OK;
     w.release();
@@ -208,6 +210,15 @@ int ensure_workspace(b200_embed* h, Workspace& w, size_t rows, size_t elt) {
         CU_TRY(cudaMalloc(&w.a_lo, rows * H * elt));
     }
     if (elt == 4 || !h->fuse_ln) CU_TRY(cudaMalloc(&w.y32, rows * H * sizeof(float)));
+    // Rows past the real token count are read (never used) by 128-row tiles; keep them finite. The memsets
+    // go on the stream that will use the buffers: the contexts' streams do not synchronise with stream 0.
+    CU_TRY(cudaMemsetAsync(w.x, 0, rows * H * elt, s));
+    CU_TRY(cudaMemsetAsync(w.qkv, 0, rows * 3 * H * elt, s));
+    CU_TRY(cudaMemsetAsync(w.ctx, 0, rows * H * elt, s));
+    CU_TRY(cudaMemsetAsync(w.a, 0, rows * H * elt, s));
+    CU_TRY(cudaMemsetAsync(w.inter, 0, rows * I * elt, s));
+    if (w.x_lo) CU_TRY(cudaMemsetAsync(w.x_lo, 0, rows * H * elt, s));
+    if (w.a_lo) CU_TRY(cudaMemsetAsync(w.a_lo, 0, rows * H * elt, s));
     w.cap = rows;
     return B200_EMBED_OK;
 }
@@ -316,7 +327,7 @@ int run_chunk(b200_embed* h, Context& c, cudaStream_t s, const Job& j) {
     const int H = h->H, I = h->I, rows = j.tokens_upper;
     const float eps = h->cfg.layer_norm_eps;
     Workspace& w = fp32 ? c.ws32 : c.ws16;
-    int rc = ensure_workspace(h, w, rows, fp32 ? 4 : 2);
+    int rc = ensure_workspace(h, w, rows, fp32 ? 4 : 2, s);
     if (rc) return rc;
     if ((rc = ensure_batch_bufs(c, static_cast<size_t>(j.batch)))) return rc;
     const int* cu = j.d_cu;
@@ -372,7 +383,9 @@ int run_chunk(b200_embed* h, Context& c, cudaStream_t s, const Job& j) {
                         b200::EPI_BIAS, h->bn_qkv, nullptr, nullptr, nullptr, nullptr, qkv, nullptr, 0);
             if (rc) return rc;
             CU_TRY(timed(h, c, s, B200_EMBED_KIND_ATTENTION, 1, [&] {
-                return b200::launch_attention_bf16(qkv, cu, j.batch, j.seq_len, h->heads, h->D, ctx, s);
+                return h->attn_mma ? b200::launch_attention_bf16(qkv, cu, j.batch, j.seq_len, h->heads, h->D, ctx, s)
+                                   : b200::launch_attention_tc(qkv, cu, rows, j.batch, j.seq_len, h->heads, h->D, ctx,
+                                                               h->num_sms, s);
             }));
             if (h->fuse_ln) {
                 rc = gemm16(h, c, s, B200_EMBED_KIND_GEMM_AO, ctx, lw.ao_w16, lw.ao_b, rows, d_rows, H, H,
@@ -522,6 +535,7 @@ int32_t b200_embed_create(const b200_embed_config* cfg, const char* path, uint64
     if (h->cap_tokens < static_cast<size_t>(cfg->max_position_embeddings)) h->cap_tokens = cfg->max_position_embeddings;
     h->fuse_ln = b200::gemm_tc_pick_block_n(H, b200::EPI_RES_LN) != 0;
     h->act_epi = b200::EPI_GELU_ERF + cfg->hidden_act;
+    if (const char* v = getenv("B200_EMBED_ATTENTION")) h->attn_mma = std::string(v) == "mma";
     h->bn_qkv = b200::gemm_tc_pick_block_n(3 * H, b200::EPI_BIAS);
     h->bn_ffn1 = b200::gemm_tc_pick_block_n(I, h->act_epi);
     h->bn_h = b200::gemm_tc_pick_block_n(H, b200::EPI_GELU_ERF);  // 256 or 128 (fp32-out instantiations)
@@ -924,16 +938,18 @@ int32_t b200_op_linear(b200_embed* h, int32_t layer, int32_t which, const void* 
     return rc;
 }
 
-int32_t b200_op_attention(b200_embed* h, const void* qkv, const int32_t* cu, int32_t batch, int32_t max_seqlen,
-                          int32_t dtype, void* ctx, void* stream) {
+int32_t b200_op_attention(b200_embed* h, const void* qkv, const int32_t* cu, int32_t batch, int32_t rows,
+                          int32_t max_seqlen, int32_t dtype, void* ctx, void* stream) {
     if (!h || !qkv || !cu || !ctx) return fail(B200_EMBED_ERR_INVALID_ARG, "null argument");
     DeviceGuard guard(h->device);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     h->launches.fetch_add(1);
-    CU_TRY(dtype ? b200::launch_attention_f32(static_cast<const float*>(qkv), cu, batch, max_seqlen, h->heads, h->D,
-                                              static_cast<float*>(ctx), s)
-                 : b200::launch_attention_bf16(static_cast<const bf16*>(qkv), cu, batch, max_seqlen, h->heads, h->D,
-                                               static_cast<bf16*>(ctx), s));
+    CU_TRY(dtype == 1 ? b200::launch_attention_f32(static_cast<const float*>(qkv), cu, batch, max_seqlen, h->heads, h->D,
+                                                   static_cast<float*>(ctx), s)
+                 : dtype == 2 ? b200::launch_attention_bf16(static_cast<const bf16*>(qkv), cu, batch, max_seqlen, h->heads,
+                                                            h->D, static_cast<bf16*>(ctx), s)
+                              : b200::launch_attention_tc(static_cast<const bf16*>(qkv), cu, rows, batch, max_seqlen, h->heads,
+                                                          h->D, static_cast<bf16*>(ctx), h->num_sms, s));
     return B200_EMBED_OK;
 }
 

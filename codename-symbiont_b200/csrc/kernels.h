@@ -40,6 +40,10 @@ cudaError_t launch_mean_pool(const T* hidden, const T* hidden_lo, const int* cu,
 cudaError_t launch_attention_bf16(const __nv_bfloat16* qkv, const int* cu, int batch, int max_seqlen, int heads,
                                   int head_dim, __nv_bfloat16* ctx, cudaStream_t s);
 
+// K3 on tcgen05 (attention_tc.cu): same contract; qkv has rows_cap rows (TMA bound), persistent grid.
+cudaError_t launch_attention_tc(const __nv_bfloat16* qkv, const int* cu, int rows_cap, int batch, int max_seqlen,
+                                int heads, int head_dim, __nv_bfloat16* ctx, int num_sms, cudaStream_t s);
+
 // fp32 validation kernels (correctness only).
 cudaError_t launch_attention_f32(const float* qkv, const int* cu, int batch, int max_seqlen, int heads,
                                  int head_dim, float* ctx, cudaStream_t s);

@@ -166,8 +166,9 @@ int32_t b200_op_embed_layernorm(b200_embed* h, const uint32_t* ids_packed, const
  * 3 output.dense (+ residual + LayerNorm). residual is read only for which = 1, 3. */
 int32_t b200_op_linear(b200_embed* h, int32_t layer, int32_t which, const void* x, const void* residual,
                        const void* residual_lo, int32_t rows, int32_t dtype, void* y, void* y_lo, void* stream);
-/* K3. ctx = softmax(q k^T / sqrt(d)) v per sentence and head over packed qkv [rows, 3H]. */
-int32_t b200_op_attention(b200_embed* h, const void* qkv, const int32_t* cu_seqlens, int32_t batch,
+/* K3. ctx = softmax(q k^T / sqrt(d)) v per sentence and head over packed qkv [rows, 3H].
+ * dtype 0: tcgen05 kernel (the one the forward uses), 1: fp32 validation, 2: mma.sync bf16 kernel (A/B checks). */
+int32_t b200_op_attention(b200_embed* h, const void* qkv, const int32_t* cu_seqlens, int32_t batch, int32_t rows,
                           int32_t max_seqlen, int32_t dtype, void* ctx, void* stream);
 /* K4. out = LN(y + residual) * gamma + beta with the LayerNorm of (layer, which = 1 or 3).
  * y is fp32 when dtype = 0 came from an unfused GEMM (y_is_f32 != 0). */

@@ -137,31 +137,33 @@ def test_k2_linear_layers(env, dtype, which):
         assert np.abs(got + host(out_lo) - want).max() <= 2e-3
 
 
-@pytest.mark.parametrize("dtype", [0, 1])
+@pytest.mark.parametrize("dtype", [0, 1, 2])
 @pytest.mark.parametrize("heads,d", [(4, 32), (2, 64)])
 def test_k3_attention(env, pkg, dtype, heads, d):
     """Varlen attention vs the oracle's padded additive-mask softmax; ragged lengths incl. 1 and > 64."""
     shape = pkg.weights.BertShape(512, heads * d, 1, heads, 512, 256, 2)
-    lengths = np.array([1, 2, 63, 64, 65, 128, 200, 17])
-    S, H = 200, heads * d
+    lengths = np.array([1, 2, 63, 64, 65, 128, 200, 17, 129, 256, 255])
+    S, H = 256, heads * d
     rng = np.random.default_rng(11)
     q, k, v = (rng.standard_normal((len(lengths), S, H)).astype(np.float32) for _ in range(3))
-    if not dtype:
+    if dtype != 1:
         q, k, v = bf16_round(q), bf16_round(k), bf16_round(v)
     mask = (np.arange(S)[None, :] < lengths[:, None]).astype(np.uint32)
     with pkg.Embedder.random_init(shape, seed=1) as e:
         o = Oracle(shape, e.export_weights(), "f32")
         want = padded_to_packed(o.attention(q, k, v, mask, heads), lengths)
         qkv = np.concatenate([padded_to_packed(t, lengths) for t in (q, k, v)], axis=1)
-        td = torch.float32 if dtype else torch.bfloat16
+        td = torch.float32 if dtype == 1 else torch.bfloat16
         dq = dev(qkv, td)
         ctx = torch.full(want.shape, float("nan"), dtype=td, device="cuda")
         d_cu = dev_i32(cu_of(lengths))
-        e.op_attention(dq.data_ptr(), d_cu.data_ptr(), len(lengths), int(lengths.max()), dtype, ctx.data_ptr())
+        e.op_attention(dq.data_ptr(), d_cu.data_ptr(), len(lengths), qkv.shape[0], int(lengths.max()), dtype,
+                       ctx.data_ptr())
         got = host(ctx)
-    tol = 2e-5 if dtype else 0.02  # bf16 P and output rounding on |ctx| <~ 3
+    tol = 2e-5 if dtype == 1 else 0.02  # bf16 P and output rounding on |ctx| <~ 3
+    assert np.isfinite(got).all()
     assert np.abs(got - want).max() <= tol, np.abs(got - want).max()
-    assert cos_rows(got, want).min() >= (0.999999 if dtype else 0.9998)
+    assert cos_rows(got, want).min() >= (0.999999 if dtype == 1 else 0.9998)
 
 
 @pytest.mark.parametrize("mode", ["bf16", "f32y", "fp32"])
