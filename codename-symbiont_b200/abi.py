@@ -20,6 +20,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libb200_embed.so")
 HEADER_PATH = os.path.join(HERE, "..", "include", "b200_embed.h")
 
+NOALLOC_MAX_ELEMS = 1 << 20  # B200_OP_NOALLOC_MAX_ELEMS
 FLAG_NORMALIZE = 1
 FLAG_FP32 = 2
 ERR_NAMES = {0: "OK", -1: "INVALID_ARG", -2: "CUDA", -3: "OOM", -4: "UNSUPPORTED_SHAPE", -5: "NO_DEVICE", -6: "IO"}
@@ -65,6 +66,7 @@ _SIGNATURES = {
     "b200_embed_profile_read": (C.c_int32, [_P, C.POINTER(KindStats), C.c_int32]),
     "b200_op_embed_layernorm": (C.c_int32, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, _P, _P, _P]),
     "b200_op_linear": (C.c_int32, [_P, C.c_int32, C.c_int32, _P, _P, _P, C.c_int32, C.c_int32, _P, _P, _P]),
+    "b200_op_linear_noalloc": (C.c_int32, [_P, C.c_int32, C.c_int32, _P, _P, _P, C.c_int32, C.c_int32, _P, _P, _P]),
     "b200_op_attention": (C.c_int32, [_P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P, _P]),
     "b200_op_add_layernorm": (C.c_int32, [_P, C.c_int32, C.c_int32, _P, C.c_int32, _P, _P, C.c_int32, C.c_int32, _P, _P,
                                           _P]),
@@ -254,6 +256,12 @@ class Embedder:
     def op_linear(self, layer, which, d_x, d_residual, rows, dtype, d_y, d_residual_lo=0, d_y_lo=0, stream=0):
         _check(self.lib.b200_op_linear(self.h, layer, which, d_x, d_residual or None, d_residual_lo or None, rows, dtype,
                                        d_y, d_y_lo or None, stream or None))
+
+    def op_linear_noalloc(self, layer, which, d_x, d_residual, rows, dtype, d_y, d_residual_lo=0, d_y_lo=0, stream=0):
+        """b200_op_linear for which = 1 / 3 with the fp32 temporary in the library's built-in 4 MiB scratch: no
+        cudaMalloc / cudaFree. rows * hidden must fit NOALLOC_MAX_ELEMS; overlapping calls race on the scratch."""
+        _check(self.lib.b200_op_linear_noalloc(self.h, layer, which, d_x, d_residual or None, d_residual_lo or None, rows,
+                                               dtype, d_y, d_y_lo or None, stream or None))
 
     def op_attention(self, d_qkv, d_cu, batch, rows, max_seqlen, dtype, d_ctx, stream=0):
         _check(self.lib.b200_op_attention(self.h, d_qkv, d_cu, batch, rows, max_seqlen, dtype, d_ctx, stream or None))

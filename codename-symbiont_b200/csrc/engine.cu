@@ -1009,3 +1009,74 @@ int32_t b200_op_gemm_bf16(const void* a, const void* b, const float* bias, int32
 }
 
 }  // extern "C"
+
+// =============================================================================================
+// b200_op_linear_noalloc: the unfused Linear + residual + LayerNorm step without any allocation
+// =============================================================================================
+// The pre-LayerNorm fp32 rows that b200_op_linear keeps in a cudaMalloc'ed temporary live here instead, in
+// device memory that is part of the loaded library image. Every GPU that loads the library carries these
+// 4 MiB until the process exits, used or not.
+static __device__ __align__(256) float g_noalloc_scratch[B200_OP_NOALLOC_MAX_ELEMS];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_noalloc_mu;
+float* g_noalloc_ptr[kMaxDevices] = {};
+
+// In host code `g_noalloc_scratch` is only a handle for the symbol, not an address a kernel can use: ask the
+// runtime for the device address once per device (with that device current) and hand that to the kernels.
+int noalloc_scratch(int device, float** out) {
+    if (device < 0 || device >= kMaxDevices) return fail(B200_EMBED_ERR_INVALID_ARG, "device ordinal too large");
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[device]) {
+        void* p = nullptr;
+        CU_TRY(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        g_noalloc_ptr[device] = static_cast<float*>(p);
+    }
+    *out = g_noalloc_ptr[device];
+    return B200_EMBED_OK;
+}
+}  // namespace
+
+extern "C" int32_t b200_op_linear_noalloc(b200_embed* h, int32_t layer, int32_t which, const void* x,
+                                          const void* residual, const void* residual_lo, int32_t rows, int32_t dtype,
+                                          void* y, void* y_lo, void* stream) {
+    if (!h || !x || !residual || !y || layer < 0 || layer >= h->L || (which != 1 && which != 3) || rows < 0)
+        return fail(B200_EMBED_ERR_INVALID_ARG, "b200_op_linear_noalloc: bad argument (which must be 1 or 3)");
+    if (dtype != 0 && dtype != 1) return fail(B200_EMBED_ERR_INVALID_ARG, "b200_op_linear_noalloc: dtype must be 0 or 1");
+    const int H = h->H, I = h->I;
+    if (static_cast<long long>(rows) * H > static_cast<long long>(B200_OP_NOALLOC_MAX_ELEMS))
+        return fail(B200_EMBED_ERR_INVALID_ARG,
+                    "b200_op_linear_noalloc: rows*hidden = " + std::to_string(static_cast<long long>(rows) * H) +
+                        " exceeds the built-in scratch of " + std::to_string(B200_OP_NOALLOC_MAX_ELEMS) +
+                        " floats (4 MiB); use b200_op_linear or split the rows");
+    if (rows == 0) return B200_EMBED_OK;
+    DeviceGuard guard(h->device);
+    if (!guard.ok) return fail(B200_EMBED_ERR_CUDA, "cudaSetDevice failed");
+    float* scratch = nullptr;
+    int rc = noalloc_scratch(h->device, &scratch);
+    if (rc) return rc;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const LayerW& w = h->layers[layer];
+    const float eps = h->cfg.layer_norm_eps;
+    const int k = which == 1 ? H : I;
+    const float* gam = which == 1 ? w.ao_g : w.o_g;
+    const float* bet = which == 1 ? w.ao_be : w.o_be;
+    const float* bias = which == 1 ? w.ao_b : w.o_b;
+    h->launches.fetch_add(2);
+    if (dtype == 1) {
+        CU_TRY(b200::launch_gemm_f32(static_cast<const float*>(x), which == 1 ? w.ao_w : w.o_w, bias, rows, nullptr, H, k,
+                                     -1, scratch, s));
+        CU_TRY((b200::launch_add_layernorm<float, float>(scratch, static_cast<const float*>(residual), nullptr, rows,
+                                                         nullptr, gam, bet, eps, H, static_cast<float*>(y), nullptr, s)));
+        return B200_EMBED_OK;
+    }
+    b200::GemmTcArgs g{};
+    g.a = x; g.b = which == 1 ? w.ao_w16 : w.o_w16; g.m = rows; g.n = H; g.k = k; g.bias = bias; g.eps = eps;
+    g.out = scratch; g.out_f32 = 1; g.epi = b200::EPI_BIAS; g.block_n = h->bn_h;
+    CU_TRY(b200::gemm_tc_launch(g, s, h->num_sms));
+    CU_TRY((b200::launch_add_layernorm<float, bf16>(scratch, static_cast<const bf16*>(residual),
+                                                    static_cast<const bf16*>(residual_lo), rows, nullptr, gam, bet, eps, H,
+                                                    static_cast<bf16*>(y), static_cast<bf16*>(y_lo), s)));
+    return B200_EMBED_OK;
+}

@@ -166,6 +166,27 @@ int32_t b200_op_embed_layernorm(b200_embed* h, const uint32_t* ids_packed, const
  * 3 output.dense (+ residual + LayerNorm). residual is read only for which = 1, 3. */
 int32_t b200_op_linear(b200_embed* h, int32_t layer, int32_t which, const void* x, const void* residual,
                        const void* residual_lo, int32_t rows, int32_t dtype, void* y, void* y_lo, void* stream);
+/* The same Linear + residual + LayerNorm step as b200_op_linear(which = 1 or 3) for callers that must not
+ * allocate. It has no counterpart in the reference. b200_op_linear parks the fp32 pre-LayerNorm rows in a
+ * cudaMalloc'ed temporary when the LayerNorm is not fused into the GEMM (hidden sizes other than 128/256/384,
+ * and the fp32 mode); cudaMalloc and cudaFree are off limits for a caller that has already handed every byte
+ * of the GPU to its own pool, and they synchronise the whole device, which a caller with other streams in
+ * flight in a latency-bound loop cannot afford. Here those rows go to a fixed 4 MiB array that is part of the
+ * library image instead (resident on every GPU that loads the library until the process exits), and the call
+ * runs the GEMM and the add + LayerNorm kernel back to back on `stream`; it never calls cudaMalloc, cudaFree
+ * or any allocating library routine.
+ *   - rows * hidden_size must not exceed B200_OP_NOALLOC_MAX_ELEMS (else B200_EMBED_ERR_INVALID_ARG).
+ *   - The first call on a device looks up the array's device address (cudaGetSymbolAddress); make that first
+ *     call outside any stream capture.
+ *   - All calls share the one array and it keeps whatever the last call left there. Nothing in it has to start
+ *     at zero (every row that is read is written first), but two calls that overlap on the GPU -- different
+ *     streams, different handles, different threads -- race on it: serialise them.
+ * Arguments and results are those of b200_op_linear; which = 0 / 2 use no temporary and are not offered. */
+#define B200_OP_NOALLOC_MAX_ELEMS (1 << 20)
+int32_t b200_op_linear_noalloc(b200_embed* h, int32_t layer, int32_t which, const void* x, const void* residual,
+                               const void* residual_lo, int32_t rows, int32_t dtype, void* y, void* y_lo,
+                               void* stream);
+
 /* K3. ctx = softmax(q k^T / sqrt(d)) v per sentence and head over packed qkv [rows, 3H].
  * dtype 0: tcgen05 kernel (the one the forward uses), 1: fp32 validation, 2: mma.sync bf16 kernel (A/B checks). */
 int32_t b200_op_attention(b200_embed* h, const void* qkv, const int32_t* cu_seqlens, int32_t batch, int32_t rows,
