@@ -149,6 +149,7 @@ def cpu_reference_path(pkg, shape, n_sentences, s, schedule, seed=42):
     from oracle.oracle import Oracle
     w = pkg.weights.init_weights(shape, 1234)
     o = Oracle(shape, w, "f32")
+    o.use_all_cores()
     pad = shape.max_position_embeddings if schedule == "reference" else s
     ids, mask, tt = pkg.synth.padded_batch(shape.vocab_size, pkg.synth.lengths_dense(n_sentences, s), pad, seed=seed)
     chunk = 8 if schedule == "reference" else n_sentences

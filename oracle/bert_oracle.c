@@ -90,6 +90,14 @@ typedef struct {
 
 int oracle_real_bytes(void) { return (int)sizeof(real); }
 
+void oracle_set_num_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 int oracle_num_threads(void) {
 #ifdef _OPENMP
     return omp_get_max_threads();

@@ -89,6 +89,12 @@ class Oracle:
     def threads(self) -> int:
         return int(self.lib.oracle_num_threads())
 
+    def use_all_cores(self) -> int:
+        """torchrun exports OMP_NUM_THREADS=1; the CPU baseline is meant to use every host core."""
+        n = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+        self.lib.oracle_set_num_threads(n)
+        return self.threads
+
     def layer(self, i: int, name: str) -> np.ndarray:
         return self._keep[f"encoder.layer.{i}.{name}"]
 
