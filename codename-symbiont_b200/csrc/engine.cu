@@ -106,7 +106,7 @@ struct b200_embed {
     int H = 0, I = 0, L = 0, heads = 0, D = 0;
     size_t cap_tokens = 0;
     bool fuse_ln = false;
-    int bn_qkv = 0, bn_ffn1 = 0, bn_h = 0;
+    int bn_qkv = 0, bn_ffn1 = 0, bn_h = 0, bn_ln = 0;
     int act_epi = b200::EPI_GELU_ERF;
     bool attn_mma = false;  // B200_EMBED_ATTENTION=mma selects the mma.sync attention kernel (A/B checks)
     // weights
@@ -389,7 +389,7 @@ int run_chunk(b200_embed* h, Context& c, cudaStream_t s, const Job& j) {
             }));
             if (h->fuse_ln) {
                 rc = gemm16(h, c, s, B200_EMBED_KIND_GEMM_AO, ctx, lw.ao_w16, lw.ao_b, rows, d_rows, H, H,
-                            b200::EPI_RES_LN, H, x, x_lo, lw.ao_g, lw.ao_be, a, a_lo, 0);
+                            b200::EPI_RES_LN, h->bn_ln, x, x_lo, lw.ao_g, lw.ao_be, a, a_lo, 0);
                 if (rc) return rc;
             } else {
                 rc = gemm16(h, c, s, B200_EMBED_KIND_GEMM_AO, ctx, lw.ao_w16, lw.ao_b, rows, d_rows, H, H,
@@ -404,7 +404,7 @@ int run_chunk(b200_embed* h, Context& c, cudaStream_t s, const Job& j) {
             if (rc) return rc;
             if (h->fuse_ln) {
                 rc = gemm16(h, c, s, B200_EMBED_KIND_GEMM_FFN2, inter, lw.o_w16, lw.o_b, rows, d_rows, H, I,
-                            b200::EPI_RES_LN, H, a, a_lo, lw.o_g, lw.o_be, x, x_lo, 0);
+                            b200::EPI_RES_LN, h->bn_ln, a, a_lo, lw.o_g, lw.o_be, x, x_lo, 0);
                 if (rc) return rc;
             } else {
                 rc = gemm16(h, c, s, B200_EMBED_KIND_GEMM_FFN2, inter, lw.o_w16, lw.o_b, rows, d_rows, H, I,
@@ -533,7 +533,9 @@ int32_t b200_embed_create(const b200_embed_config* cfg, const char* path, uint64
     h->H = H; h->I = I; h->L = L; h->heads = heads; h->D = H / heads;
     h->cap_tokens = cfg->max_tokens_per_launch > 0 ? static_cast<size_t>(cfg->max_tokens_per_launch) : (1u << 20);
     if (h->cap_tokens < static_cast<size_t>(cfg->max_position_embeddings)) h->cap_tokens = cfg->max_position_embeddings;
-    h->fuse_ln = b200::gemm_tc_pick_block_n(H, b200::EPI_RES_LN) != 0;
+    h->bn_ln = b200::gemm_tc_pick_block_n(H, b200::EPI_RES_LN);
+    h->fuse_ln = h->bn_ln != 0;
+    if (const char* v = getenv("B200_EMBED_FUSE_LN")) h->fuse_ln = h->fuse_ln && std::string(v) != "0";
     h->act_epi = b200::EPI_GELU_ERF + cfg->hidden_act;
     if (const char* v = getenv("B200_EMBED_ATTENTION")) h->attn_mma = std::string(v) == "mma";
     h->bn_qkv = b200::gemm_tc_pick_block_n(3 * H, b200::EPI_BIAS);
@@ -919,8 +921,8 @@ int32_t b200_op_linear(b200_embed* h, int32_t layer, int32_t which, const void* 
     }
     if (h->fuse_ln)
         return gemm16(h, c, s, which == 1 ? B200_EMBED_KIND_GEMM_AO : B200_EMBED_KIND_GEMM_FFN2, x, w16[which],
-                      bias[which], rows, nullptr, H, k[which], b200::EPI_RES_LN, H, residual, residual_lo, gam, bet, y,
-                      y_lo, 0);
+                      bias[which], rows, nullptr, H, k[which], b200::EPI_RES_LN, h->bn_ln, residual, residual_lo, gam, bet,
+                      y, y_lo, 0);
     float* tmp = nullptr;
     CU_TRY(cudaMalloc(&tmp, (size_t)rows * H * 4));
     int rc = gemm16(h, c, s, which == 1 ? B200_EMBED_KIND_GEMM_AO : B200_EMBED_KIND_GEMM_FFN2, x, w16[which],

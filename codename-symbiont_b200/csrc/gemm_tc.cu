@@ -20,7 +20,10 @@
 // residual add + LayerNorm run in the epilogue (EPI_RES_LN): pass 1 adds bias and the residual
 // (TMA-loaded per chunk into a per-warp ring, prefetched one tile ahead), parks the sum back in TMEM
 // and accumulates the row statistics; pass 2 normalises and stores. The pre-LN activations never
-// reach HBM. Both operands are K-major ("TN"): activations [M,K] and HF weights [N,K] as stored.
+// reach HBM. For N = 384 / 768 the row is split over a thread-block CLUSTER of 2 / 4 CTAs (192 columns each, so
+// the TMEM accumulators stay double-buffered and the smem stages small); the CTAs of a cluster walk the same row
+// blocks and exchange their per-row partial (sum, sum of squares) through distributed shared memory.
+// Both operands are K-major ("TN"): activations [M,K] and HF weights [N,K] as stored.
 #include "gemm_tc.h"
 
 #include <cuda.h>
@@ -52,16 +55,60 @@ __host__ __device__ constexpr int b_stage_bytes(int block_n) { return block_n * 
 __host__ __device__ constexpr int epi_warp_bytes(int epi, bool out_f32) {
     return (epi == EPI_RES_LN ? 2 * 2 * CHUNK_BF16 : 0) + 2 * (out_f32 ? CHUNK_F32 : CHUNK_BF16);
 }
-// mbarriers (<= 8 + 8 stage, 4 TMEM, 16 residual) + TMEM pointer + LayerNorm partial statistics
-constexpr int AUX_BYTES = 512 + 2 * BLOCK_M * 8;
+// mbarriers (<= 8 + 8 stage, 4 TMEM, 16 residual, 2 cluster exchange) + TMEM pointer, then the LayerNorm partial
+// statistics of the two column halves, then (clusters) the slots peers write their row partials into
+constexpr int MAX_CLUSTER = 4;
+constexpr int AUX_BARRIERS = 512;
+constexpr int AUX_LN_PART = 2 * BLOCK_M * 8;
+constexpr int AUX_LN_PEER = 2 * MAX_CLUSTER * BLOCK_M * 8;  // [tile parity][sender rank][row] float2
+__host__ __device__ constexpr int aux_bytes(int epi) {
+    return AUX_BARRIERS + (epi == EPI_RES_LN ? AUX_LN_PART + AUX_LN_PEER : 0);
+}
 __host__ __device__ constexpr int num_stages(int block_n, int epi, bool out_f32) {
-    int s = (SMEM_LIMIT - AUX_BYTES - EPI_WARPS * epi_warp_bytes(epi, out_f32)) /
+    int s = (SMEM_LIMIT - aux_bytes(epi) - EPI_WARPS * epi_warp_bytes(epi, out_f32)) /
             (A_STAGE_BYTES + b_stage_bytes(block_n));
     return s > 8 ? 8 : s;
 }
 __host__ __device__ constexpr int smem_bytes(int block_n, int epi, bool out_f32) {
     return num_stages(block_n, epi, out_f32) * (A_STAGE_BYTES + b_stage_bytes(block_n)) +
-           EPI_WARPS * epi_warp_bytes(epi, out_f32) + AUX_BYTES;
+           EPI_WARPS * epi_warp_bytes(epi, out_f32) + aux_bytes(epi);
+}
+
+// ---- thread-block cluster helpers (distributed shared memory) ----
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t local_smem, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_smem), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void st_cluster_f32x2(uint32_t addr, float a, float b) {
+    asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" ::"r"(addr), "f"(a), "f"(b) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t remote_bar) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote_bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    long long t0 = 0;
+    for (uint32_t it = 0;; ++it) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (done) break;
+        if (it == 64) t0 = clock64();
+        if (it > 64 && (it & 63) == 0 && clock64() - t0 > 8000000000LL) __trap();
+    }
 }
 
 struct GemmDev {
@@ -149,7 +196,7 @@ __device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
     return v;
 }
 
-template <int BLOCK_N, int EPI, typename OutT>
+template <int BLOCK_N, int EPI, typename OutT, int CL>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const __grid_constant__ CUtensorMap tmap_c, const __grid_constant__ CUtensorMap tmap_c_lo,
@@ -169,6 +216,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     static_assert(HALF_N % CHUNK == 0, "epilogue works in 32-column chunks");
     static_assert(STAGES >= 2, "not enough shared memory for a pipeline");
     static_assert(EPI != EPI_RES_LN || !OUT_F32, "LayerNorm epilogue writes bf16 (hi, lo)");
+    static_assert(CL == 1 || EPI == EPI_RES_LN, "clusters are only used to split LayerNorm rows");
+    static_assert(CL <= MAX_CLUSTER, "cluster too large");
 
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     const uint32_t base = smem_u32(smem_raw);
@@ -184,8 +233,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     const uint32_t bar_tempty = aux + 144;  // 2 x 8 B
     const uint32_t bar_res = aux + 192;     // EPI_WARPS x 2 x 8 B (residual ring, one pair per epilogue warp)
     const uint32_t tmem_slot = aux + 320;   // 4 B
+    const uint32_t bar_ln = aux + 336;      // 2 x 8 B: peers' row partials have arrived (per tile parity)
     volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(aux_ptr + 320);
-    float2* ln_part = reinterpret_cast<float2*>(aux_ptr + 512);  // [2][BLOCK_M]
+    float2* ln_part = reinterpret_cast<float2*>(aux_ptr + AUX_BARRIERS);                // [2][BLOCK_M]
+    float2* ln_peer = reinterpret_cast<float2*>(aux_ptr + AUX_BARRIERS + AUX_LN_PART);  // [2][MAX_CLUSTER][BLOCK_M]
+    const uint32_t ln_peer_addr = aux + AUX_BARRIERS + AUX_LN_PART;
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -196,9 +248,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         rows = r < rows ? r : rows;
     }
     const int num_m_tiles = (rows + BLOCK_M - 1) / BLOCK_M;
-    const int num_n_tiles = p.n / BLOCK_N;
-    const int num_tiles = num_m_tiles * num_n_tiles;
+    const int num_n_tiles = p.n / BLOCK_N;  // == CL when the row is split over a cluster
     const int num_kb = (p.k + BLOCK_K - 1) / BLOCK_K;
+    // Work units: CL == 1: unit = (m_tile, n_tile), one CTA each. CL > 1: unit = m_tile, shared by the CL CTAs of
+    // a cluster, CTA `crank` taking columns [crank * BLOCK_N, +BLOCK_N). All CTAs of a cluster see the same units.
+    const int crank = CL > 1 ? static_cast<int>(cluster_ctarank()) : 0;
+    const int num_tiles = CL > 1 ? num_m_tiles : num_m_tiles * num_n_tiles;
+    const int tile0 = static_cast<int>(blockIdx.x) / CL;
+    const int tile_step = static_cast<int>(gridDim.x) / CL;
+    auto tile_m = [&](int t) { return CL > 1 ? t : t / num_n_tiles; };
+    auto tile_n = [&](int t) { return CL > 1 ? crank : t % num_n_tiles; };
 
     if (threadIdx.x == 0) {
         prefetch_tmap(&tmap_a);
@@ -213,11 +272,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             mbar_init(bar_tempty + 8 * s, EPI_THREADS);
         }
         for (int s = 0; s < 2 * EPI_WARPS; ++s) mbar_init(bar_res + 8 * s, 1);
+        for (int s = 0; s < 2; ++s) mbar_init(bar_ln + 8 * s, CL > 1 ? (CL - 1) * BLOCK_M : 1);
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc(tmem_slot, 512);
     tc_fence_before_sync();
     __syncthreads();
+    if constexpr (CL > 1) cluster_sync_all();  // peers' barriers exist before anyone arrives on them remotely
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot_ptr;
 
@@ -226,8 +287,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-                const int m_tile = t / num_n_tiles, n_tile = t % num_n_tiles;
+            for (int t = tile0; t < num_tiles; t += tile_step) {
+                const int m_tile = tile_m(t), n_tile = tile_n(t);
                 for (int kb = 0; kb < num_kb; ++kb) {
                     mbar_wait(bar_empty + 8 * stage, phase ^ 1);
                     mbar_arrive_expect_tx(bar_full + 8 * stage, A_STAGE_BYTES + B_STAGE_BYTES);
@@ -248,7 +309,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             int stage = 0;
             uint32_t phase = 0;
             int it = 0;
-            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+            for (int t = tile0; t < num_tiles; t += tile_step, ++it) {
                 const int acc = it % ACC_STAGES;
                 const uint32_t acc_phase = (it / ACC_STAGES) & 1;
                 mbar_wait(bar_tempty + 8 * acc, acc_phase ^ 1);
@@ -306,7 +367,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         uint32_t ld_issued = 0, ld_used = 0;
         auto issue_residual = [&](int tile, int c) {
             if (lane == 0) {
-                const int m_tile = tile / num_n_tiles, n_tile = tile % num_n_tiles;
+                const int m_tile = tile_m(tile), n_tile = tile_n(tile);
                 const uint32_t s = ld_issued & 1;
                 const uint32_t bar = bar_res + 8 * (2 * ew + s);
                 const uint32_t dst = my_smem + s * (2 * CHUNK_BF16);
@@ -318,15 +379,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             ++ld_issued;
         };
         if constexpr (EPI == EPI_RES_LN) {
-            if (static_cast<int>(blockIdx.x) < num_tiles) {
-                issue_residual(blockIdx.x, 0);
-                if (NCH > 1) issue_residual(blockIdx.x, 1);
+            if (tile0 < num_tiles) {
+                issue_residual(tile0, 0);
+                if (NCH > 1) issue_residual(tile0, 1);
             }
         }
 
         int it = 0;
-        for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
-            const int m_tile = t / num_n_tiles, n_tile = t % num_n_tiles;
+        for (int t = tile0; t < num_tiles; t += tile_step, ++it) {
+            const int m_tile = tile_m(t), n_tile = tile_n(t);
             const int acc = it % ACC_STAGES;
             const uint32_t acc_phase = (it / ACC_STAGES) & 1;
             const int row0 = m_tile * BLOCK_M + quad * 32;
@@ -405,16 +466,40 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     tmem_st_32x32(taddr + c * CHUNK, v);
                     __syncwarp();  // every lane has read this ring stage: refill it
                     if (c + 2 < NCH) issue_residual(t, c + 2);
-                    else if (t + static_cast<int>(gridDim.x) < num_tiles && c + 2 - NCH < NCH)
-                        issue_residual(t + gridDim.x, c + 2 - NCH);  // prefetch the next tile's first chunks
+                    else if (t + tile_step < num_tiles && c + 2 - NCH < NCH)
+                        issue_residual(t + tile_step, c + 2 - NCH);  // prefetch the next tile's first chunks
                 }
                 tmem_st_wait();
                 ln_part[half * BLOCK_M + row_in_tile] = make_float2(sum, sumsq);
                 asm volatile("bar.sync 1, %0;" ::"n"(EPI_THREADS) : "memory");
                 const float2 other = ln_part[(half ^ 1) * BLOCK_M + row_in_tile];
+                sum += other.x;
+                sumsq += other.y;
+                if constexpr (CL > 1) {
+                    // this CTA's 2 x 128 threads now hold the partials of its BLOCK_N columns; one thread per row
+                    // publishes them into every peer's slot [tile parity][my rank][row] and arrives on its barrier
+                    const uint32_t par = it & 1;
+                    if (half == 0) {
+#pragma unroll
+                        for (int pr = 0; pr < CL; ++pr) {
+                            if (pr == crank) continue;
+                            const uint32_t slot = ln_peer_addr + ((par * MAX_CLUSTER + crank) * BLOCK_M + row_in_tile) * 8;
+                            st_cluster_f32x2(map_to_cta(slot, pr), sum, sumsq);
+                            mbar_arrive_cluster(map_to_cta(bar_ln + 8 * par, pr));
+                        }
+                    }
+                    mbar_wait_cluster(bar_ln + 8 * par, (it >> 1) & 1);
+#pragma unroll
+                    for (int pr = 0; pr < CL; ++pr) {
+                        if (pr == crank) continue;
+                        const float2 o = ln_peer[(par * MAX_CLUSTER + pr) * BLOCK_M + row_in_tile];
+                        sum += o.x;
+                        sumsq += o.y;
+                    }
+                }
                 const float inv_n = 1.0f / static_cast<float>(p.n);
-                const float mean = (sum + other.x) * inv_n;
-                const float var = fmaxf((sumsq + other.y) * inv_n - mean * mean, 0.f);
+                const float mean = sum * inv_n;
+                const float var = fmaxf(sumsq * inv_n - mean * mean, 0.f);
                 const float rstd = rsqrtf(var + p.eps);
                 // pass 2: normalise, scale, shift, store (hi, lo)
 #pragma unroll 1
@@ -450,6 +535,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 
     tc_fence_before_sync();
     __syncthreads();
+    if constexpr (CL > 1) cluster_sync_all();  // no CTA leaves while a peer may still write into its shared memory
     if (warp == 2) {
         tc_fence_after_sync();
         tmem_dealloc(tmem_base, 512);
@@ -488,7 +574,7 @@ bool make_tmap(CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t cols, 
     return r == CUDA_SUCCESS;
 }
 
-template <int BLOCK_N, int EPI, typename OutT>
+template <int BLOCK_N, int EPI, typename OutT, int CL = 1>
 cudaError_t launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms) {
     constexpr int NSPLIT = BLOCK_N > 256 ? 2 : 1;
     constexpr bool OUT_F32 = sizeof(OutT) == 4;
@@ -508,7 +594,7 @@ cudaError_t launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms) {
         if (a.residual_lo && !make_tmap(&trl, a.residual_lo, a.m, a.n, CHUNK, 32, false, csw))
             return cudaErrorInvalidValue;
     }
-    auto kern = gemm_tc_kernel<BLOCK_N, EPI, OutT>;
+    auto kern = gemm_tc_kernel<BLOCK_N, EPI, OutT, CL>;
     constexpr int smem = smem_bytes(BLOCK_N, EPI, OUT_F32);
     static_assert(smem <= SMEM_LIMIT, "shared memory budget exceeded");
     static bool attr_set = false;  // per instantiation; benign race (idempotent)
@@ -521,17 +607,50 @@ cudaError_t launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms) {
     p.m = a.m; p.d_rows = a.d_rows; p.n = a.n; p.k = a.k; p.bias = a.bias;
     p.gamma = a.gamma; p.beta = a.beta; p.eps = a.eps;
     p.has_res_lo = a.residual_lo != nullptr; p.has_out_lo = a.out_lo != nullptr;
-    const int tiles = ((a.m + BLOCK_M - 1) / BLOCK_M) * (a.n / BLOCK_N);
-    const int grid = tiles < num_sms ? tiles : num_sms;
+    const int m_tiles = (a.m + BLOCK_M - 1) / BLOCK_M;
+    const int units = CL > 1 ? m_tiles : m_tiles * (a.n / BLOCK_N);
+    cudaLaunchConfig_t cfg{};
+    cfg.blockDim = dim3(NUM_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CL;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = CL > 1 ? 1 : 0;
+    // persistent grid: as many clusters as the device can hold at once (size-4 clusters do not tile all 148 SMs)
+    static int max_units = 0;
+    if (max_units == 0) {
+        max_units = num_sms / CL;
+        if (CL > 1) {
+            cfg.gridDim = dim3((num_sms / CL) * CL);
+            int n = 0;
+            if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) == cudaSuccess && n > 0 && n < max_units) max_units = n;
+        }
+    }
+    const int grid = (units < max_units ? units : max_units) * CL;
     if (grid <= 0) return cudaSuccess;
-    kern<<<grid, NUM_THREADS, smem, stream>>>(ta, tb, tc, tcl, tr, trl, p);
-    return cudaGetLastError();
+    cfg.gridDim = dim3(grid);
+    return cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, tcl, tr, trl, p);
 }
 
 }  // namespace
 
+int gemm_tc_pick_cluster(int n, int epi) {
+    if (epi != EPI_RES_LN) return 1;
+    if (n == 128 || n == 256) return 1;
+    if (n == 384 || n == 512) return 2;
+    if (n == 768 || n == 1024) return 4;
+    return 0;
+}
+
 int gemm_tc_pick_block_n(int n, int epi) {
-    if (epi == EPI_RES_LN) return (n == 128 || n == 256 || n == 384) ? n : 0;
+    if (epi == EPI_RES_LN) {
+        const int cl = gemm_tc_pick_cluster(n, epi);
+        return cl ? n / cl : 0;
+    }
     if (n % 256 == 0) return 256;
     if (epi == EPI_BIAS && n % 192 == 0) return 192;
     if (n % 128 == 0) return 128;
@@ -542,6 +661,16 @@ cudaError_t gemm_tc_launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms
     if (a.m <= 0) return cudaSuccess;
     // TMA needs 16-byte row pitches: k % 8 (bf16 operands) and n % 8 (bf16 output rows)
     if (a.k % 8 != 0 || a.n % a.block_n != 0) return cudaErrorInvalidValue;
+    if (a.epi == EPI_RES_LN) {  // a CTA, or a cluster of 2 / 4 CTAs, owns whole rows
+        const int cl = a.n / a.block_n;
+        if (a.block_n == 128 && cl == 1) return launch<128, EPI_RES_LN, __nv_bfloat16, 1>(a, stream, num_sms);
+        if (a.block_n == 256 && cl == 1) return launch<256, EPI_RES_LN, __nv_bfloat16, 1>(a, stream, num_sms);
+        if (a.block_n == 192 && cl == 2) return launch<192, EPI_RES_LN, __nv_bfloat16, 2>(a, stream, num_sms);
+        if (a.block_n == 256 && cl == 2) return launch<256, EPI_RES_LN, __nv_bfloat16, 2>(a, stream, num_sms);
+        if (a.block_n == 192 && cl == 4) return launch<192, EPI_RES_LN, __nv_bfloat16, 4>(a, stream, num_sms);
+        if (a.block_n == 256 && cl == 4) return launch<256, EPI_RES_LN, __nv_bfloat16, 4>(a, stream, num_sms);
+        return cudaErrorInvalidValue;
+    }
 #define B200_CASE(BN, EP, T) \
     if (a.block_n == BN && a.epi == EP && a.out_f32 == (sizeof(T) == 4)) return launch<BN, EP, T>(a, stream, num_sms);
     B200_CASE(128, EPI_BIAS, __nv_bfloat16)
@@ -555,9 +684,6 @@ cudaError_t gemm_tc_launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms
     B200_CASE(256, EPI_GELU_TANH, __nv_bfloat16)
     B200_CASE(128, EPI_RELU, __nv_bfloat16)
     B200_CASE(256, EPI_RELU, __nv_bfloat16)
-    B200_CASE(128, EPI_RES_LN, __nv_bfloat16)
-    B200_CASE(256, EPI_RES_LN, __nv_bfloat16)
-    B200_CASE(384, EPI_RES_LN, __nv_bfloat16)
 #undef B200_CASE
     return cudaErrorInvalidValue;
 }

@@ -9,7 +9,7 @@ enum GemmEpilogue {
     EPI_GELU_ERF = 1,   // y = gelu_erf(x.W^T + b)      (candle HiddenAct::Gelu)
     EPI_GELU_TANH = 2,  // tanh-form GELU               (HiddenAct::GeluApproximate)
     EPI_RELU = 3,       // relu                         (HiddenAct::Relu)
-    EPI_RES_LN = 4,     // y = LayerNorm(x.W^T + b + residual); needs block_n == n
+    EPI_RES_LN = 4,     // y = LayerNorm(x.W^T + b + residual); block_n * cluster size == n
 };
 
 struct GemmTcArgs {
@@ -27,9 +27,11 @@ struct GemmTcArgs {
     void* out_lo;          // EPI_RES_LN: optional [m, n] bf16 low half of the output
     int out_f32;           // only with EPI_BIAS
     int epi;               // GemmEpilogue
-    int block_n;           // 128, 192, 256 (EPI_RES_LN: == n, one of 128/256/384)
+    int block_n;           // 128, 192, 256 (EPI_RES_LN: n / cluster size, from gemm_tc_pick_block_n)
 };
 
+// EPI_RES_LN: CTAs per cluster that share one row block (1, 2 or 4); 0 if this N cannot be fused.
+int gemm_tc_pick_cluster(int n, int epi);
 // Largest supported tile width for this N and epilogue; 0 if none.
 int gemm_tc_pick_block_n(int n, int epi);
 cudaError_t gemm_tc_launch(const GemmTcArgs& args, cudaStream_t stream, int num_sms);

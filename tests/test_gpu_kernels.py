@@ -137,6 +137,36 @@ def test_k2_linear_layers(env, dtype, which):
         assert np.abs(got + host(out_lo) - want).max() <= 2e-3
 
 
+@pytest.mark.parametrize("which", [1, 3])
+@pytest.mark.parametrize("H,heads,I", [(256, 8, 512), (384, 12, 1536), (512, 8, 1024), (768, 12, 3072), (640, 10, 1280)])
+def test_k2_layernorm_epilogue_across_hidden_sizes(pkg, built, H, heads, I, which):
+    """The fused residual + LayerNorm epilogue for every row width: one CTA (128, 256), a cluster of 2 CTAs
+    (384, 512) or of 4 (768, 1024) exchanging row statistics through distributed shared memory; 640 is not
+    fusable and takes the GEMM + K4 route. Rows deliberately not a multiple of 128."""
+    shape = pkg.weights.BertShape(512, H, 1, heads, I, 64, 2)
+    rows = 1000
+    rng = np.random.default_rng(H + which)
+    kin = I if which == 3 else H
+    x = bf16_round(rng.standard_normal((rows, kin)).astype(np.float32))
+    res = rng.standard_normal((rows, H)).astype(np.float32) * 2
+    with pkg.Embedder.random_init(shape, seed=2) as emb:
+        w = emb.export_weights()
+        o = Oracle(shape, {k: bf16_round(v) if v.ndim == 2 else v for k, v in w.items()}, "f32")
+        pre = "attention.output" if which == 1 else "output"
+        y = o.linear(x, o.layer(0, pre + ".dense.weight"), o.layer(0, pre + ".dense.bias"))
+        want = o.add_layer_norm(y, res, o.layer(0, pre + ".LayerNorm.weight"), o.layer(0, pre + ".LayerNorm.bias"),
+                                shape.layer_norm_eps)
+        dx, dr, dr_lo = dev(x, torch.bfloat16), dev(res, torch.bfloat16), dev(res - bf16_round(res), torch.bfloat16)
+        out = torch.full(want.shape, float("nan"), dtype=torch.bfloat16, device="cuda")
+        out_lo = torch.full(want.shape, float("nan"), dtype=torch.bfloat16, device="cuda")
+        emb.op_linear(0, which, dx.data_ptr(), dr.data_ptr(), rows, 0, out.data_ptr(), d_residual_lo=dr_lo.data_ptr(),
+                      d_y_lo=out_lo.data_ptr())
+        got, got_lo = host(out), host(out_lo)
+    assert np.isfinite(got).all() and np.isfinite(got_lo).all()
+    assert np.abs(got - want).max() <= 0.006 * np.abs(want).max() + 1e-3
+    assert np.abs(got + got_lo - want).max() <= 2e-3
+
+
 @pytest.mark.parametrize("dtype", [0, 1, 2])
 @pytest.mark.parametrize("heads,d", [(4, 32), (2, 64)])
 def test_k3_attention(env, pkg, dtype, heads, d):
