@@ -118,13 +118,20 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot_ptr;
 
-    // item i -> (sentence b, query block qb, head h); items whose query block lies past the sentence end are empty
-    auto decode = [&](int i, int& b, int& qb, int& h, int& start, int& len) {
-        const int per_b = p.heads * p.q_blocks;
-        b = i / per_b;
-        const int r = i - b * per_b;
-        qb = r / p.heads;
-        h = r - qb * p.heads;
+    // item i -> (sentence b, query block qb, head h), i = (b * q_blocks + qb) * heads + h. Items advance by gridDim.x,
+    // so (b, r) is carried along instead of dividing every time; items whose query block lies past the sentence
+    // end are empty and skipped by every role alike.
+    const int per_b = p.heads * p.q_blocks;
+    struct Walk { int b, r; };
+    auto walk_init = [&]() { return Walk{static_cast<int>(blockIdx.x) / per_b, static_cast<int>(blockIdx.x) % per_b}; };
+    auto walk_next = [&](Walk& w) {
+        w.r += gridDim.x;
+        while (w.r >= per_b) { w.r -= per_b; ++w.b; }
+    };
+    auto decode = [&](const Walk& w, int& b, int& qb, int& h, int& start, int& len) {
+        b = w.b;
+        qb = w.r / p.heads;
+        h = w.r - qb * p.heads;
         start = p.cu[b];
         len = p.cu[b + 1] - start;
         return qb * BLK < len;
@@ -133,9 +140,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
     if (warp == 0) {
         if (lane == 0) {
             uint32_t q_it = 0, kv_it = 0;
-            for (int i = blockIdx.x; i < items; i += gridDim.x) {
+            Walk w = walk_init();
+            for (int i = blockIdx.x; i < items; i += gridDim.x, walk_next(w)) {
                 int b, qb, h, start, len;
-                if (!decode(i, b, qb, h, start, len)) continue;
+                if (!decode(w, b, qb, h, start, len)) continue;
                 const uint32_t qs = q_it & 1;
                 mbar_wait(bar_q_empty + 8 * qs, ((q_it >> 1) & 1) ^ 1);
                 mbar_arrive_expect_tx(bar_q_full + 8 * qs, TILE);
@@ -157,9 +165,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
             constexpr uint32_t idesc_s = umma_idesc_bf16(BLK, BLK);
             constexpr uint32_t idesc_o = umma_idesc_bf16(BLK, D) | (1u << 16);  // B (= V) is MN-major
             uint32_t q_it = 0, kv_it = 0, blk_it = 0;
-            for (int i = blockIdx.x; i < items; i += gridDim.x) {
+            Walk w = walk_init();
+            for (int i = blockIdx.x; i < items; i += gridDim.x, walk_next(w)) {
                 int b, qb, h, start, len;
-                if (!decode(i, b, qb, h, start, len)) continue;
+                if (!decode(w, b, qb, h, start, len)) continue;
                 const uint32_t qs = q_it & 1;
                 mbar_wait(bar_q_full + 8 * qs, (q_it >> 1) & 1);
                 const int nkb = (len + BLK - 1) / BLK;
@@ -198,9 +207,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
         const uint32_t t_s = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
         const uint32_t t_o = t_s + O_COL;
         uint32_t blk_it = 0;
-        for (int i = blockIdx.x; i < items; i += gridDim.x) {
+        Walk w = walk_init();
+        for (int i = blockIdx.x; i < items; i += gridDim.x, walk_next(w)) {
             int b, qb, h, start, len;
-            if (!decode(i, b, qb, h, start, len)) continue;
+            if (!decode(w, b, qb, h, start, len)) continue;
             float m = -INFINITY, l = 0.f;
             float o[D];
 #pragma unroll

@@ -88,27 +88,14 @@ __device__ __forceinline__ uint32_t map_to_cta(uint32_t local_smem, uint32_t ran
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_smem), "r"(rank));
     return r;
 }
-__device__ __forceinline__ void st_cluster_f32x2(uint32_t addr, float a, float b) {
-    asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" ::"r"(addr), "f"(a), "f"(b) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive_cluster(uint32_t remote_bar) {
-    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote_bar) : "memory");
-}
-__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
-    uint32_t done = 0;
-    long long t0 = 0;
-    for (uint32_t it = 0;; ++it) {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(done)
-            : "r"(bar), "r"(parity)
-            : "memory");
-        if (done) break;
-        if (it == 64) t0 = clock64();
-        if (it > 64 && (it & 63) == 0 && clock64() - t0 > 8000000000LL) __trap();
-    }
+// One 8-byte store into a peer CTA's shared memory that also counts 8 bytes on the peer's mbarrier
+// (complete_tx): the data is visible to whoever observes that barrier phase complete. No fence, no remote arrive.
+__device__ __forceinline__ void st_async_cluster_b64(uint32_t remote_addr, float a, float b, uint32_t remote_bar) {
+    const unsigned long long v =
+        static_cast<unsigned long long>(__float_as_uint(a)) | (static_cast<unsigned long long>(__float_as_uint(b)) << 32);
+    asm volatile("st.async.shared::cluster.mbarrier::complete_tx::bytes.b64 [%0], %1, [%2];" ::"r"(remote_addr), "l"(v),
+                 "r"(remote_bar)
+                 : "memory");
 }
 
 struct GemmDev {
@@ -272,7 +259,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             mbar_init(bar_tempty + 8 * s, EPI_THREADS);
         }
         for (int s = 0; s < 2 * EPI_WARPS; ++s) mbar_init(bar_res + 8 * s, 1);
-        for (int s = 0; s < 2; ++s) mbar_init(bar_ln + 8 * s, CL > 1 ? (CL - 1) * BLOCK_M : 1);
+        for (int s = 0; s < 2; ++s) mbar_init(bar_ln + 8 * s, 1);
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc(tmem_slot, 512);
@@ -476,19 +463,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 sum += other.x;
                 sumsq += other.y;
                 if constexpr (CL > 1) {
-                    // this CTA's 2 x 128 threads now hold the partials of its BLOCK_N columns; one thread per row
-                    // publishes them into every peer's slot [tile parity][my rank][row] and arrives on its barrier
+                    // this CTA's 2 x 128 threads now hold the partials of its BLOCK_N columns. One thread arms the
+                    // barrier of this tile parity with the bytes the peers will deliver; one thread per row stores
+                    // its (sum, sumsq) into every peer's slot [parity][my rank][row] with st.async, which counts the
+                    // bytes on the peer's barrier. A peer can be at most one tile ahead, so two parities suffice.
                     const uint32_t par = it & 1;
+                    if (ew == 0 && lane == 0) mbar_arrive_expect_tx(bar_ln + 8 * par, (CL - 1) * BLOCK_M * 8);
                     if (half == 0) {
+                        const uint32_t slot = ln_peer_addr + ((par * MAX_CLUSTER + crank) * BLOCK_M + row_in_tile) * 8;
 #pragma unroll
                         for (int pr = 0; pr < CL; ++pr) {
                             if (pr == crank) continue;
-                            const uint32_t slot = ln_peer_addr + ((par * MAX_CLUSTER + crank) * BLOCK_M + row_in_tile) * 8;
-                            st_cluster_f32x2(map_to_cta(slot, pr), sum, sumsq);
-                            mbar_arrive_cluster(map_to_cta(bar_ln + 8 * par, pr));
+                            st_async_cluster_b64(map_to_cta(slot, pr), sum, sumsq, map_to_cta(bar_ln + 8 * par, pr));
                         }
                     }
-                    mbar_wait_cluster(bar_ln + 8 * par, (it >> 1) & 1);
+                    mbar_wait(bar_ln + 8 * par, (it >> 1) & 1);
 #pragma unroll
                     for (int pr = 0; pr < CL; ++pr) {
                         if (pr == crank) continue;
