@@ -282,17 +282,22 @@ def run_b200(args, pkg, rank, world, local_rank):
     emb.profile(False)
     pk = peaks()
     kernels, total_ms = {}, sum(v["total_ms"] for v in stats.values()) / prof_steps
+    per_layer = {"gemm_qkv", "attention", "gemm_attn_out", "gemm_ffn1", "gemm_ffn2"}
     for kind, v in stats.items():
         if v["launches"] == 0:
             continue
         ms = v["total_ms"] / v["launches"]
+        # work of one full pass of this kind over the batch x how many passes a step makes (calls larger than the
+        # workspace are split into several launches per pass; their times add up)
+        passes = (2 if kind == "add_ln" else 1) * (shape.num_hidden_layers if kind in per_layer or kind == "add_ln" else 1)
         work, what = kernel_work(shape, lengths, kind)
+        step_ms = v["total_ms"] / prof_steps
         if what == "flops":
-            ach, peak, unit, bound = work / (ms * 1e-3) / 1e12, pk["tf_sustained"], "TFLOP/s", "tensor"
+            ach, peak, unit, bound = work * passes / (step_ms * 1e-3) / 1e12, pk["tf_sustained"], "TFLOP/s", "tensor"
         else:
-            ach, peak, unit, bound = work / (ms * 1e-3) / 1e9, pk["hbm_gbs"], "GB/s", "hbm"
+            ach, peak, unit, bound = work * passes / (step_ms * 1e-3) / 1e9, pk["hbm_gbs"], "GB/s", "hbm"
         kernels[kind] = {"ms_per_launch": round(ms, 4), "launches_per_step": v["launches"] // prof_steps,
-                         "share_of_step": round(v["total_ms"] / prof_steps / total_ms, 4), "bound": bound,
+                         "share_of_step": round(step_ms / total_ms, 4), "bound": bound,
                          "achieved": round(ach, 2), "peak": peak, "unit": unit, "frac": round(ach / peak, 4)}
     top = max(kernels, key=lambda k: kernels[k]["share_of_step"])
     traffic = None

@@ -102,6 +102,16 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst_smem, const void* tmap,
         ::"r"(dst_smem), "l"(tmap), "r"(bar), "r"(c0), "r"(c1)
         : "memory");
 }
+// Same load, delivered to the same shared-memory offset of every CTA in `cta_mask` of the cluster; each
+// destination CTA's mbarrier (same offset) receives the complete_tx for the bytes that land in it.
+__device__ __forceinline__ void tma_load_2d_multicast(uint32_t dst_smem, const void* tmap, int c0, int c1, uint32_t bar,
+                                                      uint16_t cta_mask) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
+        " [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(dst_smem),
+        "l"(tmap), "r"(bar), "r"(c0), "r"(c1), "h"(cta_mask)
+        : "memory");
+}
 __device__ __forceinline__ void tma_store_2d(const void* tmap, uint32_t src_smem, int c0, int c1) {
     asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(tmap),
                  "r"(src_smem), "r"(c0), "r"(c1)
@@ -149,6 +159,12 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint
 // (implies tcgen05.fence::before_thread_sync).
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar)
+                 : "memory");
+}
+// Same, arriving on the barrier at this offset in every CTA of `cta_mask` (shared operand stages).
+__device__ __forceinline__ void umma_commit_multicast(uint32_t bar, uint16_t cta_mask) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+                 "h"(cta_mask)
                  : "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }

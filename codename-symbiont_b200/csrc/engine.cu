@@ -108,6 +108,10 @@ struct b200_embed {
     bool fuse_ln = false;
     int bn_qkv = 0, bn_ffn1 = 0, bn_h = 0, bn_ln = 0;
     int act_epi = b200::EPI_GELU_ERF;
+    bool gemm_pair = false;  // B200_EMBED_GEMM_PAIR=1: plain GEMMs as W-sharing CTA pairs (no gain measured: TMA
+                             // multicast across 2 CTAs does not cut L2 reads; kept for A/B checks)
+    bool gemm_res_a = false;  // B200_EMBED_GEMM_RESIDENT_A=1: keep the A tile resident across column tiles (K <= 384);
+                              // measured neutral (these tiles are bound by shared-memory bandwidth, not L2 reads)
     bool attn_mma = false;  // B200_EMBED_ATTENTION=mma selects the mma.sync attention kernel (A/B checks)
     // weights
     float* arena32 = nullptr;
@@ -318,6 +322,8 @@ int gemm16(b200_embed* h, Context& c, cudaStream_t s, int kind, const void* x, c
     g.residual_lo = residual_lo; g.out_lo = out_lo;
     g.gamma = gamma; g.beta = beta; g.eps = h->cfg.layer_norm_eps; g.out = out; g.out_f32 = out_f32; g.epi = epi;
     g.block_n = block_n;
+    g.pair = h->gemm_pair ? 1 : 0;
+    g.no_resident_a = h->gemm_res_a ? 0 : 1;
     CU_TRY(timed(h, c, s, kind, 1, [&] { return b200::gemm_tc_launch(g, s, h->num_sms); }));
     return B200_EMBED_OK;
 }
@@ -538,6 +544,8 @@ int32_t b200_embed_create(const b200_embed_config* cfg, const char* path, uint64
     if (const char* v = getenv("B200_EMBED_FUSE_LN")) h->fuse_ln = h->fuse_ln && std::string(v) != "0";
     h->act_epi = b200::EPI_GELU_ERF + cfg->hidden_act;
     if (const char* v = getenv("B200_EMBED_ATTENTION")) h->attn_mma = std::string(v) == "mma";
+    if (const char* v = getenv("B200_EMBED_GEMM_PAIR")) h->gemm_pair = std::string(v) == "1";
+    if (const char* v = getenv("B200_EMBED_GEMM_RESIDENT_A")) h->gemm_res_a = std::string(v) == "1";
     h->bn_qkv = b200::gemm_tc_pick_block_n(3 * H, b200::EPI_BIAS);
     h->bn_ffn1 = b200::gemm_tc_pick_block_n(I, h->act_epi);
     h->bn_h = b200::gemm_tc_pick_block_n(H, b200::EPI_GELU_ERF);  // 256 or 128 (fp32-out instantiations)
@@ -1006,6 +1014,10 @@ int32_t b200_op_gemm_bf16(const void* a, const void* b, const float* bias, int32
     if (block_n == 0 || n % block_n) return fail(B200_EMBED_ERR_UNSUPPORTED_SHAPE, "n has no supported tile width");
     b200::GemmTcArgs g{};
     g.a = a; g.b = b; g.m = m; g.n = n; g.k = k; g.bias = bias; g.out = c; g.epi = epi; g.block_n = block_n;
+    const char* pv = getenv("B200_EMBED_GEMM_PAIR");
+    g.pair = (pv && std::string(pv) == "1") ? 1 : 0;
+    const char* rv = getenv("B200_EMBED_GEMM_RESIDENT_A");
+    g.no_resident_a = (rv && std::string(rv) == "1") ? 0 : 1;
     CU_TRY(b200::gemm_tc_launch(g, static_cast<cudaStream_t>(stream), sms));
     return B200_EMBED_OK;
 }

@@ -23,6 +23,11 @@
 // reach HBM. For N = 384 / 768 the row is split over a thread-block CLUSTER of 2 / 4 CTAs (192 columns each, so
 // the TMEM accumulators stay double-buffered and the smem stages small); the CTAs of a cluster walk the same row
 // blocks and exchange their per-row partial (sum, sum of squares) through distributed shared memory.
+// Shared operand tiles are loaded once per cluster with TMA multicast: the CTAs of a LayerNorm cluster share the A
+// tile (each loads 1/CL of its rows and multicasts), and the plain GEMMs run as pairs of CTAs on adjacent row
+// blocks that share the W tile (each loads half of it). Both halve that operand's L2 -> SM traffic, which is what
+// bounds 128-row tiles at K = 384 (12 TB/s of L2 reads at 930 TFLOP/s, profiles/r01b). A stage is released to the
+// producers of all sharing CTAs by a multicast tcgen05.commit.
 // Both operands are K-major ("TN"): activations [M,K] and HF weights [N,K] as stored.
 #include "gemm_tc.h"
 
@@ -64,14 +69,17 @@ constexpr int AUX_LN_PEER = 2 * MAX_CLUSTER * BLOCK_M * 8;  // [tile parity][sen
 __host__ __device__ constexpr int aux_bytes(int epi) {
     return AUX_BARRIERS + (epi == EPI_RES_LN ? AUX_LN_PART + AUX_LN_PEER : 0);
 }
-__host__ __device__ constexpr int num_stages(int block_n, int epi, bool out_f32) {
-    int s = (SMEM_LIMIT - aux_bytes(epi) - EPI_WARPS * epi_warp_bytes(epi, out_f32)) /
-            (A_STAGE_BYTES + b_stage_bytes(block_n));
+// kslots == 0: A and W stream through the same ring of stages. kslots > 0 ("resident A"): the whole 128 x K
+// activation tile sits in `kslots` fixed 16 KB slots while the CTA walks every column tile of that row block, and
+// only W streams through the ring.
+__host__ __device__ constexpr int num_stages(int block_n, int epi, bool out_f32, int kslots) {
+    int s = (SMEM_LIMIT - aux_bytes(epi) - EPI_WARPS * epi_warp_bytes(epi, out_f32) - kslots * A_STAGE_BYTES) /
+            ((kslots ? 0 : A_STAGE_BYTES) + b_stage_bytes(block_n));
     return s > 8 ? 8 : s;
 }
-__host__ __device__ constexpr int smem_bytes(int block_n, int epi, bool out_f32) {
-    return num_stages(block_n, epi, out_f32) * (A_STAGE_BYTES + b_stage_bytes(block_n)) +
-           EPI_WARPS * epi_warp_bytes(epi, out_f32) + aux_bytes(epi);
+__host__ __device__ constexpr int smem_bytes(int block_n, int epi, bool out_f32, int kslots) {
+    return num_stages(block_n, epi, out_f32, kslots) * ((kslots ? 0 : A_STAGE_BYTES) + b_stage_bytes(block_n)) +
+           kslots * A_STAGE_BYTES + EPI_WARPS * epi_warp_bytes(epi, out_f32) + aux_bytes(epi);
 }
 
 // ---- thread-block cluster helpers (distributed shared memory) ----
@@ -183,7 +191,7 @@ __device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
     return v;
 }
 
-template <int BLOCK_N, int EPI, typename OutT, int CL>
+template <int BLOCK_N, int EPI, typename OutT, int CL, int PAIR, int KSLOTS>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const __grid_constant__ CUtensorMap tmap_c, const __grid_constant__ CUtensorMap tmap_c_lo,
@@ -194,7 +202,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     constexpr int UMMA_N = BLOCK_N / NSPLIT;
     constexpr int ACC_STAGES = (2 * BLOCK_N <= 512) ? 2 : 1;
     constexpr int B_STAGE_BYTES = b_stage_bytes(BLOCK_N);
-    constexpr int STAGES = num_stages(BLOCK_N, EPI, OUT_F32);
+    constexpr int STAGES = num_stages(BLOCK_N, EPI, OUT_F32, KSLOTS);
+    constexpr bool RES_A = KSLOTS > 0;
+    static_assert(!RES_A || (CL == 1 && PAIR == 0 && KSLOTS <= 8), "resident A is for the plain single-CTA GEMMs");
     constexpr int HALF_N = BLOCK_N / 2;  // columns per epilogue warp group
     constexpr int NCH = HALF_N / CHUNK;  // chunks per warp per tile
     constexpr int EPI_WARP_BYTES = epi_warp_bytes(EPI, OUT_F32);
@@ -203,15 +213,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     static_assert(HALF_N % CHUNK == 0, "epilogue works in 32-column chunks");
     static_assert(STAGES >= 2, "not enough shared memory for a pipeline");
     static_assert(EPI != EPI_RES_LN || !OUT_F32, "LayerNorm epilogue writes bf16 (hi, lo)");
-    static_assert(CL == 1 || EPI == EPI_RES_LN, "clusters are only used to split LayerNorm rows");
+    static_assert(CL == 1 || EPI == EPI_RES_LN, "row-splitting clusters are only used by the LayerNorm epilogue");
     static_assert(CL <= MAX_CLUSTER, "cluster too large");
+    static_assert(PAIR == 0 || (CL == 1 && NSPLIT == 1), "W-sharing pairs are for the plain epilogues");
+    constexpr int CSIZE = CL > 1 ? CL : (PAIR ? 2 : 1);       // CTAs per cluster
+    constexpr uint16_t CMASK = static_cast<uint16_t>((1u << CSIZE) - 1);
+    constexpr int A_SLICE_ROWS = BLOCK_M / (CL > 1 ? CL : 1);  // rows of the A tile this CTA loads (and multicasts)
+    constexpr int B_SLICE_ROWS = BLOCK_N / (PAIR ? 2 : 1);     // rows of the W tile this CTA loads (and multicasts)
 
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     const uint32_t base = smem_u32(smem_raw);
     if ((base & 1023u) != 0) __trap();  // swizzled TMA / UMMA tiles need 1024-byte alignment
-    const uint32_t smem_a = base;
-    const uint32_t smem_b = base + STAGES * A_STAGE_BYTES;
-    const uint32_t smem_epi = base + STAGES * (A_STAGE_BYTES + B_STAGE_BYTES);
+    const uint32_t smem_a = base;  // STAGES ring slots, or KSLOTS resident k-blocks
+    const uint32_t smem_b = base + (RES_A ? KSLOTS : STAGES) * A_STAGE_BYTES;
+    const uint32_t smem_epi = smem_b + STAGES * B_STAGE_BYTES;
     const uint32_t aux = smem_epi + EPI_WARPS * EPI_WARP_BYTES;
     uint8_t* aux_ptr = smem_raw + (aux - base);
     const uint32_t bar_full = aux;          // STAGES x 8 B
@@ -221,6 +236,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     const uint32_t bar_res = aux + 192;     // EPI_WARPS x 2 x 8 B (residual ring, one pair per epilogue warp)
     const uint32_t tmem_slot = aux + 320;   // 4 B
     const uint32_t bar_ln = aux + 336;      // 2 x 8 B: peers' row partials have arrived (per tile parity)
+    const uint32_t bar_a_full = aux + 384;  // 8 x 8 B: resident A k-block landed
+    const uint32_t bar_a_empty = aux + 448; // 8 x 8 B: resident A k-block no longer needed by this row block
     volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(aux_ptr + 320);
     float2* ln_part = reinterpret_cast<float2*>(aux_ptr + AUX_BARRIERS);                // [2][BLOCK_M]
     float2* ln_peer = reinterpret_cast<float2*>(aux_ptr + AUX_BARRIERS + AUX_LN_PART);  // [2][MAX_CLUSTER][BLOCK_M]
@@ -237,14 +254,29 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     const int num_m_tiles = (rows + BLOCK_M - 1) / BLOCK_M;
     const int num_n_tiles = p.n / BLOCK_N;  // == CL when the row is split over a cluster
     const int num_kb = (p.k + BLOCK_K - 1) / BLOCK_K;
-    // Work units: CL == 1: unit = (m_tile, n_tile), one CTA each. CL > 1: unit = m_tile, shared by the CL CTAs of
-    // a cluster, CTA `crank` taking columns [crank * BLOCK_N, +BLOCK_N). All CTAs of a cluster see the same units.
-    const int crank = CL > 1 ? static_cast<int>(cluster_ctarank()) : 0;
-    const int num_tiles = CL > 1 ? num_m_tiles : num_m_tiles * num_n_tiles;
-    const int tile0 = static_cast<int>(blockIdx.x) / CL;
-    const int tile_step = static_cast<int>(gridDim.x) / CL;
-    auto tile_m = [&](int t) { return CL > 1 ? t : t / num_n_tiles; };
-    auto tile_n = [&](int t) { return CL > 1 ? crank : t % num_n_tiles; };
+    // Work units, walked identically by all CTAs of a cluster:
+    //   plain:      unit = (m_tile, n_tile), one CTA each;
+    //   CL > 1:     unit = m_tile, CTA `crank` takes columns [crank * BLOCK_N, +BLOCK_N) of it;
+    //   PAIR:       unit = (pair of adjacent m_tiles, n_tile), CTA `crank` takes m_tile 2 * pair + crank. With an odd
+    //               number of row blocks the last pair's second CTA works on an out-of-range block: its loads are
+    //               zero-filled and its stores clipped, but it keeps its side of the shared-stage protocol.
+    const int crank = CSIZE > 1 ? static_cast<int>(cluster_ctarank()) : 0;
+    //   RES_A:      unit = m_tile; the CTA walks all n_tiles of it back to back with the A tile resident.
+    const int num_units =
+        (CL > 1 || RES_A) ? num_m_tiles : (PAIR ? ((num_m_tiles + 1) / 2) * num_n_tiles : num_m_tiles * num_n_tiles);
+    const int unit0 = static_cast<int>(blockIdx.x) / CSIZE;
+    const int unit_step = static_cast<int>(gridDim.x) / CSIZE;
+    const int my_units = unit0 < num_units ? (num_units - unit0 + unit_step - 1) / unit_step : 0;
+    const int my_tiles = RES_A ? my_units * num_n_tiles : my_units;  // output tiles this CTA produces, in order
+    auto tile_m = [&](int i) {
+        if constexpr (RES_A) return unit0 + (i / num_n_tiles) * unit_step;
+        const int t = unit0 + i * unit_step;
+        return CL > 1 ? t : (PAIR ? 2 * (t / num_n_tiles) + crank : t / num_n_tiles);
+    };
+    auto tile_n = [&](int i) {
+        if constexpr (RES_A) return i % num_n_tiles;
+        return CL > 1 ? crank : (unit0 + i * unit_step) % num_n_tiles;
+    };
 
     if (threadIdx.x == 0) {
         prefetch_tmap(&tmap_a);
@@ -252,7 +284,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         prefetch_tmap(&tmap_c);
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(bar_full + 8 * s, 1);
-            mbar_init(bar_empty + 8 * s, 1);
+            mbar_init(bar_empty + 8 * s, CSIZE);  // one multicast commit from every CTA that shares the stage
         }
         for (int s = 0; s < 2; ++s) {
             mbar_init(bar_tfull + 8 * s, 1);
@@ -260,12 +292,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         }
         for (int s = 0; s < 2 * EPI_WARPS; ++s) mbar_init(bar_res + 8 * s, 1);
         for (int s = 0; s < 2; ++s) mbar_init(bar_ln + 8 * s, 1);
+        for (int s = 0; s < 8; ++s) {
+            mbar_init(bar_a_full + 8 * s, 1);
+            mbar_init(bar_a_empty + 8 * s, 1);
+        }
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc(tmem_slot, 512);
     tc_fence_before_sync();
     __syncthreads();
-    if constexpr (CL > 1) cluster_sync_all();  // peers' barriers exist before anyone arrives on them remotely
+    if constexpr (CSIZE > 1) cluster_sync_all();  // peers' barriers exist before anyone arrives on them remotely
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot_ptr;
 
@@ -274,17 +310,39 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int t = tile0; t < num_tiles; t += tile_step) {
-                const int m_tile = tile_m(t), n_tile = tile_n(t);
+            for (int i = 0; i < my_tiles; ++i) {
+                const int m_tile = tile_m(i), n_tile = tile_n(i);
                 for (int kb = 0; kb < num_kb; ++kb) {
+                    if constexpr (RES_A) {
+                        if (n_tile == 0) {  // new row block: (re)fill resident slot kb once the previous block let go of it
+                            const uint32_t au = static_cast<uint32_t>(i / num_n_tiles);
+                            mbar_wait(bar_a_empty + 8 * kb, (au & 1) ^ 1);
+                            mbar_arrive_expect_tx(bar_a_full + 8 * kb, A_STAGE_BYTES);
+                            tma_load_2d(smem_a + kb * A_STAGE_BYTES, &tmap_a, kb * BLOCK_K, m_tile * BLOCK_M,
+                                        bar_a_full + 8 * kb);
+                        }
+                    }
                     mbar_wait(bar_empty + 8 * stage, phase ^ 1);
-                    mbar_arrive_expect_tx(bar_full + 8 * stage, A_STAGE_BYTES + B_STAGE_BYTES);
-                    tma_load_2d(smem_a + stage * A_STAGE_BYTES, &tmap_a, kb * BLOCK_K, m_tile * BLOCK_M,
-                                bar_full + 8 * stage);
+                    mbar_arrive_expect_tx(bar_full + 8 * stage, (RES_A ? 0 : A_STAGE_BYTES) + B_STAGE_BYTES);
+                    if constexpr (RES_A) {
+                    } else if constexpr (CL > 1) {  // my slice of the A tile, delivered to every CTA of the cluster
+                        tma_load_2d_multicast(smem_a + stage * A_STAGE_BYTES + crank * (A_SLICE_ROWS * BLOCK_K * 2), &tmap_a,
+                                              kb * BLOCK_K, m_tile * BLOCK_M + crank * A_SLICE_ROWS, bar_full + 8 * stage,
+                                              CMASK);
+                    } else {
+                        tma_load_2d(smem_a + stage * A_STAGE_BYTES, &tmap_a, kb * BLOCK_K, m_tile * BLOCK_M,
+                                    bar_full + 8 * stage);
+                    }
+                    if constexpr (PAIR) {  // my half of the W tile, delivered to both CTAs of the pair
+                        tma_load_2d_multicast(smem_b + stage * B_STAGE_BYTES + crank * (B_SLICE_ROWS * BLOCK_K * 2), &tmap_b,
+                                              kb * BLOCK_K, n_tile * BLOCK_N + crank * B_SLICE_ROWS, bar_full + 8 * stage,
+                                              CMASK);
+                    } else {
 #pragma unroll
-                    for (int s = 0; s < NSPLIT; ++s)
-                        tma_load_2d(smem_b + stage * B_STAGE_BYTES + s * (UMMA_N * BLOCK_K * 2), &tmap_b,
-                                    kb * BLOCK_K, n_tile * BLOCK_N + s * UMMA_N, bar_full + 8 * stage);
+                        for (int s = 0; s < NSPLIT; ++s)
+                            tma_load_2d(smem_b + stage * B_STAGE_BYTES + s * (UMMA_N * BLOCK_K * 2), &tmap_b,
+                                        kb * BLOCK_K, n_tile * BLOCK_N + s * UMMA_N, bar_full + 8 * stage);
+                    }
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
             }
@@ -295,17 +353,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             constexpr uint32_t idesc = umma_idesc_bf16(BLOCK_M, UMMA_N);
             int stage = 0;
             uint32_t phase = 0;
-            int it = 0;
-            for (int t = tile0; t < num_tiles; t += tile_step, ++it) {
+            for (int it = 0; it < my_tiles; ++it) {
                 const int acc = it % ACC_STAGES;
                 const uint32_t acc_phase = (it / ACC_STAGES) & 1;
+                const int n_tile = tile_n(it);
                 mbar_wait(bar_tempty + 8 * acc, acc_phase ^ 1);
                 tc_fence_after_sync();
                 const uint32_t tmem_d = tmem_base + acc * BLOCK_N;
                 for (int kb = 0; kb < num_kb; ++kb) {
+                    if constexpr (RES_A) {
+                        if (n_tile == 0) mbar_wait(bar_a_full + 8 * kb, static_cast<uint32_t>(it / num_n_tiles) & 1);
+                    }
                     mbar_wait(bar_full + 8 * stage, phase);
                     tc_fence_after_sync();
-                    const uint64_t desc_a = umma_desc_sw128(smem_a + stage * A_STAGE_BYTES);
+                    const uint64_t desc_a = umma_desc_sw128(smem_a + (RES_A ? kb : stage) * A_STAGE_BYTES);
                     const uint64_t desc_b = umma_desc_sw128(smem_b + stage * B_STAGE_BYTES);
 #pragma unroll
                     for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
@@ -317,7 +378,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                                       (kb > 0 || k > 0) ? 1u : 0u);
                         }
                     }
-                    umma_commit(bar_empty + 8 * stage);  // frees the smem stage when these MMAs finish
+                    // frees the smem stage (in every CTA that shares it) when these MMAs finish
+                    if constexpr (CSIZE > 1) umma_commit_multicast(bar_empty + 8 * stage, CMASK);
+                    else umma_commit(bar_empty + 8 * stage);
+                    if constexpr (RES_A) {  // last column tile of this row block: slot kb may take the next block's A
+                        if (n_tile == num_n_tiles - 1) umma_commit(bar_a_empty + 8 * kb);
+                    }
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
                 umma_commit(bar_tfull + 8 * acc);  // accumulator complete
@@ -366,14 +432,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             ++ld_issued;
         };
         if constexpr (EPI == EPI_RES_LN) {
-            if (tile0 < num_tiles) {
-                issue_residual(tile0, 0);
-                if (NCH > 1) issue_residual(tile0, 1);
+            if (my_tiles > 0) {
+                issue_residual(0, 0);
+                if (NCH > 1) issue_residual(0, 1);
             }
         }
 
-        int it = 0;
-        for (int t = tile0; t < num_tiles; t += tile_step, ++it) {
+        for (int it = 0; it < my_tiles; ++it) {
+            const int t = it;
             const int m_tile = tile_m(t), n_tile = tile_n(t);
             const int acc = it % ACC_STAGES;
             const uint32_t acc_phase = (it / ACC_STAGES) & 1;
@@ -453,8 +519,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     tmem_st_32x32(taddr + c * CHUNK, v);
                     __syncwarp();  // every lane has read this ring stage: refill it
                     if (c + 2 < NCH) issue_residual(t, c + 2);
-                    else if (t + tile_step < num_tiles && c + 2 - NCH < NCH)
-                        issue_residual(t + tile_step, c + 2 - NCH);  // prefetch the next tile's first chunks
+                    else if (t + 1 < my_tiles && c + 2 - NCH < NCH)
+                        issue_residual(t + 1, c + 2 - NCH);  // prefetch the next tile's first chunks
                 }
                 tmem_st_wait();
                 ln_part[half * BLOCK_M + row_in_tile] = make_float2(sum, sumsq);
@@ -524,7 +590,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 
     tc_fence_before_sync();
     __syncthreads();
-    if constexpr (CL > 1) cluster_sync_all();  // no CTA leaves while a peer may still write into its shared memory
+    if constexpr (CSIZE > 1) cluster_sync_all();  // no CTA leaves while a peer may still write into its shared memory
     if (warp == 2) {
         tc_fence_after_sync();
         tmem_dealloc(tmem_base, 512);
@@ -563,14 +629,15 @@ bool make_tmap(CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t cols, 
     return r == CUDA_SUCCESS;
 }
 
-template <int BLOCK_N, int EPI, typename OutT, int CL = 1>
+template <int BLOCK_N, int EPI, typename OutT, int CL = 1, int PAIR = 0, int KSLOTS = 0>
 cudaError_t launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms) {
     constexpr int NSPLIT = BLOCK_N > 256 ? 2 : 1;
     constexpr bool OUT_F32 = sizeof(OutT) == 4;
+    constexpr int CSIZE = CL > 1 ? CL : (PAIR ? 2 : 1);
     alignas(64) CUtensorMap ta, tb, tc, tcl, tr, trl;
-    if (!make_tmap(&ta, a.a, a.m, a.k, BLOCK_K, BLOCK_M, false, CU_TENSOR_MAP_SWIZZLE_128B))
+    if (!make_tmap(&ta, a.a, a.m, a.k, BLOCK_K, BLOCK_M / (CL > 1 ? CL : 1), false, CU_TENSOR_MAP_SWIZZLE_128B))
         return cudaErrorInvalidValue;
-    if (!make_tmap(&tb, a.b, a.n, a.k, BLOCK_K, BLOCK_N / NSPLIT, false, CU_TENSOR_MAP_SWIZZLE_128B))
+    if (!make_tmap(&tb, a.b, a.n, a.k, BLOCK_K, BLOCK_N / NSPLIT / (PAIR ? 2 : 1), false, CU_TENSOR_MAP_SWIZZLE_128B))
         return cudaErrorInvalidValue;
     const CUtensorMapSwizzle csw = OUT_F32 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
     if (!make_tmap(&tc, a.out, a.m, a.n, CHUNK, 32, OUT_F32, csw)) return cudaErrorInvalidValue;
@@ -583,8 +650,9 @@ cudaError_t launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms) {
         if (a.residual_lo && !make_tmap(&trl, a.residual_lo, a.m, a.n, CHUNK, 32, false, csw))
             return cudaErrorInvalidValue;
     }
-    auto kern = gemm_tc_kernel<BLOCK_N, EPI, OutT, CL>;
-    constexpr int smem = smem_bytes(BLOCK_N, EPI, OUT_F32);
+    auto kern = gemm_tc_kernel<BLOCK_N, EPI, OutT, CL, PAIR, KSLOTS>;
+    constexpr int smem = smem_bytes(BLOCK_N, EPI, OUT_F32, KSLOTS);
+    static_assert(num_stages(BLOCK_N, EPI, OUT_F32, KSLOTS) >= 2, "not enough shared memory for a pipeline");
     static_assert(smem <= SMEM_LIMIT, "shared memory budget exceeded");
     static bool attr_set = false;  // per instantiation; benign race (idempotent)
     if (!attr_set) {
@@ -597,29 +665,29 @@ cudaError_t launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms) {
     p.gamma = a.gamma; p.beta = a.beta; p.eps = a.eps;
     p.has_res_lo = a.residual_lo != nullptr; p.has_out_lo = a.out_lo != nullptr;
     const int m_tiles = (a.m + BLOCK_M - 1) / BLOCK_M;
-    const int units = CL > 1 ? m_tiles : m_tiles * (a.n / BLOCK_N);
+    const int units = (CL > 1 || KSLOTS > 0) ? m_tiles : (PAIR ? ((m_tiles + 1) / 2) : m_tiles) * (a.n / BLOCK_N);
     cudaLaunchConfig_t cfg{};
     cfg.blockDim = dim3(NUM_THREADS);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = CL;
+    attr[0].val.clusterDim.x = CSIZE;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = CL > 1 ? 1 : 0;
+    cfg.numAttrs = CSIZE > 1 ? 1 : 0;
     // persistent grid: as many clusters as the device can hold at once (size-4 clusters do not tile all 148 SMs)
     static int max_units = 0;
     if (max_units == 0) {
-        max_units = num_sms / CL;
-        if (CL > 1) {
-            cfg.gridDim = dim3((num_sms / CL) * CL);
+        max_units = num_sms / CSIZE;
+        if (CSIZE > 1) {
+            cfg.gridDim = dim3((num_sms / CSIZE) * CSIZE);
             int n = 0;
             if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) == cudaSuccess && n > 0 && n < max_units) max_units = n;
         }
     }
-    const int grid = (units < max_units ? units : max_units) * CL;
+    const int grid = (units < max_units ? units : max_units) * CSIZE;
     if (grid <= 0) return cudaSuccess;
     cfg.gridDim = dim3(grid);
     return cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, tcl, tr, trl, p);
@@ -660,8 +728,13 @@ cudaError_t gemm_tc_launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms
         if (a.block_n == 256 && cl == 4) return launch<256, EPI_RES_LN, __nv_bfloat16, 4>(a, stream, num_sms);
         return cudaErrorInvalidValue;
     }
-#define B200_CASE(BN, EP, T) \
-    if (a.block_n == BN && a.epi == EP && a.out_f32 == (sizeof(T) == 4)) return launch<BN, EP, T>(a, stream, num_sms);
+    // K <= 384 with several column tiles per row block: keep the activation tile resident (6 x 64 columns)
+    const bool res_a = !a.pair && !a.no_resident_a && a.k <= 6 * BLOCK_K && a.n / a.block_n >= 2;
+#define B200_CASE(BN, EP, T)                                                        \
+    if (a.block_n == BN && a.epi == EP && a.out_f32 == (sizeof(T) == 4))            \
+        return a.pair ? launch<BN, EP, T, 1, 1, 0>(a, stream, num_sms)              \
+               : res_a ? launch<BN, EP, T, 1, 0, 6>(a, stream, num_sms)             \
+                       : launch<BN, EP, T, 1, 0, 0>(a, stream, num_sms);
     B200_CASE(128, EPI_BIAS, __nv_bfloat16)
     B200_CASE(192, EPI_BIAS, __nv_bfloat16)
     B200_CASE(256, EPI_BIAS, __nv_bfloat16)
