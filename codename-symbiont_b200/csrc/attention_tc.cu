@@ -4,15 +4,18 @@
 // + (1-mask)*f32::MIN, softmax, .v, head merge; called from embedding_generator.rs:198). See attention.cu
 // for the mma.sync variant of the same math; this kernel is the one the forward uses.
 //
-// Work item = (sentence, head, block of 128 query rows). A persistent CTA walks items; per item it walks the
-// sentence's keys in blocks of 128:
-//   warp 0     TMA producer: Q tile once per item, K and V tiles per key block (2-stage rings), straight from
+// Work item = (sentence, head, block of 128 query rows). A persistent CTA (2 per SM for d = 32) walks items; per
+// item it walks the sentence's keys in UNITS of 64 keys, two units in flight:
+//   warp 0     TMA producer: Q tile once per item, K and V tiles per 128-key block (2-stage rings), straight from
 //              the packed qkv [tokens, 3H] activations (box D x 128 rows; D*2-byte swizzle)
-//   warp 1     one thread issues tcgen05.mma: S = Q.K^T (128 x 128, fp32 in TMEM), then O_blk = P.V (128 x D)
-//   warp 2     TMEM allocator (256 columns: S 128 + O_blk D)
-//   warps 4-7  softmax: thread r owns query row r (TMEM lane r): two passes over S with tcgen05.ld (row max,
-//              then p = exp2(s*scale - max)), P written as bf16 into a 128B-swizzled K-major smem tile (the A
-//              operand of the second MMA), running max / sum / output kept in registers (online softmax, fp32)
+//   warp 1     one thread issues tcgen05.mma: S_u = Q.K_u^T (128 x 64, fp32 in TMEM, double-buffered) one unit
+//              ahead of the softmax, then O_u = P_u.V_u (128 x D, double-buffered) as soon as P_u is in smem
+//   warp 2     TMEM allocator (256 columns: 2 x 64 S + 2 x D O)
+//   warps 4-7  softmax: thread r owns query row r (= TMEM lane r). One tcgen05.ld brings the unit's 64 scores
+//              into registers (read once: row max, p = exp2(s*scale - max) and the row sum all work from there),
+//              P goes as bf16 into a 128B-swizzled K-major smem tile (the A operand of the second MMA), and the
+//              previous unit's O_u is folded into the running output while this unit's P.V runs. Running max /
+//              sum / output live in registers (online softmax, fp32).
 // Keys past the sentence end get p = 0, which is exactly what the reference's additive f32::MIN mask yields.
 // Rows of the 128-row tiles that lie past the sentence end belong to the next sentence (or are zero-filled
 // by TMA past the last token); they are computed and never stored.
@@ -29,9 +32,13 @@ namespace b200 {
 
 namespace {
 
-constexpr int BLK = 128;  // query rows per item and keys per block
+constexpr int BLK = 128;   // query rows per item; keys per K/V tile
+constexpr int UNIT = 64;   // keys per softmax unit
 constexpr int ATT_THREADS = 256;
-constexpr int SM_WARP0 = 4;
+constexpr int SM_WARP0 = 4;       // softmax warps 4-7; the single-thread roles keep the low warp ids: putting them
+constexpr int PRODUCER_WARP = 0;  // after the softmax warps (ids 4-6) was measured 28 % slower
+constexpr int MMA_WARP = 1;
+constexpr int ALLOC_WARP = 2;
 constexpr int SM_THREADS = 128;
 
 // K-major operand, rows of 64 bytes (D = 32): SWIZZLE_64B, 8-row groups 512 B apart.
@@ -66,12 +73,12 @@ struct AttnDev {
 
 template <int D>
 struct AttnSmem {
-    static constexpr int TILE = BLK * D * 2;      // one Q / K / V tile
-    static constexpr int P_BYTES = BLK * BLK * 2;  // two K-major 128 x 64 bf16 tiles
-    static constexpr int OFF_Q = 0;                // 2 stages
-    static constexpr int OFF_KV = 2 * TILE;        // 2 stages x (K, V)
-    static constexpr int OFF_P = OFF_KV + 4 * TILE;
-    static constexpr int OFF_AUX = OFF_P + P_BYTES;
+    static constexpr int TILE = BLK * D * 2;         // one Q / K / V tile
+    static constexpr int P_UNIT = BLK * UNIT * 2;     // one K-major 128 x 64 bf16 tile (16 KB)
+    static constexpr int OFF_Q = 0;                   // 2 stages
+    static constexpr int OFF_KV = 2 * TILE;           // 2 stages x (K, V)
+    static constexpr int OFF_P = OFF_KV + 4 * TILE;   // 2 units
+    static constexpr int OFF_AUX = OFF_P + 2 * P_UNIT;
     static constexpr int BYTES = OFF_AUX + 256;
 };
 
@@ -81,7 +88,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
     using L = AttnSmem<D>;
     constexpr int TILE = L::TILE;
     constexpr uint32_t TMEM_COLS = 256;
-    constexpr int O_COL = BLK;  // O_blk columns start after the 128 S columns
+    constexpr int O_COL = 2 * UNIT;  // O buffers start after the two S buffers
 
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     const uint32_t base = smem_u32(smem_raw);
@@ -89,10 +96,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
     const uint32_t smem_q = base + L::OFF_Q, smem_kv = base + L::OFF_KV, smem_p = base + L::OFF_P;
     const uint32_t aux = base + L::OFF_AUX;
     const uint32_t bar_q_full = aux, bar_q_empty = aux + 16, bar_kv_full = aux + 32, bar_kv_empty = aux + 48;
-    const uint32_t bar_s_full = aux + 64, bar_s_empty = aux + 72, bar_p_full = aux + 80, bar_o_full = aux + 88,
-                   bar_o_empty = aux + 96;
-    const uint32_t tmem_slot = aux + 128;
-    volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + L::OFF_AUX + 128);
+    const uint32_t bar_s_full = aux + 64, bar_s_empty = aux + 80, bar_p_full = aux + 96, bar_o_full = aux + 112,
+                   bar_o_empty = aux + 128;  // two of each: buffer u & 1
+    const uint32_t tmem_slot = aux + 160;
+    volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + L::OFF_AUX + 160);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int items = p.batch * p.heads * p.q_blocks;
@@ -104,15 +111,15 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
             mbar_init(bar_q_empty + 8 * s, 1);
             mbar_init(bar_kv_full + 8 * s, 1);
             mbar_init(bar_kv_empty + 8 * s, 1);
+            mbar_init(bar_s_full + 8 * s, 1);
+            mbar_init(bar_s_empty + 8 * s, SM_THREADS);
+            mbar_init(bar_p_full + 8 * s, SM_THREADS);
+            mbar_init(bar_o_full + 8 * s, 1);
+            mbar_init(bar_o_empty + 8 * s, SM_THREADS);
         }
-        mbar_init(bar_s_full, 1);
-        mbar_init(bar_s_empty, SM_THREADS);
-        mbar_init(bar_p_full, SM_THREADS);
-        mbar_init(bar_o_full, 1);
-        mbar_init(bar_o_empty, SM_THREADS);
         fence_barrier_init();
     }
-    if (warp == 2) tmem_alloc(tmem_slot, TMEM_COLS);
+    if (warp == ALLOC_WARP) tmem_alloc(tmem_slot, TMEM_COLS);
     tc_fence_before_sync();
     __syncthreads();
     tc_fence_after_sync();
@@ -137,7 +144,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
         return qb * BLK < len;
     };
 
-    if (warp == 0) {
+    if (warp == PRODUCER_WARP) {
         if (lane == 0) {
             uint32_t q_it = 0, kv_it = 0;
             Walk w = walk_init();
@@ -160,43 +167,55 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
                 }
             }
         }
-    } else if (warp == 1) {
+    } else if (warp == MMA_WARP) {
         if (lane == 0) {
-            constexpr uint32_t idesc_s = umma_idesc_bf16(BLK, BLK);
+            constexpr uint32_t idesc_s = umma_idesc_bf16(BLK, UNIT);
             constexpr uint32_t idesc_o = umma_idesc_bf16(BLK, D) | (1u << 16);  // B (= V) is MN-major
-            uint32_t q_it = 0, kv_it = 0, blk_it = 0;
+            uint32_t q_it = 0, kv_it = 0;
+            uint32_t us = 0;  // units whose S MMA has been issued (buffer us & 1)
+            uint32_t uo = 0;  // units whose P.V MMA has been issued
             Walk w = walk_init();
             for (int i = blockIdx.x; i < items; i += gridDim.x, walk_next(w)) {
                 int b, qb, h, start, len;
                 if (!decode(w, b, qb, h, start, len)) continue;
                 const uint32_t qs = q_it & 1;
                 mbar_wait(bar_q_full + 8 * qs, (q_it >> 1) & 1);
-                const int nkb = (len + BLK - 1) / BLK;
-                for (int kb = 0; kb < nkb; ++kb, ++kv_it, ++blk_it) {
-                    const uint32_t s = kv_it & 1;
-                    const uint32_t k_smem = smem_kv + s * 2 * TILE, v_smem = k_smem + TILE;
-                    mbar_wait(bar_kv_full + 8 * s, (kv_it >> 1) & 1);
-                    mbar_wait(bar_s_empty, (blk_it & 1) ^ 1);  // softmax has drained the previous S
+                const uint64_t dq = umma_desc_k<D>(smem_q + qs * TILE);
+                const int nunits = (len + UNIT - 1) / UNIT;  // unit u: keys [u*64, u*64+64); block u/2, half u&1
+                const uint32_t kv0 = kv_it;                 // ring position of this item's first K/V block
+
+                // S_u = Q . K_u^T into S buffer (us & 1)
+                auto issue_s = [&](int u) {
+                    const uint32_t kvi = kv0 + (u >> 1), s = kvi & 1;
+                    if ((u & 1) == 0) mbar_wait(bar_kv_full + 8 * s, (kvi >> 1) & 1);  // first touch of this block
+                    mbar_wait(bar_s_empty + 8 * (us & 1), ((us >> 1) & 1) ^ 1);        // softmax drained this S buffer
                     tc_fence_after_sync();
-                    const uint64_t dq = umma_desc_k<D>(smem_q + qs * TILE), dk = umma_desc_k<D>(k_smem);
+                    const uint64_t dk = umma_desc_k<D>(smem_kv + s * 2 * TILE + (u & 1) * (UNIT * D * 2));
 #pragma unroll
                     for (int k = 0; k < D / 16; ++k)
-                        umma_bf16(tmem_base, dq + 2 * k, dk + 2 * k, idesc_s, k > 0 ? 1u : 0u);
-                    umma_commit(bar_s_full);
-                    mbar_wait(bar_p_full, blk_it & 1);           // P is in shared memory
-                    mbar_wait(bar_o_empty, (blk_it & 1) ^ 1);    // previous O_blk has been read
+                        umma_bf16(tmem_base + (us & 1) * UNIT, dq + 2 * k, dk + 2 * k, idesc_s, k > 0 ? 1u : 0u);
+                    umma_commit(bar_s_full + 8 * (us & 1));
+                    ++us;
+                };
+                issue_s(0);
+                for (int u = 0; u < nunits; ++u) {
+                    if (u + 1 < nunits) issue_s(u + 1);  // one unit ahead of the softmax
+                    const uint32_t kvi = kv0 + (u >> 1), s = kvi & 1, ob = uo & 1;
+                    mbar_wait(bar_p_full + 8 * ob, (uo >> 1) & 1);         // P_u is in shared memory
+                    mbar_wait(bar_o_empty + 8 * ob, ((uo >> 1) & 1) ^ 1);  // the O buffer has been read
                     tc_fence_after_sync();
+                    const uint32_t v_smem = smem_kv + s * 2 * TILE + TILE + (u & 1) * (UNIT * D * 2);
 #pragma unroll
-                    for (int k = 0; k < BLK / 16; ++k) {
-                        // P: two K-major 128x64 tiles (16 KB each), 32 B per 16-key step inside a tile
-                        const uint64_t dp = umma_desc_sw128(smem_p + (k >> 2) * (BLK * 128)) + 2 * (k & 3);
-                        // V: 16 keys per step = 16 rows of D*2 bytes
-                        const uint64_t dv = umma_desc_mn<D>(v_smem + k * 16 * D * 2);
-                        umma_bf16(tmem_base + O_COL, dp, dv, idesc_o, k > 0 ? 1u : 0u);
+                    for (int k = 0; k < UNIT / 16; ++k) {
+                        const uint64_t dp = umma_desc_sw128(smem_p + ob * L::P_UNIT) + 2 * k;  // 32 B per 16 keys
+                        const uint64_t dv = umma_desc_mn<D>(v_smem + k * 16 * D * 2);           // 16 rows of D*2 B
+                        umma_bf16(tmem_base + O_COL + ob * D, dp, dv, idesc_o, k > 0 ? 1u : 0u);
                     }
-                    umma_commit(bar_o_full);
-                    umma_commit(bar_kv_empty + 8 * s);
+                    umma_commit(bar_o_full + 8 * ob);
+                    ++uo;
+                    if ((u & 1) == 1 || u == nunits - 1) umma_commit(bar_kv_empty + 8 * s);  // block fully consumed
                 }
+                kv_it += (nunits + 1) >> 1;
                 umma_commit(bar_q_empty + 8 * qs);
                 ++q_it;
             }
@@ -204,94 +223,92 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
     } else if (warp >= SM_WARP0) {
         const int quad = warp & 3;
         const int row = quad * 32 + lane;  // query row inside the item = TMEM lane
-        const uint32_t t_s = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
-        const uint32_t t_o = t_s + O_COL;
-        uint32_t blk_it = 0;
+        const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
+        uint32_t uc = 0;  // units processed so far by this CTA (buffer uc & 1, phase (uc >> 1) & 1)
         Walk w = walk_init();
         for (int i = blockIdx.x; i < items; i += gridDim.x, walk_next(w)) {
             int b, qb, h, start, len;
             if (!decode(w, b, qb, h, start, len)) continue;
-            float m = -INFINITY, l = 0.f;
+            float m = -INFINITY, l = 0.f, corr_prev = 0.f;
             float o[D];
 #pragma unroll
             for (int j = 0; j < D; ++j) o[j] = 0.f;
-            const int nkb = (len + BLK - 1) / BLK;
-            for (int kb = 0; kb < nkb; ++kb, ++blk_it) {
-                const int nvalid = min(BLK, len - kb * BLK);  // keys of this block inside the sentence
-                mbar_wait(bar_s_full, blk_it & 1);
-                tc_fence_after_sync();
-                // pass 1: row maximum over the valid keys
-                float mx = -INFINITY;
-#pragma unroll 1
-                for (int c = 0; c < BLK / 32; ++c) {
-                    uint32_t v[32];
-                    tmem_ld_32x32(t_s + c * 32, v);
-                    tmem_ld_wait();
-                    if (c * 32 + 32 <= nvalid) {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(v[j]));
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j)
-                            if (c * 32 + j < nvalid) mx = fmaxf(mx, __uint_as_float(v[j]));
-                    }
-                }
-                const float m_new = fmaxf(m, mx * p.scale_log2);
-                const float corr = ex2(m - m_new);
-                m = m_new;
-                // pass 2: p = exp2(s*scale - m); bf16 P into the swizzled K-major tiles; row sum
-                float lb = 0.f;
-#pragma unroll 1
-                for (int c = 0; c < BLK / 32; ++c) {
-                    uint32_t v[32];
-                    tmem_ld_32x32(t_s + c * 32, v);
-                    tmem_ld_wait();
-                    if (c == BLK / 32 - 1) {  // S fully read: the next Q.K^T may overwrite it
-                        tc_fence_before_sync();
-                        mbar_arrive(bar_s_empty);
-                    }
-                    float pj[32];
-                    if (c * 32 + 32 <= nvalid) {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) pj[j] = ex2(fmaf(__uint_as_float(v[j]), p.scale_log2, -m_new));
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j)
-                            pj[j] = (c * 32 + j < nvalid) ? ex2(fmaf(__uint_as_float(v[j]), p.scale_log2, -m_new)) : 0.f;
-                    }
-                    // tile (c >> 1), row `row`, 16-byte pieces (c & 1) * 4 .. +3, swizzled by row & 7
-                    const uint32_t prow = smem_p + (c >> 1) * (BLK * 128) + row * 128;
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        const uint32_t w0 = pack_bf16x2(pj[q * 8 + 0], pj[q * 8 + 1]), w1 = pack_bf16x2(pj[q * 8 + 2], pj[q * 8 + 3]),
-                                       w2 = pack_bf16x2(pj[q * 8 + 4], pj[q * 8 + 5]), w3 = pack_bf16x2(pj[q * 8 + 6], pj[q * 8 + 7]);
-                        // the row sum uses the rounded values the tensor core will multiply
-                        const float2 a0 = unpack_bf16x2(w0), a1 = unpack_bf16x2(w1), a2 = unpack_bf16x2(w2), a3 = unpack_bf16x2(w3);
-                        lb += ((a0.x + a0.y) + (a1.x + a1.y)) + ((a2.x + a2.y) + (a3.x + a3.y));
-                        const uint32_t piece = ((c & 1) * 4 + q) ^ (row & 7);
-                        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(prow + (piece << 4)), "r"(w0), "r"(w1),
-                                     "r"(w2), "r"(w3)
-                                     : "memory");
-                    }
-                }
-                fence_proxy_async_smem();
-                mbar_arrive(bar_p_full);
-                l = fmaf(l, corr, lb);
-                // O = O * corr + P.V
-                mbar_wait(bar_o_full, blk_it & 1);
+            const int nunits = (len + UNIT - 1) / UNIT;
+
+            // folds unit (uc - 1)'s O into the running output: o = o * corr + O_u
+            auto retire = [&](uint32_t ur, float corr) {
+                const uint32_t ob = ur & 1;
+                mbar_wait(bar_o_full + 8 * ob, (ur >> 1) & 1);
                 tc_fence_after_sync();
 #pragma unroll
                 for (int c = 0; c < D / 32; ++c) {
                     uint32_t v[32];
-                    tmem_ld_32x32(t_o + c * 32, v);
+                    tmem_ld_32x32(t_lane + O_COL + ob * D + c * 32, v);
                     tmem_ld_wait();
 #pragma unroll
                     for (int j = 0; j < 32; ++j) o[c * 32 + j] = fmaf(o[c * 32 + j], corr, __uint_as_float(v[j]));
                 }
                 tc_fence_before_sync();
-                mbar_arrive(bar_o_empty);
+                mbar_arrive(bar_o_empty + 8 * ob);
+            };
+
+            for (int u = 0; u < nunits; ++u, ++uc) {
+                const uint32_t sb = uc & 1;
+                const int nvalid = min(UNIT, len - u * UNIT);  // keys of this unit inside the sentence
+                mbar_wait(bar_s_full + 8 * sb, (uc >> 1) & 1);
+                tc_fence_after_sync();
+                uint32_t v[UNIT];
+                tmem_ld_32x32(t_lane + sb * UNIT, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+                tmem_ld_32x32(t_lane + sb * UNIT + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+                tmem_ld_wait();
+                tc_fence_before_sync();
+                mbar_arrive(bar_s_empty + 8 * sb);  // S is in registers: the MMA warp may overwrite the buffer
+                // four independent chains for the row max (a single 64-deep FMNMX chain is pure latency)
+                float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+                if (nvalid == UNIT) {
+#pragma unroll
+                    for (int j = 0; j < UNIT; ++j) mx4[j & 3] = fmaxf(mx4[j & 3], __uint_as_float(v[j]));
+                } else {
+#pragma unroll
+                    for (int j = 0; j < UNIT; ++j)
+                        if (j < nvalid) mx4[j & 3] = fmaxf(mx4[j & 3], __uint_as_float(v[j]));
+                }
+                const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+                const float m_new = fmaxf(m, mx * p.scale_log2);
+                const float corr = ex2(m - m_new);
+                m = m_new;
+                // p = exp2(s*scale - m), rounded to bf16 into the swizzled K-major tile; row sum (4 chains)
+                float lb4[4] = {0.f, 0.f, 0.f, 0.f};
+                const uint32_t prow = smem_p + sb * L::P_UNIT + row * 128;
+                const bool full = nvalid == UNIT;
+#pragma unroll
+                for (int q = 0; q < UNIT / 8; ++q) {
+                    float pj[8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) pj[j] = ex2(fmaf(__uint_as_float(v[q * 8 + j]), p.scale_log2, -m_new));
+                    if (!full) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j)
+                            if (q * 8 + j >= nvalid) pj[j] = 0.f;
+                    }
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) lb4[j & 3] += pj[j];
+                    const uint32_t piece = static_cast<uint32_t>(q) ^ (row & 7);
+                    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(prow + (piece << 4)),
+                                 "r"(pack_bf16x2(pj[0], pj[1])), "r"(pack_bf16x2(pj[2], pj[3])),
+                                 "r"(pack_bf16x2(pj[4], pj[5])), "r"(pack_bf16x2(pj[6], pj[7]))
+                                 : "memory");
+                }
+                const float lb = (lb4[0] + lb4[1]) + (lb4[2] + lb4[3]);
+                fence_proxy_async_smem();
+                mbar_arrive(bar_p_full + 8 * sb);
+                l = fmaf(l, corr, lb);
+                // while P_u . V_u runs, fold the previous unit's output in
+                if (u > 0) retire(uc - 1, corr_prev);
+                corr_prev = corr;
             }
-            // finalise: O / l, staged through the (now idle) P buffer so that global stores are row-contiguous
+            retire(uc - 1, corr_prev);
+            // finalise: O / l, staged through the (now idle) P buffers so that global stores are row-contiguous
             const float inv = 1.0f / l;
             constexpr int PITCH = D * 2 + 16;  // bytes; the pad spreads rows over banks
             const uint32_t orow = smem_p + row * PITCH;
@@ -325,7 +342,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
 
     tc_fence_before_sync();
     __syncthreads();
-    if (warp == 2) {
+    if (warp == ALLOC_WARP) {
         tc_fence_after_sync();
         tmem_dealloc(tmem_base, TMEM_COLS);
     }

@@ -20,7 +20,7 @@ def dev_i32(a):
 
 def bf16_round(a):
     """fp32 ndarray rounded to bf16 (RNE) and back: what the library's bf16 copies hold."""
-    return torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32)).bfloat16().float().numpy()
+    return torch.from_numpy(np.array(a, dtype=np.float32, copy=True)).bfloat16().float().numpy()
 
 
 def host(t):
