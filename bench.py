@@ -130,6 +130,8 @@ def kernel_work(shape, lengths, kind):
         return 2 * T * H * H, "flops"
     if kind in ("gemm_ffn1", "gemm_ffn2"):
         return 2 * T * I * H, "flops"
+    if kind == "ffn_fused":
+        return 4 * T * I * H, "flops"
     if kind == "attention":
         return 4 * H * s2, "flops"
     if kind == "embed_ln":  # fp32 word row in, (hi, lo) bf16 rows out, ids + type ids + mask
@@ -282,7 +284,7 @@ def run_b200(args, pkg, rank, world, local_rank):
     emb.profile(False)
     pk = peaks()
     kernels, total_ms = {}, sum(v["total_ms"] for v in stats.values()) / prof_steps
-    per_layer = {"gemm_qkv", "attention", "gemm_attn_out", "gemm_ffn1", "gemm_ffn2"}
+    per_layer = {"gemm_qkv", "attention", "gemm_attn_out", "gemm_ffn1", "gemm_ffn2", "ffn_fused"}
     for kind, v in stats.items():
         if v["launches"] == 0:
             continue

@@ -25,7 +25,7 @@ FLAG_NORMALIZE = 1
 FLAG_FP32 = 2
 ERR_NAMES = {0: "OK", -1: "INVALID_ARG", -2: "CUDA", -3: "OOM", -4: "UNSUPPORTED_SHAPE", -5: "NO_DEVICE", -6: "IO"}
 KIND_NAMES = ["lengths", "embed_ln", "gemm_qkv", "attention", "gemm_attn_out", "gemm_ffn1", "gemm_ffn2", "add_ln",
-              "pool"]
+              "pool", "ffn_fused"]
 
 
 class B200EmbedError(RuntimeError):
@@ -66,6 +66,7 @@ _SIGNATURES = {
     "b200_embed_profile_read": (C.c_int32, [_P, C.POINTER(KindStats), C.c_int32]),
     "b200_op_embed_layernorm": (C.c_int32, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, _P, _P, _P]),
     "b200_op_linear": (C.c_int32, [_P, C.c_int32, C.c_int32, _P, _P, _P, C.c_int32, C.c_int32, _P, _P, _P]),
+    "b200_op_ffn": (C.c_int32, [_P, C.c_int32, _P, _P, C.c_int32, _P, _P, _P]),
     "b200_op_linear_noalloc": (C.c_int32, [_P, C.c_int32, C.c_int32, _P, _P, _P, C.c_int32, C.c_int32, _P, _P, _P]),
     "b200_op_attention": (C.c_int32, [_P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P, _P]),
     "b200_op_add_layernorm": (C.c_int32, [_P, C.c_int32, C.c_int32, _P, C.c_int32, _P, _P, C.c_int32, C.c_int32, _P, _P,
@@ -256,6 +257,9 @@ class Embedder:
     def op_linear(self, layer, which, d_x, d_residual, rows, dtype, d_y, d_residual_lo=0, d_y_lo=0, stream=0):
         _check(self.lib.b200_op_linear(self.h, layer, which, d_x, d_residual or None, d_residual_lo or None, rows, dtype,
                                        d_y, d_y_lo or None, stream or None))
+
+    def op_ffn(self, layer, d_x, d_x_lo, rows, d_y, d_y_lo=0, stream=0):
+        _check(self.lib.b200_op_ffn(self.h, layer, d_x, d_x_lo or None, rows, d_y, d_y_lo or None, stream or None))
 
     def op_linear_noalloc(self, layer, which, d_x, d_residual, rows, dtype, d_y, d_residual_lo=0, d_y_lo=0, stream=0):
         """b200_op_linear for which = 1 / 3 with the fp32 temporary in the library's built-in 4 MiB scratch: no

@@ -1,0 +1,429 @@
+// K2f: the whole feed-forward block of one BERT layer in one kernel (hidden size <= 384):
+//
+//     x' = LayerNorm( gelu(a . W1^T + b1) . W2^T + b2 + a )
+//
+// Replaces candle bert.rs BertIntermediate::forward + BertOutput::forward (called from
+// /root/reference/services/preprocessing_service/src/embedding_generator.rs:198), which the reference runs as
+// two f32 matmuls with separate bias / GELU / residual / LayerNorm passes. Run as two GEMM kernels the
+// [tokens, I] intermediate costs an HBM write and a read (3.2 GB per layer at c2), and both GEMMs are bound by
+// that traffic, not by the tensor pipe (HBM write bandwidth is 3.9 TB/s; profiles/). Here it never leaves the SM.
+//
+// One persistent CTA per SM owns 128 token rows at a time. The activation tile a[128,H] is loaded once and stays
+// in shared memory. The intermediate is produced and consumed in chunks of 128 columns:
+//     S1  = a . W1[chunk]^T                (tcgen05.mma 128x128xH, fp32 in TMEM columns 0..127)
+//     h   = gelu(S1 + b1[chunk]) -> bf16   (epilogue warps: tcgen05.ld -> registers -> 128B-swizzled K-major smem)
+//     OUT += h . W2[:, chunk]^T            (tcgen05.mma 128xHx128, fp32 in TMEM columns 128..128+H)
+// software-pipelined so that the tensor pipe runs S1 of chunk c+1 and OUT of chunk c-1 while the epilogue warps work
+// on chunk c. After the last chunk the epilogue warps add b2 and the residual (hi, lo), LayerNorm the rows and
+// store (hi, lo) exactly as the LayerNorm epilogue of gemm_tc.cu does.
+//   warp 0      TMA producer: a tile, W1 blocks [128 x 64] and W2 blocks [H/NS x 64] through two rings
+//   warp 1      one thread issues all tcgen05.mma
+//   warp 2      TMEM allocator (512 columns)
+//   warps 4-11  epilogue (warp w: TMEM lane quadrant w % 4, column half (w - 4) / 4)
+#include "kernels.h"
+#include "tc_helpers.cuh"
+
+namespace b200 {
+
+namespace {
+
+constexpr int FF_THREADS = 384;
+constexpr int FF_EPI_WARP0 = 4;
+constexpr int FF_EPI_WARPS = 8;
+constexpr int FF_EPI_THREADS = FF_EPI_WARPS * 32;
+constexpr int BM = 128;            // token rows per tile
+constexpr int BK = 64;             // bf16 per 128-byte swizzle row
+constexpr int IC = 128;            // intermediate columns per chunk
+constexpr int BLK16 = BM * BK * 2;  // a [128 x 64] bf16 block: 16 KB
+
+template <int H>
+struct FfnCfg {
+    static constexpr int KB1 = H / BK;                // k-blocks of GEMM1 (and of the resident a tile)
+    static constexpr int NS = H > 256 ? 2 : 1;        // GEMM2 N split (UMMA N <= 256)
+    static constexpr int UN2 = H / NS;                // GEMM2 UMMA N
+    static constexpr int W2_BLK = UN2 * BK * 2;       // one W2 block [UN2 x 64]
+    static constexpr int S1N = 3;                     // W1 ring stages
+    static constexpr int S2N = 2;                     // W2 ring stages
+    static constexpr int OFF_A = 0;
+    static constexpr int OFF_H = KB1 * BLK16;         // h chunk: 2 k-blocks [128 x 64]
+    static constexpr int OFF_W1 = OFF_H + 2 * BLK16;
+    static constexpr int OFF_W2 = OFF_W1 + S1N * BLK16;
+    static constexpr int OFF_AUX = OFF_W2 + S2N * W2_BLK;
+    static constexpr int AUX = 1024 + 2 * BM * 8;     // barriers + tmem slot, LayerNorm partial statistics
+    static constexpr int BYTES = OFF_AUX + AUX;
+    static constexpr int SCRATCH = OFF_AUX - OFF_H;   // h + rings: per-warp scratch of the final epilogue
+    static constexpr int HALF = H / 2;                // output columns per epilogue warp
+    static constexpr int NCH = HALF / CHUNK;
+    static_assert(H % 128 == 0 && H <= 384, "fused FFN needs the OUT accumulator (H columns) next to S1 (128) in TMEM");
+    static_assert(SCRATCH >= FF_EPI_WARPS * 6 * CHUNK_BF16, "final epilogue scratch does not fit");
+    static_assert(BYTES <= SMEM_LIMIT, "shared memory budget exceeded");
+};
+
+struct FfnDev {
+    int m;
+    const int* d_rows;
+    int inter;  // I
+    const float *b1, *b2, *gamma, *beta;
+    float eps;
+    int has_lo;
+};
+
+template <int H>
+__global__ void __launch_bounds__(FF_THREADS, 1)
+ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w1,
+                 const __grid_constant__ CUtensorMap tmap_w2, const __grid_constant__ CUtensorMap tmap_r,
+                 const __grid_constant__ CUtensorMap tmap_r_lo, const __grid_constant__ CUtensorMap tmap_c,
+                 const __grid_constant__ CUtensorMap tmap_c_lo, const FfnDev p) {
+    using C = FfnCfg<H>;
+    constexpr int KB1 = C::KB1, NS = C::NS, UN2 = C::UN2, W2_BLK = C::W2_BLK, S1N = C::S1N, S2N = C::S2N;
+    constexpr int HALF = C::HALF, NCH = C::NCH;
+    constexpr int OUT_COL = IC;  // OUT accumulator starts after the 128 S1 columns
+
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    const uint32_t base = smem_u32(smem_raw);
+    if ((base & 1023u) != 0) __trap();
+    const uint32_t smem_a = base + C::OFF_A, smem_h = base + C::OFF_H, smem_w1 = base + C::OFF_W1,
+                   smem_w2 = base + C::OFF_W2, aux = base + C::OFF_AUX;
+    uint8_t* aux_ptr = smem_raw + C::OFF_AUX;
+    const uint32_t bar_a_full = aux, bar_a_empty = aux + 8;
+    const uint32_t bar_w1_full = aux + 16, bar_w1_empty = aux + 48;  // S1N each
+    const uint32_t bar_w2_full = aux + 80, bar_w2_empty = aux + 112; // S2N each
+    const uint32_t bar_s1_full = aux + 144, bar_s1_empty = aux + 152, bar_h_full = aux + 160, bar_h_empty = aux + 168;
+    const uint32_t bar_out_full = aux + 176, bar_out_empty = aux + 184, bar_epi_done = aux + 192;
+    const uint32_t bar_res = aux + 256;   // FF_EPI_WARPS x 2
+    const uint32_t tmem_slot = aux + 512;
+    volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(aux_ptr + 512);
+    float2* ln_part = reinterpret_cast<float2*>(aux_ptr + 1024);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    int rows = p.m;
+    if (p.d_rows != nullptr) {
+        const int r = *p.d_rows;
+        rows = r < rows ? r : rows;
+    }
+    const int num_tiles = (rows + BM - 1) / BM;
+    const int NC = p.inter / IC;  // chunks per tile
+
+    if (threadIdx.x == 0) {
+        prefetch_tmap(&tmap_a); prefetch_tmap(&tmap_w1); prefetch_tmap(&tmap_w2);
+        mbar_init(bar_a_full, 1); mbar_init(bar_a_empty, 1);
+        for (int s = 0; s < S1N; ++s) { mbar_init(bar_w1_full + 8 * s, 1); mbar_init(bar_w1_empty + 8 * s, 1); }
+        for (int s = 0; s < S2N; ++s) { mbar_init(bar_w2_full + 8 * s, 1); mbar_init(bar_w2_empty + 8 * s, 1); }
+        mbar_init(bar_s1_full, 1); mbar_init(bar_s1_empty, FF_EPI_THREADS);
+        mbar_init(bar_h_full, FF_EPI_THREADS); mbar_init(bar_h_empty, 1);
+        mbar_init(bar_out_full, 1); mbar_init(bar_out_empty, FF_EPI_THREADS);
+        mbar_init(bar_epi_done, FF_EPI_THREADS);
+        for (int s = 0; s < 2 * FF_EPI_WARPS; ++s) mbar_init(bar_res + 8 * s, 1);
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc(tmem_slot, 512);
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = *tmem_slot_ptr;
+
+    // Both the producer and the MMA thread walk the tensor-pipe schedule of a tile in the same order:
+    //   G1(0), [G1(1), G2(0)], [G1(2), G2(1)], ..., [G1(NC-1), G2(NC-2)], G2(NC-1)
+    if (warp == 0) {
+        if (lane == 0) {
+            uint32_t w1_it = 0, w2_it = 0, tile_it = 0;
+            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++tile_it) {
+                // the a tile: free once the previous tile's last GEMM1 has completed
+                mbar_wait(bar_a_empty, (tile_it & 1) ^ 1);
+                mbar_arrive_expect_tx(bar_a_full, KB1 * BLK16);
+                for (int kb = 0; kb < KB1; ++kb) tma_load_2d(smem_a + kb * BLK16, &tmap_a, kb * BK, t * BM, bar_a_full);
+                // the rings double as scratch of the previous tile's final epilogue
+                mbar_wait(bar_epi_done, (tile_it & 1) ^ 1);
+                for (int step = 0; step <= NC; ++step) {
+                    if (step < NC) {
+                        for (int kb = 0; kb < KB1; ++kb, ++w1_it) {
+                            const uint32_t s = w1_it % S1N;
+                            mbar_wait(bar_w1_empty + 8 * s, ((w1_it / S1N) & 1) ^ 1);
+                            mbar_arrive_expect_tx(bar_w1_full + 8 * s, BLK16);
+                            tma_load_2d(smem_w1 + s * BLK16, &tmap_w1, kb * BK, step * IC, bar_w1_full + 8 * s);
+                        }
+                    }
+                    if (step >= 1) {
+                        const int ic = step - 1;
+                        for (int ns = 0; ns < NS; ++ns)
+                            for (int kb = 0; kb < IC / BK; ++kb, ++w2_it) {
+                                const uint32_t s = w2_it % S2N;
+                                mbar_wait(bar_w2_empty + 8 * s, ((w2_it / S2N) & 1) ^ 1);
+                                mbar_arrive_expect_tx(bar_w2_full + 8 * s, W2_BLK);
+                                tma_load_2d(smem_w2 + s * W2_BLK, &tmap_w2, ic * IC + kb * BK, ns * UN2, bar_w2_full + 8 * s);
+                            }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc1 = umma_idesc_bf16(BM, IC);
+            constexpr uint32_t idesc2 = umma_idesc_bf16(BM, UN2);
+            uint32_t w1_it = 0, w2_it = 0, tile_it = 0, g1_it = 0, g2_it = 0;  // g*_it: chunks issued so far
+            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++tile_it) {
+                mbar_wait(bar_a_full, tile_it & 1);
+                for (int step = 0; step <= NC; ++step) {
+                    if (step < NC) {  // G1(step): S1 = a . W1[chunk]^T
+                        mbar_wait(bar_s1_empty, (g1_it & 1) ^ 1);  // the epilogue has drained the previous S1
+                        tc_fence_after_sync();
+                        for (int kb = 0; kb < KB1; ++kb, ++w1_it) {
+                            const uint32_t s = w1_it % S1N;
+                            mbar_wait(bar_w1_full + 8 * s, (w1_it / S1N) & 1);
+                            tc_fence_after_sync();
+                            const uint64_t da = umma_desc_sw128(smem_a + kb * BLK16);
+                            const uint64_t db = umma_desc_sw128(smem_w1 + s * BLK16);
+#pragma unroll
+                            for (int k = 0; k < BK / 16; ++k)
+                                umma_bf16(tmem_base, da + 2 * k, db + 2 * k, idesc1, (kb > 0 || k > 0) ? 1u : 0u);
+                            umma_commit(bar_w1_empty + 8 * s);
+                        }
+                        umma_commit(bar_s1_full);
+                        ++g1_it;
+                        if (step == NC - 1) umma_commit(bar_a_empty);  // the a tile has been read for the last time
+                    }
+                    if (step >= 1) {  // G2(step - 1): OUT += h . W2[:, chunk]^T
+                        const int ic = step - 1;
+                        mbar_wait(bar_h_full, g2_it & 1);  // h(ic) is in shared memory
+                        if (ic == 0) mbar_wait(bar_out_empty, (tile_it & 1) ^ 1);  // previous tile's OUT has been read
+                        tc_fence_after_sync();
+                        for (int ns = 0; ns < NS; ++ns)
+                            for (int kb = 0; kb < IC / BK; ++kb, ++w2_it) {
+                                const uint32_t s = w2_it % S2N;
+                                mbar_wait(bar_w2_full + 8 * s, (w2_it / S2N) & 1);
+                                tc_fence_after_sync();
+                                const uint64_t da = umma_desc_sw128(smem_h + kb * BLK16);
+                                const uint64_t db = umma_desc_sw128(smem_w2 + s * W2_BLK);
+#pragma unroll
+                                for (int k = 0; k < BK / 16; ++k)
+                                    umma_bf16(tmem_base + OUT_COL + ns * UN2, da + 2 * k, db + 2 * k, idesc2,
+                                              (ic > 0 || kb > 0 || k > 0) ? 1u : 0u);
+                                umma_commit(bar_w2_empty + 8 * s);
+                            }
+                        umma_commit(bar_h_empty);  // h(ic) consumed
+                        ++g2_it;
+                        if (ic == NC - 1) umma_commit(bar_out_full);
+                    }
+                }
+            }
+        }
+    } else if (warp >= FF_EPI_WARP0) {
+        const int ew = warp - FF_EPI_WARP0;
+        const int quad = warp & 3, half = ew >> 2;
+        const int row_in_tile = quad * 32 + lane;
+        const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
+        // final-epilogue scratch of this warp inside the (then idle) h / ring region: 2-stage (hi, lo) residual ring
+        // and two output staging buffers
+        const uint32_t my_smem = smem_h + ew * (6 * CHUNK_BF16);
+        const uint32_t out_buf = my_smem + 4 * CHUNK_BF16;
+        uint32_t chunk_it = 0, tile_it = 0, st_it = 0, ld_issued = 0, ld_used = 0;
+
+        auto store_chunk = [&](const CUtensorMap* map, int col0, int row0, const float (&f)[32], bool lo) {
+            const uint32_t buf = out_buf + (st_it & 1) * CHUNK_BF16;
+            if (lane == 0) tma_store_wait_read<1>();
+            __syncwarp();
+            if (lo) stage_row_bf16_lo(buf, lane, f);
+            else stage_row_bf16(buf, lane, f);
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+                tma_store_2d(map, buf, col0, row0);
+                tma_store_commit();
+            }
+            ++st_it;
+        };
+        auto issue_residual = [&](int tile, int c) {
+            if (lane == 0) {
+                const uint32_t s = ld_issued & 1;
+                const uint32_t bar = bar_res + 8 * (2 * ew + s);
+                const uint32_t dst = my_smem + s * (2 * CHUNK_BF16);
+                const int col0 = half * HALF + c * CHUNK, row0 = tile * BM + quad * 32;
+                mbar_arrive_expect_tx(bar, p.has_lo ? 2 * CHUNK_BF16 : CHUNK_BF16);
+                tma_load_2d(dst, &tmap_r, col0, row0, bar);
+                if (p.has_lo) tma_load_2d(dst + CHUNK_BF16, &tmap_r_lo, col0, row0, bar);
+            }
+            ++ld_issued;
+        };
+
+        for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++tile_it) {
+            // ---- per chunk: h = gelu(S1 + b1) as the bf16 A operand of the second GEMM ----
+            for (int ic = 0; ic < NC; ++ic, ++chunk_it) {
+                mbar_wait(bar_s1_full, chunk_it & 1);
+                tc_fence_after_sync();
+                uint32_t v[64];  // this thread's row, S1 columns half*64 .. +63
+                tmem_ld_32x32(t_lane + half * 64, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+                tmem_ld_32x32(t_lane + half * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+                tmem_ld_wait();
+                tc_fence_before_sync();
+                mbar_arrive(bar_s1_empty);  // S1 is in registers: the next chunk's GEMM1 may overwrite it
+                const float4* b4 = reinterpret_cast<const float4*>(p.b1 + ic * IC + half * 64);
+                uint32_t hp[32];
+#pragma unroll
+                for (int q = 0; q < 16; ++q) {
+                    const float4 b = __ldg(b4 + q);
+                    const float g0 = gelu_erf_fast(__uint_as_float(v[q * 4 + 0]) + b.x);
+                    const float g1 = gelu_erf_fast(__uint_as_float(v[q * 4 + 1]) + b.y);
+                    const float g2 = gelu_erf_fast(__uint_as_float(v[q * 4 + 2]) + b.z);
+                    const float g3 = gelu_erf_fast(__uint_as_float(v[q * 4 + 3]) + b.w);
+                    hp[q * 2 + 0] = pack_bf16x2(g0, g1);
+                    hp[q * 2 + 1] = pack_bf16x2(g2, g3);
+                }
+                // the h buffer is free once GEMM2 of the previous chunk has completed
+                mbar_wait(bar_h_empty, (chunk_it & 1) ^ 1);
+                // k-block `half` of the h chunk, K-major, 128-byte rows, SWIZZLE_128B
+                const uint32_t hrow = smem_h + half * BLK16 + row_in_tile * 128;
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    const uint32_t a = hrow + ((static_cast<uint32_t>(q) ^ (row_in_tile & 7)) << 4);
+                    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(hp[q * 4 + 0]), "r"(hp[q * 4 + 1]),
+                                 "r"(hp[q * 4 + 2]), "r"(hp[q * 4 + 3])
+                                 : "memory");
+                }
+                fence_proxy_async_smem();
+                mbar_arrive(bar_h_full);
+            }
+            // ---- final: x' = LayerNorm(OUT + b2 + a) -> (hi, lo) ----
+            mbar_wait(bar_out_full, tile_it & 1);  // every MMA of this tile has completed: h and the rings are idle
+            tc_fence_after_sync();
+            issue_residual(t, 0);
+            if (NCH > 1) issue_residual(t, 1);
+            const uint32_t taddr = t_lane + OUT_COL + half * HALF;
+            const int row0 = t * BM + quad * 32;
+            float sum = 0.f, sumsq = 0.f;
+#pragma unroll 1
+            for (int c = 0; c < NCH; ++c) {
+                uint32_t v[32];
+                tmem_ld_32x32(taddr + c * CHUNK, v);
+                const uint32_t s = ld_used & 1;
+                mbar_wait(bar_res + 8 * (2 * ew + s), (ld_used >> 1) & 1);
+                ++ld_used;
+                const uint32_t rbuf = my_smem + s * (2 * CHUNK_BF16) + lane * 64;
+                const int sw = (lane >> 1) & 3;
+                tmem_ld_wait();
+                const float4* b4 = reinterpret_cast<const float4*>(p.b2 + half * HALF + c * CHUNK);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const uint4 r = lds_v4(rbuf + ((q ^ sw) << 4));
+                    const float4 b0 = __ldg(b4 + 2 * q), b1 = __ldg(b4 + 2 * q + 1);
+                    float2 r0 = unpack_bf16x2(r.x), r1 = unpack_bf16x2(r.y), r2 = unpack_bf16x2(r.z), r3 = unpack_bf16x2(r.w);
+                    if (p.has_lo) {
+                        const uint4 l = lds_v4(rbuf + CHUNK_BF16 + ((q ^ sw) << 4));
+                        const float2 l0 = unpack_bf16x2(l.x), l1 = unpack_bf16x2(l.y), l2 = unpack_bf16x2(l.z),
+                                     l3 = unpack_bf16x2(l.w);
+                        r0.x += l0.x; r0.y += l0.y; r1.x += l1.x; r1.y += l1.y;
+                        r2.x += l2.x; r2.y += l2.y; r3.x += l3.x; r3.y += l3.y;
+                    }
+                    float x[8];
+                    x[0] = __uint_as_float(v[q * 8 + 0]) + b0.x + r0.x;
+                    x[1] = __uint_as_float(v[q * 8 + 1]) + b0.y + r0.y;
+                    x[2] = __uint_as_float(v[q * 8 + 2]) + b0.z + r1.x;
+                    x[3] = __uint_as_float(v[q * 8 + 3]) + b0.w + r1.y;
+                    x[4] = __uint_as_float(v[q * 8 + 4]) + b1.x + r2.x;
+                    x[5] = __uint_as_float(v[q * 8 + 5]) + b1.y + r2.y;
+                    x[6] = __uint_as_float(v[q * 8 + 6]) + b1.z + r3.x;
+                    x[7] = __uint_as_float(v[q * 8 + 7]) + b1.w + r3.y;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        sum += x[j];
+                        sumsq = fmaf(x[j], x[j], sumsq);
+                        v[q * 8 + j] = __float_as_uint(x[j]);
+                    }
+                }
+                tmem_st_32x32(taddr + c * CHUNK, v);
+                __syncwarp();
+                if (c + 2 < NCH) issue_residual(t, c + 2);
+            }
+            tmem_st_wait();
+            ln_part[half * BM + row_in_tile] = make_float2(sum, sumsq);
+            asm volatile("bar.sync 1, %0;" ::"n"(FF_EPI_THREADS) : "memory");
+            const float2 other = ln_part[(half ^ 1) * BM + row_in_tile];
+            const float inv_n = 1.0f / static_cast<float>(H);
+            const float mean = (sum + other.x) * inv_n;
+            const float var = fmaxf((sumsq + other.y) * inv_n - mean * mean, 0.f);
+            const float rstd = rsqrtf(var + p.eps);
+#pragma unroll 1
+            for (int c = 0; c < NCH; ++c) {
+                float f[32];
+                tmem_ld_32x32(taddr + c * CHUNK, *reinterpret_cast<uint32_t(*)[32]>(&f[0]));
+                tmem_ld_wait();
+                if (c == NCH - 1) {  // OUT fully read: the next tile's GEMM2 may overwrite it
+                    tc_fence_before_sync();
+                    mbar_arrive(bar_out_empty);
+                }
+                const int col0 = half * HALF + c * CHUNK;
+                const float4* g4 = reinterpret_cast<const float4*>(p.gamma + col0);
+                const float4* be4 = reinterpret_cast<const float4*>(p.beta + col0);
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    const float4 g = __ldg(g4 + q), be = __ldg(be4 + q);
+                    f[q * 4 + 0] = fmaf((f[q * 4 + 0] - mean) * rstd, g.x, be.x);
+                    f[q * 4 + 1] = fmaf((f[q * 4 + 1] - mean) * rstd, g.y, be.y);
+                    f[q * 4 + 2] = fmaf((f[q * 4 + 2] - mean) * rstd, g.z, be.z);
+                    f[q * 4 + 3] = fmaf((f[q * 4 + 3] - mean) * rstd, g.w, be.w);
+                }
+                store_chunk(&tmap_c, col0, row0, f, false);
+                if (p.has_lo) store_chunk(&tmap_c_lo, col0, row0, f, true);
+            }
+            // scratch (h + rings) may be refilled once the TMA stores have read their staging buffers
+            if (lane == 0) tma_store_wait_read<0>();
+            __syncwarp();
+            asm volatile("bar.sync 1, %0;" ::"n"(FF_EPI_THREADS) : "memory");  // also protects ln_part
+            mbar_arrive(bar_epi_done);
+        }
+        if (lane == 0) tma_store_wait<0>();
+    }
+
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after_sync();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+template <int H>
+cudaError_t launch_ffn(const FfnFusedArgs& a, cudaStream_t stream, int num_sms) {
+    using C = FfnCfg<H>;
+    alignas(64) CUtensorMap ta, tw1, tw2, tr, trl, tc, tcl;
+    if (!make_tmap(&ta, a.a, a.m, H, BK, BM, false, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
+    if (!make_tmap(&tw1, a.w1, a.inter, H, BK, IC, false, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
+    if (!make_tmap(&tw2, a.w2, H, a.inter, BK, C::UN2, false, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
+    if (!make_tmap(&tr, a.a, a.m, H, CHUNK, 32, false, CU_TENSOR_MAP_SWIZZLE_64B)) return cudaErrorInvalidValue;
+    trl = tr;
+    if (a.a_lo && !make_tmap(&trl, a.a_lo, a.m, H, CHUNK, 32, false, CU_TENSOR_MAP_SWIZZLE_64B)) return cudaErrorInvalidValue;
+    if (!make_tmap(&tc, a.out, a.m, H, CHUNK, 32, false, CU_TENSOR_MAP_SWIZZLE_64B)) return cudaErrorInvalidValue;
+    tcl = tc;
+    if (a.out_lo && !make_tmap(&tcl, a.out_lo, a.m, H, CHUNK, 32, false, CU_TENSOR_MAP_SWIZZLE_64B)) return cudaErrorInvalidValue;
+    auto kern = ffn_fused_kernel<H>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::BYTES);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    FfnDev p;
+    p.m = a.m; p.d_rows = a.d_rows; p.inter = a.inter; p.b1 = a.b1; p.b2 = a.b2; p.gamma = a.gamma; p.beta = a.beta;
+    p.eps = a.eps; p.has_lo = (a.a_lo != nullptr && a.out_lo != nullptr) ? 1 : 0;
+    const int tiles = (a.m + BM - 1) / BM;
+    const int grid = tiles < num_sms ? tiles : num_sms;
+    if (grid <= 0) return cudaSuccess;
+    kern<<<grid, FF_THREADS, C::BYTES, stream>>>(ta, tw1, tw2, tr, trl, tc, tcl, p);
+    return cudaGetLastError();
+}
+
+}  // namespace
+
+bool ffn_fused_supported(int hidden, int inter, int act) {
+    return (hidden == 128 || hidden == 256 || hidden == 384) && inter % IC == 0 && act == 0;
+}
+
+cudaError_t ffn_fused_launch(const FfnFusedArgs& a, cudaStream_t stream, int num_sms) {
+    if (a.m <= 0) return cudaSuccess;
+    if (a.inter % IC != 0) return cudaErrorInvalidValue;
+    if (a.hidden == 128) return launch_ffn<128>(a, stream, num_sms);
+    if (a.hidden == 256) return launch_ffn<256>(a, stream, num_sms);
+    if (a.hidden == 384) return launch_ffn<384>(a, stream, num_sms);
+    return cudaErrorInvalidValue;
+}
+
+}  // namespace b200

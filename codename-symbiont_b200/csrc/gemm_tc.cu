@@ -38,6 +38,7 @@
 #include <mutex>
 
 #include "common.cuh"
+#include "tc_helpers.cuh"
 
 namespace b200 {
 
@@ -51,10 +52,6 @@ constexpr int EPI_WARP0 = 4;
 constexpr int EPI_WARPS = 8;
 constexpr int EPI_THREADS = EPI_WARPS * 32;
 constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;
-constexpr int CHUNK = 32;                   // epilogue chunk: 32 rows x 32 columns per warp
-constexpr int CHUNK_BF16 = 32 * CHUNK * 2;  // 2 KB, 64-byte rows (SWIZZLE_64B)
-constexpr int CHUNK_F32 = 32 * CHUNK * 4;   // 4 KB, 128-byte rows (SWIZZLE_128B)
-constexpr int SMEM_LIMIT = 232448;          // 227 KB per CTA on sm_100
 
 __host__ __device__ constexpr int b_stage_bytes(int block_n) { return block_n * BLOCK_K * 2; }
 // per-warp epilogue shared memory: 2 output staging buffers (+ a `ring`-stage (hi, lo) residual ring for LN)
@@ -119,88 +116,14 @@ struct GemmDev {
     int dbg;  // timing experiments only (B200_EMBED_GEMM_DBG): 1 no TMA stores, 2 no cluster exchange, 4 no pass-2 math
 };
 
-// gelu_erf(x) = 0.5 x (1 + erf(x / sqrt 2)) with erf(x / sqrt 2) ~= tanh(x (c1 + c3 x^2 + c5 x^4 + c7 x^6)) on
-// |x| <= 5 (clamped; beyond that both sides are 1 to 1e-6). Coefficients from scripts/fit_gelu.py: max abs error
-// 1.2e-5 (2.5e-5 |x|), 40x tighter than the usual tanh-GELU and far below the bf16 rounding of the output.
-// One MUFU.TANH + 8 FMA-pipe ops instead of ~25 for erff().
-__device__ __forceinline__ float gelu_erf_fast(float x) {
-    const float xc = fminf(fmaxf(x, -5.0f), 5.0f);
-    const float x2 = xc * xc;
-    float p = fmaf(x2, -8.645902750674527e-06f, -2.546073342664881e-04f);
-    p = fmaf(x2, p, 3.672949335123125e-02f);
-    p = fmaf(x2, p, 7.976898743684135e-01f);
-    float t;
-    asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(xc * p));
-    const float hx = 0.5f * x;
-    return fmaf(hx, t, hx);
-}
-
-template <int EPI>
-__device__ __forceinline__ float epi_act(float x) {
-    if constexpr (EPI == EPI_GELU_ERF) return gelu_erf_fast(x);
-    else if constexpr (EPI == EPI_GELU_TANH) return activate(x, 1);
-    else if constexpr (EPI == EPI_RELU) return fmaxf(x, 0.f);
-    else return x;
-}
-
-// Writes this thread's row of a 32x32 chunk into a staging buffer laid out as the TMA box expects.
-// bf16: 64-byte rows, SWIZZLE_64B (16-byte piece q of row r lands at piece q ^ ((r >> 1) & 3)).
-__device__ __forceinline__ void stage_row_bf16(uint32_t buf, int r, const float (&f)[32]) {
-    const uint32_t row = buf + r * 64;
-    const int sw = (r >> 1) & 3;
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        const uint32_t a = row + ((q ^ sw) << 4);
-        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(pack_bf16x2(f[q * 8 + 0], f[q * 8 + 1])),
-                     "r"(pack_bf16x2(f[q * 8 + 2], f[q * 8 + 3])), "r"(pack_bf16x2(f[q * 8 + 4], f[q * 8 + 5])),
-                     "r"(pack_bf16x2(f[q * 8 + 6], f[q * 8 + 7]))
-                     : "memory");
-    }
-}
-// lo[j] = bf16(f[j] - bf16(f[j])): the part of the fp32 value the bf16 "hi" tensor dropped
-__device__ __forceinline__ void stage_row_bf16_lo(uint32_t buf, int r, const float (&f)[32]) {
-    const uint32_t row = buf + r * 64;
-    const int sw = (r >> 1) & 3;
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        uint32_t w[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const float a = f[q * 8 + 2 * j], b = f[q * 8 + 2 * j + 1];
-            const float2 h = unpack_bf16x2(pack_bf16x2(a, b));
-            w[j] = pack_bf16x2(a - h.x, b - h.y);
-        }
-        const uint32_t a = row + ((q ^ sw) << 4);
-        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3])
-                     : "memory");
-    }
-}
-// fp32: 128-byte rows, SWIZZLE_128B (piece q of row r lands at piece q ^ (r & 7)).
-__device__ __forceinline__ void stage_row_f32(uint32_t buf, int r, const float (&f)[32]) {
-    const uint32_t row = buf + r * 128;
-    const int sw = r & 7;
-#pragma unroll
-    for (int q = 0; q < 8; ++q) {
-        const uint32_t a = row + ((q ^ sw) << 4);
-        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(f[q * 4 + 0]), "f"(f[q * 4 + 1]),
-                     "f"(f[q * 4 + 2]), "f"(f[q * 4 + 3])
-                     : "memory");
-    }
-}
-__device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
-    uint4 v;
-    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
-    return v;
-}
-
-template <int BLOCK_N, int EPI, typename OutT, int CL, int PAIR, int KSLOTS, int RING>
+template <int BLOCK_N, int EPI, typename OutT, int CL, int PAIR, int KSLOTS, int RING, int NSP>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const __grid_constant__ CUtensorMap tmap_c, const __grid_constant__ CUtensorMap tmap_c_lo,
                const __grid_constant__ CUtensorMap tmap_r, const __grid_constant__ CUtensorMap tmap_r_lo,
                const GemmDev p) {
     constexpr bool OUT_F32 = sizeof(OutT) == 4;
-    constexpr int NSPLIT = BLOCK_N > 256 ? 2 : 1;
+    constexpr int NSPLIT = NSP ? NSP : (BLOCK_N > 256 ? 2 : 1);  // independent accumulator column ranges per k-step
     constexpr int UMMA_N = BLOCK_N / NSPLIT;
     constexpr int ACC_STAGES = (2 * BLOCK_N <= 512) ? 2 : 1;
     constexpr int B_STAGE_BYTES = b_stage_bytes(BLOCK_N);
@@ -622,38 +545,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
-PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
-    static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
-    static std::once_flag once;
-    std::call_once(once, [] {
-        void* ptr = nullptr;
-        cudaDriverEntryPointQueryResult qres;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
-            qres == cudaDriverEntryPointSuccess)
-            fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(ptr);
-    });
-    return fn;
-}
-
-// Row-major [rows, cols] matrix of 2- or 4-byte elements; box = box_cols x box_rows.
-bool make_tmap(CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t cols, uint32_t box_cols, uint32_t box_rows,
-               bool f32, CUtensorMapSwizzle swizzle) {
-    auto fn = get_encode_fn();
-    if (!fn) return false;
-    const uint64_t es = f32 ? 4 : 2;
-    cuuint64_t dims[2] = {cols, rows};
-    cuuint64_t strides[1] = {cols * es};
-    cuuint32_t box[2] = {box_cols, box_rows};
-    cuuint32_t estr[2] = {1, 1};
-    CUresult r = fn(map, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
-                    const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle,
-                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    return r == CUDA_SUCCESS;
-}
-
-template <int BLOCK_N, int EPI, typename OutT, int CL = 1, int PAIR = 0, int KSLOTS = 0, int RING = 2>
+template <int BLOCK_N, int EPI, typename OutT, int CL = 1, int PAIR = 0, int KSLOTS = 0, int RING = 2, int NSP = 0>
 cudaError_t launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms) {
-    constexpr int NSPLIT = BLOCK_N > 256 ? 2 : 1;
+    constexpr int NSPLIT = NSP ? NSP : (BLOCK_N > 256 ? 2 : 1);
     constexpr bool OUT_F32 = sizeof(OutT) == 4;
     constexpr int CSIZE = CL > 1 ? CL : (PAIR ? 2 : 1);
     alignas(64) CUtensorMap ta, tb, tc, tcl, tr, trl;
@@ -672,7 +566,7 @@ cudaError_t launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms) {
         if (a.residual_lo && !make_tmap(&trl, a.residual_lo, a.m, a.n, CHUNK, 32, false, csw))
             return cudaErrorInvalidValue;
     }
-    auto kern = gemm_tc_kernel<BLOCK_N, EPI, OutT, CL, PAIR, KSLOTS, RING>;
+    auto kern = gemm_tc_kernel<BLOCK_N, EPI, OutT, CL, PAIR, KSLOTS, RING, NSP>;
     constexpr int smem = smem_bytes(BLOCK_N, EPI, OUT_F32, KSLOTS, RING);
     static_assert(num_stages(BLOCK_N, EPI, OUT_F32, KSLOTS, RING) >= 2, "not enough shared memory for a pipeline");
     static_assert(smem <= SMEM_LIMIT, "shared memory budget exceeded");
@@ -754,13 +648,18 @@ cudaError_t gemm_tc_launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms
         if (a.block_n == 256 && cl == 4) return launch<256, EPI_RES_LN, __nv_bfloat16, 4>(a, stream, num_sms);
         return cudaErrorInvalidValue;
     }
+    const bool nsplit2 = a.block_n == 256 && a.nsplit == 2;
     // K <= 384 with several column tiles per row block: keep the activation tile resident (6 x 64 columns)
     const bool res_a = !a.pair && !a.no_resident_a && a.k <= 6 * BLOCK_K && a.n / a.block_n >= 2;
-#define B200_CASE(BN, EP, T)                                                        \
-    if (a.block_n == BN && a.epi == EP && a.out_f32 == (sizeof(T) == 4))            \
-        return a.pair ? launch<BN, EP, T, 1, 1, 0>(a, stream, num_sms)              \
-               : res_a ? launch<BN, EP, T, 1, 0, 6>(a, stream, num_sms)             \
-                       : launch<BN, EP, T, 1, 0, 0>(a, stream, num_sms);
+    // nsplit == 2 (B200_EMBED_GEMM_NSPLIT=2): 256-wide tiles issued as two independent 128-column accumulator chains per
+    // k-step. Measured 62 % -> 71 % of the MMA rate at K = 4096 but slower at K = 384 with the GELU epilogue
+    // (FFN1 0.78 vs 0.68 ms), so it is off by default.
+#define B200_CASE(BN, EP, T)                                                                   \
+    if (a.block_n == BN && a.epi == EP && a.out_f32 == (sizeof(T) == 4))                       \
+        return a.pair    ? launch<BN, EP, T, 1, 1, 0, 2, 0>(a, stream, num_sms)                \
+               : res_a   ? launch<BN, EP, T, 1, 0, 6, 2, 0>(a, stream, num_sms)                \
+               : nsplit2 ? launch<BN, EP, T, 1, 0, 0, 2, (BN == 256 ? 2 : 0)>(a, stream, num_sms) \
+                         : launch<BN, EP, T, 1, 0, 0, 2, 0>(a, stream, num_sms);
     B200_CASE(128, EPI_BIAS, __nv_bfloat16)
     B200_CASE(192, EPI_BIAS, __nv_bfloat16)
     B200_CASE(256, EPI_BIAS, __nv_bfloat16)

@@ -44,6 +44,22 @@ cudaError_t launch_attention_bf16(const __nv_bfloat16* qkv, const int* cu, int b
 cudaError_t launch_attention_tc(const __nv_bfloat16* qkv, const int* cu, int rows_cap, int batch, int max_seqlen,
                                 int heads, int head_dim, __nv_bfloat16* ctx, int num_sms, cudaStream_t s);
 
+// K2f (ffn_fused.cu): x' = LayerNorm(gelu(a.W1^T + b1).W2^T + b2 + a) in one kernel; hidden 128 / 256 / 384, erf-GELU.
+struct FfnFusedArgs {
+    const void* a;       // [m, hidden] bf16: GEMM operand and high half of the residual
+    const void* a_lo;    // [m, hidden] bf16 low half of the residual, or nullptr
+    const void* w1;      // [inter, hidden] bf16 (intermediate.dense.weight)
+    const void* w2;      // [hidden, inter] bf16 (output.dense.weight)
+    const float *b1, *b2, *gamma, *beta;
+    float eps;
+    int m, hidden, inter;
+    const int* d_rows;   // optional device-side row count
+    void* out;           // [m, hidden] bf16 (hi)
+    void* out_lo;        // [m, hidden] bf16 (lo) or nullptr
+};
+bool ffn_fused_supported(int hidden, int inter, int act);
+cudaError_t ffn_fused_launch(const FfnFusedArgs& a, cudaStream_t stream, int num_sms);
+
 // fp32 validation kernels (correctness only).
 cudaError_t launch_attention_f32(const float* qkv, const int* cu, int batch, int max_seqlen, int heads,
                                  int head_dim, float* ctx, cudaStream_t s);

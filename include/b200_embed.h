@@ -139,7 +139,9 @@ int64_t b200_embed_kernel_launches(const b200_embed* h);
 #define B200_EMBED_KIND_GEMM_FFN2 6 /* K2 output.dense (+res+LN fused)  (BertOutput) */
 #define B200_EMBED_KIND_ADD_LN 7    /* K4 residual + LayerNorm when not fused */
 #define B200_EMBED_KIND_POOL 8      /* K5 masked mean-pool (+L2)        (embedding_generator.rs:201-207) */
-#define B200_EMBED_NUM_KINDS 9
+#define B200_EMBED_KIND_FFN_FUSED 9 /* K2f intermediate.dense + GELU + output.dense + residual + LayerNorm in one kernel
+                                       (BertIntermediate + BertOutput); replaces kinds 5 and 6 when hidden <= 384 */
+#define B200_EMBED_NUM_KINDS 10
 typedef struct b200_embed_kind_stats {
     double total_ms;  /* sum of event-timed durations */
     int64_t launches;
@@ -166,6 +168,12 @@ int32_t b200_op_embed_layernorm(b200_embed* h, const uint32_t* ids_packed, const
  * 3 output.dense (+ residual + LayerNorm). residual is read only for which = 1, 3. */
 int32_t b200_op_linear(b200_embed* h, int32_t layer, int32_t which, const void* x, const void* residual,
                        const void* residual_lo, int32_t rows, int32_t dtype, void* y, void* y_lo, void* stream);
+/* K2f. y = LayerNorm(gelu(x . Wi^T + bi) . Wo^T + bo + x) with the feed-forward weights of `layer`, in one kernel
+ * (bf16 tensor cores; hidden size 128 / 256 / 384 with erf-GELU, else B200_EMBED_ERR_UNSUPPORTED_SHAPE).
+ * x / x_lo and y / y_lo are (hi, lo) bf16 pairs as above. (bert.rs BertIntermediate::forward + BertOutput::forward) */
+int32_t b200_op_ffn(b200_embed* h, int32_t layer, const void* x, const void* x_lo, int32_t rows, void* y, void* y_lo,
+                    void* stream);
+
 /* The same Linear + residual + LayerNorm step as b200_op_linear(which = 1 or 3) for callers that must not
  * allocate. It has no counterpart in the reference. b200_op_linear parks the fp32 pre-LayerNorm rows in a
  * cudaMalloc'ed temporary when the LayerNorm is not fused into the GEMM (hidden sizes other than 128/256/384,

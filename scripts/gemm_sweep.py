@@ -23,8 +23,14 @@ def run(m, n, k, bn, act=-1, reps=20):
     tf = 2.0 * m * n * k / (ms * 1e-3) / 1e12
     print(f"M {m:7d} N {n:5d} K {k:5d} BN {bn:3d} act {act:2d}: {ms:8.3f} ms  {tf:7.1f} TFLOP/s  sm clock {clk} MHz  "
           f"= {100*tf/(148*8192*clk*1e6/1e12):.1f}% of MMA peak at that clock", flush=True)
-for bn in (256, 192, 128):
-    run(65536, 3072 if bn != 192 else 2304, 4096, bn)
+for ns in ('1', '2'):
+    os.environ['B200_EMBED_GEMM_NSPLIT'] = ns
+    print('NSPLIT', ns)
+    for bn in (256, 192, 128):
+        run(65536, 3072 if bn != 192 else 2304, 4096, bn)
+    run(524288, 1152, 384, 192)
+    run(524288, 1536, 384, 256)
+os.environ['B200_EMBED_GEMM_NSPLIT'] = '1'
 run(524288, 1152, 384, 192)
 run(524288, 1536, 384, 256)
 run(524288, 1536, 384, 256, act=0)

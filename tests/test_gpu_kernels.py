@@ -137,6 +137,32 @@ def test_k2_linear_layers(env, dtype, which):
         assert np.abs(got + host(out_lo) - want).max() <= 2e-3
 
 
+@pytest.mark.parametrize("H,heads,I,rows", [(128, 4, 512, 333), (256, 8, 1024, 1000), (384, 12, 1536, 3000)])
+def test_k2f_fused_ffn(pkg, built, H, heads, I, rows):
+    """intermediate.dense + GELU + output.dense + residual + LayerNorm in one kernel (bert.rs BertIntermediate +
+    BertOutput): the intermediate never leaves the SM. Oracle on the same bf16-rounded weights and input; the
+    intermediate is rounded to bf16 on the GPU (it is the second GEMM's operand), hence the tolerance."""
+    shape = pkg.weights.BertShape(512, H, 1, heads, I, 64, 2)
+    rng = np.random.default_rng(H)
+    x = rng.standard_normal((rows, H)).astype(np.float32)
+    x_hi = bf16_round(x)
+    with pkg.Embedder.random_init(shape, seed=4) as emb:
+        w = emb.export_weights()
+        o = Oracle(shape, {k: bf16_round(v) if v.ndim == 2 else v for k, v in w.items()}, "f32")
+        inter = o.activation(o.linear(x_hi, o.layer(0, "intermediate.dense.weight"), o.layer(0, "intermediate.dense.bias")), 0)
+        y = o.linear(bf16_round(inter), o.layer(0, "output.dense.weight"), o.layer(0, "output.dense.bias"))
+        want = o.add_layer_norm(y, x, o.layer(0, "output.LayerNorm.weight"), o.layer(0, "output.LayerNorm.bias"),
+                                shape.layer_norm_eps)
+        dx, dx_lo = dev(x, torch.bfloat16), dev(x - x_hi, torch.bfloat16)
+        out = torch.full((rows, H), float("nan"), dtype=torch.bfloat16, device="cuda")
+        out_lo = torch.full((rows, H), float("nan"), dtype=torch.bfloat16, device="cuda")
+        emb.op_ffn(0, dx.data_ptr(), dx_lo.data_ptr(), rows, out.data_ptr(), out_lo.data_ptr())
+        got, got_lo = host(out), host(out_lo)
+    assert np.isfinite(got).all() and np.isfinite(got_lo).all()
+    assert np.abs(got - want).max() <= 0.006 * np.abs(want).max() + 1e-3
+    assert np.abs(got + got_lo - want).max() <= 2e-3
+
+
 @pytest.mark.parametrize("which", [1, 3])
 @pytest.mark.parametrize("H,heads,I", [(256, 8, 512), (384, 12, 1536), (512, 8, 1024), (768, 12, 3072), (640, 10, 1280)])
 def test_k2_layernorm_epilogue_across_hidden_sizes(pkg, built, H, heads, I, which):
