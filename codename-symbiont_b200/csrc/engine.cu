@@ -328,6 +328,8 @@ int gemm16(b200_embed* h, Context& c, cudaStream_t s, int kind, const void* x, c
     g.pair = h->gemm_pair ? 1 : 0;
     g.no_resident_a = h->gemm_res_a ? 0 : 1;
     if (const char* nv = getenv("B200_EMBED_GEMM_NSPLIT")) g.nsplit = atoi(nv);
+    if (const char* wv = getenv("B200_EMBED_GEMM_WIDE_STORE")) g.wide_store = atoi(wv);
+    if (getenv("B200_EMBED_QKV_BN128") && kind == B200_EMBED_KIND_GEMM_QKV) g.block_n = 128;
     CU_TRY(timed(h, c, s, kind, 1, [&] { return b200::gemm_tc_launch(g, s, h->num_sms); }));
     return B200_EMBED_OK;
 }

@@ -55,8 +55,8 @@ constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;
 
 __host__ __device__ constexpr int b_stage_bytes(int block_n) { return block_n * BLOCK_K * 2; }
 // per-warp epilogue shared memory: 2 output staging buffers (+ a `ring`-stage (hi, lo) residual ring for LN)
-__host__ __device__ constexpr int epi_warp_bytes(int epi, bool out_f32, int ring) {
-    return (epi == EPI_RES_LN ? ring * 2 * CHUNK_BF16 : 0) + 2 * (out_f32 ? CHUNK_F32 : CHUNK_BF16);
+__host__ __device__ constexpr int epi_warp_bytes(int epi, bool out_f32, int ring, bool wide = false) {
+    return (epi == EPI_RES_LN ? ring * 2 * CHUNK_BF16 : 0) + 2 * ((out_f32 || wide) ? CHUNK_F32 : CHUNK_BF16);
 }
 // mbarriers (<= 8 + 8 stage, 4 TMEM, 16 residual, 2 cluster exchange) + TMEM pointer, then the LayerNorm partial
 // statistics of the two column halves, then (clusters) the slots peers write their row partials into
@@ -64,20 +64,21 @@ constexpr int MAX_CLUSTER = 4;
 constexpr int AUX_BARRIERS = 512;
 constexpr int AUX_LN_PART = 2 * BLOCK_M * 8;
 constexpr int AUX_LN_PEER = 2 * MAX_CLUSTER * BLOCK_M * 8;  // [tile parity][sender rank][row] float2
-__host__ __device__ constexpr int aux_bytes(int epi) {
-    return AUX_BARRIERS + (epi == EPI_RES_LN ? AUX_LN_PART + AUX_LN_PEER : 0);
+// plain epilogues instead keep the bias of the current and the next tile's columns there ([tile parity][BLOCK_N] fp32)
+__host__ __device__ constexpr int aux_bytes(int epi, int block_n) {
+    return AUX_BARRIERS + (epi == EPI_RES_LN ? AUX_LN_PART + AUX_LN_PEER : 2 * block_n * 4);
 }
 // kslots == 0: A and W stream through the same ring of stages. kslots > 0 ("resident A"): the whole 128 x K
 // activation tile sits in `kslots` fixed 16 KB slots while the CTA walks every column tile of that row block, and
 // only W streams through the ring.
-__host__ __device__ constexpr int num_stages(int block_n, int epi, bool out_f32, int kslots, int ring) {
-    int s = (SMEM_LIMIT - aux_bytes(epi) - EPI_WARPS * epi_warp_bytes(epi, out_f32, ring) - kslots * A_STAGE_BYTES) /
+__host__ __device__ constexpr int num_stages(int block_n, int epi, bool out_f32, int kslots, int ring, bool wide = false) {
+    int s = (SMEM_LIMIT - aux_bytes(epi, block_n) - EPI_WARPS * epi_warp_bytes(epi, out_f32, ring, wide) - kslots * A_STAGE_BYTES) /
             ((kslots ? 0 : A_STAGE_BYTES) + b_stage_bytes(block_n));
     return s > 8 ? 8 : s;
 }
-__host__ __device__ constexpr int smem_bytes(int block_n, int epi, bool out_f32, int kslots, int ring) {
-    return num_stages(block_n, epi, out_f32, kslots, ring) * ((kslots ? 0 : A_STAGE_BYTES) + b_stage_bytes(block_n)) +
-           kslots * A_STAGE_BYTES + EPI_WARPS * epi_warp_bytes(epi, out_f32, ring) + aux_bytes(epi);
+__host__ __device__ constexpr int smem_bytes(int block_n, int epi, bool out_f32, int kslots, int ring, bool wide = false) {
+    return num_stages(block_n, epi, out_f32, kslots, ring, wide) * ((kslots ? 0 : A_STAGE_BYTES) + b_stage_bytes(block_n)) +
+           kslots * A_STAGE_BYTES + EPI_WARPS * epi_warp_bytes(epi, out_f32, ring, wide) + aux_bytes(epi, block_n);
 }
 
 // ---- thread-block cluster helpers (distributed shared memory) ----
@@ -116,7 +117,7 @@ struct GemmDev {
     int dbg;  // timing experiments only (B200_EMBED_GEMM_DBG): 1 no TMA stores, 2 no cluster exchange, 4 no pass-2 math
 };
 
-template <int BLOCK_N, int EPI, typename OutT, int CL, int PAIR, int KSLOTS, int RING, int NSP>
+template <int BLOCK_N, int EPI, typename OutT, int CL, int PAIR, int KSLOTS, int RING, int NSP, int WST>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const __grid_constant__ CUtensorMap tmap_c, const __grid_constant__ CUtensorMap tmap_c_lo,
@@ -127,12 +128,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     constexpr int UMMA_N = BLOCK_N / NSPLIT;
     constexpr int ACC_STAGES = (2 * BLOCK_N <= 512) ? 2 : 1;
     constexpr int B_STAGE_BYTES = b_stage_bytes(BLOCK_N);
-    constexpr int STAGES = num_stages(BLOCK_N, EPI, OUT_F32, KSLOTS, RING);
+    constexpr bool WIDE = WST != 0;  // stage two chunks side by side and store 128-byte row segments
+    constexpr int STAGES = num_stages(BLOCK_N, EPI, OUT_F32, KSLOTS, RING, WIDE);
     constexpr bool RES_A = KSLOTS > 0;
     static_assert(!RES_A || (CL == 1 && PAIR == 0 && KSLOTS <= 8), "resident A is for the plain single-CTA GEMMs");
     constexpr int HALF_N = BLOCK_N / 2;  // columns per epilogue warp group
     constexpr int NCH = HALF_N / CHUNK;  // chunks per warp per tile
-    constexpr int EPI_WARP_BYTES = epi_warp_bytes(EPI, OUT_F32, RING);
+    constexpr int EPI_WARP_BYTES = epi_warp_bytes(EPI, OUT_F32, RING, WIDE);
+    static_assert(!WIDE || (EPI != EPI_RES_LN && !OUT_F32 && NCH % 2 == 0), "wide stores: plain bf16 epilogues, even chunk count");
     constexpr bool KEEP_IN_REGS = NCH <= 3;  // LN: hold acc + bias + residual in registers between the two passes
     static_assert(RING >= 2 && RING <= 3, "residual ring depth");
     constexpr int OUT_CHUNK_BYTES = OUT_F32 ? CHUNK_F32 : CHUNK_BF16;
@@ -237,8 +240,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
+            const uint64_t pol_w = l2_policy_evict_last();
             for (int i = 0; i < my_tiles; ++i) {
                 const int m_tile = tile_m(i), n_tile = tile_n(i);
+                if ((p.dbg & 16) && i + 2 < my_tiles) {  // A tile of the tile after next -> L2
+                    const int pm = tile_m(i + 2);
+                    if (CL > 1 || tile_n(i + 2) == 0 || (p.dbg & 128))
+                        for (int kb = 0; kb < num_kb; ++kb) tma_prefetch_2d(&tmap_a, kb * BLOCK_K, pm * BLOCK_M);
+                }
                 for (int kb = 0; kb < num_kb; ++kb) {
                     if constexpr (RES_A) {
                         if (n_tile == 0) {  // new row block: (re)fill resident slot kb once the previous block let go of it
@@ -266,9 +275,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                                               CMASK);
                     } else {
 #pragma unroll
-                        for (int s = 0; s < NSPLIT; ++s)
-                            tma_load_2d(smem_b + stage * B_STAGE_BYTES + s * (UMMA_N * BLOCK_K * 2), &tmap_b,
-                                        kb * BLOCK_K, n_tile * BLOCK_N + s * UMMA_N, bar_full + 8 * stage);
+                        for (int s = 0; s < NSPLIT; ++s) {
+                            if (p.dbg & 64)
+                                tma_load_2d_hint(smem_b + stage * B_STAGE_BYTES + s * (UMMA_N * BLOCK_K * 2), &tmap_b,
+                                                 kb * BLOCK_K, n_tile * BLOCK_N + s * UMMA_N, bar_full + 8 * stage, pol_w);
+                            else
+                                tma_load_2d(smem_b + stage * B_STAGE_BYTES + s * (UMMA_N * BLOCK_K * 2), &tmap_b,
+                                            kb * BLOCK_K, n_tile * BLOCK_N + s * UMMA_N, bar_full + 8 * stage);
+                        }
                     }
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
@@ -325,6 +339,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         const uint32_t my_smem = smem_epi + ew * EPI_WARP_BYTES;
         const uint32_t out_buf = my_smem + (EPI == EPI_RES_LN ? RING * 2 * CHUNK_BF16 : 0);  // 2 x OUT_CHUNK_BYTES
         uint32_t st_it = 0;  // output staging buffers used so far (alternating)
+        const uint64_t pol_out = l2_policy_evict_first();
 
         // stages one chunk and hands it to the TMA store engine; at most one older store may still be reading
         auto store_chunk = [&](const CUtensorMap* map, int col0, int row0, const float (&f)[32], bool lo) {
@@ -338,7 +353,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0) {
-                tma_store_2d(map, buf, col0, row0);
+                if (p.dbg & 32) tma_store_2d_hint(map, buf, col0, row0, pol_out);
+                else tma_store_2d(map, buf, col0, row0);
                 tma_store_commit();
             }
             ++st_it;
@@ -374,10 +390,85 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             const int col_base = n_tile * BLOCK_N + half * HALF_N;
             const uint32_t taddr =
                 tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * BLOCK_N + half * HALF_N;
-            mbar_wait(bar_tfull + 8 * acc, acc_phase);
-            tc_fence_after_sync();
-
-            if constexpr (EPI != EPI_RES_LN) {
+            if (p.dbg & 8) {  // mainloop only
+                mbar_wait(bar_tfull + 8 * acc, acc_phase);
+                tc_fence_before_sync();
+                mbar_arrive(bar_tempty + 8 * acc);
+                continue;
+            }
+            if constexpr (EPI != EPI_RES_LN && !OUT_F32) {
+                // Bias of this tile's columns -> shared memory (one warp per column half loads, the half's four warps
+                // meet on a named barrier); the accumulator chunks are then read one ahead of the math on them.
+                const uint32_t bias_s = aux + AUX_BARRIERS + ((it & 1) * BLOCK_N + half * HALF_N) * 4;
+                if (quad == 0 && lane * 4 < HALF_N) {
+                    const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col_base) + lane);
+                    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(bias_s + lane * 16), "f"(b.x), "f"(b.y),
+                                 "f"(b.z), "f"(b.w)
+                                 : "memory");
+                }
+                asm volatile("bar.sync %0, 128;" ::"r"(1 + half) : "memory");
+                mbar_wait(bar_tfull + 8 * acc, acc_phase);
+                tc_fence_after_sync();
+                uint32_t v[2][32];
+                tmem_ld_32x32(taddr, v[0]);
+#pragma unroll
+                for (int c = 0; c < NCH; ++c) {
+                    tmem_ld_wait();
+                    if (c + 1 < NCH) {
+                        tmem_ld_32x32(taddr + (c + 1) * CHUNK, v[(c + 1) & 1]);
+                    } else {  // accumulator drained: the MMA warp may start the tile after next
+                        tc_fence_before_sync();
+                        mbar_arrive(bar_tempty + 8 * acc);
+                    }
+                    const int col0 = col_base + c * CHUNK;
+                    uint32_t w[16];
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) {
+                        const uint4 bq = lds_v4(bias_s + (c * CHUNK + q * 4) * 4);
+                        w[q * 2 + 0] = epi_pair_bf16<EPI>(v[c & 1][q * 4 + 0], v[c & 1][q * 4 + 1], __uint_as_float(bq.x),
+                                                          __uint_as_float(bq.y));
+                        w[q * 2 + 1] = epi_pair_bf16<EPI>(v[c & 1][q * 4 + 2], v[c & 1][q * 4 + 3], __uint_as_float(bq.z),
+                                                          __uint_as_float(bq.w));
+                    }
+                    if (p.dbg & 1) continue;
+                    if constexpr (WIDE) {
+                        const uint32_t buf = out_buf + ((st_it >> 1) & 1) * CHUNK_F32;
+                        if ((c & 1) == 0) {
+                            if (lane == 0) tma_store_wait_read<1>();
+                            __syncwarp();
+                        }
+                        const uint32_t row = buf + lane * 128;
+#pragma unroll
+                        for (int q = 0; q < 4; ++q)
+                            sts_v4(row + ((((c & 1) * 4 + q) ^ (lane & 7)) << 4), w[q * 4], w[q * 4 + 1], w[q * 4 + 2], w[q * 4 + 3]);
+                        if (c & 1) {
+                            fence_proxy_async_smem();
+                            __syncwarp();
+                            if (lane == 0) {
+                                tma_store_2d(&tmap_c, buf, col0 - CHUNK, row0);
+                                tma_store_commit();
+                            }
+                        }
+                    } else {
+                        const uint32_t buf = out_buf + (st_it & 1) * CHUNK_BF16;
+                        if (lane == 0) tma_store_wait_read<1>();
+                        __syncwarp();
+                        const uint32_t row = buf + lane * 64;
+#pragma unroll
+                        for (int q = 0; q < 4; ++q)
+                            sts_v4(row + ((q ^ ((lane >> 1) & 3)) << 4), w[q * 4], w[q * 4 + 1], w[q * 4 + 2], w[q * 4 + 3]);
+                        fence_proxy_async_smem();
+                        __syncwarp();
+                        if (lane == 0) {
+                            tma_store_2d(&tmap_c, buf, col0, row0);
+                            tma_store_commit();
+                        }
+                    }
+                    ++st_it;
+                }
+            } else if constexpr (EPI != EPI_RES_LN) {
+                mbar_wait(bar_tfull + 8 * acc, acc_phase);
+                tc_fence_after_sync();
 #pragma unroll 1
                 for (int c = 0; c < NCH; ++c) {
                     uint32_t v[32];
@@ -401,6 +492,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     store_chunk(&tmap_c, col0, row0, f, false);
                 }
             } else {
+                mbar_wait(bar_tfull + 8 * acc, acc_phase);
+                tc_fence_after_sync();
                 // pass 1: x = acc + bias + residual; row sum and sum of squares. x stays in registers when the warp's
                 // share of the row is at most 3 chunks (the accumulator is then free after this pass), else it is
                 // parked back in TMEM.
@@ -545,7 +638,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
-template <int BLOCK_N, int EPI, typename OutT, int CL = 1, int PAIR = 0, int KSLOTS = 0, int RING = 2, int NSP = 0>
+template <int BLOCK_N, int EPI, typename OutT, int CL = 1, int PAIR = 0, int KSLOTS = 0, int RING = 2, int NSP = 0, int WST = 0>
 cudaError_t launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms) {
     constexpr int NSPLIT = NSP ? NSP : (BLOCK_N > 256 ? 2 : 1);
     constexpr bool OUT_F32 = sizeof(OutT) == 4;
@@ -555,8 +648,8 @@ cudaError_t launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms) {
         return cudaErrorInvalidValue;
     if (!make_tmap(&tb, a.b, a.n, a.k, BLOCK_K, BLOCK_N / NSPLIT / (PAIR ? 2 : 1), false, CU_TENSOR_MAP_SWIZZLE_128B))
         return cudaErrorInvalidValue;
-    const CUtensorMapSwizzle csw = OUT_F32 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
-    if (!make_tmap(&tc, a.out, a.m, a.n, CHUNK, 32, OUT_F32, csw)) return cudaErrorInvalidValue;
+    const CUtensorMapSwizzle csw = (OUT_F32 || WST) ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+    if (!make_tmap(&tc, a.out, a.m, a.n, WST ? 2 * CHUNK : CHUNK, 32, OUT_F32, csw)) return cudaErrorInvalidValue;
     tcl = tc; tr = tc; trl = tc;
     if (a.out_lo && !make_tmap(&tcl, a.out_lo, a.m, a.n, CHUNK, 32, false, csw)) return cudaErrorInvalidValue;
     if (EPI == EPI_RES_LN) {
@@ -566,9 +659,9 @@ cudaError_t launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms) {
         if (a.residual_lo && !make_tmap(&trl, a.residual_lo, a.m, a.n, CHUNK, 32, false, csw))
             return cudaErrorInvalidValue;
     }
-    auto kern = gemm_tc_kernel<BLOCK_N, EPI, OutT, CL, PAIR, KSLOTS, RING, NSP>;
-    constexpr int smem = smem_bytes(BLOCK_N, EPI, OUT_F32, KSLOTS, RING);
-    static_assert(num_stages(BLOCK_N, EPI, OUT_F32, KSLOTS, RING) >= 2, "not enough shared memory for a pipeline");
+    auto kern = gemm_tc_kernel<BLOCK_N, EPI, OutT, CL, PAIR, KSLOTS, RING, NSP, WST>;
+    constexpr int smem = smem_bytes(BLOCK_N, EPI, OUT_F32, KSLOTS, RING, WST != 0);
+    static_assert(num_stages(BLOCK_N, EPI, OUT_F32, KSLOTS, RING, WST != 0) >= 2, "not enough shared memory for a pipeline");
     static_assert(smem <= SMEM_LIMIT, "shared memory budget exceeded");
     static bool attr_set = false;  // per instantiation; benign race (idempotent)
     if (!attr_set) {
@@ -649,6 +742,11 @@ cudaError_t gemm_tc_launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms
         return cudaErrorInvalidValue;
     }
     const bool nsplit2 = a.block_n == 256 && a.nsplit == 2;
+    if (a.wide_store && !a.out_f32 && !a.pair && a.epi != EPI_RES_LN) {  // 128-byte row segments per TMA store
+        if (a.block_n == 256 && a.epi == EPI_BIAS) return launch<256, EPI_BIAS, __nv_bfloat16, 1, 0, 0, 2, 0, 1>(a, stream, num_sms);
+        if (a.block_n == 256 && a.epi == EPI_GELU_ERF) return launch<256, EPI_GELU_ERF, __nv_bfloat16, 1, 0, 0, 2, 0, 1>(a, stream, num_sms);
+        if (a.block_n == 128 && a.epi == EPI_BIAS) return launch<128, EPI_BIAS, __nv_bfloat16, 1, 0, 0, 2, 0, 1>(a, stream, num_sms);
+    }
     // K <= 384 with several column tiles per row block: keep the activation tile resident (6 x 64 columns)
     const bool res_a = !a.pair && !a.no_resident_a && a.k <= 6 * BLOCK_K && a.n / a.block_n >= 2;
     // nsplit == 2 (B200_EMBED_GEMM_NSPLIT=2): 256-wide tiles issued as two independent 128-column accumulator chains per

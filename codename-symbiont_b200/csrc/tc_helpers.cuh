@@ -34,12 +34,67 @@ __device__ __forceinline__ float gelu_erf_fast(float x) {
     return fmaf(hx, t, hx);
 }
 
+// ---- packed fp32 pairs (FFMA2 / FMUL2 / FADD2): same FMA-pipe time as two scalar ops, half the issue slots ----
+__device__ __forceinline__ uint64_t pk2(float a, float b) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+    return r;
+}
+__device__ __forceinline__ void upk2(uint64_t v, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
+    uint64_t r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ uint64_t mul2(uint64_t a, uint64_t b) {
+    uint64_t r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) {
+    uint64_t r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+// gelu_erf_fast on a pair; same arithmetic as the scalar form for |x| <= 5 (x^2 is clamped instead of x: beyond 5 the
+// tanh argument only grows, so the result is 0.5 x (1 +- 1) either way).
+__device__ __forceinline__ uint64_t gelu_erf_fast2(uint64_t x) {
+    float a, b;
+    upk2(mul2(x, x), a, b);
+    const uint64_t x2 = pk2(fminf(a, 25.0f), fminf(b, 25.0f));
+    uint64_t p = fma2(x2, pk2(-8.645902750674527e-06f, -8.645902750674527e-06f), pk2(-2.546073342664881e-04f, -2.546073342664881e-04f));
+    p = fma2(x2, p, pk2(3.672949335123125e-02f, 3.672949335123125e-02f));
+    p = fma2(x2, p, pk2(7.976898743684135e-01f, 7.976898743684135e-01f));
+    upk2(mul2(x, p), a, b);
+    float ta, tb;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(ta) : "f"(a));
+    asm("tanh.approx.f32 %0, %1;" : "=f"(tb) : "f"(b));
+    const uint64_t hx = mul2(x, pk2(0.5f, 0.5f));
+    return fma2(hx, pk2(ta, tb), hx);
+}
+// (acc pair + bias pair) through the epilogue's activation -> two bf16 in one word
+template <int EPI>
+__device__ __forceinline__ uint32_t epi_pair_bf16(uint32_t acc0, uint32_t acc1, float b0, float b1);
+
 template <int EPI>
 __device__ __forceinline__ float epi_act(float x) {
     if constexpr (EPI == EPI_GELU_ERF) return gelu_erf_fast(x);
     else if constexpr (EPI == EPI_GELU_TANH) return activate(x, 1);
     else if constexpr (EPI == EPI_RELU) return fmaxf(x, 0.f);
     else return x;
+}
+
+template <int EPI>
+__device__ __forceinline__ uint32_t epi_pair_bf16(uint32_t acc0, uint32_t acc1, float b0, float b1) {
+    if constexpr (EPI == EPI_GELU_ERF || EPI == EPI_BIAS) {
+        uint64_t x = add2(pk2(__uint_as_float(acc0), __uint_as_float(acc1)), pk2(b0, b1));
+        if constexpr (EPI == EPI_GELU_ERF) x = gelu_erf_fast2(x);
+        float a, b;
+        upk2(x, a, b);
+        return pack_bf16x2(a, b);
+    } else {
+        return pack_bf16x2(epi_act<EPI>(__uint_as_float(acc0) + b0), epi_act<EPI>(__uint_as_float(acc1) + b1));
+    }
 }
 
 // Writes this thread's row of a 32x32 chunk into a staging buffer laid out as the TMA box expects.
@@ -50,6 +105,20 @@ __device__ __forceinline__ void stage_row_bf16(uint32_t buf, int r, const float 
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
         const uint32_t a = row + ((q ^ sw) << 4);
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(pack_bf16x2(f[q * 8 + 0], f[q * 8 + 1])),
+                     "r"(pack_bf16x2(f[q * 8 + 2], f[q * 8 + 3])), "r"(pack_bf16x2(f[q * 8 + 4], f[q * 8 + 5])),
+                     "r"(pack_bf16x2(f[q * 8 + 6], f[q * 8 + 7]))
+                     : "memory");
+    }
+}
+// Same row into a 128-byte-row staging buffer (two chunks side by side, SWIZZLE_128B): chunk `side` fills pieces
+// side * 4 .. side * 4 + 3 of the row.
+__device__ __forceinline__ void stage_row_bf16_wide(uint32_t buf, int r, int side, const float (&f)[32]) {
+    const uint32_t row = buf + r * 128;
+    const int sw = r & 7;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const uint32_t a = row + (((side * 4 + q) ^ sw) << 4);
         asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(pack_bf16x2(f[q * 8 + 0], f[q * 8 + 1])),
                      "r"(pack_bf16x2(f[q * 8 + 2], f[q * 8 + 3])), "r"(pack_bf16x2(f[q * 8 + 4], f[q * 8 + 5])),
                      "r"(pack_bf16x2(f[q * 8 + 6], f[q * 8 + 7]))
@@ -85,6 +154,9 @@ __device__ __forceinline__ void stage_row_f32(uint32_t buf, int r, const float (
                      "f"(f[q * 4 + 2]), "f"(f[q * 4 + 3])
                      : "memory");
     }
+}
+__device__ __forceinline__ void sts_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 __device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
     uint4 v;
