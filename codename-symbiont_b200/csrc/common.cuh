@@ -117,6 +117,46 @@ __device__ __forceinline__ void tma_store_2d(const void* tmap, uint32_t src_smem
                  "r"(src_smem), "r"(c0), "r"(c1)
                  : "memory");
 }
+// ---- thread-block cluster helpers (distributed shared memory) ----
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// shared::cluster address of `local_smem` (a shared::cta address) in CTA `rank` of this cluster
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t local_smem, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_smem), "r"(rank));
+    return r;
+}
+// mbar_wait whose acquire covers arrivals (and the writes released by them) from other CTAs of the cluster
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    long long t0 = 0;
+    for (uint32_t it = 0;; ++it) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (done) break;
+        if (it == 64) t0 = clock64();
+        if (it > 64 && (it & 63) == 0 && clock64() - t0 > 8000000000LL) __trap();
+    }
+}
+// CTA-pair (cta_group::2) forms. The load lands in the executing CTA's shared memory but may signal an mbarrier in
+// the peer CTA (`bar` is a shared::cluster address, e.g. from mapa): the pair's leader waits once for both halves.
+__device__ __forceinline__ void tma_load_2d_cg2(uint32_t dst_smem, const void* tmap, int c0, int c1, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst_smem), "l"(tmap), "r"(bar), "r"(c0), "r"(c1)
+        : "memory");
+}
 // L2 cache policies for the hinted TMA forms below.
 __device__ __forceinline__ uint64_t l2_policy_evict_first() {
     uint64_t p;
@@ -172,6 +212,18 @@ __device__ __forceinline__ void tc_fence_before_sync() {
 __device__ __forceinline__ void tc_fence_after_sync() {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 }
+// True in exactly one lane of a fully converged warp. Keeps the surrounding control flow warp-uniform: the compiler
+// then issues the single-thread tcgen05 / TMA instructions straight from uniform registers instead of wrapping each
+// one in a divergence-safe ELECT loop (which made the MMA-issuing thread, not the tensor pipe, the bottleneck).
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "elect.sync _|p, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(pred));
+    return pred != 0;
+}
 // D[tmem] (+)= A[smem desc] . B[smem desc]; issued by ONE thread for the whole CTA.
 __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
                                           uint32_t accumulate) {
@@ -193,6 +245,36 @@ __device__ __forceinline__ void umma_commit_multicast(uint32_t bar, uint16_t cta
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
                  "h"(cta_mask)
                  : "memory");
+}
+// One MMA over a CTA pair: M = 256 (128 rows from each CTA's A tile), B rows [0, N/2) from the leader's shared memory and
+// [N/2, N) from the peer's, at the same offsets; each CTA's TMEM receives its own 128 rows. Issued by the leader only.
+__device__ __forceinline__ void umma_bf16_cg2(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                              uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit_cg2(uint32_t bar, uint16_t cta_mask) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+                 "h"(cta_mask)
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_cg2(uint32_t dst_smem, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_cg2(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+// Arrive on an mbarrier of another CTA of the cluster (address from mapa). Default semantics (release at CTA scope):
+// the cluster-scope release form costs a MEMBAR.ALL.GPU per arrive and is not needed here - what the waiter consumes
+// is either TMEM state (ordered by tcgen05.fence) or shared memory already pushed to the async proxy by
+// fence.proxy.async in the writing threads.
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t remote_bar) {
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(remote_bar) : "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }

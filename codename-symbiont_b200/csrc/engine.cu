@@ -329,6 +329,7 @@ int gemm16(b200_embed* h, Context& c, cudaStream_t s, int kind, const void* x, c
     g.no_resident_a = h->gemm_res_a ? 0 : 1;
     if (const char* nv = getenv("B200_EMBED_GEMM_NSPLIT")) g.nsplit = atoi(nv);
     if (const char* wv = getenv("B200_EMBED_GEMM_WIDE_STORE")) g.wide_store = atoi(wv);
+    if (const char* pv = getenv("B200_EMBED_GEMM_PAIR")) g.pair = atoi(pv);
     if (getenv("B200_EMBED_QKV_BN128") && kind == B200_EMBED_KIND_GEMM_QKV) g.block_n = 128;
     CU_TRY(timed(h, c, s, kind, 1, [&] { return b200::gemm_tc_launch(g, s, h->num_sms); }));
     return B200_EMBED_OK;
@@ -1046,7 +1047,7 @@ int32_t b200_op_gemm_bf16(const void* a, const void* b, const float* bias, int32
     b200::GemmTcArgs g{};
     g.a = a; g.b = b; g.m = m; g.n = n; g.k = k; g.bias = bias; g.out = c; g.epi = epi; g.block_n = block_n;
     const char* pv = getenv("B200_EMBED_GEMM_PAIR");
-    g.pair = (pv && std::string(pv) == "1") ? 1 : 0;
+    g.pair = pv ? atoi(pv) : 0;
     if (const char* nv = getenv("B200_EMBED_GEMM_NSPLIT")) g.nsplit = atoi(nv);
     const char* rv = getenv("B200_EMBED_GEMM_RESIDENT_A");
     g.no_resident_a = (rv && std::string(rv) == "1") ? 0 : 1;

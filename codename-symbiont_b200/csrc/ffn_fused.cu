@@ -8,16 +8,21 @@
 // [tokens, I] intermediate costs an HBM write and a read (3.2 GB per layer at c2), and both GEMMs are bound by
 // that traffic, not by the tensor pipe (HBM write bandwidth is 3.9 TB/s; profiles/). Here it never leaves the SM.
 //
-// One persistent CTA per SM owns 128 token rows at a time. The activation tile a[128,H] is loaded once and stays
-// in shared memory. The intermediate is produced and consumed in chunks of 128 columns:
-//     S1  = a . W1[chunk]^T                (tcgen05.mma 128x128xH, fp32 in TMEM columns 0..127)
+// A persistent pair of CTAs (one thread-block cluster on two SMs) owns 256 token rows at a time, 128 per CTA, and
+// runs every GEMM step as one cta_group::2 MMA: each CTA stages its own rows of a and h but only HALF of every W
+// block, so the W stream (the same for all rows, 2.4 MB per 128 rows from L2) is shared by 256 rows and the rings
+// cover twice the lookahead. (A single-CTA version measured 1.6 ms per layer at c2 against 1.4 ms for the two
+// separate GEMMs: it could not keep 192 KB of W per chunk in flight.) The activation tile a[128,H] of each CTA is
+// loaded once and stays in shared memory. The intermediate is produced and consumed in chunks of 128 columns:
+//     S1  = a . W1[chunk]^T                (tcgen05.mma 256x128xH, fp32 in TMEM columns 0..127 of both CTAs)
 //     h   = gelu(S1 + b1[chunk]) -> bf16   (epilogue warps: tcgen05.ld -> registers -> 128B-swizzled K-major smem)
-//     OUT += h . W2[:, chunk]^T            (tcgen05.mma 128xHx128, fp32 in TMEM columns 128..128+H)
+//     OUT += h . W2[:, chunk]^T            (tcgen05.mma 256xHx128, fp32 in TMEM columns 128..128+H)
 // software-pipelined so that the tensor pipe runs S1 of chunk c+1 and OUT of chunk c-1 while the epilogue warps work
 // on chunk c. After the last chunk the epilogue warps add b2 and the residual (hi, lo), LayerNorm the rows and
 // store (hi, lo) exactly as the LayerNorm epilogue of gemm_tc.cu does.
-//   warp 0      TMA producer: a tile, W1 blocks [128 x 64] and W2 blocks [H/NS x 64] through two rings
-//   warp 1      one thread issues all tcgen05.mma
+//   warp 0      TMA producer: own a tile, own halves of the W1 blocks [64 x 64] and W2 blocks [H/NS/2 x 64] through
+//               two rings; all loads of the pair complete on the leader's (rank 0) "full" barriers
+//   warp 1      leader only: one thread issues all tcgen05.mma for the pair; its commits arrive in both CTAs
 //   warp 2      TMEM allocator (512 columns)
 //   warps 4-11  epilogue (warp w: TMEM lane quadrant w % 4, column half (w - 4) / 4)
 #include "kernels.h"
@@ -41,13 +46,14 @@ struct FfnCfg {
     static constexpr int KB1 = H / BK;                // k-blocks of GEMM1 (and of the resident a tile)
     static constexpr int NS = H > 256 ? 2 : 1;        // GEMM2 N split (UMMA N <= 256)
     static constexpr int UN2 = H / NS;                // GEMM2 UMMA N
-    static constexpr int W2_BLK = UN2 * BK * 2;       // one W2 block [UN2 x 64]
-    static constexpr int S1N = 3;                     // W1 ring stages
-    static constexpr int S2N = 2;                     // W2 ring stages
+    static constexpr int W1_BLK = (IC / 2) * BK * 2;  // this CTA's half of a W1 block: [64 x 64]
+    static constexpr int W2_BLK = (UN2 / 2) * BK * 2; // this CTA's half of a W2 block: [UN2/2 x 64]
+    static constexpr int S1N = 6;                     // W1 ring stages
+    static constexpr int S2N = 4;                     // W2 ring stages
     static constexpr int OFF_A = 0;
     static constexpr int OFF_H = KB1 * BLK16;         // h chunk: 2 k-blocks [128 x 64]
     static constexpr int OFF_W1 = OFF_H + 2 * BLK16;
-    static constexpr int OFF_W2 = OFF_W1 + S1N * BLK16;
+    static constexpr int OFF_W2 = OFF_W1 + S1N * W1_BLK;
     static constexpr int OFF_AUX = OFF_W2 + S2N * W2_BLK;
     static constexpr int AUX = 1024 + 2 * BM * 8;     // barriers + tmem slot, LayerNorm partial statistics
     static constexpr int BYTES = OFF_AUX + AUX;
@@ -57,6 +63,7 @@ struct FfnCfg {
     static_assert(H % 128 == 0 && H <= 384, "fused FFN needs the OUT accumulator (H columns) next to S1 (128) in TMEM");
     static_assert(SCRATCH >= FF_EPI_WARPS * 6 * CHUNK_BF16, "final epilogue scratch does not fit");
     static_assert(BYTES <= SMEM_LIMIT, "shared memory budget exceeded");
+    static_assert(W1_BLK % 1024 == 0 && W2_BLK % 1024 == 0 && (UN2 / 2) % 8 == 0, "swizzle atoms must stay 1024-byte aligned");
 };
 
 struct FfnDev {
@@ -75,7 +82,8 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                  const __grid_constant__ CUtensorMap tmap_r_lo, const __grid_constant__ CUtensorMap tmap_c,
                  const __grid_constant__ CUtensorMap tmap_c_lo, const FfnDev p) {
     using C = FfnCfg<H>;
-    constexpr int KB1 = C::KB1, NS = C::NS, UN2 = C::UN2, W2_BLK = C::W2_BLK, S1N = C::S1N, S2N = C::S2N;
+    constexpr int KB1 = C::KB1, NS = C::NS, UN2 = C::UN2, W1_BLK = C::W1_BLK, W2_BLK = C::W2_BLK, S1N = C::S1N, S2N = C::S2N;
+    constexpr uint16_t BOTH = 3;  // multicast mask: both CTAs of the pair
     constexpr int HALF = C::HALF, NCH = C::NCH;
     constexpr int OUT_COL = IC;  // OUT accumulator starts after the 128 S1 columns
 
@@ -86,11 +94,11 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                    smem_w2 = base + C::OFF_W2, aux = base + C::OFF_AUX;
     uint8_t* aux_ptr = smem_raw + C::OFF_AUX;
     const uint32_t bar_a_full = aux, bar_a_empty = aux + 8;
-    const uint32_t bar_w1_full = aux + 16, bar_w1_empty = aux + 48;  // S1N each
-    const uint32_t bar_w2_full = aux + 80, bar_w2_empty = aux + 112; // S2N each
-    const uint32_t bar_s1_full = aux + 144, bar_s1_empty = aux + 152, bar_h_full = aux + 160, bar_h_empty = aux + 168;
-    const uint32_t bar_out_full = aux + 176, bar_out_empty = aux + 184, bar_epi_done = aux + 192;
-    const uint32_t bar_res = aux + 256;   // FF_EPI_WARPS x 2
+    const uint32_t bar_w1_full = aux + 16, bar_w1_empty = aux + 80;    // <= 8 each
+    const uint32_t bar_w2_full = aux + 144, bar_w2_empty = aux + 208;  // <= 8 each
+    const uint32_t bar_s1_full = aux + 272, bar_s1_empty = aux + 280, bar_h_full = aux + 288, bar_h_empty = aux + 296;
+    const uint32_t bar_out_full = aux + 304, bar_out_empty = aux + 312, bar_epi_done = aux + 320;
+    const uint32_t bar_res = aux + 384;   // FF_EPI_WARPS x 2
     const uint32_t tmem_slot = aux + 512;
     volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(aux_ptr + 512);
     float2* ln_part = reinterpret_cast<float2*>(aux_ptr + 1024);
@@ -103,22 +111,34 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     }
     const int num_tiles = (rows + BM - 1) / BM;
     const int NC = p.inter / IC;  // chunks per tile
+    // Pair `pr` owns row tiles 2 pr (leader) and 2 pr + 1 (peer). With an odd tile count the last peer tile is out of
+    // range: its loads are zero-filled and its stores clipped, and it keeps its side of every handshake.
+    const uint32_t crank = cluster_ctarank();
+    const bool leader = crank == 0;
+    const int num_pairs = (num_tiles + 1) / 2;
+    const int pair0 = static_cast<int>(blockIdx.x) / 2, pair_step = static_cast<int>(gridDim.x) / 2;
+    // "full" barriers and the barriers the MMA thread waits on live in the leader CTA
+    const uint32_t l_a_full = map_to_cta(bar_a_full, 0), l_w1_full = map_to_cta(bar_w1_full, 0),
+                   l_w2_full = map_to_cta(bar_w2_full, 0), l_s1_empty = map_to_cta(bar_s1_empty, 0),
+                   l_h_full = map_to_cta(bar_h_full, 0), l_out_empty = map_to_cta(bar_out_empty, 0);
 
     if (threadIdx.x == 0) {
         prefetch_tmap(&tmap_a); prefetch_tmap(&tmap_w1); prefetch_tmap(&tmap_w2);
         mbar_init(bar_a_full, 1); mbar_init(bar_a_empty, 1);
         for (int s = 0; s < S1N; ++s) { mbar_init(bar_w1_full + 8 * s, 1); mbar_init(bar_w1_empty + 8 * s, 1); }
         for (int s = 0; s < S2N; ++s) { mbar_init(bar_w2_full + 8 * s, 1); mbar_init(bar_w2_empty + 8 * s, 1); }
-        mbar_init(bar_s1_full, 1); mbar_init(bar_s1_empty, FF_EPI_THREADS);
-        mbar_init(bar_h_full, FF_EPI_THREADS); mbar_init(bar_h_empty, 1);
-        mbar_init(bar_out_full, 1); mbar_init(bar_out_empty, FF_EPI_THREADS);
+        // one arrive per epilogue warp of both CTAs on the barriers the MMA thread waits on
+        mbar_init(bar_s1_full, 1); mbar_init(bar_s1_empty, 2 * FF_EPI_WARPS);
+        mbar_init(bar_h_full, 2 * FF_EPI_WARPS); mbar_init(bar_h_empty, 1);
+        mbar_init(bar_out_full, 1); mbar_init(bar_out_empty, 2 * FF_EPI_WARPS);
         mbar_init(bar_epi_done, FF_EPI_THREADS);
         for (int s = 0; s < 2 * FF_EPI_WARPS; ++s) mbar_init(bar_res + 8 * s, 1);
         fence_barrier_init();
     }
-    if (warp == 2) tmem_alloc(tmem_slot, 512);
+    if (warp == 2) tmem_alloc_cg2(tmem_slot, 512);
     tc_fence_before_sync();
     __syncthreads();
+    cluster_sync_all();  // the peer's barriers exist before anything arrives on them
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot_ptr;
 
@@ -127,11 +147,12 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     if (warp == 0) {
         if (lane == 0) {
             uint32_t w1_it = 0, w2_it = 0, tile_it = 0;
-            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++tile_it) {
+            for (int pr = pair0; pr < num_pairs; pr += pair_step, ++tile_it) {
+                const int t = 2 * pr + static_cast<int>(crank);
                 // the a tile: free once the previous tile's last GEMM1 has completed
                 mbar_wait(bar_a_empty, (tile_it & 1) ^ 1);
-                mbar_arrive_expect_tx(bar_a_full, KB1 * BLK16);
-                for (int kb = 0; kb < KB1; ++kb) tma_load_2d(smem_a + kb * BLK16, &tmap_a, kb * BK, t * BM, bar_a_full);
+                if (leader) mbar_arrive_expect_tx(bar_a_full, 2 * KB1 * BLK16);
+                for (int kb = 0; kb < KB1; ++kb) tma_load_2d_cg2(smem_a + kb * BLK16, &tmap_a, kb * BK, t * BM, l_a_full);
                 // the rings double as scratch of the previous tile's final epilogue
                 mbar_wait(bar_epi_done, (tile_it & 1) ^ 1);
                 for (int step = 0; step <= NC; ++step) {
@@ -139,8 +160,9 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                         for (int kb = 0; kb < KB1; ++kb, ++w1_it) {
                             const uint32_t s = w1_it % S1N;
                             mbar_wait(bar_w1_empty + 8 * s, ((w1_it / S1N) & 1) ^ 1);
-                            mbar_arrive_expect_tx(bar_w1_full + 8 * s, BLK16);
-                            tma_load_2d(smem_w1 + s * BLK16, &tmap_w1, kb * BK, step * IC, bar_w1_full + 8 * s);
+                            if (leader) mbar_arrive_expect_tx(bar_w1_full + 8 * s, 2 * W1_BLK);
+                            tma_load_2d_cg2(smem_w1 + s * W1_BLK, &tmap_w1, kb * BK, step * IC + crank * (IC / 2),
+                                            l_w1_full + 8 * s);
                         }
                     }
                     if (step >= 1) {
@@ -149,60 +171,75 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                             for (int kb = 0; kb < IC / BK; ++kb, ++w2_it) {
                                 const uint32_t s = w2_it % S2N;
                                 mbar_wait(bar_w2_empty + 8 * s, ((w2_it / S2N) & 1) ^ 1);
-                                mbar_arrive_expect_tx(bar_w2_full + 8 * s, W2_BLK);
-                                tma_load_2d(smem_w2 + s * W2_BLK, &tmap_w2, ic * IC + kb * BK, ns * UN2, bar_w2_full + 8 * s);
+                                if (leader) mbar_arrive_expect_tx(bar_w2_full + 8 * s, 2 * W2_BLK);
+                                tma_load_2d_cg2(smem_w2 + s * W2_BLK, &tmap_w2, ic * IC + kb * BK,
+                                                ns * UN2 + crank * (UN2 / 2), l_w2_full + 8 * s);
                             }
                     }
                 }
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            constexpr uint32_t idesc1 = umma_idesc_bf16(BM, IC);
-            constexpr uint32_t idesc2 = umma_idesc_bf16(BM, UN2);
+        // The whole warp walks the schedule (waits included) so that control flow stays uniform; one elected lane issues.
+        if (leader) {
+            constexpr uint32_t idesc1 = umma_idesc_bf16(2 * BM, IC);
+            constexpr uint32_t idesc2 = umma_idesc_bf16(2 * BM, UN2);
             uint32_t w1_it = 0, w2_it = 0, tile_it = 0, g1_it = 0, g2_it = 0;  // g*_it: chunks issued so far
-            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++tile_it) {
+            for (int pr = pair0; pr < num_pairs; pr += pair_step, ++tile_it) {
                 mbar_wait(bar_a_full, tile_it & 1);
                 for (int step = 0; step <= NC; ++step) {
                     if (step < NC) {  // G1(step): S1 = a . W1[chunk]^T
-                        mbar_wait(bar_s1_empty, (g1_it & 1) ^ 1);  // the epilogue has drained the previous S1
+                        mbar_wait_cluster(bar_s1_empty, (g1_it & 1) ^ 1);  // both epilogues have drained the previous S1
                         tc_fence_after_sync();
+#pragma unroll 1
                         for (int kb = 0; kb < KB1; ++kb, ++w1_it) {
                             const uint32_t s = w1_it % S1N;
                             mbar_wait(bar_w1_full + 8 * s, (w1_it / S1N) & 1);
                             tc_fence_after_sync();
-                            const uint64_t da = umma_desc_sw128(smem_a + kb * BLK16);
-                            const uint64_t db = umma_desc_sw128(smem_w1 + s * BLK16);
+                            if (elect_one()) {
+                                const uint64_t da = umma_desc_sw128(smem_a + kb * BLK16);
+                                const uint64_t db = umma_desc_sw128(smem_w1 + s * W1_BLK);
 #pragma unroll
-                            for (int k = 0; k < BK / 16; ++k)
-                                umma_bf16(tmem_base, da + 2 * k, db + 2 * k, idesc1, (kb > 0 || k > 0) ? 1u : 0u);
-                            umma_commit(bar_w1_empty + 8 * s);
+                                for (int k = 0; k < BK / 16; ++k)
+                                    umma_bf16_cg2(tmem_base, da + 2 * k, db + 2 * k, idesc1, (kb > 0 || k > 0) ? 1u : 0u);
+                                umma_commit_cg2(bar_w1_empty + 8 * s, BOTH);
+                                if (kb == KB1 - 1) {
+                                    umma_commit_cg2(bar_s1_full, BOTH);
+                                    // the a tiles have been read for the last time
+                                    if (step == NC - 1) umma_commit_cg2(bar_a_empty, BOTH);
+                                }
+                            }
+                            __syncwarp();
                         }
-                        umma_commit(bar_s1_full);
                         ++g1_it;
-                        if (step == NC - 1) umma_commit(bar_a_empty);  // the a tile has been read for the last time
                     }
                     if (step >= 1) {  // G2(step - 1): OUT += h . W2[:, chunk]^T
                         const int ic = step - 1;
-                        mbar_wait(bar_h_full, g2_it & 1);  // h(ic) is in shared memory
-                        if (ic == 0) mbar_wait(bar_out_empty, (tile_it & 1) ^ 1);  // previous tile's OUT has been read
+                        mbar_wait_cluster(bar_h_full, g2_it & 1);  // h(ic) is in both CTAs' shared memory
+                        if (ic == 0) mbar_wait_cluster(bar_out_empty, (tile_it & 1) ^ 1);  // previous tiles' OUT has been read
                         tc_fence_after_sync();
-                        for (int ns = 0; ns < NS; ++ns)
-                            for (int kb = 0; kb < IC / BK; ++kb, ++w2_it) {
-                                const uint32_t s = w2_it % S2N;
-                                mbar_wait(bar_w2_full + 8 * s, (w2_it / S2N) & 1);
-                                tc_fence_after_sync();
+#pragma unroll 1
+                        for (int blk = 0; blk < NS * (IC / BK); ++blk, ++w2_it) {
+                            const int ns = blk / (IC / BK), kb = blk % (IC / BK);
+                            const uint32_t s = w2_it % S2N;
+                            mbar_wait(bar_w2_full + 8 * s, (w2_it / S2N) & 1);
+                            tc_fence_after_sync();
+                            if (elect_one()) {
                                 const uint64_t da = umma_desc_sw128(smem_h + kb * BLK16);
                                 const uint64_t db = umma_desc_sw128(smem_w2 + s * W2_BLK);
 #pragma unroll
                                 for (int k = 0; k < BK / 16; ++k)
-                                    umma_bf16(tmem_base + OUT_COL + ns * UN2, da + 2 * k, db + 2 * k, idesc2,
-                                              (ic > 0 || kb > 0 || k > 0) ? 1u : 0u);
-                                umma_commit(bar_w2_empty + 8 * s);
+                                    umma_bf16_cg2(tmem_base + OUT_COL + ns * UN2, da + 2 * k, db + 2 * k, idesc2,
+                                                  (ic > 0 || kb > 0 || k > 0) ? 1u : 0u);
+                                umma_commit_cg2(bar_w2_empty + 8 * s, BOTH);
+                                if (blk == NS * (IC / BK) - 1) {
+                                    umma_commit_cg2(bar_h_empty, BOTH);  // h(ic) consumed
+                                    if (ic == NC - 1) umma_commit_cg2(bar_out_full, BOTH);
+                                }
                             }
-                        umma_commit(bar_h_empty);  // h(ic) consumed
+                            __syncwarp();
+                        }
                         ++g2_it;
-                        if (ic == NC - 1) umma_commit(bar_out_full);
                     }
                 }
             }
@@ -245,7 +282,8 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             ++ld_issued;
         };
 
-        for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++tile_it) {
+        for (int pr = pair0; pr < num_pairs; pr += pair_step, ++tile_it) {
+            const int t = 2 * pr + static_cast<int>(crank);
             // ---- per chunk: h = gelu(S1 + b1) as the bf16 A operand of the second GEMM ----
             for (int ic = 0; ic < NC; ++ic, ++chunk_it) {
                 mbar_wait(bar_s1_full, chunk_it & 1);
@@ -255,18 +293,15 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 tmem_ld_32x32(t_lane + half * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
                 tmem_ld_wait();
                 tc_fence_before_sync();
-                mbar_arrive(bar_s1_empty);  // S1 is in registers: the next chunk's GEMM1 may overwrite it
+                __syncwarp();
+                if (lane == 0) mbar_arrive_cluster(l_s1_empty);  // S1 is in registers: the next chunk's GEMM1 may overwrite it
                 const float4* b4 = reinterpret_cast<const float4*>(p.b1 + ic * IC + half * 64);
                 uint32_t hp[32];
 #pragma unroll
                 for (int q = 0; q < 16; ++q) {
                     const float4 b = __ldg(b4 + q);
-                    const float g0 = gelu_erf_fast(__uint_as_float(v[q * 4 + 0]) + b.x);
-                    const float g1 = gelu_erf_fast(__uint_as_float(v[q * 4 + 1]) + b.y);
-                    const float g2 = gelu_erf_fast(__uint_as_float(v[q * 4 + 2]) + b.z);
-                    const float g3 = gelu_erf_fast(__uint_as_float(v[q * 4 + 3]) + b.w);
-                    hp[q * 2 + 0] = pack_bf16x2(g0, g1);
-                    hp[q * 2 + 1] = pack_bf16x2(g2, g3);
+                    hp[q * 2 + 0] = epi_pair_bf16<EPI_GELU_ERF>(v[q * 4 + 0], v[q * 4 + 1], b.x, b.y);
+                    hp[q * 2 + 1] = epi_pair_bf16<EPI_GELU_ERF>(v[q * 4 + 2], v[q * 4 + 3], b.z, b.w);
                 }
                 // the h buffer is free once GEMM2 of the previous chunk has completed
                 mbar_wait(bar_h_empty, (chunk_it & 1) ^ 1);
@@ -280,7 +315,8 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                                  : "memory");
                 }
                 fence_proxy_async_smem();
-                mbar_arrive(bar_h_full);
+                __syncwarp();
+                if (lane == 0) mbar_arrive_cluster(l_h_full);
             }
             // ---- final: x' = LayerNorm(OUT + b2 + a) -> (hi, lo) ----
             mbar_wait(bar_out_full, tile_it & 1);  // every MMA of this tile has completed: h and the rings are idle
@@ -348,7 +384,8 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 tmem_ld_wait();
                 if (c == NCH - 1) {  // OUT fully read: the next tile's GEMM2 may overwrite it
                     tc_fence_before_sync();
-                    mbar_arrive(bar_out_empty);
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_cluster(l_out_empty);
                 }
                 const int col0 = half * HALF + c * CHUNK;
                 const float4* g4 = reinterpret_cast<const float4*>(p.gamma + col0);
@@ -375,9 +412,10 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 
     tc_fence_before_sync();
     __syncthreads();
+    cluster_sync_all();  // neither CTA leaves while the pair's MMAs or barrier arrivals may still touch it
     if (warp == 2) {
         tc_fence_after_sync();
-        tmem_dealloc(tmem_base, 512);
+        tmem_dealloc_cg2(tmem_base, 512);
     }
 }
 
@@ -386,8 +424,8 @@ cudaError_t launch_ffn(const FfnFusedArgs& a, cudaStream_t stream, int num_sms) 
     using C = FfnCfg<H>;
     alignas(64) CUtensorMap ta, tw1, tw2, tr, trl, tc, tcl;
     if (!make_tmap(&ta, a.a, a.m, H, BK, BM, false, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
-    if (!make_tmap(&tw1, a.w1, a.inter, H, BK, IC, false, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
-    if (!make_tmap(&tw2, a.w2, H, a.inter, BK, C::UN2, false, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
+    if (!make_tmap(&tw1, a.w1, a.inter, H, BK, IC / 2, false, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
+    if (!make_tmap(&tw2, a.w2, H, a.inter, BK, C::UN2 / 2, false, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
     if (!make_tmap(&tr, a.a, a.m, H, CHUNK, 32, false, CU_TENSOR_MAP_SWIZZLE_64B)) return cudaErrorInvalidValue;
     trl = tr;
     if (a.a_lo && !make_tmap(&trl, a.a_lo, a.m, H, CHUNK, 32, false, CU_TENSOR_MAP_SWIZZLE_64B)) return cudaErrorInvalidValue;
@@ -404,11 +442,29 @@ cudaError_t launch_ffn(const FfnFusedArgs& a, cudaStream_t stream, int num_sms) 
     FfnDev p;
     p.m = a.m; p.d_rows = a.d_rows; p.inter = a.inter; p.b1 = a.b1; p.b2 = a.b2; p.gamma = a.gamma; p.beta = a.beta;
     p.eps = a.eps; p.has_lo = (a.a_lo != nullptr && a.out_lo != nullptr) ? 1 : 0;
-    const int tiles = (a.m + BM - 1) / BM;
-    const int grid = tiles < num_sms ? tiles : num_sms;
+    const int pairs = ((a.m + BM - 1) / BM + 1) / 2;
+    cudaLaunchConfig_t cfg{};
+    cfg.blockDim = dim3(FF_THREADS);
+    cfg.dynamicSmemBytes = C::BYTES;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    static int max_pairs = 0;  // CTA pairs the device holds at once
+    if (max_pairs == 0) {
+        max_pairs = num_sms / 2;
+        cfg.gridDim = dim3(2 * (num_sms / 2));
+        int n = 0;
+        if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) == cudaSuccess && n > 0 && n < max_pairs) max_pairs = n;
+    }
+    const int grid = 2 * (pairs < max_pairs ? pairs : max_pairs);
     if (grid <= 0) return cudaSuccess;
-    kern<<<grid, FF_THREADS, C::BYTES, stream>>>(ta, tw1, tw2, tr, trl, tc, tcl, p);
-    return cudaGetLastError();
+    cfg.gridDim = dim3(grid);
+    return cudaLaunchKernelEx(&cfg, kern, ta, tw1, tw2, tr, trl, tc, tcl, p);
 }
 
 }  // namespace

@@ -71,30 +71,20 @@ __host__ __device__ constexpr int aux_bytes(int epi, int block_n) {
 // kslots == 0: A and W stream through the same ring of stages. kslots > 0 ("resident A"): the whole 128 x K
 // activation tile sits in `kslots` fixed 16 KB slots while the CTA walks every column tile of that row block, and
 // only W streams through the ring.
-__host__ __device__ constexpr int num_stages(int block_n, int epi, bool out_f32, int kslots, int ring, bool wide = false) {
+// pair == 2 (one MMA over a CTA pair): each CTA stages only its half of the W tile's rows
+__host__ __device__ constexpr int num_stages(int block_n, int epi, bool out_f32, int kslots, int ring, bool wide = false,
+                                             int pair = 0) {
     int s = (SMEM_LIMIT - aux_bytes(epi, block_n) - EPI_WARPS * epi_warp_bytes(epi, out_f32, ring, wide) - kslots * A_STAGE_BYTES) /
-            ((kslots ? 0 : A_STAGE_BYTES) + b_stage_bytes(block_n));
+            ((kslots ? 0 : A_STAGE_BYTES) + b_stage_bytes(pair == 2 ? block_n / 2 : block_n));
     return s > 8 ? 8 : s;
 }
-__host__ __device__ constexpr int smem_bytes(int block_n, int epi, bool out_f32, int kslots, int ring, bool wide = false) {
-    return num_stages(block_n, epi, out_f32, kslots, ring, wide) * ((kslots ? 0 : A_STAGE_BYTES) + b_stage_bytes(block_n)) +
+__host__ __device__ constexpr int smem_bytes(int block_n, int epi, bool out_f32, int kslots, int ring, bool wide = false,
+                                             int pair = 0) {
+    return num_stages(block_n, epi, out_f32, kslots, ring, wide, pair) *
+               ((kslots ? 0 : A_STAGE_BYTES) + b_stage_bytes(pair == 2 ? block_n / 2 : block_n)) +
            kslots * A_STAGE_BYTES + EPI_WARPS * epi_warp_bytes(epi, out_f32, ring, wide) + aux_bytes(epi, block_n);
 }
 
-// ---- thread-block cluster helpers (distributed shared memory) ----
-__device__ __forceinline__ uint32_t cluster_ctarank() {
-    uint32_t r;
-    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-    return r;
-}
-__device__ __forceinline__ void cluster_sync_all() {
-    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-__device__ __forceinline__ uint32_t map_to_cta(uint32_t local_smem, uint32_t rank) {
-    uint32_t r;
-    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_smem), "r"(rank));
-    return r;
-}
 // One 8-byte store into a peer CTA's shared memory that also counts 8 bytes on the peer's mbarrier
 // (complete_tx): the data is visible to whoever observes that barrier phase complete. No fence, no remote arrive.
 __device__ __forceinline__ void st_async_cluster_b64(uint32_t remote_addr, float a, float b, uint32_t remote_bar) {
@@ -110,6 +100,7 @@ struct GemmDev {
     const int* d_rows;  // optional device-side row count (<= m)
     int n, k;
     const float* bias;
+    __nv_bfloat16* out_bf16;  // direct-store epilogue only
     const float* gamma;
     const float* beta;
     float eps;
@@ -127,9 +118,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     constexpr int NSPLIT = NSP ? NSP : (BLOCK_N > 256 ? 2 : 1);  // independent accumulator column ranges per k-step
     constexpr int UMMA_N = BLOCK_N / NSPLIT;
     constexpr int ACC_STAGES = (2 * BLOCK_N <= 512) ? 2 : 1;
-    constexpr int B_STAGE_BYTES = b_stage_bytes(BLOCK_N);
-    constexpr bool WIDE = WST != 0;  // stage two chunks side by side and store 128-byte row segments
-    constexpr int STAGES = num_stages(BLOCK_N, EPI, OUT_F32, KSLOTS, RING, WIDE);
+    constexpr bool CG2 = PAIR == 2;  // one cta_group::2 MMA per k-step over a pair of CTAs (256 x BLOCK_N per pair)
+    constexpr int B_STAGE_BYTES = b_stage_bytes(CG2 ? BLOCK_N / 2 : BLOCK_N);
+    constexpr bool WIDE = WST == 1;    // stage two chunks side by side and store 128-byte row segments
+    constexpr bool DIRECT = WST == 2;  // no staging: every lane stores its 64 bytes of the chunk straight from registers
+    constexpr int STAGES = num_stages(BLOCK_N, EPI, OUT_F32, KSLOTS, RING, WIDE, PAIR);
+    static_assert(!CG2 || (EPI != EPI_RES_LN && !OUT_F32 && NSPLIT == 1 && KSLOTS == 0), "CTA-pair MMA: plain bf16 epilogues");
     constexpr bool RES_A = KSLOTS > 0;
     static_assert(!RES_A || (CL == 1 && PAIR == 0 && KSLOTS <= 8), "resident A is for the plain single-CTA GEMMs");
     constexpr int HALF_N = BLOCK_N / 2;  // columns per epilogue warp group
@@ -214,11 +208,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         prefetch_tmap(&tmap_c);
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(bar_full + 8 * s, 1);
-            mbar_init(bar_empty + 8 * s, CSIZE);  // one multicast commit from every CTA that shares the stage
+            mbar_init(bar_empty + 8 * s, CG2 ? 1 : CSIZE);  // one multicast commit from every CTA that issues MMAs on the stage
         }
         for (int s = 0; s < 2; ++s) {
             mbar_init(bar_tfull + 8 * s, 1);
-            mbar_init(bar_tempty + 8 * s, EPI_THREADS);
+            mbar_init(bar_tempty + 8 * s, CG2 ? 2 * EPI_WARPS : EPI_THREADS);  // pair: one arrive per epilogue warp of both CTAs
         }
         for (int s = 0; s < RING * EPI_WARPS; ++s) mbar_init(bar_res + 8 * s, 1);
         for (int s = 0; s < 2; ++s) mbar_init(bar_ln + 8 * s, 1);
@@ -228,7 +222,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         }
         fence_barrier_init();
     }
-    if (warp == 2) tmem_alloc(tmem_slot, 512);
+    if (warp == 2) {
+        if constexpr (CG2) tmem_alloc_cg2(tmem_slot, 512);
+        else tmem_alloc(tmem_slot, 512);
+    }
     tc_fence_before_sync();
     __syncthreads();
     if constexpr (CSIZE > 1) cluster_sync_all();  // peers' barriers exist before anyone arrives on them remotely
@@ -259,6 +256,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                         }
                     }
                     mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+                    if constexpr (CG2) {  // both CTAs' boxes count on the leader's barrier
+                        if (crank == 0) mbar_arrive_expect_tx(bar_full + 8 * stage, 2 * (A_STAGE_BYTES + B_STAGE_BYTES));
+                        const uint32_t fb = map_to_cta(bar_full + 8 * stage, 0);
+                        tma_load_2d_cg2(smem_a + stage * A_STAGE_BYTES, &tmap_a, kb * BLOCK_K, m_tile * BLOCK_M, fb);
+                        tma_load_2d_cg2(smem_b + stage * B_STAGE_BYTES, &tmap_b, kb * BLOCK_K,
+                                        n_tile * BLOCK_N + crank * B_SLICE_ROWS, fb);
+                        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                        continue;
+                    }
                     mbar_arrive_expect_tx(bar_full + 8 * stage, (RES_A ? 0 : A_STAGE_BYTES) + B_STAGE_BYTES);
                     if constexpr (RES_A) {
                     } else if constexpr (CL > 1) {  // my slice of the A tile, delivered to every CTA of the cluster
@@ -290,8 +296,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         }
     } else if (warp == 1) {
         // ------------------------------ MMA issuer --------------------------------
-        if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_bf16(BLOCK_M, UMMA_N);
+        // The whole warp walks the loop (waits included) so that control flow stays uniform; one elected lane issues.
+        if (!CG2 || crank == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(CG2 ? 2 * BLOCK_M : BLOCK_M, UMMA_N);
             int stage = 0;
             uint32_t phase = 0;
             for (int it = 0; it < my_tiles; ++it) {
@@ -307,27 +314,37 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     }
                     mbar_wait(bar_full + 8 * stage, phase);
                     tc_fence_after_sync();
-                    const uint64_t desc_a = umma_desc_sw128(smem_a + (RES_A ? kb : stage) * A_STAGE_BYTES);
-                    const uint64_t desc_b = umma_desc_sw128(smem_b + stage * B_STAGE_BYTES);
+                    if (elect_one()) {
+                        const uint64_t desc_a = umma_desc_sw128(smem_a + (RES_A ? kb : stage) * A_STAGE_BYTES);
+                        const uint64_t desc_b = umma_desc_sw128(smem_b + stage * B_STAGE_BYTES);
 #pragma unroll
-                    for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+                        for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
 #pragma unroll
-                        for (int s = 0; s < NSPLIT; ++s) {
-                            // +2 per 16-element K step (32 B >> 4); second N split starts UMMA_N rows later
-                            umma_bf16(tmem_d + s * UMMA_N, desc_a + 2 * k,
-                                      desc_b + 2 * k + ((s * UMMA_N * BLOCK_K * 2) >> 4), idesc,
-                                      (kb > 0 || k > 0) ? 1u : 0u);
+                            for (int s = 0; s < NSPLIT; ++s) {
+                                // +2 per 16-element K step (32 B >> 4); second N split starts UMMA_N rows later
+                                if constexpr (CG2)
+                                    umma_bf16_cg2(tmem_d, desc_a + 2 * k, desc_b + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+                                else
+                                    umma_bf16(tmem_d + s * UMMA_N, desc_a + 2 * k,
+                                              desc_b + 2 * k + ((s * UMMA_N * BLOCK_K * 2) >> 4), idesc,
+                                              (kb > 0 || k > 0) ? 1u : 0u);
+                            }
+                        }
+                        // frees the smem stage (in every CTA that shares it) when these MMAs finish
+                        if constexpr (CG2) umma_commit_cg2(bar_empty + 8 * stage, CMASK);
+                        else if constexpr (CSIZE > 1) umma_commit_multicast(bar_empty + 8 * stage, CMASK);
+                        else umma_commit(bar_empty + 8 * stage);
+                        if constexpr (RES_A) {  // last column tile of this row block: slot kb may take the next block's A
+                            if (n_tile == num_n_tiles - 1) umma_commit(bar_a_empty + 8 * kb);
+                        }
+                        if (kb == num_kb - 1) {
+                            if constexpr (CG2) umma_commit_cg2(bar_tfull + 8 * acc, CMASK);  // accumulator halves complete in both CTAs
+                            else umma_commit(bar_tfull + 8 * acc);                             // accumulator complete
                         }
                     }
-                    // frees the smem stage (in every CTA that shares it) when these MMAs finish
-                    if constexpr (CSIZE > 1) umma_commit_multicast(bar_empty + 8 * stage, CMASK);
-                    else umma_commit(bar_empty + 8 * stage);
-                    if constexpr (RES_A) {  // last column tile of this row block: slot kb may take the next block's A
-                        if (n_tile == num_n_tiles - 1) umma_commit(bar_a_empty + 8 * kb);
-                    }
+                    __syncwarp();
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
-                umma_commit(bar_tfull + 8 * acc);  // accumulator complete
             }
         }
     } else if (warp >= EPI_WARP0) {
@@ -393,7 +410,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             if (p.dbg & 8) {  // mainloop only
                 mbar_wait(bar_tfull + 8 * acc, acc_phase);
                 tc_fence_before_sync();
-                mbar_arrive(bar_tempty + 8 * acc);
+                if constexpr (CG2) {
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_cluster(map_to_cta(bar_tempty + 8 * acc, 0));
+                } else {
+                    mbar_arrive(bar_tempty + 8 * acc);
+                }
                 continue;
             }
             if constexpr (EPI != EPI_RES_LN && !OUT_F32) {
@@ -418,7 +440,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                         tmem_ld_32x32(taddr + (c + 1) * CHUNK, v[(c + 1) & 1]);
                     } else {  // accumulator drained: the MMA warp may start the tile after next
                         tc_fence_before_sync();
-                        mbar_arrive(bar_tempty + 8 * acc);
+                        if constexpr (CG2) {
+                            __syncwarp();
+                            if (lane == 0) mbar_arrive_cluster(map_to_cta(bar_tempty + 8 * acc, 0));
+                        } else {
+                            mbar_arrive(bar_tempty + 8 * acc);
+                        }
                     }
                     const int col0 = col_base + c * CHUNK;
                     uint32_t w[16];
@@ -431,7 +458,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                                                           __uint_as_float(bq.w));
                     }
                     if (p.dbg & 1) continue;
-                    if constexpr (WIDE) {
+                    if constexpr (DIRECT) {
+                        const int row = row0 + lane;
+                        if (row < p.m) {
+                            __nv_bfloat16* dst = p.out_bf16 + static_cast<size_t>(row) * p.n + col0;
+                            stg_v8(dst, w);
+                            stg_v8(dst + 16, w + 8);
+                        }
+                    } else if constexpr (WIDE) {
                         const uint32_t buf = out_buf + ((st_it >> 1) & 1) * CHUNK_F32;
                         if ((c & 1) == 0) {
                             if (lane == 0) tma_store_wait_read<1>();
@@ -444,8 +478,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                         if (c & 1) {
                             fence_proxy_async_smem();
                             __syncwarp();
-                            if (lane == 0) {
-                                tma_store_2d(&tmap_c, buf, col0 - CHUNK, row0);
+                            if (lane == 0 && !(p.dbg & 256)) {
+                                tma_store_2d(&tmap_c, buf, col0 - CHUNK, (p.dbg & 512) ? (row0 & 4095) : row0);
                                 tma_store_commit();
                             }
                         }
@@ -459,8 +493,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                             sts_v4(row + ((q ^ ((lane >> 1) & 3)) << 4), w[q * 4], w[q * 4 + 1], w[q * 4 + 2], w[q * 4 + 3]);
                         fence_proxy_async_smem();
                         __syncwarp();
-                        if (lane == 0) {
-                            tma_store_2d(&tmap_c, buf, col0, row0);
+                        if (lane == 0 && !(p.dbg & 256)) {
+                            tma_store_2d(&tmap_c, buf, col0, (p.dbg & 512) ? (row0 & 4095) : row0);
                             tma_store_commit();
                         }
                     }
@@ -631,7 +665,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     if constexpr (CSIZE > 1) cluster_sync_all();  // no CTA leaves while a peer may still write into its shared memory
     if (warp == 2) {
         tc_fence_after_sync();
-        tmem_dealloc(tmem_base, 512);
+        if constexpr (CG2) tmem_dealloc_cg2(tmem_base, 512);
+        else tmem_dealloc(tmem_base, 512);
     }
 }
 
@@ -648,8 +683,8 @@ cudaError_t launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms) {
         return cudaErrorInvalidValue;
     if (!make_tmap(&tb, a.b, a.n, a.k, BLOCK_K, BLOCK_N / NSPLIT / (PAIR ? 2 : 1), false, CU_TENSOR_MAP_SWIZZLE_128B))
         return cudaErrorInvalidValue;
-    const CUtensorMapSwizzle csw = (OUT_F32 || WST) ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
-    if (!make_tmap(&tc, a.out, a.m, a.n, WST ? 2 * CHUNK : CHUNK, 32, OUT_F32, csw)) return cudaErrorInvalidValue;
+    const CUtensorMapSwizzle csw = (OUT_F32 || WST == 1) ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+    if (!make_tmap(&tc, a.out, a.m, a.n, WST == 1 ? 2 * CHUNK : CHUNK, 32, OUT_F32, csw)) return cudaErrorInvalidValue;
     tcl = tc; tr = tc; trl = tc;
     if (a.out_lo && !make_tmap(&tcl, a.out_lo, a.m, a.n, CHUNK, 32, false, csw)) return cudaErrorInvalidValue;
     if (EPI == EPI_RES_LN) {
@@ -660,8 +695,8 @@ cudaError_t launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms) {
             return cudaErrorInvalidValue;
     }
     auto kern = gemm_tc_kernel<BLOCK_N, EPI, OutT, CL, PAIR, KSLOTS, RING, NSP, WST>;
-    constexpr int smem = smem_bytes(BLOCK_N, EPI, OUT_F32, KSLOTS, RING, WST != 0);
-    static_assert(num_stages(BLOCK_N, EPI, OUT_F32, KSLOTS, RING, WST != 0) >= 2, "not enough shared memory for a pipeline");
+    constexpr int smem = smem_bytes(BLOCK_N, EPI, OUT_F32, KSLOTS, RING, WST == 1, PAIR);
+    static_assert(num_stages(BLOCK_N, EPI, OUT_F32, KSLOTS, RING, WST == 1, PAIR) >= 2, "not enough shared memory for a pipeline");
     static_assert(smem <= SMEM_LIMIT, "shared memory budget exceeded");
     static bool attr_set = false;  // per instantiation; benign race (idempotent)
     if (!attr_set) {
@@ -671,6 +706,7 @@ cudaError_t launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms) {
     }
     GemmDev p;
     p.m = a.m; p.d_rows = a.d_rows; p.n = a.n; p.k = a.k; p.bias = a.bias;
+    p.out_bf16 = static_cast<__nv_bfloat16*>(a.out);
     p.gamma = a.gamma; p.beta = a.beta; p.eps = a.eps;
     p.has_res_lo = a.residual_lo != nullptr; p.has_out_lo = a.out_lo != nullptr;
     p.dbg = 0;
@@ -741,11 +777,29 @@ cudaError_t gemm_tc_launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms
         if (a.block_n == 256 && cl == 4) return launch<256, EPI_RES_LN, __nv_bfloat16, 4>(a, stream, num_sms);
         return cudaErrorInvalidValue;
     }
+    if (a.pair == 2 && !a.out_f32) {  // one MMA over a CTA pair; each CTA stages half of the W tile
+#define B200_CG2(BN, EP)                                                                                     \
+    if (a.block_n == BN && a.epi == EP)                                                                      \
+        return a.wide_store == 1 ? launch<BN, EP, __nv_bfloat16, 1, 2, 0, 2, 0, ((BN / 64) % 2 == 0 ? 1 : 0)>(a, stream, num_sms) \
+                            : launch<BN, EP, __nv_bfloat16, 1, 2, 0, 2, 0, 0>(a, stream, num_sms);
+        B200_CG2(256, EPI_BIAS)
+        B200_CG2(192, EPI_BIAS)
+        B200_CG2(128, EPI_BIAS)
+        B200_CG2(256, EPI_GELU_ERF)
+        B200_CG2(128, EPI_GELU_ERF)
+#undef B200_CG2
+    }
     const bool nsplit2 = a.block_n == 256 && a.nsplit == 2;
-    if (a.wide_store && !a.out_f32 && !a.pair && a.epi != EPI_RES_LN) {  // 128-byte row segments per TMA store
+    if (a.wide_store == 1 && !a.out_f32 && !a.pair && a.epi != EPI_RES_LN) {  // 128-byte row segments per TMA store
         if (a.block_n == 256 && a.epi == EPI_BIAS) return launch<256, EPI_BIAS, __nv_bfloat16, 1, 0, 0, 2, 0, 1>(a, stream, num_sms);
         if (a.block_n == 256 && a.epi == EPI_GELU_ERF) return launch<256, EPI_GELU_ERF, __nv_bfloat16, 1, 0, 0, 2, 0, 1>(a, stream, num_sms);
         if (a.block_n == 128 && a.epi == EPI_BIAS) return launch<128, EPI_BIAS, __nv_bfloat16, 1, 0, 0, 2, 0, 1>(a, stream, num_sms);
+    }
+    if (a.wide_store == 2 && !a.out_f32 && !a.pair && a.epi != EPI_RES_LN) {  // direct stores from registers
+        if (a.block_n == 256 && a.epi == EPI_BIAS) return launch<256, EPI_BIAS, __nv_bfloat16, 1, 0, 0, 2, 0, 2>(a, stream, num_sms);
+        if (a.block_n == 256 && a.epi == EPI_GELU_ERF) return launch<256, EPI_GELU_ERF, __nv_bfloat16, 1, 0, 0, 2, 0, 2>(a, stream, num_sms);
+        if (a.block_n == 192 && a.epi == EPI_BIAS) return launch<192, EPI_BIAS, __nv_bfloat16, 1, 0, 0, 2, 0, 2>(a, stream, num_sms);
+        if (a.block_n == 128 && a.epi == EPI_BIAS) return launch<128, EPI_BIAS, __nv_bfloat16, 1, 0, 0, 2, 0, 2>(a, stream, num_sms);
     }
     // K <= 384 with several column tiles per row block: keep the activation tile resident (6 x 64 columns)
     const bool res_a = !a.pair && !a.no_resident_a && a.k <= 6 * BLOCK_K && a.n / a.block_n >= 2;
@@ -754,7 +808,7 @@ cudaError_t gemm_tc_launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms
     // (FFN1 0.78 vs 0.68 ms), so it is off by default.
 #define B200_CASE(BN, EP, T)                                                                   \
     if (a.block_n == BN && a.epi == EP && a.out_f32 == (sizeof(T) == 4))                       \
-        return a.pair    ? launch<BN, EP, T, 1, 1, 0, 2, 0>(a, stream, num_sms)                \
+        return a.pair == 1 ? launch<BN, EP, T, 1, 1, 0, 2, 0>(a, stream, num_sms)                \
                : res_a   ? launch<BN, EP, T, 1, 0, 6, 2, 0>(a, stream, num_sms)                \
                : nsplit2 ? launch<BN, EP, T, 1, 0, 0, 2, (BN == 256 ? 2 : 0)>(a, stream, num_sms) \
                          : launch<BN, EP, T, 1, 0, 0, 2, 0>(a, stream, num_sms);
