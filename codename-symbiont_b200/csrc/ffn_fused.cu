@@ -48,8 +48,14 @@ struct FfnCfg {
     static constexpr int UN2 = H / NS;                // GEMM2 UMMA N
     static constexpr int W1_BLK = (IC / 2) * BK * 2;  // this CTA's half of a W1 block: [64 x 64]
     static constexpr int W2_BLK = (UN2 / 2) * BK * 2; // this CTA's half of a W2 block: [UN2/2 x 64]
-    static constexpr int S1N = 6;                     // W1 ring stages
-    static constexpr int S2N = 4;                     // W2 ring stages
+    // Both rings hold a whole number of GEMM steps, so a block's ring slot is a compile-time function of its place
+    // in the step (the MMA-issuing warp has no index arithmetic to do: its issue rate bounds the kernel otherwise).
+    static constexpr int R1 = H == 384 ? 1 : 2;       // GEMM1 steps in the W1 ring
+    static constexpr int R2 = H == 384 ? 1 : 2;       // GEMM2 steps in the W2 ring
+    static constexpr int NB2 = NS * (IC / BK);        // W2 blocks per GEMM2 step
+    static constexpr int S1N = R1 * KB1;              // W1 ring stages
+    static constexpr int S2N = R2 * NB2;              // W2 ring stages
+    static_assert(S1N <= 8 && S2N <= 8, "barrier slots");
     static constexpr int OFF_A = 0;
     static constexpr int OFF_H = KB1 * BLK16;         // h chunk: 2 k-blocks [128 x 64]
     static constexpr int OFF_W1 = OFF_H + 2 * BLK16;
@@ -83,6 +89,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                  const __grid_constant__ CUtensorMap tmap_c_lo, const FfnDev p) {
     using C = FfnCfg<H>;
     constexpr int KB1 = C::KB1, NS = C::NS, UN2 = C::UN2, W1_BLK = C::W1_BLK, W2_BLK = C::W2_BLK, S1N = C::S1N, S2N = C::S2N;
+    constexpr int R1 = C::R1, R2 = C::R2, NB2 = C::NB2;
     constexpr uint16_t BOTH = 3;  // multicast mask: both CTAs of the pair
     constexpr int HALF = C::HALF, NCH = C::NCH;
     constexpr int OUT_COL = IC;  // OUT accumulator starts after the 128 S1 columns
@@ -145,37 +152,50 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     // Both the producer and the MMA thread walk the tensor-pipe schedule of a tile in the same order:
     //   G1(0), [G1(1), G2(0)], [G1(2), G2(1)], ..., [G1(NC-1), G2(NC-2)], G2(NC-1)
     if (warp == 0) {
-        if (lane == 0) {
-            uint32_t w1_it = 0, w2_it = 0, tile_it = 0;
-            for (int pr = pair0; pr < num_pairs; pr += pair_step, ++tile_it) {
-                const int t = 2 * pr + static_cast<int>(crank);
-                // the a tile: free once the previous tile's last GEMM1 has completed
-                mbar_wait(bar_a_empty, (tile_it & 1) ^ 1);
+        // The whole warp walks the schedule so that control flow stays uniform; one elected lane issues the copies.
+        uint32_t g1_it = 0, g2_it = 0, tile_it = 0;
+        for (int pr = pair0; pr < num_pairs; pr += pair_step, ++tile_it) {
+            const int t = 2 * pr + static_cast<int>(crank);
+            // the a tile: free once the previous tile's last GEMM1 has completed
+            mbar_wait(bar_a_empty, (tile_it & 1) ^ 1);
+            if (elect_one()) {
                 if (leader) mbar_arrive_expect_tx(bar_a_full, 2 * KB1 * BLK16);
+#pragma unroll
                 for (int kb = 0; kb < KB1; ++kb) tma_load_2d_cg2(smem_a + kb * BLK16, &tmap_a, kb * BK, t * BM, l_a_full);
-                // the rings double as scratch of the previous tile's final epilogue
-                mbar_wait(bar_epi_done, (tile_it & 1) ^ 1);
-                for (int step = 0; step <= NC; ++step) {
-                    if (step < NC) {
-                        for (int kb = 0; kb < KB1; ++kb, ++w1_it) {
-                            const uint32_t s = w1_it % S1N;
-                            mbar_wait(bar_w1_empty + 8 * s, ((w1_it / S1N) & 1) ^ 1);
-                            if (leader) mbar_arrive_expect_tx(bar_w1_full + 8 * s, 2 * W1_BLK);
-                            tma_load_2d_cg2(smem_w1 + s * W1_BLK, &tmap_w1, kb * BK, step * IC + crank * (IC / 2),
-                                            l_w1_full + 8 * s);
+            }
+            __syncwarp();
+            // the rings double as scratch of the previous tile's final epilogue
+            mbar_wait(bar_epi_done, (tile_it & 1) ^ 1);
+            for (int step = 0; step <= NC; ++step) {
+                if (step < NC) {
+                    const uint32_t s0 = (g1_it % R1) * KB1, ph = ((g1_it / R1) & 1) ^ 1;
+#pragma unroll
+                    for (int kb = 0; kb < KB1; ++kb) {
+                        mbar_wait(bar_w1_empty + 8 * (s0 + kb), ph);
+                        if (elect_one()) {
+                            if (leader) mbar_arrive_expect_tx(bar_w1_full + 8 * (s0 + kb), 2 * W1_BLK);
+                            tma_load_2d_cg2(smem_w1 + (s0 + kb) * W1_BLK, &tmap_w1, kb * BK, step * IC + crank * (IC / 2),
+                                            l_w1_full + 8 * (s0 + kb));
                         }
+                        __syncwarp();
                     }
-                    if (step >= 1) {
-                        const int ic = step - 1;
-                        for (int ns = 0; ns < NS; ++ns)
-                            for (int kb = 0; kb < IC / BK; ++kb, ++w2_it) {
-                                const uint32_t s = w2_it % S2N;
-                                mbar_wait(bar_w2_empty + 8 * s, ((w2_it / S2N) & 1) ^ 1);
-                                if (leader) mbar_arrive_expect_tx(bar_w2_full + 8 * s, 2 * W2_BLK);
-                                tma_load_2d_cg2(smem_w2 + s * W2_BLK, &tmap_w2, ic * IC + kb * BK,
-                                                ns * UN2 + crank * (UN2 / 2), l_w2_full + 8 * s);
-                            }
+                    ++g1_it;
+                }
+                if (step >= 1) {
+                    const int ic = step - 1;
+                    const uint32_t s0 = (g2_it % R2) * NB2, ph = ((g2_it / R2) & 1) ^ 1;
+#pragma unroll
+                    for (int blk = 0; blk < NB2; ++blk) {
+                        const int ns = blk / (IC / BK), kb = blk % (IC / BK);
+                        mbar_wait(bar_w2_empty + 8 * (s0 + blk), ph);
+                        if (elect_one()) {
+                            if (leader) mbar_arrive_expect_tx(bar_w2_full + 8 * (s0 + blk), 2 * W2_BLK);
+                            tma_load_2d_cg2(smem_w2 + (s0 + blk) * W2_BLK, &tmap_w2, ic * IC + kb * BK,
+                                            ns * UN2 + crank * (UN2 / 2), l_w2_full + 8 * (s0 + blk));
+                        }
+                        __syncwarp();
                     }
+                    ++g2_it;
                 }
             }
         }
@@ -184,25 +204,27 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         if (leader) {
             constexpr uint32_t idesc1 = umma_idesc_bf16(2 * BM, IC);
             constexpr uint32_t idesc2 = umma_idesc_bf16(2 * BM, UN2);
-            uint32_t w1_it = 0, w2_it = 0, tile_it = 0, g1_it = 0, g2_it = 0;  // g*_it: chunks issued so far
+            uint32_t tile_it = 0, g1_it = 0, g2_it = 0;  // g*_it: chunks issued so far
+            const uint64_t da0 = umma_desc_sw128(smem_a), dh0 = umma_desc_sw128(smem_h);
+            const uint64_t dw1 = umma_desc_sw128(smem_w1), dw2 = umma_desc_sw128(smem_w2);
             for (int pr = pair0; pr < num_pairs; pr += pair_step, ++tile_it) {
                 mbar_wait(bar_a_full, tile_it & 1);
                 for (int step = 0; step <= NC; ++step) {
                     if (step < NC) {  // G1(step): S1 = a . W1[chunk]^T
                         mbar_wait_cluster(bar_s1_empty, (g1_it & 1) ^ 1);  // both epilogues have drained the previous S1
                         tc_fence_after_sync();
-#pragma unroll 1
-                        for (int kb = 0; kb < KB1; ++kb, ++w1_it) {
-                            const uint32_t s = w1_it % S1N;
-                            mbar_wait(bar_w1_full + 8 * s, (w1_it / S1N) & 1);
+                        const uint32_t s0 = (g1_it % R1) * KB1, ph = (g1_it / R1) & 1;
+#pragma unroll
+                        for (int kb = 0; kb < KB1; ++kb) {
+                            mbar_wait(bar_w1_full + 8 * (s0 + kb), ph);
                             tc_fence_after_sync();
                             if (elect_one()) {
-                                const uint64_t da = umma_desc_sw128(smem_a + kb * BLK16);
-                                const uint64_t db = umma_desc_sw128(smem_w1 + s * W1_BLK);
+                                const uint64_t da = da0 + ((kb * BLK16) >> 4);
+                                const uint64_t db = dw1 + (((s0 + kb) * W1_BLK) >> 4);
 #pragma unroll
                                 for (int k = 0; k < BK / 16; ++k)
                                     umma_bf16_cg2(tmem_base, da + 2 * k, db + 2 * k, idesc1, (kb > 0 || k > 0) ? 1u : 0u);
-                                umma_commit_cg2(bar_w1_empty + 8 * s, BOTH);
+                                umma_commit_cg2(bar_w1_empty + 8 * (s0 + kb), BOTH);
                                 if (kb == KB1 - 1) {
                                     umma_commit_cg2(bar_s1_full, BOTH);
                                     // the a tiles have been read for the last time
@@ -218,21 +240,21 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                         mbar_wait_cluster(bar_h_full, g2_it & 1);  // h(ic) is in both CTAs' shared memory
                         if (ic == 0) mbar_wait_cluster(bar_out_empty, (tile_it & 1) ^ 1);  // previous tiles' OUT has been read
                         tc_fence_after_sync();
-#pragma unroll 1
-                        for (int blk = 0; blk < NS * (IC / BK); ++blk, ++w2_it) {
+                        const uint32_t s0 = (g2_it % R2) * NB2, ph = (g2_it / R2) & 1;
+#pragma unroll
+                        for (int blk = 0; blk < NB2; ++blk) {
                             const int ns = blk / (IC / BK), kb = blk % (IC / BK);
-                            const uint32_t s = w2_it % S2N;
-                            mbar_wait(bar_w2_full + 8 * s, (w2_it / S2N) & 1);
+                            mbar_wait(bar_w2_full + 8 * (s0 + blk), ph);
                             tc_fence_after_sync();
                             if (elect_one()) {
-                                const uint64_t da = umma_desc_sw128(smem_h + kb * BLK16);
-                                const uint64_t db = umma_desc_sw128(smem_w2 + s * W2_BLK);
+                                const uint64_t da = dh0 + ((kb * BLK16) >> 4);
+                                const uint64_t db = dw2 + (((s0 + blk) * W2_BLK) >> 4);
 #pragma unroll
                                 for (int k = 0; k < BK / 16; ++k)
                                     umma_bf16_cg2(tmem_base + OUT_COL + ns * UN2, da + 2 * k, db + 2 * k, idesc2,
                                                   (ic > 0 || kb > 0 || k > 0) ? 1u : 0u);
-                                umma_commit_cg2(bar_w2_empty + 8 * s, BOTH);
-                                if (blk == NS * (IC / BK) - 1) {
+                                umma_commit_cg2(bar_w2_empty + 8 * (s0 + blk), BOTH);
+                                if (blk == NB2 - 1) {
                                     umma_commit_cg2(bar_h_empty, BOTH);  // h(ic) consumed
                                     if (ic == NC - 1) umma_commit_cg2(bar_out_full, BOTH);
                                 }
@@ -286,6 +308,15 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             const int t = 2 * pr + static_cast<int>(crank);
             // ---- per chunk: h = gelu(S1 + b1) as the bf16 A operand of the second GEMM ----
             for (int ic = 0; ic < NC; ++ic, ++chunk_it) {
+                // this warp's 64 bias values -> its 256 B slot of the (now idle) LayerNorm scratch, fetched while S1 is
+                // still being computed
+                const uint32_t bias_s = aux + 1024 + ew * 256;
+                {
+                    const float2 b = __ldg(reinterpret_cast<const float2*>(p.b1 + ic * IC + half * 64) + lane);
+                    __syncwarp();  // every lane has finished reading the previous chunk's values
+                    asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(bias_s + lane * 8), "f"(b.x), "f"(b.y) : "memory");
+                    __syncwarp();
+                }
                 mbar_wait(bar_s1_full, chunk_it & 1);
                 tc_fence_after_sync();
                 uint32_t v[64];  // this thread's row, S1 columns half*64 .. +63
@@ -295,13 +326,12 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 tc_fence_before_sync();
                 __syncwarp();
                 if (lane == 0) mbar_arrive_cluster(l_s1_empty);  // S1 is in registers: the next chunk's GEMM1 may overwrite it
-                const float4* b4 = reinterpret_cast<const float4*>(p.b1 + ic * IC + half * 64);
                 uint32_t hp[32];
 #pragma unroll
                 for (int q = 0; q < 16; ++q) {
-                    const float4 b = __ldg(b4 + q);
-                    hp[q * 2 + 0] = epi_pair_bf16<EPI_GELU_ERF>(v[q * 4 + 0], v[q * 4 + 1], b.x, b.y);
-                    hp[q * 2 + 1] = epi_pair_bf16<EPI_GELU_ERF>(v[q * 4 + 2], v[q * 4 + 3], b.z, b.w);
+                    const uint4 b = lds_v4(bias_s + q * 16);
+                    hp[q * 2 + 0] = epi_pair_bf16<EPI_GELU_ERF>(v[q * 4 + 0], v[q * 4 + 1], __uint_as_float(b.x), __uint_as_float(b.y));
+                    hp[q * 2 + 1] = epi_pair_bf16<EPI_GELU_ERF>(v[q * 4 + 2], v[q * 4 + 3], __uint_as_float(b.z), __uint_as_float(b.w));
                 }
                 // the h buffer is free once GEMM2 of the previous chunk has completed
                 mbar_wait(bar_h_empty, (chunk_it & 1) ^ 1);
