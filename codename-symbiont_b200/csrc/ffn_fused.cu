@@ -50,7 +50,7 @@ struct FfnCfg {
     static constexpr int W2_BLK = (UN2 / 2) * BK * 2; // this CTA's half of a W2 block: [UN2/2 x 64]
     // Both rings hold a whole number of GEMM steps, so a block's ring slot is a compile-time function of its place
     // in the step (the MMA-issuing warp has no index arithmetic to do: its issue rate bounds the kernel otherwise).
-    static constexpr int R1 = H == 384 ? 1 : 2;       // GEMM1 steps in the W1 ring
+    static constexpr int R1 = H == 384 ? 1 : (H == 256 ? 2 : 3);  // GEMM1 steps in the W1 ring
     static constexpr int R2 = H == 384 ? 1 : 2;       // GEMM2 steps in the W2 ring
     static constexpr int NB2 = NS * (IC / BK);        // W2 blocks per GEMM2 step
     static constexpr int S1N = R1 * KB1;              // W1 ring stages
@@ -67,7 +67,7 @@ struct FfnCfg {
     static constexpr int HALF = H / 2;                // output columns per epilogue warp
     static constexpr int NCH = HALF / CHUNK;
     static_assert(H % 128 == 0 && H <= 384, "fused FFN needs the OUT accumulator (H columns) next to S1 (128) in TMEM");
-    static_assert(SCRATCH >= FF_EPI_WARPS * 6 * CHUNK_BF16, "final epilogue scratch does not fit");
+    static_assert(SCRATCH >= FF_EPI_WARPS * 6 * CHUNK_BF16 + 3 * H * 4, "final epilogue scratch does not fit");
     static_assert(BYTES <= SMEM_LIMIT, "shared memory budget exceeded");
     static_assert(W1_BLK % 1024 == 0 && W2_BLK % 1024 == 0 && (UN2 / 2) % 8 == 0, "swizzle atoms must stay 1024-byte aligned");
 };
@@ -85,10 +85,11 @@ template <int H>
 __global__ void __launch_bounds__(FF_THREADS, 1)
 ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w1,
                  const __grid_constant__ CUtensorMap tmap_w2, const __grid_constant__ CUtensorMap tmap_r,
-                 const __grid_constant__ CUtensorMap tmap_r_lo, const __grid_constant__ CUtensorMap tmap_c,
+                 const __grid_constant__ CUtensorMap tmap_r_lo, const __grid_constant__ CUtensorMap tmap_lo_pf,
+                 const __grid_constant__ CUtensorMap tmap_c,
                  const __grid_constant__ CUtensorMap tmap_c_lo, const FfnDev p) {
     using C = FfnCfg<H>;
-    constexpr int KB1 = C::KB1, NS = C::NS, UN2 = C::UN2, W1_BLK = C::W1_BLK, W2_BLK = C::W2_BLK, S1N = C::S1N, S2N = C::S2N;
+    constexpr int KB1 = C::KB1, UN2 = C::UN2, W1_BLK = C::W1_BLK, W2_BLK = C::W2_BLK, S1N = C::S1N, S2N = C::S2N;
     constexpr int R1 = C::R1, R2 = C::R2, NB2 = C::NB2;
     constexpr uint16_t BOTH = 3;  // multicast mask: both CTAs of the pair
     constexpr int HALF = C::HALF, NCH = C::NCH;
@@ -105,9 +106,9 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     const uint32_t bar_w2_full = aux + 144, bar_w2_empty = aux + 208;  // <= 8 each
     const uint32_t bar_s1_full = aux + 272, bar_s1_empty = aux + 280, bar_h_full = aux + 288, bar_h_empty = aux + 296;
     const uint32_t bar_out_full = aux + 304, bar_out_empty = aux + 312, bar_epi_done = aux + 320;
-    const uint32_t bar_res = aux + 384;   // FF_EPI_WARPS x 2
-    const uint32_t tmem_slot = aux + 512;
-    volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(aux_ptr + 512);
+    const uint32_t bar_res = aux + 384;   // FF_EPI_WARPS x 4
+    const uint32_t tmem_slot = aux + 768;
+    volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(aux_ptr + 768);
     float2* ln_part = reinterpret_cast<float2*>(aux_ptr + 1024);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -131,7 +132,8 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 
     if (threadIdx.x == 0) {
         prefetch_tmap(&tmap_a); prefetch_tmap(&tmap_w1); prefetch_tmap(&tmap_w2);
-        mbar_init(bar_a_full, 1); mbar_init(bar_a_empty, 1);
+        mbar_init(bar_a_full, 1);
+        mbar_init(bar_a_empty, 1 + FF_EPI_WARPS);  // last GEMM1 done + every epilogue warp has read its residual rows
         for (int s = 0; s < S1N; ++s) { mbar_init(bar_w1_full + 8 * s, 1); mbar_init(bar_w1_empty + 8 * s, 1); }
         for (int s = 0; s < S2N; ++s) { mbar_init(bar_w2_full + 8 * s, 1); mbar_init(bar_w2_empty + 8 * s, 1); }
         // one arrive per epilogue warp of both CTAs on the barriers the MMA thread waits on
@@ -139,7 +141,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         mbar_init(bar_h_full, 2 * FF_EPI_WARPS); mbar_init(bar_h_empty, 1);
         mbar_init(bar_out_full, 1); mbar_init(bar_out_empty, 2 * FF_EPI_WARPS);
         mbar_init(bar_epi_done, FF_EPI_THREADS);
-        for (int s = 0; s < 2 * FF_EPI_WARPS; ++s) mbar_init(bar_res + 8 * s, 1);
+        for (int s = 0; s < 4 * FF_EPI_WARPS; ++s) mbar_init(bar_res + 8 * s, 1);
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc_cg2(tmem_slot, 512);
@@ -162,6 +164,10 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 if (leader) mbar_arrive_expect_tx(bar_a_full, 2 * KB1 * BLK16);
 #pragma unroll
                 for (int kb = 0; kb < KB1; ++kb) tma_load_2d_cg2(smem_a + kb * BLK16, &tmap_a, kb * BK, t * BM, l_a_full);
+                if (p.has_lo) {  // the low halves of the same rows are needed by the final epilogue: pull them into L2 now
+#pragma unroll
+                    for (int kb = 0; kb < KB1; ++kb) tma_prefetch_2d(&tmap_lo_pf, kb * BK, t * BM);
+                }
             }
             __syncwarp();
             // the rings double as scratch of the previous tile's final epilogue
@@ -271,35 +277,20 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         const int quad = warp & 3, half = ew >> 2;
         const int row_in_tile = quad * 32 + lane;
         const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
-        // final-epilogue scratch of this warp inside the (then idle) h / ring region: 2-stage (hi, lo) residual ring
-        // and two output staging buffers
+        // final-epilogue scratch of this warp inside the (then idle) h / ring region: 4-slot residual-lo ring and two
+        // output staging buffers
         const uint32_t my_smem = smem_h + ew * (6 * CHUNK_BF16);
         const uint32_t out_buf = my_smem + 4 * CHUNK_BF16;
-        uint32_t chunk_it = 0, tile_it = 0, st_it = 0, ld_issued = 0, ld_used = 0;
+        const uint32_t const_s = smem_h + FF_EPI_WARPS * (6 * CHUNK_BF16);  // b2 | gamma | beta, fp32 (final epilogue)
+        uint32_t chunk_it = 0, tile_it = 0, ld_issued = 0, ld_used = 0;
 
-        auto store_chunk = [&](const CUtensorMap* map, int col0, int row0, const float (&f)[32], bool lo) {
-            const uint32_t buf = out_buf + (st_it & 1) * CHUNK_BF16;
-            if (lane == 0) tma_store_wait_read<1>();
-            __syncwarp();
-            if (lo) stage_row_bf16_lo(buf, lane, f);
-            else stage_row_bf16(buf, lane, f);
-            fence_proxy_async_smem();
-            __syncwarp();
+        // residual: the hi half is the a tile itself (still in shared memory); the lo half comes through a 4-slot ring
+        auto issue_lo = [&](int tile, int c) {
             if (lane == 0) {
-                tma_store_2d(map, buf, col0, row0);
-                tma_store_commit();
-            }
-            ++st_it;
-        };
-        auto issue_residual = [&](int tile, int c) {
-            if (lane == 0) {
-                const uint32_t s = ld_issued & 1;
-                const uint32_t bar = bar_res + 8 * (2 * ew + s);
-                const uint32_t dst = my_smem + s * (2 * CHUNK_BF16);
-                const int col0 = half * HALF + c * CHUNK, row0 = tile * BM + quad * 32;
-                mbar_arrive_expect_tx(bar, p.has_lo ? 2 * CHUNK_BF16 : CHUNK_BF16);
-                tma_load_2d(dst, &tmap_r, col0, row0, bar);
-                if (p.has_lo) tma_load_2d(dst + CHUNK_BF16, &tmap_r_lo, col0, row0, bar);
+                const uint32_t s = ld_issued & 3;
+                const uint32_t bar = bar_res + 8 * (4 * ew + s);
+                mbar_arrive_expect_tx(bar, CHUNK_BF16);
+                tma_load_2d(my_smem + s * CHUNK_BF16, &tmap_r_lo, half * HALF + c * CHUNK, tile * BM + quad * 32, bar);
             }
             ++ld_issued;
         };
@@ -351,53 +342,52 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             // ---- final: x' = LayerNorm(OUT + b2 + a) -> (hi, lo) ----
             mbar_wait(bar_out_full, tile_it & 1);  // every MMA of this tile has completed: h and the rings are idle
             tc_fence_after_sync();
-            issue_residual(t, 0);
-            if (NCH > 1) issue_residual(t, 1);
+            if (p.has_lo) {
+#pragma unroll
+                for (int c = 0; c < (NCH < 4 ? NCH : 4); ++c) issue_lo(t, c);
+            }
+            // b2, gamma, beta -> scratch behind the per-warp areas, read back with broadcast LDS in the loops
+            for (int i = threadIdx.x - FF_EPI_WARP0 * 32; i < 3 * H; i += FF_EPI_THREADS) {
+                const float* src = i < H ? p.b2 + i : (i < 2 * H ? p.gamma + (i - H) : p.beta + (i - 2 * H));
+                asm volatile("st.shared.f32 [%0], %1;" ::"r"(const_s + i * 4), "f"(__ldg(src)) : "memory");
+            }
+            asm volatile("bar.sync 1, %0;" ::"n"(FF_EPI_THREADS) : "memory");
             const uint32_t taddr = t_lane + OUT_COL + half * HALF;
             const int row0 = t * BM + quad * 32;
-            float sum = 0.f, sumsq = 0.f;
-#pragma unroll 1
-            for (int c = 0; c < NCH; ++c) {
-                uint32_t v[32];
-                tmem_ld_32x32(taddr + c * CHUNK, v);
-                const uint32_t s = ld_used & 1;
-                mbar_wait(bar_res + 8 * (2 * ew + s), (ld_used >> 1) & 1);
-                ++ld_used;
-                const uint32_t rbuf = my_smem + s * (2 * CHUNK_BF16) + lane * 64;
-                const int sw = (lane >> 1) & 3;
-                tmem_ld_wait();
-                const float4* b4 = reinterpret_cast<const float4*>(p.b2 + half * HALF + c * CHUNK);
+            uint64_t sum2 = 0, sq2 = 0;  // (0.f, 0.f)
+            {
+                uint32_t v[2][32];
+                tmem_ld_32x32(taddr, v[0]);
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const uint4 r = lds_v4(rbuf + ((q ^ sw) << 4));
-                    const float4 b0 = __ldg(b4 + 2 * q), b1 = __ldg(b4 + 2 * q + 1);
-                    float2 r0 = unpack_bf16x2(r.x), r1 = unpack_bf16x2(r.y), r2 = unpack_bf16x2(r.z), r3 = unpack_bf16x2(r.w);
+                for (int c = 0; c < NCH; ++c) {
+                    const int col0 = half * HALF + c * CHUNK;
+                    uint32_t hi_addr[4], lo_addr[4];
+                    // a tile: k-block col0 / 64, 128-byte rows, SWIZZLE_128B; lo slot: 64-byte rows, SWIZZLE_64B
+                    const uint32_t arow = smem_a + (col0 / BK) * BLK16 + row_in_tile * 128;
+                    const uint32_t lrow = my_smem + (ld_used & 3) * CHUNK_BF16 + lane * 64;
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        hi_addr[q] = arow + ((((col0 % BK) / 8 + q) ^ (row_in_tile & 7)) << 4);
+                        lo_addr[q] = lrow + ((q ^ ((lane >> 1) & 3)) << 4);
+                    }
                     if (p.has_lo) {
-                        const uint4 l = lds_v4(rbuf + CHUNK_BF16 + ((q ^ sw) << 4));
-                        const float2 l0 = unpack_bf16x2(l.x), l1 = unpack_bf16x2(l.y), l2 = unpack_bf16x2(l.z),
-                                     l3 = unpack_bf16x2(l.w);
-                        r0.x += l0.x; r0.y += l0.y; r1.x += l1.x; r1.y += l1.y;
-                        r2.x += l2.x; r2.y += l2.y; r3.x += l3.x; r3.y += l3.y;
+                        mbar_wait(bar_res + 8 * (4 * ew + (ld_used & 3)), (ld_used >> 2) & 1);
+                        ++ld_used;
                     }
-                    float x[8];
-                    x[0] = __uint_as_float(v[q * 8 + 0]) + b0.x + r0.x;
-                    x[1] = __uint_as_float(v[q * 8 + 1]) + b0.y + r0.y;
-                    x[2] = __uint_as_float(v[q * 8 + 2]) + b0.z + r1.x;
-                    x[3] = __uint_as_float(v[q * 8 + 3]) + b0.w + r1.y;
-                    x[4] = __uint_as_float(v[q * 8 + 4]) + b1.x + r2.x;
-                    x[5] = __uint_as_float(v[q * 8 + 5]) + b1.y + r2.y;
-                    x[6] = __uint_as_float(v[q * 8 + 6]) + b1.z + r3.x;
-                    x[7] = __uint_as_float(v[q * 8 + 7]) + b1.w + r3.y;
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        sum += x[j];
-                        sumsq = fmaf(x[j], x[j], sumsq);
-                        v[q * 8 + j] = __float_as_uint(x[j]);
-                    }
+                    tmem_ld_wait();
+                    if (c + 1 < NCH) tmem_ld_32x32(taddr + (c + 1) * CHUNK, v[(c + 1) & 1]);
+                    ln_accumulate_chunk(v[c & 1], const_s + col0 * 4, hi_addr, lo_addr, p.has_lo != 0, sum2, sq2);
+                    tmem_st_32x32(taddr + c * CHUNK, v[c & 1]);
+                    __syncwarp();
+                    if (p.has_lo && c + 4 < NCH) issue_lo(t, c + 4);
                 }
-                tmem_st_32x32(taddr + c * CHUNK, v);
-                __syncwarp();
-                if (c + 2 < NCH) issue_residual(t, c + 2);
+            }
+            if (lane == 0) mbar_arrive(bar_a_empty);  // this warp's residual rows have been read from the a tile
+            float sum, sumsq;
+            {
+                float a, b;
+                upk2(sum2, a, b); sum = a + b;
+                upk2(sq2, a, b); sumsq = a + b;
             }
             tmem_st_wait();
             ln_part[half * BM + row_in_tile] = make_float2(sum, sumsq);
@@ -407,29 +397,35 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             const float mean = (sum + other.x) * inv_n;
             const float var = fmaxf((sumsq + other.y) * inv_n - mean * mean, 0.f);
             const float rstd = rsqrtf(var + p.eps);
-#pragma unroll 1
-            for (int c = 0; c < NCH; ++c) {
-                float f[32];
-                tmem_ld_32x32(taddr + c * CHUNK, *reinterpret_cast<uint32_t(*)[32]>(&f[0]));
-                tmem_ld_wait();
-                if (c == NCH - 1) {  // OUT fully read: the next tile's GEMM2 may overwrite it
-                    tc_fence_before_sync();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive_cluster(l_out_empty);
-                }
-                const int col0 = half * HALF + c * CHUNK;
-                const float4* g4 = reinterpret_cast<const float4*>(p.gamma + col0);
-                const float4* be4 = reinterpret_cast<const float4*>(p.beta + col0);
+            {
+                uint32_t x[2][32];
+                tmem_ld_32x32(taddr, x[0]);
 #pragma unroll
-                for (int q = 0; q < 8; ++q) {
-                    const float4 g = __ldg(g4 + q), be = __ldg(be4 + q);
-                    f[q * 4 + 0] = fmaf((f[q * 4 + 0] - mean) * rstd, g.x, be.x);
-                    f[q * 4 + 1] = fmaf((f[q * 4 + 1] - mean) * rstd, g.y, be.y);
-                    f[q * 4 + 2] = fmaf((f[q * 4 + 2] - mean) * rstd, g.z, be.z);
-                    f[q * 4 + 3] = fmaf((f[q * 4 + 3] - mean) * rstd, g.w, be.w);
+                for (int c = 0; c < NCH; ++c) {
+                    tmem_ld_wait();
+                    if (c + 1 < NCH) {
+                        tmem_ld_32x32(taddr + (c + 1) * CHUNK, x[(c + 1) & 1]);
+                    } else {  // OUT fully read: the next tile's GEMM2 may overwrite it
+                        tc_fence_before_sync();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive_cluster(l_out_empty);
+                    }
+                    const int col0 = half * HALF + c * CHUNK;
+                    uint32_t hi[16], lo[16];
+                    ln_normalize_chunk(x[c & 1], mean, rstd, const_s + (H + col0) * 4, const_s + (2 * H + col0) * 4, hi, lo);
+                    const uint32_t buf_hi = out_buf, buf_lo = out_buf + CHUNK_BF16;
+                    if (lane == 0) tma_store_wait_read<0>();
+                    __syncwarp();
+                    stage_words_bf16(buf_hi, lane, hi);
+                    if (p.has_lo) stage_words_bf16(buf_lo, lane, lo);
+                    fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0) {
+                        tma_store_2d(&tmap_c, buf_hi, col0, row0);
+                        if (p.has_lo) tma_store_2d(&tmap_c_lo, buf_lo, col0, row0);
+                        tma_store_commit();
+                    }
                 }
-                store_chunk(&tmap_c, col0, row0, f, false);
-                if (p.has_lo) store_chunk(&tmap_c_lo, col0, row0, f, true);
             }
             // scratch (h + rings) may be refilled once the TMA stores have read their staging buffers
             if (lane == 0) tma_store_wait_read<0>();
@@ -452,13 +448,15 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 template <int H>
 cudaError_t launch_ffn(const FfnFusedArgs& a, cudaStream_t stream, int num_sms) {
     using C = FfnCfg<H>;
-    alignas(64) CUtensorMap ta, tw1, tw2, tr, trl, tc, tcl;
+    alignas(64) CUtensorMap ta, tw1, tw2, tr, trl, tlp, tc, tcl;
     if (!make_tmap(&ta, a.a, a.m, H, BK, BM, false, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
     if (!make_tmap(&tw1, a.w1, a.inter, H, BK, IC / 2, false, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
     if (!make_tmap(&tw2, a.w2, H, a.inter, BK, C::UN2 / 2, false, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
     if (!make_tmap(&tr, a.a, a.m, H, CHUNK, 32, false, CU_TENSOR_MAP_SWIZZLE_64B)) return cudaErrorInvalidValue;
     trl = tr;
     if (a.a_lo && !make_tmap(&trl, a.a_lo, a.m, H, CHUNK, 32, false, CU_TENSOR_MAP_SWIZZLE_64B)) return cudaErrorInvalidValue;
+    tlp = ta;
+    if (a.a_lo && !make_tmap(&tlp, a.a_lo, a.m, H, BK, BM, false, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
     if (!make_tmap(&tc, a.out, a.m, H, CHUNK, 32, false, CU_TENSOR_MAP_SWIZZLE_64B)) return cudaErrorInvalidValue;
     tcl = tc;
     if (a.out_lo && !make_tmap(&tcl, a.out_lo, a.m, H, CHUNK, 32, false, CU_TENSOR_MAP_SWIZZLE_64B)) return cudaErrorInvalidValue;
@@ -494,7 +492,7 @@ cudaError_t launch_ffn(const FfnFusedArgs& a, cudaStream_t stream, int num_sms) 
     const int grid = 2 * (pairs < max_pairs ? pairs : max_pairs);
     if (grid <= 0) return cudaSuccess;
     cfg.gridDim = dim3(grid);
-    return cudaLaunchKernelEx(&cfg, kern, ta, tw1, tw2, tr, trl, tc, tcl, p);
+    return cudaLaunchKernelEx(&cfg, kern, ta, tw1, tw2, tr, trl, tlp, tc, tcl, p);
 }
 
 }  // namespace

@@ -170,6 +170,67 @@ __device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
     return v;
 }
 
+// ---- residual + LayerNorm epilogue arithmetic on one 32-column chunk of this thread's row (packed fp32 pairs) ----
+// Pass 1: x = acc + bias + residual_hi (+ residual_lo), accumulated into (sum, sum of squares) pairs; x replaces acc
+// in v. bias_s: shared address of the chunk's 32 bias floats; hi_addr / lo_addr: shared addresses of the four 16-byte
+// pieces (8 bf16 each) of this thread's row of the residual chunk, whatever layout they sit in.
+__device__ __forceinline__ void ln_accumulate_chunk(uint32_t (&v)[32], uint32_t bias_s, const uint32_t (&hi_addr)[4],
+                                                    const uint32_t (&lo_addr)[4], bool has_lo, uint64_t& sum2,
+                                                    uint64_t& sq2) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const uint4 r = lds_v4(hi_addr[q]);
+        uint4 l = make_uint4(0, 0, 0, 0);
+        if (has_lo) l = lds_v4(lo_addr[q]);
+        const uint4 b0 = lds_v4(bias_s + q * 32), b1 = lds_v4(bias_s + q * 32 + 16);
+        const uint32_t rw[4] = {r.x, r.y, r.z, r.w}, lw[4] = {l.x, l.y, l.z, l.w};
+        const uint32_t bw[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            uint64_t x = add2(pk2(__uint_as_float(v[q * 8 + 2 * j]), __uint_as_float(v[q * 8 + 2 * j + 1])),
+                              pk2(__uint_as_float(bw[2 * j]), __uint_as_float(bw[2 * j + 1])));
+            x = add2(x, pk2(__uint_as_float(rw[j] << 16), __uint_as_float(rw[j] & 0xffff0000u)));
+            if (has_lo) x = add2(x, pk2(__uint_as_float(lw[j] << 16), __uint_as_float(lw[j] & 0xffff0000u)));
+            sum2 = add2(sum2, x);
+            sq2 = fma2(x, x, sq2);
+            float a, b;
+            upk2(x, a, b);
+            v[q * 8 + 2 * j] = __float_as_uint(a);
+            v[q * 8 + 2 * j + 1] = __float_as_uint(b);
+        }
+    }
+}
+// Pass 2: y = (x - mean) * rstd * gamma + beta -> hi = bf16(y) and lo = bf16(y - hi), two values per word.
+// gamma_s / beta_s: shared addresses of the chunk's 32 floats.
+__device__ __forceinline__ void ln_normalize_chunk(const uint32_t (&x)[32], float mean, float rstd, uint32_t gamma_s,
+                                                   uint32_t beta_s, uint32_t (&hi)[16], uint32_t (&lo)[16]) {
+    const uint64_t r2 = pk2(rstd, rstd), nm2 = pk2(-mean * rstd, -mean * rstd), m1 = pk2(-1.0f, -1.0f);
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+        const uint4 g = lds_v4(gamma_s + q * 16), be = lds_v4(beta_s + q * 16);
+        const uint32_t gw[4] = {g.x, g.y, g.z, g.w}, bw[4] = {be.x, be.y, be.z, be.w};
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const uint64_t t = fma2(pk2(__uint_as_float(x[q * 4 + 2 * j]), __uint_as_float(x[q * 4 + 2 * j + 1])), r2, nm2);
+            const uint64_t y = fma2(t, pk2(__uint_as_float(gw[2 * j]), __uint_as_float(gw[2 * j + 1])),
+                                    pk2(__uint_as_float(bw[2 * j]), __uint_as_float(bw[2 * j + 1])));
+            float a, b;
+            upk2(y, a, b);
+            const uint32_t h = pack_bf16x2(a, b);
+            hi[q * 2 + j] = h;
+            upk2(fma2(pk2(__uint_as_float(h << 16), __uint_as_float(h & 0xffff0000u)), m1, y), a, b);
+            lo[q * 2 + j] = pack_bf16x2(a, b);
+        }
+    }
+}
+// one staged 32 x 32 bf16 chunk (SWIZZLE_64B rows of 64 bytes): this lane's 16 words
+__device__ __forceinline__ void stage_words_bf16(uint32_t buf, int r, const uint32_t (&w)[16]) {
+    const uint32_t row = buf + r * 64;
+    const int sw = (r >> 1) & 3;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) sts_v4(row + ((q ^ sw) << 4), w[q * 4], w[q * 4 + 1], w[q * 4 + 2], w[q * 4 + 3]);
+}
+
 PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
     static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
     static std::once_flag once;
