@@ -132,6 +132,11 @@ __device__ __forceinline__ uint32_t map_to_cta(uint32_t local_smem, uint32_t ran
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_smem), "r"(rank));
     return r;
 }
+// Warp-level wait for warp-uniform pipelines: one lane polls, the warp reconverges behind it.
+__device__ __forceinline__ void mbar_wait_warp(uint32_t bar, uint32_t parity) {
+    if ((threadIdx.x & 31) == 0) mbar_wait(bar, parity);
+    __syncwarp();
+}
 // mbar_wait whose acquire covers arrivals (and the writes released by them) from other CTAs of the cluster
 __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
     uint32_t done = 0;
@@ -155,29 +160,6 @@ __device__ __forceinline__ void tma_load_2d_cg2(uint32_t dst_smem, const void* t
     asm volatile(
         "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
         ::"r"(dst_smem), "l"(tmap), "r"(bar), "r"(c0), "r"(c1)
-        : "memory");
-}
-// L2 cache policies for the hinted TMA forms below.
-__device__ __forceinline__ uint64_t l2_policy_evict_first() {
-    uint64_t p;
-    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
-    return p;
-}
-__device__ __forceinline__ uint64_t l2_policy_evict_last() {
-    uint64_t p;
-    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
-    return p;
-}
-__device__ __forceinline__ void tma_store_2d_hint(const void* tmap, uint32_t src_smem, int c0, int c1, uint64_t policy) {
-    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group.L2::cache_hint [%0, {%2, %3}], [%1], %4;" ::"l"(tmap),
-                 "r"(src_smem), "r"(c0), "r"(c1), "l"(policy)
-                 : "memory");
-}
-__device__ __forceinline__ void tma_load_2d_hint(uint32_t dst_smem, const void* tmap, int c0, int c1, uint32_t bar,
-                                                 uint64_t policy) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5;"
-        ::"r"(dst_smem), "l"(tmap), "r"(bar), "r"(c0), "r"(c1), "l"(policy)
         : "memory");
 }
 // Pull one box of a tiled tensor into L2 without a shared-memory destination.

@@ -108,13 +108,9 @@ struct b200_embed {
     bool fuse_ln = false;
     int bn_qkv = 0, bn_ffn1 = 0, bn_h = 0, bn_ln = 0;
     int act_epi = b200::EPI_GELU_ERF;
-    bool gemm_pair = false;  // B200_EMBED_GEMM_PAIR=1: plain GEMMs as W-sharing CTA pairs (no gain measured: TMA
-                             // multicast across 2 CTAs does not cut L2 reads; kept for A/B checks)
-    bool gemm_res_a = false;  // B200_EMBED_GEMM_RESIDENT_A=1: keep the A tile resident across column tiles (K <= 384);
-                              // measured neutral (these tiles are bound by shared-memory bandwidth, not L2 reads)
-    bool ffn_fused = false;  // B200_EMBED_FFN_FUSED=1: K2f replaces the FFN1 / FFN2 GEMM pair (hidden <= 384, erf-GELU).
-                             // Off by default: with one CTA per tile its 128-column chunks run the tensor pipe at 38 %
-                             // and it measured 1.72 ms vs 1.47 ms for the two GEMMs at c2
+    bool gemm_pair = true;   // plain bf16 GEMMs as CTA pairs (one cta_group::2 MMA per pair); B200_EMBED_GEMM_PAIR=0 for A/B
+    bool ffn_fused = false;  // K2f replaces the FFN1 / FFN2 GEMM pair: on whenever it supports the shape (hidden 128 / 256 /
+                             // 384, erf-GELU); B200_EMBED_FFN_FUSED=0 for A/B
     bool attn_mma = false;  // B200_EMBED_ATTENTION=mma selects the mma.sync attention kernel (A/B checks)
     // weights
     float* arena32 = nullptr;
@@ -325,12 +321,7 @@ int gemm16(b200_embed* h, Context& c, cudaStream_t s, int kind, const void* x, c
     g.residual_lo = residual_lo; g.out_lo = out_lo;
     g.gamma = gamma; g.beta = beta; g.eps = h->cfg.layer_norm_eps; g.out = out; g.out_f32 = out_f32; g.epi = epi;
     g.block_n = block_n;
-    g.pair = h->gemm_pair ? 1 : 0;
-    g.no_resident_a = h->gemm_res_a ? 0 : 1;
-    if (const char* nv = getenv("B200_EMBED_GEMM_NSPLIT")) g.nsplit = atoi(nv);
-    if (const char* wv = getenv("B200_EMBED_GEMM_WIDE_STORE")) g.wide_store = atoi(wv);
-    if (const char* pv = getenv("B200_EMBED_GEMM_PAIR")) g.pair = atoi(pv);
-    if (getenv("B200_EMBED_QKV_BN128") && kind == B200_EMBED_KIND_GEMM_QKV) g.block_n = 128;
+    g.pair = (h->gemm_pair && epi != b200::EPI_RES_LN && !out_f32) ? 1 : 0;
     CU_TRY(timed(h, c, s, kind, 1, [&] { return b200::gemm_tc_launch(g, s, h->num_sms); }));
     return B200_EMBED_OK;
 }
@@ -558,11 +549,10 @@ int32_t b200_embed_create(const b200_embed_config* cfg, const char* path, uint64
     h->fuse_ln = h->bn_ln != 0;
     if (const char* v = getenv("B200_EMBED_FUSE_LN")) h->fuse_ln = h->fuse_ln && std::string(v) != "0";
     h->act_epi = b200::EPI_GELU_ERF + cfg->hidden_act;
-    if (const char* v = getenv("B200_EMBED_FFN_FUSED"))
-        h->ffn_fused = std::string(v) == "1" && b200::ffn_fused_supported(H, I, cfg->hidden_act);
+    h->ffn_fused = h->fuse_ln && b200::ffn_fused_supported(H, I, cfg->hidden_act);
+    if (const char* v = getenv("B200_EMBED_FFN_FUSED")) h->ffn_fused = h->ffn_fused && std::string(v) != "0";
     if (const char* v = getenv("B200_EMBED_ATTENTION")) h->attn_mma = std::string(v) == "mma";
-    if (const char* v = getenv("B200_EMBED_GEMM_PAIR")) h->gemm_pair = std::string(v) == "1";
-    if (const char* v = getenv("B200_EMBED_GEMM_RESIDENT_A")) h->gemm_res_a = std::string(v) == "1";
+    if (const char* v = getenv("B200_EMBED_GEMM_PAIR")) h->gemm_pair = std::string(v) != "0";
     h->bn_qkv = b200::gemm_tc_pick_block_n(3 * H, b200::EPI_BIAS);
     h->bn_ffn1 = b200::gemm_tc_pick_block_n(I, h->act_epi);
     h->bn_h = b200::gemm_tc_pick_block_n(H, b200::EPI_GELU_ERF);  // 256 or 128 (fp32-out instantiations)
@@ -1047,10 +1037,7 @@ int32_t b200_op_gemm_bf16(const void* a, const void* b, const float* bias, int32
     b200::GemmTcArgs g{};
     g.a = a; g.b = b; g.m = m; g.n = n; g.k = k; g.bias = bias; g.out = c; g.epi = epi; g.block_n = block_n;
     const char* pv = getenv("B200_EMBED_GEMM_PAIR");
-    g.pair = pv ? atoi(pv) : 0;
-    if (const char* nv = getenv("B200_EMBED_GEMM_NSPLIT")) g.nsplit = atoi(nv);
-    const char* rv = getenv("B200_EMBED_GEMM_RESIDENT_A");
-    g.no_resident_a = (rv && std::string(rv) == "1") ? 0 : 1;
+    g.pair = (pv && std::string(pv) == "0") ? 0 : 1;
     CU_TRY(b200::gemm_tc_launch(g, static_cast<cudaStream_t>(stream), sms));
     return B200_EMBED_OK;
 }

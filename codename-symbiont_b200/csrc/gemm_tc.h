@@ -27,10 +27,7 @@ struct GemmTcArgs {
     void* out_lo;          // EPI_RES_LN: optional [m, n] bf16 low half of the output
     int out_f32;           // only with EPI_BIAS
     int epi;               // GemmEpilogue
-    int no_resident_a;     // plain epilogues: 1 disables the resident-A schedule used when k <= 384 (A/B checks)
-    int wide_store;        // plain bf16 epilogues with block_n 128 / 256: TMA-store 128-byte row segments (two chunks)
-    int nsplit;            // 2 = issue 256-wide tiles as two independent 128-column MMAs per k-step (measured option)
-    int pair;              // plain epilogues: run as clusters of 2 CTAs on adjacent row blocks that share the W tile
+    int pair;              // plain bf16 epilogues: 1 = clusters of 2 CTAs on adjacent row blocks, one cta_group::2 MMA per pair
     int block_n;           // 128, 192, 256 (EPI_RES_LN: n / cluster size, from gemm_tc_pick_block_n)
 };
 

@@ -97,52 +97,7 @@ __device__ __forceinline__ uint32_t epi_pair_bf16(uint32_t acc0, uint32_t acc1, 
     }
 }
 
-// Writes this thread's row of a 32x32 chunk into a staging buffer laid out as the TMA box expects.
-// bf16: 64-byte rows, SWIZZLE_64B (16-byte piece q of row r lands at piece q ^ ((r >> 1) & 3)).
-__device__ __forceinline__ void stage_row_bf16(uint32_t buf, int r, const float (&f)[32]) {
-    const uint32_t row = buf + r * 64;
-    const int sw = (r >> 1) & 3;
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        const uint32_t a = row + ((q ^ sw) << 4);
-        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(pack_bf16x2(f[q * 8 + 0], f[q * 8 + 1])),
-                     "r"(pack_bf16x2(f[q * 8 + 2], f[q * 8 + 3])), "r"(pack_bf16x2(f[q * 8 + 4], f[q * 8 + 5])),
-                     "r"(pack_bf16x2(f[q * 8 + 6], f[q * 8 + 7]))
-                     : "memory");
-    }
-}
-// Same row into a 128-byte-row staging buffer (two chunks side by side, SWIZZLE_128B): chunk `side` fills pieces
-// side * 4 .. side * 4 + 3 of the row.
-__device__ __forceinline__ void stage_row_bf16_wide(uint32_t buf, int r, int side, const float (&f)[32]) {
-    const uint32_t row = buf + r * 128;
-    const int sw = r & 7;
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        const uint32_t a = row + (((side * 4 + q) ^ sw) << 4);
-        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(pack_bf16x2(f[q * 8 + 0], f[q * 8 + 1])),
-                     "r"(pack_bf16x2(f[q * 8 + 2], f[q * 8 + 3])), "r"(pack_bf16x2(f[q * 8 + 4], f[q * 8 + 5])),
-                     "r"(pack_bf16x2(f[q * 8 + 6], f[q * 8 + 7]))
-                     : "memory");
-    }
-}
-// lo[j] = bf16(f[j] - bf16(f[j])): the part of the fp32 value the bf16 "hi" tensor dropped
-__device__ __forceinline__ void stage_row_bf16_lo(uint32_t buf, int r, const float (&f)[32]) {
-    const uint32_t row = buf + r * 64;
-    const int sw = (r >> 1) & 3;
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        uint32_t w[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const float a = f[q * 8 + 2 * j], b = f[q * 8 + 2 * j + 1];
-            const float2 h = unpack_bf16x2(pack_bf16x2(a, b));
-            w[j] = pack_bf16x2(a - h.x, b - h.y);
-        }
-        const uint32_t a = row + ((q ^ sw) << 4);
-        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3])
-                     : "memory");
-    }
-}
+// Staging buffers are laid out as the TMA store box expects.
 // fp32: 128-byte rows, SWIZZLE_128B (piece q of row r lands at piece q ^ (r & 7)).
 __device__ __forceinline__ void stage_row_f32(uint32_t buf, int r, const float (&f)[32]) {
     const uint32_t row = buf + r * 128;
@@ -157,12 +112,6 @@ __device__ __forceinline__ void stage_row_f32(uint32_t buf, int r, const float (
 }
 __device__ __forceinline__ void sts_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
     asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
-}
-// 32 bytes (one full sector) per lane straight to global memory
-__device__ __forceinline__ void stg_v8(void* ptr, const uint32_t* w) {
-    asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(ptr), "r"(w[0]), "r"(w[1]), "r"(w[2]),
-                 "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7])
-                 : "memory");
 }
 __device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
     uint4 v;

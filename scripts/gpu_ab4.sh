@@ -8,6 +8,4 @@ d=json.loads(sys.stdin.read())
 print('value',round(d['value']),'ms',round(d['ms_per_step'],2), d['clocks']['sm_mhz'], {k:v['ms_per_launch'] for k,v in d['kernels'].items()})"
 }
 run X=0
-run B200_EMBED_FFN_FUSED=1
-run B200_EMBED_GEMM_PAIR=2
-run B200_EMBED_FFN_FUSED=1 B200_EMBED_GEMM_PAIR=2
+run B200_EMBED_FFN_FUSED=0
