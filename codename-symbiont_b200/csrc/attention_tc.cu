@@ -131,9 +131,11 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
     const int per_b = p.heads * p.q_blocks;
     struct Walk { int b, r; };
     auto walk_init = [&]() { return Walk{static_cast<int>(blockIdx.x) / per_b, static_cast<int>(blockIdx.x) % per_b}; };
+    const int step_b = static_cast<int>(gridDim.x) / per_b, step_r = static_cast<int>(gridDim.x) % per_b;
     auto walk_next = [&](Walk& w) {
-        w.r += gridDim.x;
-        while (w.r >= per_b) { w.r -= per_b; ++w.b; }
+        w.b += step_b;
+        w.r += step_r;
+        if (w.r >= per_b) { w.r -= per_b; ++w.b; }
     };
     auto decode = [&](const Walk& w, int& b, int& qb, int& h, int& start, int& len) {
         b = w.b;
@@ -144,81 +146,92 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
         return qb * BLK < len;
     };
 
+    // The producer and MMA warps walk their loops as whole warps (uniform control flow) and elect one lane to issue:
+    // under `if (lane == 0)` every single-thread instruction gets wrapped in a divergence-safe ELECT loop and the issue
+    // rate of that one thread becomes the bottleneck.
     if (warp == PRODUCER_WARP) {
-        if (lane == 0) {
-            uint32_t q_it = 0, kv_it = 0;
-            Walk w = walk_init();
-            for (int i = blockIdx.x; i < items; i += gridDim.x, walk_next(w)) {
-                int b, qb, h, start, len;
-                if (!decode(w, b, qb, h, start, len)) continue;
-                const uint32_t qs = q_it & 1;
-                mbar_wait(bar_q_empty + 8 * qs, ((q_it >> 1) & 1) ^ 1);
+        uint32_t q_it = 0, kv_it = 0;
+        Walk w = walk_init();
+        for (int i = blockIdx.x; i < items; i += gridDim.x, walk_next(w)) {
+            int b, qb, h, start, len;
+            if (!decode(w, b, qb, h, start, len)) continue;
+            const uint32_t qs = q_it & 1;
+            mbar_wait(bar_q_empty + 8 * qs, ((q_it >> 1) & 1) ^ 1);
+            if (elect_one()) {
                 mbar_arrive_expect_tx(bar_q_full + 8 * qs, TILE);
                 tma_load_2d(smem_q + qs * TILE, &tmap_qkv, h * D, start + qb * BLK, bar_q_full + 8 * qs);
-                ++q_it;
-                const int nkb = (len + BLK - 1) / BLK;
-                for (int kb = 0; kb < nkb; ++kb, ++kv_it) {
-                    const uint32_t s = kv_it & 1;
-                    mbar_wait(bar_kv_empty + 8 * s, ((kv_it >> 1) & 1) ^ 1);
+            }
+            __syncwarp();
+            ++q_it;
+            const int nkb = (len + BLK - 1) / BLK;
+            for (int kb = 0; kb < nkb; ++kb, ++kv_it) {
+                const uint32_t s = kv_it & 1;
+                mbar_wait(bar_kv_empty + 8 * s, ((kv_it >> 1) & 1) ^ 1);
+                if (elect_one()) {
                     mbar_arrive_expect_tx(bar_kv_full + 8 * s, 2 * TILE);
                     tma_load_2d(smem_kv + s * 2 * TILE, &tmap_qkv, p.H + h * D, start + kb * BLK, bar_kv_full + 8 * s);
                     tma_load_2d(smem_kv + s * 2 * TILE + TILE, &tmap_qkv, 2 * p.H + h * D, start + kb * BLK,
                                 bar_kv_full + 8 * s);
                 }
+                __syncwarp();
             }
         }
     } else if (warp == MMA_WARP) {
-        if (lane == 0) {
-            constexpr uint32_t idesc_s = umma_idesc_bf16(BLK, UNIT);
-            constexpr uint32_t idesc_o = umma_idesc_bf16(BLK, D) | (1u << 16);  // B (= V) is MN-major
-            uint32_t q_it = 0, kv_it = 0;
-            uint32_t us = 0;  // units whose S MMA has been issued (buffer us & 1)
-            uint32_t uo = 0;  // units whose P.V MMA has been issued
-            Walk w = walk_init();
-            for (int i = blockIdx.x; i < items; i += gridDim.x, walk_next(w)) {
-                int b, qb, h, start, len;
-                if (!decode(w, b, qb, h, start, len)) continue;
-                const uint32_t qs = q_it & 1;
-                mbar_wait(bar_q_full + 8 * qs, (q_it >> 1) & 1);
-                const uint64_t dq = umma_desc_k<D>(smem_q + qs * TILE);
-                const int nunits = (len + UNIT - 1) / UNIT;  // unit u: keys [u*64, u*64+64); block u/2, half u&1
-                const uint32_t kv0 = kv_it;                 // ring position of this item's first K/V block
+        constexpr uint32_t idesc_s = umma_idesc_bf16(BLK, UNIT);
+        constexpr uint32_t idesc_o = umma_idesc_bf16(BLK, D) | (1u << 16);  // B (= V) is MN-major
+        const uint64_t dq0 = umma_desc_k<D>(smem_q), dk0 = umma_desc_k<D>(smem_kv);
+        const uint64_t dp0 = umma_desc_sw128(smem_p), dv0 = umma_desc_mn<D>(smem_kv + TILE);
+        uint32_t q_it = 0, kv_it = 0;
+        uint32_t us = 0;  // units whose S MMA has been issued (buffer us & 1)
+        uint32_t uo = 0;  // units whose P.V MMA has been issued
+        Walk w = walk_init();
+        for (int i = blockIdx.x; i < items; i += gridDim.x, walk_next(w)) {
+            int b, qb, h, start, len;
+            if (!decode(w, b, qb, h, start, len)) continue;
+            const uint32_t qs = q_it & 1;
+            mbar_wait(bar_q_full + 8 * qs, (q_it >> 1) & 1);
+            const uint64_t dq = dq0 + ((qs * TILE) >> 4);
+            const int nunits = (len + UNIT - 1) / UNIT;  // unit u: keys [u*64, u*64+64); block u/2, half u&1
+            const uint32_t kv0 = kv_it;                 // ring position of this item's first K/V block
 
-                // S_u = Q . K_u^T into S buffer (us & 1)
-                auto issue_s = [&](int u) {
-                    const uint32_t kvi = kv0 + (u >> 1), s = kvi & 1;
-                    if ((u & 1) == 0) mbar_wait(bar_kv_full + 8 * s, (kvi >> 1) & 1);  // first touch of this block
-                    mbar_wait(bar_s_empty + 8 * (us & 1), ((us >> 1) & 1) ^ 1);        // softmax drained this S buffer
-                    tc_fence_after_sync();
-                    const uint64_t dk = umma_desc_k<D>(smem_kv + s * 2 * TILE + (u & 1) * (UNIT * D * 2));
+            // S_u = Q . K_u^T into S buffer (us & 1)
+            auto issue_s = [&](int u) {
+                const uint32_t kvi = kv0 + (u >> 1), s = kvi & 1;
+                if ((u & 1) == 0) mbar_wait(bar_kv_full + 8 * s, (kvi >> 1) & 1);  // first touch of this block
+                mbar_wait(bar_s_empty + 8 * (us & 1), ((us >> 1) & 1) ^ 1);        // softmax drained this S buffer
+                tc_fence_after_sync();
+                if (elect_one()) {
+                    const uint64_t dk = dk0 + ((s * 2 * TILE + (u & 1) * (UNIT * D * 2)) >> 4);
 #pragma unroll
                     for (int k = 0; k < D / 16; ++k)
                         umma_bf16(tmem_base + (us & 1) * UNIT, dq + 2 * k, dk + 2 * k, idesc_s, k > 0 ? 1u : 0u);
                     umma_commit(bar_s_full + 8 * (us & 1));
-                    ++us;
-                };
-                issue_s(0);
-                for (int u = 0; u < nunits; ++u) {
-                    if (u + 1 < nunits) issue_s(u + 1);  // one unit ahead of the softmax
-                    const uint32_t kvi = kv0 + (u >> 1), s = kvi & 1, ob = uo & 1;
-                    mbar_wait(bar_p_full + 8 * ob, (uo >> 1) & 1);         // P_u is in shared memory
-                    mbar_wait(bar_o_empty + 8 * ob, ((uo >> 1) & 1) ^ 1);  // the O buffer has been read
-                    tc_fence_after_sync();
-                    const uint32_t v_smem = smem_kv + s * 2 * TILE + TILE + (u & 1) * (UNIT * D * 2);
-#pragma unroll
-                    for (int k = 0; k < UNIT / 16; ++k) {
-                        const uint64_t dp = umma_desc_sw128(smem_p + ob * L::P_UNIT) + 2 * k;  // 32 B per 16 keys
-                        const uint64_t dv = umma_desc_mn<D>(v_smem + k * 16 * D * 2);           // 16 rows of D*2 B
-                        umma_bf16(tmem_base + O_COL + ob * D, dp, dv, idesc_o, k > 0 ? 1u : 0u);
-                    }
-                    umma_commit(bar_o_full + 8 * ob);
-                    ++uo;
-                    if ((u & 1) == 1 || u == nunits - 1) umma_commit(bar_kv_empty + 8 * s);  // block fully consumed
                 }
-                kv_it += (nunits + 1) >> 1;
-                umma_commit(bar_q_empty + 8 * qs);
-                ++q_it;
+                __syncwarp();
+                ++us;
+            };
+            issue_s(0);
+            for (int u = 0; u < nunits; ++u) {
+                if (u + 1 < nunits) issue_s(u + 1);  // one unit ahead of the softmax
+                const uint32_t kvi = kv0 + (u >> 1), s = kvi & 1, ob = uo & 1;
+                mbar_wait(bar_p_full + 8 * ob, (uo >> 1) & 1);         // P_u is in shared memory
+                mbar_wait(bar_o_empty + 8 * ob, ((uo >> 1) & 1) ^ 1);  // the O buffer has been read
+                tc_fence_after_sync();
+                if (elect_one()) {
+                    const uint64_t dp = dp0 + ((ob * L::P_UNIT) >> 4);
+                    const uint64_t dv = dv0 + ((s * 2 * TILE + (u & 1) * (UNIT * D * 2)) >> 4);
+#pragma unroll
+                    for (int k = 0; k < UNIT / 16; ++k)  // P: 32 B per 16 keys; V: 16 rows of D*2 B
+                        umma_bf16(tmem_base + O_COL + ob * D, dp + 2 * k, dv + ((k * 16 * D * 2) >> 4), idesc_o, k > 0 ? 1u : 0u);
+                    umma_commit(bar_o_full + 8 * ob);
+                    if ((u & 1) == 1 || u == nunits - 1) umma_commit(bar_kv_empty + 8 * s);  // block fully consumed
+                    if (u == nunits - 1) umma_commit(bar_q_empty + 8 * qs);
+                }
+                __syncwarp();
+                ++uo;
             }
+            kv_it += (nunits + 1) >> 1;
+            ++q_it;
         }
     } else if (warp >= SM_WARP0) {
         const int quad = warp & 3;
