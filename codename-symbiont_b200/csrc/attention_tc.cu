@@ -27,6 +27,7 @@
 #include <mutex>
 
 #include "common.cuh"
+#include "tc_helpers.cuh"
 
 namespace b200 {
 
@@ -276,41 +277,47 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
                 tmem_ld_wait();
                 tc_fence_before_sync();
                 mbar_arrive(bar_s_empty + 8 * sb);  // S is in registers: the MMA warp may overwrite the buffer
-                // four independent chains for the row max (a single 64-deep FMNMX chain is pure latency)
-                float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-                if (nvalid == UNIT) {
-#pragma unroll
-                    for (int j = 0; j < UNIT; ++j) mx4[j & 3] = fmaxf(mx4[j & 3], __uint_as_float(v[j]));
-                } else {
+                // Keys past the sentence end become -inf once, up front (exp2 then gives exactly 0), so that everything
+                // below is straight-line code the compiler can interleave freely: 64 independent exp chains.
+                if (nvalid < UNIT) {
 #pragma unroll
                     for (int j = 0; j < UNIT; ++j)
-                        if (j < nvalid) mx4[j & 3] = fmaxf(mx4[j & 3], __uint_as_float(v[j]));
+                        if (j >= nvalid) v[j] = 0xff800000u;  // -inf
                 }
+                // four independent chains for the row max (a single 64-deep FMNMX chain is pure latency)
+                float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+                for (int j = 0; j < UNIT; ++j) mx4[j & 3] = fmaxf(mx4[j & 3], __uint_as_float(v[j]));
                 const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
                 const float m_new = fmaxf(m, mx * p.scale_log2);
                 const float corr = ex2(m - m_new);
                 m = m_new;
-                // p = exp2(s*scale - m), rounded to bf16 into the swizzled K-major tile; row sum (4 chains)
-                float lb4[4] = {0.f, 0.f, 0.f, 0.f};
+                // p = exp2(s*scale - m) (packed-pair FMA), rounded to bf16 into the swizzled K-major tile; row sum in
+                // four packed chains
+                const uint64_t sc2 = pk2(p.scale_log2, p.scale_log2), nm2 = pk2(-m_new, -m_new);
+                uint64_t lb2[4] = {0, 0, 0, 0};
                 const uint32_t prow = smem_p + sb * L::P_UNIT + row * 128;
-                const bool full = nvalid == UNIT;
 #pragma unroll
                 for (int q = 0; q < UNIT / 8; ++q) {
-                    float pj[8];
+                    uint32_t w[4];
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) pj[j] = ex2(fmaf(__uint_as_float(v[q * 8 + j]), p.scale_log2, -m_new));
-                    if (!full) {
-#pragma unroll
-                        for (int j = 0; j < 8; ++j)
-                            if (q * 8 + j >= nvalid) pj[j] = 0.f;
+                    for (int j = 0; j < 4; ++j) {
+                        float a, b;
+                        upk2(fma2(pk2(__uint_as_float(v[q * 8 + 2 * j]), __uint_as_float(v[q * 8 + 2 * j + 1])), sc2, nm2), a, b);
+                        const float pa = ex2(a), pb = ex2(b);
+                        lb2[j] = add2(lb2[j], pk2(pa, pb));
+                        w[j] = pack_bf16x2(pa, pb);
                     }
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) lb4[j & 3] += pj[j];
                     const uint32_t piece = static_cast<uint32_t>(q) ^ (row & 7);
-                    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(prow + (piece << 4)),
-                                 "r"(pack_bf16x2(pj[0], pj[1])), "r"(pack_bf16x2(pj[2], pj[3])),
-                                 "r"(pack_bf16x2(pj[4], pj[5])), "r"(pack_bf16x2(pj[6], pj[7]))
+                    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(prow + (piece << 4)), "r"(w[0]), "r"(w[1]),
+                                 "r"(w[2]), "r"(w[3])
                                  : "memory");
+                }
+                float lb4[4];
+                {
+                    float a, b;
+                    upk2(add2(lb2[0], lb2[1]), a, b); lb4[0] = a; lb4[1] = b;
+                    upk2(add2(lb2[2], lb2[3]), a, b); lb4[2] = a; lb4[3] = b;
                 }
                 const float lb = (lb4[0] + lb4[1]) + (lb4[2] + lb4[3]);
                 fence_proxy_async_smem();
@@ -321,35 +328,19 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
                 corr_prev = corr;
             }
             retire(uc - 1, corr_prev);
-            // finalise: O / l, staged through the (now idle) P buffers so that global stores are row-contiguous
+            // finalise: O / l. Each lane owns one row of D bf16 (64 or 128 contiguous bytes of ctx): whole 32-byte
+            // sectors straight from registers, no staging and no barrier between the softmax warps.
             const float inv = 1.0f / l;
-            constexpr int PITCH = D * 2 + 16;  // bytes; the pad spreads rows over banks
-            const uint32_t orow = smem_p + row * PITCH;
+            if (qb * BLK + row < len) {
+                __nv_bfloat16* dst = p.ctx + static_cast<size_t>(start + qb * BLK + row) * p.H + h * D;
 #pragma unroll
-            for (int q = 0; q < D / 8; ++q)
-                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(orow + q * 16),
-                             "r"(pack_bf16x2(o[q * 8 + 0] * inv, o[q * 8 + 1] * inv)),
-                             "r"(pack_bf16x2(o[q * 8 + 2] * inv, o[q * 8 + 3] * inv)),
-                             "r"(pack_bf16x2(o[q * 8 + 4] * inv, o[q * 8 + 5] * inv)),
-                             "r"(pack_bf16x2(o[q * 8 + 6] * inv, o[q * 8 + 7] * inv))
-                             : "memory");
-            asm volatile("bar.sync 1, %0;" ::"n"(SM_THREADS) : "memory");
-            constexpr int PPR = D / 8;  // 16-byte pieces per row
-            const int t = threadIdx.x - SM_WARP0 * 32;
-            const int q0 = qb * BLK;
+                for (int q = 0; q < D / 16; ++q) {
+                    uint32_t w[8];
 #pragma unroll
-            for (int k = 0; k < PPR; ++k) {
-                const int idx = k * SM_THREADS + t;
-                const int r = idx / PPR, pc = idx % PPR;
-                if (q0 + r < len) {
-                    uint4 val;
-                    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
-                                 : "=r"(val.x), "=r"(val.y), "=r"(val.z), "=r"(val.w)
-                                 : "r"(smem_p + r * PITCH + pc * 16));
-                    *reinterpret_cast<uint4*>(p.ctx + static_cast<size_t>(start + q0 + r) * p.H + h * D + pc * 8) = val;
+                    for (int j = 0; j < 8; ++j) w[j] = pack_bf16x2(o[q * 16 + 2 * j] * inv, o[q * 16 + 2 * j + 1] * inv);
+                    stg_v8(dst + q * 16, w);
                 }
             }
-            asm volatile("bar.sync 1, %0;" ::"n"(SM_THREADS) : "memory");  // staging reads done before the next P writes
         }
     }
 
