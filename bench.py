@@ -119,29 +119,32 @@ def make_lengths(pkg, batch, seq, ragged, seed):
 
 
 def kernel_work(shape, lengths, kind):
-    """Algorithmic FLOPs / bytes of ONE launch of a kernel kind for this batch."""
+    """Algorithmic (FLOPs, HBM bytes) of ONE launch of a kernel kind for this batch. The kernel's
+    roofline is whichever of the two takes longer at the measured peaks."""
     H, I = shape.hidden_size, shape.intermediate_size
     T = float(np.sum(lengths))
     s2 = float(np.sum(np.asarray(lengths, dtype=np.float64) ** 2))
     B = len(lengths)
-    if kind == "gemm_qkv":
-        return 2 * T * 3 * H * H, "flops"
-    if kind == "gemm_attn_out":
-        return 2 * T * H * H, "flops"
-    if kind in ("gemm_ffn1", "gemm_ffn2"):
-        return 2 * T * I * H, "flops"
-    if kind == "ffn_fused":
-        return 4 * T * I * H, "flops"
-    if kind == "attention":
-        return 4 * H * s2, "flops"
+    if kind == "gemm_qkv":  # x (hi) in, qkv out, bf16
+        return 2 * T * 3 * H * H, (2 * H + 6 * H) * T
+    if kind == "gemm_attn_out":  # ctx + (hi, lo) residual in, (hi, lo) out
+        return 2 * T * H * H, (2 * H + 4 * H + 4 * H) * T
+    if kind == "gemm_ffn1":
+        return 2 * T * I * H, (2 * H + 2 * I) * T
+    if kind == "gemm_ffn2":
+        return 2 * T * I * H, (2 * I + 4 * H + 4 * H) * T
+    if kind == "ffn_fused":  # (hi, lo) in, (hi, lo) out; the intermediate stays on chip
+        return 4 * T * I * H, (4 * H + 4 * H) * T
+    if kind == "attention":  # qkv in, ctx out
+        return 4 * H * s2, (6 * H + 2 * H) * T
     if kind == "embed_ln":  # fp32 word row in, (hi, lo) bf16 rows out, ids + type ids + mask
-        return (8 * H + 12) * T, "bytes"
+        return 0.0, (8 * H + 12) * T
     if kind == "add_ln":  # fp32 GEMM output + (hi, lo) residual in, (hi, lo) out
-        return 12 * H * T, "bytes"
+        return 0.0, 12 * H * T
     if kind == "pool":  # (hi, lo) rows in, f32 [B,H] out
-        return 4 * H * T + 4 * T + 4 * H * B, "bytes"
+        return 0.0, 4 * H * T + 4 * T + 4 * H * B
     if kind == "lengths":
-        return 4.0 * B * (T / max(B, 1)) + 8 * B, "bytes"
+        return 0.0, 4.0 * B * (T / max(B, 1)) + 8 * B
     raise KeyError(kind)
 
 
@@ -292,12 +295,14 @@ def run_b200(args, pkg, rank, world, local_rank):
         # work of one full pass of this kind over the batch x how many passes a step makes (calls larger than the
         # workspace are split into several launches per pass; their times add up)
         passes = (2 if kind == "add_ln" else 1) * (shape.num_hidden_layers if kind in per_layer or kind == "add_ln" else 1)
-        work, what = kernel_work(shape, lengths, kind)
+        flops, nbytes = kernel_work(shape, lengths, kind)
         step_ms = v["total_ms"] / prof_steps
-        if what == "flops":
-            ach, peak, unit, bound = work * passes / (step_ms * 1e-3) / 1e12, pk["tf_sustained"], "TFLOP/s", "tensor"
+        t_tensor = flops * passes / (pk["tf_sustained"] * 1e12) * 1e3  # ms this kind needs at the tensor peak
+        t_hbm = nbytes * passes / (pk["hbm_gbs"] * 1e9) * 1e3           # ms at the HBM peak
+        if t_tensor >= t_hbm:
+            ach, peak, unit, bound = flops * passes / (step_ms * 1e-3) / 1e12, pk["tf_sustained"], "TFLOP/s", "tensor"
         else:
-            ach, peak, unit, bound = work * passes / (step_ms * 1e-3) / 1e9, pk["hbm_gbs"], "GB/s", "hbm"
+            ach, peak, unit, bound = nbytes * passes / (step_ms * 1e-3) / 1e9, pk["hbm_gbs"], "GB/s", "hbm"
         kernels[kind] = {"ms_per_launch": round(ms, 4), "launches_per_step": v["launches"] // prof_steps,
                          "share_of_step": round(step_ms / total_ms, 4), "bound": bound,
                          "achieved": round(ach, 2), "peak": peak, "unit": unit, "frac": round(ach / peak, 4)}

@@ -38,4 +38,26 @@ if len(rr) > 2:
                 if w in idx:
                     f.write(f"| {w} | {r[idx[w]]} | {units[idx[w]]} |\n")
             f.write("\n")
+# dram bytes per launch of each kernel kind (default c2 workload) -> profiles/traffic.json, read by bench.py
+import json, os
+kind_of = [("ffn_fused_kernel", "ffn_fused"), ("attention_tc_kernel", "attention"), ("embed_layernorm", "embed_ln"),
+           ("mean_pool", "pool"), ("gemm_tc_kernel<192, 0", "gemm_qkv"), ("gemm_tc_kernel<256, 1", "gemm_ffn1"),
+           ("gemm_tc_kernel<192, 4", "gemm_attn_out")]
+if len(rr) > 2:
+    tj = "profiles/traffic.json"
+    traffic = json.load(open(tj)) if os.path.exists(tj) else {}
+    acc = {}
+    for r in rr[2:]:
+        name = r[idx["Kernel Name"]]
+        for pat, kind in kind_of:
+            if pat in name:
+                scale = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}
+                b = float(r[idx["dram__bytes_read.sum"]]) * scale[units[idx["dram__bytes_read.sum"]]] + \
+                    float(r[idx["dram__bytes_write.sum"]]) * scale[units[idx["dram__bytes_write.sum"]]]
+                acc.setdefault(kind, []).append(b)
+                break
+    for kind, v in acc.items():
+        traffic["c2:" + kind] = round(sum(v) / len(v))
+    traffic["_source"] = f"profiles/{tag}_full.md (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per launch)"
+    json.dump(traffic, open(tj, "w"), indent=1, sort_keys=True)
 print("wrote profiles/%s_*.md" % tag)
