@@ -130,21 +130,34 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
     // so (b, r) is carried along instead of dividing every time; items whose query block lies past the sentence
     // end are empty and skipped by every role alike.
     const int per_b = p.heads * p.q_blocks;
-    struct Walk { int b, r; };
-    auto walk_init = [&]() { return Walk{static_cast<int>(blockIdx.x) / per_b, static_cast<int>(blockIdx.x) % per_b}; };
     const int step_b = static_cast<int>(gridDim.x) / per_b, step_r = static_cast<int>(gridDim.x) % per_b;
-    auto walk_next = [&](Walk& w) {
-        w.b += step_b;
-        w.r += step_r;
-        if (w.r >= per_b) { w.r -= per_b; ++w.b; }
+    // Every role walks the same item sequence. The sentence bounds (two loads from cu_seqlens) of the NEXT item are
+    // fetched while the current one is processed, so their latency is never on an item's critical path.
+    struct Walk {
+        int i, b, r;   // item index, sentence, (query block, head) index inside the sentence
+        int s0, s1;    // cu[b], cu[b + 1] of this item (prefetched)
     };
-    auto decode = [&](const Walk& w, int& b, int& qb, int& h, int& start, int& len) {
+    auto fetch = [&](Walk& w) {
+        if (w.i < items) { w.s0 = __ldg(p.cu + w.b); w.s1 = __ldg(p.cu + w.b + 1); }
+    };
+    auto walk_init = [&]() {
+        Walk w{static_cast<int>(blockIdx.x), static_cast<int>(blockIdx.x) / per_b, static_cast<int>(blockIdx.x) % per_b, 0, 0};
+        fetch(w);
+        return w;
+    };
+    // returns the current item in (b, qb, h, start, len) and advances w to the next one (issuing its loads)
+    auto take = [&](Walk& w, int& b, int& qb, int& h, int& start, int& len) {
         b = w.b;
         qb = w.r / p.heads;
         h = w.r - qb * p.heads;
-        start = p.cu[b];
-        len = p.cu[b + 1] - start;
-        return qb * BLK < len;
+        start = w.s0;
+        len = w.s1 - w.s0;
+        w.i += gridDim.x;
+        w.b += step_b;
+        w.r += step_r;
+        if (w.r >= per_b) { w.r -= per_b; ++w.b; }
+        fetch(w);
+        return qb * BLK < len;  // items whose query block lies past the sentence end are empty: skipped by every role
     };
 
     // The producer and MMA warps walk their loops as whole warps (uniform control flow) and elect one lane to issue:
@@ -153,9 +166,9 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
     if (warp == PRODUCER_WARP) {
         uint32_t q_it = 0, kv_it = 0;
         Walk w = walk_init();
-        for (int i = blockIdx.x; i < items; i += gridDim.x, walk_next(w)) {
+        while (w.i < items) {
             int b, qb, h, start, len;
-            if (!decode(w, b, qb, h, start, len)) continue;
+            if (!take(w, b, qb, h, start, len)) continue;
             const uint32_t qs = q_it & 1;
             mbar_wait(bar_q_empty + 8 * qs, ((q_it >> 1) & 1) ^ 1);
             if (elect_one()) {
@@ -186,9 +199,9 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
         uint32_t us = 0;  // units whose S MMA has been issued (buffer us & 1)
         uint32_t uo = 0;  // units whose P.V MMA has been issued
         Walk w = walk_init();
-        for (int i = blockIdx.x; i < items; i += gridDim.x, walk_next(w)) {
+        while (w.i < items) {
             int b, qb, h, start, len;
-            if (!decode(w, b, qb, h, start, len)) continue;
+            if (!take(w, b, qb, h, start, len)) continue;
             const uint32_t qs = q_it & 1;
             mbar_wait(bar_q_full + 8 * qs, (q_it >> 1) & 1);
             const uint64_t dq = dq0 + ((qs * TILE) >> 4);
@@ -240,9 +253,9 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
         const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
         uint32_t uc = 0;  // units processed so far by this CTA (buffer uc & 1, phase (uc >> 1) & 1)
         Walk w = walk_init();
-        for (int i = blockIdx.x; i < items; i += gridDim.x, walk_next(w)) {
+        while (w.i < items) {
             int b, qb, h, start, len;
-            if (!decode(w, b, qb, h, start, len)) continue;
+            if (!take(w, b, qb, h, start, len)) continue;
             float m = -INFINITY, l = 0.f, corr_prev = 0.f;
             float o[D];
 #pragma unroll

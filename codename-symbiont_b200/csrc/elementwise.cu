@@ -43,19 +43,19 @@ __device__ __forceinline__ float4 load_split(const T* hi, const T* lo, size_t of
 }
 
 // Exact two-pass LayerNorm of one row held across a warp (chunk i of lane l = columns 128 i + 4 l ..+3).
-template <typename T>
-__device__ __forceinline__ void warp_layernorm_store(float4 (&v)[MAX_CHUNKS], int nchunk, int H, int lane,
+template <typename T, int NC>
+__device__ __forceinline__ void warp_layernorm_store(float4 (&v)[NC], int nchunk, int H, int lane,
                                                      const float* __restrict__ gamma,
                                                      const float* __restrict__ beta, float eps, T* out_row,
                                                      T* out_lo_row) {
     float s = 0.f;
 #pragma unroll
-    for (int i = 0; i < MAX_CHUNKS; ++i)
+    for (int i = 0; i < NC; ++i)
         if (i < nchunk) s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
     const float mean = warp_sum(s) / static_cast<float>(H);
     float q = 0.f;
 #pragma unroll
-    for (int i = 0; i < MAX_CHUNKS; ++i)
+    for (int i = 0; i < NC; ++i)
         if (i < nchunk) {
             const float a = v[i].x - mean, b = v[i].y - mean, c = v[i].z - mean, d = v[i].w - mean;
             q += (a * a + b * b) + (c * c + d * d);
@@ -63,7 +63,7 @@ __device__ __forceinline__ void warp_layernorm_store(float4 (&v)[MAX_CHUNKS], in
     const float var = warp_sum(q) / static_cast<float>(H);
     const float rstd = 1.0f / sqrtf(var + eps);
 #pragma unroll
-    for (int i = 0; i < MAX_CHUNKS; ++i)
+    for (int i = 0; i < NC; ++i)
         if (i < nchunk) {
             const int col = i * 128 + lane * 4;
             const float4 g = __ldg(reinterpret_cast<const float4*>(gamma + col));
@@ -140,60 +140,80 @@ __global__ void scan_lengths_kernel(const int* __restrict__ lens, int batch, int
 }
 
 // ---- K1 -------------------------------------------------------------------------------------------
-// One warp per token. PADDED: grid over [batch, seq_len] positions, pad positions exit, the row is
-// written packed at cu[b] + j. Packed: grid over tokens, sentence found by binary search in cu.
-template <typename T, bool PADDED>
-__global__ void embed_layernorm_kernel(const uint32_t* __restrict__ ids, const uint32_t* __restrict__ type_ids,
-                                       const int* __restrict__ cu, int batch, int seq_len, int total_tokens,
-                                       const float* __restrict__ word, const float* __restrict__ pos,
-                                       const float* __restrict__ type, const float* __restrict__ gamma,
-                                       const float* __restrict__ beta, float eps, int H, int vocab,
-                                       int type_vocab, int max_pos, T* __restrict__ out, T* __restrict__ out_lo,
-                                       int* __restrict__ status) {
-    const long long w = static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+// One warp per TOK consecutive token slots. PADDED: slots are [batch, seq_len] positions, pad positions are skipped,
+// the row is written packed at cu[b] + j. Packed: slots are tokens, sentence found by binary search in cu.
+// The work per token is a chain of dependent loads (bounds -> id -> three table rows) followed by a short reduction:
+// all TOK tokens' loads are issued before any of them is consumed, which is what keeps enough bytes in flight.
+template <typename T, bool PADDED, int TOK, int NCH>  // NCH: 128-column chunks a token needs (H <= 128 NCH)
+__global__ void __launch_bounds__(256)
+embed_layernorm_kernel(const uint32_t* __restrict__ ids, const uint32_t* __restrict__ type_ids,
+                       const int* __restrict__ cu, int batch, int seq_len, int total_tokens,
+                       const float* __restrict__ word, const float* __restrict__ pos,
+                       const float* __restrict__ type, const float* __restrict__ gamma,
+                       const float* __restrict__ beta, float eps, int H, int vocab,
+                       int type_vocab, int max_pos, T* __restrict__ out, T* __restrict__ out_lo,
+                       int* __restrict__ status) {
+    const long long w0 = (static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5)) * TOK;
     const int lane = threadIdx.x & 31;
-    long long src, dst;
-    int j;
-    if (PADDED) {
-        if (w >= static_cast<long long>(batch) * seq_len) return;
-        const int b = static_cast<int>(w / seq_len);
-        j = static_cast<int>(w - static_cast<long long>(b) * seq_len);
-        const int start = cu[b];
-        if (j >= cu[b + 1] - start) return;
-        src = w;
-        dst = start + j;
-    } else {
-        if (w >= total_tokens) return;
-        int lo = 0, hi = batch;  // largest b with cu[b] <= w
-        while (hi - lo > 1) {
-            const int mid = (lo + hi) >> 1;
-            if (cu[mid] <= w) lo = mid; else hi = mid;
-        }
-        j = static_cast<int>(w - cu[lo]);
-        src = w;
-        dst = w;
-    }
-    uint32_t id = ids[src], tt = type_ids[src];
-    if (id >= static_cast<uint32_t>(vocab) || tt >= static_cast<uint32_t>(type_vocab) || j >= max_pos) {
-        if (lane == 0) atomicOr(status, 2);
-        id = id >= static_cast<uint32_t>(vocab) ? 0u : id;
-        tt = tt >= static_cast<uint32_t>(type_vocab) ? 0u : tt;
-        j = j >= max_pos ? 0 : j;
-    }
-    const float* wr = word + static_cast<size_t>(id) * H;
-    const float* tr = type + static_cast<size_t>(tt) * H;
-    const float* pr = pos + static_cast<size_t>(j) * H;
-    const int nchunk = H >> 7;
-    float4 v[MAX_CHUNKS];
+    const long long slots = PADDED ? static_cast<long long>(batch) * seq_len : total_tokens;
+    long long src[TOK], dst[TOK];
+    int j[TOK];
+    bool live[TOK];
 #pragma unroll
-    for (int i = 0; i < MAX_CHUNKS; ++i)
-        if (i < nchunk) {
-            const int col = i * 128 + lane * 4;
-            const float4 a = Vec4<float>::load(wr + col), t = Vec4<float>::load(tr + col), p = Vec4<float>::load(pr + col);
-            v[i] = make_float4((a.x + t.x) + p.x, (a.y + t.y) + p.y, (a.z + t.z) + p.z, (a.w + t.w) + p.w);
+    for (int t = 0; t < TOK; ++t) {
+        const long long w = w0 + t;
+        live[t] = w < slots;
+        src[t] = w; dst[t] = w; j[t] = 0;
+        if (!live[t]) continue;
+        if (PADDED) {
+            const int b = static_cast<int>(w / seq_len);
+            j[t] = static_cast<int>(w - static_cast<long long>(b) * seq_len);
+            const int start = __ldg(cu + b);
+            live[t] = j[t] < __ldg(cu + b + 1) - start;
+            dst[t] = start + j[t];
+        } else {
+            int lo = 0, hi = batch;  // largest b with cu[b] <= w
+            while (hi - lo > 1) {
+                const int mid = (lo + hi) >> 1;
+                if (__ldg(cu + mid) <= w) lo = mid; else hi = mid;
+            }
+            j[t] = static_cast<int>(w - __ldg(cu + lo));
         }
-    warp_layernorm_store<T>(v, nchunk, H, lane, gamma, beta, eps, out + static_cast<size_t>(dst) * H,
-                            out_lo ? out_lo + static_cast<size_t>(dst) * H : nullptr);
+    }
+    uint32_t id[TOK], tt[TOK];
+#pragma unroll
+    for (int t = 0; t < TOK; ++t) {
+        id[t] = live[t] ? __ldg(ids + src[t]) : 0u;
+        tt[t] = live[t] ? __ldg(type_ids + src[t]) : 0u;
+    }
+    bool bad = false;
+#pragma unroll
+    for (int t = 0; t < TOK; ++t) {
+        if (id[t] >= static_cast<uint32_t>(vocab)) { bad = true; id[t] = 0u; }
+        if (tt[t] >= static_cast<uint32_t>(type_vocab)) { bad = true; tt[t] = 0u; }
+        if (j[t] >= max_pos) { bad = true; j[t] = 0; }
+    }
+    if (bad && lane == 0) atomicOr(status, 2);
+    const int nchunk = H >> 7;
+    float4 v[TOK][NCH];
+#pragma unroll
+    for (int t = 0; t < TOK; ++t) {
+        const float* wr = word + static_cast<size_t>(id[t]) * H;
+        const float* tr = type + static_cast<size_t>(tt[t]) * H;
+        const float* pr = pos + static_cast<size_t>(j[t]) * H;
+#pragma unroll
+        for (int i = 0; i < NCH; ++i)
+            if (i < nchunk && live[t]) {
+                const int col = i * 128 + lane * 4;
+                const float4 a = Vec4<float>::load(wr + col), ty = Vec4<float>::load(tr + col), p = Vec4<float>::load(pr + col);
+                v[t][i] = make_float4((a.x + ty.x) + p.x, (a.y + ty.y) + p.y, (a.z + ty.z) + p.z, (a.w + ty.w) + p.w);
+            }
+    }
+#pragma unroll
+    for (int t = 0; t < TOK; ++t)
+        if (live[t])
+            warp_layernorm_store<T, NCH>(v[t], nchunk, H, lane, gamma, beta, eps, out + static_cast<size_t>(dst[t]) * H,
+                                    out_lo ? out_lo + static_cast<size_t>(dst[t]) * H : nullptr);
 }
 
 // ---- K4 -------------------------------------------------------------------------------------------
@@ -217,7 +237,7 @@ __global__ void add_layernorm_kernel(const TY* __restrict__ y, const T* __restri
             const float4 a = Vec4<TY>::load(y + r * H + col), b = load_split<T>(residual, residual_lo, r * H + col);
             v[i] = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
         }
-    warp_layernorm_store<T>(v, nchunk, H, lane, gamma, beta, eps, out + r * H, out_lo ? out_lo + r * H : nullptr);
+    warp_layernorm_store<T, MAX_CHUNKS>(v, nchunk, H, lane, gamma, beta, eps, out + r * H, out_lo ? out_lo + r * H : nullptr);
 }
 
 // ---- K5 -------------------------------------------------------------------------------------------
@@ -284,17 +304,24 @@ cudaError_t launch_mask_lengths(const uint32_t* mask, int batch, int seq_len, in
 
 template <typename T>
 cudaError_t launch_embed_layernorm(const EmbedArgs& a, cudaStream_t s) {
-    const long long warps = a.padded ? static_cast<long long>(a.batch) * a.seq_len : a.total_tokens;
-    if (warps <= 0) return cudaSuccess;
-    const unsigned grid = static_cast<unsigned>((warps + 7) / 8);
-    if (a.padded)
-        embed_layernorm_kernel<T, true><<<grid, 256, 0, s>>>(
-            a.ids, a.type_ids, a.cu, a.batch, a.seq_len, a.total_tokens, a.word, a.pos, a.type, a.gamma, a.beta, a.eps,
-            a.H, a.vocab, a.type_vocab, a.max_pos, static_cast<T*>(a.out), static_cast<T*>(a.out_lo), a.status);
-    else
-        embed_layernorm_kernel<T, false><<<grid, 256, 0, s>>>(
-            a.ids, a.type_ids, a.cu, a.batch, a.seq_len, a.total_tokens, a.word, a.pos, a.type, a.gamma, a.beta, a.eps,
-            a.H, a.vocab, a.type_vocab, a.max_pos, static_cast<T*>(a.out), static_cast<T*>(a.out_lo), a.status);
+    const long long slots = a.padded ? static_cast<long long>(a.batch) * a.seq_len : a.total_tokens;
+    if (slots <= 0) return cudaSuccess;
+    // two tokens per warp (measured at H = 384: 0.51 ms with one, 0.41 with two, 0.50 with four per warp)
+    const int nch = a.H <= 256 ? 2 : (a.H <= 384 ? 3 : (a.H <= 512 ? 4 : 8));
+    const int tok = nch <= 4 ? 2 : 1;
+    const unsigned grid = static_cast<unsigned>((slots + 8LL * tok - 1) / (8LL * tok));
+#define B200_EMBED_LAUNCH(PAD, TOK, NCH)                                                                                   \
+    embed_layernorm_kernel<T, PAD, TOK, NCH><<<grid, 256, 0, s>>>(                                                         \
+        a.ids, a.type_ids, a.cu, a.batch, a.seq_len, a.total_tokens, a.word, a.pos, a.type, a.gamma, a.beta, a.eps, a.H,  \
+        a.vocab, a.type_vocab, a.max_pos, static_cast<T*>(a.out), static_cast<T*>(a.out_lo), a.status)
+#define B200_EMBED_PICK(PAD)                                    \
+    if (nch == 2) B200_EMBED_LAUNCH(PAD, 2, 2);                 \
+    else if (nch == 3) B200_EMBED_LAUNCH(PAD, 2, 3);            \
+    else if (nch == 4) B200_EMBED_LAUNCH(PAD, 2, 4);            \
+    else B200_EMBED_LAUNCH(PAD, 1, 8)
+    if (a.padded) { B200_EMBED_PICK(true); } else { B200_EMBED_PICK(false); }
+#undef B200_EMBED_PICK
+#undef B200_EMBED_LAUNCH
     return cudaGetLastError();
 }
 template cudaError_t launch_embed_layernorm<__nv_bfloat16>(const EmbedArgs&, cudaStream_t);
