@@ -191,94 +191,136 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
             }
         }
     } else if (warp == MMA_WARP) {
+        // The units of all of this CTA's items form one stream. S_k = Q.K_k^T is issued one unit ahead of O_k = P_k.V_k
+        // ACROSS item boundaries, so the softmax warps never wait for the tensor pipe at the end of an item: two
+        // cursors walk the same item sequence, `sc` for the S MMAs and `pc` (one unit behind) for the P.V MMAs.
         constexpr uint32_t idesc_s = umma_idesc_bf16(BLK, UNIT);
         constexpr uint32_t idesc_o = umma_idesc_bf16(BLK, D) | (1u << 16);  // B (= V) is MN-major
         const uint64_t dq0 = umma_desc_k<D>(smem_q), dk0 = umma_desc_k<D>(smem_kv);
         const uint64_t dp0 = umma_desc_sw128(smem_p), dv0 = umma_desc_mn<D>(smem_kv + TILE);
-        uint32_t q_it = 0, kv_it = 0;
-        uint32_t us = 0;  // units whose S MMA has been issued (buffer us & 1)
-        uint32_t uo = 0;  // units whose P.V MMA has been issued
-        Walk w = walk_init();
-        while (w.i < items) {
-            int b, qb, h, start, len;
-            if (!take(w, b, qb, h, start, len)) continue;
-            const uint32_t qs = q_it & 1;
-            mbar_wait(bar_q_full + 8 * qs, (q_it >> 1) & 1);
-            const uint64_t dq = dq0 + ((qs * TILE) >> 4);
-            const int nunits = (len + UNIT - 1) / UNIT;  // unit u: keys [u*64, u*64+64); block u/2, half u&1
-            const uint32_t kv0 = kv_it;                 // ring position of this item's first K/V block
-
-            // S_u = Q . K_u^T into S buffer (us & 1)
-            auto issue_s = [&](int u) {
-                const uint32_t kvi = kv0 + (u >> 1), s = kvi & 1;
-                if ((u & 1) == 0) mbar_wait(bar_kv_full + 8 * s, (kvi >> 1) & 1);  // first touch of this block
-                mbar_wait(bar_s_empty + 8 * (us & 1), ((us >> 1) & 1) ^ 1);        // softmax drained this S buffer
-                tc_fence_after_sync();
-                if (elect_one()) {
-                    const uint64_t dk = dk0 + ((s * 2 * TILE + (u & 1) * (UNIT * D * 2)) >> 4);
-#pragma unroll
-                    for (int k = 0; k < D / 16; ++k)
-                        umma_bf16(tmem_base + (us & 1) * UNIT, dq + 2 * k, dk + 2 * k, idesc_s, k > 0 ? 1u : 0u);
-                    umma_commit(bar_s_full + 8 * (us & 1));
-                }
-                __syncwarp();
-                ++us;
-            };
-            issue_s(0);
-            for (int u = 0; u < nunits; ++u) {
-                if (u + 1 < nunits) issue_s(u + 1);  // one unit ahead of the softmax
-                const uint32_t kvi = kv0 + (u >> 1), s = kvi & 1, ob = uo & 1;
-                mbar_wait(bar_p_full + 8 * ob, (uo >> 1) & 1);         // P_u is in shared memory
-                mbar_wait(bar_o_empty + 8 * ob, ((uo >> 1) & 1) ^ 1);  // the O buffer has been read
-                tc_fence_after_sync();
-                if (elect_one()) {
-                    const uint64_t dp = dp0 + ((ob * L::P_UNIT) >> 4);
-                    const uint64_t dv = dv0 + ((s * 2 * TILE + (u & 1) * (UNIT * D * 2)) >> 4);
-#pragma unroll
-                    for (int k = 0; k < UNIT / 16; ++k)  // P: 32 B per 16 keys; V: 16 rows of D*2 B
-                        umma_bf16(tmem_base + O_COL + ob * D, dp + 2 * k, dv + ((k * 16 * D * 2) >> 4), idesc_o, k > 0 ? 1u : 0u);
-                    umma_commit(bar_o_full + 8 * ob);
-                    if ((u & 1) == 1 || u == nunits - 1) umma_commit(bar_kv_empty + 8 * s);  // block fully consumed
-                    if (u == nunits - 1) umma_commit(bar_q_empty + 8 * qs);
-                }
-                __syncwarp();
-                ++uo;
+        struct Cursor {
+            Walk w;
+            bool valid;        // points at a unit
+            int nunits, u;     // units of the current item, current unit (keys [u*64, u*64+64): block u/2, half u&1)
+            uint32_t q_it, kv_it;  // ring positions of the current item's Q tile and first K/V block
+        };
+        auto advance = [&](Cursor& c) {
+            if (c.valid && c.u + 1 < c.nunits) { ++c.u; return true; }
+            if (c.valid) { c.kv_it += (c.nunits + 1) >> 1; ++c.q_it; c.valid = false; }
+            while (c.w.i < items) {
+                int b, qb, h, start, len;
+                if (!take(c.w, b, qb, h, start, len)) continue;
+                c.nunits = (len + UNIT - 1) / UNIT;
+                c.u = 0;
+                c.valid = true;
+                return true;
             }
-            kv_it += (nunits + 1) >> 1;
-            ++q_it;
+            return false;
+        };
+        uint32_t us = 0;  // units whose S MMA has been issued (S buffer us & 1)
+        uint32_t uo = 0;  // units whose P.V MMA has been issued (O buffer uo & 1)
+        auto issue_s = [&](const Cursor& c) {
+            const uint32_t qs = c.q_it & 1, kvi = c.kv_it + (c.u >> 1), s = kvi & 1;
+            if (c.u == 0) mbar_wait(bar_q_full + 8 * qs, (c.q_it >> 1) & 1);       // first touch of this item's Q
+            if ((c.u & 1) == 0) mbar_wait(bar_kv_full + 8 * s, (kvi >> 1) & 1);    // first touch of this K/V block
+            mbar_wait(bar_s_empty + 8 * (us & 1), ((us >> 1) & 1) ^ 1);            // softmax drained this S buffer
+            tc_fence_after_sync();
+            if (elect_one()) {
+                const uint64_t dq = dq0 + ((qs * TILE) >> 4);
+                const uint64_t dk = dk0 + ((s * 2 * TILE + (c.u & 1) * (UNIT * D * 2)) >> 4);
+#pragma unroll
+                for (int k = 0; k < D / 16; ++k)
+                    umma_bf16(tmem_base + (us & 1) * UNIT, dq + 2 * k, dk + 2 * k, idesc_s, k > 0 ? 1u : 0u);
+                umma_commit(bar_s_full + 8 * (us & 1));
+                if (c.u == c.nunits - 1) umma_commit(bar_q_empty + 8 * qs);  // Q is only read by the S MMAs
+            }
+            __syncwarp();
+            ++us;
+        };
+        auto issue_pv = [&](const Cursor& c) {
+            const uint32_t kvi = c.kv_it + (c.u >> 1), s = kvi & 1, ob = uo & 1;
+            mbar_wait(bar_p_full + 8 * ob, (uo >> 1) & 1);         // P_u is in shared memory
+            mbar_wait(bar_o_empty + 8 * ob, ((uo >> 1) & 1) ^ 1);  // the O buffer has been read
+            tc_fence_after_sync();
+            if (elect_one()) {
+                const uint64_t dp = dp0 + ((ob * L::P_UNIT) >> 4);
+                const uint64_t dv = dv0 + ((s * 2 * TILE + (c.u & 1) * (UNIT * D * 2)) >> 4);
+#pragma unroll
+                for (int k = 0; k < UNIT / 16; ++k)  // P: 32 B per 16 keys; V: 16 rows of D*2 B
+                    umma_bf16(tmem_base + O_COL + ob * D, dp + 2 * k, dv + ((k * 16 * D * 2) >> 4), idesc_o, k > 0 ? 1u : 0u);
+                umma_commit(bar_o_full + 8 * ob);
+                if ((c.u & 1) == 1 || c.u == c.nunits - 1) umma_commit(bar_kv_empty + 8 * s);  // block fully consumed
+            }
+            __syncwarp();
+            ++uo;
+        };
+        Cursor sc{walk_init(), false, 0, 0, 0, 0}, pc{walk_init(), false, 0, 0, 0, 0};
+        bool s_more = advance(sc);
+        if (s_more) issue_s(sc);
+        while (advance(pc)) {
+            if (s_more) {
+                s_more = advance(sc);
+                if (s_more) issue_s(sc);
+            }
+            issue_pv(pc);
         }
     } else if (warp >= SM_WARP0) {
         const int quad = warp & 3;
         const int row = quad * 32 + lane;  // query row inside the item = TMEM lane
         const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
         uint32_t uc = 0;  // units processed so far by this CTA (buffer uc & 1, phase (uc >> 1) & 1)
+        float o[D];       // running output of the item being retired
+#pragma unroll
+        for (int j = 0; j < D; ++j) o[j] = 0.f;
+
+        // The previous unit of the stream, whose P.V is still running while this unit's softmax is computed. It is folded
+        // into the running output afterwards; if it was its item's last unit the item is finalised then - i.e. during
+        // the NEXT item's first unit, so the end of an item never waits for the tensor pipe.
+        struct Pending {
+            bool valid, last;
+            uint32_t ur;   // stream index of the unit
+            float corr;    // rescale of the running output before this unit's O is added
+            float l;       // row sum of the item after this unit
+            int start, len, qb, h;
+        } pend{false, false, 0, 0.f, 0.f, 0, 0, 0, 0};
+        auto retire_pending = [&]() {
+            const uint32_t ob = pend.ur & 1;
+            mbar_wait(bar_o_full + 8 * ob, (pend.ur >> 1) & 1);
+            tc_fence_after_sync();
+#pragma unroll
+            for (int c = 0; c < D / 32; ++c) {
+                uint32_t v[32];
+                tmem_ld_32x32(t_lane + O_COL + ob * D + c * 32, v);
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 32; ++j) o[c * 32 + j] = fmaf(o[c * 32 + j], pend.corr, __uint_as_float(v[j]));
+            }
+            tc_fence_before_sync();
+            mbar_arrive(bar_o_empty + 8 * ob);
+            if (pend.last) {
+                // finalise: O / l. Each lane owns one row of D bf16 (64 or 128 contiguous bytes of ctx): whole 32-byte
+                // sectors straight from registers.
+                const float inv = 1.0f / pend.l;
+                if (pend.qb * BLK + row < pend.len) {
+                    __nv_bfloat16* dst = p.ctx + static_cast<size_t>(pend.start + pend.qb * BLK + row) * p.H + pend.h * D;
+#pragma unroll
+                    for (int q = 0; q < D / 16; ++q) {
+                        uint32_t w[8];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) w[j] = pack_bf16x2(o[q * 16 + 2 * j] * inv, o[q * 16 + 2 * j + 1] * inv);
+                        stg_v8(dst + q * 16, w);
+                    }
+                }
+            }
+            pend.valid = false;
+        };
+
         Walk w = walk_init();
         while (w.i < items) {
             int b, qb, h, start, len;
             if (!take(w, b, qb, h, start, len)) continue;
-            float m = -INFINITY, l = 0.f, corr_prev = 0.f;
-            float o[D];
-#pragma unroll
-            for (int j = 0; j < D; ++j) o[j] = 0.f;
+            float m = -INFINITY, l = 0.f;  // the first unit's corr is exp2(-inf) = 0: the previous item's output vanishes
             const int nunits = (len + UNIT - 1) / UNIT;
-
-            // folds unit (uc - 1)'s O into the running output: o = o * corr + O_u
-            auto retire = [&](uint32_t ur, float corr) {
-                const uint32_t ob = ur & 1;
-                mbar_wait(bar_o_full + 8 * ob, (ur >> 1) & 1);
-                tc_fence_after_sync();
-#pragma unroll
-                for (int c = 0; c < D / 32; ++c) {
-                    uint32_t v[32];
-                    tmem_ld_32x32(t_lane + O_COL + ob * D + c * 32, v);
-                    tmem_ld_wait();
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) o[c * 32 + j] = fmaf(o[c * 32 + j], corr, __uint_as_float(v[j]));
-                }
-                tc_fence_before_sync();
-                mbar_arrive(bar_o_empty + 8 * ob);
-            };
-
             for (int u = 0; u < nunits; ++u, ++uc) {
                 const uint32_t sb = uc & 1;
                 const int nvalid = min(UNIT, len - u * UNIT);  // keys of this unit inside the sentence
@@ -312,49 +354,35 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
                 const uint32_t prow = smem_p + sb * L::P_UNIT + row * 128;
 #pragma unroll
                 for (int q = 0; q < UNIT / 8; ++q) {
-                    uint32_t w[4];
+                    uint32_t wd[4];
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
-                        float a, b;
-                        upk2(fma2(pk2(__uint_as_float(v[q * 8 + 2 * j]), __uint_as_float(v[q * 8 + 2 * j + 1])), sc2, nm2), a, b);
-                        const float pa = ex2(a), pb = ex2(b);
+                        float a, bb;
+                        upk2(fma2(pk2(__uint_as_float(v[q * 8 + 2 * j]), __uint_as_float(v[q * 8 + 2 * j + 1])), sc2, nm2), a, bb);
+                        const float pa = ex2(a), pb = ex2(bb);
                         lb2[j] = add2(lb2[j], pk2(pa, pb));
-                        w[j] = pack_bf16x2(pa, pb);
+                        wd[j] = pack_bf16x2(pa, pb);
                     }
                     const uint32_t piece = static_cast<uint32_t>(q) ^ (row & 7);
-                    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(prow + (piece << 4)), "r"(w[0]), "r"(w[1]),
-                                 "r"(w[2]), "r"(w[3])
-                                 : "memory");
+                    sts_v4(prow + (piece << 4), wd[0], wd[1], wd[2], wd[3]);
                 }
-                float lb4[4];
+                float lb;
                 {
-                    float a, b;
-                    upk2(add2(lb2[0], lb2[1]), a, b); lb4[0] = a; lb4[1] = b;
-                    upk2(add2(lb2[2], lb2[3]), a, b); lb4[2] = a; lb4[3] = b;
+                    float a0, a1, a2, a3;
+                    upk2(add2(lb2[0], lb2[1]), a0, a1);
+                    upk2(add2(lb2[2], lb2[3]), a2, a3);
+                    lb = (a0 + a1) + (a2 + a3);
                 }
-                const float lb = (lb4[0] + lb4[1]) + (lb4[2] + lb4[3]);
                 fence_proxy_async_smem();
                 mbar_arrive(bar_p_full + 8 * sb);
                 l = fmaf(l, corr, lb);
-                // while P_u . V_u runs, fold the previous unit's output in
-                if (u > 0) retire(uc - 1, corr_prev);
-                corr_prev = corr;
-            }
-            retire(uc - 1, corr_prev);
-            // finalise: O / l. Each lane owns one row of D bf16 (64 or 128 contiguous bytes of ctx): whole 32-byte
-            // sectors straight from registers, no staging and no barrier between the softmax warps.
-            const float inv = 1.0f / l;
-            if (qb * BLK + row < len) {
-                __nv_bfloat16* dst = p.ctx + static_cast<size_t>(start + qb * BLK + row) * p.H + h * D;
-#pragma unroll
-                for (int q = 0; q < D / 16; ++q) {
-                    uint32_t w[8];
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) w[j] = pack_bf16x2(o[q * 16 + 2 * j] * inv, o[q * 16 + 2 * j + 1] * inv);
-                    stg_v8(dst + q * 16, w);
-                }
+                // while P_u . V_u runs, fold the previous unit of the stream in (and finalise its item if it ended there)
+                if (pend.valid) retire_pending();
+                pend.valid = true; pend.last = u == nunits - 1; pend.ur = uc; pend.corr = corr; pend.l = l;
+                pend.start = start; pend.len = len; pend.qb = qb; pend.h = h;
             }
         }
+        if (pend.valid) retire_pending();
     }
 
     tc_fence_before_sync();
