@@ -63,13 +63,11 @@ struct FfnCfg {
     static constexpr int OFF_AUX = OFF_W2 + S2N * W2_BLK;
     static constexpr int AUX = 1024 + 2 * BM * 8;     // barriers + tmem slot, LayerNorm partial statistics
     static constexpr int BYTES = OFF_AUX + AUX;
+    static constexpr int SCRATCH = OFF_AUX - OFF_H;   // h + rings: per-warp scratch of the final epilogue
     static constexpr int HALF = H / 2;                // output columns per epilogue warp
     static constexpr int NCH = HALF / CHUNK;
     static_assert(H % 128 == 0 && H <= 384, "fused FFN needs the OUT accumulator (H columns) next to S1 (128) in TMEM");
-    // final-epilogue scratch (section "final" below): residual-lo ring in the W1 ring, constants in the W2 ring
-    static constexpr int LO_SLOTS = 3;
-    static_assert(S1N * W1_BLK >= FF_EPI_WARPS * LO_SLOTS * CHUNK_BF16, "residual-lo ring does not fit the W1 ring");
-    static_assert(S2N * W2_BLK >= 3 * H * 4, "constants do not fit the W2 ring");
+    static_assert(SCRATCH >= FF_EPI_WARPS * 6 * CHUNK_BF16 + 3 * H * 4, "final epilogue scratch does not fit");
     static_assert(BYTES <= SMEM_LIMIT, "shared memory budget exceeded");
     static_assert(W1_BLK % 1024 == 0 && W2_BLK % 1024 == 0 && (UN2 / 2) % 8 == 0, "swizzle atoms must stay 1024-byte aligned");
 };
@@ -81,17 +79,18 @@ struct FfnDev {
     const float *b1, *b2, *gamma, *beta;
     float eps;
     int has_lo;
-    __nv_bfloat16 *out, *out_lo;
 };
 
 template <int H>
 __global__ void __launch_bounds__(FF_THREADS, 1)
 ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w1,
-                 const __grid_constant__ CUtensorMap tmap_w2, const __grid_constant__ CUtensorMap tmap_r_lo,
-                 const __grid_constant__ CUtensorMap tmap_lo_pf, const FfnDev p) {
+                 const __grid_constant__ CUtensorMap tmap_w2, const __grid_constant__ CUtensorMap tmap_r,
+                 const __grid_constant__ CUtensorMap tmap_r_lo, const __grid_constant__ CUtensorMap tmap_lo_pf,
+                 const __grid_constant__ CUtensorMap tmap_c,
+                 const __grid_constant__ CUtensorMap tmap_c_lo, const FfnDev p) {
     using C = FfnCfg<H>;
     constexpr int KB1 = C::KB1, UN2 = C::UN2, W1_BLK = C::W1_BLK, W2_BLK = C::W2_BLK, S1N = C::S1N, S2N = C::S2N;
-    constexpr int R1 = C::R1, R2 = C::R2, NB2 = C::NB2, LO_SLOTS = C::LO_SLOTS;
+    constexpr int R1 = C::R1, R2 = C::R2, NB2 = C::NB2;
     constexpr uint16_t BOTH = 3;  // multicast mask: both CTAs of the pair
     constexpr int HALF = C::HALF, NCH = C::NCH;
     constexpr int OUT_COL = IC;  // OUT accumulator starts after the 128 S1 columns
@@ -107,7 +106,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     const uint32_t bar_w2_full = aux + 144, bar_w2_empty = aux + 208;  // <= 8 each
     const uint32_t bar_s1_full = aux + 272, bar_s1_empty = aux + 280, bar_h_full = aux + 288, bar_h_empty = aux + 296;
     const uint32_t bar_out_full = aux + 304, bar_out_empty = aux + 312, bar_epi_done = aux + 320;
-    const uint32_t bar_res = aux + 384;   // FF_EPI_WARPS x LO_SLOTS
+    const uint32_t bar_res = aux + 384;   // FF_EPI_WARPS x 4
     const uint32_t tmem_slot = aux + 768;
     volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(aux_ptr + 768);
     float2* ln_part = reinterpret_cast<float2*>(aux_ptr + 1024);
@@ -142,7 +141,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         mbar_init(bar_h_full, 2 * FF_EPI_WARPS); mbar_init(bar_h_empty, 1);
         mbar_init(bar_out_full, 1); mbar_init(bar_out_empty, 2 * FF_EPI_WARPS);
         mbar_init(bar_epi_done, FF_EPI_THREADS);
-        for (int s = 0; s < LO_SLOTS * FF_EPI_WARPS; ++s) mbar_init(bar_res + 8 * s, 1);
+        for (int s = 0; s < 4 * FF_EPI_WARPS; ++s) mbar_init(bar_res + 8 * s, 1);
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc_cg2(tmem_slot, 512);
@@ -278,21 +277,20 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         const int quad = warp & 3, half = ew >> 2;
         const int row_in_tile = quad * 32 + lane;
         const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
-        // Final-epilogue scratch of this warp, all inside regions that are idle by then:
-        //   residual-lo ring (LO_SLOTS x 2 KB) in the W1 ring - idle once the tile's last GEMM1 has completed, so the
-        //                                                        first loads go out one chunk before the final phase
-        //   b2 | gamma | beta (fp32) in the W2 ring
-        const uint32_t lo_ring = smem_w1 + ew * (LO_SLOTS * CHUNK_BF16);
-        const uint32_t const_s = smem_w2;
+        // final-epilogue scratch of this warp inside the (then idle) h / ring region: 4-slot residual-lo ring and two
+        // output staging buffers
+        const uint32_t my_smem = smem_h + ew * (6 * CHUNK_BF16);
+        const uint32_t out_buf = my_smem + 4 * CHUNK_BF16;
+        const uint32_t const_s = smem_h + FF_EPI_WARPS * (6 * CHUNK_BF16);  // b2 | gamma | beta, fp32 (final epilogue)
         uint32_t chunk_it = 0, tile_it = 0, ld_issued = 0, ld_used = 0;
 
-        // residual: the hi half is the a tile itself (still in shared memory); the lo half comes through the ring
+        // residual: the hi half is the a tile itself (still in shared memory); the lo half comes through a 4-slot ring
         auto issue_lo = [&](int tile, int c) {
             if (lane == 0) {
-                const uint32_t s = ld_issued % LO_SLOTS;
-                const uint32_t bar = bar_res + 8 * (LO_SLOTS * ew + s);
+                const uint32_t s = ld_issued & 3;
+                const uint32_t bar = bar_res + 8 * (4 * ew + s);
                 mbar_arrive_expect_tx(bar, CHUNK_BF16);
-                tma_load_2d(lo_ring + s * CHUNK_BF16, &tmap_r_lo, half * HALF + c * CHUNK, tile * BM + quad * 32, bar);
+                tma_load_2d(my_smem + s * CHUNK_BF16, &tmap_r_lo, half * HALF + c * CHUNK, tile * BM + quad * 32, bar);
             }
             ++ld_issued;
         };
@@ -312,10 +310,6 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 }
                 mbar_wait(bar_s1_full, chunk_it & 1);
                 tc_fence_after_sync();
-                if (ic == NC - 1 && p.has_lo) {  // the last GEMM1 is done: the W1 ring is idle, start the residual-lo loads
-#pragma unroll
-                    for (int c = 0; c < (NCH < LO_SLOTS ? NCH : LO_SLOTS); ++c) issue_lo(t, c);
-                }
                 uint32_t v[64];  // this thread's row, S1 columns half*64 .. +63
                 tmem_ld_32x32(t_lane + half * 64, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
                 tmem_ld_32x32(t_lane + half * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
@@ -348,6 +342,10 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             // ---- final: x' = LayerNorm(OUT + b2 + a) -> (hi, lo) ----
             mbar_wait(bar_out_full, tile_it & 1);  // every MMA of this tile has completed: h and the rings are idle
             tc_fence_after_sync();
+            if (p.has_lo) {
+#pragma unroll
+                for (int c = 0; c < (NCH < 4 ? NCH : 4); ++c) issue_lo(t, c);
+            }
             // b2, gamma, beta -> scratch behind the per-warp areas, read back with broadcast LDS in the loops
             for (int i = threadIdx.x - FF_EPI_WARP0 * 32; i < 3 * H; i += FF_EPI_THREADS) {
                 const float* src = i < H ? p.b2 + i : (i < 2 * H ? p.gamma + (i - H) : p.beta + (i - 2 * H));
@@ -366,15 +364,14 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     uint32_t hi_addr[4], lo_addr[4];
                     // a tile: k-block col0 / 64, 128-byte rows, SWIZZLE_128B; lo slot: 64-byte rows, SWIZZLE_64B
                     const uint32_t arow = smem_a + (col0 / BK) * BLK16 + row_in_tile * 128;
-                    const uint32_t ls = ld_used % LO_SLOTS;
-                    const uint32_t lrow = lo_ring + ls * CHUNK_BF16 + lane * 64;
+                    const uint32_t lrow = my_smem + (ld_used & 3) * CHUNK_BF16 + lane * 64;
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
                         hi_addr[q] = arow + ((((col0 % BK) / 8 + q) ^ (row_in_tile & 7)) << 4);
                         lo_addr[q] = lrow + ((q ^ ((lane >> 1) & 3)) << 4);
                     }
                     if (p.has_lo) {
-                        mbar_wait(bar_res + 8 * (LO_SLOTS * ew + ls), (ld_used / LO_SLOTS) & 1);
+                        mbar_wait(bar_res + 8 * (4 * ew + (ld_used & 3)), (ld_used >> 2) & 1);
                         ++ld_used;
                     }
                     tmem_ld_wait();
@@ -382,7 +379,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     ln_accumulate_chunk(v[c & 1], const_s + col0 * 4, hi_addr, lo_addr, p.has_lo != 0, sum2, sq2);
                     tmem_st_32x32(taddr + c * CHUNK, v[c & 1]);
                     __syncwarp();
-                    if (p.has_lo && c + LO_SLOTS < NCH) issue_lo(t, c + LO_SLOTS);
+                    if (p.has_lo && c + 4 < NCH) issue_lo(t, c + 4);
                 }
             }
             if (lane == 0) mbar_arrive(bar_a_empty);  // this warp's residual rows have been read from the a tile
@@ -416,25 +413,27 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     const int col0 = half * HALF + c * CHUNK;
                     uint32_t hi[16], lo[16];
                     ln_normalize_chunk(x[c & 1], mean, rstd, const_s + (H + col0) * 4, const_s + (2 * H + col0) * 4, hi, lo);
-                    // each lane owns 64 contiguous bytes of its row in both outputs: whole 32-byte sectors straight from
-                    // registers (this phase runs with the tensor pipe idle, so store latency, not bandwidth, is what counts)
-                    const int grow = row0 + lane;
-                    if (grow < p.m) {
-                        __nv_bfloat16* dh = p.out + static_cast<size_t>(grow) * H + col0;
-                        stg_v8(dh, hi);
-                        stg_v8(dh + 16, hi + 8);
-                        if (p.has_lo) {
-                            __nv_bfloat16* dl = p.out_lo + static_cast<size_t>(grow) * H + col0;
-                            stg_v8(dl, lo);
-                            stg_v8(dl + 16, lo + 8);
-                        }
+                    const uint32_t buf_hi = out_buf, buf_lo = out_buf + CHUNK_BF16;
+                    if (lane == 0) tma_store_wait_read<0>();
+                    __syncwarp();
+                    stage_words_bf16(buf_hi, lane, hi);
+                    if (p.has_lo) stage_words_bf16(buf_lo, lane, lo);
+                    fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0) {
+                        tma_store_2d(&tmap_c, buf_hi, col0, row0);
+                        if (p.has_lo) tma_store_2d(&tmap_c_lo, buf_lo, col0, row0);
+                        tma_store_commit();
                     }
                 }
             }
-            // scratch (the rings) may be refilled once every warp is done with it; also protects ln_part
-            asm volatile("bar.sync 1, %0;" ::"n"(FF_EPI_THREADS) : "memory");
+            // scratch (h + rings) may be refilled once the TMA stores have read their staging buffers
+            if (lane == 0) tma_store_wait_read<0>();
+            __syncwarp();
+            asm volatile("bar.sync 1, %0;" ::"n"(FF_EPI_THREADS) : "memory");  // also protects ln_part
             mbar_arrive(bar_epi_done);
         }
+        if (lane == 0) tma_store_wait<0>();
     }
 
     tc_fence_before_sync();
@@ -449,13 +448,18 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 template <int H>
 cudaError_t launch_ffn(const FfnFusedArgs& a, cudaStream_t stream, int num_sms) {
     using C = FfnCfg<H>;
-    alignas(64) CUtensorMap ta, tw1, tw2, trl, tlp;
+    alignas(64) CUtensorMap ta, tw1, tw2, tr, trl, tlp, tc, tcl;
     if (!make_tmap(&ta, a.a, a.m, H, BK, BM, false, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
     if (!make_tmap(&tw1, a.w1, a.inter, H, BK, IC / 2, false, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
     if (!make_tmap(&tw2, a.w2, H, a.inter, BK, C::UN2 / 2, false, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
-    trl = ta; tlp = ta;  // residual low half: per-warp 32 x 32 chunks (ring) and whole k-blocks (L2 prefetch)
+    if (!make_tmap(&tr, a.a, a.m, H, CHUNK, 32, false, CU_TENSOR_MAP_SWIZZLE_64B)) return cudaErrorInvalidValue;
+    trl = tr;
     if (a.a_lo && !make_tmap(&trl, a.a_lo, a.m, H, CHUNK, 32, false, CU_TENSOR_MAP_SWIZZLE_64B)) return cudaErrorInvalidValue;
+    tlp = ta;
     if (a.a_lo && !make_tmap(&tlp, a.a_lo, a.m, H, BK, BM, false, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
+    if (!make_tmap(&tc, a.out, a.m, H, CHUNK, 32, false, CU_TENSOR_MAP_SWIZZLE_64B)) return cudaErrorInvalidValue;
+    tcl = tc;
+    if (a.out_lo && !make_tmap(&tcl, a.out_lo, a.m, H, CHUNK, 32, false, CU_TENSOR_MAP_SWIZZLE_64B)) return cudaErrorInvalidValue;
     auto kern = ffn_fused_kernel<H>;
     static bool attr_set = false;
     if (!attr_set) {
@@ -466,7 +470,6 @@ cudaError_t launch_ffn(const FfnFusedArgs& a, cudaStream_t stream, int num_sms) 
     FfnDev p;
     p.m = a.m; p.d_rows = a.d_rows; p.inter = a.inter; p.b1 = a.b1; p.b2 = a.b2; p.gamma = a.gamma; p.beta = a.beta;
     p.eps = a.eps; p.has_lo = (a.a_lo != nullptr && a.out_lo != nullptr) ? 1 : 0;
-    p.out = static_cast<__nv_bfloat16*>(a.out); p.out_lo = static_cast<__nv_bfloat16*>(a.out_lo);
     const int pairs = ((a.m + BM - 1) / BM + 1) / 2;
     cudaLaunchConfig_t cfg{};
     cfg.blockDim = dim3(FF_THREADS);
@@ -489,7 +492,7 @@ cudaError_t launch_ffn(const FfnFusedArgs& a, cudaStream_t stream, int num_sms) 
     const int grid = 2 * (pairs < max_pairs ? pairs : max_pairs);
     if (grid <= 0) return cudaSuccess;
     cfg.gridDim = dim3(grid);
-    return cudaLaunchKernelEx(&cfg, kern, ta, tw1, tw2, trl, tlp, p);
+    return cudaLaunchKernelEx(&cfg, kern, ta, tw1, tw2, tr, trl, tlp, tc, tcl, p);
 }
 
 }  // namespace
