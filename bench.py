@@ -135,6 +135,8 @@ def kernel_work(shape, lengths, kind):
         return 2 * T * I * H, (2 * I + 4 * H + 4 * H) * T
     if kind == "ffn_fused":  # (hi, lo) in, (hi, lo) out; the intermediate stays on chip
         return 4 * T * I * H, (4 * H + 4 * H) * T
+    if kind == "qkv_attention":  # x (hi) in, ctx out; q, k, v stay on chip
+        return 2 * T * 3 * H * H + 4 * H * s2, (2 * H + 2 * H) * T
     if kind == "attention":  # qkv in, ctx out
         return 4 * H * s2, (6 * H + 2 * H) * T
     if kind == "embed_ln":  # fp32 word row in, (hi, lo) bf16 rows out, ids + type ids + mask
@@ -287,7 +289,7 @@ def run_b200(args, pkg, rank, world, local_rank):
     emb.profile(False)
     pk = peaks()
     kernels, total_ms = {}, sum(v["total_ms"] for v in stats.values()) / prof_steps
-    per_layer = {"gemm_qkv", "attention", "gemm_attn_out", "gemm_ffn1", "gemm_ffn2", "ffn_fused"}
+    per_layer = {"gemm_qkv", "attention", "gemm_attn_out", "gemm_ffn1", "gemm_ffn2", "ffn_fused", "qkv_attention"}
     for kind, v in stats.items():
         if v["launches"] == 0:
             continue

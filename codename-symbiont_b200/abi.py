@@ -25,7 +25,7 @@ FLAG_NORMALIZE = 1
 FLAG_FP32 = 2
 ERR_NAMES = {0: "OK", -1: "INVALID_ARG", -2: "CUDA", -3: "OOM", -4: "UNSUPPORTED_SHAPE", -5: "NO_DEVICE", -6: "IO"}
 KIND_NAMES = ["lengths", "embed_ln", "gemm_qkv", "attention", "gemm_attn_out", "gemm_ffn1", "gemm_ffn2", "add_ln",
-              "pool", "ffn_fused"]
+              "pool", "ffn_fused", "qkv_attention"]
 
 
 class B200EmbedError(RuntimeError):
@@ -69,6 +69,7 @@ _SIGNATURES = {
     "b200_op_ffn": (C.c_int32, [_P, C.c_int32, _P, _P, C.c_int32, _P, _P, _P]),
     "b200_op_linear_noalloc": (C.c_int32, [_P, C.c_int32, C.c_int32, _P, _P, _P, C.c_int32, C.c_int32, _P, _P, _P]),
     "b200_op_attention": (C.c_int32, [_P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P, _P]),
+    "b200_op_qkv_attention": (C.c_int32, [_P, C.c_int32, _P, _P, C.c_int32, C.c_int32, C.c_int32, _P, _P]),
     "b200_op_add_layernorm": (C.c_int32, [_P, C.c_int32, C.c_int32, _P, C.c_int32, _P, _P, C.c_int32, C.c_int32, _P, _P,
                                           _P]),
     "b200_op_mean_pool": (C.c_int32, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, _P, _P]),
@@ -269,6 +270,9 @@ class Embedder:
 
     def op_attention(self, d_qkv, d_cu, batch, rows, max_seqlen, dtype, d_ctx, stream=0):
         _check(self.lib.b200_op_attention(self.h, d_qkv, d_cu, batch, rows, max_seqlen, dtype, d_ctx, stream or None))
+
+    def op_qkv_attention(self, layer, d_x, d_cu, batch, rows, max_seqlen, d_ctx, stream=0):
+        _check(self.lib.b200_op_qkv_attention(self.h, layer, d_x, d_cu, batch, rows, max_seqlen, d_ctx, stream or None))
 
     def op_add_layernorm(self, layer, which, d_y, y_is_f32, d_residual, rows, dtype, d_out, d_residual_lo=0,
                          d_out_lo=0, stream=0):

@@ -111,6 +111,7 @@ struct b200_embed {
     bool gemm_pair = true;   // plain bf16 GEMMs as CTA pairs (one cta_group::2 MMA per pair); B200_EMBED_GEMM_PAIR=0 for A/B
     bool ffn_fused = false;  // K2f replaces the FFN1 / FFN2 GEMM pair: on whenever it supports the shape (hidden 128 / 256 /
                              // 384, erf-GELU); B200_EMBED_FFN_FUSED=0 for A/B
+    bool qkv_attn = false;   // K23 replaces the QKV GEMM + attention pair (off until B200_EMBED_QKV_ATTN=1 while it is being tuned)
     bool attn_mma = false;  // B200_EMBED_ATTENTION=mma selects the mma.sync attention kernel (A/B checks)
     // weights
     float* arena32 = nullptr;
@@ -383,14 +384,21 @@ int run_chunk(b200_embed* h, Context& c, cudaStream_t s, const Job& j) {
             bf16 *x = static_cast<bf16*>(w.x), *qkv = static_cast<bf16*>(w.qkv), *ctx = static_cast<bf16*>(w.ctx),
                  *a = static_cast<bf16*>(w.a), *inter = static_cast<bf16*>(w.inter);
             bf16 *x_lo = static_cast<bf16*>(w.x_lo), *a_lo = static_cast<bf16*>(w.a_lo);
-            rc = gemm16(h, c, s, B200_EMBED_KIND_GEMM_QKV, x, lw.qkv_w16, lw.qkv_b, rows, d_rows, 3 * H, H,
-                        b200::EPI_BIAS, h->bn_qkv, nullptr, nullptr, nullptr, nullptr, qkv, nullptr, 0);
-            if (rc) return rc;
-            CU_TRY(timed(h, c, s, B200_EMBED_KIND_ATTENTION, 1, [&] {
-                return h->attn_mma ? b200::launch_attention_bf16(qkv, cu, j.batch, j.seq_len, h->heads, h->D, ctx, s)
-                                   : b200::launch_attention_tc(qkv, cu, rows, j.batch, j.seq_len, h->heads, h->D, ctx,
-                                                               h->num_sms, s);
-            }));
+            if (h->qkv_attn && b200::qkv_attention_supported(H, h->heads, j.seq_len)) {
+                CU_TRY(timed(h, c, s, B200_EMBED_KIND_QKV_ATTN, 1, [&] {
+                    return b200::launch_qkv_attention(x, lw.qkv_w16, lw.qkv_b, cu, rows, j.batch, j.seq_len, H, h->heads, ctx,
+                                                      h->num_sms, s);
+                }));
+            } else {
+                rc = gemm16(h, c, s, B200_EMBED_KIND_GEMM_QKV, x, lw.qkv_w16, lw.qkv_b, rows, d_rows, 3 * H, H,
+                            b200::EPI_BIAS, h->bn_qkv, nullptr, nullptr, nullptr, nullptr, qkv, nullptr, 0);
+                if (rc) return rc;
+                CU_TRY(timed(h, c, s, B200_EMBED_KIND_ATTENTION, 1, [&] {
+                    return h->attn_mma ? b200::launch_attention_bf16(qkv, cu, j.batch, j.seq_len, h->heads, h->D, ctx, s)
+                                       : b200::launch_attention_tc(qkv, cu, rows, j.batch, j.seq_len, h->heads, h->D, ctx,
+                                                                   h->num_sms, s);
+                }));
+            }
             if (h->fuse_ln) {
                 rc = gemm16(h, c, s, B200_EMBED_KIND_GEMM_AO, ctx, lw.ao_w16, lw.ao_b, rows, d_rows, H, H,
                             b200::EPI_RES_LN, h->bn_ln, x, x_lo, lw.ao_g, lw.ao_be, a, a_lo, 0);
@@ -552,6 +560,7 @@ int32_t b200_embed_create(const b200_embed_config* cfg, const char* path, uint64
     h->ffn_fused = h->fuse_ln && b200::ffn_fused_supported(H, I, cfg->hidden_act);
     if (const char* v = getenv("B200_EMBED_FFN_FUSED")) h->ffn_fused = h->ffn_fused && std::string(v) != "0";
     if (const char* v = getenv("B200_EMBED_ATTENTION")) h->attn_mma = std::string(v) == "mma";
+    if (const char* v = getenv("B200_EMBED_QKV_ATTN")) h->qkv_attn = std::string(v) == "1";
     if (const char* v = getenv("B200_EMBED_GEMM_PAIR")) h->gemm_pair = std::string(v) != "0";
     h->bn_qkv = b200::gemm_tc_pick_block_n(3 * H, b200::EPI_BIAS);
     h->bn_ffn1 = b200::gemm_tc_pick_block_n(I, h->act_epi);
@@ -982,6 +991,19 @@ int32_t b200_op_attention(b200_embed* h, const void* qkv, const int32_t* cu, int
                                                             h->D, static_cast<bf16*>(ctx), s)
                               : b200::launch_attention_tc(static_cast<const bf16*>(qkv), cu, rows, batch, max_seqlen, h->heads,
                                                           h->D, static_cast<bf16*>(ctx), h->num_sms, s));
+    return B200_EMBED_OK;
+}
+
+int32_t b200_op_qkv_attention(b200_embed* h, int32_t layer, const void* x, const int32_t* cu, int32_t batch, int32_t rows,
+                              int32_t max_seqlen, void* ctx, void* stream) {
+    if (!h || !x || !cu || !ctx || layer < 0 || layer >= h->L) return fail(B200_EMBED_ERR_INVALID_ARG, "bad argument");
+    if (!b200::qkv_attention_supported(h->H, h->heads, max_seqlen))
+        return fail(B200_EMBED_ERR_UNSUPPORTED_SHAPE, "fused QKV + attention: hidden 128/256/384, head_dim 32, seq <= 128");
+    DeviceGuard guard(h->device);
+    const LayerW& w = h->layers[layer];
+    h->launches.fetch_add(1);
+    CU_TRY(b200::launch_qkv_attention(static_cast<const bf16*>(x), w.qkv_w16, w.qkv_b, cu, rows, batch, max_seqlen, h->H,
+                                      h->heads, static_cast<bf16*>(ctx), h->num_sms, static_cast<cudaStream_t>(stream)));
     return B200_EMBED_OK;
 }
 

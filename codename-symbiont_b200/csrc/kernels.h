@@ -44,6 +44,13 @@ cudaError_t launch_attention_bf16(const __nv_bfloat16* qkv, const int* cu, int b
 cudaError_t launch_attention_tc(const __nv_bfloat16* qkv, const int* cu, int rows_cap, int batch, int max_seqlen,
                                 int heads, int head_dim, __nv_bfloat16* ctx, int num_sms, cudaStream_t s);
 
+// K23 (qkv_attention.cu): Q/K/V projection + attention of whole sentences in one kernel: ctx from x (hi) directly, the
+// packed qkv tensor never exists. hidden 128 / 256 / 384 with head_dim 32, sentences of at most 128 tokens.
+bool qkv_attention_supported(int hidden, int heads, int max_seqlen);
+cudaError_t launch_qkv_attention(const __nv_bfloat16* x, const __nv_bfloat16* wqkv, const float* bqkv, const int* cu,
+                                 int rows_cap, int batch, int max_seqlen, int hidden, int heads, __nv_bfloat16* ctx,
+                                 int num_sms, cudaStream_t s);
+
 // K2f (ffn_fused.cu): x' = LayerNorm(gelu(a.W1^T + b1).W2^T + b2 + a) in one kernel; hidden 128 / 256 / 384, erf-GELU.
 struct FfnFusedArgs {
     const void* a;       // [m, hidden] bf16: GEMM operand and high half of the residual

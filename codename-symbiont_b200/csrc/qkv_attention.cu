@@ -1,0 +1,475 @@
+// K23: Q/K/V projection + self-attention of one sentence in one kernel (hidden <= 384, head_dim 32, sentences of at
+// most 128 tokens):
+//
+//     ctx[s, h*d:(h+1)*d] = softmax(q_h . k_h^T / sqrt(d) + mask) . v_h,   [q_h | k_h | v_h] = x_s . Wqkv_h^T + bqkv_h
+//
+// Replaces candle bert.rs BertSelfAttention::forward as a whole (query / key / value Linear, scores, softmax, .v, head
+// merge; called from /root/reference/services/preprocessing_service/src/embedding_generator.rs:198). Run as the K2 QKV
+// GEMM followed by K3 the packed [tokens, 3H] qkv tensor costs an HBM write and a read (2.4 GB per layer at c2) and the
+// GEMM is bound by exactly that write; here q, k, v never leave the SM.
+//
+// Work item = sentence. A persistent CTA (one per SM) keeps the sentence's activation tile x[128, H] resident in
+// shared memory (rows past the sentence end belong to the next sentence or are zero-filled: they are computed and
+// never used) and walks its heads; the heads of all of the CTA's sentences form one stream g = 0, 1, 2, ...:
+//   warp 0      TMA producer: the x tile once per sentence; per head 6 blocks of Wqkv rows {h*d.., H + h*d.., 2H + h*d..}
+//               x 64 columns (three 4 KB boxes = one 96-row K-major B operand) through a 3-slot ring
+//   warp 1      MMA issuer (whole warp walks the schedule, one elected lane issues):
+//                 G(g): ACC[g & 1] = x . Wqkv_h^T           128 x 96 x H, fp32 in TMEM, two heads ahead
+//                 S(g, u) = Q . K_u^T                       128 x 64 x d per unit u of 64 keys
+//                 O(g, u) = P_u . V_u                       128 x d x 64
+//   warp 2      TMEM allocator (512 columns: 2 x 128 ACC, 2 x 64 S, 2 x 32 O)
+//   warps 4-7   convert: ACC + bias -> bf16 Q / K / V tiles in shared memory (two buffers), in the layouts K3 gets from
+//               TMA (64-byte rows, SWIZZLE_64B; V consumed MN-major as stored)
+//   warps 8-11  softmax: as in attention_tc.cu (thread = query row = TMEM lane, a unit read once into registers, P as
+//               bf16 into a 128B-swizzled K-major tile, online softmax in registers, retire of a unit deferred until
+//               the next one's softmax is done, ctx rows stored as whole 32-byte sectors)
+#include <cuda.h>
+#include <cudaTypedefs.h>
+
+#include "common.cuh"
+#include "kernels.h"
+#include "tc_helpers.cuh"
+
+namespace b200 {
+
+namespace {
+
+constexpr int QA_THREADS = 384;
+constexpr int QA_CONVERT_WARP0 = 4, QA_SOFTMAX_WARP0 = 8;
+constexpr int QA_GROUP = 128;  // threads per convert / softmax group
+constexpr int BLK = 128;       // token rows per item
+constexpr int UNIT = 64;       // keys per softmax unit
+constexpr int BK = 64;         // bf16 per 128-byte swizzle row
+constexpr int X_BLK = BLK * BK * 2;
+
+template <int H, int D>
+struct QaCfg {
+    static constexpr int KB = H / BK;
+    static constexpr int HEADS = H / D;
+    static constexpr int NQ = 3 * D;                 // accumulator columns per head: q | k | v
+    static constexpr int W_SUB = D * BK * 2;         // one [D x 64] box of Wqkv rows
+    static constexpr int W_BLK = 3 * W_SUB;          // [3D x 64]: one K-major B operand block
+    static constexpr int WS = KB % 3 == 0 ? 3 : 2;   // W ring slots (KB % WS == 0: slots are compile-time in the k loop)
+    static constexpr int T_TILE = BLK * D * 2;       // one Q / K / V tile
+    static constexpr int P_UNIT = BLK * UNIT * 2;    // one K-major 128 x 64 bf16 tile
+    static constexpr int OFF_X = 0;
+    static constexpr int OFF_W = KB * X_BLK;
+    static constexpr int OFF_T = OFF_W + WS * W_BLK;   // 2 buffers x (Q, K, V)
+    static constexpr int OFF_P = OFF_T + 2 * 3 * T_TILE;
+    static constexpr int OFF_AUX = OFF_P + 2 * P_UNIT;
+    static constexpr int OFF_BIAS = OFF_AUX + 512;     // bqkv [3H] fp32
+    static constexpr int BYTES = OFF_BIAS + 3 * H * 4;
+    static constexpr int ACC_COL = 0, ACC_STRIDE = 128, S_COL = 256, O_COL = 384;
+    static_assert(D == 32, "the q / k / v tiles use 64-byte rows");
+    static_assert(KB % WS == 0 && H % BK == 0 && H % D == 0, "shape");
+    static_assert(W_SUB % 1024 == 0, "swizzle atoms must stay 1024-byte aligned");
+    static_assert(NQ % 16 == 0 && NQ <= ACC_STRIDE, "UMMA N");
+    static_assert(BYTES <= SMEM_LIMIT, "shared memory budget exceeded");
+};
+
+struct QaDev {
+    const int* cu;
+    const float* bias;  // [3H]
+    int batch, H;
+    float scale_log2;
+    __nv_bfloat16* ctx;
+};
+
+template <int H, int D>
+__global__ void __launch_bounds__(QA_THREADS, 1)
+qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w, const QaDev p) {
+    using C = QaCfg<H, D>;
+    constexpr int KB = C::KB, HEADS = C::HEADS, NQ = C::NQ, W_SUB = C::W_SUB, W_BLK = C::W_BLK, WS = C::WS;
+    constexpr int T_TILE = C::T_TILE, P_UNIT = C::P_UNIT;
+
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    const uint32_t base = smem_u32(smem_raw);
+    if ((base & 1023u) != 0) __trap();
+    const uint32_t smem_x = base + C::OFF_X, smem_w = base + C::OFF_W, smem_t = base + C::OFF_T, smem_p = base + C::OFF_P;
+    const uint32_t aux = base + C::OFF_AUX;
+    const uint32_t bar_x_full = aux, bar_x_empty = aux + 8;
+    const uint32_t bar_w_full = aux + 16, bar_w_empty = aux + 48;        // WS each
+    const uint32_t bar_acc_full = aux + 80, bar_acc_empty = aux + 96;    // two of each from here on: buffer index & 1
+    const uint32_t bar_t_full = aux + 112, bar_t_empty = aux + 128;      // Q / K / V tiles of a head
+    const uint32_t bar_s_full = aux + 144, bar_s_empty = aux + 160, bar_p_full = aux + 176, bar_o_full = aux + 192,
+                   bar_o_empty = aux + 208;
+    const uint32_t tmem_slot = aux + 256;
+    volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + C::OFF_AUX + 256);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        prefetch_tmap(&tmap_x);
+        prefetch_tmap(&tmap_w);
+        mbar_init(bar_x_full, 1);
+        mbar_init(bar_x_empty, 1);
+        for (int s = 0; s < WS; ++s) { mbar_init(bar_w_full + 8 * s, 1); mbar_init(bar_w_empty + 8 * s, 1); }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(bar_acc_full + 8 * s, 1);
+            mbar_init(bar_acc_empty + 8 * s, QA_GROUP);
+            mbar_init(bar_t_full + 8 * s, QA_GROUP);
+            mbar_init(bar_t_empty + 8 * s, 1);
+            mbar_init(bar_s_full + 8 * s, 1);
+            mbar_init(bar_s_empty + 8 * s, QA_GROUP);
+            mbar_init(bar_p_full + 8 * s, QA_GROUP);
+            mbar_init(bar_o_full + 8 * s, 1);
+            mbar_init(bar_o_empty + 8 * s, QA_GROUP);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc(tmem_slot, 512);
+    const uint32_t smem_bias = base + C::OFF_BIAS;
+    for (int i = threadIdx.x; i < 3 * H; i += QA_THREADS)
+        asm volatile("st.shared.f32 [%0], %1;" ::"r"(smem_bias + i * 4), "f"(__ldg(p.bias + i)) : "memory");
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = *tmem_slot_ptr;
+
+    // Every role walks the same sentence sequence b = blockIdx.x, + gridDim.x, ...; empty sentences are skipped by all.
+    // The bounds of the NEXT sentence are fetched while the current one is processed.
+    struct Walk { int b, s0, s1; };
+    auto fetch = [&](Walk& w) {
+        if (w.b < p.batch) { w.s0 = __ldg(p.cu + w.b); w.s1 = __ldg(p.cu + w.b + 1); }
+    };
+    auto walk_init = [&]() {
+        Walk w{static_cast<int>(blockIdx.x), 0, 0};
+        fetch(w);
+        return w;
+    };
+    auto take = [&](Walk& w, int& start, int& len) {  // current sentence -> (start, len); advances w
+        start = w.s0;
+        len = min(w.s1 - w.s0, BLK);
+        w.b += gridDim.x;
+        fetch(w);
+        return len > 0;
+    };
+
+    if (warp == 0) {
+        // ------------------------------ TMA producer ------------------------------
+        uint32_t it = 0, wb = 0;  // sentences taken, W blocks loaded (ring slot wb % WS)
+        Walk w = walk_init();
+        while (w.b < p.batch) {
+            int start, len;
+            if (!take(w, start, len)) continue;
+            mbar_wait(bar_x_empty, (it & 1) ^ 1);
+            if (elect_one()) {
+                mbar_arrive_expect_tx(bar_x_full, KB * X_BLK);
+#pragma unroll
+                for (int kb = 0; kb < KB; ++kb) tma_load_2d(smem_x + kb * X_BLK, &tmap_x, kb * BK, start, bar_x_full);
+            }
+            __syncwarp();
+            ++it;
+            for (int h = 0; h < HEADS; ++h) {
+#pragma unroll
+                for (int kb = 0; kb < KB; ++kb, ++wb) {
+                    const uint32_t s = kb % WS;
+                    mbar_wait(bar_w_empty + 8 * s, ((wb / WS) & 1) ^ 1);
+                    if (elect_one()) {
+                        mbar_arrive_expect_tx(bar_w_full + 8 * s, W_BLK);
+#pragma unroll
+                        for (int j = 0; j < 3; ++j)  // q, k, v rows of this head
+                            tma_load_2d(smem_w + s * W_BLK + j * W_SUB, &tmap_w, kb * BK, j * H + h * D, bar_w_full + 8 * s);
+                    }
+                    __syncwarp();
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------ MMA issuer --------------------------------
+        constexpr uint32_t idesc_g = umma_idesc_bf16(BLK, NQ);
+        constexpr uint32_t idesc_s = umma_idesc_bf16(BLK, UNIT);
+        constexpr uint32_t idesc_o = umma_idesc_bf16(BLK, D) | (1u << 16);  // B (= V) is MN-major
+        const uint64_t dx0 = umma_desc_sw128(smem_x), dw0 = umma_desc_sw128(smem_w);
+        const uint64_t dq0 = umma_desc_k_sw64(smem_t), dp0 = umma_desc_sw128(smem_p);
+        const uint64_t dv0 = umma_desc_mn<D>(smem_t + 2 * T_TILE);
+        // G cursor: the projection of head g + 1 is issued between S(g) and P.V(g), so that it runs on the tensor pipe
+        // while the softmax warps work on head g (issued before S(g + 1) it would delay that head's softmax by its
+        // whole length). Where it needs the next sentence's x tile it is issued after P.V(g) instead: that wait must
+        // not hold back MMAs whose operands are ready.
+        Walk wg = walk_init();
+        int g_h = HEADS;        // head the cursor points at (HEADS: needs the next sentence)
+        uint32_t g_it = 0;      // sentences the cursor has entered
+        uint32_t gg = 0;        // heads projected so far (ACC buffer gg & 1)
+        uint32_t wb = 0;        // W blocks consumed
+        auto issue_g = [&]() -> bool {
+            if (g_h == HEADS) {
+                int start, len;
+                bool ok = false;
+                while (wg.b < p.batch) {
+                    if (take(wg, start, len)) { ok = true; break; }
+                }
+                if (!ok) return false;
+                g_h = 0;
+                mbar_wait(bar_x_full, g_it & 1);
+                ++g_it;
+            }
+            mbar_wait(bar_acc_empty + 8 * (gg & 1), ((gg >> 1) & 1) ^ 1);  // convert has drained this accumulator
+            tc_fence_after_sync();
+#pragma unroll
+            for (int kb = 0; kb < KB; ++kb, ++wb) {
+                const uint32_t s = kb % WS;
+                mbar_wait(bar_w_full + 8 * s, (wb / WS) & 1);
+                tc_fence_after_sync();
+                if (elect_one()) {
+                    const uint64_t da = dx0 + ((kb * X_BLK) >> 4), db = dw0 + ((s * W_BLK) >> 4);
+#pragma unroll
+                    for (int k = 0; k < BK / 16; ++k)
+                        umma_bf16(tmem_base + C::ACC_COL + (gg & 1) * C::ACC_STRIDE, da + 2 * k, db + 2 * k, idesc_g,
+                                  (kb > 0 || k > 0) ? 1u : 0u);
+                    umma_commit(bar_w_empty + 8 * s);
+                    if (kb == KB - 1) {
+                        umma_commit(bar_acc_full + 8 * (gg & 1));
+                        if (g_h == HEADS - 1) umma_commit(bar_x_empty);  // the x tile has been read for the last time
+                    }
+                }
+                __syncwarp();
+            }
+            ++g_h;
+            ++gg;
+            return true;
+        };
+        uint32_t g = 0;   // heads attended so far (tile buffer g & 1)
+        uint32_t us = 0;  // units whose S MMA has been issued (S buffer us & 1)
+        uint32_t uo = 0;  // units whose P.V MMA has been issued (O buffer uo & 1)
+        bool more = issue_g();
+        Walk w = walk_init();
+        while (w.b < p.batch) {
+            int start, len;
+            if (!take(w, start, len)) continue;
+            const int nunits = (len + UNIT - 1) / UNIT;
+            for (int h = 0; h < HEADS; ++h, ++g) {
+                const uint32_t tb = g & 1;
+                mbar_wait(bar_t_full + 8 * tb, (g >> 1) & 1);  // Q / K / V of this head are in shared memory
+                for (int u = 0; u < nunits; ++u, ++us) {
+                    mbar_wait(bar_s_empty + 8 * (us & 1), ((us >> 1) & 1) ^ 1);  // softmax drained this S buffer
+                    tc_fence_after_sync();
+                    if (elect_one()) {
+                        const uint64_t dq = dq0 + ((tb * 3 * T_TILE) >> 4);
+                        const uint64_t dk = dq0 + ((tb * 3 * T_TILE + T_TILE + u * (UNIT * D * 2)) >> 4);
+#pragma unroll
+                        for (int k = 0; k < D / 16; ++k)
+                            umma_bf16(tmem_base + C::S_COL + (us & 1) * UNIT, dq + 2 * k, dk + 2 * k, idesc_s, k > 0 ? 1u : 0u);
+                        umma_commit(bar_s_full + 8 * (us & 1));
+                    }
+                    __syncwarp();
+                }
+                const bool g_early = more && g_h < HEADS;  // next projection is of the same sentence: x is resident
+                if (g_early) more = issue_g();
+                for (int u = 0; u < nunits; ++u, ++uo) {
+                    const uint32_t ob = uo & 1;
+                    mbar_wait(bar_p_full + 8 * ob, (uo >> 1) & 1);         // P_u is in shared memory
+                    mbar_wait(bar_o_empty + 8 * ob, ((uo >> 1) & 1) ^ 1);  // the O buffer has been read
+                    tc_fence_after_sync();
+                    if (elect_one()) {
+                        const uint64_t dp = dp0 + ((ob * P_UNIT) >> 4);
+                        const uint64_t dv = dv0 + ((tb * 3 * T_TILE + u * (UNIT * D * 2)) >> 4);
+#pragma unroll
+                        for (int k = 0; k < UNIT / 16; ++k)  // P: 32 B per 16 keys; V: 16 rows of D*2 B
+                            umma_bf16(tmem_base + C::O_COL + ob * D, dp + 2 * k, dv + ((k * 16 * D * 2) >> 4), idesc_o,
+                                      k > 0 ? 1u : 0u);
+                        umma_commit(bar_o_full + 8 * ob);
+                        if (u == nunits - 1) umma_commit(bar_t_empty + 8 * tb);  // this head's tiles are consumed
+                    }
+                    __syncwarp();
+                }
+                if (more && !g_early) more = issue_g();  // first head of the next sentence
+            }
+        }
+    } else if (warp >= QA_CONVERT_WARP0 && warp < QA_SOFTMAX_WARP0) {
+        // ------------------------------ convert: ACC + bias -> Q / K / V tiles ------------------------------
+        const int quad = warp & 3;
+        const int row = quad * 32 + lane;
+        const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
+        uint32_t g = 0;
+        Walk w = walk_init();
+        while (w.b < p.batch) {
+            int start, len;
+            if (!take(w, start, len)) continue;
+            for (int h = 0; h < HEADS; ++h, ++g) {
+                const uint32_t ab = g & 1;
+                mbar_wait(bar_acc_full + 8 * ab, (g >> 1) & 1);
+                tc_fence_after_sync();
+                uint32_t words[3][16];
+#pragma unroll
+                for (int j = 0; j < 3; ++j) {  // q, k, v
+                    uint32_t v[32];
+                    tmem_ld_32x32(t_lane + C::ACC_COL + ab * C::ACC_STRIDE + j * D, v);
+                    const uint32_t bs = smem_bias + (j * H + h * D) * 4;
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) {
+                        const uint4 b = lds_v4(bs + q * 16);
+                        words[j][q * 2 + 0] = epi_pair_bf16<EPI_BIAS>(v[q * 4 + 0], v[q * 4 + 1], __uint_as_float(b.x), __uint_as_float(b.y));
+                        words[j][q * 2 + 1] = epi_pair_bf16<EPI_BIAS>(v[q * 4 + 2], v[q * 4 + 3], __uint_as_float(b.z), __uint_as_float(b.w));
+                    }
+                }
+                tc_fence_before_sync();
+                mbar_arrive(bar_acc_empty + 8 * ab);  // the accumulator is in registers
+                mbar_wait(bar_t_empty + 8 * ab, ((g >> 1) & 1) ^ 1);  // the head two back has finished with this buffer
+                const uint32_t tile = smem_t + ab * 3 * T_TILE;
+#pragma unroll
+                for (int j = 0; j < 3; ++j) stage_words_bf16(tile + j * T_TILE, row, words[j]);
+                fence_proxy_async_smem();
+                mbar_arrive(bar_t_full + 8 * ab);
+            }
+        }
+    } else if (warp >= QA_SOFTMAX_WARP0) {
+        // ------------------------------ softmax ------------------------------
+        const int quad = warp & 3;
+        const int row = quad * 32 + lane;  // query row inside the item = TMEM lane
+        const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
+        uint32_t uc = 0;  // units processed so far by this CTA (buffer uc & 1, phase (uc >> 1) & 1)
+        float o[D];       // running output of the head being retired
+#pragma unroll
+        for (int j = 0; j < D; ++j) o[j] = 0.f;
+        // the previous unit of the stream: folded in (and its head finalised if it ended there) after the current
+        // unit's softmax, while the current P.V runs
+        struct Pending {
+            bool valid, last;
+            uint32_t ur;
+            float corr, l;
+            int start, len, h;
+        } pend{false, false, 0, 0.f, 0.f, 0, 0, 0};
+        auto retire_pending = [&]() {
+            const uint32_t ob = pend.ur & 1;
+            mbar_wait(bar_o_full + 8 * ob, (pend.ur >> 1) & 1);
+            tc_fence_after_sync();
+            {
+                uint32_t v[32];
+                tmem_ld_32x32(t_lane + C::O_COL + ob * D, v);
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 32; ++j) o[j] = fmaf(o[j], pend.corr, __uint_as_float(v[j]));
+            }
+            tc_fence_before_sync();
+            mbar_arrive(bar_o_empty + 8 * ob);
+            if (pend.last) {
+                const float inv = 1.0f / pend.l;
+                if (row < pend.len) {
+                    __nv_bfloat16* dst = p.ctx + static_cast<size_t>(pend.start + row) * p.H + pend.h * D;
+#pragma unroll
+                    for (int q = 0; q < D / 16; ++q) {
+                        uint32_t wd[8];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) wd[j] = pack_bf16x2(o[q * 16 + 2 * j] * inv, o[q * 16 + 2 * j + 1] * inv);
+                        stg_v8(dst + q * 16, wd);
+                    }
+                }
+            }
+            pend.valid = false;
+        };
+        Walk w = walk_init();
+        while (w.b < p.batch) {
+            int start, len;
+            if (!take(w, start, len)) continue;
+            const int nunits = (len + UNIT - 1) / UNIT;
+            for (int h = 0; h < HEADS; ++h) {
+                float m = -INFINITY, l = 0.f;  // the first unit's corr is exp2(-inf) = 0: the previous head's output vanishes
+                for (int u = 0; u < nunits; ++u, ++uc) {
+                    const uint32_t sb = uc & 1;
+                    const int nvalid = min(UNIT, len - u * UNIT);  // keys of this unit inside the sentence
+                    mbar_wait(bar_s_full + 8 * sb, (uc >> 1) & 1);
+                    tc_fence_after_sync();
+                    uint32_t v[UNIT];
+                    tmem_ld_32x32(t_lane + C::S_COL + sb * UNIT, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+                    tmem_ld_32x32(t_lane + C::S_COL + sb * UNIT + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+                    tmem_ld_wait();
+                    tc_fence_before_sync();
+                    mbar_arrive(bar_s_empty + 8 * sb);  // S is in registers: the MMA warp may overwrite the buffer
+                    if (nvalid < UNIT) {  // keys past the sentence end -> -inf (exp2 then gives exactly 0)
+#pragma unroll
+                        for (int j = 0; j < UNIT; ++j)
+                            if (j >= nvalid) v[j] = 0xff800000u;
+                    }
+                    float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+                    for (int j = 0; j < UNIT; ++j) mx4[j & 3] = fmaxf(mx4[j & 3], __uint_as_float(v[j]));
+                    const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+                    const float m_new = fmaxf(m, mx * p.scale_log2);
+                    const float corr = ex2(m - m_new);
+                    m = m_new;
+                    const uint64_t sc2 = pk2(p.scale_log2, p.scale_log2), nm2 = pk2(-m_new, -m_new);
+                    uint64_t lb2[4] = {0, 0, 0, 0};
+                    const uint32_t prow = smem_p + sb * P_UNIT + row * 128;
+#pragma unroll
+                    for (int q = 0; q < UNIT / 8; ++q) {
+                        uint32_t wd[4];
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            float a, bb;
+                            upk2(fma2(pk2(__uint_as_float(v[q * 8 + 2 * j]), __uint_as_float(v[q * 8 + 2 * j + 1])), sc2, nm2), a, bb);
+                            const float pa = ex2(a), pb = ex2(bb);
+                            lb2[j] = add2(lb2[j], pk2(pa, pb));
+                            wd[j] = pack_bf16x2(pa, pb);
+                        }
+                        const uint32_t piece = static_cast<uint32_t>(q) ^ (row & 7);
+                        sts_v4(prow + (piece << 4), wd[0], wd[1], wd[2], wd[3]);
+                    }
+                    float lb;
+                    {
+                        float a0, a1, a2, a3;
+                        upk2(add2(lb2[0], lb2[1]), a0, a1);
+                        upk2(add2(lb2[2], lb2[3]), a2, a3);
+                        lb = (a0 + a1) + (a2 + a3);
+                    }
+                    fence_proxy_async_smem();
+                    mbar_arrive(bar_p_full + 8 * sb);
+                    l = fmaf(l, corr, lb);
+                    if (pend.valid) retire_pending();
+                    pend.valid = true; pend.last = u == nunits - 1; pend.ur = uc; pend.corr = corr; pend.l = l;
+                    pend.start = start; pend.len = len; pend.h = h;
+                }
+            }
+        }
+        if (pend.valid) retire_pending();
+    }
+
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after_sync();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+template <int H, int D>
+cudaError_t launch_qa(const __nv_bfloat16* x, const __nv_bfloat16* wqkv, const float* bqkv, const int* cu, int rows_cap,
+                      int batch, __nv_bfloat16* ctx, int num_sms, cudaStream_t s) {
+    using C = QaCfg<H, D>;
+    alignas(64) CUtensorMap tx, tw;
+    if (!make_tmap(&tx, x, rows_cap, H, BK, BLK, false, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
+    if (!make_tmap(&tw, wqkv, 3 * H, H, BK, D, false, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
+    auto kern = qkv_attention_kernel<H, D>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::BYTES);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    QaDev p;
+    p.cu = cu; p.bias = bqkv; p.batch = batch; p.H = H; p.ctx = ctx;
+    p.scale_log2 = 1.4426950408889634f / sqrtf(static_cast<float>(D));
+    const int grid = batch < num_sms ? batch : num_sms;
+    if (grid <= 0) return cudaSuccess;
+    kern<<<grid, QA_THREADS, C::BYTES, s>>>(tx, tw, p);
+    return cudaGetLastError();
+}
+
+}  // namespace
+
+bool qkv_attention_supported(int hidden, int heads, int max_seqlen) {
+    return (hidden == 384 || hidden == 256 || hidden == 128) && heads * 32 == hidden && max_seqlen <= BLK;
+}
+
+cudaError_t launch_qkv_attention(const __nv_bfloat16* x, const __nv_bfloat16* wqkv, const float* bqkv, const int* cu,
+                                 int rows_cap, int batch, int max_seqlen, int hidden, int heads, __nv_bfloat16* ctx,
+                                 int num_sms, cudaStream_t s) {
+    if (batch <= 0 || max_seqlen <= 0) return cudaSuccess;
+    if (!qkv_attention_supported(hidden, heads, max_seqlen)) return cudaErrorInvalidValue;
+    if (hidden == 384) return launch_qa<384, 32>(x, wqkv, bqkv, cu, rows_cap, batch, ctx, num_sms, s);
+    if (hidden == 256) return launch_qa<256, 32>(x, wqkv, bqkv, cu, rows_cap, batch, ctx, num_sms, s);
+    return launch_qa<128, 32>(x, wqkv, bqkv, cu, rows_cap, batch, ctx, num_sms, s);
+}
+
+}  // namespace b200

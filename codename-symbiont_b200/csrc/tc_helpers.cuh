@@ -186,6 +186,30 @@ __device__ __forceinline__ void stage_words_bf16(uint32_t buf, int r, const uint
     for (int q = 0; q < 4; ++q) sts_v4(row + ((q ^ sw) << 4), w[q * 4], w[q * 4 + 1], w[q * 4 + 2], w[q * 4 + 3]);
 }
 
+// ---- attention operand descriptors (attention_tc.cu, qkv_attention.cu) ----
+// K-major operand, rows of 64 bytes (D = 32): SWIZZLE_64B, 8-row groups 512 B apart.
+__device__ __forceinline__ uint64_t umma_desc_k_sw64(uint32_t a) {
+    return static_cast<uint64_t>((a & 0x3FFFFu) >> 4) | (1ull << 16) | (32ull << 32) | (1ull << 46) | (4ull << 61);
+}
+// MN-major operand (V as stored: [key, d], d contiguous). The swizzle atom is one row of D*2 bytes (MN) by 8 keys
+// (K); SBO = distance between 8-key groups; LBO (between MN atoms) is unused because N = D fits one atom.
+template <int D>
+__device__ __forceinline__ uint64_t umma_desc_mn(uint32_t a) {
+    constexpr uint64_t sbo = (8 * D * 2) >> 4;
+    constexpr uint64_t layout = D == 32 ? 4 : 2;  // SWIZZLE_64B : SWIZZLE_128B
+    return static_cast<uint64_t>((a & 0x3FFFFu) >> 4) | (1ull << 16) | (sbo << 32) | (1ull << 46) | (layout << 61);
+}
+template <int D>
+__device__ __forceinline__ uint64_t umma_desc_k(uint32_t a) {
+    return D == 32 ? umma_desc_k_sw64(a) : umma_desc_sw128(a);
+}
+
+__device__ __forceinline__ float ex2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
 PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
     static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
     static std::once_flag once;

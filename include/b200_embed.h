@@ -141,7 +141,9 @@ int64_t b200_embed_kernel_launches(const b200_embed* h);
 #define B200_EMBED_KIND_POOL 8      /* K5 masked mean-pool (+L2)        (embedding_generator.rs:201-207) */
 #define B200_EMBED_KIND_FFN_FUSED 9 /* K2f intermediate.dense + GELU + output.dense + residual + LayerNorm in one kernel
                                        (BertIntermediate + BertOutput); replaces kinds 5 and 6 when hidden <= 384 */
-#define B200_EMBED_NUM_KINDS 10
+#define B200_EMBED_KIND_QKV_ATTN 10 /* K23 Q/K/V projection + attention of whole sentences in one kernel (BertSelfAttention);
+                                       replaces kinds 2 and 3 when hidden <= 384, head_dim 32, seq_len <= 128 */
+#define B200_EMBED_NUM_KINDS 11
 typedef struct b200_embed_kind_stats {
     double total_ms;  /* sum of event-timed durations */
     int64_t launches;
@@ -199,6 +201,11 @@ int32_t b200_op_linear_noalloc(b200_embed* h, int32_t layer, int32_t which, cons
  * dtype 0: tcgen05 kernel (the one the forward uses), 1: fp32 validation, 2: mma.sync bf16 kernel (A/B checks). */
 int32_t b200_op_attention(b200_embed* h, const void* qkv, const int32_t* cu_seqlens, int32_t batch, int32_t rows,
                           int32_t max_seqlen, int32_t dtype, void* ctx, void* stream);
+/* K23. ctx = attention(x . Wqkv^T + bqkv) of layer `layer` straight from the bf16 activations x [rows, H]: the fused
+ * form of b200_op_linear(which = 0) + b200_op_attention(dtype = 0), used by the forward whenever it applies (hidden
+ * 128 / 256 / 384, head_dim 32, max_seqlen <= 128; otherwise B200_EMBED_ERR_UNSUPPORTED_SHAPE). */
+int32_t b200_op_qkv_attention(b200_embed* h, int32_t layer, const void* x, const int32_t* cu_seqlens, int32_t batch,
+                              int32_t rows, int32_t max_seqlen, void* ctx, void* stream);
 /* K4. out = LN(y + residual) * gamma + beta with the LayerNorm of (layer, which = 1 or 3).
  * y is fp32 when dtype = 0 came from an unfused GEMM (y_is_f32 != 0). */
 int32_t b200_op_add_layernorm(b200_embed* h, int32_t layer, int32_t which, const void* y, int32_t y_is_f32,

@@ -8,4 +8,4 @@ d=json.loads(sys.stdin.read())
 print('value',round(d['value']),'ms',round(d['ms_per_step'],2), d['clocks']['sm_mhz'], {k:v['ms_per_launch'] for k,v in d['kernels'].items()})"
 }
 run X=0
-run X=0
+run B200_EMBED_QKV_ATTN=1

@@ -222,6 +222,37 @@ def test_k3_attention(env, pkg, dtype, heads, d):
     assert cos_rows(got, want).min() >= (0.999999 if dtype == 1 else 0.9998)
 
 
+@pytest.mark.parametrize("heads", [4, 8, 12])
+def test_k23_qkv_attention_fused(pkg, built, heads):
+    """Q/K/V projection + attention of whole sentences in one kernel (bert.rs BertSelfAttention::forward) vs the
+    oracle's Linear + padded additive-mask softmax on the same bf16-rounded weights and input; q, k, v are rounded to
+    bf16 on the GPU (they are the attention MMAs' operands). Ragged lengths 1 .. 128 incl. both sides of 64."""
+    d = 32
+    H = heads * d
+    shape = pkg.weights.BertShape(512, H, 1, heads, 4 * H, 128, 2)
+    lengths = np.array([1, 2, 63, 64, 65, 128, 100, 17, 127, 128, 33, 5] * 3)
+    S = 128
+    rng = np.random.default_rng(heads)
+    x = bf16_round(rng.standard_normal((len(lengths), S, H)).astype(np.float32))
+    mask = (np.arange(S)[None, :] < lengths[:, None]).astype(np.uint32)
+    with pkg.Embedder.random_init(shape, seed=5) as e:
+        w = e.export_weights()
+        o = Oracle(shape, {k: bf16_round(v) if v.ndim == 2 else v for k, v in w.items()}, "f32")
+        pre = "attention.self."
+        q, k, v = (bf16_round(o.linear(x.reshape(-1, H), o.layer(0, pre + n + ".weight"), o.layer(0, pre + n + ".bias"))
+                              .reshape(len(lengths), S, H)) for n in ("query", "key", "value"))
+        want = padded_to_packed(o.attention(q, k, v, mask, heads), lengths)
+        xp = padded_to_packed(x, lengths)
+        dx = dev(xp, torch.bfloat16)
+        ctx = torch.full(want.shape, float("nan"), dtype=torch.bfloat16, device="cuda")
+        d_cu = dev_i32(cu_of(lengths))
+        e.op_qkv_attention(0, dx.data_ptr(), d_cu.data_ptr(), len(lengths), xp.shape[0], S, ctx.data_ptr())
+        got = host(ctx)
+    assert np.isfinite(got).all()
+    assert np.abs(got - want).max() <= 0.02 * max(1.0, np.abs(want).max()), np.abs(got - want).max()
+    assert cos_rows(got, want).min() >= 0.9998
+
+
 @pytest.mark.parametrize("mode", ["bf16", "f32y", "fp32"])
 def test_k4_add_layernorm(env, mode):
     pkg, shape, emb, w, o32, _ = env
