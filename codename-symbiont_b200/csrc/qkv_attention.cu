@@ -10,19 +10,20 @@
 //
 // Work item = sentence. A persistent CTA (one per SM) keeps the sentence's activation tile x[128, H] resident in
 // shared memory (rows past the sentence end belong to the next sentence or are zero-filled: they are computed and
-// never used) and walks its heads; the heads of all of the CTA's sentences form one stream g = 0, 1, 2, ...:
-//   warp 0      TMA producer: the x tile once per sentence; per head 6 blocks of Wqkv rows {h*d.., H + h*d.., 2H + h*d..}
-//               x 64 columns (three 4 KB boxes = one 96-row K-major B operand) through a 3-slot ring
-//   warp 1      MMA issuer (whole warp walks the schedule, one elected lane issues):
-//                 G(g): ACC[g & 1] = x . Wqkv_h^T           128 x 96 x H, fp32 in TMEM, two heads ahead
-//                 S(g, u) = Q . K_u^T                       128 x 64 x d per unit u of 64 keys
-//                 O(g, u) = P_u . V_u                       128 x d x 64
-//   warp 2      TMEM allocator (512 columns: 2 x 128 ACC, 2 x 64 S, 2 x 32 O)
-//   warps 4-7   convert: ACC + bias -> bf16 Q / K / V tiles in shared memory (two buffers), in the layouts K3 gets from
-//               TMA (64-byte rows, SWIZZLE_64B; V consumed MN-major as stored)
-//   warps 8-11  softmax: as in attention_tc.cu (thread = query row = TMEM lane, a unit read once into registers, P as
-//               bf16 into a 128B-swizzled K-major tile, online softmax in registers, retire of a unit deferred until
-//               the next one's softmax is done, ctx rows stored as whole 32-byte sectors)
+// never used) and walks its heads. Two GROUPS of four warps take alternate heads (even / odd; the head count is even)
+// and each does everything the head needs outside the tensor pipe:
+//   warp 0      TMA producer: the x tile once per sentence; per head KB blocks of Wqkv rows {h*d.., H + h*d.., 2H + h*d..}
+//               x 64 columns (three 4 KB boxes = one 96-row K-major B operand) through a small ring
+//   warp 1      MMA issuer, fixed schedule per pair of heads (whole warp walks it, one elected lane issues):
+//                 projection  ACC[g & 1] = x . Wqkv_h^T      128 x 96 x H per head g, two heads ahead
+//                 group 0/1   S = Q . K_u^T (128 x 64 x d) and O_u = P_u . V_u (128 x d x 64) per unit u of 64 keys
+//   warp 2      TMEM allocator (512 columns: 2 x 128 ACC, 2 x 64 S, 2 x 2 x 32 O)
+//   warps 4-7 / 8-11  group 0 / 1, thread = token row = TMEM lane. Per head: convert ACC + bias -> bf16 Q / K / V tiles
+//               in shared memory, in the layouts K3 gets from TMA (64-byte rows, SWIZZLE_64B; V consumed MN-major as
+//               stored); then per unit the softmax of attention_tc.cu (unit read once into registers, P as bf16 into a
+//               128B-swizzled K-major tile, online softmax, ctx rows stored as whole 32-byte sectors). A group has one
+//               S and one P buffer: the previous unit's P.V is retired (which also proves P free) between the row
+//               maximum and the exponentials of the next unit.
 #include <cuda.h>
 #include <cudaTypedefs.h>
 
@@ -35,11 +36,11 @@ namespace b200 {
 namespace {
 
 constexpr int QA_THREADS = 384;
-constexpr int QA_CONVERT_WARP0 = 4, QA_SOFTMAX_WARP0 = 8;
-constexpr int QA_GROUP = 128;  // threads per convert / softmax group
-constexpr int BLK = 128;       // token rows per item
-constexpr int UNIT = 64;       // keys per softmax unit
-constexpr int BK = 64;         // bf16 per 128-byte swizzle row
+constexpr int QA_GROUP_WARP0 = 4;  // group 0: warps 4-7, group 1: warps 8-11
+constexpr int QA_GROUP = 128;      // threads per group
+constexpr int BLK = 128;           // token rows per item
+constexpr int UNIT = 64;           // keys per softmax unit
+constexpr int BK = 64;             // bf16 per 128-byte swizzle row
 constexpr int X_BLK = BLK * BK * 2;
 
 template <int H, int D>
@@ -54,12 +55,13 @@ struct QaCfg {
     static constexpr int P_UNIT = BLK * UNIT * 2;    // one K-major 128 x 64 bf16 tile
     static constexpr int OFF_X = 0;
     static constexpr int OFF_W = KB * X_BLK;
-    static constexpr int OFF_T = OFF_W + WS * W_BLK;   // 2 buffers x (Q, K, V)
+    static constexpr int OFF_T = OFF_W + WS * W_BLK;   // per group: Q, K, V
     static constexpr int OFF_P = OFF_T + 2 * 3 * T_TILE;
-    static constexpr int OFF_AUX = OFF_P + 2 * P_UNIT;
+    static constexpr int OFF_AUX = OFF_P + 2 * P_UNIT;  // per group: one P unit
     static constexpr int OFF_BIAS = OFF_AUX + 512;     // bqkv [3H] fp32
     static constexpr int BYTES = OFF_BIAS + 3 * H * 4;
-    static constexpr int ACC_COL = 0, ACC_STRIDE = 128, S_COL = 256, O_COL = 384;
+    static constexpr int ACC_COL = 0, ACC_STRIDE = 128, S_COL = 256, O_COL = 384;  // S: + group * 64; O: + group * 64 + (unit & 1) * 32
+    static_assert(HEADS % 2 == 0, "the two groups take alternate heads");
     static_assert(D == 32, "the q / k / v tiles use 64-byte rows");
     static_assert(KB % WS == 0 && H % BK == 0 && H % D == 0, "shape");
     static_assert(W_SUB % 1024 == 0, "swizzle atoms must stay 1024-byte aligned");
@@ -89,10 +91,11 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
     const uint32_t aux = base + C::OFF_AUX;
     const uint32_t bar_x_full = aux, bar_x_empty = aux + 8;
     const uint32_t bar_w_full = aux + 16, bar_w_empty = aux + 48;        // WS each
-    const uint32_t bar_acc_full = aux + 80, bar_acc_empty = aux + 96;    // two of each from here on: buffer index & 1
-    const uint32_t bar_t_full = aux + 112, bar_t_empty = aux + 128;      // Q / K / V tiles of a head
-    const uint32_t bar_s_full = aux + 144, bar_s_empty = aux + 160, bar_p_full = aux + 176, bar_o_full = aux + 192,
-                   bar_o_empty = aux + 208;
+    // two of each from here on, index = ACC buffer / group
+    const uint32_t bar_acc_full = aux + 80, bar_acc_empty = aux + 96;
+    const uint32_t bar_t_full = aux + 112, bar_t_empty = aux + 128;      // Q / K / V tiles of the group's head
+    const uint32_t bar_s_full = aux + 144, bar_s_empty = aux + 160, bar_p_full = aux + 176;
+    const uint32_t bar_o_full = aux + 192, bar_o_empty = aux + 224;      // [group][unit & 1]
     const uint32_t tmem_slot = aux + 256;
     volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + C::OFF_AUX + 256);
 
@@ -112,6 +115,8 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
             mbar_init(bar_s_full + 8 * s, 1);
             mbar_init(bar_s_empty + 8 * s, QA_GROUP);
             mbar_init(bar_p_full + 8 * s, QA_GROUP);
+        }
+        for (int s = 0; s < 4; ++s) {
             mbar_init(bar_o_full + 8 * s, 1);
             mbar_init(bar_o_empty + 8 * s, QA_GROUP);
         }
@@ -176,155 +181,133 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
             }
         }
     } else if (warp == 1) {
-        // ------------------------------ MMA issuer --------------------------------
+        // ------------------------------ MMA issuer: event loop ------------------------------
         constexpr uint32_t idesc_g = umma_idesc_bf16(BLK, NQ);
         constexpr uint32_t idesc_s = umma_idesc_bf16(BLK, UNIT);
         constexpr uint32_t idesc_o = umma_idesc_bf16(BLK, D) | (1u << 16);  // B (= V) is MN-major
         const uint64_t dx0 = umma_desc_sw128(smem_x), dw0 = umma_desc_sw128(smem_w);
         const uint64_t dq0 = umma_desc_k_sw64(smem_t), dp0 = umma_desc_sw128(smem_p);
         const uint64_t dv0 = umma_desc_mn<D>(smem_t + 2 * T_TILE);
-        // G cursor: the projection of head g + 1 is issued between S(g) and P.V(g), so that it runs on the tensor pipe
-        // while the softmax warps work on head g (issued before S(g + 1) it would delay that head's softmax by its
-        // whole length). Where it needs the next sentence's x tile it is issued after P.V(g) instead: that wait must
-        // not hold back MMAs whose operands are ready.
-        Walk wg = walk_init();
-        int g_h = HEADS;        // head the cursor points at (HEADS: needs the next sentence)
-        uint32_t g_it = 0;      // sentences the cursor has entered
-        uint32_t gg = 0;        // heads projected so far (ACC buffer gg & 1)
-        uint32_t wb = 0;        // W blocks consumed
-        auto issue_g = [&]() -> bool {
-            if (g_h == HEADS) {
-                int start, len;
+        // A fixed schedule (the two groups do the same work at the same pace, so an event loop buys nothing and a polling
+        // one was measured 2x slower: its own instructions became the bottleneck). Per PAIR of heads (h for group 0,
+        // h + 1 for group 1):   S(u0) x2 | projection of head h + 2 | S(u1) x2 | P.V(u0) x2 | projection of head h + 3 |
+        // P.V(u1) x2 - the projections run on the tensor pipe while the groups are busy with their softmax.
+        Walk wp = walk_init();
+        int ph = HEADS;                 // projection cursor: head within its sentence (HEADS: needs the next sentence)
+        uint32_t pit = 0, gg = 0, wb = 0;  // sentences entered, heads projected, W blocks consumed
+        auto proj_head = [&]() -> bool {
+            if (ph == HEADS) {
+                int a, b;
                 bool ok = false;
-                while (wg.b < p.batch) {
-                    if (take(wg, start, len)) { ok = true; break; }
+                while (wp.b < p.batch) {
+                    if (take(wp, a, b)) { ok = true; break; }
                 }
                 if (!ok) return false;
-                g_h = 0;
-                mbar_wait(bar_x_full, g_it & 1);
-                ++g_it;
+                mbar_wait(bar_x_full, pit & 1);
+                ++pit;
+                ph = 0;
             }
-            mbar_wait(bar_acc_empty + 8 * (gg & 1), ((gg >> 1) & 1) ^ 1);  // convert has drained this accumulator
+            const uint32_t ab = gg & 1;
+            mbar_wait(bar_acc_empty + 8 * ab, ((gg >> 1) & 1) ^ 1);  // the group has drained this accumulator
             tc_fence_after_sync();
 #pragma unroll
             for (int kb = 0; kb < KB; ++kb, ++wb) {
-                const uint32_t s = kb % WS;
-                mbar_wait(bar_w_full + 8 * s, (wb / WS) & 1);
+                const uint32_t sl = kb % WS;
+                mbar_wait(bar_w_full + 8 * sl, (wb / WS) & 1);
                 tc_fence_after_sync();
                 if (elect_one()) {
-                    const uint64_t da = dx0 + ((kb * X_BLK) >> 4), db = dw0 + ((s * W_BLK) >> 4);
+                    const uint64_t da = dx0 + ((kb * X_BLK) >> 4), db = dw0 + ((sl * W_BLK) >> 4);
 #pragma unroll
                     for (int k = 0; k < BK / 16; ++k)
-                        umma_bf16(tmem_base + C::ACC_COL + (gg & 1) * C::ACC_STRIDE, da + 2 * k, db + 2 * k, idesc_g,
+                        umma_bf16(tmem_base + C::ACC_COL + ab * C::ACC_STRIDE, da + 2 * k, db + 2 * k, idesc_g,
                                   (kb > 0 || k > 0) ? 1u : 0u);
-                    umma_commit(bar_w_empty + 8 * s);
+                    umma_commit(bar_w_empty + 8 * sl);
                     if (kb == KB - 1) {
-                        umma_commit(bar_acc_full + 8 * (gg & 1));
-                        if (g_h == HEADS - 1) umma_commit(bar_x_empty);  // the x tile has been read for the last time
+                        umma_commit(bar_acc_full + 8 * ab);
+                        if (ph == HEADS - 1) umma_commit(bar_x_empty);  // the x tile has been read for the last time
                     }
                 }
                 __syncwarp();
             }
-            ++g_h;
+            ++ph;
             ++gg;
             return true;
         };
-        uint32_t g = 0;   // heads attended so far (tile buffer g & 1)
-        uint32_t us = 0;  // units whose S MMA has been issued (S buffer us & 1)
-        uint32_t uo = 0;  // units whose P.V MMA has been issued (O buffer uo & 1)
-        bool more = issue_g();
+        uint32_t hc = 0;          // head pairs completed (both groups advance together)
+        uint32_t us = 0, uo = 0;  // S / P.V units issued per group (the same for both)
+        auto issue_s = [&](int G, int u, bool first) {
+            if (first) mbar_wait(bar_t_full + 8 * G, hc & 1);       // this head's Q / K / V are staged
+            mbar_wait(bar_s_empty + 8 * G, (us & 1) ^ 1);           // the group has read the previous S
+            tc_fence_after_sync();
+            if (elect_one()) {
+                const uint64_t dq = dq0 + ((G * 3 * T_TILE) >> 4);
+                const uint64_t dk = dq0 + ((G * 3 * T_TILE + T_TILE + u * (UNIT * D * 2)) >> 4);
+#pragma unroll
+                for (int k = 0; k < D / 16; ++k)
+                    umma_bf16(tmem_base + C::S_COL + G * UNIT, dq + 2 * k, dk + 2 * k, idesc_s, k > 0 ? 1u : 0u);
+                umma_commit(bar_s_full + 8 * G);
+            }
+            __syncwarp();
+        };
+        auto issue_pv = [&](int G, int u, bool last) {
+            const uint32_t ob = uo & 1;
+            mbar_wait(bar_p_full + 8 * G, uo & 1);                                  // P_u is in shared memory
+            mbar_wait(bar_o_empty + 8 * (2 * G + ob), ((uo >> 1) & 1) ^ 1);         // the O buffer has been read
+            tc_fence_after_sync();
+            if (elect_one()) {
+                const uint64_t dp = dp0 + ((G * P_UNIT) >> 4);
+                const uint64_t dv = dv0 + ((G * 3 * T_TILE + u * (UNIT * D * 2)) >> 4);
+#pragma unroll
+                for (int k = 0; k < UNIT / 16; ++k)  // P: 32 B per 16 keys; V: 16 rows of D*2 B
+                    umma_bf16(tmem_base + C::O_COL + G * 64 + ob * D, dp + 2 * k, dv + ((k * 16 * D * 2) >> 4), idesc_o,
+                              k > 0 ? 1u : 0u);
+                umma_commit(bar_o_full + 8 * (2 * G + ob));
+                if (last) umma_commit(bar_t_empty + 8 * G);  // this head's tiles are consumed
+            }
+            __syncwarp();
+        };
+        bool more = proj_head();
+        if (more) more = proj_head();
         Walk w = walk_init();
         while (w.b < p.batch) {
             int start, len;
             if (!take(w, start, len)) continue;
             const int nunits = (len + UNIT - 1) / UNIT;
-            for (int h = 0; h < HEADS; ++h, ++g) {
-                const uint32_t tb = g & 1;
-                mbar_wait(bar_t_full + 8 * tb, (g >> 1) & 1);  // Q / K / V of this head are in shared memory
-                for (int u = 0; u < nunits; ++u, ++us) {
-                    mbar_wait(bar_s_empty + 8 * (us & 1), ((us >> 1) & 1) ^ 1);  // softmax drained this S buffer
-                    tc_fence_after_sync();
-                    if (elect_one()) {
-                        const uint64_t dq = dq0 + ((tb * 3 * T_TILE) >> 4);
-                        const uint64_t dk = dq0 + ((tb * 3 * T_TILE + T_TILE + u * (UNIT * D * 2)) >> 4);
-#pragma unroll
-                        for (int k = 0; k < D / 16; ++k)
-                            umma_bf16(tmem_base + C::S_COL + (us & 1) * UNIT, dq + 2 * k, dk + 2 * k, idesc_s, k > 0 ? 1u : 0u);
-                        umma_commit(bar_s_full + 8 * (us & 1));
-                    }
-                    __syncwarp();
+            for (int h = 0; h < HEADS; h += 2, ++hc) {
+                issue_s(0, 0, true);
+                issue_s(1, 0, true);
+                ++us;
+                if (more) more = proj_head();
+                if (nunits > 1) {
+                    issue_s(0, 1, false);
+                    issue_s(1, 1, false);
+                    ++us;
                 }
-                const bool g_early = more && g_h < HEADS;  // next projection is of the same sentence: x is resident
-                if (g_early) more = issue_g();
-                for (int u = 0; u < nunits; ++u, ++uo) {
-                    const uint32_t ob = uo & 1;
-                    mbar_wait(bar_p_full + 8 * ob, (uo >> 1) & 1);         // P_u is in shared memory
-                    mbar_wait(bar_o_empty + 8 * ob, ((uo >> 1) & 1) ^ 1);  // the O buffer has been read
-                    tc_fence_after_sync();
-                    if (elect_one()) {
-                        const uint64_t dp = dp0 + ((ob * P_UNIT) >> 4);
-                        const uint64_t dv = dv0 + ((tb * 3 * T_TILE + u * (UNIT * D * 2)) >> 4);
-#pragma unroll
-                        for (int k = 0; k < UNIT / 16; ++k)  // P: 32 B per 16 keys; V: 16 rows of D*2 B
-                            umma_bf16(tmem_base + C::O_COL + ob * D, dp + 2 * k, dv + ((k * 16 * D * 2) >> 4), idesc_o,
-                                      k > 0 ? 1u : 0u);
-                        umma_commit(bar_o_full + 8 * ob);
-                        if (u == nunits - 1) umma_commit(bar_t_empty + 8 * tb);  // this head's tiles are consumed
-                    }
-                    __syncwarp();
+                issue_pv(0, 0, nunits == 1);
+                issue_pv(1, 0, nunits == 1);
+                ++uo;
+                if (more) more = proj_head();
+                if (nunits > 1) {
+                    issue_pv(0, 1, true);
+                    issue_pv(1, 1, true);
+                    ++uo;
                 }
-                if (more && !g_early) more = issue_g();  // first head of the next sentence
             }
         }
-    } else if (warp >= QA_CONVERT_WARP0 && warp < QA_SOFTMAX_WARP0) {
-        // ------------------------------ convert: ACC + bias -> Q / K / V tiles ------------------------------
+    } else if (warp >= QA_GROUP_WARP0) {
+        // ------------------------------ groups: convert + softmax of alternate heads ------------------------------
+        const int G = (warp - QA_GROUP_WARP0) >> 2;
         const int quad = warp & 3;
-        const int row = quad * 32 + lane;
+        const int row = quad * 32 + lane;  // token row inside the item = TMEM lane
         const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
-        uint32_t g = 0;
-        Walk w = walk_init();
-        while (w.b < p.batch) {
-            int start, len;
-            if (!take(w, start, len)) continue;
-            for (int h = 0; h < HEADS; ++h, ++g) {
-                const uint32_t ab = g & 1;
-                mbar_wait(bar_acc_full + 8 * ab, (g >> 1) & 1);
-                tc_fence_after_sync();
-                uint32_t words[3][16];
-#pragma unroll
-                for (int j = 0; j < 3; ++j) {  // q, k, v
-                    uint32_t v[32];
-                    tmem_ld_32x32(t_lane + C::ACC_COL + ab * C::ACC_STRIDE + j * D, v);
-                    const uint32_t bs = smem_bias + (j * H + h * D) * 4;
-                    tmem_ld_wait();
-#pragma unroll
-                    for (int q = 0; q < 8; ++q) {
-                        const uint4 b = lds_v4(bs + q * 16);
-                        words[j][q * 2 + 0] = epi_pair_bf16<EPI_BIAS>(v[q * 4 + 0], v[q * 4 + 1], __uint_as_float(b.x), __uint_as_float(b.y));
-                        words[j][q * 2 + 1] = epi_pair_bf16<EPI_BIAS>(v[q * 4 + 2], v[q * 4 + 3], __uint_as_float(b.z), __uint_as_float(b.w));
-                    }
-                }
-                tc_fence_before_sync();
-                mbar_arrive(bar_acc_empty + 8 * ab);  // the accumulator is in registers
-                mbar_wait(bar_t_empty + 8 * ab, ((g >> 1) & 1) ^ 1);  // the head two back has finished with this buffer
-                const uint32_t tile = smem_t + ab * 3 * T_TILE;
-#pragma unroll
-                for (int j = 0; j < 3; ++j) stage_words_bf16(tile + j * T_TILE, row, words[j]);
-                fence_proxy_async_smem();
-                mbar_arrive(bar_t_full + 8 * ab);
-            }
-        }
-    } else if (warp >= QA_SOFTMAX_WARP0) {
-        // ------------------------------ softmax ------------------------------
-        const int quad = warp & 3;
-        const int row = quad * 32 + lane;  // query row inside the item = TMEM lane
-        const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
-        uint32_t uc = 0;  // units processed so far by this CTA (buffer uc & 1, phase (uc >> 1) & 1)
+        const uint32_t tile = smem_t + G * 3 * T_TILE, ptile = smem_p + G * P_UNIT;
+        uint32_t hc = 0;  // heads done by this group
+        uint32_t ug = 0;  // units done by this group (O buffer ug & 1)
         float o[D];       // running output of the head being retired
 #pragma unroll
         for (int j = 0; j < D; ++j) o[j] = 0.f;
-        // the previous unit of the stream: folded in (and its head finalised if it ended there) after the current
-        // unit's softmax, while the current P.V runs
+        // the group's previous unit: folded in (and its head finalised if it ended there) between the row maximum and
+        // the exponentials of the next unit - its P.V has had that long to finish, and P is free again once it has
         struct Pending {
             bool valid, last;
             uint32_t ur;
@@ -333,17 +316,17 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
         } pend{false, false, 0, 0.f, 0.f, 0, 0, 0};
         auto retire_pending = [&]() {
             const uint32_t ob = pend.ur & 1;
-            mbar_wait(bar_o_full + 8 * ob, (pend.ur >> 1) & 1);
+            mbar_wait(bar_o_full + 8 * (2 * G + ob), (pend.ur >> 1) & 1);
             tc_fence_after_sync();
             {
                 uint32_t v[32];
-                tmem_ld_32x32(t_lane + C::O_COL + ob * D, v);
+                tmem_ld_32x32(t_lane + C::O_COL + G * 64 + ob * D, v);
                 tmem_ld_wait();
 #pragma unroll
                 for (int j = 0; j < 32; ++j) o[j] = fmaf(o[j], pend.corr, __uint_as_float(v[j]));
             }
             tc_fence_before_sync();
-            mbar_arrive(bar_o_empty + 8 * ob);
+            mbar_arrive(bar_o_empty + 8 * (2 * G + ob));
             if (pend.last) {
                 const float inv = 1.0f / pend.l;
                 if (row < pend.len) {
@@ -364,19 +347,45 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
             int start, len;
             if (!take(w, start, len)) continue;
             const int nunits = (len + UNIT - 1) / UNIT;
-            for (int h = 0; h < HEADS; ++h) {
+            for (int h = G; h < HEADS; h += 2, ++hc) {
+                // ---- convert: ACC[G] + bias -> Q / K / V tiles ----
+                mbar_wait(bar_acc_full + 8 * G, hc & 1);
+                tc_fence_after_sync();
+                {
+                    uint32_t words[3][16];
+#pragma unroll
+                    for (int j = 0; j < 3; ++j) {  // q, k, v
+                        uint32_t v[32];
+                        tmem_ld_32x32(t_lane + C::ACC_COL + G * C::ACC_STRIDE + j * D, v);
+                        const uint32_t bs = smem_bias + (j * H + h * D) * 4;
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) {
+                            const uint4 b = lds_v4(bs + q * 16);
+                            words[j][q * 2 + 0] = epi_pair_bf16<EPI_BIAS>(v[q * 4 + 0], v[q * 4 + 1], __uint_as_float(b.x), __uint_as_float(b.y));
+                            words[j][q * 2 + 1] = epi_pair_bf16<EPI_BIAS>(v[q * 4 + 2], v[q * 4 + 3], __uint_as_float(b.z), __uint_as_float(b.w));
+                        }
+                    }
+                    tc_fence_before_sync();
+                    mbar_arrive(bar_acc_empty + 8 * G);  // the accumulator is in registers
+                    mbar_wait(bar_t_empty + 8 * G, (hc & 1) ^ 1);  // the group's previous head has finished with the tiles
+#pragma unroll
+                    for (int j = 0; j < 3; ++j) stage_words_bf16(tile + j * T_TILE, row, words[j]);
+                    fence_proxy_async_smem();
+                    mbar_arrive(bar_t_full + 8 * G);
+                }
+                // ---- softmax ----
                 float m = -INFINITY, l = 0.f;  // the first unit's corr is exp2(-inf) = 0: the previous head's output vanishes
-                for (int u = 0; u < nunits; ++u, ++uc) {
-                    const uint32_t sb = uc & 1;
+                for (int u = 0; u < nunits; ++u, ++ug) {
                     const int nvalid = min(UNIT, len - u * UNIT);  // keys of this unit inside the sentence
-                    mbar_wait(bar_s_full + 8 * sb, (uc >> 1) & 1);
+                    mbar_wait(bar_s_full + 8 * G, ug & 1);
                     tc_fence_after_sync();
                     uint32_t v[UNIT];
-                    tmem_ld_32x32(t_lane + C::S_COL + sb * UNIT, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
-                    tmem_ld_32x32(t_lane + C::S_COL + sb * UNIT + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+                    tmem_ld_32x32(t_lane + C::S_COL + G * UNIT, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+                    tmem_ld_32x32(t_lane + C::S_COL + G * UNIT + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
                     tmem_ld_wait();
                     tc_fence_before_sync();
-                    mbar_arrive(bar_s_empty + 8 * sb);  // S is in registers: the MMA warp may overwrite the buffer
+                    mbar_arrive(bar_s_empty + 8 * G);  // S is in registers: the MMA warp may overwrite the buffer
                     if (nvalid < UNIT) {  // keys past the sentence end -> -inf (exp2 then gives exactly 0)
 #pragma unroll
                         for (int j = 0; j < UNIT; ++j)
@@ -389,9 +398,10 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                     const float m_new = fmaxf(m, mx * p.scale_log2);
                     const float corr = ex2(m - m_new);
                     m = m_new;
+                    if (pend.valid) retire_pending();  // also: the previous P.V is done, the P buffer is free
                     const uint64_t sc2 = pk2(p.scale_log2, p.scale_log2), nm2 = pk2(-m_new, -m_new);
                     uint64_t lb2[4] = {0, 0, 0, 0};
-                    const uint32_t prow = smem_p + sb * P_UNIT + row * 128;
+                    const uint32_t prow = ptile + row * 128;
 #pragma unroll
                     for (int q = 0; q < UNIT / 8; ++q) {
                         uint32_t wd[4];
@@ -414,10 +424,9 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                         lb = (a0 + a1) + (a2 + a3);
                     }
                     fence_proxy_async_smem();
-                    mbar_arrive(bar_p_full + 8 * sb);
+                    mbar_arrive(bar_p_full + 8 * G);
                     l = fmaf(l, corr, lb);
-                    if (pend.valid) retire_pending();
-                    pend.valid = true; pend.last = u == nunits - 1; pend.ur = uc; pend.corr = corr; pend.l = l;
+                    pend.valid = true; pend.last = u == nunits - 1; pend.ur = ug; pend.corr = corr; pend.l = l;
                     pend.start = start; pend.len = len; pend.h = h;
                 }
             }
