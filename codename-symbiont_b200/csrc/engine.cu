@@ -111,7 +111,8 @@ struct b200_embed {
     bool gemm_pair = true;   // plain bf16 GEMMs as CTA pairs (one cta_group::2 MMA per pair); B200_EMBED_GEMM_PAIR=0 for A/B
     bool ffn_fused = false;  // K2f replaces the FFN1 / FFN2 GEMM pair: on whenever it supports the shape (hidden 128 / 256 /
                              // 384, erf-GELU); B200_EMBED_FFN_FUSED=0 for A/B
-    bool qkv_attn = false;   // K23 replaces the QKV GEMM + attention pair (off until B200_EMBED_QKV_ATTN=1 while it is being tuned)
+    bool qkv_attn = true;    // K23 replaces the QKV GEMM + attention pair whenever it supports the call (hidden 128 / 256 / 384,
+                             // head_dim 32, seq_len <= 128); B200_EMBED_QKV_ATTN=0 for A/B
     bool attn_mma = false;  // B200_EMBED_ATTENTION=mma selects the mma.sync attention kernel (A/B checks)
     // weights
     float* arena32 = nullptr;
@@ -560,7 +561,7 @@ int32_t b200_embed_create(const b200_embed_config* cfg, const char* path, uint64
     h->ffn_fused = h->fuse_ln && b200::ffn_fused_supported(H, I, cfg->hidden_act);
     if (const char* v = getenv("B200_EMBED_FFN_FUSED")) h->ffn_fused = h->ffn_fused && std::string(v) != "0";
     if (const char* v = getenv("B200_EMBED_ATTENTION")) h->attn_mma = std::string(v) == "mma";
-    if (const char* v = getenv("B200_EMBED_QKV_ATTN")) h->qkv_attn = std::string(v) == "1";
+    if (const char* v = getenv("B200_EMBED_QKV_ATTN")) h->qkv_attn = std::string(v) != "0";
     if (const char* v = getenv("B200_EMBED_GEMM_PAIR")) h->gemm_pair = std::string(v) != "0";
     h->bn_qkv = b200::gemm_tc_pick_block_n(3 * H, b200::EPI_BIAS);
     h->bn_ffn1 = b200::gemm_tc_pick_block_n(I, h->act_epi);

@@ -211,8 +211,8 @@ def test_device_entry_matches_host_entry(pkg, tiny):
     assert np.array_equal(out.cpu().numpy(), tiny.forward(ids, mask, tt))
     n0 = tiny.kernel_launches()
     tiny.forward(ids, mask, tt)
-    # lengths + scan, embeddings; per layer QKV, attention, attention-output GEMM (+LN), fused FFN; pooling
-    assert tiny.kernel_launches() - n0 == 2 + 1 + shape.num_hidden_layers * 4 + 1
+    # lengths + scan, embeddings; per layer fused QKV + attention, attention-output GEMM (+LN), fused FFN; pooling
+    assert tiny.kernel_launches() - n0 == 2 + 1 + shape.num_hidden_layers * 3 + 1
 
 
 def test_embedding_generator_end_to_end_text(pkg, built, tmp_path):
