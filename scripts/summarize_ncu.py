@@ -40,7 +40,7 @@ if len(rr) > 2:
             f.write("\n")
 # dram bytes per launch of each kernel kind (default c2 workload) -> profiles/traffic.json, read by bench.py
 import json, os
-kind_of = [("ffn_fused_kernel", "ffn_fused"), ("attention_tc_kernel", "attention"), ("embed_layernorm", "embed_ln"),
+kind_of = [("ffn_fused_kernel", "ffn_fused"), ("qkv_attention_kernel", "qkv_attention"), ("attention_tc_kernel", "attention"), ("embed_layernorm", "embed_ln"),
            ("mean_pool", "pool"), ("gemm_tc_kernel<192, 0", "gemm_qkv"), ("gemm_tc_kernel<256, 1", "gemm_ffn1"),
            ("gemm_tc_kernel<192, 4", "gemm_attn_out")]
 if len(rr) > 2:
