@@ -111,8 +111,10 @@ int32_t b200_embed_wait(b200_embed* h, int64_t ticket);
 
 /* Same computation with all four buffers already resident in device memory (replaces the
  * candle-on-CUDA tensors of :189-198 when the caller keeps data on the GPU). Enqueues on `stream`
- * (a cudaStream_t, NULL = the handle's own stream) and returns after enqueueing when stream is
- * non-NULL; input errors are reported by the next synchronising call. */
+ * (a cudaStream_t, NULL = the handle's own stream). With stream == NULL the call synchronises and reports input
+ * errors (ids / type ids out of range, a mask that is not a right-padded prefix) like b200_embed_forward. With a
+ * caller stream it returns after enqueueing and input errors are NOT reported: out-of-range ids are clamped to
+ * row 0 on the device, so validate on the host (or call once with stream == NULL) when the inputs are untrusted. */
 int32_t b200_embed_forward_device(b200_embed* h, const uint32_t* device_ids, const uint32_t* device_mask,
                                   const uint32_t* device_type_ids, int32_t batch, int32_t seq_len,
                                   uint32_t flags, float* device_out, void* stream);
