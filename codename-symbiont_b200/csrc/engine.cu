@@ -111,6 +111,11 @@ struct b200_embed {
     bool gemm_pair = true;   // plain bf16 GEMMs as CTA pairs (one cta_group::2 MMA per pair); B200_EMBED_GEMM_PAIR=0 for A/B
     bool ffn_fused = false;  // K2f replaces the FFN1 / FFN2 GEMM pair: on whenever it supports the shape (hidden 128 / 256 /
                              // 384, erf-GELU); B200_EMBED_FFN_FUSED=0 for A/B
+    // The fused kernels parallelise over sentences (K23) / pairs of 128-row blocks (K2f): with too few of those for the
+    // SMs the unfused kernels, which also split the output columns, finish a call sooner (measured on MiniLM, one
+    // B200: K2f wins from 64 x 128 tokens, K23 from 256 sentences; a single query takes 0.39 ms unfused, 0.55 fused).
+    // 0 = auto by call size, 1 = always when the shape is supported (B200_EMBED_FFN_FUSED / _QKV_ATTN = 1), used by tests.
+    bool force_fused_ffn = false, force_qkv_attn = false;
     bool qkv_attn = true;    // K23 replaces the QKV GEMM + attention pair whenever it supports the call (hidden 128 / 256 / 384,
                              // head_dim 32, seq_len <= 128); B200_EMBED_QKV_ATTN=0 for A/B
     bool attn_mma = false;  // B200_EMBED_ATTENTION=mma selects the mma.sync attention kernel (A/B checks)
@@ -385,7 +390,8 @@ int run_chunk(b200_embed* h, Context& c, cudaStream_t s, const Job& j) {
             bf16 *x = static_cast<bf16*>(w.x), *qkv = static_cast<bf16*>(w.qkv), *ctx = static_cast<bf16*>(w.ctx),
                  *a = static_cast<bf16*>(w.a), *inter = static_cast<bf16*>(w.inter);
             bf16 *x_lo = static_cast<bf16*>(w.x_lo), *a_lo = static_cast<bf16*>(w.a_lo);
-            if (h->qkv_attn && b200::qkv_attention_supported(H, h->heads, j.seq_len)) {
+            if (h->qkv_attn && b200::qkv_attention_supported(H, h->heads, j.seq_len) &&
+                (h->force_qkv_attn || j.batch >= 256)) {
                 CU_TRY(timed(h, c, s, B200_EMBED_KIND_QKV_ATTN, 1, [&] {
                     return b200::launch_qkv_attention(x, lw.qkv_w16, lw.qkv_b, cu, rows, j.batch, j.seq_len, H, h->heads, ctx,
                                                       h->num_sms, s);
@@ -412,7 +418,7 @@ int run_chunk(b200_embed* h, Context& c, cudaStream_t s, const Job& j) {
                     return b200::launch_add_layernorm<float, bf16>(w.y32, x, x_lo, rows, d_rows, lw.ao_g, lw.ao_be, eps, H, a, a_lo, s);
                 }));
             }
-            if (h->ffn_fused) {
+            if (h->ffn_fused && (h->force_fused_ffn || rows >= 64 * 128)) {
                 b200::FfnFusedArgs f{};
                 f.a = a; f.a_lo = a_lo; f.w1 = lw.i_w16; f.w2 = lw.o_w16; f.b1 = lw.i_b; f.b2 = lw.o_b; f.gamma = lw.o_g;
                 f.beta = lw.o_be; f.eps = eps; f.m = rows; f.hidden = H; f.inter = I; f.d_rows = d_rows; f.out = x;
@@ -559,9 +565,15 @@ int32_t b200_embed_create(const b200_embed_config* cfg, const char* path, uint64
     if (const char* v = getenv("B200_EMBED_FUSE_LN")) h->fuse_ln = h->fuse_ln && std::string(v) != "0";
     h->act_epi = b200::EPI_GELU_ERF + cfg->hidden_act;
     h->ffn_fused = h->fuse_ln && b200::ffn_fused_supported(H, I, cfg->hidden_act);
-    if (const char* v = getenv("B200_EMBED_FFN_FUSED")) h->ffn_fused = h->ffn_fused && std::string(v) != "0";
+    if (const char* v = getenv("B200_EMBED_FFN_FUSED")) {
+        h->ffn_fused = h->ffn_fused && std::string(v) != "0";
+        h->force_fused_ffn = std::string(v) == "1";
+    }
     if (const char* v = getenv("B200_EMBED_ATTENTION")) h->attn_mma = std::string(v) == "mma";
-    if (const char* v = getenv("B200_EMBED_QKV_ATTN")) h->qkv_attn = std::string(v) != "0";
+    if (const char* v = getenv("B200_EMBED_QKV_ATTN")) {
+        h->qkv_attn = std::string(v) != "0";
+        h->force_qkv_attn = std::string(v) == "1";
+    }
     if (const char* v = getenv("B200_EMBED_GEMM_PAIR")) h->gemm_pair = std::string(v) != "0";
     h->bn_qkv = b200::gemm_tc_pick_block_n(3 * H, b200::EPI_BIAS);
     h->bn_ffn1 = b200::gemm_tc_pick_block_n(I, h->act_epi);

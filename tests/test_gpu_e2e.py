@@ -1,5 +1,6 @@
 """GPU: the whole path through the C ABI with HOST buffers (the call the reference-side binding makes),
 against the committed golden vectors and the oracle. Gates: BASELINE.md section 5."""
+import os
 import threading
 
 import numpy as np
@@ -72,6 +73,60 @@ def test_golden_tiny(pkg, built, name, fp32):
     check(got, g["expected_oracle_f32"], fp32)
 
 
+@pytest.fixture(scope="module")
+def minilm_fused(pkg, built):
+    """Same weights, with the fused kernels (K23, K2f) forced on for every call size: by default calls this small
+    take the unfused schedule (the switches are read when the handle is created)."""
+    old = {k: os.environ.get(k) for k in ("B200_EMBED_FFN_FUSED", "B200_EMBED_QKV_ATTN")}
+    os.environ["B200_EMBED_FFN_FUSED"] = "1"
+    os.environ["B200_EMBED_QKV_ATTN"] = "1"
+    try:
+        emb = pkg.Embedder.random_init(pkg.weights.MINILM_L6, seed=1234)
+    finally:  # the switches are read at create: restore at once so that no other handle inherits them
+        for k, v in old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+    with emb:
+        yield emb
+
+
+def test_fused_schedule_golden_and_ragged(pkg, minilm, minilm_fused):
+    """K23 + K2f end to end on small calls: the HuggingFace golden, and ragged lengths 2..128 against the f32 oracle
+    and against the unfused schedule of the same weights."""
+    g = load_golden("minilm_b8_s128")
+    n0 = minilm_fused.kernel_launches()
+    got = minilm_fused.forward(g["ids"], g["mask"], g["type_ids"])
+    assert minilm_fused.kernel_launches() - n0 == 2 + 1 + pkg.weights.MINILM_L6.num_hidden_layers * 3 + 1
+    check(got, g["expected_hf_f64"], False)
+    shape = pkg.weights.MINILM_L6
+    lengths = np.array([2, 2, 7, 31, 32, 33, 63, 64, 65, 100, 127, 128, 128, 5, 90, 17, 64, 3])
+    ids, mask, tt = pkg.synth.padded_batch(shape.vocab_size, lengths, 128, seed=9)
+    o, o16 = oracle_pair(minilm, shape)
+    want = o.generate(ids, tt, mask, chunk=8)
+    got = minilm_fused.forward(ids, mask, tt)
+    check(got, want, False, o16.generate(ids, tt, mask, chunk=8), lengths)
+    other = minilm.forward(ids, mask, tt)
+    assert np.abs(got - other).max() <= 4e-3  # two bf16 schedules of the same math
+    assert cos_rows(got, other).min() >= 0.9999
+
+
+def test_auto_schedule_switches_to_fused_kernels(pkg, minilm):
+    """A call with >= 256 sentences and >= 8192 tokens takes K23 + K2f (3 launches per layer); results must agree
+    with the same sentences sent in small calls (unfused schedule)."""
+    shape = pkg.weights.MINILM_L6
+    lengths = pkg.synth.lengths_loguniform(320, 4, 128, seed=3)
+    ids, mask, tt = pkg.synth.padded_batch(shape.vocab_size, lengths, 128, seed=4)
+    n0 = minilm.kernel_launches()
+    big = minilm.forward(ids, mask, tt)
+    assert minilm.kernel_launches() - n0 == 2 + 1 + shape.num_hidden_layers * 3 + 1
+    small = np.concatenate([minilm.forward(ids[i:i + 40], mask[i:i + 40], tt[i:i + 40]) for i in range(0, 320, 40)])
+    assert np.isfinite(big).all()
+    assert np.abs(big - small).max() <= 4e-3
+    assert cos_rows(big, small).min() >= 0.9999
+
+
 @pytest.mark.parametrize("fp32", [False, True])
 def test_golden_minilm(pkg, minilm, fp32):
     """BASELINE config 1 shape (MiniLM-L6, seq 128), HuggingFace fp64 expectation."""
@@ -103,7 +158,12 @@ def test_config3_ragged_8_512_vs_oracle(pkg, minilm):
     check(got, want, False, o16.generate(ids, tt, mask, chunk=8), lengths)
     pi, pt, cu = pkg.synth.pack(ids, mask, tt)
     got_v = minilm.forward_varlen(pi, pt, cu, 512)
-    assert np.array_equal(got, got_v)  # same kernels, same packed layout: bit-identical
+    # The padded call is scheduled by its bound batch * seq_len (8192 tokens: fused FFN), the packed one by its real
+    # token count (unfused): two bf16 schedules of the same math.
+    assert np.abs(got - got_v).max() <= 4e-3 and cos_rows(got, got_v).min() >= 0.9999
+    # Calls that take the same schedule run the same kernels on the same packed layout: bit-identical.
+    p4 = pkg.synth.pack(ids[:4], mask[:4], tt[:4])
+    assert np.array_equal(minilm.forward(ids[:4], mask[:4], tt[:4]), minilm.forward_varlen(p4[0], p4[1], p4[2], 512))
     check(minilm.forward_varlen(pi, pt, cu, 512, flags=pkg.FLAG_FP32), want, True)
 
 
@@ -211,8 +271,9 @@ def test_device_entry_matches_host_entry(pkg, tiny):
     assert np.array_equal(out.cpu().numpy(), tiny.forward(ids, mask, tt))
     n0 = tiny.kernel_launches()
     tiny.forward(ids, mask, tt)
-    # lengths + scan, embeddings; per layer fused QKV + attention, attention-output GEMM (+LN), fused FFN; pooling
-    assert tiny.kernel_launches() - n0 == 2 + 1 + shape.num_hidden_layers * 3 + 1
+    # lengths + scan, embeddings; per layer (a call this small takes the unfused schedule) QKV, attention,
+    # attention-output GEMM (+LN), FFN1, FFN2 (+LN); pooling
+    assert tiny.kernel_launches() - n0 == 2 + 1 + shape.num_hidden_layers * 5 + 1
 
 
 def test_embedding_generator_end_to_end_text(pkg, built, tmp_path):
