@@ -61,9 +61,12 @@ constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;
 
 // W bytes per stage in one CTA (a pair stages half of the tile's rows in each CTA)
 __host__ __device__ constexpr int b_stage_bytes(int block_n, bool pair) { return (pair ? block_n / 2 : block_n) * BLOCK_K * 2; }
-// per-warp epilogue shared memory: 2 output staging buffers (+ a `ring`-stage (hi, lo) residual ring for LN)
+// per-warp epilogue shared memory: 2 output staging buffers (+ a `ring`-stage (hi, lo) residual ring for LN).
+// ring == 1 is the lean LayerNorm epilogue for long K (one residual slot, one staging buffer): with 48 k-blocks per
+// tile the epilogue hides behind the next tile's mainloop anyway, and the 40 KB it gives back are a 4th stage.
+__host__ __device__ constexpr int staging_buffers(int ring) { return ring == 1 ? 1 : 2; }
 __host__ __device__ constexpr int epi_warp_bytes(int epi, bool out_f32, int ring) {
-    return (epi == EPI_RES_LN ? ring * 2 * CHUNK_BF16 : 0) + 2 * (out_f32 ? CHUNK_F32 : CHUNK_BF16);
+    return (epi == EPI_RES_LN ? ring * 2 * CHUNK_BF16 : 0) + staging_buffers(ring) * (out_f32 ? CHUNK_F32 : CHUNK_BF16);
 }
 // mbarriers (<= 8 + 8 stage, 4 TMEM, 24 residual, 2 cluster exchange) + TMEM pointer; then
 //   LayerNorm: partial statistics of the two column halves, the slots peers write their row partials into, and
@@ -123,7 +126,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     constexpr int EPI_WARP_BYTES = epi_warp_bytes(EPI, OUT_F32, RING);
     constexpr bool KEEP_IN_REGS = NCH <= 3;  // LN: hold acc + bias + residual in registers between the two passes
     constexpr int OUT_CHUNK_BYTES = OUT_F32 ? CHUNK_F32 : CHUNK_BF16;
-    static_assert(RING >= 2 && RING <= 3, "residual ring depth");
+    static_assert(RING >= 1 && RING <= 3, "residual ring depth");
+    constexpr int STG = staging_buffers(RING);
     static_assert(BLOCK_N % 16 == 0 && BLOCK_N <= 256, "invalid UMMA N / TMEM double buffering needs 2 * BLOCK_N <= 512");
     static_assert(HALF_N % CHUNK == 0, "epilogue works in 32-column chunks");
     static_assert(STAGES >= 2, "not enough shared memory for a pipeline");
@@ -310,9 +314,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         };
         // hands a staged chunk to the TMA store engine; at most one older store may still be reading its buffer
         auto stage_begin = [&]() {
-            if (lane == 0) tma_store_wait_read<1>();
+            if (lane == 0) tma_store_wait_read<STG - 1>();
             __syncwarp();
-            return out_buf + (st_it & 1) * OUT_CHUNK_BYTES;
+            return out_buf + (st_it % STG) * OUT_CHUNK_BYTES;
         };
         auto stage_end = [&](const CUtensorMap* map, uint32_t buf, int col0, int row0) {
             fence_proxy_async_smem();
@@ -649,6 +653,10 @@ cudaError_t gemm_tc_launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms
         if (a.block_n == 256 && cl == 1) return launch<256, EPI_RES_LN, __nv_bfloat16, 1>(a, stream, num_sms);
         // short K: the epilogue is the critical path -> deeper residual prefetch, fewer mainloop stages
         if (a.block_n == 192 && cl == 2 && a.k <= 768) return launch<192, EPI_RES_LN, __nv_bfloat16, 2, false, 3>(a, stream, num_sms);
+        // long K: the mainloop is the critical path -> lean epilogue, one more mainloop stage
+        const bool lean = a.k >= 1536 && getenv("B200_EMBED_LN_LEAN_OFF") == nullptr;
+        if (a.block_n == 192 && cl == 2 && lean) return launch<192, EPI_RES_LN, __nv_bfloat16, 2, false, 1>(a, stream, num_sms);
+        if (a.block_n == 192 && cl == 4 && lean) return launch<192, EPI_RES_LN, __nv_bfloat16, 4, false, 1>(a, stream, num_sms);
         if (a.block_n == 192 && cl == 2) return launch<192, EPI_RES_LN, __nv_bfloat16, 2>(a, stream, num_sms);
         if (a.block_n == 256 && cl == 2) return launch<256, EPI_RES_LN, __nv_bfloat16, 2>(a, stream, num_sms);
         if (a.block_n == 192 && cl == 4) return launch<192, EPI_RES_LN, __nv_bfloat16, 4>(a, stream, num_sms);

@@ -7,11 +7,11 @@ from __graft_entry__ import load_package
 pkg = load_package()
 rows = int(sys.argv[1]) if len(sys.argv) > 1 else 524288
 reps = int(sys.argv[2]) if len(sys.argv) > 2 else 5
-shape = pkg.weights.BertShape(512, 384, 1, 12, 1536, 64, 2)
+H = int(os.environ.get("LN_H", "384")); shape = pkg.weights.BertShape(512, H, 1, 12, 4 * H, 64, 2)
 with pkg.Embedder.random_init(shape, seed=4) as emb:
-    for which, k in ((1, 384), (3, 1536)):
+    for which, k in ((1, H), (3, 4 * H)):
         x = torch.randn((rows, k), device="cuda").bfloat16()
-        r = torch.randn((rows, 384), device="cuda").bfloat16(); rl = torch.zeros_like(r)
+        r = torch.randn((rows, H), device="cuda").bfloat16(); rl = torch.zeros_like(r)
         y = torch.empty_like(r); yl = torch.empty_like(r)
         f = lambda: emb.op_linear(0, which, x.data_ptr(), r.data_ptr(), rows, 0, y.data_ptr(), rl.data_ptr(), yl.data_ptr())
         f(); f(); torch.cuda.synchronize()
