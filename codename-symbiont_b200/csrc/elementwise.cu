@@ -194,7 +194,7 @@ embed_layernorm_kernel(const uint32_t* __restrict__ ids, const uint32_t* __restr
         if (j[t] >= max_pos) { bad = true; j[t] = 0; }
     }
     if (bad && lane == 0) atomicOr(status, 2);
-    const int nchunk = H >> 7;
+    constexpr int nchunk = NCH;  // H == 128 * NCH: no predicated chunks
     float4 v[TOK][NCH];
 #pragma unroll
     for (int t = 0; t < TOK; ++t) {
@@ -307,7 +307,8 @@ cudaError_t launch_embed_layernorm(const EmbedArgs& a, cudaStream_t s) {
     const long long slots = a.padded ? static_cast<long long>(a.batch) * a.seq_len : a.total_tokens;
     if (slots <= 0) return cudaSuccess;
     // two tokens per warp (measured at H = 384: 0.51 ms with one, 0.41 with two, 0.50 with four per warp)
-    const int nch = a.H <= 256 ? 2 : (a.H <= 384 ? 3 : (a.H <= 512 ? 4 : 8));
+    const int nch = a.H / 128;
+    if (a.H % 128 != 0 || nch < 1 || nch > MAX_CHUNKS) return cudaErrorInvalidValue;
     const int tok = nch <= 4 ? 2 : 1;
     const unsigned grid = static_cast<unsigned>((slots + 8LL * tok - 1) / (8LL * tok));
 #define B200_EMBED_LAUNCH(PAD, TOK, NCH)                                                                                   \
@@ -315,10 +316,16 @@ cudaError_t launch_embed_layernorm(const EmbedArgs& a, cudaStream_t s) {
         a.ids, a.type_ids, a.cu, a.batch, a.seq_len, a.total_tokens, a.word, a.pos, a.type, a.gamma, a.beta, a.eps, a.H,  \
         a.vocab, a.type_vocab, a.max_pos, static_cast<T*>(a.out), static_cast<T*>(a.out_lo), a.status)
 #define B200_EMBED_PICK(PAD)                                    \
-    if (nch == 2) B200_EMBED_LAUNCH(PAD, 2, 2);                 \
-    else if (nch == 3) B200_EMBED_LAUNCH(PAD, 2, 3);            \
-    else if (nch == 4) B200_EMBED_LAUNCH(PAD, 2, 4);            \
-    else B200_EMBED_LAUNCH(PAD, 1, 8)
+    switch (nch) {                                              \
+        case 1: B200_EMBED_LAUNCH(PAD, 2, 1); break;            \
+        case 2: B200_EMBED_LAUNCH(PAD, 2, 2); break;            \
+        case 3: B200_EMBED_LAUNCH(PAD, 2, 3); break;            \
+        case 4: B200_EMBED_LAUNCH(PAD, 2, 4); break;            \
+        case 5: B200_EMBED_LAUNCH(PAD, 1, 5); break;            \
+        case 6: B200_EMBED_LAUNCH(PAD, 1, 6); break;            \
+        case 7: B200_EMBED_LAUNCH(PAD, 1, 7); break;            \
+        default: B200_EMBED_LAUNCH(PAD, 1, 8); break;           \
+    }
     if (a.padded) { B200_EMBED_PICK(true); } else { B200_EMBED_PICK(false); }
 #undef B200_EMBED_PICK
 #undef B200_EMBED_LAUNCH
