@@ -139,6 +139,71 @@ __global__ void scan_lengths_kernel(const int* __restrict__ lens, int batch, int
     }
 }
 
+// Tiles for K23: consecutive whole sentences with at most `cap` tokens together (a longer sentence gets a tile of its
+// own; K23 is only used when none is). tile_first[t] = first sentence of tile t, tile_first[n_tiles] = batch.
+// Greedy packing is sequential, so it runs per SEGMENT of 32 sentences (a tile never crosses a segment boundary: at
+// most one tile per segment is cut short) by one thread each; counts are scanned in shared memory by the single
+// block, which then writes the compacted list. seg_off: [ceil(batch / 32) + 1] scratch.
+constexpr int PACK_SEG = 32;
+__device__ __forceinline__ int pack_segment(const int* __restrict__ cu, int b0, int b1, int cap, int* __restrict__ out) {
+    int n = 0, first = b0;
+    int base = cu[b0];
+    for (int b = b0; b < b1; ++b) {
+        const int end = cu[b + 1];
+        if (end - base > cap && b > first) {  // sentence b does not fit: it starts the next tile
+            if (out) out[n] = first;
+            ++n;
+            first = b;
+            base = cu[b];
+        }
+    }
+    if (out) out[n] = first;
+    return n + 1;
+}
+__global__ void pack_tiles_kernel(const int* __restrict__ cu, int batch, int cap, int* __restrict__ seg_off,
+                                  int* __restrict__ tile_first, int* __restrict__ n_tiles) {
+    __shared__ int warp_tot[32];
+    __shared__ int carry;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int nseg = (batch + PACK_SEG - 1) / PACK_SEG;
+    if (threadIdx.x == 0) { carry = 0; seg_off[0] = 0; }
+    __syncthreads();
+    for (int base = 0; base < nseg; base += blockDim.x) {  // count tiles per segment, exclusive scan into seg_off
+        const int sg = base + threadIdx.x;
+        const int v = sg < nseg ? pack_segment(cu, sg * PACK_SEG, min(batch, (sg + 1) * PACK_SEG), cap, nullptr) : 0;
+        int x = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int y = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= o) x += y;
+        }
+        if (lane == 31) warp_tot[warp] = x;
+        __syncthreads();
+        if (warp == 0) {
+            int w = lane < (blockDim.x >> 5) ? warp_tot[lane] : 0;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int y = __shfl_up_sync(0xffffffffu, w, o);
+                if (lane >= o) w += y;
+            }
+            warp_tot[lane] = w;
+        }
+        __syncthreads();
+        const int prefix = carry + (warp > 0 ? warp_tot[warp - 1] : 0) + x;  // inclusive
+        if (sg < nseg) seg_off[sg + 1] = prefix;
+        __syncthreads();
+        if (threadIdx.x == blockDim.x - 1) carry = prefix;
+        __syncthreads();
+    }
+    for (int sg = threadIdx.x; sg < nseg; sg += blockDim.x)  // same walk again, now writing the compacted list
+        pack_segment(cu, sg * PACK_SEG, min(batch, (sg + 1) * PACK_SEG), cap, tile_first + seg_off[sg]);
+    if (threadIdx.x == 0) {
+        const int n = carry;
+        *n_tiles = n;
+        tile_first[n] = batch;
+    }
+}
+
 // ---- K1 -------------------------------------------------------------------------------------------
 // One warp per TOK consecutive token slots. PADDED: slots are [batch, seq_len] positions, pad positions are skipped,
 // the row is written packed at cu[b] + j. Packed: slots are tokens, sentence found by binary search in cu.
@@ -299,6 +364,13 @@ cudaError_t launch_mask_lengths(const uint32_t* mask, int batch, int seq_len, in
     if (batch <= 0) return cudaSuccess;
     mask_lengths_kernel<<<(batch + 7) / 8, 256, 0, s>>>(mask, batch, seq_len, lens, status);
     scan_lengths_kernel<<<1, 1024, 0, s>>>(lens, batch, cu);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_pack_tiles(const int* cu, int batch, int cap, int* seg_off, int* tile_first, int* n_tiles,
+                              cudaStream_t s) {
+    if (batch <= 0) return cudaSuccess;
+    pack_tiles_kernel<<<1, 1024, 0, s>>>(cu, batch, cap, seg_off, tile_first, n_tiles);
     return cudaGetLastError();
 }
 

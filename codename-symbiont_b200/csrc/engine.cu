@@ -85,6 +85,7 @@ struct Context {
     uint32_t *d_ids = nullptr, *d_mask = nullptr, *d_tt = nullptr;
     size_t in_cap = 0;
     int *d_lens = nullptr, *d_cu = nullptr;
+    int *d_tile_first = nullptr, *d_seg_off = nullptr, *d_n_tiles = nullptr;  // K23 work list (launch_pack_tiles)
     size_t b_cap = 0;
     float* d_out = nullptr;
     size_t out_cap = 0;
@@ -174,7 +175,8 @@ void destroy_context(Context& c) {
     c.ws32.release();
     for (void* p : {static_cast<void*>(c.d_ids), static_cast<void*>(c.d_mask), static_cast<void*>(c.d_tt),
                     static_cast<void*>(c.d_lens), static_cast<void*>(c.d_cu), static_cast<void*>(c.d_out),
-                    static_cast<void*>(c.d_status)})
+                    static_cast<void*>(c.d_status), static_cast<void*>(c.d_tile_first), static_cast<void*>(c.d_seg_off),
+                    static_cast<void*>(c.d_n_tiles)})
         if (p) cudaFree(p);
     if (c.h_status) cudaFreeHost(c.h_status);
     for (cudaEvent_t e : c.ev_pool) cudaEventDestroy(e);
@@ -262,7 +264,7 @@ int ensure_input_bufs(Context& c, size_t n) {
 
 int ensure_batch_bufs(Context& c, size_t nb) {
     if (nb + 2 <= c.b_cap) return B200_EMBED_OK;
-    for (int** p : {&c.d_lens, &c.d_cu}) {
+    for (int** p : {&c.d_lens, &c.d_cu, &c.d_tile_first, &c.d_seg_off, &c.d_n_tiles}) {
         if (*p) cudaFree(*p);
         *p = nullptr;
     }
@@ -270,6 +272,9 @@ int ensure_batch_bufs(Context& c, size_t nb) {
     const size_t want = nb + nb / 4 + 2;
     CU_TRY(cudaMalloc(&c.d_lens, want * 4));
     CU_TRY(cudaMalloc(&c.d_cu, want * 4));
+    CU_TRY(cudaMalloc(&c.d_tile_first, want * 4));
+    CU_TRY(cudaMalloc(&c.d_seg_off, (want / 32 + 2) * 4));
+    CU_TRY(cudaMalloc(&c.d_n_tiles, 4));
     c.b_cap = want;
     return B200_EMBED_OK;
 }
@@ -349,6 +354,13 @@ int run_chunk(b200_embed* h, Context& c, cudaStream_t s, const Job& j) {
         cu = c.d_cu;
     }
     const int* d_rows = cu + j.batch;
+    // K23 (fused Q/K/V projection + attention) works on tiles of whole sentences: list them once per call
+    const bool use_k23 = !fp32 && h->qkv_attn && b200::qkv_attention_supported(H, h->heads, j.seq_len) &&
+                         (h->force_qkv_attn || j.batch >= 256);
+    if (use_k23)
+        CU_TRY(timed(h, c, s, B200_EMBED_KIND_LENGTHS, 1, [&] {
+            return b200::launch_pack_tiles(cu, j.batch, 128, c.d_seg_off, c.d_tile_first, c.d_n_tiles, s);
+        }));
 
     b200::EmbedArgs e{};
     e.ids = j.d_ids; e.type_ids = j.d_tt; e.cu = cu; e.batch = j.batch; e.seq_len = j.seq_len;
@@ -390,11 +402,10 @@ int run_chunk(b200_embed* h, Context& c, cudaStream_t s, const Job& j) {
             bf16 *x = static_cast<bf16*>(w.x), *qkv = static_cast<bf16*>(w.qkv), *ctx = static_cast<bf16*>(w.ctx),
                  *a = static_cast<bf16*>(w.a), *inter = static_cast<bf16*>(w.inter);
             bf16 *x_lo = static_cast<bf16*>(w.x_lo), *a_lo = static_cast<bf16*>(w.a_lo);
-            if (h->qkv_attn && b200::qkv_attention_supported(H, h->heads, j.seq_len) &&
-                (h->force_qkv_attn || j.batch >= 256)) {
+            if (use_k23) {
                 CU_TRY(timed(h, c, s, B200_EMBED_KIND_QKV_ATTN, 1, [&] {
-                    return b200::launch_qkv_attention(x, lw.qkv_w16, lw.qkv_b, cu, rows, j.batch, j.seq_len, H, h->heads, ctx,
-                                                      h->num_sms, s);
+                    return b200::launch_qkv_attention(x, lw.qkv_w16, lw.qkv_b, cu, c.d_tile_first, c.d_n_tiles, rows, j.batch,
+                                                      j.seq_len, H, h->heads, ctx, h->num_sms, s);
                 }));
             } else {
                 rc = gemm16(h, c, s, B200_EMBED_KIND_GEMM_QKV, x, lw.qkv_w16, lw.qkv_b, rows, d_rows, 3 * H, H,
@@ -1014,9 +1025,18 @@ int32_t b200_op_qkv_attention(b200_embed* h, int32_t layer, const void* x, const
         return fail(B200_EMBED_ERR_UNSUPPORTED_SHAPE, "fused QKV + attention: hidden 128/256/384, head_dim 32, seq <= 128");
     DeviceGuard guard(h->device);
     const LayerW& w = h->layers[layer];
-    h->launches.fetch_add(1);
-    CU_TRY(b200::launch_qkv_attention(static_cast<const bf16*>(x), w.qkv_w16, w.qkv_b, cu, rows, batch, max_seqlen, h->H,
-                                      h->heads, static_cast<bf16*>(ctx), h->num_sms, static_cast<cudaStream_t>(stream)));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    int* tmp = nullptr;  // tile list of this call: tile_first [batch + 1] | n_tiles | seg_off [batch / 32 + 2]
+    const size_t n_ints = static_cast<size_t>(batch) + 2 + static_cast<size_t>(batch) / 32 + 2;
+    CU_TRY(cudaMalloc(&tmp, n_ints * 4));
+    h->launches.fetch_add(2);
+    cudaError_t e = b200::launch_pack_tiles(cu, batch, 128, tmp + batch + 2, tmp, tmp + batch + 1, s);
+    if (e == cudaSuccess)
+        e = b200::launch_qkv_attention(static_cast<const bf16*>(x), w.qkv_w16, w.qkv_b, cu, tmp, tmp + batch + 1, rows, batch,
+                                       max_seqlen, h->H, h->heads, static_cast<bf16*>(ctx), h->num_sms, s);
+    cudaStreamSynchronize(s);
+    cudaFree(tmp);
+    CU_TRY(e);
     return B200_EMBED_OK;
 }
 

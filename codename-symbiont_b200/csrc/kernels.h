@@ -46,10 +46,14 @@ cudaError_t launch_attention_tc(const __nv_bfloat16* qkv, const int* cu, int row
 
 // K23 (qkv_attention.cu): Q/K/V projection + attention of whole sentences in one kernel: ctx from x (hi) directly, the
 // packed qkv tensor never exists. hidden 128 / 256 / 384 with head_dim 32, sentences of at most 128 tokens.
+// Its work items are tiles of whole sentences with at most 128 tokens together, listed by launch_pack_tiles
+// (tile_first [batch + 1], n_tiles device scalar, seg_off [batch / 32 + 2] scratch; cap = 128).
 bool qkv_attention_supported(int hidden, int heads, int max_seqlen);
+cudaError_t launch_pack_tiles(const int* cu, int batch, int cap, int* seg_off, int* tile_first, int* n_tiles,
+                              cudaStream_t s);
 cudaError_t launch_qkv_attention(const __nv_bfloat16* x, const __nv_bfloat16* wqkv, const float* bqkv, const int* cu,
-                                 int rows_cap, int batch, int max_seqlen, int hidden, int heads, __nv_bfloat16* ctx,
-                                 int num_sms, cudaStream_t s);
+                                 const int* tile_first, const int* n_tiles, int rows_cap, int batch, int max_seqlen,
+                                 int hidden, int heads, __nv_bfloat16* ctx, int num_sms, cudaStream_t s);
 
 // K2f (ffn_fused.cu): x' = LayerNorm(gelu(a.W1^T + b1).W2^T + b2 + a) in one kernel; hidden 128 / 256 / 384, erf-GELU.
 struct FfnFusedArgs {

@@ -8,9 +8,10 @@
 // GEMM followed by K3 the packed [tokens, 3H] qkv tensor costs an HBM write and a read (2.4 GB per layer at c2) and the
 // GEMM is bound by exactly that write; here q, k, v never leave the SM.
 //
-// Work item = sentence. A persistent CTA (one per SM) keeps the sentence's activation tile x[128, H] resident in
-// shared memory (rows past the sentence end belong to the next sentence or are zero-filled: they are computed and
-// never used) and walks its heads. Two GROUPS of four warps take alternate heads (even / odd; the head count is even)
+// Work item = a TILE of up to 128 token rows holding whole sentences (one sentence of 65..128 tokens, or several short
+// ones packed by pack_tiles_kernel; attention is then block-diagonal: every row only sees the keys of its own
+// sentence). A persistent CTA (one per SM) keeps the tile's activations x[128, H] resident in shared memory (rows past
+// the tile's tokens belong to the next tile or are zero-filled: they are computed and never used) and walks its heads. Two GROUPS of four warps take alternate heads (even / odd; the head count is even)
 // and each does everything the head needs outside the tensor pipe:
 //   warp 0      TMA producer: the x tile once per sentence; per head KB blocks of Wqkv rows {h*d.., H + h*d.., 2H + h*d..}
 //               x 64 columns (three 4 KB boxes = one 96-row K-major B operand) through a small ring
@@ -71,6 +72,8 @@ struct QaCfg {
 
 struct QaDev {
     const int* cu;
+    const int* tile_first;  // [n_tiles + 1] first sentence of every tile
+    const int* n_tiles;     // device scalar
     const float* bias;  // [3H]
     int batch, H;
     float scale_log2;
@@ -131,30 +134,45 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot_ptr;
 
-    // Every role walks the same sentence sequence b = blockIdx.x, + gridDim.x, ...; empty sentences are skipped by all.
-    // The bounds of the NEXT sentence are fetched while the current one is processed.
-    struct Walk { int b, s0, s1; };
+    // Work items are TILES: runs of whole sentences that together have at most 128 tokens (built on the device by
+    // pack_tiles_kernel; a sentence of 65..128 tokens is a tile of its own, short ones share one). Every role walks the
+    // same tile sequence b = blockIdx.x, + gridDim.x, ...; empty tiles are skipped by all. The bounds of the NEXT tile are
+    // fetched while the current one is processed.
+    const int n_items = min(__ldg(p.n_tiles), p.batch);
+    struct Walk { int b, first, last, s0, s1; };
     auto fetch = [&](Walk& w) {
-        if (w.b < p.batch) { w.s0 = __ldg(p.cu + w.b); w.s1 = __ldg(p.cu + w.b + 1); }
+        if (w.b < n_items) {
+            w.first = __ldg(p.tile_first + w.b);
+            w.last = __ldg(p.tile_first + w.b + 1);
+            w.s0 = __ldg(p.cu + w.first);
+            w.s1 = __ldg(p.cu + w.last);
+        }
     };
     auto walk_init = [&]() {
-        Walk w{static_cast<int>(blockIdx.x), 0, 0};
+        Walk w{static_cast<int>(blockIdx.x), 0, 0, 0, 0};
         fetch(w);
         return w;
     };
-    auto take = [&](Walk& w, int& start, int& len) {  // current sentence -> (start, len); advances w
+    // current tile -> (first token row, rows); advances w
+    auto take2 = [&](Walk& w, int& start, int& len, int& first, int& last) {
         start = w.s0;
         len = min(w.s1 - w.s0, BLK);
+        first = w.first;
+        last = w.last;
         w.b += gridDim.x;
         fetch(w);
         return len > 0;
+    };
+    auto take = [&](Walk& w, int& start, int& len) {
+        int f, l;
+        return take2(w, start, len, f, l);
     };
 
     if (warp == 0) {
         // ------------------------------ TMA producer ------------------------------
         uint32_t it = 0, wb = 0;  // sentences taken, W blocks loaded (ring slot wb % WS)
         Walk w = walk_init();
-        while (w.b < p.batch) {
+        while (w.b < n_items) {
             int start, len;
             if (!take(w, start, len)) continue;
             mbar_wait(bar_x_empty, (it & 1) ^ 1);
@@ -199,7 +217,7 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
             if (ph == HEADS) {
                 int a, b;
                 bool ok = false;
-                while (wp.b < p.batch) {
+                while (wp.b < n_items) {
                     if (take(wp, a, b)) { ok = true; break; }
                 }
                 if (!ok) return false;
@@ -269,7 +287,7 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
         bool more = proj_head();
         if (more) more = proj_head();
         Walk w = walk_init();
-        while (w.b < p.batch) {
+        while (w.b < n_items) {
             int start, len;
             if (!take(w, start, len)) continue;
             const int nunits = (len + UNIT - 1) / UNIT;
@@ -343,10 +361,21 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
             pend.valid = false;
         };
         Walk w = walk_init();
-        while (w.b < p.batch) {
-            int start, len;
-            if (!take(w, start, len)) continue;
+        while (w.b < n_items) {
+            int start, len, first, last;
+            if (!take2(w, start, len, first, last)) continue;
             const int nunits = (len + UNIT - 1) / UNIT;
+            // keys [klo, khi) of the tile are this row's own sentence (rows past the tile's tokens: none)
+            int klo = 0, khi = row < len ? len : 0;
+            if (last - first > 1 && row < len) {  // several sentences share the tile: find mine
+                int a = first, b = last;          // cu[a] - start <= row < cu[b] - start
+                while (b - a > 1) {
+                    const int mid = (a + b) >> 1;
+                    if (__ldg(p.cu + mid) - start <= row) a = mid; else b = mid;
+                }
+                klo = __ldg(p.cu + a) - start;
+                khi = __ldg(p.cu + b) - start;
+            }
             for (int h = G; h < HEADS; h += 2, ++hc) {
                 // ---- convert: ACC[G] + bias -> Q / K / V tiles ----
                 mbar_wait(bar_acc_full + 8 * G, hc & 1);
@@ -377,7 +406,8 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                 // ---- softmax ----
                 float m = -INFINITY, l = 0.f;  // the first unit's corr is exp2(-inf) = 0: the previous head's output vanishes
                 for (int u = 0; u < nunits; ++u, ++ug) {
-                    const int nvalid = min(UNIT, len - u * UNIT);  // keys of this unit inside the sentence
+                    // this unit's keys u*64 + j, j in [jlo, jhi), belong to the row's sentence
+                    const int jlo = min(max(klo - u * UNIT, 0), UNIT), jhi = min(max(khi - u * UNIT, 0), UNIT);
                     mbar_wait(bar_s_full + 8 * G, ug & 1);
                     tc_fence_after_sync();
                     uint32_t v[UNIT];
@@ -386,20 +416,24 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                     tmem_ld_wait();
                     tc_fence_before_sync();
                     mbar_arrive(bar_s_empty + 8 * G);  // S is in registers: the MMA warp may overwrite the buffer
-                    if (nvalid < UNIT) {  // keys past the sentence end -> -inf (exp2 then gives exactly 0)
+                    if (jlo > 0 || jhi < UNIT) {  // keys of other sentences / past the end -> -inf (exp2 then gives exactly 0)
+                        const uint32_t span = static_cast<uint32_t>(jhi - jlo);
 #pragma unroll
                         for (int j = 0; j < UNIT; ++j)
-                            if (j >= nvalid) v[j] = 0xff800000u;
+                            if (static_cast<uint32_t>(j - jlo) >= span) v[j] = 0xff800000u;
                     }
                     float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
                     for (int j = 0; j < UNIT; ++j) mx4[j & 3] = fmaxf(mx4[j & 3], __uint_as_float(v[j]));
                     const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
                     const float m_new = fmaxf(m, mx * p.scale_log2);
-                    const float corr = ex2(m - m_new);
+                    // a row with no key yet (its sentence lies in the other unit, or the row is past the tile's tokens)
+                    // keeps m = -inf; 0 stands in for it below so that exp2 sees -inf, not inf - inf
+                    const float m_use = m_new == -INFINITY ? 0.f : m_new;
+                    const float corr = ex2(m - m_use);
                     m = m_new;
                     if (pend.valid) retire_pending();  // also: the previous P.V is done, the P buffer is free
-                    const uint64_t sc2 = pk2(p.scale_log2, p.scale_log2), nm2 = pk2(-m_new, -m_new);
+                    const uint64_t sc2 = pk2(p.scale_log2, p.scale_log2), nm2 = pk2(-m_use, -m_use);
                     uint64_t lb2[4] = {0, 0, 0, 0};
                     const uint32_t prow = ptile + row * 128;
 #pragma unroll
@@ -443,8 +477,9 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
 }
 
 template <int H, int D>
-cudaError_t launch_qa(const __nv_bfloat16* x, const __nv_bfloat16* wqkv, const float* bqkv, const int* cu, int rows_cap,
-                      int batch, __nv_bfloat16* ctx, int num_sms, cudaStream_t s) {
+cudaError_t launch_qa(const __nv_bfloat16* x, const __nv_bfloat16* wqkv, const float* bqkv, const int* cu,
+                      const int* tile_first, const int* n_tiles, int rows_cap, int batch, __nv_bfloat16* ctx, int num_sms,
+                      cudaStream_t s) {
     using C = QaCfg<H, D>;
     alignas(64) CUtensorMap tx, tw;
     if (!make_tmap(&tx, x, rows_cap, H, BK, BLK, false, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
@@ -457,7 +492,7 @@ cudaError_t launch_qa(const __nv_bfloat16* x, const __nv_bfloat16* wqkv, const f
         attr_set = true;
     }
     QaDev p;
-    p.cu = cu; p.bias = bqkv; p.batch = batch; p.H = H; p.ctx = ctx;
+    p.cu = cu; p.tile_first = tile_first; p.n_tiles = n_tiles; p.bias = bqkv; p.batch = batch; p.H = H; p.ctx = ctx;
     p.scale_log2 = 1.4426950408889634f / sqrtf(static_cast<float>(D));
     const int grid = batch < num_sms ? batch : num_sms;
     if (grid <= 0) return cudaSuccess;
@@ -472,13 +507,13 @@ bool qkv_attention_supported(int hidden, int heads, int max_seqlen) {
 }
 
 cudaError_t launch_qkv_attention(const __nv_bfloat16* x, const __nv_bfloat16* wqkv, const float* bqkv, const int* cu,
-                                 int rows_cap, int batch, int max_seqlen, int hidden, int heads, __nv_bfloat16* ctx,
-                                 int num_sms, cudaStream_t s) {
+                                 const int* tile_first, const int* n_tiles, int rows_cap, int batch, int max_seqlen,
+                                 int hidden, int heads, __nv_bfloat16* ctx, int num_sms, cudaStream_t s) {
     if (batch <= 0 || max_seqlen <= 0) return cudaSuccess;
     if (!qkv_attention_supported(hidden, heads, max_seqlen)) return cudaErrorInvalidValue;
-    if (hidden == 384) return launch_qa<384, 32>(x, wqkv, bqkv, cu, rows_cap, batch, ctx, num_sms, s);
-    if (hidden == 256) return launch_qa<256, 32>(x, wqkv, bqkv, cu, rows_cap, batch, ctx, num_sms, s);
-    return launch_qa<128, 32>(x, wqkv, bqkv, cu, rows_cap, batch, ctx, num_sms, s);
+    if (hidden == 384) return launch_qa<384, 32>(x, wqkv, bqkv, cu, tile_first, n_tiles, rows_cap, batch, ctx, num_sms, s);
+    if (hidden == 256) return launch_qa<256, 32>(x, wqkv, bqkv, cu, tile_first, n_tiles, rows_cap, batch, ctx, num_sms, s);
+    return launch_qa<128, 32>(x, wqkv, bqkv, cu, tile_first, n_tiles, rows_cap, batch, ctx, num_sms, s);
 }
 
 }  // namespace b200

@@ -98,7 +98,8 @@ def test_fused_schedule_golden_and_ragged(pkg, minilm, minilm_fused):
     g = load_golden("minilm_b8_s128")
     n0 = minilm_fused.kernel_launches()
     got = minilm_fused.forward(g["ids"], g["mask"], g["type_ids"])
-    assert minilm_fused.kernel_launches() - n0 == 2 + 1 + pkg.weights.MINILM_L6.num_hidden_layers * 3 + 1
+    # lengths + scan, tile list, embeddings; per layer K23, attention-output GEMM (+LN), K2f; pooling
+    assert minilm_fused.kernel_launches() - n0 == 2 + 1 + 1 + pkg.weights.MINILM_L6.num_hidden_layers * 3 + 1
     check(got, g["expected_hf_f64"], False)
     shape = pkg.weights.MINILM_L6
     lengths = np.array([2, 2, 7, 31, 32, 33, 63, 64, 65, 100, 127, 128, 128, 5, 90, 17, 64, 3])
@@ -120,7 +121,7 @@ def test_auto_schedule_switches_to_fused_kernels(pkg, minilm):
     ids, mask, tt = pkg.synth.padded_batch(shape.vocab_size, lengths, 128, seed=4)
     n0 = minilm.kernel_launches()
     big = minilm.forward(ids, mask, tt)
-    assert minilm.kernel_launches() - n0 == 2 + 1 + shape.num_hidden_layers * 3 + 1
+    assert minilm.kernel_launches() - n0 == 2 + 1 + 1 + shape.num_hidden_layers * 3 + 1
     small = np.concatenate([minilm.forward(ids[i:i + 40], mask[i:i + 40], tt[i:i + 40]) for i in range(0, 320, 40)])
     assert np.isfinite(big).all()
     assert np.abs(big - small).max() <= 4e-3
@@ -221,16 +222,25 @@ def test_chunked_launches_match_single_launch(pkg):
 
 def test_permutation_and_padding_invariance_at_scale(pkg, minilm):
     """Size-independent properties at a BASELINE-sized batch (config 2 shape, 4096 x 128 dense is run by
-    bench.py; here 1024 ragged sentences): shuffling sentences shuffles rows bit-exactly, and extra right
-    padding changes nothing."""
+    bench.py; here ragged sentences): shuffling sentences shuffles rows, and extra right padding changes nothing.
+    Bit-exact where every sentence is computed on its own (unfused schedule, < 256 sentences); with K23 short sentences
+    share a 128-row tile, so a sentence's rounding depends on its neighbours: two bf16 runs of the same math."""
     shape = pkg.weights.MINILM_L6
-    lengths = pkg.synth.lengths_uniform(1024, 8, 128, seed=3)
+    wide = lambda a: np.concatenate([a, np.zeros((a.shape[0], 64), np.uint32)], axis=1)
+    lengths = pkg.synth.lengths_uniform(200, 8, 128, seed=3)
     ids, mask, tt = pkg.synth.padded_batch(shape.vocab_size, lengths, 128)
     base = minilm.forward(ids, mask, tt)
     perm = np.random.default_rng(0).permutation(len(lengths))
     assert np.array_equal(minilm.forward(ids[perm], mask[perm], tt[perm]), base[perm])
-    wide = lambda a: np.concatenate([a, np.zeros((a.shape[0], 64), np.uint32)], axis=1)
     assert np.array_equal(minilm.forward(wide(ids), wide(mask), wide(tt)), base)
+
+    lengths = pkg.synth.lengths_uniform(1024, 8, 128, seed=3)
+    ids, mask, tt = pkg.synth.padded_batch(shape.vocab_size, lengths, 128)
+    base = minilm.forward(ids, mask, tt)
+    perm = np.random.default_rng(0).permutation(len(lengths))
+    for other, ref in ((minilm.forward(ids[perm], mask[perm], tt[perm]), base[perm]),
+                       (minilm.forward(wide(ids), wide(mask), wide(tt)), base)):
+        assert np.abs(other - ref).max() <= 4e-3 and cos_rows(other, ref).min() >= 0.9999
     sub = np.arange(0, 1024, 97)
     want = Oracle(shape, minilm.export_weights(), "f32").generate(ids[sub], tt[sub], mask[sub])
     check(base[sub], want, False)

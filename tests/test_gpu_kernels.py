@@ -222,15 +222,19 @@ def test_k3_attention(env, pkg, dtype, heads, d):
     assert cos_rows(got, want).min() >= (0.999999 if dtype == 1 else 0.9998)
 
 
+@pytest.mark.parametrize("lens", ["mixed", "tiny"])
 @pytest.mark.parametrize("heads", [4, 8, 12])
-def test_k23_qkv_attention_fused(pkg, built, heads):
+def test_k23_qkv_attention_fused(pkg, built, heads, lens):
     """Q/K/V projection + attention of whole sentences in one kernel (bert.rs BertSelfAttention::forward) vs the
     oracle's Linear + padded additive-mask softmax on the same bf16-rounded weights and input; q, k, v are rounded to
     bf16 on the GPU (they are the attention MMAs' operands). Ragged lengths 1 .. 128 incl. both sides of 64."""
     d = 32
     H = heads * d
     shape = pkg.weights.BertShape(512, H, 1, heads, 4 * H, 128, 2)
-    lengths = np.array([1, 2, 63, 64, 65, 128, 100, 17, 127, 128, 33, 5] * 3)
+    # short sentences share a 128-row tile (block-diagonal attention); "tiny": up to 128 sentences in one tile, tiles
+    # cut at the 32-sentence segments of the packing kernel
+    lengths = (np.array([1, 2, 63, 64, 65, 128, 100, 17, 127, 128, 33, 5] * 3) if lens == "mixed"
+               else np.random.default_rng(7).integers(1, 4, size=301))
     S = 128
     rng = np.random.default_rng(heads)
     x = bf16_round(rng.standard_normal((len(lengths), S, H)).astype(np.float32))
