@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- sentences/sec of the embedding hot path (BASELINE.json metric) on N B200s of one node.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload c2|c1|c3|c4]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload c2|c1|c3|c4|c5]
   python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
 A "step" is one pass of the hot path (mask -> lengths, embed+LN, L encoder layers, masked mean-pool)
@@ -48,6 +48,8 @@ WORKLOADS = {
     "c2": ("minilm-l6", 4096, 128, False),
     "c3": ("minilm-l6", 2048, 512, True),
     "c4": ("bert-base", 8192, 256, False),
+    # SURVEY config c5's length distribution (one shard of the corpus): clip(round(LogNormal(ln 24, 0.6)), 4, 128)
+    "c5": ("minilm-l6", 16384, 128, "corpus"),
 }
 
 
@@ -113,6 +115,8 @@ class ClockSampler:
 
 
 def make_lengths(pkg, batch, seq, ragged, seed):
+    if ragged == "corpus":
+        return np.minimum(pkg.synth.lengths_corpus(batch, seed=2026 + seed), seq)
     if ragged:
         return pkg.synth.lengths_loguniform(batch, 8, seq, seed=seed)
     return pkg.synth.lengths_dense(batch, seq)
@@ -346,7 +350,8 @@ def run_b200(args, pkg, rank, world, local_rank):
             "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic",
             "config": {"workload": f"{args.workload}: {shape_key} random-init bf16, batch {batch} x seq {seq} per GPU"
-                                   + (" ragged log-uniform 8..seq packed varlen" if ragged else " dense"),
+                                   + (" corpus lengths clip(LogNormal(ln 24, 0.6), 4, 128)" if ragged == "corpus"
+                                      else " ragged log-uniform 8..seq packed varlen" if ragged else " dense"),
                        "tokens_per_step_per_gpu": int(np.sum(lengths)), "normalize": bool(args.normalize),
                        "parallelism": f"replica per GPU x{world}, sentence batches sharded, no data-path collective",
                        "l2": "activations per step (>= 4 GB at c2) exceed the 126 MB L2; no explicit flush"},

@@ -1,7 +1,7 @@
 #!/bin/bash
 # Short bench of every workload (c1..c4) -> gpurun_out/workloads.log; one line of key numbers each.
 mkdir -p gpurun_out; : > gpurun_out/workloads.log
-for w in c1 c3 c4 c2; do
+for w in c1 c3 c4 c5 c2; do
   python bench.py --workload $w --steps 5 --warmup 3 --no-cpu-baseline 2>&1 | grep "^{" | tail -1 >> gpurun_out/workloads.log
 done
 python - <<'PY'
