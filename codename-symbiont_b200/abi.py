@@ -74,6 +74,10 @@ _SIGNATURES = {
                                           _P]),
     "b200_op_mean_pool": (C.c_int32, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, _P, _P]),
     "b200_op_gemm_bf16": (C.c_int32, [_P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P, _P]),
+    "b200_json_text_with_embeddings": (C.c_int64, [C.c_char_p, C.c_char_p, _P, _P, C.c_int32, C.c_int32, C.c_char_p,
+                                                   C.c_uint64, C.c_int32, _P, C.c_int64]),
+    "b200_json_query_embedding_result": (C.c_int64, [C.c_char_p, _P, C.c_int32, C.c_char_p, C.c_char_p, _P, C.c_int64]),
+    "b200_json_format_f32": (C.c_int32, [C.c_float, _P]),
 }
 
 _lib = None
@@ -117,6 +121,48 @@ def _check(rc: int):
 def _u32(a):
     a = np.ascontiguousarray(a, dtype=np.uint32)
     return a, a.ctypes.data
+
+
+def json_text_with_embeddings(original_id: str, source_url: str, sentences, embeddings: np.ndarray, model_name: str,
+                              timestamp_ms: int, threads: int = 0) -> bytes:
+    """serde_json::to_vec(&TextWithEmbeddingsMessage) (libs/shared_models/src/lib.rs:45-52) for these fields."""
+    lib = load_library()
+    emb = np.ascontiguousarray(embeddings, dtype=np.float32)
+    n = len(sentences)
+    dim = emb.shape[1] if emb.ndim == 2 else 0
+    if emb.ndim != 2 or emb.shape[0] != n:
+        raise ValueError("embeddings must be [len(sentences), dim]")
+    enc = [s.encode("utf-8") for s in sentences]
+    arr = (C.c_char_p * max(n, 1))(*enc)
+    args = (original_id.encode(), source_url.encode(), C.cast(arr, _P), emb.ctypes.data_as(_P), n, dim,
+            model_name.encode(), int(timestamp_ms), int(threads))
+    cap = n * (dim * 13 + 48) + sum(len(e) for e in enc) * 6 + 4096  # upper bound: one formatting pass
+    buf = C.create_string_buffer(cap)
+    need = lib.b200_json_text_with_embeddings(*args, C.cast(buf, _P), cap)
+    if need < 0:
+        raise ValueError("bad argument")
+    if need > cap:  # cannot happen with the bound above; kept as the documented fallback
+        buf = C.create_string_buffer(need)
+        lib.b200_json_text_with_embeddings(*args, C.cast(buf, _P), need)
+    return buf.raw[:need]
+
+
+def json_query_embedding_result(request_id: str, embedding=None, model_name=None, error_message=None) -> bytes:
+    """serde_json::to_vec(&QueryEmbeddingResult) (libs/shared_models/src/lib.rs:66-72); None -> null."""
+    lib = load_library()
+    emb = None if embedding is None else np.ascontiguousarray(embedding, dtype=np.float32)
+    args = (request_id.encode(), None if emb is None else emb.ctypes.data_as(_P), 0 if emb is None else emb.size,
+            None if model_name is None else model_name.encode(), None if error_message is None else error_message.encode())
+    need = lib.b200_json_query_embedding_result(*args, None, 0)
+    buf = C.create_string_buffer(max(need, 1))
+    lib.b200_json_query_embedding_result(*args, C.cast(buf, _P), need)
+    return buf.raw[:need]
+
+
+def json_format_f32(v: float) -> str:
+    buf = C.create_string_buffer(24)
+    n = load_library().b200_json_format_f32(C.c_float(v), C.cast(buf, _P))
+    return buf.raw[:n].decode()
 
 
 def host_alloc(shape, dtype) -> np.ndarray:

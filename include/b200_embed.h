@@ -221,6 +221,24 @@ int32_t b200_op_mean_pool(b200_embed* h, const void* hidden, const void* hidden_
 int32_t b200_op_gemm_bf16(const void* a, const void* b, const float* bias, int32_t m, int32_t n, int32_t k,
                           int32_t act, int32_t block_n, void* c, void* stream);
 
+/* -- wire format of the results (host only, no GPU involved) --------------------------------------------
+ * The JSON text serde_json::to_vec produces for the messages the service publishes after the embedding call
+ * (preprocessing_service/src/main.rs:138-142, :238-245): compact, struct fields in declaration order, f32 in the
+ * shortest decimal that round-trips (ryu "pretty" layout), non-finite floats as null, UTF-8 strings with JSON
+ * escapes. Replaces serde's derive(Serialize) for shared_models::TextWithEmbeddingsMessage
+ * (libs/shared_models/src/lib.rs:45-52, SentenceEmbedding :39-43) and QueryEmbeddingResult (:66-72); the schema is
+ * unchanged. Each call returns the number of bytes of the document; it is written to `out` (no terminator) when
+ * out != NULL and out_cap is large enough - call with out = NULL to size the buffer. Negative on bad arguments. */
+int64_t b200_json_text_with_embeddings(const char* original_id, const char* source_url, const char* const* sentences,
+                                       const float* embeddings /* [n * dim] row-major */, int32_t n, int32_t dim,
+                                       const char* model_name, uint64_t timestamp_ms,
+                                       int32_t threads /* 0 = all host cores */, char* out, int64_t out_cap);
+int64_t b200_json_query_embedding_result(const char* request_id, const float* embedding_or_null, int32_t dim,
+                                         const char* model_name_or_null, const char* error_message_or_null, char* out,
+                                         int64_t out_cap);
+/* One f32 as serde_json writes it; out24 must hold 24 bytes. Returns the number of characters. */
+int32_t b200_json_format_f32(float value, char* out24);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,83 @@
+"""CPU: the JSON wire format of the results (include/b200_embed.h b200_json_*) against the Python
+restatement in oracle/json_oracle.py, exact f32 round trip, and the schema of libs/shared_models/src/lib.rs."""
+import json
+import time
+
+import numpy as np
+import pytest
+
+from oracle import json_oracle
+
+
+@pytest.fixture(scope="module")
+def abi(pkg, built):
+    return pkg.abi
+
+
+def test_f32_layout_and_round_trip(abi):
+    rng = np.random.default_rng(5)
+    bits = rng.integers(0, 2**32, size=20000, dtype=np.uint64).astype(np.uint32)
+    vals = np.concatenate([
+        bits.view(np.float32),                                   # the whole range, subnormals, inf, nan
+        rng.standard_normal(20000).astype(np.float32) * 0.1,    # embedding-like
+        np.float32([0.0, -0.0, 1.0, -1.0, 0.1, 1e-5, 1e-6, 1e-7, 9.999999e12, 1e13, 1e12, 16777216.0, 3.4028235e38,
+                    1e-45, 1.17549435e-38, 123456.79, 0.001234, 12.34, 1e21]),
+    ])
+    for v in vals:
+        got = abi.json_format_f32(float(v))
+        assert got == json_oracle.format_f32(v), (v, got)
+        if np.isfinite(v):
+            back = np.float32(json.loads(got))
+            assert back.view(np.uint32) == np.float32(v).view(np.uint32) or (back == 0 and v == 0), (v, got)
+            assert "e+" not in got and not got.startswith(".") and got == got.strip()
+
+
+def test_text_with_embeddings_message(abi):
+    rng = np.random.default_rng(1)
+    sentences = ['Plain sentence.', 'Quotes " and \\ backslash?', "tabs\tnew\nlines\r!", "Ünïcödé – 文字 🙂.", "ctl\x01\x1f."]
+    emb = rng.standard_normal((len(sentences), 384)).astype(np.float32)
+    emb[0, :4] = [0.0, -0.0, 1e-7, 1e13]
+    got = abi.json_text_with_embeddings("id-1", "https://example.org/a?b=c", sentences, emb,
+                                        "sentence-transformers/paraphrase-multilingual-mpnet-base-v2", 1717171717171, threads=3)
+    want = json_oracle.text_with_embeddings("id-1", "https://example.org/a?b=c", sentences, emb,
+                                            "sentence-transformers/paraphrase-multilingual-mpnet-base-v2", 1717171717171)
+    assert got == want
+    doc = json.loads(got)
+    # field names and order of TextWithEmbeddingsMessage / SentenceEmbedding (lib.rs:39-52)
+    assert list(doc) == ["original_id", "source_url", "embeddings_data", "model_name", "timestamp_ms"]
+    assert all(list(d) == ["sentence_text", "embedding"] for d in doc["embeddings_data"])
+    assert [d["sentence_text"] for d in doc["embeddings_data"]] == sentences
+    back = np.array([d["embedding"] for d in doc["embeddings_data"]], dtype=np.float32)
+    assert np.array_equal(back.view(np.uint32) & 0x7fffffff, emb.view(np.uint32) & 0x7fffffff)  # exact (sign of zero aside)
+    assert abi.json_text_with_embeddings("x", "", [], np.zeros((0, 384), np.float32), "m", 0) == \
+        b'{"original_id":"x","source_url":"","embeddings_data":[],"model_name":"m","timestamp_ms":0}'
+    # thread count must not change the bytes
+    assert got == abi.json_text_with_embeddings("id-1", "https://example.org/a?b=c", sentences, emb,
+                                                "sentence-transformers/paraphrase-multilingual-mpnet-base-v2", 1717171717171, threads=1)
+
+
+def test_query_embedding_result(abi):
+    e = np.linspace(-1, 1, 768, dtype=np.float32)
+    got = abi.json_query_embedding_result("req-7", e, "model", None)
+    assert got == json_oracle.query_embedding_result("req-7", e, "model", None)
+    doc = json.loads(got)
+    assert list(doc) == ["request_id", "embedding", "model_name", "error_message"] and doc["error_message"] is None
+    assert np.array_equal(np.float32(doc["embedding"]), e)
+    err = abi.json_query_embedding_result("req-8", None, None, 'failed: "x"')
+    assert err == b'{"request_id":"req-8","embedding":null,"model_name":null,"error_message":"failed: \\"x\\""}'
+
+
+def test_formatter_throughput_is_reported(abi, capsys):
+    """Not a gate: prints MB/s of the native formatter next to Python's json.dumps on one ingest-sized message."""
+    rng = np.random.default_rng(2)
+    n, dim = 2048, 384
+    emb = rng.standard_normal((n, dim)).astype(np.float32) * 0.05
+    sentences = ["Sentence number %d of the document." % i for i in range(n)]
+    t0 = time.perf_counter(); a = abi.json_text_with_embeddings("i", "u", sentences, emb, "m", 1); t1 = time.perf_counter()
+    b = json.dumps({"original_id": "i", "source_url": "u",
+                    "embeddings_data": [{"sentence_text": s, "embedding": e.tolist()} for s, e in zip(sentences, emb)],
+                    "model_name": "m", "timestamp_ms": 1}); t2 = time.perf_counter()
+    with capsys.disabled():
+        print(f"\n[json] native {len(a) / 1e6 / (t1 - t0):.0f} MB/s ({n / (t1 - t0):,.0f} sentences/s), "
+              f"python json.dumps {len(b) / 1e6 / (t2 - t1):.0f} MB/s")
+    assert len(a) > n * dim * 4
