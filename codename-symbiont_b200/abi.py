@@ -78,6 +78,13 @@ _SIGNATURES = {
                                                    C.c_uint64, C.c_int32, _P, C.c_int64]),
     "b200_json_query_embedding_result": (C.c_int64, [C.c_char_p, _P, C.c_int32, C.c_char_p, C.c_char_p, _P, C.c_int64]),
     "b200_json_format_f32": (C.c_int32, [C.c_float, _P]),
+    "b200_ingest_last_error": (C.c_char_p, []),
+    "b200_ingest_create": (C.c_int32, [C.c_char_p, C.POINTER(_P)]),
+    "b200_ingest_destroy": (None, [_P]),
+    "b200_ingest_vocab_size": (C.c_int32, [_P]),
+    "b200_ingest_pad_id": (C.c_int32, [_P]),
+    "b200_ingest_split_sentences": (C.c_int64, [_P, C.c_int64, _P, C.c_int64, C.POINTER(C.c_int64), _P, _P, C.c_int64]),
+    "b200_ingest_encode": (C.c_int32, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, _P, _P, _P, _P]),
 }
 
 _lib = None
@@ -88,7 +95,7 @@ def declared_symbols() -> list:
     with open(HEADER_PATH) as f:
         text = f.read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
-    return sorted(set(re.findall(r"\b(b200_(?:embed|op)_[a-z0-9_]+)\s*\(", text)))
+    return sorted(set(re.findall(r"\b(b200_(?:embed|op|json|ingest)_[a-z0-9_]+)\s*\(", text)))
 
 
 def load_library():
@@ -163,6 +170,77 @@ def json_format_f32(v: float) -> str:
     buf = C.create_string_buffer(24)
     n = load_library().b200_json_format_f32(C.c_float(v), C.cast(buf, _P))
     return buf.raw[:n].decode()
+
+
+def _check_ingest(rc: int):
+    if rc < 0:
+        raise B200EmbedError(int(rc), load_library().b200_ingest_last_error().decode(errors="replace"))
+
+
+def split_sentences(raw_text: str):
+    """process_raw_text_message's splitter (preprocessing_service/src/main.rs:28-63) -> (cleaned: bytes, begin, end);
+    sentence i is cleaned[begin[i]:end[i]]. An empty cleaned text raises like the reference's Err("Cleaned text is empty")."""
+    lib = load_library()
+    raw = raw_text.encode("utf-8")
+    cleaned = np.empty(max(len(raw), 1), dtype=np.uint8)
+    clen = C.c_int64(0)
+    cap = raw.count(b".") + raw.count(b"?") + raw.count(b"!") + 1
+    begin = np.zeros(cap, dtype=np.int64)
+    end = np.zeros(cap, dtype=np.int64)
+    n = lib.b200_ingest_split_sentences(raw, len(raw), cleaned.ctypes.data, len(cleaned), C.byref(clen), begin.ctypes.data,
+                                        end.ctypes.data, cap)
+    _check_ingest(n)
+    if n == 0:
+        raise ValueError("Cleaned text is empty")
+    return cleaned[:clen.value].tobytes(), begin[:n], end[:n]
+
+
+class Ingest:
+    """Owns one b200_ingest handle: the WordPiece tokenizer of a tokenizer.json (embedding_generator.rs:73-99, :160-187)."""
+
+    def __init__(self, tokenizer_json_path: str):
+        self._h = _P()
+        _check_ingest(load_library().b200_ingest_create(os.fsencode(tokenizer_json_path), C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            load_library().b200_ingest_destroy(self._h)
+            self._h = _P()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def vocab_size(self) -> int:
+        return load_library().b200_ingest_vocab_size(self._h)
+
+    @property
+    def pad_id(self) -> int:
+        return load_library().b200_ingest_pad_id(self._h)
+
+    def encode_ranges(self, text: bytes, begin, end, seq_len: int, threads: int = 0, out=None):
+        """Sentence i = text[begin[i]:end[i]] (UTF-8) -> ids, mask, type_ids [n, seq_len] u32 and lengths [n] i32."""
+        begin = np.ascontiguousarray(begin, dtype=np.int64)
+        end = np.ascontiguousarray(end, dtype=np.int64)
+        n = len(begin)
+        if out is None:
+            out = tuple(np.empty((n, seq_len), dtype=np.uint32) for _ in range(3))
+        ids, mask, tt = out
+        lengths = np.empty(n, dtype=np.int32)
+        _check_ingest(load_library().b200_ingest_encode(self._h, C.c_char_p(text), begin.ctypes.data, end.ctypes.data, n, seq_len,
+                                                        threads, ids.ctypes.data, mask.ctypes.data, tt.ctypes.data,
+                                                        lengths.ctypes.data))
+        return ids, mask, tt, lengths
+
+    def encode(self, sentences, seq_len: int, threads: int = 0):
+        """tokenizer.encode_batch(sentences, true) with Fixed(seq_len) padding and LongestFirst truncation."""
+        enc = [s.encode("utf-8") for s in sentences]
+        end = np.cumsum([len(b) for b in enc], dtype=np.int64) if enc else np.zeros(0, dtype=np.int64)
+        begin = np.concatenate([np.zeros(1, dtype=np.int64), end[:-1]]) if enc else end
+        return self.encode_ranges(b"".join(enc), begin, end, seq_len, threads)
 
 
 def host_alloc(shape, dtype) -> np.ndarray:

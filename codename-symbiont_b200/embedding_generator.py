@@ -5,8 +5,10 @@ points, same argument meaning, same error behaviour, with the tensor work behind
     EmbeddingGenerator.new(model_dir, revision, force_cpu)          (:17)
     generator.generate_sentence_embeddings(sentences) -> [[f32]]    (:134)
 
-What is unchanged from the reference: the tokenizer (HuggingFace `tokenizers`, here its Python
-binding of the same Rust core), Fixed right padding to `max_position_embeddings` with `[PAD]`
+What is unchanged from the reference: the tokenizer's behaviour (a BERT WordPiece tokenizer.json goes through the
+native b200_ingest_* entries, checked bit-exactly against the `tokenizers` library in tests/test_ingest.py; any other
+tokenizer.json goes through the `tokenizers` library itself, the Python binding of the Rust core the reference
+links), Fixed right padding to `max_position_embeddings` with `[PAD]`
 (:75-91), LongestFirst truncation to the same length (:93-99), `encode_batch(inputs, true)` (:160-164),
 the length check (:172-177), the flattening of ids / attention mask / type ids (:179-187), the order of
 the results and "empty in => empty out" (:135-137). What changes: lines :189-214 (three candle tensors,
@@ -26,13 +28,16 @@ from typing import List, Sequence
 import numpy as np
 
 from . import weights as W
-from .abi import Embedder, B200EmbedError, FLAG_NORMALIZE
+from .abi import Embedder, B200EmbedError, FLAG_NORMALIZE, Ingest, split_sentences
+
+ERR_UNSUPPORTED = -4  # B200_EMBED_ERR_UNSUPPORTED_SHAPE
 
 
 class EmbeddingGenerator:
-    def __init__(self, embedder: Embedder, tokenizer, shape: W.BertShape, normalize: bool = False):
+    def __init__(self, embedder: Embedder, tokenizer, shape: W.BertShape, normalize: bool = False, ingest: Ingest | None = None):
         self.model = embedder
-        self.tokenizer = tokenizer
+        self.tokenizer = tokenizer  # the `tokenizers` library object, used only when `ingest` is None
+        self.ingest = ingest        # native WordPiece front-end (b200_ingest_*), None for a non-WordPiece tokenizer.json
         self.config = shape
         self.normalize = normalize
 
@@ -41,14 +46,20 @@ class EmbeddingGenerator:
             normalize: bool = False) -> "EmbeddingGenerator":
         if force_cpu:
             raise B200EmbedError(-5, "force_cpu=true: this embedding path has no CPU fallback (NO_DEVICE)")
-        from tokenizers import Tokenizer
-
         d = model_id
         shape = W.BertShape.from_config_json(os.path.join(d, "config.json"))
-        tok = Tokenizer.from_file(os.path.join(d, "tokenizer.json"))
-        configure_tokenizer(tok, shape.max_position_embeddings)
+        tok, ingest = None, None
+        try:
+            ingest = Ingest(os.path.join(d, "tokenizer.json"))
+        except B200EmbedError as e:
+            if e.code != ERR_UNSUPPORTED:
+                raise
+            from tokenizers import Tokenizer  # e.g. the Unigram tokenizer of an XLM-R checkpoint
+
+            tok = Tokenizer.from_file(os.path.join(d, "tokenizer.json"))
+            configure_tokenizer(tok, shape.max_position_embeddings)
         emb = Embedder(shape, os.path.join(d, "model.safetensors"), device=device)
-        return cls(emb, tok, shape, normalize)
+        return cls(emb, tok, shape, normalize, ingest)
 
     def generate_sentence_embeddings(self, sentences: Sequence[str]) -> List[List[float]]:
         if len(sentences) == 0:
@@ -59,9 +70,28 @@ class EmbeddingGenerator:
         """Same call, returning the [n, hidden] float32 matrix without the nested-list conversion."""
         if len(sentences) == 0:
             return np.empty((0, self.config.hidden_size), dtype=np.float32)
-        ids, mask, type_ids = tokenize_fixed(self.tokenizer, sentences, self.config.max_position_embeddings)
+        P = self.config.max_position_embeddings
+        if self.ingest is not None:
+            ids, mask, type_ids, _ = self.ingest.encode(sentences, P)
+        else:
+            ids, mask, type_ids = tokenize_fixed(self.tokenizer, sentences, P)
         flags = FLAG_NORMALIZE if self.normalize else 0
         return self.model.forward(ids, mask, type_ids, flags=flags)
+
+    def process_raw_text(self, raw_text: str, doc_id: str = ""):
+        """process_raw_text_message up to the embeddings (preprocessing_service/src/main.rs:28-95): clean, split into
+        sentences, embed. Returns (sentences, [n, hidden] float32); raises ValueError with the reference's messages."""
+        try:
+            cleaned, begin, end = split_sentences(raw_text)
+        except ValueError:
+            raise ValueError(f"Cleaned text is empty for id: {doc_id}") from None
+        if self.ingest is None:
+            sentences = [cleaned[b:e].decode() for b, e in zip(begin, end)]
+            return sentences, self.generate_sentence_embeddings_array(sentences)
+        ids, mask, type_ids, _ = self.ingest.encode_ranges(cleaned, begin, end, self.config.max_position_embeddings)
+        flags = FLAG_NORMALIZE if self.normalize else 0
+        out = self.model.forward(ids, mask, type_ids, flags=flags)
+        return [cleaned[b:e].decode() for b, e in zip(begin, end)], out
 
     def close(self):
         self.model.close()

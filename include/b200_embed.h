@@ -239,6 +239,40 @@ int64_t b200_json_query_embedding_result(const char* request_id, const float* em
 /* One f32 as serde_json writes it; out24 must hold 24 bytes. Returns the number of characters. */
 int32_t b200_json_format_f32(float value, char* out24);
 
+/* -- ingest front-end: raw text -> sentences -> token arrays (host only, no GPU involved) ------------------
+ * What runs on the host before the embedding call. Errors of these entries are reported through
+ * b200_ingest_last_error() (calling thread), with the same B200_EMBED_ERR_* codes. */
+typedef struct b200_ingest b200_ingest;
+const char* b200_ingest_last_error(void);
+
+/* Loads a HuggingFace tokenizer.json holding a BERT WordPiece pipeline (BertNormalizer, BertPreTokenizer, WordPiece,
+ * BertProcessing or TemplateProcessing). Replaces Tokenizer::from_file plus the padding / truncation set-up of
+ * preprocessing_service/src/embedding_generator.rs:73-99: padding is Fixed(seq_len) on the right with the id of
+ * "[PAD]" (0 when the vocabulary has none), type id 0; truncation is LongestFirst to seq_len (seq_len is passed to
+ * b200_ingest_encode). B200_EMBED_ERR_IO when the file cannot be read, B200_EMBED_ERR_UNSUPPORTED_SHAPE for any other
+ * tokenizer (Unigram / BPE models, other normalizers, added tokens with lstrip / rstrip / single_word / normalized). */
+int32_t b200_ingest_create(const char* tokenizer_json_path, b200_ingest** out);
+void b200_ingest_destroy(b200_ingest* t);
+int32_t b200_ingest_vocab_size(const b200_ingest* t); /* largest id + 1, added tokens included */
+int32_t b200_ingest_pad_id(const b200_ingest* t);
+
+/* The sentence splitter of process_raw_text_message (preprocessing_service/src/main.rs:28-63): whitespace runs
+ * collapsed to one space (split_whitespace + join), a cut after every '.', '?' or '!', every piece trimmed, a
+ * non-empty remainder kept. Writes the cleaned text to `cleaned` (cleaned_cap >= len is always enough, no
+ * terminator) and sentence i as the byte range [begin[i], end[i]) of it. Returns the number of sentences; when it
+ * exceeds max_sentences only the first max_sentences ranges are written. 0 means the cleaned text is empty (the
+ * reference answers "Cleaned text is empty for id: .."). Negative on bad arguments. */
+int64_t b200_ingest_split_sentences(const char* raw_text, int64_t len, char* cleaned, int64_t cleaned_cap,
+                                    int64_t* cleaned_len, int64_t* begin, int64_t* end, int64_t max_sentences);
+
+/* tokenizer.encode_batch(inputs, true) (embedding_generator.rs:160-187): sentence i is text[begin[i], end[i]) in
+ * UTF-8; row i of ids / mask / type_ids ([n, seq_len] u32, row-major) receives [CLS] tokens [SEP] then padding,
+ * exactly what b200_embed_forward takes. lengths_or_null[i] = number of real tokens of row i. `threads` = 0 uses
+ * every host core. */
+int32_t b200_ingest_encode(const b200_ingest* t, const char* text, const int64_t* begin, const int64_t* end, int32_t n,
+                           int32_t seq_len, int32_t threads, uint32_t* ids, uint32_t* mask, uint32_t* type_ids,
+                           int32_t* lengths_or_null);
+
 #ifdef __cplusplus
 }
 #endif

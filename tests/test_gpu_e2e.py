@@ -311,10 +311,21 @@ def test_embedding_generator_end_to_end_text(pkg, built, tmp_path):
         sents = ["The quick brown fox jumps over the lazy dog.", "A symbiont reads web pages!", "Embeds sentences?"] * 4
         out = gen.generate_sentence_embeddings(sents)
         assert len(out) == len(sents) and len(out[0]) == shape.hidden_size
-        from codename_symbiont_b200.embedding_generator import tokenize_fixed
-        ids, mask, tt = tokenize_fixed(gen.tokenizer, sents, shape.max_position_embeddings)
+        from codename_symbiont_b200.embedding_generator import configure_tokenizer, tokenize_fixed
+        assert gen.ingest is not None and gen.tokenizer is None  # a WordPiece tokenizer.json takes the native front-end
+        lib_tok = Tokenizer.from_file(str(tmp_path / "tokenizer.json"))  # the reference's library as the checker
+        configure_tokenizer(lib_tok, shape.max_position_embeddings)
+        ids, mask, tt = tokenize_fixed(lib_tok, sents, shape.max_position_embeddings)
+        got_ids, got_mask, got_tt, _ = gen.ingest.encode(sents, shape.max_position_embeddings)
+        assert np.array_equal(ids, got_ids) and np.array_equal(mask, got_mask) and np.array_equal(tt, got_tt)
         want = Oracle(shape, w, "f32").generate(ids, tt, mask, chunk=8)
         check(np.array(out, np.float32), want, False)
         assert np.array_equal(np.array(out[0]), np.array(out[3]))  # same sentence, same vector, any position
+        # raw text in, sentences and vectors out (main.rs:28-95)
+        split, vecs = gen.process_raw_text("  " + "   ".join(sents) + " trailing words\n")
+        assert split == sents + ["trailing words"] and vecs.shape == (len(sents) + 1, shape.hidden_size)
+        assert np.array_equal(vecs[:len(sents)], np.array(out, np.float32))
+        with pytest.raises(ValueError, match="Cleaned text is empty for id: doc7"):
+            gen.process_raw_text(" \n\t ", "doc7")
     finally:
         gen.close()
