@@ -76,6 +76,8 @@ _SIGNATURES = {
     "b200_op_gemm_bf16": (C.c_int32, [_P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P, _P]),
     "b200_json_text_with_embeddings": (C.c_int64, [C.c_char_p, C.c_char_p, _P, _P, C.c_int32, C.c_int32, C.c_char_p,
                                                    C.c_uint64, C.c_int32, _P, C.c_int64]),
+    "b200_json_text_with_embeddings_ranges": (C.c_int64, [C.c_char_p, C.c_char_p, _P, _P, _P, _P, C.c_int32, C.c_int32, C.c_char_p,
+                                                          C.c_uint64, C.c_int32, _P, C.c_int64]),
     "b200_json_query_embedding_result": (C.c_int64, [C.c_char_p, _P, C.c_int32, C.c_char_p, C.c_char_p, _P, C.c_int64]),
     "b200_json_format_f32": (C.c_int32, [C.c_float, _P]),
     "b200_ingest_last_error": (C.c_char_p, []),
@@ -130,28 +132,42 @@ def _u32(a):
     return a, a.ctypes.data
 
 
+def _json_out(call, cap: int, as_array: bool):
+    buf = np.empty(cap, dtype=np.uint8)  # upper bound: one formatting pass
+    need = call(buf.ctypes.data, cap)
+    if need < 0:
+        raise ValueError("bad argument")
+    if need > cap:  # cannot happen with the bounds used below; kept as the documented fallback
+        buf = np.empty(need, dtype=np.uint8)
+        call(buf.ctypes.data, need)
+    return buf[:need] if as_array else buf[:need].tobytes()
+
+
 def json_text_with_embeddings(original_id: str, source_url: str, sentences, embeddings: np.ndarray, model_name: str,
-                              timestamp_ms: int, threads: int = 0) -> bytes:
-    """serde_json::to_vec(&TextWithEmbeddingsMessage) (libs/shared_models/src/lib.rs:45-52) for these fields."""
+                              timestamp_ms: int, threads: int = 0, as_array: bool = False):
+    """serde_json::to_vec(&TextWithEmbeddingsMessage) (libs/shared_models/src/lib.rs:45-52) for these fields.
+    `sentences` is a list of str, or (text: bytes, begin, end) as split_sentences returns them."""
     lib = load_library()
     emb = np.ascontiguousarray(embeddings, dtype=np.float32)
-    n = len(sentences)
+    ranges = isinstance(sentences, tuple)
+    n = len(sentences[1]) if ranges else len(sentences)
     dim = emb.shape[1] if emb.ndim == 2 else 0
     if emb.ndim != 2 or emb.shape[0] != n:
         raise ValueError("embeddings must be [len(sentences), dim]")
+    tail = (emb.ctypes.data_as(_P), n, dim, model_name.encode(), int(timestamp_ms), int(threads))
+    head = (original_id.encode(), source_url.encode())
+    fixed = n * (dim * 17 + 48) + 6 * (len(head[0]) + len(head[1]) + len(tail[3])) + 4096
+    if ranges:
+        text, begin, end = sentences
+        begin = np.ascontiguousarray(begin, dtype=np.int64)
+        end = np.ascontiguousarray(end, dtype=np.int64)
+        cap = fixed + int((end - begin).sum()) * 6
+        return _json_out(lambda p, c: lib.b200_json_text_with_embeddings_ranges(*head, C.c_char_p(text), begin.ctypes.data, end.ctypes.data,
+                                                                               *tail, p, c), cap, as_array)
     enc = [s.encode("utf-8") for s in sentences]
     arr = (C.c_char_p * max(n, 1))(*enc)
-    args = (original_id.encode(), source_url.encode(), C.cast(arr, _P), emb.ctypes.data_as(_P), n, dim,
-            model_name.encode(), int(timestamp_ms), int(threads))
-    cap = n * (dim * 13 + 48) + sum(len(e) for e in enc) * 6 + 4096  # upper bound: one formatting pass
-    buf = C.create_string_buffer(cap)
-    need = lib.b200_json_text_with_embeddings(*args, C.cast(buf, _P), cap)
-    if need < 0:
-        raise ValueError("bad argument")
-    if need > cap:  # cannot happen with the bound above; kept as the documented fallback
-        buf = C.create_string_buffer(need)
-        lib.b200_json_text_with_embeddings(*args, C.cast(buf, _P), need)
-    return buf.raw[:need]
+    cap = fixed + sum(len(e) for e in enc) * 6
+    return _json_out(lambda p, c: lib.b200_json_text_with_embeddings(*head, C.cast(arr, _P), *tail, p, c), cap, as_array)
 
 
 def json_query_embedding_result(request_id: str, embedding=None, model_name=None, error_message=None) -> bytes:

@@ -13,6 +13,7 @@
 #include <cmath>
 #include <cstdint>
 #include <cstring>
+#include <memory>
 #include <string>
 #include <thread>
 #include <vector>
@@ -21,7 +22,8 @@
 
 namespace {
 
-// shortest round-trip digits of a finite non-zero float: value = 0.d1d2...dn x 10^kk  (n = ndig)
+// shortest round-trip digits of a finite non-zero float: value = 0.d1d2...dn x 10^kk  (n = ndig), through the C++
+// library (its to_chars is shortest round-trip, Ryu inside). `digits` must hold 24 bytes: copies are fixed-size.
 inline int shortest_digits(float v, char* digits, int* kk) {
     char buf[32];
     const auto r = std::to_chars(buf, buf + sizeof(buf), v, std::chars_format::scientific);
@@ -33,48 +35,48 @@ inline int shortest_digits(float v, char* digits, int* kk) {
     digits[0] = buf[0];
     int n = 1;
     if (mant_len > 1) {  // skip the '.'
-        std::memcpy(digits + 1, buf + 2, static_cast<size_t>(mant_len - 2));
+        std::memcpy(digits + 1, buf + 2, 16);
         n = mant_len - 1;
     }
     *kk = (neg ? -e : e) + 1;
     return n;
 }
 
-// ryu "pretty" layout for f32 (format32): returns characters written
+// ryu "pretty" layout for f32 (format32): returns characters written (at most 16). Copies are fixed-size so that no
+// memcpy call is made per float: `out` must have 32 writable bytes; what lies beyond the returned length is scratch.
 inline int format_f32(float v, char* out) {
     if (!std::isfinite(v)) { std::memcpy(out, "null", 4); return 4; }
     int i = 0;
     if (std::signbit(v)) { out[i++] = '-'; v = -v; }
     if (v == 0.0f) { std::memcpy(out + i, "0.0", 3); return i + 3; }
-    char d[16];
+    char d[32];
     int kk;
-    const int n = shortest_digits(v, d, &kk);
+    const int n = shortest_digits(v, d, &kk);  // n <= 9
+    if (-6 < kk && kk <= 0) {  // 1234e-6 -> 0.001234 : where embedding components live, so tested first
+        std::memcpy(out + i, "0.000000", 8);
+        i += 2 - kk;
+        std::memcpy(out + i, d, 16);
+        return i + n;
+    }
     const int k = kk - n;  // value = digits x 10^k
     if (0 <= k && kk <= 13) {  // 1234e7 -> 12340000000.0
-        std::memcpy(out + i, d, n);
+        std::memcpy(out + i, d, 16);
         for (int j = n; j < kk; ++j) out[i + j] = '0';
         out[i + kk] = '.';
         out[i + kk + 1] = '0';
         return i + kk + 2;
     }
     if (0 < kk && kk <= 13) {  // 1234e-2 -> 12.34
-        std::memcpy(out + i, d, kk);
+        std::memcpy(out + i, d, 16);
         out[i + kk] = '.';
-        std::memcpy(out + i + kk + 1, d + kk, n - kk);
+        std::memcpy(out + i + kk + 1, d + kk, 8);
         return i + n + 1;
-    }
-    if (-6 < kk && kk <= 0) {  // 1234e-6 -> 0.001234
-        out[i++] = '0';
-        out[i++] = '.';
-        for (int j = 0; j < -kk; ++j) out[i++] = '0';
-        std::memcpy(out + i, d, n);
-        return i + n;
     }
     // scientific: d[.ddd]e[-]X
     out[i++] = d[0];
     if (n > 1) {
         out[i++] = '.';
-        std::memcpy(out + i, d + 1, n - 1);
+        std::memcpy(out + i, d + 1, 8);
         i += n - 1;
     }
     out[i++] = 'e';
@@ -85,129 +87,177 @@ inline int format_f32(float v, char* out) {
     return i;
 }
 
-inline void append_string(std::string& o, const char* s) {
+// JSON string escapes of serde_json (ESCAPE table of serde_json/src/ser.rs): \" \\ \b \f \n \r \t, \u00XX for the other
+// control characters, everything else as is. Writes at p, returns the new end; at most 6 * n + 2 characters.
+inline char* put_string(char* p, const char* s, size_t n) {
     static const char* hex = "0123456789abcdef";
-    o.push_back('"');
-    for (const unsigned char* p = reinterpret_cast<const unsigned char*>(s ? s : ""); *p; ++p) {
-        const unsigned char c = *p;
+    *p++ = '"';
+    for (size_t i = 0; i < n; ++i) {
+        const unsigned char c = static_cast<unsigned char>(s[i]);
+        if (c >= 0x20 && c != '"' && c != '\\') { *p++ = static_cast<char>(c); continue; }
+        *p++ = '\\';
         switch (c) {
-            case '"': o += "\\\""; break;
-            case '\\': o += "\\\\"; break;
-            case '\b': o += "\\b"; break;
-            case '\f': o += "\\f"; break;
-            case '\n': o += "\\n"; break;
-            case '\r': o += "\\r"; break;
-            case '\t': o += "\\t"; break;
+            case '"': *p++ = '"'; break;
+            case '\\': *p++ = '\\'; break;
+            case '\b': *p++ = 'b'; break;
+            case '\f': *p++ = 'f'; break;
+            case '\n': *p++ = 'n'; break;
+            case '\r': *p++ = 'r'; break;
+            case '\t': *p++ = 't'; break;
             default:
-                if (c < 0x20) {
-                    o += "\\u00";
-                    o.push_back(hex[c >> 4]);
-                    o.push_back(hex[c & 15]);
-                } else {
-                    o.push_back(static_cast<char>(c));
-                }
+                *p++ = 'u'; *p++ = '0'; *p++ = '0';
+                *p++ = hex[c >> 4];
+                *p++ = hex[c & 15];
         }
     }
-    o.push_back('"');
+    *p++ = '"';
+    return p;
 }
-
-// Every float takes at most 16 characters ("-1.17549435e-38"): grow once, then write through a raw pointer (appending
-// float by float through std::string cost twice the time of the digit generation itself).
-inline void append_vector(std::string& o, const float* v, int dim) {
-    const size_t at = o.size();
-    o.resize(at + static_cast<size_t>(dim) * 17 + 2);
-    char* p = &o[at];
+inline char* put_cstr(char* p, const char* s) { return put_string(p, s ? s : "", s ? std::strlen(s) : 0); }
+inline char* put_lit(char* p, const char* lit) {
+    const size_t n = std::strlen(lit);
+    std::memcpy(p, lit, n);
+    return p + n;
+}
+// Every float takes at most 16 characters ("-1.17549435e-38")
+inline char* put_vector(char* p, const float* v, int dim) {
     *p++ = '[';
     for (int j = 0; j < dim; ++j) {
         if (j) *p++ = ',';
         p += format_f32(v[j], p);
     }
     *p++ = ']';
-    o.resize(static_cast<size_t>(p - o.data()));
+    return p;
 }
+inline size_t vector_bound(int dim) { return static_cast<size_t>(dim) * 17 + 2 + 32; }  // + the scratch format_f32 may touch
+inline size_t string_bound(size_t n) { return n * 6 + 2; }
 
-inline void append_u64(std::string& o, uint64_t v) {
-    char buf[24];
-    const auto r = std::to_chars(buf, buf + sizeof(buf), v);
-    o.append(buf, r.ptr);
-}
+struct Sentences {  // either NUL-terminated strings or byte ranges of one text
+    const char* const* strs;
+    const char* text;
+    const int64_t* begin;
+    const int64_t* end;
+    const char* ptr(int i) const { return strs ? (strs[i] ? strs[i] : "") : text + begin[i]; }
+    size_t len(int i) const { return strs ? (strs[i] ? std::strlen(strs[i]) : 0) : static_cast<size_t>(end[i] - begin[i]); }
+};
 
-inline int64_t deliver(const std::string& s, char* out, int64_t cap) {
-    const int64_t n = static_cast<int64_t>(s.size());
-    if (out != nullptr && cap >= n) std::memcpy(out, s.data(), s.size());
-    return n;
+// The document is produced in slices: every thread formats a contiguous run of sentences into its own (uninitialised)
+// buffer sized by the upper bounds above, then copies it to its final offset in `out`; only the sizes are exchanged.
+int64_t text_with_embeddings(const char* original_id, const char* source_url, const Sentences& sn, const float* embeddings,
+                             int32_t n, int32_t dim, const char* model_name, uint64_t timestamp_ms, int32_t threads, char* out,
+                             int64_t out_cap) {
+    int t = threads > 0 ? threads : static_cast<int>(std::thread::hardware_concurrency());
+    if (t < 1) t = 1;
+    if (t > n / 8) t = n / 8 > 0 ? n / 8 : 1;
+    std::vector<std::unique_ptr<char[]>> parts(static_cast<size_t>(t));
+    std::vector<size_t> part_len(static_cast<size_t>(t), 0);
+    auto range = [&](int k, int* lo, int* hi) {
+        *lo = static_cast<int>(static_cast<int64_t>(n) * k / t);
+        *hi = static_cast<int>(static_cast<int64_t>(n) * (k + 1) / t);
+    };
+    auto format_part = [&](int k) {
+        int lo, hi;
+        range(k, &lo, &hi);
+        size_t bound = 0;
+        for (int i = lo; i < hi; ++i) bound += string_bound(sn.len(i)) + vector_bound(dim) + 40;
+        parts[static_cast<size_t>(k)].reset(new char[bound + 1]);
+        char* p = parts[static_cast<size_t>(k)].get();
+        char* const p0 = p;
+        for (int i = lo; i < hi; ++i) {
+            if (i) *p++ = ',';
+            p = put_lit(p, "{\"sentence_text\":");
+            p = put_string(p, sn.ptr(i), sn.len(i));
+            p = put_lit(p, ",\"embedding\":");
+            p = put_vector(p, embeddings + static_cast<size_t>(i) * dim, dim);
+            *p++ = '}';
+        }
+        part_len[static_cast<size_t>(k)] = static_cast<size_t>(p - p0);
+    };
+    auto run = [&](auto&& fn) {
+        if (t <= 1) { fn(0); return; }
+        std::vector<std::thread> pool;
+        for (int k = 0; k < t; ++k) pool.emplace_back(fn, k);
+        for (auto& th : pool) th.join();
+    };
+    run(format_part);
+    std::vector<char> head(string_bound(std::strlen(original_id ? original_id : "")) + string_bound(std::strlen(source_url ? source_url : "")) + 64);
+    char* h = head.data();
+    h = put_lit(h, "{\"original_id\":");
+    h = put_cstr(h, original_id);
+    h = put_lit(h, ",\"source_url\":");
+    h = put_cstr(h, source_url);
+    h = put_lit(h, ",\"embeddings_data\":[");
+    const size_t head_len = static_cast<size_t>(h - head.data());
+    std::vector<char> tail(string_bound(std::strlen(model_name ? model_name : "")) + 64);
+    char* q = tail.data();
+    q = put_lit(q, "],\"model_name\":");
+    q = put_cstr(q, model_name);
+    q = put_lit(q, ",\"timestamp_ms\":");
+    q = std::to_chars(q, q + 24, timestamp_ms).ptr;
+    *q++ = '}';
+    const size_t tail_len = static_cast<size_t>(q - tail.data());
+    std::vector<size_t> off(static_cast<size_t>(t) + 1, head_len);
+    for (int k = 0; k < t; ++k) off[static_cast<size_t>(k) + 1] = off[static_cast<size_t>(k)] + part_len[static_cast<size_t>(k)];
+    const int64_t total = static_cast<int64_t>(off[static_cast<size_t>(t)] + tail_len);
+    if (out != nullptr && out_cap >= total) {
+        std::memcpy(out, head.data(), head_len);
+        run([&](int k) { std::memcpy(out + off[static_cast<size_t>(k)], parts[static_cast<size_t>(k)].get(), part_len[static_cast<size_t>(k)]); });
+        std::memcpy(out + off[static_cast<size_t>(t)], tail.data(), tail_len);
+    }
+    return total;
 }
 
 }  // namespace
 
 extern "C" {
 
-int32_t b200_json_format_f32(float value, char* out24) { return out24 ? format_f32(value, out24) : -1; }
+int32_t b200_json_format_f32(float value, char* out24) {
+    if (!out24) return -1;
+    char tmp[48];
+    const int n = format_f32(value, tmp);
+    std::memcpy(out24, tmp, static_cast<size_t>(n));
+    return n;
+}
 
 int64_t b200_json_text_with_embeddings(const char* original_id, const char* source_url, const char* const* sentences,
                                        const float* embeddings, int32_t n, int32_t dim, const char* model_name,
                                        uint64_t timestamp_ms, int32_t threads, char* out, int64_t out_cap) {
     if (n < 0 || dim < 0 || (n > 0 && (!sentences || !embeddings))) return -1;
-    // one {"sentence_text":..,"embedding":[..]} object per sentence; every thread formats a contiguous slice of the
-    // sentences into its own buffer, the buffers are concatenated in order
-    int t = threads > 0 ? threads : static_cast<int>(std::thread::hardware_concurrency());
-    if (t < 1) t = 1;
-    if (t > n / 8) t = n / 8 > 0 ? n / 8 : 1;
-    std::vector<std::string> parts(static_cast<size_t>(t));
-    auto work = [&](int k) {
-        const int lo = static_cast<int>(static_cast<int64_t>(n) * k / t), hi = static_cast<int>(static_cast<int64_t>(n) * (k + 1) / t);
-        std::string& o = parts[static_cast<size_t>(k)];
-        o.reserve(static_cast<size_t>(hi - lo) * (static_cast<size_t>(dim) * 12 + 96));
-        for (int i = lo; i < hi; ++i) {
-            if (i) o.push_back(',');
-            o += "{\"sentence_text\":";
-            append_string(o, sentences[i]);
-            o += ",\"embedding\":";
-            append_vector(o, embeddings + static_cast<size_t>(i) * dim, dim);
-            o.push_back('}');
-        }
-    };
-    if (t <= 1) {
-        work(0);
-    } else {
-        std::vector<std::thread> pool;
-        for (int k = 0; k < t; ++k) pool.emplace_back(work, k);
-        for (auto& th : pool) th.join();
-    }
-    size_t total = 256;
-    for (const auto& s : parts) total += s.size();
-    std::string o;
-    o.reserve(total + std::strlen(original_id ? original_id : "") * 6 + std::strlen(source_url ? source_url : "") * 6);
-    o += "{\"original_id\":";
-    append_string(o, original_id);
-    o += ",\"source_url\":";
-    append_string(o, source_url);
-    o += ",\"embeddings_data\":[";
-    for (const auto& s : parts) o += s;
-    o += "],\"model_name\":";
-    append_string(o, model_name);
-    o += ",\"timestamp_ms\":";
-    append_u64(o, timestamp_ms);
-    o.push_back('}');
-    return deliver(o, out, out_cap);
+    const Sentences sn{sentences, nullptr, nullptr, nullptr};
+    return text_with_embeddings(original_id, source_url, sn, embeddings, n, dim, model_name, timestamp_ms, threads, out, out_cap);
+}
+
+int64_t b200_json_text_with_embeddings_ranges(const char* original_id, const char* source_url, const char* text,
+                                              const int64_t* begin, const int64_t* end, const float* embeddings, int32_t n,
+                                              int32_t dim, const char* model_name, uint64_t timestamp_ms, int32_t threads,
+                                              char* out, int64_t out_cap) {
+    if (n < 0 || dim < 0 || (n > 0 && (!text || !begin || !end || !embeddings))) return -1;
+    for (int32_t i = 0; i < n; ++i)
+        if (begin[i] < 0 || end[i] < begin[i]) return -1;
+    const Sentences sn{nullptr, text, begin, end};
+    return text_with_embeddings(original_id, source_url, sn, embeddings, n, dim, model_name, timestamp_ms, threads, out, out_cap);
 }
 
 int64_t b200_json_query_embedding_result(const char* request_id, const float* embedding_or_null, int32_t dim,
                                          const char* model_name_or_null, const char* error_message_or_null, char* out,
                                          int64_t out_cap) {
     if (dim < 0) return -1;
-    std::string o;
-    o.reserve(static_cast<size_t>(dim) * 12 + 128);
-    o += "{\"request_id\":";
-    append_string(o, request_id);
-    o += ",\"embedding\":";
-    if (embedding_or_null) append_vector(o, embedding_or_null, dim); else o += "null";
-    o += ",\"model_name\":";
-    if (model_name_or_null) append_string(o, model_name_or_null); else o += "null";
-    o += ",\"error_message\":";
-    if (error_message_or_null) append_string(o, error_message_or_null); else o += "null";
-    o.push_back('}');
-    return deliver(o, out, out_cap);
+    auto len = [](const char* s) { return s ? std::strlen(s) : size_t(0); };
+    std::vector<char> buf(string_bound(len(request_id)) + vector_bound(dim) + string_bound(len(model_name_or_null)) +
+                          string_bound(len(error_message_or_null)) + 96);
+    char* p = buf.data();
+    p = put_lit(p, "{\"request_id\":");
+    p = put_cstr(p, request_id);
+    p = put_lit(p, ",\"embedding\":");
+    p = embedding_or_null ? put_vector(p, embedding_or_null, dim) : put_lit(p, "null");
+    p = put_lit(p, ",\"model_name\":");
+    p = model_name_or_null ? put_cstr(p, model_name_or_null) : put_lit(p, "null");
+    p = put_lit(p, ",\"error_message\":");
+    p = error_message_or_null ? put_cstr(p, error_message_or_null) : put_lit(p, "null");
+    *p++ = '}';
+    const int64_t total = static_cast<int64_t>(p - buf.data());
+    if (out != nullptr && out_cap >= total) std::memcpy(out, buf.data(), static_cast<size_t>(total));
+    return total;
 }
 
 }  // extern "C"

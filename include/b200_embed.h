@@ -12,8 +12,10 @@
  *     :201-207 masked mean-pool                                         (fused epilogue)
  *     :214  to_vec2::<f32>()                                            (float* out, [batch][hidden])
  * Everything above that call (NATS handling, tokenizers, sentence split) and below it
- * (libs/shared_models payloads, the Qdrant upsert) is unchanged; see INTEGRATION.md for the
- * Rust binding a maintainer would add.
+ * (libs/shared_models payloads, the Qdrant upsert) can stay unchanged; see INTEGRATION.md for the
+ * Rust binding a maintainer would add. The host stages either side of the call have optional
+ * replacements at the end of this header: b200_ingest_* (sentence split + WordPiece tokeniser,
+ * main.rs:28-63, embedding_generator.rs:73-99, :160-187) and b200_json_* (the serde_json payloads).
  *
  * Conventions: every entry point returns B200_EMBED_OK (0) or a negative B200_EMBED_ERR_* code and
  * never throws or aborts across the boundary; the message of the last failure on the calling
@@ -233,6 +235,12 @@ int64_t b200_json_text_with_embeddings(const char* original_id, const char* sour
                                        const float* embeddings /* [n * dim] row-major */, int32_t n, int32_t dim,
                                        const char* model_name, uint64_t timestamp_ms,
                                        int32_t threads /* 0 = all host cores */, char* out, int64_t out_cap);
+/* Same document, the sentences given as byte ranges [begin[i], end[i]) of one UTF-8 text - the form
+ * b200_ingest_split_sentences produces - so that no per-sentence string is built between the two calls. */
+int64_t b200_json_text_with_embeddings_ranges(const char* original_id, const char* source_url, const char* text,
+                                              const int64_t* begin, const int64_t* end, const float* embeddings,
+                                              int32_t n, int32_t dim, const char* model_name, uint64_t timestamp_ms,
+                                              int32_t threads, char* out, int64_t out_cap);
 int64_t b200_json_query_embedding_result(const char* request_id, const float* embedding_or_null, int32_t dim,
                                          const char* model_name_or_null, const char* error_message_or_null, char* out,
                                          int64_t out_cap);

@@ -1,0 +1,59 @@
+"""Raw text in, JSON payload out, through every stage this repo replaces (f1 -> embedding path -> f3) on one GPU:
+split + tokenise on the host cores, b200_embed_forward with host buffers, b200_json_text_with_embeddings.
+MiniLM-L6 shape, random weights, a WordPiece vocabulary trained on the synthetic corpus. Prints the stage times.
+Usage: python scripts/text_e2e.py [n_sentences]"""
+import importlib, json, os, random, sys, tempfile, time
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+
+pkg = importlib.import_module("codename-symbiont_b200")
+abi = pkg.abi
+from tokenizers import Tokenizer, models, normalizers, pre_tokenizers, processors, trainers
+
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 65536
+rng = random.Random(3)
+syll = ["ta", "ri", "mo", "ne", "ka", "su", "lo", "pe", "di", "vu", "an", "er", "in", "st", "ch", "th", "ou", "qu", "ment", "tion", "ing", "ed"]
+lex = ["".join(rng.choice(syll) for _ in range(rng.randint(1, 4))) for _ in range(20000)]
+weights = [1.0 / (i + 1) for i in range(len(lex))]
+def sentence():
+    k = max(3, int(rng.gauss(18, 7)))
+    w = rng.choices(lex, weights, k=k)
+    w[0] = w[0].capitalize()
+    return " ".join(w) + rng.choice([".", ".", "?", "!"])
+pool = [sentence() for _ in range(20000)]
+doc = "  ".join(rng.choice(pool) for _ in range(n))
+
+shape = pkg.weights.MINILM_L6
+tok = Tokenizer(models.WordPiece(unk_token="[UNK]"))
+tok.normalizer = normalizers.BertNormalizer(lowercase=True)
+tok.pre_tokenizer = pre_tokenizers.BertPreTokenizer()
+tok.train_from_iterator(pool, trainers.WordPieceTrainer(vocab_size=8000, special_tokens=["[PAD]", "[UNK]", "[CLS]", "[SEP]", "[MASK]"], show_progress=False))
+tok.post_processor = processors.TemplateProcessing(single="[CLS] $A [SEP]", special_tokens=[("[CLS]", tok.token_to_id("[CLS]")), ("[SEP]", tok.token_to_id("[SEP]"))])
+d = tempfile.mkdtemp()
+tok.save(os.path.join(d, "tokenizer.json"))
+ing = abi.Ingest(os.path.join(d, "tokenizer.json"))
+emb = abi.Embedder.random_init(shape, seed=1)
+P = 128
+ids = abi.host_alloc((n, P), np.uint32); mask = abi.host_alloc((n, P), np.uint32); tt = abi.host_alloc((n, P), np.uint32)
+out = abi.host_alloc((n, shape.hidden_size), np.float32)
+
+def once():
+    t = [time.perf_counter()]
+    cleaned, begin, end = abi.split_sentences(doc); t.append(time.perf_counter())
+    m = len(begin)
+    ing.encode_ranges(cleaned, begin, end, P, 0, (ids[:m], mask[:m], tt[:m])); t.append(time.perf_counter())
+    emb.forward(ids[:m], mask[:m], tt[:m], out=out[:m]); t.append(time.perf_counter())
+    payload = abi.json_text_with_embeddings("doc", "http://x", (cleaned, begin, end), out[:m], "minilm", 1, as_array=True); t.append(time.perf_counter())
+    return m, len(payload), np.diff(t)
+once()
+best = None
+for _ in range(3):
+    m, nbytes, dt = once()
+    if best is None or dt.sum() < best.sum():
+        best = dt
+names = ["split", "tokenise", "embed (H2D + GPU + D2H)", "json"]
+print(f"sentences {m}  text {len(doc) / 1e6:.1f} MB  payload {nbytes / 1e6:.1f} MB  host cores {os.cpu_count()}")
+for k, v in zip(names, best):
+    print(f"  {k:28s} {v * 1e3:8.1f} ms   {m / v:12.0f} sentences/s")
+print(f"  {'total (stages in sequence)':28s} {best.sum() * 1e3:8.1f} ms   {m / best.sum():12.0f} sentences/s")

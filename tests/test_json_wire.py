@@ -81,3 +81,22 @@ def test_formatter_throughput_is_reported(abi, capsys):
         print(f"\n[json] native {len(a) / 1e6 / (t1 - t0):.0f} MB/s ({n / (t1 - t0):,.0f} sentences/s), "
               f"python json.dumps {len(b) / 1e6 / (t2 - t1):.0f} MB/s")
     assert len(a) > n * dim * 4
+
+
+def test_ranges_entry_writes_the_same_document(abi):
+    """b200_json_text_with_embeddings_ranges: sentences as byte ranges of one text (what the splitter returns), including a
+    sentence with an embedded NUL, which the char* form cannot carry."""
+    rng = np.random.default_rng(2)
+    sentences = ["First one.", 'Second "quoted" one?', "third without stop", "x" * 300 + "!"] * 25
+    emb = rng.standard_normal((len(sentences), 96)).astype(np.float32)
+    enc = [s.encode() for s in sentences]
+    text = b" ".join(enc)
+    begin = np.cumsum([0] + [len(e) + 1 for e in enc[:-1]])
+    end = begin + np.array([len(e) for e in enc])
+    a = abi.json_text_with_embeddings("i", "u", sentences, emb, "m", 7, threads=4)
+    b = abi.json_text_with_embeddings("i", "u", (text, begin, end), emb, "m", 7, threads=3)
+    c = abi.json_text_with_embeddings("i", "u", (text, begin, end), emb, "m", 7, threads=1, as_array=True)
+    assert a == b == c.tobytes() == json_oracle.text_with_embeddings("i", "u", sentences, emb, "m", 7)
+    nul = b"a\x00b."
+    got = abi.json_text_with_embeddings("i", "u", (nul, np.array([0]), np.array([4])), emb[:1], "m", 7)
+    assert json.loads(got)["embeddings_data"][0]["sentence_text"] == "a\x00b."
