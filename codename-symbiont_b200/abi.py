@@ -80,6 +80,15 @@ _SIGNATURES = {
                                                           C.c_uint64, C.c_int32, _P, C.c_int64]),
     "b200_json_query_embedding_result": (C.c_int64, [C.c_char_p, _P, C.c_int32, C.c_char_p, C.c_char_p, _P, C.c_int64]),
     "b200_json_format_f32": (C.c_int32, [C.c_float, _P]),
+    "b200_index_last_error": (C.c_char_p, []),
+    "b200_index_create": (C.c_int32, [C.c_int32, C.c_int64, C.c_int32, C.POINTER(_P)]),
+    "b200_index_destroy": (None, [_P]),
+    "b200_index_size": (C.c_int64, [_P]),
+    "b200_index_dim": (C.c_int32, [_P]),
+    "b200_index_add": (C.c_int32, [_P, _P, C.c_int64]),
+    "b200_index_add_device": (C.c_int32, [_P, _P, C.c_int64]),
+    "b200_index_search": (C.c_int32, [_P, _P, C.c_int32, C.c_int32, _P, _P]),
+    "b200_index_last_scan_ms": (C.c_float, [_P]),
     "b200_ingest_last_error": (C.c_char_p, []),
     "b200_ingest_create": (C.c_int32, [C.c_char_p, C.POINTER(_P)]),
     "b200_ingest_destroy": (None, [_P]),
@@ -97,7 +106,7 @@ def declared_symbols() -> list:
     with open(HEADER_PATH) as f:
         text = f.read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
-    return sorted(set(re.findall(r"\b(b200_(?:embed|op|json|ingest)_[a-z0-9_]+)\s*\(", text)))
+    return sorted(set(re.findall(r"\b(b200_(?:embed|op|json|ingest|index)_[a-z0-9_]+)\s*\(", text)))
 
 
 def load_library():
@@ -257,6 +266,66 @@ class Ingest:
         end = np.cumsum([len(b) for b in enc], dtype=np.int64) if enc else np.zeros(0, dtype=np.int64)
         begin = np.concatenate([np.zeros(1, dtype=np.int64), end[:-1]]) if enc else end
         return self.encode_ranges(b"".join(enc), begin, end, seq_len, threads)
+
+
+class Index:
+    """Owns one b200_index handle: exact cosine top-k over vectors resident on one GPU (vector_memory_service's Qdrant
+    collection with Distance::Cosine, main.rs:34-37, :140-202, :261-286)."""
+
+    def __init__(self, dim: int, capacity_hint: int = 0, device: int = 0):
+        self._h = _P()
+        self._check(load_library().b200_index_create(dim, capacity_hint, device, C.byref(self._h)))
+        self.dim = dim
+
+    @staticmethod
+    def _check(rc: int):
+        if rc != 0:
+            raise B200EmbedError(rc, load_library().b200_index_last_error().decode(errors="replace"))
+
+    def close(self):
+        if self._h:
+            load_library().b200_index_destroy(self._h)
+            self._h = _P()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __len__(self) -> int:
+        return int(load_library().b200_index_size(self._h))
+
+    def add(self, vectors: np.ndarray) -> None:
+        v = np.ascontiguousarray(vectors, dtype=np.float32)
+        if v.ndim != 2 or v.shape[1] != self.dim:
+            raise ValueError("vectors must be [n, dim]")
+        self._check(load_library().b200_index_add(self._h, v.ctypes.data, v.shape[0]))
+
+    def add_device(self, d_vectors: int, n: int) -> None:
+        self._check(load_library().b200_index_add_device(self._h, d_vectors, n))
+
+    def search(self, queries: np.ndarray, top_k: int):
+        """-> (ids [q, top_k] int64, scores [q, top_k] float32), best first."""
+        qv = np.ascontiguousarray(queries, dtype=np.float32)
+        if qv.ndim == 1:
+            qv = qv[None, :]
+        if qv.ndim != 2 or qv.shape[1] != self.dim:
+            raise ValueError("queries must be [q, dim]")
+        ids = np.empty((qv.shape[0], top_k), dtype=np.int64)
+        scores = np.empty((qv.shape[0], top_k), dtype=np.float32)
+        self._check(load_library().b200_index_search(self._h, qv.ctypes.data, qv.shape[0], top_k, ids.ctypes.data, scores.ctypes.data))
+        return ids, scores
+
+    @property
+    def last_scan_ms(self) -> float:
+        return float(load_library().b200_index_last_scan_ms(self._h))
 
 
 def host_alloc(shape, dtype) -> np.ndarray:

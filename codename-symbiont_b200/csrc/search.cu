@@ -1,0 +1,503 @@
+// f4: exact cosine top-k over the embeddings the path produces, resident in HBM, as the alternative to the
+// Qdrant search hop of the consumer:
+//   /root/reference/services/vector_memory_service/src/main.rs:34-37   collection: VectorParams{size, Distance::Cosine}
+//   :140-202  upsert: one point per sentence, vectors = the embedding          -> b200_index_add / _add_device
+//   :261-286  SearchPoints{vector, limit = top_k, score_threshold: None, ..}   -> b200_index_search
+//   :319-403  results in descending score order, score = cosine similarity     -> ids + scores, payload lookup stays host-side
+// Qdrant (un-vendored service; client crate qdrant-client in vector_memory_service/Cargo.toml) normalises every vector on
+// insert and the query on search for Distance::Cosine and scores with a dot product (lib/segment/src/spaces/simple.rs,
+// cosine_preprocess: unchanged if the length is < f32::EPSILON or within 1e-6 of 1); below its indexing threshold it scans
+// every vector, above it it answers from an HNSW graph (approximate). This is the exact scan at any size.
+//
+// Work per search: one pass over the [n, dim] f32 matrix (HBM-bound: 4 * dim bytes per vector, shared by up to 4 queries),
+// a score per vector and query, then a top-k selection that touches 4 bytes per vector. Kernels:
+//   normalize_rows   one warp per vector, in place (insert and query preparation)
+//   scan             one warp per block of 32 consecutive vectors, query fragments in registers, fp32 FMA, coalesced loads
+//                    (512 B per warp instruction, streaming), one coalesced 128 B score store per block
+//   topk_level       blocks of 4096 candidates sorted best-first in shared memory (bitonic, ties -> lower id), the first k
+//                    of each kept; applied level by level until one block holds the answer
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+
+#include "../../include/b200_embed.h"
+
+namespace {
+
+thread_local std::string g_index_err;
+int fail(int code, const std::string& msg) {
+    g_index_err = msg;
+    return code;
+}
+int cuda_fail(cudaError_t e, const char* what) {
+    const int code = (e == cudaErrorMemoryAllocation) ? B200_EMBED_ERR_OOM
+                     : (e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver) ? B200_EMBED_ERR_NO_DEVICE
+                                                                                   : B200_EMBED_ERR_CUDA;
+    return fail(code, std::string(what) + ": " + cudaGetErrorString(e));
+}
+#define IX_TRY(expr)                                          \
+    do {                                                      \
+        cudaError_t e__ = (expr);                             \
+        if (e__ != cudaSuccess) return cuda_fail(e__, #expr); \
+    } while (0)
+
+constexpr int QT_MAX = 4;      // queries that share one pass over the matrix
+constexpr int SEL_CHUNK = 4096;  // candidates per selection block
+constexpr int SEL_THREADS = 256;
+constexpr int K_MAX = 1024;
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// cosine_preprocess, one warp per row, in place
+__global__ void normalize_rows_kernel(float* __restrict__ v, int64_t n, int dim) {
+    const int64_t row = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (row >= n) return;
+    float4* p = reinterpret_cast<float4*>(v + row * dim);
+    const int n4 = dim >> 2;
+    float s = 0.f;
+    for (int j = lane; j < n4; j += 32) {
+        const float4 x = p[j];
+        s = fmaf(x.x, x.x, s); s = fmaf(x.y, x.y, s); s = fmaf(x.z, x.z, s); s = fmaf(x.w, x.w, s);
+    }
+    s = warp_sum(s);
+    const float len = sqrtf(s);
+    if (len < 1.1920929e-07f || fabsf(len - 1.0f) < 1e-6f) return;  // zero or already normalised: unchanged
+    for (int j = lane; j < n4; j += 32) {
+        float4 x = p[j];
+        x.x /= len; x.y /= len; x.z /= len; x.w /= len;
+        p[j] = x;
+    }
+}
+
+// scores[t][r] = <vecs[r], q[t]> for r < n. EPL = dim / 32 elements per lane (as EPL/4 float4: lane, lane+32, ...).
+template <int EPL, int QT>
+__global__ void __launch_bounds__(256) scan_kernel(const float* __restrict__ vecs, int64_t n, const float* __restrict__ queries,
+                                                   float* __restrict__ scores, int64_t score_stride) {
+    constexpr int V4 = EPL / 4, DIM = EPL * 32;
+    const int lane = threadIdx.x & 31;
+    const int64_t warp_global = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    const int64_t warps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+    float4 q[QT][V4];
+#pragma unroll
+    for (int t = 0; t < QT; ++t)
+#pragma unroll
+        for (int j = 0; j < V4; ++j) q[t][j] = reinterpret_cast<const float4*>(queries + t * DIM)[j * 32 + lane];
+    const int64_t nblocks = (n + 31) >> 5;
+    for (int64_t b = warp_global; b < nblocks; b += warps) {
+        const int64_t r0 = b << 5;
+        const int rows = static_cast<int>(n - r0 < 32 ? n - r0 : 32);
+        float mine[QT];
+#pragma unroll
+        for (int t = 0; t < QT; ++t) mine[t] = 0.f;
+        // two rows per step: both rows' loads are issued before either is consumed
+        for (int i = 0; i < rows; i += 2) {
+            const bool two = i + 1 < rows;
+            const float4* p0 = reinterpret_cast<const float4*>(vecs + (r0 + i) * DIM);
+            const float4* p1 = reinterpret_cast<const float4*>(vecs + (r0 + i + (two ? 1 : 0)) * DIM);
+            float4 x0[V4], x1[V4];
+#pragma unroll
+            for (int j = 0; j < V4; ++j) x0[j] = __ldcs(p0 + j * 32 + lane);
+#pragma unroll
+            for (int j = 0; j < V4; ++j) x1[j] = __ldcs(p1 + j * 32 + lane);
+#pragma unroll
+            for (int t = 0; t < QT; ++t) {
+                float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+                for (int j = 0; j < V4; ++j) {
+                    a0 = fmaf(x0[j].x, q[t][j].x, a0); a0 = fmaf(x0[j].y, q[t][j].y, a0);
+                    a0 = fmaf(x0[j].z, q[t][j].z, a0); a0 = fmaf(x0[j].w, q[t][j].w, a0);
+                    a1 = fmaf(x1[j].x, q[t][j].x, a1); a1 = fmaf(x1[j].y, q[t][j].y, a1);
+                    a1 = fmaf(x1[j].z, q[t][j].z, a1); a1 = fmaf(x1[j].w, q[t][j].w, a1);
+                }
+                a0 = warp_sum(a0);
+                a1 = warp_sum(a1);
+                if (lane == i) mine[t] = a0;
+                if (two && lane == i + 1) mine[t] = a1;
+            }
+        }
+        if (lane < rows) {
+#pragma unroll
+            for (int t = 0; t < QT; ++t) scores[t * score_stride + r0 + lane] = mine[t];
+        }
+    }
+}
+
+// (score, id) ordering of the results: higher score first, lower id first among equal scores; NaN never wins.
+__device__ __forceinline__ bool better(float s, int64_t id, float bs, int64_t bid) {
+    return s > bs || (s == bs && id < bid);
+}
+
+// One selection level. Block (blk, qi) takes candidates [blk * SEL_CHUNK, +SEL_CHUNK) of query qi (ids implicit = position
+// when ids_in == nullptr), sorts them best-first in shared memory (bitonic network: 78 compare-exchange stages whatever
+// k is; k rounds of block-wide argmax measured 1.5 us per round) and writes the first k to out[qi][blk * k ...]. Missing
+// ones get (-inf, -1).
+__global__ void __launch_bounds__(SEL_THREADS) topk_level_kernel(const float* __restrict__ sc_in, const int64_t* __restrict__ ids_in,
+                                                                 int64_t count, int64_t in_stride, int k,
+                                                                 float* __restrict__ sc_out, int64_t* __restrict__ ids_out,
+                                                                 int64_t out_stride) {
+    extern __shared__ __align__(16) unsigned char sel_smem[];  // SEL_CHUNK ids (8 B) then SEL_CHUNK scores (4 B)
+    int64_t* s_id = reinterpret_cast<int64_t*>(sel_smem);
+    float* s_sc = reinterpret_cast<float*>(sel_smem + SEL_CHUNK * sizeof(int64_t));
+    const int tid = threadIdx.x;
+    const int64_t base = static_cast<int64_t>(blockIdx.x) * SEL_CHUNK;
+    const float* sc = sc_in + static_cast<int64_t>(blockIdx.y) * in_stride;
+    const int64_t* ids = ids_in ? ids_in + static_cast<int64_t>(blockIdx.y) * in_stride : nullptr;
+    const float NEG = -INFINITY;
+    for (int i = tid; i < SEL_CHUNK; i += SEL_THREADS) {
+        const int64_t g = base + i;
+        float s = NEG;
+        int64_t id = INT64_MAX;  // padding sorts behind every real candidate, also behind one that scores -inf
+        if (g < count) {
+            s = sc[g];
+            id = ids ? ids[g] : g;
+            if (!(s == s) || id < 0) { s = NEG; id = INT64_MAX; }  // NaN scores and padding never win
+        }
+        s_sc[i] = s;
+        s_id[i] = id;
+    }
+    __syncthreads();
+    for (int size = 2; size <= SEL_CHUNK; size <<= 1) {
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            for (int t = tid; t < SEL_CHUNK / 2; t += SEL_THREADS) {
+                const int i = 2 * t - (t & (stride - 1));  // the lower index of the t-th pair at this stride
+                const int j = i + stride;
+                const bool best_first = (i & size) == 0;
+                const float si = s_sc[i], sj = s_sc[j];
+                const int64_t ii = s_id[i], ij = s_id[j];
+                const bool swap = best_first ? better(sj, ij, si, ii) : better(si, ii, sj, ij);
+                if (swap) { s_sc[i] = sj; s_sc[j] = si; s_id[i] = ij; s_id[j] = ii; }
+            }
+            __syncthreads();
+        }
+    }
+    float* o_sc = sc_out + static_cast<int64_t>(blockIdx.y) * out_stride + static_cast<int64_t>(blockIdx.x) * k;
+    int64_t* o_id = ids_out + static_cast<int64_t>(blockIdx.y) * out_stride + static_cast<int64_t>(blockIdx.x) * k;
+    for (int i = tid; i < k; i += SEL_THREADS) {
+        const bool real = s_id[i] != INT64_MAX;
+        o_sc[i] = real ? s_sc[i] : NEG;
+        o_id[i] = real ? s_id[i] : -1;
+    }
+}
+
+// The same level for small k: k rounds of block-wide argmax instead of a full sort (1.5 us per round against ~100 us for
+// the sort of a first level of 2 M candidates; the engine takes this one up to k = 48).
+__global__ void __launch_bounds__(SEL_THREADS) topk_rounds_kernel(const float* __restrict__ sc_in, const int64_t* __restrict__ ids_in,
+                                                                  int64_t count, int64_t in_stride, int k,
+                                                                  float* __restrict__ sc_out, int64_t* __restrict__ ids_out,
+                                                                  int64_t out_stride) {
+    extern __shared__ __align__(16) unsigned char sel_smem[];
+    int64_t* s_id = reinterpret_cast<int64_t*>(sel_smem);
+    float* s_sc = reinterpret_cast<float*>(sel_smem + SEL_CHUNK * sizeof(int64_t));
+    __shared__ float w_sc[SEL_THREADS / 32];
+    __shared__ int64_t w_id[SEL_THREADS / 32];
+    __shared__ int w_pos[SEL_THREADS / 32];
+    __shared__ int win_pos;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t base = static_cast<int64_t>(blockIdx.x) * SEL_CHUNK;
+    const float* sc = sc_in + static_cast<int64_t>(blockIdx.y) * in_stride;
+    const int64_t* ids = ids_in ? ids_in + static_cast<int64_t>(blockIdx.y) * in_stride : nullptr;
+    const float NEG = -INFINITY;
+    for (int i = tid; i < SEL_CHUNK; i += SEL_THREADS) {
+        const int64_t g = base + i;
+        float s = NEG;
+        int64_t id = -1;
+        if (g < count) {
+            s = sc[g];
+            id = ids ? ids[g] : g;
+            if (!(s == s) || id < 0) { s = NEG; id = -1; }  // NaN scores and padding never win
+        }
+        s_sc[i] = s;
+        s_id[i] = id;
+    }
+    __syncthreads();
+    // each thread owns positions tid, tid + 256, ...; its current best is cached and recomputed only when it was taken
+    float my_s = NEG;
+    int64_t my_id = INT64_MAX;
+    int my_pos = -1;
+    auto rescan = [&]() {
+        my_s = NEG; my_id = INT64_MAX; my_pos = -1;
+        for (int i = tid; i < SEL_CHUNK; i += SEL_THREADS) {
+            const int64_t id = s_id[i];
+            if (id >= 0 && (my_pos < 0 || better(s_sc[i], id, my_s, my_id))) { my_s = s_sc[i]; my_id = id; my_pos = i; }
+        }
+    };
+    rescan();
+    float* o_sc = sc_out + static_cast<int64_t>(blockIdx.y) * out_stride + static_cast<int64_t>(blockIdx.x) * k;
+    int64_t* o_id = ids_out + static_cast<int64_t>(blockIdx.y) * out_stride + static_cast<int64_t>(blockIdx.x) * k;
+    for (int round = 0; round < k; ++round) {
+        float bs = my_s;
+        int64_t bid = my_pos >= 0 ? my_id : INT64_MAX;
+        int bpos = my_pos;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float os = __shfl_xor_sync(0xffffffffu, bs, o);
+            const int64_t oid = __shfl_xor_sync(0xffffffffu, bid, o);
+            const int opos = __shfl_xor_sync(0xffffffffu, bpos, o);
+            if (opos >= 0 && (bpos < 0 || better(os, oid, bs, bid))) { bs = os; bid = oid; bpos = opos; }
+        }
+        if (lane == 0) { w_sc[warp] = bs; w_id[warp] = bid; w_pos[warp] = bpos; }
+        __syncthreads();
+        if (tid == 0) {
+            float fs = w_sc[0];
+            int64_t fid = w_id[0];
+            int fpos = w_pos[0];
+            for (int w = 1; w < SEL_THREADS / 32; ++w)
+                if (w_pos[w] >= 0 && (fpos < 0 || better(w_sc[w], w_id[w], fs, fid))) { fs = w_sc[w]; fid = w_id[w]; fpos = w_pos[w]; }
+            win_pos = fpos;
+            o_sc[round] = fpos >= 0 ? fs : NEG;
+            o_id[round] = fpos >= 0 ? fid : -1;
+            if (fpos >= 0) s_id[fpos] = -1;  // taken
+        }
+        __syncthreads();
+        const int wp = win_pos;
+        if (wp >= 0 && (wp % SEL_THREADS) == tid) rescan();  // only the owner of the taken position looks again
+    }
+}
+
+constexpr int K_ROUNDS_MAX = 48;
+
+constexpr size_t SEL_SMEM = SEL_CHUNK * (sizeof(int64_t) + sizeof(float));
+
+template <int EPL>
+cudaError_t launch_scan_qt(int qt, const float* vecs, int64_t n, const float* q, float* scores, int64_t stride, int grid,
+                           cudaStream_t s) {
+    if (qt == 1) scan_kernel<EPL, 1><<<grid, 256, 0, s>>>(vecs, n, q, scores, stride);
+    else if (qt == 2) scan_kernel<EPL, 2><<<grid, 256, 0, s>>>(vecs, n, q, scores, stride);
+    else if (qt == 3) scan_kernel<EPL, 3><<<grid, 256, 0, s>>>(vecs, n, q, scores, stride);
+    else scan_kernel<EPL, 4><<<grid, 256, 0, s>>>(vecs, n, q, scores, stride);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_scan(int dim, int qt, const float* vecs, int64_t n, const float* q, float* scores, int64_t stride,
+                        int num_sms, cudaStream_t s) {
+    // 8 warps per CTA, enough CTAs to fill every SM a few times over but never more warps than blocks of 32 rows
+    const int64_t blocks32 = (n + 31) / 32;
+    int64_t grid = (blocks32 + 7) / 8;
+    const int64_t cap = static_cast<int64_t>(num_sms) * 8;
+    if (grid > cap) grid = cap;
+    if (grid < 1) grid = 1;
+    const int g = static_cast<int>(grid);
+    switch (dim) {
+        case 128: return launch_scan_qt<4>(qt, vecs, n, q, scores, stride, g, s);
+        case 256: return launch_scan_qt<8>(qt, vecs, n, q, scores, stride, g, s);
+        case 384: return launch_scan_qt<12>(qt, vecs, n, q, scores, stride, g, s);
+        case 512: return launch_scan_qt<16>(qt, vecs, n, q, scores, stride, g, s);
+        case 768: return launch_scan_qt<24>(qt, vecs, n, q, scores, stride, g, s);
+        case 1024: return launch_scan_qt<32>(qt, vecs, n, q, scores, stride, g, s);
+        default: return cudaErrorInvalidValue;
+    }
+}
+
+}  // namespace
+
+struct b200_index {
+    int device = 0, dim = 0, num_sms = 148;
+    int64_t cap = 0, n = 0;
+    float* vecs = nullptr;          // [cap, dim] f32, rows normalised on insert
+    float* d_q = nullptr;           // [QT_MAX, dim] normalised queries of the current pass
+    float* d_scores = nullptr;      // [QT_MAX, cap]
+    float* d_csc[2] = {nullptr, nullptr};    // candidate scores of the selection levels (ping-pong)
+    int64_t* d_cid[2] = {nullptr, nullptr};  // candidate ids
+    int64_t cand_cap = 0;           // per query
+    float* d_out_sc = nullptr;      // [QT_MAX, K_MAX]
+    int64_t* d_out_id = nullptr;
+    float *h_q = nullptr, *h_out_sc = nullptr;  // pinned staging: queries in, results out
+    int64_t* h_out_id = nullptr;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    float last_scan_ms = 0.f, last_select_ms = 0.f;
+    std::mutex mu;
+};
+
+namespace {
+
+struct DevGuard {
+    int prev = -1;
+    explicit DevGuard(int d) { cudaGetDevice(&prev); if (prev != d) cudaSetDevice(d); else prev = -1; }
+    ~DevGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+int64_t level_blocks(int64_t count) { return (count + SEL_CHUNK - 1) / SEL_CHUNK; }
+
+// Normalises `q` queries already in ix->d_q, scans, selects; results land in ix->d_out_sc / d_out_id ([qt][k]).
+int search_pass(b200_index* ix, int qt, int k) {
+    cudaStream_t s = ix->stream;
+    const int64_t n = ix->n;
+    normalize_rows_kernel<<<(qt * 32 + 255) / 256, 256, 0, s>>>(ix->d_q, qt, ix->dim);
+    IX_TRY(cudaGetLastError());
+    IX_TRY(cudaEventRecord(ix->ev0, s));
+    IX_TRY(launch_scan(ix->dim, qt, ix->vecs, n, ix->d_q, ix->d_scores, ix->cap, ix->num_sms, s));
+    IX_TRY(cudaEventRecord(ix->ev1, s));
+    // selection levels: scores -> candidates -> ... -> one block
+    const float* sc_in = ix->d_scores;
+    const int64_t* id_in = nullptr;
+    int64_t count = n, in_stride = ix->cap;
+    int pp = 0;
+    for (;;) {
+        const int64_t nb = level_blocks(count);
+        const bool last = nb == 1;
+        float* sc_out = last ? ix->d_out_sc : ix->d_csc[pp];
+        int64_t* id_out = last ? ix->d_out_id : ix->d_cid[pp];
+        const int64_t out_stride = last ? K_MAX : ix->cand_cap;
+        const dim3 grid(static_cast<unsigned>(nb), static_cast<unsigned>(qt));
+        if (k <= K_ROUNDS_MAX)
+            topk_rounds_kernel<<<grid, SEL_THREADS, SEL_SMEM, s>>>(sc_in, id_in, count, in_stride, k, sc_out, id_out, out_stride);
+        else
+            topk_level_kernel<<<grid, SEL_THREADS, SEL_SMEM, s>>>(sc_in, id_in, count, in_stride, k, sc_out, id_out, out_stride);
+        IX_TRY(cudaGetLastError());
+        if (last) break;
+        sc_in = sc_out; id_in = id_out; count = nb * k; in_stride = out_stride;
+        pp ^= 1;
+    }
+    return B200_EMBED_OK;
+}
+
+int ensure_capacity(b200_index* ix, int64_t want) {
+    if (want <= ix->cap) return B200_EMBED_OK;
+    int64_t cap = ix->cap > 0 ? ix->cap : 4096;
+    while (cap < want) cap *= 2;
+    float* nv = nullptr;
+    IX_TRY(cudaMalloc(&nv, static_cast<size_t>(cap) * ix->dim * sizeof(float)));
+    if (ix->n > 0) IX_TRY(cudaMemcpyAsync(nv, ix->vecs, static_cast<size_t>(ix->n) * ix->dim * sizeof(float), cudaMemcpyDeviceToDevice, ix->stream));
+    IX_TRY(cudaStreamSynchronize(ix->stream));
+    if (ix->vecs) cudaFree(ix->vecs);
+    ix->vecs = nv;
+    if (ix->d_scores) cudaFree(ix->d_scores);
+    ix->d_scores = nullptr;
+    IX_TRY(cudaMalloc(&ix->d_scores, static_cast<size_t>(cap) * QT_MAX * sizeof(float)));
+    // first level keeps at most K_MAX of every SEL_CHUNK candidates
+    const int64_t cand = level_blocks(cap) * K_MAX;
+    for (int i = 0; i < 2; ++i) {
+        if (ix->d_csc[i]) cudaFree(ix->d_csc[i]);
+        if (ix->d_cid[i]) cudaFree(ix->d_cid[i]);
+        ix->d_csc[i] = nullptr; ix->d_cid[i] = nullptr;
+        IX_TRY(cudaMalloc(&ix->d_csc[i], static_cast<size_t>(cand) * QT_MAX * sizeof(float)));
+        IX_TRY(cudaMalloc(&ix->d_cid[i], static_cast<size_t>(cand) * QT_MAX * sizeof(int64_t)));
+    }
+    ix->cand_cap = cand;
+    ix->cap = cap;
+    return B200_EMBED_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* b200_index_last_error(void) { return g_index_err.c_str(); }
+
+int32_t b200_index_create(int32_t dim, int64_t capacity_hint, int32_t device, b200_index** out) {
+    if (!out) return fail(B200_EMBED_ERR_INVALID_ARG, "null out pointer");
+    *out = nullptr;
+    if (!(dim == 128 || dim == 256 || dim == 384 || dim == 512 || dim == 768 || dim == 1024))
+        return fail(B200_EMBED_ERR_UNSUPPORTED_SHAPE, "index dimension must be 128, 256, 384, 512, 768 or 1024");
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0)
+        return fail(B200_EMBED_ERR_NO_DEVICE, "no CUDA device: the index has no CPU fallback");
+    if (device < 0 || device >= count) return fail(B200_EMBED_ERR_INVALID_ARG, "bad device ordinal");
+    DevGuard guard(device);
+    b200_index* ix = new b200_index();
+    ix->device = device;
+    ix->dim = dim;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) ix->num_sms = prop.multiProcessorCount;
+    auto bail = [&](int rc) { b200_index_destroy(ix); return rc; };
+    if (cudaStreamCreateWithFlags(&ix->stream, cudaStreamNonBlocking) != cudaSuccess) return bail(fail(B200_EMBED_ERR_CUDA, "stream"));
+    if (cudaEventCreate(&ix->ev0) != cudaSuccess || cudaEventCreate(&ix->ev1) != cudaSuccess) return bail(fail(B200_EMBED_ERR_CUDA, "event"));
+    if (cudaMalloc(&ix->d_q, sizeof(float) * QT_MAX * dim) != cudaSuccess ||
+        cudaMalloc(&ix->d_out_sc, sizeof(float) * QT_MAX * K_MAX) != cudaSuccess ||
+        cudaMalloc(&ix->d_out_id, sizeof(int64_t) * QT_MAX * K_MAX) != cudaSuccess)
+        return bail(fail(B200_EMBED_ERR_OOM, "workspace"));
+    if (cudaHostAlloc(&ix->h_q, sizeof(float) * QT_MAX * dim, cudaHostAllocDefault) != cudaSuccess ||
+        cudaHostAlloc(&ix->h_out_sc, sizeof(float) * QT_MAX * K_MAX, cudaHostAllocDefault) != cudaSuccess ||
+        cudaHostAlloc(&ix->h_out_id, sizeof(int64_t) * QT_MAX * K_MAX, cudaHostAllocDefault) != cudaSuccess)
+        return bail(fail(B200_EMBED_ERR_OOM, "pinned staging"));
+    if (cudaFuncSetAttribute(topk_level_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(SEL_SMEM)) != cudaSuccess ||
+        cudaFuncSetAttribute(topk_rounds_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(SEL_SMEM)) != cudaSuccess)
+        return bail(fail(B200_EMBED_ERR_CUDA, "shared memory attribute"));
+    const int rc = ensure_capacity(ix, capacity_hint > 0 ? capacity_hint : 4096);
+    if (rc) return bail(rc);
+    *out = ix;
+    return B200_EMBED_OK;
+}
+
+void b200_index_destroy(b200_index* ix) {
+    if (!ix) return;
+    DevGuard guard(ix->device);
+    if (ix->stream) cudaStreamSynchronize(ix->stream);
+    for (void* p : {static_cast<void*>(ix->vecs), static_cast<void*>(ix->d_q), static_cast<void*>(ix->d_scores),
+                    static_cast<void*>(ix->d_csc[0]), static_cast<void*>(ix->d_csc[1]), static_cast<void*>(ix->d_cid[0]),
+                    static_cast<void*>(ix->d_cid[1]), static_cast<void*>(ix->d_out_sc), static_cast<void*>(ix->d_out_id)})
+        if (p) cudaFree(p);
+    for (void* p : {static_cast<void*>(ix->h_q), static_cast<void*>(ix->h_out_sc), static_cast<void*>(ix->h_out_id)})
+        if (p) cudaFreeHost(p);
+    if (ix->ev0) cudaEventDestroy(ix->ev0);
+    if (ix->ev1) cudaEventDestroy(ix->ev1);
+    if (ix->stream) cudaStreamDestroy(ix->stream);
+    delete ix;
+}
+
+int64_t b200_index_size(const b200_index* ix) { return ix ? ix->n : -1; }
+int32_t b200_index_dim(const b200_index* ix) { return ix ? ix->dim : -1; }
+
+static int32_t index_add(b200_index* ix, const float* vectors, int64_t n, bool on_device) {
+    if (!ix || n < 0 || (n > 0 && !vectors)) return fail(B200_EMBED_ERR_INVALID_ARG, "bad argument");
+    if (n == 0) return B200_EMBED_OK;
+    std::lock_guard<std::mutex> lk(ix->mu);
+    DevGuard guard(ix->device);
+    const int rc = ensure_capacity(ix, ix->n + n);
+    if (rc) return rc;
+    float* dst = ix->vecs + ix->n * ix->dim;
+    IX_TRY(cudaMemcpyAsync(dst, vectors, static_cast<size_t>(n) * ix->dim * sizeof(float),
+                           on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, ix->stream));
+    const int64_t blocks = (n * 32 + 255) / 256;
+    normalize_rows_kernel<<<static_cast<unsigned>(blocks), 256, 0, ix->stream>>>(dst, n, ix->dim);
+    IX_TRY(cudaGetLastError());
+    IX_TRY(cudaStreamSynchronize(ix->stream));
+    ix->n += n;
+    return B200_EMBED_OK;
+}
+
+int32_t b200_index_add(b200_index* ix, const float* vectors, int64_t n) { return index_add(ix, vectors, n, false); }
+int32_t b200_index_add_device(b200_index* ix, const float* device_vectors, int64_t n) { return index_add(ix, device_vectors, n, true); }
+
+int32_t b200_index_search(b200_index* ix, const float* queries, int32_t q, int32_t top_k, int64_t* ids_out, float* scores_out) {
+    if (!ix || q < 0 || (q > 0 && (!queries || !ids_out || !scores_out))) return fail(B200_EMBED_ERR_INVALID_ARG, "bad argument");
+    if (top_k < 1 || top_k > K_MAX) return fail(B200_EMBED_ERR_INVALID_ARG, "top_k must be between 1 and 1024");
+    std::lock_guard<std::mutex> lk(ix->mu);
+    DevGuard guard(ix->device);
+    ix->last_scan_ms = ix->last_select_ms = 0.f;
+    if (ix->n == 0) {
+        for (int64_t i = 0; i < static_cast<int64_t>(q) * top_k; ++i) { ids_out[i] = -1; scores_out[i] = -INFINITY; }
+        return B200_EMBED_OK;
+    }
+    for (int q0 = 0; q0 < q; q0 += QT_MAX) {
+        const int qt = q - q0 < QT_MAX ? q - q0 : QT_MAX;
+        std::memcpy(ix->h_q, queries + static_cast<size_t>(q0) * ix->dim, sizeof(float) * qt * ix->dim);
+        IX_TRY(cudaMemcpyAsync(ix->d_q, ix->h_q, sizeof(float) * qt * ix->dim, cudaMemcpyHostToDevice, ix->stream));
+        const int rc = search_pass(ix, qt, top_k);
+        if (rc) return rc;
+        IX_TRY(cudaMemcpyAsync(ix->h_out_sc, ix->d_out_sc, sizeof(float) * qt * K_MAX, cudaMemcpyDeviceToHost, ix->stream));
+        IX_TRY(cudaMemcpyAsync(ix->h_out_id, ix->d_out_id, sizeof(int64_t) * qt * K_MAX, cudaMemcpyDeviceToHost, ix->stream));
+        IX_TRY(cudaStreamSynchronize(ix->stream));
+        for (int t = 0; t < qt; ++t) {
+            std::memcpy(scores_out + static_cast<size_t>(q0 + t) * top_k, ix->h_out_sc + static_cast<size_t>(t) * K_MAX, sizeof(float) * top_k);
+            std::memcpy(ids_out + static_cast<size_t>(q0 + t) * top_k, ix->h_out_id + static_cast<size_t>(t) * K_MAX, sizeof(int64_t) * top_k);
+        }
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, ix->ev0, ix->ev1) == cudaSuccess) ix->last_scan_ms += ms;
+    }
+    return B200_EMBED_OK;
+}
+
+float b200_index_last_scan_ms(const b200_index* ix) { return ix ? ix->last_scan_ms : -1.f; }
+
+}  // extern "C"

@@ -281,6 +281,30 @@ int32_t b200_ingest_encode(const b200_ingest* t, const char* text, const int64_t
                            int32_t seq_len, int32_t threads, uint32_t* ids, uint32_t* mask, uint32_t* type_ids,
                            int32_t* lengths_or_null);
 
+/* -- resident cosine index: the search step after the path (f4; CUDA, no CPU fallback) ---------------------------
+ * Exact cosine top-k over embeddings kept in HBM, as an alternative to the Qdrant hop of vector_memory_service
+ * (vector_memory_service/src/main.rs:34-37 collection with Distance::Cosine; :140-202 upsert of one vector per
+ * sentence; :261-286 SearchPoints{vector, limit = top_k, no filter, no score threshold}; :319-403 results in
+ * descending score order). Like Qdrant for Distance::Cosine, vectors are normalised on insert and the query on
+ * search, and the score is their dot product (f32). Row numbers (insertion order, from 0) are the ids: the service
+ * keeps its id -> payload map as it keeps Qdrant's point ids today. Errors: b200_index_last_error(). */
+typedef struct b200_index b200_index;
+const char* b200_index_last_error(void);
+/* dim: 128, 256, 384, 512, 768 or 1024. capacity_hint: vectors to reserve room for (the index grows by doubling). */
+int32_t b200_index_create(int32_t dim, int64_t capacity_hint, int32_t device, b200_index** out);
+void b200_index_destroy(b200_index* ix);
+int64_t b200_index_size(const b200_index* ix);
+int32_t b200_index_dim(const b200_index* ix);
+/* Appends n vectors ([n, dim] f32 row-major, host or device memory); they get ids size() .. size() + n - 1. */
+int32_t b200_index_add(b200_index* ix, const float* vectors, int64_t n);
+int32_t b200_index_add_device(b200_index* ix, const float* device_vectors, int64_t n);
+/* q queries ([q, dim] f32, host) -> ids_out / scores_out [q, top_k] (host), best first; equal scores are ordered by
+ * id; with fewer than top_k vectors in the index the rest is (-1, -inf). 1 <= top_k <= 1024. Blocks until done. */
+int32_t b200_index_search(b200_index* ix, const float* queries, int32_t q, int32_t top_k, int64_t* ids_out,
+                          float* scores_out);
+/* Device time of the scan kernel(s) of the last search on this index, in ms (CUDA events on the index's stream). */
+float b200_index_last_scan_ms(const b200_index* ix);
+
 #ifdef __cplusplus
 }
 #endif
