@@ -73,6 +73,17 @@ struct Workspace {
     }
 };
 
+// A small call is launch-bound (about twenty kernels of 5-15 us): its kernel sequence is captured once per
+// (batch, seq_len, flags) and replayed as one CUDA graph. Every pointer in it belongs to the context, so a graph stays
+// valid until one of the context's buffers is reallocated (g_alloc_gen moves).
+struct GraphEntry {
+    uint64_t key = 0;
+    cudaGraphExec_t exec = nullptr;  // nullptr: the shape has been seen once (and run the plain way), not captured yet
+    int launches = 0;
+};
+std::atomic<uint64_t> g_alloc_gen{1};
+thread_local int64_t t_launches = 0;  // kernels this thread has enqueued (what a capture recorded = its difference)
+
 struct ProfRecord {
     int kind;
     cudaEvent_t start, stop;
@@ -94,6 +105,8 @@ struct Context {
     std::vector<cudaEvent_t> ev_pool;
     size_t ev_used = 0;
     std::vector<ProfRecord> prof;
+    std::vector<GraphEntry> graphs;
+    uint64_t graph_gen = 0;
     bool busy = false;
     bool created = false;
 };
@@ -119,6 +132,7 @@ struct b200_embed {
     bool force_fused_ffn = false, force_qkv_attn = false;
     bool qkv_attn = true;    // K23 replaces the QKV GEMM + attention pair whenever it supports the call (hidden 128 / 256 / 384,
                              // head_dim 32, seq_len <= 128); B200_EMBED_QKV_ATTN=0 for A/B
+    bool use_graphs = true;  // small host-buffer calls replay a captured CUDA graph; B200_EMBED_GRAPHS=0 for A/B
     bool attn_mma = false;  // B200_EMBED_ATTENTION=mma selects the mma.sync attention kernel (A/B checks)
     // weights
     float* arena32 = nullptr;
@@ -171,6 +185,8 @@ int init_context(b200_embed* h, Context& c) {
 void destroy_context(Context& c) {
     if (!c.created) return;
     cudaStreamSynchronize(c.stream);
+    for (GraphEntry& g : c.graphs)
+        if (g.exec) cudaGraphExecDestroy(g.exec);
     c.ws16.release();
     c.ws32.release();
     for (void* p : {static_cast<void*>(c.d_ids), static_cast<void*>(c.d_mask), static_cast<void*>(c.d_tt),
@@ -210,6 +226,7 @@ void release(b200_embed* h, Context* c) {
 int ensure_workspace(b200_embed* h, Workspace& w, size_t rows, size_t elt, cudaStream_t s) {
     rows = round_up(rows, 128);
     if (rows <= w.cap) return B200_EMBED_OK;
+    g_alloc_gen.fetch_add(1);
     w.release();
     const size_t H = h->H, I = h->I;
     CU_TRY(cudaMalloc(&w.x, rows * H * elt));
@@ -238,6 +255,7 @@ int ensure_workspace(b200_embed* h, Workspace& w, size_t rows, size_t elt, cudaS
 template <typename T>
 int ensure_buf(T** p, size_t* cap, size_t n) {
     if (n <= *cap) return B200_EMBED_OK;
+    g_alloc_gen.fetch_add(1);
     if (*p) cudaFree(*p);
     *p = nullptr;
     *cap = 0;
@@ -249,6 +267,7 @@ int ensure_buf(T** p, size_t* cap, size_t n) {
 
 int ensure_input_bufs(Context& c, size_t n) {
     if (n <= c.in_cap) return B200_EMBED_OK;
+    g_alloc_gen.fetch_add(1);
     for (uint32_t** p : {&c.d_ids, &c.d_mask, &c.d_tt}) {
         if (*p) cudaFree(*p);
         *p = nullptr;
@@ -264,6 +283,7 @@ int ensure_input_bufs(Context& c, size_t n) {
 
 int ensure_batch_bufs(Context& c, size_t nb) {
     if (nb + 2 <= c.b_cap) return B200_EMBED_OK;
+    g_alloc_gen.fetch_add(1);
     for (int** p : {&c.d_lens, &c.d_cu, &c.d_tile_first, &c.d_seg_off, &c.d_n_tiles}) {
         if (*p) cudaFree(*p);
         *p = nullptr;
@@ -292,6 +312,7 @@ cudaEvent_t next_event(Context& c) {
 template <typename F>
 cudaError_t timed(b200_embed* h, Context& c, cudaStream_t s, int kind, int nlaunch, F&& f) {
     h->launches.fetch_add(nlaunch, std::memory_order_relaxed);
+    t_launches += nlaunch;
     if (!h->profile.load(std::memory_order_relaxed)) return f();
     cudaEvent_t e0 = next_event(c), e1 = next_event(c);
     if (!e0 || !e1) return f();
@@ -463,6 +484,59 @@ int run_chunk(b200_embed* h, Context& c, cudaStream_t s, const Job& j) {
     return B200_EMBED_OK;
 }
 
+void drop_graphs(Context& c) {
+    for (GraphEntry& g : c.graphs)
+        if (g.exec) cudaGraphExecDestroy(g.exec);
+    c.graphs.clear();
+}
+
+// run_chunk, replayed from a CUDA graph when the call is small enough to be launch-bound and has been seen before.
+int run_chunk_cached(b200_embed* h, Context& c, cudaStream_t s, const Job& j) {
+    constexpr int GRAPH_MAX_TOKENS = 16384;
+    constexpr size_t GRAPH_MAX_ENTRIES = 64;
+    if (!h->use_graphs || h->profile.load(std::memory_order_relaxed) || j.d_cu != nullptr || j.tokens_upper > GRAPH_MAX_TOKENS)
+        return run_chunk(h, c, s, j);
+    if (c.graph_gen != g_alloc_gen.load()) {
+        drop_graphs(c);
+        c.graph_gen = g_alloc_gen.load();
+    }
+    const uint64_t key = static_cast<uint64_t>(j.batch) | (static_cast<uint64_t>(j.seq_len) << 24) | (static_cast<uint64_t>(j.flags) << 48);
+    GraphEntry* e = nullptr;
+    for (GraphEntry& g : c.graphs)
+        if (g.key == key) { e = &g; break; }
+    if (!e) {  // first sight: run the plain way (this also makes every allocation and one-time attribute call)
+        if (c.graphs.size() >= GRAPH_MAX_ENTRIES) drop_graphs(c);
+        const int rc = run_chunk(h, c, s, j);
+        if (!rc && c.graph_gen == g_alloc_gen.load()) c.graphs.push_back(GraphEntry{key, nullptr, 0});
+        else c.graph_gen = 0;  // something was reallocated: start over next time
+        return rc;
+    }
+    if (!e->exec) {
+        const int64_t before = t_launches;
+        if (cudaStreamBeginCapture(s, cudaStreamCaptureModeRelaxed) != cudaSuccess) { cudaGetLastError(); return run_chunk(h, c, s, j); }
+        const int rc = run_chunk(h, c, s, j);
+        cudaGraph_t graph = nullptr;
+        const cudaError_t ce = cudaStreamEndCapture(s, &graph);
+        const int captured = static_cast<int>(t_launches - before);
+        h->launches.fetch_sub(captured);  // nothing has run yet
+        cudaGraphExec_t exec = nullptr;
+        const bool ok = !rc && ce == cudaSuccess && graph && c.graph_gen == g_alloc_gen.load() &&
+                        cudaGraphInstantiate(&exec, graph, 0) == cudaSuccess;
+        if (graph) cudaGraphDestroy(graph);
+        if (!ok) {  // fall back to plain launches for good
+            cudaGetLastError();
+            if (exec) cudaGraphExecDestroy(exec);
+            h->use_graphs = false;
+            return rc ? rc : run_chunk(h, c, s, j);
+        }
+        e->exec = exec;
+        e->launches = captured;
+    }
+    h->launches.fetch_add(e->launches, std::memory_order_relaxed);
+    CU_TRY(cudaGraphLaunch(e->exec, s));
+    return B200_EMBED_OK;
+}
+
 int check_status(Context& c) {
     const int st = *c.h_status;
     if (st & 1) return fail(B200_EMBED_ERR_INVALID_ARG, "attention_mask is not a right-padded 0/1 prefix");
@@ -502,7 +576,7 @@ int enqueue_padded_host(b200_embed* h, Context& c, const uint32_t* ids, const ui
         CU_TRY(cudaMemcpyAsync(c.d_mask, mask + off, n * 4, cudaMemcpyHostToDevice, s));
         CU_TRY(cudaMemcpyAsync(c.d_tt, tt + off, n * 4, cudaMemcpyHostToDevice, s));
         Job j{c.d_ids, c.d_mask, c.d_tt, nullptr, nb, seq_len, static_cast<int>(n), flags, c.d_out};
-        rc = run_chunk(h, c, s, j);
+        rc = run_chunk_cached(h, c, s, j);
         if (rc) return rc;
         CU_TRY(cudaMemcpyAsync(out + static_cast<size_t>(b0) * h->H, c.d_out, static_cast<size_t>(nb) * h->H * 4,
                                cudaMemcpyDeviceToHost, s));
@@ -586,6 +660,7 @@ int32_t b200_embed_create(const b200_embed_config* cfg, const char* path, uint64
         h->force_qkv_attn = std::string(v) == "1";
     }
     if (const char* v = getenv("B200_EMBED_GEMM_PAIR")) h->gemm_pair = std::string(v) != "0";
+    if (const char* v = getenv("B200_EMBED_GRAPHS")) h->use_graphs = std::string(v) != "0";
     h->bn_qkv = b200::gemm_tc_pick_block_n(3 * H, b200::EPI_BIAS);
     h->bn_ffn1 = b200::gemm_tc_pick_block_n(I, h->act_epi);
     h->bn_h = b200::gemm_tc_pick_block_n(H, b200::EPI_GELU_ERF);  // 256 or 128 (fp32-out instantiations)
