@@ -329,3 +329,36 @@ def test_embedding_generator_end_to_end_text(pkg, built, tmp_path):
             gen.process_raw_text(" \n\t ", "doc7")
     finally:
         gen.close()
+
+
+def test_graph_replay_is_bit_identical_and_survives_reallocation(pkg, built, monkeypatch):
+    """Small host-buffer calls replay a CUDA graph from the third call of a shape on. The replayed call, the captured
+    call and the plainly launched call give the same bits as a handle with graphs off; a larger call in between
+    (which reallocates the context's buffers and drops the cache) does not break the small shape; the launch counter
+    counts replayed kernels."""
+    shape = pkg.weights.MINILM_L6
+    small = pkg.synth.padded_batch(shape.vocab_size, [5, 17, 64, 33], 64, seed=1)
+    other = pkg.synth.padded_batch(shape.vocab_size, [9, 2, 30], 32, seed=2)
+    big = pkg.synth.padded_batch(shape.vocab_size, [128] * 96, 128, seed=3)
+    monkeypatch.setenv("B200_EMBED_GRAPHS", "0")
+    with pkg.Embedder.random_init(shape, seed=11) as plain:
+        want_small, want_other, want_big = plain.forward(*small), plain.forward(*other), plain.forward(*big)
+        n0 = plain.kernel_launches()
+        plain.forward(*small)
+        per_call = plain.kernel_launches() - n0
+    monkeypatch.delenv("B200_EMBED_GRAPHS")
+    with pkg.Embedder.random_init(shape, seed=11) as emb:
+        for _ in range(4):  # plain, capture + launch, replay, replay
+            assert np.array_equal(emb.forward(*small), want_small)
+            assert np.array_equal(emb.forward(*other), want_other)  # two shapes interleaved
+        n0 = emb.kernel_launches()
+        emb.forward(*small)
+        assert emb.kernel_launches() - n0 == per_call
+        assert np.array_equal(emb.forward(*big), want_big)  # grows the workspace: graphs dropped
+        for _ in range(3):
+            assert np.array_equal(emb.forward(*small), want_small)
+        bad = [a.copy() for a in small]
+        bad[0][1, 2] = shape.vocab_size + 5  # input errors are still reported from a replayed call
+        with pytest.raises(pkg.abi.B200EmbedError):
+            emb.forward(*bad)
+        assert np.array_equal(emb.forward(*small), want_small)
