@@ -67,3 +67,41 @@ def imbalance(plan, lengths, shape=None) -> float:
     f = (lambda s: shape.flops_per_sentence(int(s))) if shape is not None else float
     loads = [sum(sum(f(s) for s in lengths[b]) for b in rank) for rank in plan]
     return max(loads) / (sum(loads) / len(loads))
+
+
+# ---- f4 across GPUs: every rank holds a slice of the vectors in its own b200_index --------------------------------
+def merge_topk(ids_parts, scores_parts, k: int):
+    """Merges per-shard results of the same queries: ids_parts / scores_parts are lists of [q, k_r] arrays holding GLOBAL
+    ids (-1 = padding) and scores, best first. -> ids [q, k], scores [q, k], best first, equal scores by id, padded
+    with (-1, -inf): the list a single index over all the vectors returns."""
+    ids = np.concatenate([np.asarray(a, dtype=np.int64) for a in ids_parts], axis=1)
+    scores = np.concatenate([np.asarray(a, dtype=np.float32) for a in scores_parts], axis=1)
+    q = ids.shape[0]
+    out_ids = np.full((q, k), -1, dtype=np.int64)
+    out_sc = np.full((q, k), -np.inf, dtype=np.float32)
+    for i in range(q):
+        real = np.nonzero(ids[i] >= 0)[0]
+        order = real[np.lexsort((ids[i, real], -scores[i, real].astype(np.float64)))][:k]
+        out_ids[i, :len(order)] = ids[i, order]
+        out_sc[i, :len(order)] = scores[i, order]
+    return out_ids, out_sc
+
+
+def search_sharded(local_search, id_offset: int, queries, k: int, group=None):
+    """One search over an index sharded by rows across the ranks of `group` (torch.distributed). `local_search(queries,
+    k) -> (ids, scores)` is this rank's b200_index search (local row ids); `id_offset` the global id of its row 0. The
+    only exchange is an all_gather of the [q, k] lists (8 + 4 bytes per entry): NCCL between GPUs, gloo in the CPU tests.
+    Every rank returns the merged result."""
+    import torch
+    import torch.distributed as dist
+
+    ids, scores = local_search(queries, k)
+    ids = np.where(ids >= 0, ids + id_offset, -1).astype(np.int64)
+    world = dist.get_world_size(group)
+    dev = "cuda" if dist.get_backend(group) == "nccl" else "cpu"
+    t_ids, t_sc = torch.from_numpy(ids).to(dev), torch.from_numpy(np.ascontiguousarray(scores, dtype=np.float32)).to(dev)
+    g_ids = [torch.empty_like(t_ids) for _ in range(world)]
+    g_sc = [torch.empty_like(t_sc) for _ in range(world)]
+    dist.all_gather(g_ids, t_ids, group=group)
+    dist.all_gather(g_sc, t_sc, group=group)
+    return merge_topk([t.cpu().numpy() for t in g_ids], [t.cpu().numpy() for t in g_sc], k)

@@ -70,3 +70,53 @@ def test_plan_covers_every_sentence_once_and_respects_budget(pkg):
     assert pkg.sharding.imbalance(plan, lengths, pkg.weights.MINILM_L6) < 1.05
     with pytest.raises(ValueError):
         pkg.sharding.scatter_back(3, 4, [(np.array([0, 1]), np.zeros((2, 4), np.float32))])
+
+
+def _search_worker(rank, world, port, q):
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    from __graft_entry__ import load_package
+    from oracle import search_oracle
+    pkg = load_package()
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    rng = np.random.default_rng(5)
+    vectors = rng.standard_normal((1001, 64)).astype(np.float32)
+    vectors[700:720] = vectors[10:30]  # duplicates across the shards: ties must come out ordered by global id
+    queries = rng.standard_normal((3, 64)).astype(np.float32)
+    queries[2] = vectors[15]
+    bounds = [0, 333, 1001][: world + 1] if world == 2 else np.linspace(0, 1001, world + 1).astype(int).tolist()
+    lo, hi = bounds[rank], bounds[rank + 1]
+
+    def local_search(qs, k):  # stand-in for this rank's b200_index (needs a GPU): the oracle on the rank's rows
+        ids, sc = search_oracle.search(vectors[lo:hi], qs, k)
+        return ids, sc.astype(np.float32)
+
+    ids, sc = pkg.sharding.search_sharded(local_search, lo, queries, 40)
+    want_ids, want_sc = search_oracle.search(vectors, queries, 40)
+    q.put((rank, np.array_equal(ids, want_ids), float(np.abs(sc - want_sc).max()), int(ids[2, 0]), int(ids[2, 1])))
+    dist.destroy_process_group()
+
+
+def test_two_rank_sharded_search_merges_to_the_global_answer():
+    """f4 across GPUs: rows sharded over 2 ranks, each searches its shard, one all_gather of the k-lists, merge. The
+    result equals the single-index answer on every rank, duplicates across shards ordered by global id."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_search_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(30)
+    for rank, same, err, first, second in res:
+        assert same and err <= 1e-6
+        assert (first, second) == (15, 705)  # the query's own row, then its duplicate in the other shard
+
+
+def test_merge_topk_padding_and_order(pkg):
+    ids_a = np.array([[4, 2, -1]]); sc_a = np.array([[0.9, 0.5, -np.inf]], np.float32)
+    ids_b = np.array([[7, 9, 8]]); sc_b = np.array([[0.9, 0.5, 0.1]], np.float32)
+    ids, sc = pkg.sharding.merge_topk([ids_a, ids_b], [sc_a, sc_b], 6)
+    assert ids[0].tolist() == [4, 7, 2, 9, 8, -1] and np.isneginf(sc[0, 5]) and sc[0, :5].tolist() == pytest.approx([0.9, 0.9, 0.5, 0.5, 0.1])
