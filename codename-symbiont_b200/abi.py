@@ -17,7 +17,7 @@ import numpy as np
 from . import weights as W
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libb200_embed.so")
+LIB_PATH = os.environ.get("B200_EMBED_LIB") or os.path.join(HERE, "libb200_embed.so")  # the override is for A/B timing of two builds
 HEADER_PATH = os.path.join(HERE, "..", "include", "b200_embed.h")
 
 NOALLOC_MAX_ELEMS = 1 << 20  # B200_OP_NOALLOC_MAX_ELEMS

@@ -57,17 +57,20 @@ struct FfnCfg {
     static constexpr int S2N = R2 * NB2;              // W2 ring stages
     static_assert(S1N <= 8 && S2N <= 8, "barrier slots");
     static constexpr int OFF_A = 0;
-    static constexpr int OFF_H = KB1 * BLK16;         // h chunk: 2 k-blocks [128 x 64]
-    static constexpr int OFF_W1 = OFF_H + 2 * BLK16;
-    static constexpr int OFF_W2 = OFF_W1 + S1N * W1_BLK;
+    static constexpr int OFF_W1 = KB1 * BLK16;
+    static constexpr int OFF_H = OFF_W1 + S1N * W1_BLK;  // h chunk: 2 k-blocks [128 x 64]
+    static constexpr int OFF_W2 = OFF_H + 2 * BLK16;
     static constexpr int OFF_AUX = OFF_W2 + S2N * W2_BLK;
     static constexpr int AUX = 1024 + 2 * BM * 8;     // barriers + tmem slot, LayerNorm partial statistics
     static constexpr int BYTES = OFF_AUX + AUX;
-    static constexpr int SCRATCH = OFF_AUX - OFF_H;   // h + rings: per-warp scratch of the final epilogue
+    // h + the W2 ring: per-warp scratch of the final epilogue. The W1 ring is NOT part of it, so that the first GEMM1 of
+    // the next tile is loaded and issued while the epilogue warps are still normalising this one.
+    static constexpr int SCRATCH = OFF_AUX - OFF_H;
+    static constexpr int LO_SLOTS = H == 128 ? 3 : 4;  // residual-lo ring of a warp; pass 2 reuses it as output staging
     static constexpr int HALF = H / 2;                // output columns per epilogue warp
     static constexpr int NCH = HALF / CHUNK;
     static_assert(H % 128 == 0 && H <= 384, "fused FFN needs the OUT accumulator (H columns) next to S1 (128) in TMEM");
-    static_assert(SCRATCH >= FF_EPI_WARPS * 6 * CHUNK_BF16 + 3 * H * 4, "final epilogue scratch does not fit");
+    static_assert(SCRATCH >= FF_EPI_WARPS * LO_SLOTS * CHUNK_BF16 + 3 * H * 4, "final epilogue scratch does not fit");
     static_assert(BYTES <= SMEM_LIMIT, "shared memory budget exceeded");
     static_assert(W1_BLK % 1024 == 0 && W2_BLK % 1024 == 0 && (UN2 / 2) % 8 == 0, "swizzle atoms must stay 1024-byte aligned");
 };
@@ -170,8 +173,6 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 }
             }
             __syncwarp();
-            // the rings double as scratch of the previous tile's final epilogue
-            mbar_wait(bar_epi_done, (tile_it & 1) ^ 1);
             for (int step = 0; step <= NC; ++step) {
                 if (step < NC) {
                     const uint32_t s0 = (g1_it % R1) * KB1, ph = ((g1_it / R1) & 1) ^ 1;
@@ -189,6 +190,8 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 }
                 if (step >= 1) {
                     const int ic = step - 1;
+                    // the W2 ring (and h) double as scratch of the previous tile's final epilogue
+                    if (ic == 0) mbar_wait(bar_epi_done, (tile_it & 1) ^ 1);
                     const uint32_t s0 = (g2_it % R2) * NB2, ph = ((g2_it / R2) & 1) ^ 1;
 #pragma unroll
                     for (int blk = 0; blk < NB2; ++blk) {
@@ -277,17 +280,17 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         const int quad = warp & 3, half = ew >> 2;
         const int row_in_tile = quad * 32 + lane;
         const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
-        // final-epilogue scratch of this warp inside the (then idle) h / ring region: 4-slot residual-lo ring and two
-        // output staging buffers
-        const uint32_t my_smem = smem_h + ew * (6 * CHUNK_BF16);
-        const uint32_t out_buf = my_smem + 4 * CHUNK_BF16;
-        const uint32_t const_s = smem_h + FF_EPI_WARPS * (6 * CHUNK_BF16);  // b2 | gamma | beta, fp32 (final epilogue)
+        // final-epilogue scratch of this warp inside the (then idle) h / W2-ring region: a residual-lo ring for the first
+        // pass, reused as (hi, lo) output staging by the second
+        constexpr int LO_SLOTS = C::LO_SLOTS;
+        const uint32_t my_smem = smem_h + ew * (LO_SLOTS * CHUNK_BF16);
+        const uint32_t const_s = smem_h + FF_EPI_WARPS * (LO_SLOTS * CHUNK_BF16);  // b2 | gamma | beta, fp32 (final epilogue)
         uint32_t chunk_it = 0, tile_it = 0, ld_issued = 0, ld_used = 0;
 
         // residual: the hi half is the a tile itself (still in shared memory); the lo half comes through a 4-slot ring
         auto issue_lo = [&](int tile, int c) {
             if (lane == 0) {
-                const uint32_t s = ld_issued & 3;
+                const uint32_t s = ld_issued % LO_SLOTS;
                 const uint32_t bar = bar_res + 8 * (4 * ew + s);
                 mbar_arrive_expect_tx(bar, CHUNK_BF16);
                 tma_load_2d(my_smem + s * CHUNK_BF16, &tmap_r_lo, half * HALF + c * CHUNK, tile * BM + quad * 32, bar);
@@ -344,7 +347,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             tc_fence_after_sync();
             if (p.has_lo) {
 #pragma unroll
-                for (int c = 0; c < (NCH < 4 ? NCH : 4); ++c) issue_lo(t, c);
+                for (int c = 0; c < (NCH < LO_SLOTS ? NCH : LO_SLOTS); ++c) issue_lo(t, c);
             }
             // b2, gamma, beta -> scratch behind the per-warp areas, read back with broadcast LDS in the loops
             for (int i = threadIdx.x - FF_EPI_WARP0 * 32; i < 3 * H; i += FF_EPI_THREADS) {
@@ -364,14 +367,14 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     uint32_t hi_addr[4], lo_addr[4];
                     // a tile: k-block col0 / 64, 128-byte rows, SWIZZLE_128B; lo slot: 64-byte rows, SWIZZLE_64B
                     const uint32_t arow = smem_a + (col0 / BK) * BLK16 + row_in_tile * 128;
-                    const uint32_t lrow = my_smem + (ld_used & 3) * CHUNK_BF16 + lane * 64;
+                    const uint32_t lrow = my_smem + (ld_used % LO_SLOTS) * CHUNK_BF16 + lane * 64;
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
                         hi_addr[q] = arow + ((((col0 % BK) / 8 + q) ^ (row_in_tile & 7)) << 4);
                         lo_addr[q] = lrow + ((q ^ ((lane >> 1) & 3)) << 4);
                     }
                     if (p.has_lo) {
-                        mbar_wait(bar_res + 8 * (4 * ew + (ld_used & 3)), (ld_used >> 2) & 1);
+                        mbar_wait(bar_res + 8 * (4 * ew + (ld_used % LO_SLOTS)), (ld_used / LO_SLOTS) & 1);
                         ++ld_used;
                     }
                     tmem_ld_wait();
@@ -379,7 +382,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     ln_accumulate_chunk(v[c & 1], const_s + col0 * 4, hi_addr, lo_addr, p.has_lo != 0, sum2, sq2);
                     tmem_st_32x32(taddr + c * CHUNK, v[c & 1]);
                     __syncwarp();
-                    if (p.has_lo && c + 4 < NCH) issue_lo(t, c + 4);
+                    if (p.has_lo && c + LO_SLOTS < NCH) issue_lo(t, c + LO_SLOTS);
                 }
             }
             if (lane == 0) mbar_arrive(bar_a_empty);  // this warp's residual rows have been read from the a tile
@@ -413,7 +416,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     const int col0 = half * HALF + c * CHUNK;
                     uint32_t hi[16], lo[16];
                     ln_normalize_chunk(x[c & 1], mean, rstd, const_s + (H + col0) * 4, const_s + (2 * H + col0) * 4, hi, lo);
-                    const uint32_t buf_hi = out_buf, buf_lo = out_buf + CHUNK_BF16;
+                    const uint32_t buf_hi = my_smem, buf_lo = my_smem + CHUNK_BF16;
                     if (lane == 0) tma_store_wait_read<0>();
                     __syncwarp();
                     stage_words_bf16(buf_hi, lane, hi);
