@@ -42,6 +42,170 @@ inline int shortest_digits(float v, char* digits, int* kk) {
     return n;
 }
 
+// The same digits without the library call: Schubfach (R. Giulietti, "The Schubfach way to render doubles", 2020) for
+// binary32. v = c * 2^q; k = floor(log10(2^q)) picks the decade in which the rounding interval of v is at least one unit
+// wide, the interval ends and v are scaled by 10^-k with one 64 x 32 bit multiplication each against a 64-bit upper
+// approximation g of the power of ten (kPow10_64, exact values from integer arithmetic), rounded to odd so that
+// comparisons stay exact; the answer is the shortest decimal in the interval, the closest to v among equals, ties to
+// even. Checked against the library for every finite float (scripts/probes/f32_digits_check.cpp: all 2^31 - 2^23
+// positive values). About 3x faster than std::to_chars + re-layout here.
+constexpr int kPow10Min = -31, kPow10Max = 45;
+const uint64_t kPow10_64[kPow10Max - kPow10Min + 1] = {
+    0x81CEB32C4B43FCF5ULL,
+    0xA2425FF75E14FC32ULL,
+    0xCAD2F7F5359A3B3FULL,
+    0xFD87B5F28300CA0EULL,
+    0x9E74D1B791E07E49ULL,
+    0xC612062576589DDBULL,
+    0xF79687AED3EEC552ULL,
+    0x9ABE14CD44753B53ULL,
+    0xC16D9A0095928A28ULL,
+    0xF1C90080BAF72CB2ULL,
+    0x971DA05074DA7BEFULL,
+    0xBCE5086492111AEBULL,
+    0xEC1E4A7DB69561A6ULL,
+    0x9392EE8E921D5D08ULL,
+    0xB877AA3236A4B44AULL,
+    0xE69594BEC44DE15CULL,
+    0x901D7CF73AB0ACDAULL,
+    0xB424DC35095CD810ULL,
+    0xE12E13424BB40E14ULL,
+    0x8CBCCC096F5088CCULL,
+    0xAFEBFF0BCB24AAFFULL,
+    0xDBE6FECEBDEDD5BFULL,
+    0x89705F4136B4A598ULL,
+    0xABCC77118461CEFDULL,
+    0xD6BF94D5E57A42BDULL,
+    0x8637BD05AF6C69B6ULL,
+    0xA7C5AC471B478424ULL,
+    0xD1B71758E219652CULL,
+    0x83126E978D4FDF3CULL,
+    0xA3D70A3D70A3D70BULL,
+    0xCCCCCCCCCCCCCCCDULL,
+    0x8000000000000000ULL,
+    0xA000000000000000ULL,
+    0xC800000000000000ULL,
+    0xFA00000000000000ULL,
+    0x9C40000000000000ULL,
+    0xC350000000000000ULL,
+    0xF424000000000000ULL,
+    0x9896800000000000ULL,
+    0xBEBC200000000000ULL,
+    0xEE6B280000000000ULL,
+    0x9502F90000000000ULL,
+    0xBA43B74000000000ULL,
+    0xE8D4A51000000000ULL,
+    0x9184E72A00000000ULL,
+    0xB5E620F480000000ULL,
+    0xE35FA931A0000000ULL,
+    0x8E1BC9BF04000000ULL,
+    0xB1A2BC2EC5000000ULL,
+    0xDE0B6B3A76400000ULL,
+    0x8AC7230489E80000ULL,
+    0xAD78EBC5AC620001ULL,
+    0xD8D726B7177A8001ULL,
+    0x878678326EAC9001ULL,
+    0xA968163F0A57B401ULL,
+    0xD3C21BCECCEDA101ULL,
+    0x84595161401484A1ULL,
+    0xA56FA5B99019A5C9ULL,
+    0xCECB8F27F4200F3BULL,
+    0x813F3978F8940985ULL,
+    0xA18F07D736B90BE6ULL,
+    0xC9F2C9CD04674EDFULL,
+    0xFC6F7C4045812297ULL,
+    0x9DC5ADA82B70B59EULL,
+    0xC5371912364CE306ULL,
+    0xF684DF56C3E01BC7ULL,
+    0x9A130B963A6C115DULL,
+    0xC097CE7BC90715B4ULL,
+    0xF0BDC21ABB48DB21ULL,
+    0x96769950B50D88F5ULL,
+    0xBC143FA4E250EB32ULL,
+    0xEB194F8E1AE525FEULL,
+    0x92EFD1B8D0CF37BFULL,
+    0xB7ABC627050305AEULL,
+    0xE596B7B0C643C71AULL,
+    0x8F7E32CE7BEA5C70ULL,
+    0xB35DBF821AE4F38CULL
+};
+inline int floor_log10_pow2(int e) { return (e * 1262611) >> 22; }
+inline int floor_log10_three_quarters_pow2(int e) { return (e * 1262611 - 524031) >> 22; }
+inline int floor_log2_pow10(int e) { return (e * 1741647) >> 19; }
+inline uint32_t round_to_odd(uint64_t g, uint32_t cp) {
+    const unsigned __int128 p = static_cast<unsigned __int128>(g) * cp;
+    const uint32_t y1 = static_cast<uint32_t>(p >> 64);
+    const uint32_t y0 = static_cast<uint32_t>(static_cast<uint64_t>(p) >> 32);
+    return y1 | (y0 > 1 ? 1u : 0u);
+}
+
+// -> decimal significand (<= 9 digits, may end in zeros) and exponent: v = sig * 10^exp. v finite, > 0.
+inline uint32_t schubfach_f32(float v, int* exp10) {
+    uint32_t bits;
+    std::memcpy(&bits, &v, 4);
+    const uint32_t frac = bits & 0x7FFFFFu, E = (bits >> 23) & 0xFFu;
+    uint32_t c;
+    int q;
+    if (E != 0) {
+        c = frac | 0x800000u;
+        q = static_cast<int>(E) - 150;
+        if (0 <= -q && -q < 24 && (c & ((1u << -q) - 1)) == 0) {  // a small integer
+            *exp10 = 0;
+            return c >> -q;
+        }
+    } else {
+        c = frac;
+        q = -149;
+    }
+    const bool even = (c & 1) == 0;
+    const bool lower_closer = frac == 0 && E > 1;
+    const uint32_t cbl = 4 * c - 2 + (lower_closer ? 1 : 0), cb = 4 * c, cbr = 4 * c + 2;
+    const int k = lower_closer ? floor_log10_three_quarters_pow2(q) : floor_log10_pow2(q);
+    const int h = q + floor_log2_pow10(-k) + 1;
+    const uint64_t g = kPow10_64[-k - kPow10Min];
+    const uint32_t vbl = round_to_odd(g, cbl << h), vb = round_to_odd(g, cb << h), vbr = round_to_odd(g, cbr << h);
+    const uint32_t lower = vbl + (even ? 0 : 1), upper = vbr - (even ? 0 : 1);
+    const uint32_t s = vb / 4;
+    if (s >= 10) {  // a shorter candidate one decade up?
+        const uint32_t sp = s / 10;
+        const bool up_inside = lower <= 40 * sp, wp_inside = 40 * sp + 40 <= upper;
+        if (up_inside != wp_inside) {
+            *exp10 = k + 1;
+            return sp + (wp_inside ? 1 : 0);
+        }
+    }
+    const bool u_inside = lower <= 4 * s, w_inside = 4 * s + 4 <= upper;
+    *exp10 = k;
+    if (u_inside != w_inside) return s + (w_inside ? 1 : 0);
+    const uint32_t mid = 4 * s + 2;
+    const bool round_up = vb > mid || (vb == mid && (s & 1));
+    return s + (round_up ? 1 : 0);
+}
+
+// digits of a finite non-zero float (see shortest_digits): n <= 9, value = 0.d1..dn x 10^kk. `digits` must hold 24 bytes.
+inline int shortest_digits_fast(float v, char* digits, int* kk) {
+    static const char kPairs[] =
+        "00010203040506070809101112131415161718192021222324252627282930313233343536373839404142434445464748495051525354555657585960616263646566676869707172737475767778798081828384858687888990919293949596979899";
+    int e10;
+    const uint32_t sig = schubfach_f32(v, &e10);
+    // nine digits, zero-padded on the left, two at a time
+    char t[24];
+    const uint32_t top = sig / 100000000u, rest = sig - top * 100000000u;
+    const uint32_t hi = rest / 10000u, lo = rest - hi * 10000u;
+    t[0] = static_cast<char>('0' + top);
+    std::memcpy(t + 1, kPairs + 2 * (hi / 100u), 2);
+    std::memcpy(t + 3, kPairs + 2 * (hi % 100u), 2);
+    std::memcpy(t + 5, kPairs + 2 * (lo / 100u), 2);
+    std::memcpy(t + 7, kPairs + 2 * (lo % 100u), 2);
+    int n = sig >= 100000000u ? 9 : sig >= 10000000u ? 8 : sig >= 1000000u ? 7 : sig >= 100000u ? 6 : sig >= 10000u ? 5
+            : sig >= 1000u ? 4 : sig >= 100u ? 3 : sig >= 10u ? 2 : 1;
+    std::memcpy(digits, t + 9 - n, 9);
+    e10 += n;  // value = 0.d1..dn x 10^(n + e10)
+    while (n > 1 && digits[n - 1] == '0') --n;  // small integers and carried roundings end in zeros
+    *kk = e10;
+    return n;
+}
+
 // ryu "pretty" layout for f32 (format32): returns characters written (at most 16). Copies are fixed-size so that no
 // memcpy call is made per float: `out` must have 32 writable bytes; what lies beyond the returned length is scratch.
 inline int format_f32(float v, char* out) {
@@ -51,7 +215,7 @@ inline int format_f32(float v, char* out) {
     if (v == 0.0f) { std::memcpy(out + i, "0.0", 3); return i + 3; }
     char d[32];
     int kk;
-    const int n = shortest_digits(v, d, &kk);  // n <= 9
+    const int n = shortest_digits_fast(v, d, &kk);  // n <= 9
     if (-6 < kk && kk <= 0) {  // 1234e-6 -> 0.001234 : where embedding components live, so tested first
         std::memcpy(out + i, "0.000000", 8);
         i += 2 - kk;
