@@ -209,11 +209,15 @@ def split_sentences(raw_text: str):
     raw = raw_text.encode("utf-8")
     cleaned = np.empty(max(len(raw), 1), dtype=np.uint8)
     clen = C.c_int64(0)
-    cap = raw.count(b".") + raw.count(b"?") + raw.count(b"!") + 1
-    begin = np.zeros(cap, dtype=np.int64)
-    end = np.zeros(cap, dtype=np.int64)
-    n = lib.b200_ingest_split_sentences(raw, len(raw), cleaned.ctypes.data, len(cleaned), C.byref(clen), begin.ctypes.data,
-                                        end.ctypes.data, cap)
+    cap = len(raw) // 16 + 16  # a guess; the call returns the full count, so a second call fixes an underestimate
+    while True:
+        begin = np.empty(cap, dtype=np.int64)
+        end = np.empty(cap, dtype=np.int64)
+        n = lib.b200_ingest_split_sentences(raw, len(raw), cleaned.ctypes.data, len(cleaned), C.byref(clen), begin.ctypes.data,
+                                            end.ctypes.data, cap)
+        if n <= cap:
+            break
+        cap = int(n)
     _check_ingest(n)
     if n == 0:
         raise ValueError("Cleaned text is empty")

@@ -643,33 +643,19 @@ void b200_ingest_destroy(b200_ingest* t) { delete t; }
 int32_t b200_ingest_vocab_size(const b200_ingest* t) { return t ? t->vocab_size : -1; }
 int32_t b200_ingest_pad_id(const b200_ingest* t) { return t ? t->pad_id : -1; }
 
-int64_t b200_ingest_split_sentences(const char* raw_text, int64_t len, char* cleaned, int64_t cleaned_cap,
-                                    int64_t* cleaned_len, int64_t* begin, int64_t* end, int64_t max_sentences) {
-    if (!raw_text || len < 0 || !cleaned || cleaned_cap < len || !cleaned_len || max_sentences < 0 ||
-        (max_sentences > 0 && (!begin || !end)))
-        return fail(B200_EMBED_ERR_INVALID_ARG, "split_sentences: bad pointer or capacity (cleaned_cap must be >= len)");
-    // split_whitespace().collect().join(" ") and the cut after '.', '?', '!' in one pass over the text
-    const unsigned char* p = reinterpret_cast<const unsigned char*>(raw_text);
-    const unsigned char* e = p + len;
-    int64_t o = 0, n = 0, start = 0;
+// One chunk of the raw text [p, e): words joined by single spaces into `out` (never a leading or trailing space) and the
+// offsets just after every '.', '?' or '!' in `cuts`. Chunks are cut at ASCII whitespace, so their outputs join with
+// exactly one space and the cut offsets only need the chunk's base added.
+static void clean_chunk(const unsigned char* p, const unsigned char* e, char* out, int64_t* out_len, std::vector<int64_t>* cuts) {
+    int64_t o = 0;
     bool pending_space = false;
-    auto push = [&](int64_t b, int64_t en) {  // [b, en) trimmed: only single spaces can be left at the ends
-        while (b < en && cleaned[b] == ' ') ++b;
-        while (en > b && cleaned[en - 1] == ' ') --en;
-        if (b == en) return;
-        if (n < max_sentences) { begin[n] = b; end[n] = en; }
-        ++n;
-    };
     while (p < e) {
         const unsigned char c0 = *p;
         if (c0 > ' ' && c0 < 0x80) {  // printable ASCII: the common case
-            if (pending_space) { cleaned[o++] = ' '; pending_space = false; }
-            cleaned[o++] = static_cast<char>(c0);
+            if (pending_space) { out[o++] = ' '; pending_space = false; }
+            out[o++] = static_cast<char>(c0);
             ++p;
-            if (c0 == '.' || c0 == '?' || c0 == '!') {
-                push(start, o);
-                start = o;
-            }
+            if (c0 == '.' || c0 == '?' || c0 == '!') cuts->push_back(o);
             continue;
         }
         int l = 1;
@@ -677,14 +663,89 @@ int64_t b200_ingest_split_sentences(const char* raw_text, int64_t len, char* cle
         if (rust_is_whitespace(c)) {
             pending_space = o > 0;
         } else {
-            if (pending_space) { cleaned[o++] = ' '; pending_space = false; }
-            std::memcpy(cleaned + o, p, static_cast<size_t>(l));
+            if (pending_space) { out[o++] = ' '; pending_space = false; }
+            std::memcpy(out + o, p, static_cast<size_t>(l));
             o += l;
         }
         p += l;
     }
+    *out_len = o;
+}
+
+int64_t b200_ingest_split_sentences(const char* raw_text, int64_t len, char* cleaned, int64_t cleaned_cap,
+                                    int64_t* cleaned_len, int64_t* begin, int64_t* end, int64_t max_sentences) {
+    if (!raw_text || len < 0 || !cleaned || cleaned_cap < len || !cleaned_len || max_sentences < 0 ||
+        (max_sentences > 0 && (!begin || !end)))
+        return fail(B200_EMBED_ERR_INVALID_ARG, "split_sentences: bad pointer or capacity (cleaned_cap must be >= len)");
+    const unsigned char* base = reinterpret_cast<const unsigned char*>(raw_text);
+    // split_whitespace().collect().join(" ") and the cuts after '.', '?', '!' in one pass; a long text is processed in
+    // chunks (cut at ASCII whitespace) on several threads - the result does not depend on the chunking
+    int nt = static_cast<int>(std::thread::hardware_concurrency());
+    if (nt < 1) nt = 1;
+    if (static_cast<int64_t>(nt) > len / (256 * 1024)) nt = static_cast<int>(len / (256 * 1024));
+    if (nt < 1) nt = 1;
+    std::vector<int64_t> bounds(1, 0);
+    for (int k = 1; k < nt; ++k) {
+        int64_t b = len * k / nt;
+        if (b <= bounds.back()) b = bounds.back();
+        while (b < len && !(base[b] == ' ' || (base[b] >= 0x09 && base[b] <= 0x0D))) ++b;
+        if (b > bounds.back() && b < len) bounds.push_back(b);
+    }
+    bounds.push_back(len);
+    const int nc = static_cast<int>(bounds.size()) - 1;
+    std::vector<std::vector<int64_t>> cuts(static_cast<size_t>(nc));
+    std::vector<int64_t> out_len(static_cast<size_t>(nc), 0);
+    std::vector<std::unique_ptr<char[]>> bufs(static_cast<size_t>(nc));
+    auto work = [&](int k) {
+        const int64_t n = bounds[static_cast<size_t>(k) + 1] - bounds[static_cast<size_t>(k)];
+        // the first chunk writes straight into the caller's buffer (its output starts at offset 0)
+        char* out = cleaned;
+        if (k > 0) {
+            bufs[static_cast<size_t>(k)].reset(new char[static_cast<size_t>(n) + 1]);
+            out = bufs[static_cast<size_t>(k)].get();
+        }
+        clean_chunk(base + bounds[static_cast<size_t>(k)], base + bounds[static_cast<size_t>(k) + 1], out,
+                    &out_len[static_cast<size_t>(k)], &cuts[static_cast<size_t>(k)]);
+    };
+    if (nc == 1) {
+        work(0);
+    } else {
+        std::vector<std::thread> pool;
+        for (int k = 0; k < nc; ++k) pool.emplace_back(work, k);
+        for (auto& th : pool) th.join();
+    }
+    // offsets of the chunk outputs in the joined text: one space between two non-empty neighbours
+    std::vector<int64_t> off(static_cast<size_t>(nc), 0);
+    int64_t o = 0;
+    for (int k = 0; k < nc; ++k) {
+        if (out_len[static_cast<size_t>(k)] == 0) { off[static_cast<size_t>(k)] = o; continue; }
+        if (o > 0) cleaned[o++] = ' ';
+        off[static_cast<size_t>(k)] = o;
+        o += out_len[static_cast<size_t>(k)];
+    }
+    if (nc > 1) {
+        std::vector<std::thread> pool;
+        for (int k = 1; k < nc; ++k)
+            pool.emplace_back([&, k] { std::memcpy(cleaned + off[static_cast<size_t>(k)], bufs[static_cast<size_t>(k)].get(), static_cast<size_t>(out_len[static_cast<size_t>(k)])); });
+        for (auto& th : pool) th.join();
+    }
     *cleaned_len = o;
     if (o == 0) return 0;  // the caller reports "Cleaned text is empty" (main.rs:33-39)
+    int64_t n = 0;
+    auto push = [&](int64_t b, int64_t en) {  // [b, en) trimmed: only single spaces can be left at the ends
+        while (b < en && cleaned[b] == ' ') ++b;
+        while (en > b && cleaned[en - 1] == ' ') --en;
+        if (b == en) return;
+        if (n < max_sentences) { begin[n] = b; end[n] = en; }
+        ++n;
+    };
+    int64_t start = 0;
+    for (int k = 0; k < nc; ++k)
+        for (const int64_t c : cuts[static_cast<size_t>(k)]) {
+            const int64_t cut = off[static_cast<size_t>(k)] + c;
+            push(start, cut);
+            start = cut;
+        }
     if (start < o) push(start, o);
     return n;
 }

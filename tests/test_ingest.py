@@ -218,3 +218,19 @@ def test_split_then_encode_feeds_the_embedding_call(pkg, tmp_path):
     want = _library(tok, ingest_oracle.split_sentences(raw)[1], 32)
     assert np.array_equal(ids, want[0]) and np.array_equal(mask, want[1]) and np.array_equal(tt, want[2])
     assert ids.dtype == np.uint32 and ids.shape == (len(begin), 32) and (lengths >= 2).all()
+
+
+def test_split_sentences_of_a_long_text_is_chunked_across_threads(pkg):
+    """Texts above 256 KB per core are cleaned in chunks (cut at ASCII whitespace) on several threads: same cleaned text,
+    same sentences as the sequential restatement, including sentences and whitespace runs that straddle chunk borders."""
+    rng = random.Random(11)
+    pieces = ["word", "Sentence end.", "what?", "yes!", "...", "caf" + chr(0xE9), chr(0x4E2D) + chr(0x6587), "a.b", "x" * 50,
+              NBSP, IDSP, "\t", "\n\n", "   ", " ", " ", " ", NEL, "tail"]
+    raw = "".join(rng.choice(pieces) + rng.choice(["", " ", " ", "  ", "\n"]) for _ in range(400000))
+    assert len(raw.encode()) > 8 * 256 * 1024
+    cleaned, begin, end = pkg.abi.split_sentences(raw)
+    want_cleaned, want = ingest_oracle.split_sentences(raw)
+    assert cleaned.decode() == want_cleaned
+    assert len(begin) == len(want)
+    got = [cleaned[b:e].decode() for b, e in zip(begin, end)]
+    assert got == want
