@@ -95,6 +95,7 @@ _SIGNATURES = {
     "b200_ingest_vocab_size": (C.c_int32, [_P]),
     "b200_ingest_pad_id": (C.c_int32, [_P]),
     "b200_ingest_split_sentences": (C.c_int64, [_P, C.c_int64, _P, C.c_int64, C.POINTER(C.c_int64), _P, _P, C.c_int64]),
+    "b200_ingest_encode_packed": (C.c_int64, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, _P, _P, C.c_int64, _P]),
     "b200_ingest_encode": (C.c_int32, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, _P, _P, _P, _P]),
 }
 
@@ -264,6 +265,23 @@ class Ingest:
                                                         lengths.ctypes.data))
         return ids, mask, tt, lengths
 
+    def encode_ranges_packed(self, text: bytes, begin, end, max_len: int, threads: int = 0, out=None):
+        """Sentence i = text[begin[i]:end[i]] -> (ids_packed, type_ids_packed, cu_seqlens): the input of forward_varlen.
+        `out` = (ids, type_ids) u32 arrays to fill (e.g. pinned); they are grown if too small."""
+        begin = np.ascontiguousarray(begin, dtype=np.int64)
+        end = np.ascontiguousarray(end, dtype=np.int64)
+        n = len(begin)
+        cu = np.empty(n + 1, dtype=np.int32)
+        ids, tt = out if out is not None else (np.empty(n * 32 + 64, dtype=np.uint32), np.empty(n * 32 + 64, dtype=np.uint32))
+        while True:
+            cap = min(ids.size, tt.size)
+            total = load_library().b200_ingest_encode_packed(self._h, C.c_char_p(text), begin.ctypes.data, end.ctypes.data, n, max_len,
+                                                             threads, ids.ctypes.data, tt.ctypes.data, cap, cu.ctypes.data)
+            _check_ingest(total)
+            if total <= cap:
+                return ids[:total], tt[:total], cu
+            ids, tt = np.empty(total, dtype=np.uint32), np.empty(total, dtype=np.uint32)
+
     def encode(self, sentences, seq_len: int, threads: int = 0):
         """tokenizer.encode_batch(sentences, true) with Fixed(seq_len) padding and LongestFirst truncation."""
         enc = [s.encode("utf-8") for s in sentences]
@@ -414,12 +432,14 @@ class Embedder:
         _check(self.lib.b200_embed_forward(self.h, p_ids, p_mask, p_tt, b, s, flags, out.ctypes.data))
         return out
 
-    def forward_varlen(self, ids_packed, type_ids_packed, cu_seqlens, max_seqlen: int, flags: int = 0) -> np.ndarray:
+    def forward_varlen(self, ids_packed, type_ids_packed, cu_seqlens, max_seqlen: int, flags: int = 0,
+                       out: np.ndarray | None = None) -> np.ndarray:
         ids, p_ids = _u32(ids_packed)
         tt, p_tt = _u32(type_ids_packed)
         cu = np.ascontiguousarray(cu_seqlens, dtype=np.int32)
         b = len(cu) - 1
-        out = np.empty((b, self.shape.hidden_size), dtype=np.float32)
+        if out is None:
+            out = np.empty((b, self.shape.hidden_size), dtype=np.float32)
         _check(self.lib.b200_embed_forward_varlen(self.h, p_ids, p_tt, cu.ctypes.data, b, int(ids.size), max_seqlen,
                                                   flags, out.ctypes.data))
         return out

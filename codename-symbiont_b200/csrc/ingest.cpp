@@ -581,7 +581,8 @@ void encode_piece(const b200_ingest& t, Scratch& sc, const unsigned char* b, con
 }
 
 // One sentence -> row of ids / mask / type_ids (length P). Returns the number of real tokens.
-int encode_sentence(const b200_ingest& t, Scratch& sc, const char* s, size_t n, int P, uint32_t* ids, uint32_t* mask, uint32_t* types) {
+// The sentence's tokens (without the template) into sc.toks; returns how many of them survive truncation to P.
+size_t tokenize_sentence(const b200_ingest& t, Scratch& sc, const char* s, size_t n, int P) {
     const size_t n_special = t.prefix.size() + t.suffix.size();
     const size_t budget = static_cast<size_t>(P) - n_special;
     sc.toks.clear();
@@ -609,7 +610,11 @@ int encode_sentence(const b200_ingest& t, Scratch& sc, const char* s, size_t n, 
         }
         if (sc.toks.size() < budget) encode_piece(t, sc, seg, e, budget);
     }
-    const size_t keep = std::min(sc.toks.size(), budget);  // LongestFirst, direction right, one sequence
+    return std::min(sc.toks.size(), budget);  // LongestFirst, direction right, one sequence
+}
+
+int encode_sentence(const b200_ingest& t, Scratch& sc, const char* s, size_t n, int P, uint32_t* ids, uint32_t* mask, uint32_t* types) {
+    const size_t keep = tokenize_sentence(t, sc, s, n, P);
     int at = 0;
     for (const Special& sp : t.prefix) { ids[at] = static_cast<uint32_t>(sp.id); types[at] = sp.type_id; mask[at++] = 1; }
     for (size_t i = 0; i < keep; ++i) { ids[at] = static_cast<uint32_t>(sc.toks[i]); types[at] = t.seq_type_id; mask[at++] = 1; }
@@ -783,6 +788,70 @@ int32_t b200_ingest_encode(const b200_ingest* t, const char* text, const int64_t
         for (auto& th : pool) th.join();
     }
     return B200_EMBED_OK;
+}
+
+int64_t b200_ingest_encode_packed(const b200_ingest* t, const char* text, const int64_t* begin, const int64_t* end, int32_t n,
+                                  int32_t max_len, int32_t threads, uint32_t* ids_packed, uint32_t* type_ids_packed,
+                                  int64_t capacity_tokens, int32_t* cu_seqlens) {
+    if (!t) return fail(B200_EMBED_ERR_INVALID_ARG, "null tokenizer");
+    if (n < 0 || !cu_seqlens || capacity_tokens < 0 || (n > 0 && (!text || !begin || !end)) ||
+        (capacity_tokens > 0 && (!ids_packed || !type_ids_packed)))
+        return fail(B200_EMBED_ERR_INVALID_ARG, "encode_packed: null pointer");
+    if (max_len < static_cast<int32_t>(t->prefix.size() + t->suffix.size()) || max_len <= 0)
+        return fail(B200_EMBED_ERR_INVALID_ARG, "encode_packed: max_len is smaller than the special tokens of the template");
+    for (int32_t i = 0; i < n; ++i)
+        if (begin[i] < 0 || end[i] < begin[i]) return fail(B200_EMBED_ERR_INVALID_ARG, "encode_packed: bad sentence range");
+    int nt = threads > 0 ? threads : static_cast<int>(std::thread::hardware_concurrency());
+    if (nt < 1) nt = 1;
+    if (nt > n / 16) nt = n / 16 > 0 ? n / 16 : 1;
+    // every thread tokenises a contiguous run of sentences into its own buffers (lengths go straight into cu_seqlens),
+    // then copies them to the offsets a prefix sum over the lengths gives
+    struct Part { std::vector<uint32_t> ids, types; };
+    std::vector<Part> parts(static_cast<size_t>(nt));
+    auto span = [&](int k, int* lo, int* hi) {
+        *lo = static_cast<int>(static_cast<int64_t>(n) * k / nt);
+        *hi = static_cast<int>(static_cast<int64_t>(n) * (k + 1) / nt);
+    };
+    auto run = [&](auto&& fn) {
+        if (nt <= 1) { fn(0); return; }
+        std::vector<std::thread> pool;
+        for (int k = 0; k < nt; ++k) pool.emplace_back(fn, k);
+        for (auto& th : pool) th.join();
+    };
+    run([&](int k) {
+        Scratch sc;
+        sc.word.reserve(256);
+        sc.toks.reserve(static_cast<size_t>(max_len) + 64);
+        int lo, hi;
+        span(k, &lo, &hi);
+        Part& p = parts[static_cast<size_t>(k)];
+        p.ids.reserve(static_cast<size_t>(hi - lo) * 32);
+        p.types.reserve(static_cast<size_t>(hi - lo) * 32);
+        for (int i = lo; i < hi; ++i) {
+            const size_t keep = tokenize_sentence(*t, sc, text + begin[i], static_cast<size_t>(end[i] - begin[i]), max_len);
+            for (const Special& sp : t->prefix) { p.ids.push_back(static_cast<uint32_t>(sp.id)); p.types.push_back(sp.type_id); }
+            for (size_t j = 0; j < keep; ++j) { p.ids.push_back(static_cast<uint32_t>(sc.toks[j])); p.types.push_back(t->seq_type_id); }
+            for (const Special& sp : t->suffix) { p.ids.push_back(static_cast<uint32_t>(sp.id)); p.types.push_back(sp.type_id); }
+            cu_seqlens[i + 1] = static_cast<int32_t>(keep + t->prefix.size() + t->suffix.size());
+        }
+    });
+    int64_t total = 0;
+    cu_seqlens[0] = 0;
+    for (int32_t i = 0; i < n; ++i) {
+        total += cu_seqlens[i + 1];
+        if (total > INT32_MAX) return fail(B200_EMBED_ERR_INVALID_ARG, "encode_packed: more than 2^31 tokens in one call");
+        cu_seqlens[i + 1] = static_cast<int32_t>(total);
+    }
+    if (total > capacity_tokens) return total;  // nothing written: call again with room for `total` tokens
+    run([&](int k) {
+        int lo, hi;
+        span(k, &lo, &hi);
+        const Part& p = parts[static_cast<size_t>(k)];
+        if (p.ids.empty()) return;
+        std::memcpy(ids_packed + cu_seqlens[lo], p.ids.data(), p.ids.size() * sizeof(uint32_t));
+        std::memcpy(type_ids_packed + cu_seqlens[lo], p.types.data(), p.types.size() * sizeof(uint32_t));
+    });
+    return total;
 }
 
 }  // extern "C"

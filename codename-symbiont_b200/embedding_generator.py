@@ -88,9 +88,11 @@ class EmbeddingGenerator:
         if self.ingest is None:
             sentences = [cleaned[b:e].decode() for b, e in zip(begin, end)]
             return sentences, self.generate_sentence_embeddings_array(sentences)
-        ids, mask, type_ids, _ = self.ingest.encode_ranges(cleaned, begin, end, self.config.max_position_embeddings)
+        # packed tokens (no padding materialised on the host or copied to the device) -> b200_embed_forward_varlen
+        P = self.config.max_position_embeddings
+        ids, type_ids, cu = self.ingest.encode_ranges_packed(cleaned, begin, end, P)
         flags = FLAG_NORMALIZE if self.normalize else 0
-        out = self.model.forward(ids, mask, type_ids, flags=flags)
+        out = self.model.forward_varlen(ids, type_ids, cu, int(np.diff(cu).max()), flags=flags)
         return [cleaned[b:e].decode() for b, e in zip(begin, end)], out
 
     def close(self):

@@ -280,6 +280,14 @@ int64_t b200_ingest_split_sentences(const char* raw_text, int64_t len, char* cle
 int32_t b200_ingest_encode(const b200_ingest* t, const char* text, const int64_t* begin, const int64_t* end, int32_t n,
                            int32_t seq_len, int32_t threads, uint32_t* ids, uint32_t* mask, uint32_t* type_ids,
                            int32_t* lengths_or_null);
+/* The same tokens without the padding, in the form b200_embed_forward_varlen takes: the real tokens of all sentences
+ * back to back in ids_packed / type_ids_packed and cu_seqlens[n + 1] (exclusive prefix sums). max_len is the truncation
+ * length (max_position_embeddings). Returns the total number of tokens; when it exceeds capacity_tokens only
+ * cu_seqlens is written - call again with room for that many. For sentences of ~20 tokens this is 1/6 of the bytes the
+ * padded arrays take at seq_len 128, on the host and over PCIe. Negative on bad arguments. */
+int64_t b200_ingest_encode_packed(const b200_ingest* t, const char* text, const int64_t* begin, const int64_t* end,
+                                  int32_t n, int32_t max_len, int32_t threads, uint32_t* ids_packed,
+                                  uint32_t* type_ids_packed, int64_t capacity_tokens, int32_t* cu_seqlens);
 
 /* -- resident cosine index: the search step after the path (f4; CUDA, no CPU fallback) ---------------------------
  * Exact cosine top-k over embeddings kept in HBM, as an alternative to the Qdrant hop of vector_memory_service

@@ -52,11 +52,26 @@ for _ in range(3):
     m, nbytes, dt = once()
     if best is None or dt.sum() < best.sum():
         best = dt
+pid = abi.host_alloc((n * 64,), np.uint32); ptt = abi.host_alloc((n * 64,), np.uint32)
+def once_packed():
+    t = [time.perf_counter()]
+    cleaned, begin, end = abi.split_sentences(doc); t.append(time.perf_counter())
+    m = len(begin)
+    a, b, cu = ing.encode_ranges_packed(cleaned, begin, end, P, 0, (pid, ptt)); t.append(time.perf_counter())
+    emb.forward_varlen(a, b, cu, int(np.diff(cu).max()), out=out[:m]); t.append(time.perf_counter())
+    payload = abi.json_text_with_embeddings("doc", "http://x", (cleaned, begin, end), out[:m], "minilm", 1, as_array=True); t.append(time.perf_counter())
+    return m, len(payload), np.diff(t)
+once_packed()
+best_packed = min((once_packed()[2] for _ in range(3)), key=lambda d: d.sum())
 names = ["split", "tokenise", "embed (H2D + GPU + D2H)", "json"]
 print(f"sentences {m}  text {len(doc) / 1e6:.1f} MB  payload {nbytes / 1e6:.1f} MB  host cores {os.cpu_count()}")
 for k, v in zip(names, best):
     print(f"  {k:28s} {v * 1e3:8.1f} ms   {m / v:12.0f} sentences/s")
 print(f"  {'total (stages in sequence)':28s} {best.sum() * 1e3:8.1f} ms   {m / best.sum():12.0f} sentences/s")
+print("packed tokens (b200_ingest_encode_packed -> b200_embed_forward_varlen):")
+for k, v in zip(names, best_packed):
+    print(f"  {k:28s} {v * 1e3:8.1f} ms   {m / v:12.0f} sentences/s")
+print(f"  {'total (stages in sequence)':28s} {best_packed.sum() * 1e3:8.1f} ms   {m / best_packed.sum():12.0f} sentences/s")
 
 # The same work pipelined over chunks of sentences: while the GPU embeds chunk i (b200_embed_submit), the host cores
 # write the JSON message of chunk i-1 (one message per chunk, as the NATS payload limit forces anyway).

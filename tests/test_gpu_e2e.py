@@ -324,7 +324,10 @@ def test_embedding_generator_end_to_end_text(pkg, built, tmp_path):
         # raw text in, sentences and vectors out (main.rs:28-95)
         split, vecs = gen.process_raw_text("  " + "   ".join(sents) + " trailing words\n")
         assert split == sents + ["trailing words"] and vecs.shape == (len(sents) + 1, shape.hidden_size)
-        assert np.array_equal(vecs[:len(sents)], np.array(out, np.float32))
+        # process_raw_text goes through the packed entries (encode_packed -> forward_varlen): same values as the padded
+        # call up to the bf16 schedule (the same sentences in a different batch composition)
+        assert np.abs(vecs[:len(sents)] - np.array(out, np.float32)).max() <= 4e-3
+        assert cos_rows(vecs[:len(sents)], np.array(out, np.float32)).min() >= 0.9999
         with pytest.raises(ValueError, match="Cleaned text is empty for id: doc7"):
             gen.process_raw_text(" \n\t ", "doc7")
     finally:

@@ -234,3 +234,28 @@ def test_split_sentences_of_a_long_text_is_chunked_across_threads(pkg):
     assert len(begin) == len(want)
     got = [cleaned[b:e].decode() for b, e in zip(begin, end)]
     assert got == want
+
+
+def test_packed_encoding_is_the_padded_one_without_the_padding(pkg, tmp_path):
+    """b200_ingest_encode_packed (the input of b200_embed_forward_varlen): the real tokens of the padded rows back to back,
+    cu_seqlens = prefix sums of the lengths; a too-small output only reports the total; thread count does not matter."""
+    tok = _trained()
+    path = os.path.join(tmp_path, "tokenizer.json")
+    tok.save(path)
+    ing = pkg.abi.Ingest(path)
+    sentences = _fuzz(3000, 5) + EDGE
+    P = 40
+    ids, mask, tt, lengths = ing.encode(sentences, P)
+    enc = [s.encode("utf-8") for s in sentences]
+    end = np.cumsum([len(b) for b in enc], dtype=np.int64)
+    begin = np.concatenate([np.zeros(1, dtype=np.int64), end[:-1]])
+    text = b"".join(enc)
+    pi, pt, cu = ing.encode_ranges_packed(text, begin, end, P)
+    assert cu.dtype == np.int32 and cu[0] == 0 and np.array_equal(np.diff(cu), lengths) and cu[-1] == len(pi) == len(pt)
+    assert np.array_equal(pi, ids[mask == 1]) and np.array_equal(pt, tt[mask == 1])
+    # a small caller buffer: the wrapper's first call only learns the total, the second fills
+    small = (np.empty(10, np.uint32), np.empty(10, np.uint32))
+    pi2, pt2, cu2 = ing.encode_ranges_packed(text, begin, end, P, threads=3, out=small)
+    assert np.array_equal(pi2, pi) and np.array_equal(pt2, pt) and np.array_equal(cu2, cu)
+    pi3, _, cu3 = ing.encode_ranges_packed(text, begin[:0], end[:0], P)
+    assert len(pi3) == 0 and cu3.tolist() == [0]
