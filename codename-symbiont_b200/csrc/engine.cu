@@ -132,7 +132,8 @@ struct b200_embed {
     bool force_fused_ffn = false, force_qkv_attn = false;
     bool qkv_attn = true;    // K23 replaces the QKV GEMM + attention pair whenever it supports the call (hidden 128 / 256 / 384,
                              // head_dim 32, seq_len <= 128); B200_EMBED_QKV_ATTN=0 for A/B
-    bool use_graphs = true;  // small host-buffer calls replay a captured CUDA graph; B200_EMBED_GRAPHS=0 for A/B
+    std::atomic<bool> use_graphs{true};  // small host-buffer calls replay a captured CUDA graph; B200_EMBED_GRAPHS=0 for
+                                         // A/B; cleared for good if a capture ever fails (any calling thread may do that)
     bool attn_mma = false;  // B200_EMBED_ATTENTION=mma selects the mma.sync attention kernel (A/B checks)
     // weights
     float* arena32 = nullptr;
