@@ -562,6 +562,18 @@ cudaError_t launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms) {
     constexpr bool OUT_F32 = sizeof(OutT) == 4;
     constexpr int CSIZE = CL > 1 ? CL : (PAIR ? 2 : 1);
     alignas(64) CUtensorMap ta, tb, tc, tcl, tr, trl;
+    if constexpr (CL > 1) {
+        // The A tile is multicast inside the cluster. TMA multicast loads here read only this GPU's memory, since on B200 a
+        // TMA multicast load from another GPU's memory hung the GPU: an operand that is not plain device memory of the
+        // current device (a peer allocation, an IPC or managed mapping) is refused before anything is launched.
+        cudaPointerAttributes pa{};
+        int dev = -1;
+        if (cudaGetDevice(&dev) != cudaSuccess || cudaPointerGetAttributes(&pa, a.a) != cudaSuccess ||
+            pa.type != cudaMemoryTypeDevice || pa.device != dev) {
+            cudaGetLastError();
+            return cudaErrorInvalidDevicePointer;
+        }
+    }
     if (!make_tmap(&ta, a.a, a.m, a.k, BLOCK_K, BLOCK_M / (CL > 1 ? CL : 1), false, CU_TENSOR_MAP_SWIZZLE_128B))
         return cudaErrorInvalidValue;
     if (!make_tmap(&tb, a.b, a.n, a.k, BLOCK_K, BLOCK_N / (PAIR ? 2 : 1), false, CU_TENSOR_MAP_SWIZZLE_128B))
