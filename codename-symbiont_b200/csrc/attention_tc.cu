@@ -82,6 +82,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int items = p.batch * p.heads * p.q_blocks;
 
+    pdl_trigger();
     if (threadIdx.x == 0) {
         prefetch_tmap(&tmap_qkv);
         for (int s = 0; s < 2; ++s) {
@@ -102,6 +103,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
     __syncthreads();
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot_ptr;
+    pdl_wait();  // nothing above reads or writes global memory
 
     // item i -> (sentence b, query block qb, head h), i = (b * q_blocks + qb) * heads + h. Items advance by gridDim.x,
     // so (b, r) is carried along instead of dividing every time; items whose query block lies past the sentence
@@ -414,8 +416,7 @@ cudaError_t launch(const __nv_bfloat16* qkv, const int* cu, int rows_cap, int ba
     if (items <= 0) return cudaSuccess;
     const int ctas = num_sms * (D == 32 ? 2 : 1);
     const int grid = static_cast<int>(items < ctas ? items : ctas);
-    kern<<<grid, ATT_THREADS, smem, s>>>(map, p);
-    return cudaGetLastError();
+    return launch_pdl(kern, dim3(grid), dim3(ATT_THREADS), smem, s, map, p);
 }
 
 }  // namespace

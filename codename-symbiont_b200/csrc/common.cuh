@@ -5,6 +5,7 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 namespace b200 {
 
@@ -188,6 +189,14 @@ template <int N>
 __device__ __forceinline__ void tma_store_wait() {
     asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
 }
+// Programmatic dependent launch: a kernel launched with the programmatic-stream-serialization attribute (launch_pdl
+// below) may start while its predecessor in the stream is still running. It sets up what does not depend on the
+// predecessor (barriers, TMEM, descriptor prefetch), then pdl_wait() blocks until the predecessor grid has completed
+// and its writes are visible; no global memory may be touched before that. pdl_trigger() at the top lets the successor
+// be launched as soon as every CTA of this grid is resident. Both are no-ops in a kernel launched the plain way.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 __device__ __forceinline__ void prefetch_tmap(const void* tmap) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(tmap) : "memory");
 }
@@ -310,6 +319,33 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
 __host__ __device__ constexpr uint32_t umma_idesc_bf16(int m, int n) {
     return (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(n >> 3) << 17) |
            (static_cast<uint32_t>(m >> 4) << 24);
+}
+
+// ---- host: launches with the programmatic-dependent-launch attribute --------------------------------------------------
+// B200_EMBED_PDL=0 (read once) launches everything the plain way, for A/B timing.
+inline bool pdl_enabled() {
+    static const bool on = [] {
+        const char* v = getenv("B200_EMBED_PDL");
+        return !(v && v[0] == '0');
+    }();
+    return on;
+}
+inline void pdl_attribute(cudaLaunchAttribute* a) {
+    a->id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    a->val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    pdl_attribute(&attr[0]);
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
 }
 
 }  // namespace b200

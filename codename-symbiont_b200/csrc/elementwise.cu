@@ -82,6 +82,8 @@ __device__ __forceinline__ void warp_layernorm_store(float4 (&v)[NC], int nchunk
 // embedding_generator.rs:85); anything else sets status bit 0.
 __global__ void mask_lengths_kernel(const uint32_t* __restrict__ mask, int batch, int seq_len,
                                     int* __restrict__ lens, int* __restrict__ status) {
+    pdl_trigger();
+    pdl_wait();
     const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (b >= batch) return;
@@ -108,6 +110,8 @@ __global__ void scan_lengths_kernel(const int* __restrict__ lens, int batch, int
     __shared__ int warp_tot[32];
     __shared__ int carry;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    pdl_trigger();
+    pdl_wait();
     if (threadIdx.x == 0) { carry = 0; cu[0] = 0; }
     __syncthreads();
     for (int base = 0; base < batch; base += blockDim.x) {
@@ -218,6 +222,8 @@ embed_layernorm_kernel(const uint32_t* __restrict__ ids, const uint32_t* __restr
                        const float* __restrict__ beta, float eps, int H, int vocab,
                        int type_vocab, int max_pos, T* __restrict__ out, T* __restrict__ out_lo,
                        int* __restrict__ status) {
+    pdl_trigger();
+    pdl_wait();
     const long long w0 = (static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5)) * TOK;
     const int lane = threadIdx.x & 31;
     const long long slots = PADDED ? static_cast<long long>(batch) * seq_len : total_tokens;
@@ -317,6 +323,8 @@ __global__ void mean_pool_kernel(const T* __restrict__ hidden, const T* __restri
     const int cols4 = H >> 2;
     const int G = blockDim.x / cols4;
     const int g = threadIdx.x / cols4, c = threadIdx.x - g * cols4;
+    pdl_trigger();
+    pdl_wait();
     const int start = cu[b], len = cu[b + 1] - start;
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     if (g < G) {
@@ -362,9 +370,10 @@ __global__ void mean_pool_kernel(const T* __restrict__ hidden, const T* __restri
 cudaError_t launch_mask_lengths(const uint32_t* mask, int batch, int seq_len, int* lens, int* cu, int* status,
                                 cudaStream_t s) {
     if (batch <= 0) return cudaSuccess;
-    mask_lengths_kernel<<<(batch + 7) / 8, 256, 0, s>>>(mask, batch, seq_len, lens, status);
-    scan_lengths_kernel<<<1, 1024, 0, s>>>(lens, batch, cu);
-    return cudaGetLastError();
+    if (cudaError_t e = launch_pdl(mask_lengths_kernel, dim3((batch + 7) / 8), dim3(256), 0, s, mask, batch, seq_len, lens, status);
+        e != cudaSuccess)
+        return e;
+    return launch_pdl(scan_lengths_kernel, dim3(1), dim3(1024), 0, s, static_cast<const int*>(lens), batch, cu);
 }
 
 cudaError_t launch_pack_tiles(const int* cu, int batch, int cap, int* seg_off, int* tile_first, int* n_tiles,
@@ -383,8 +392,9 @@ cudaError_t launch_embed_layernorm(const EmbedArgs& a, cudaStream_t s) {
     if (a.H % 128 != 0 || nch < 1 || nch > MAX_CHUNKS) return cudaErrorInvalidValue;
     const int tok = nch <= 4 ? 2 : 1;
     const unsigned grid = static_cast<unsigned>((slots + 8LL * tok - 1) / (8LL * tok));
+    cudaError_t launch_err = cudaSuccess;
 #define B200_EMBED_LAUNCH(PAD, TOK, NCH)                                                                                   \
-    embed_layernorm_kernel<T, PAD, TOK, NCH><<<grid, 256, 0, s>>>(                                                         \
+    launch_err = launch_pdl(embed_layernorm_kernel<T, PAD, TOK, NCH>, dim3(grid), dim3(256), 0, s,                       \
         a.ids, a.type_ids, a.cu, a.batch, a.seq_len, a.total_tokens, a.word, a.pos, a.type, a.gamma, a.beta, a.eps, a.H,  \
         a.vocab, a.type_vocab, a.max_pos, static_cast<T*>(a.out), static_cast<T*>(a.out_lo), a.status)
 #define B200_EMBED_PICK(PAD)                                    \
@@ -401,7 +411,7 @@ cudaError_t launch_embed_layernorm(const EmbedArgs& a, cudaStream_t s) {
     if (a.padded) { B200_EMBED_PICK(true); } else { B200_EMBED_PICK(false); }
 #undef B200_EMBED_PICK
 #undef B200_EMBED_LAUNCH
-    return cudaGetLastError();
+    return launch_err;
 }
 template cudaError_t launch_embed_layernorm<__nv_bfloat16>(const EmbedArgs&, cudaStream_t);
 template cudaError_t launch_embed_layernorm<float>(const EmbedArgs&, cudaStream_t);
@@ -436,8 +446,8 @@ cudaError_t launch_mean_pool(const T* hidden, const T* hidden_lo, const int* cu,
     if (G < 1) G = 1;
     if (G > 8) G = 8;
     const int threads = ((G * cols4 + 31) / 32) * 32;
-    mean_pool_kernel<T><<<batch, threads, G * cols4 * sizeof(float4), s>>>(hidden, hidden_lo, cu, H, normalize, out);
-    return cudaGetLastError();
+    return launch_pdl(mean_pool_kernel<T>, dim3(batch), dim3(threads), G * cols4 * sizeof(float4), s, hidden, hidden_lo, cu, H,
+                      normalize, out);
 }
 template cudaError_t launch_mean_pool<__nv_bfloat16>(const __nv_bfloat16*, const __nv_bfloat16*, const int*, int, int,
                                                      int, float*, cudaStream_t);

@@ -168,31 +168,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
 
-    int rows = p.m;
-    if (p.d_rows != nullptr) {
-        const int r = *p.d_rows;
-        rows = r < rows ? r : rows;
-    }
-    const int num_m_tiles = (rows + BLOCK_M - 1) / BLOCK_M;
-    const int num_n_tiles = p.n / BLOCK_N;  // == CL when the row is split over a cluster
-    const int num_kb = (p.k + BLOCK_K - 1) / BLOCK_K;
-    // Work units, walked identically by all CTAs of a cluster:
-    //   plain:  unit = (m_tile, n_tile), one CTA each;
-    //   CL > 1: unit = m_tile, CTA `crank` takes columns [crank * BLOCK_N, +BLOCK_N) of it;
-    //   PAIR:   unit = (pair of adjacent m_tiles, n_tile), CTA `crank` takes m_tile 2 * pair + crank. With an odd number
-    //           of row blocks the last pair's second CTA works on an out-of-range block: its loads are zero-filled and
-    //           its stores clipped, but it keeps its side of every handshake.
-    const int crank = CSIZE > 1 ? static_cast<int>(cluster_ctarank()) : 0;
-    const int num_units = CL > 1 ? num_m_tiles : (PAIR ? ((num_m_tiles + 1) / 2) * num_n_tiles : num_m_tiles * num_n_tiles);
-    const int unit0 = static_cast<int>(blockIdx.x) / CSIZE;
-    const int unit_step = static_cast<int>(gridDim.x) / CSIZE;
-    const int my_tiles = unit0 < num_units ? (num_units - unit0 + unit_step - 1) / unit_step : 0;
-    auto tile_m = [&](int i) {
-        const int t = unit0 + i * unit_step;
-        return CL > 1 ? t : (PAIR ? 2 * (t / num_n_tiles) + crank : t / num_n_tiles);
-    };
-    auto tile_n = [&](int i) { return CL > 1 ? crank : (unit0 + i * unit_step) % num_n_tiles; };
-
+    pdl_trigger();
     if (threadIdx.x == 0) {
         prefetch_tmap(&tmap_a);
         prefetch_tmap(&tmap_b);
@@ -218,6 +194,33 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     if constexpr (CSIZE > 1) cluster_sync_all();  // peers' barriers exist before anyone arrives on them remotely
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot_ptr;
+    pdl_wait();  // nothing above reads or writes global memory
+
+    int rows = p.m;
+    if (p.d_rows != nullptr) {
+        const int r = *p.d_rows;
+        rows = r < rows ? r : rows;
+    }
+    const int num_m_tiles = (rows + BLOCK_M - 1) / BLOCK_M;
+    const int num_n_tiles = p.n / BLOCK_N;  // == CL when the row is split over a cluster
+    const int num_kb = (p.k + BLOCK_K - 1) / BLOCK_K;
+    // Work units, walked identically by all CTAs of a cluster:
+    //   plain:  unit = (m_tile, n_tile), one CTA each;
+    //   CL > 1: unit = m_tile, CTA `crank` takes columns [crank * BLOCK_N, +BLOCK_N) of it;
+    //   PAIR:   unit = (pair of adjacent m_tiles, n_tile), CTA `crank` takes m_tile 2 * pair + crank. With an odd number
+    //           of row blocks the last pair's second CTA works on an out-of-range block: its loads are zero-filled and
+    //           its stores clipped, but it keeps its side of every handshake.
+    const int crank = CSIZE > 1 ? static_cast<int>(cluster_ctarank()) : 0;
+    const int num_units = CL > 1 ? num_m_tiles : (PAIR ? ((num_m_tiles + 1) / 2) * num_n_tiles : num_m_tiles * num_n_tiles);
+    const int unit0 = static_cast<int>(blockIdx.x) / CSIZE;
+    const int unit_step = static_cast<int>(gridDim.x) / CSIZE;
+    const int my_tiles = unit0 < num_units ? (num_units - unit0 + unit_step - 1) / unit_step : 0;
+    auto tile_m = [&](int i) {
+        const int t = unit0 + i * unit_step;
+        return CL > 1 ? t : (PAIR ? 2 * (t / num_n_tiles) + crank : t / num_n_tiles);
+    };
+    auto tile_n = [&](int i) { return CL > 1 ? crank : (unit0 + i * unit_step) % num_n_tiles; };
+
 
     if (warp == 0) {
         // ------------------------------ TMA producer ------------------------------
@@ -611,13 +614,14 @@ cudaError_t launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms) {
     cfg.blockDim = dim3(NUM_THREADS);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = CSIZE;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
+    cudaLaunchAttribute attr[2];
+    pdl_attribute(&attr[0]);
+    attr[1].id = cudaLaunchAttributeClusterDimension;
+    attr[1].val.clusterDim.x = CSIZE;
+    attr[1].val.clusterDim.y = 1;
+    attr[1].val.clusterDim.z = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = CSIZE > 1 ? 1 : 0;
+    cfg.numAttrs = CSIZE > 1 ? 2 : 1;
     // persistent grid: as many clusters as the device can hold at once (size-4 clusters do not tile all 148 SMs)
     static int max_units = 0;
     if (max_units == 0) {
