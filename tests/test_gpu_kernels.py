@@ -304,3 +304,25 @@ def test_k5_mean_pool(env, dtype, normalize):
                      d_hidden_lo=0 if dtype else d_lo.data_ptr())
     got = host(out)
     assert np.abs(got - want).max() <= (2e-6 if dtype else 3e-5)  # bf16: hi + lo keeps ~16 bits of each element
+
+
+def test_k2_layernorm_gemm_refuses_operands_outside_this_gpus_memory(pkg, built):
+    """The LayerNorm-fused GEMM multicasts its A tile inside a cluster, and multicast loads read only plain device memory
+    of the current GPU: an operand in pinned host memory (a stand-in for any mapping that is not a local allocation) is
+    refused with an error before anything is launched; the same call with a device operand works."""
+    shape = pkg.weights.BertShape(512, 384, 1, 12, 1536, 64, 2)
+    rows = 256
+    with pkg.Embedder.random_init(shape, seed=2) as emb:
+        x_host = pkg.abi.host_alloc((rows, 384), np.uint16)
+        x_host[:] = 0
+        res = torch.zeros((rows, 384), dtype=torch.bfloat16, device="cuda")
+        out, out_lo = torch.empty_like(res), torch.empty_like(res)
+        with pytest.raises(pkg.abi.B200EmbedError):
+            emb.op_linear(0, 1, x_host.ctypes.data, res.data_ptr(), rows, 0, out.data_ptr(), d_residual_lo=res.data_ptr(),
+                          d_y_lo=out_lo.data_ptr())
+        x_dev = torch.zeros((rows, 384), dtype=torch.bfloat16, device="cuda")
+        emb.op_linear(0, 1, x_dev.data_ptr(), res.data_ptr(), rows, 0, out.data_ptr(), d_residual_lo=res.data_ptr(),
+                      d_y_lo=out_lo.data_ptr())
+        torch.cuda.synchronize()
+        assert torch.isfinite(out.float()).all()
+        pkg.abi.host_free(x_host)
