@@ -114,3 +114,25 @@ def test_embeddings_from_the_path_feed_the_index(pkg, built):
         got_ids, got_sc = ix.search(out[4], 3)
     assert got_ids[0, 0] == 4 and abs(got_sc[0, 0] - 1.0) <= 2e-6
     _check(got_ids, got_sc, out, out[4:5], 3)
+
+
+def test_selection_with_many_survivors_falls_back_to_the_full_sort(pkg, built):
+    """The k <= 256 selection keeps what is at least as good as the k-th best of the 256 per-thread bests of a 4096-block.
+    When the good candidates all sit in the slots of k threads (slot i belongs to thread i % 256) there are 16 k
+    survivors, more than the 1024 the filter sorts, and the block is sorted as a whole instead: same answer."""
+    dim, n, k = 128, 4096 * 3 + 500, 100
+    rng = np.random.default_rng(9)
+    theta = np.full(n, 2.0)  # cos(2.0) < 0: never in the answer
+    good = np.nonzero((np.arange(n) % 256) < k)[0]
+    theta[good] = 0.01 + 0.001 * rng.permutation(len(good))
+    vectors = np.zeros((n, dim), dtype=np.float32)
+    vectors[:, 0] = np.cos(theta)
+    vectors[:, 1] = np.sin(theta)
+    q = np.zeros((1, dim), dtype=np.float32)
+    q[0, 0] = 1.0
+    with pkg.abi.Index(dim) as ix:
+        ix.add(vectors)
+        ids, scores = ix.search(q, k)
+    want_ids, want_sc = search_oracle.search(vectors, q, k)
+    assert np.array_equal(ids, want_ids)
+    assert np.abs(scores - want_sc).max() <= 2e-6
