@@ -89,6 +89,8 @@ _SIGNATURES = {
     "b200_index_add_device": (C.c_int32, [_P, _P, C.c_int64]),
     "b200_index_search": (C.c_int32, [_P, _P, C.c_int32, C.c_int32, _P, _P]),
     "b200_index_last_scan_ms": (C.c_float, [_P]),
+    "b200_index_save": (C.c_int32, [_P, C.c_char_p]),
+    "b200_index_load": (C.c_int32, [C.c_char_p, C.c_int32, C.POINTER(_P)]),
     "b200_ingest_last_error": (C.c_char_p, []),
     "b200_ingest_create": (C.c_int32, [C.c_char_p, C.POINTER(_P)]),
     "b200_ingest_destroy": (None, [_P]),
@@ -348,6 +350,17 @@ class Index:
     @property
     def last_scan_ms(self) -> float:
         return float(load_library().b200_index_last_scan_ms(self._h))
+
+    def save(self, path: str) -> None:
+        self._check(load_library().b200_index_save(self._h, os.fsencode(path)))
+
+    @classmethod
+    def load(cls, path: str, device: int = 0) -> "Index":
+        self = cls.__new__(cls)
+        self._h = _P()
+        cls._check(load_library().b200_index_load(os.fsencode(path), device, C.byref(self._h)))
+        self.dim = int(load_library().b200_index_dim(self._h))
+        return self
 
 
 def host_alloc(shape, dtype) -> np.ndarray:

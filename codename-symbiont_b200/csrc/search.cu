@@ -22,6 +22,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
+#include <memory>
 #include <mutex>
 #include <string>
 
@@ -522,5 +523,69 @@ int32_t b200_index_search(b200_index* ix, const float* queries, int32_t q, int32
 }
 
 float b200_index_last_scan_ms(const b200_index* ix) { return ix ? ix->last_scan_ms : -1.f; }
+
+// ---- persistence: the rows as they are in HBM (already normalised), so that a restarted service does not have to embed
+// its corpus again (the Qdrant collection the reference writes to is persistent). File: "B200IDX1", dim (i32), n (i64),
+// then n * dim f32, little endian.
+int32_t b200_index_save(b200_index* ix, const char* path) {
+    if (!ix || !path) return fail(B200_EMBED_ERR_INVALID_ARG, "bad argument");
+    std::lock_guard<std::mutex> lk(ix->mu);
+    DevGuard guard(ix->device);
+    FILE* f = std::fopen(path, "wb");
+    if (!f) return fail(B200_EMBED_ERR_IO, std::string("cannot create ") + path);
+    const int32_t dim = ix->dim;
+    const int64_t n = ix->n;
+    bool ok = std::fwrite("B200IDX1", 1, 8, f) == 8 && std::fwrite(&dim, 4, 1, f) == 1 && std::fwrite(&n, 8, 1, f) == 1;
+    const int64_t rows_per_chunk = (int64_t(32) << 20) / (dim * 4);
+    std::unique_ptr<float[]> buf(new float[static_cast<size_t>(rows_per_chunk) * dim]);
+    int rc = B200_EMBED_OK;
+    for (int64_t r = 0; ok && r < n; r += rows_per_chunk) {
+        const int64_t m = n - r < rows_per_chunk ? n - r : rows_per_chunk;
+        const cudaError_t e = cudaMemcpy(buf.get(), ix->vecs + r * dim, static_cast<size_t>(m) * dim * 4, cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) { rc = cuda_fail(e, "cudaMemcpy (index save)"); break; }
+        ok = std::fwrite(buf.get(), 4, static_cast<size_t>(m) * dim, f) == static_cast<size_t>(m) * dim;
+    }
+    if (std::fclose(f) != 0) ok = false;
+    if (rc) return rc;
+    return ok ? B200_EMBED_OK : fail(B200_EMBED_ERR_IO, std::string("short write to ") + path);
+}
+
+int32_t b200_index_load(const char* path, int32_t device, b200_index** out) {
+    if (!path || !out) return fail(B200_EMBED_ERR_INVALID_ARG, "bad argument");
+    *out = nullptr;
+    FILE* f = std::fopen(path, "rb");
+    if (!f) return fail(B200_EMBED_ERR_IO, std::string("cannot open ") + path);
+    char magic[8];
+    int32_t dim = 0;
+    int64_t n = 0;
+    if (std::fread(magic, 1, 8, f) != 8 || std::memcmp(magic, "B200IDX1", 8) != 0 || std::fread(&dim, 4, 1, f) != 1 ||
+        std::fread(&n, 8, 1, f) != 1 || n < 0) {
+        std::fclose(f);
+        return fail(B200_EMBED_ERR_IO, std::string(path) + " is not an index file");
+    }
+    b200_index* ix = nullptr;
+    int rc = b200_index_create(dim, n, device, &ix);
+    if (rc) { std::fclose(f); return rc; }
+    {
+        DevGuard guard(device);
+        const int64_t rows_per_chunk = (int64_t(32) << 20) / (dim * 4);
+        std::unique_ptr<float[]> buf(new float[static_cast<size_t>(rows_per_chunk) * dim]);
+        for (int64_t r = 0; r < n; r += rows_per_chunk) {
+            const int64_t m = n - r < rows_per_chunk ? n - r : rows_per_chunk;
+            if (std::fread(buf.get(), 4, static_cast<size_t>(m) * dim, f) != static_cast<size_t>(m) * dim) {
+                rc = fail(B200_EMBED_ERR_IO, std::string(path) + " is truncated");
+                break;
+            }
+            // rows are stored normalised: copied as they are, bit for bit
+            const cudaError_t e = cudaMemcpy(ix->vecs + r * dim, buf.get(), static_cast<size_t>(m) * dim * 4, cudaMemcpyHostToDevice);
+            if (e != cudaSuccess) { rc = cuda_fail(e, "cudaMemcpy (index load)"); break; }
+        }
+    }
+    std::fclose(f);
+    if (rc) { b200_index_destroy(ix); return rc; }
+    ix->n = n;
+    *out = ix;
+    return B200_EMBED_OK;
+}
 
 }  // extern "C"

@@ -312,6 +312,11 @@ int32_t b200_index_search(b200_index* ix, const float* queries, int32_t q, int32
                           float* scores_out);
 /* Device time of the scan kernel(s) of the last search on this index, in ms (CUDA events on the index's stream). */
 float b200_index_last_scan_ms(const b200_index* ix);
+/* The index as a file and back (the Qdrant collection of the reference is persistent; this is how a restarted service
+ * avoids embedding its corpus again): the normalised rows, bit for bit, so a loaded index answers exactly like the saved
+ * one. B200_EMBED_ERR_IO when the file cannot be written / read or is not an index file. */
+int32_t b200_index_save(b200_index* ix, const char* path);
+int32_t b200_index_load(const char* path, int32_t device, b200_index** out);
 
 #ifdef __cplusplus
 }

@@ -1,5 +1,7 @@
 """f4: the resident cosine index (b200_index_*) against oracle/search_oracle.py - the exact answer Qdrant's
 Distance::Cosine search gives (vector_memory_service/src/main.rs:34-37, :261-286)."""
+import os
+
 import numpy as np
 import pytest
 
@@ -136,3 +138,27 @@ def test_selection_with_many_survivors_falls_back_to_the_full_sort(pkg, built):
     want_ids, want_sc = search_oracle.search(vectors, q, k)
     assert np.array_equal(ids, want_ids)
     assert np.abs(scores - want_sc).max() <= 2e-6
+
+
+def test_save_and_load_give_the_same_answers(pkg, built, tmp_path):
+    rng = np.random.default_rng(4)
+    vectors = rng.standard_normal((30000, 256)).astype(np.float32)
+    queries = rng.standard_normal((3, 256)).astype(np.float32)
+    path = str(tmp_path / "corpus.b200idx")
+    with pkg.abi.Index(256) as ix:
+        ix.add(vectors)
+        want = ix.search(queries, 20)
+        ix.save(path)
+    assert os.path.getsize(path) == 8 + 4 + 8 + vectors.size * 4
+    with pkg.abi.Index.load(path) as ix2:
+        assert len(ix2) == 30000 and ix2.dim == 256
+        got = ix2.search(queries, 20)
+        assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])  # bit for bit
+        ix2.add(vectors[:5])  # a loaded index keeps growing
+        assert len(ix2) == 30005
+    with open(path, "r+b") as f:
+        f.truncate(1000)
+    with pytest.raises(pkg.abi.B200EmbedError, match="truncated"):
+        pkg.abi.Index.load(path)
+    with pytest.raises(pkg.abi.B200EmbedError, match="cannot open"):
+        pkg.abi.Index.load(str(tmp_path / "missing"))
