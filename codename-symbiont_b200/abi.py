@@ -89,6 +89,8 @@ _SIGNATURES = {
     "b200_index_add_device": (C.c_int32, [_P, _P, C.c_int64]),
     "b200_index_search": (C.c_int32, [_P, _P, C.c_int32, C.c_int32, _P, _P]),
     "b200_index_last_scan_ms": (C.c_float, [_P]),
+    "b200_index_enable_prescan": (C.c_int32, [_P]),
+    "b200_index_exact_fallbacks": (C.c_int64, [_P]),
     "b200_index_save": (C.c_int32, [_P, C.c_char_p]),
     "b200_index_load": (C.c_int32, [C.c_char_p, C.c_int32, C.POINTER(_P)]),
     "b200_ingest_last_error": (C.c_char_p, []),
@@ -350,6 +352,14 @@ class Index:
     @property
     def last_scan_ms(self) -> float:
         return float(load_library().b200_index_last_scan_ms(self._h))
+
+    def enable_prescan(self) -> None:
+        """Keep a bf16 copy of the rows and search in two stages (same answers, half the scan bytes)."""
+        self._check(load_library().b200_index_enable_prescan(self._h))
+
+    @property
+    def exact_fallbacks(self) -> int:
+        return int(load_library().b200_index_exact_fallbacks(self._h))
 
     def save(self, path: str) -> None:
         self._check(load_library().b200_index_save(self._h, os.fsencode(path)))

@@ -312,6 +312,14 @@ int32_t b200_index_search(b200_index* ix, const float* queries, int32_t q, int32
                           float* scores_out);
 /* Device time of the scan kernel(s) of the last search on this index, in ms (CUDA events on the index's stream). */
 float b200_index_last_scan_ms(const b200_index* ix);
+/* Optional: keep a bf16 copy of the rows (+50 % memory) and answer single-query searches with top_k <= 64 in two stages
+ * (the case of the reference: one query per request; other calls keep the one-stage f32 scan): the scan reads the
+ * copy (half the bytes), the best max(32, 4 top_k) candidates are rescored from the f32 rows. Rounding a unit row to
+ * bf16 moves a score by at most 2^-8, so a candidate list whose last approximate score lies more than 2^-7 below the
+ * top_k-th provably holds the whole answer; otherwise the search is repeated on the f32 matrix
+ * (b200_index_exact_fallbacks counts those). Ids and scores are the same bits as without the copy. */
+int32_t b200_index_enable_prescan(b200_index* ix);
+int64_t b200_index_exact_fallbacks(const b200_index* ix);
 /* The index as a file and back (the Qdrant collection of the reference is persistent; this is how a restarted service
  * avoids embedding its corpus again): the normalised rows, bit for bit, so a loaded index answers exactly like the saved
  * one. B200_EMBED_ERR_IO when the file cannot be written / read or is not an index file. */

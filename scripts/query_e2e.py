@@ -34,8 +34,11 @@ def once():
     vec = emb.forward(ids, mask, tt); t.append(time.perf_counter())
     hit_ids, scores = ix.search(vec, 10); t.append(time.perf_counter())
     return np.diff(t)
-for _ in range(20): once()
-ts = np.array([once() for _ in range(200)])
-med = np.median(ts, axis=0) * 1e3
-print(f"index {n} x {shape.hidden_size}: tokenise {med[0]:.3f} ms, embed {med[1]:.3f} ms, search top-10 {med[2]:.3f} ms, "
-      f"total {np.median(ts.sum(1)) * 1e3:.3f} ms (p90 {np.percentile(ts.sum(1), 90) * 1e3:.3f} ms)")
+for stage in ("one-stage f32 scan", "two-stage (bf16 copy)"):
+  if stage.startswith("two"):
+      ix.enable_prescan()
+  for _ in range(20): once()
+  ts = np.array([once() for _ in range(200)])
+  med = np.median(ts, axis=0) * 1e3
+  print(f"{stage}: index {n} x {shape.hidden_size}: tokenise {med[0]:.3f} ms, embed {med[1]:.3f} ms, search top-10 {med[2]:.3f} ms, "
+        f"total {np.median(ts.sum(1)) * 1e3:.3f} ms (p90 {np.percentile(ts.sum(1), 90) * 1e3:.3f} ms)")

@@ -162,3 +162,43 @@ def test_save_and_load_give_the_same_answers(pkg, built, tmp_path):
         pkg.abi.Index.load(path)
     with pytest.raises(pkg.abi.B200EmbedError, match="cannot open"):
         pkg.abi.Index.load(str(tmp_path / "missing"))
+
+
+@pytest.mark.parametrize("dim,n,k", [(384, 120000, 10), (768, 50000, 64), (128, 9000, 256), (256, 300, 5), (1024, 20000, 1)])
+def test_two_stage_search_gives_the_same_bits(pkg, built, dim, n, k):
+    """With the bf16 copy enabled the scan reads half the bytes and the candidates are rescored from the f32 rows: ids and
+    scores must be the very same bits as the one-stage search, for rows added before and after enabling it."""
+    rng = np.random.default_rng(dim + k)
+    vectors = rng.standard_normal((n, dim)).astype(np.float32)
+    queries = rng.standard_normal((5, dim)).astype(np.float32)
+    with pkg.abi.Index(dim) as plain, pkg.abi.Index(dim) as fast:
+        plain.add(vectors)
+        fast.add(vectors[: n // 3])
+        fast.enable_prescan()
+        fast.add(vectors[n // 3:])  # grows the matrix and its copy
+        want = plain.search(queries, k)
+        got = fast.search(queries, k)  # 5 queries: a pass of four (one stage) and a pass of one (two stages if k <= 64)
+        assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
+        for i in range(5):  # one query per call, like the reference's search requests
+            one = fast.search(queries[i], k)
+            assert np.array_equal(one[0][0], want[0][i]) and np.array_equal(one[1][0], want[1][i])
+        assert fast.exact_fallbacks == 0
+    _check(got[0], got[1], vectors, queries, k)
+
+
+def test_two_stage_search_falls_back_when_scores_crowd(pkg, built):
+    """Thousands of rows within 1e-3 of each other: the bf16 stage cannot separate them, the bound says so, and the search
+    is repeated on the f32 matrix - still the exact answer."""
+    dim, n, k = 256, 20000, 10
+    rng = np.random.default_rng(3)
+    base = rng.standard_normal(dim).astype(np.float32)
+    vectors = (base[None, :] + 1e-4 * rng.standard_normal((n, dim))).astype(np.float32)
+    q = base[None, :].copy()
+    with pkg.abi.Index(dim) as plain, pkg.abi.Index(dim) as fast:
+        plain.add(vectors)
+        fast.add(vectors)
+        fast.enable_prescan()
+        want = plain.search(q, k)
+        got = fast.search(q, k)
+        assert fast.exact_fallbacks == 1
+    assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
