@@ -14,6 +14,8 @@
 //   normalize_rows   one warp per vector, in place (insert and query preparation)
 //   scan             one warp per block of 32 consecutive vectors, query fragments in registers, fp32 FMA, coalesced loads
 //                    (512 B per warp instruction, streaming), one coalesced 128 B score store per block
+//   rescore          exact f32 scores of a short candidate list (second stage when the optional bf16 copy of the rows serves
+//                    the scan: same lane layout and operation order as scan, so the bits agree)
 //   topk_filter /    blocks of 4096 candidates: the k best of each kept (k <= 256: threshold from the 256 per-thread bests, then
 //   topk_level       a sort of the few survivors; above: a bitonic sort of the block), ties -> lower id; applied level by
 //                    level until one block holds the answer
