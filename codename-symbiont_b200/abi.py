@@ -80,6 +80,12 @@ _SIGNATURES = {
                                                           C.c_uint64, C.c_int32, _P, C.c_int64]),
     "b200_json_query_embedding_result": (C.c_int64, [C.c_char_p, _P, C.c_int32, C.c_char_p, C.c_char_p, _P, C.c_int64]),
     "b200_json_format_f32": (C.c_int32, [C.c_float, _P]),
+    "b200_json_envelope": (C.c_int64, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_uint64, _P, C.c_int64, C.POINTER(C.c_int64), _P, C.c_int64,
+                                       C.POINTER(C.c_int64)]),
+    "b200_json_sentence_items_ranges": (C.c_int64, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P, C.c_int64]),
+    "b200_pipeline_last_error": (C.c_char_p, []),
+    "b200_pipeline_text_to_json": (C.c_int32, [_P, _P, _P, C.c_int64, C.c_char_p, C.c_char_p, C.c_char_p, C.c_uint64, C.c_int32, C.c_uint32,
+                                               _P, C.c_int64, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "b200_index_last_error": (C.c_char_p, []),
     "b200_index_create": (C.c_int32, [C.c_int32, C.c_int64, C.c_int32, C.POINTER(_P)]),
     "b200_index_destroy": (None, [_P]),
@@ -111,7 +117,7 @@ def declared_symbols() -> list:
     with open(HEADER_PATH) as f:
         text = f.read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
-    return sorted(set(re.findall(r"\b(b200_(?:embed|op|json|ingest|index)_[a-z0-9_]+)\s*\(", text)))
+    return sorted(set(re.findall(r"\b(b200_(?:embed|op|json|ingest|index|pipeline)_[a-z0-9_]+)\s*\(", text)))
 
 
 def load_library():
@@ -371,6 +377,24 @@ class Index:
         cls._check(load_library().b200_index_load(os.fsencode(path), device, C.byref(self._h)))
         self.dim = int(load_library().b200_index_dim(self._h))
         return self
+
+
+def pipeline_text_to_json(embedder, ingest, raw_text: str, original_id: str, source_url: str, model_name: str, timestamp_ms: int,
+                          chunk_sentences: int = 0, flags: int = 0):
+    """b200_pipeline_text_to_json: raw text -> (JSON bytes as a uint8 array, number of sentences), stages overlapped."""
+    lib = load_library()
+    raw = raw_text.encode("utf-8")
+    out_len, n = C.c_int64(0), C.c_int64(0)
+    args = (embedder.h, ingest._h, raw, len(raw), original_id.encode(), source_url.encode(), model_name.encode(), int(timestamp_ms),
+            int(chunk_sentences), int(flags))
+    rc = lib.b200_pipeline_text_to_json(*args, None, 0, C.byref(out_len), C.byref(n))  # learns the capacity to provide
+    if out_len.value <= 0:
+        raise B200EmbedError(rc, lib.b200_pipeline_last_error().decode(errors="replace"))
+    buf = np.empty(out_len.value, dtype=np.uint8)
+    rc = lib.b200_pipeline_text_to_json(*args, buf.ctypes.data, buf.size, C.byref(out_len), C.byref(n))
+    if rc != 0:
+        raise B200EmbedError(rc, lib.b200_pipeline_last_error().decode(errors="replace"))
+    return buf[:out_len.value], int(n.value)
 
 
 def host_alloc(shape, dtype) -> np.ndarray:

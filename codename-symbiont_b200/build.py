@@ -10,7 +10,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libb200_embed.so")
 OBJ_DIR = os.path.join(HERE, "build")
-SOURCES = ["engine.cu", "gemm_tc.cu", "ffn_fused.cu", "attention.cu", "attention_tc.cu", "qkv_attention.cu", "elementwise.cu", "fp32_ref.cu", "weights_io.cpp", "json_out.cpp", "ingest.cpp", "search.cu"]
+SOURCES = ["engine.cu", "gemm_tc.cu", "ffn_fused.cu", "attention.cu", "attention_tc.cu", "qkv_attention.cu", "elementwise.cu", "fp32_ref.cu", "weights_io.cpp", "json_out.cpp", "ingest.cpp", "search.cu", "pipeline.cpp"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-std=c++17", "-O3", "-lineinfo",
               "-Xcompiler", "-fPIC,-Wall,-Wno-unused-function", "--expt-relaxed-constexpr"]
 

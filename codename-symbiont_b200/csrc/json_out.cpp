@@ -307,66 +307,89 @@ struct Sentences {  // either NUL-terminated strings or byte ranges of one text
 
 // The document is produced in slices: every thread formats a contiguous run of sentences into its own (uninitialised)
 // buffer sized by the upper bounds above, then copies it to its final offset in `out`; only the sizes are exchanged.
-int64_t text_with_embeddings(const char* original_id, const char* source_url, const Sentences& sn, const float* embeddings,
-                             int32_t n, int32_t dim, const char* model_name, uint64_t timestamp_ms, int32_t threads, char* out,
-                             int64_t out_cap) {
+// The items `{"sentence_text":..,"embedding":[..]}` of sentences [0, n), comma-separated, formatted in slices: every thread
+// formats a contiguous run of sentences into its own (uninitialised) buffer sized by the upper bounds above. `first`
+// tells whether item 0 is the first of its array (no comma in front).
+struct ItemParts {
+    int t = 1;
+    std::vector<std::unique_ptr<char[]>> parts;
+    std::vector<size_t> len;
+    size_t total = 0;
+    template <typename F>
+    void run(F&& fn) const {
+        if (t <= 1) { fn(0); return; }
+        std::vector<std::thread> pool;
+        for (int k = 0; k < t; ++k) pool.emplace_back(fn, k);
+        for (auto& th : pool) th.join();
+    }
+    void copy_to(char* out) const {  // the slices to their final offsets, in parallel
+        std::vector<size_t> off(static_cast<size_t>(t) + 1, 0);
+        for (int k = 0; k < t; ++k) off[static_cast<size_t>(k) + 1] = off[static_cast<size_t>(k)] + len[static_cast<size_t>(k)];
+        run([&](int k) { std::memcpy(out + off[static_cast<size_t>(k)], parts[static_cast<size_t>(k)].get(), len[static_cast<size_t>(k)]); });
+    }
+};
+
+void format_items(const Sentences& sn, const float* embeddings, int32_t n, int32_t dim, int32_t threads, bool first, ItemParts* ip) {
     int t = threads > 0 ? threads : static_cast<int>(std::thread::hardware_concurrency());
     if (t < 1) t = 1;
     if (t > n / 8) t = n / 8 > 0 ? n / 8 : 1;
-    std::vector<std::unique_ptr<char[]>> parts(static_cast<size_t>(t));
-    std::vector<size_t> part_len(static_cast<size_t>(t), 0);
-    auto range = [&](int k, int* lo, int* hi) {
-        *lo = static_cast<int>(static_cast<int64_t>(n) * k / t);
-        *hi = static_cast<int>(static_cast<int64_t>(n) * (k + 1) / t);
-    };
-    auto format_part = [&](int k) {
-        int lo, hi;
-        range(k, &lo, &hi);
+    ip->t = t;
+    ip->parts.resize(static_cast<size_t>(t));
+    ip->len.assign(static_cast<size_t>(t), 0);
+    ip->run([&](int k) {
+        const int lo = static_cast<int>(static_cast<int64_t>(n) * k / t), hi = static_cast<int>(static_cast<int64_t>(n) * (k + 1) / t);
         size_t bound = 0;
         for (int i = lo; i < hi; ++i) bound += string_bound(sn.len(i)) + vector_bound(dim) + 40;
-        parts[static_cast<size_t>(k)].reset(new char[bound + 1]);
-        char* p = parts[static_cast<size_t>(k)].get();
+        ip->parts[static_cast<size_t>(k)].reset(new char[bound + 1]);
+        char* p = ip->parts[static_cast<size_t>(k)].get();
         char* const p0 = p;
         for (int i = lo; i < hi; ++i) {
-            if (i) *p++ = ',';
+            if (i || !first) *p++ = ',';
             p = put_lit(p, "{\"sentence_text\":");
             p = put_string(p, sn.ptr(i), sn.len(i));
             p = put_lit(p, ",\"embedding\":");
             p = put_vector(p, embeddings + static_cast<size_t>(i) * dim, dim);
             *p++ = '}';
         }
-        part_len[static_cast<size_t>(k)] = static_cast<size_t>(p - p0);
-    };
-    auto run = [&](auto&& fn) {
-        if (t <= 1) { fn(0); return; }
-        std::vector<std::thread> pool;
-        for (int k = 0; k < t; ++k) pool.emplace_back(fn, k);
-        for (auto& th : pool) th.join();
-    };
-    run(format_part);
-    std::vector<char> head(string_bound(std::strlen(original_id ? original_id : "")) + string_bound(std::strlen(source_url ? source_url : "")) + 64);
-    char* h = head.data();
+        ip->len[static_cast<size_t>(k)] = static_cast<size_t>(p - p0);
+    });
+    ip->total = 0;
+    for (size_t l : ip->len) ip->total += l;
+}
+
+// `{"original_id":..,"source_url":..,"embeddings_data":[` and `],"model_name":..,"timestamp_ms":..}`
+void envelope(const char* original_id, const char* source_url, const char* model_name, uint64_t timestamp_ms, std::string* head,
+              std::string* tail) {
+    std::vector<char> hb(string_bound(std::strlen(original_id ? original_id : "")) + string_bound(std::strlen(source_url ? source_url : "")) + 64);
+    char* h = hb.data();
     h = put_lit(h, "{\"original_id\":");
     h = put_cstr(h, original_id);
     h = put_lit(h, ",\"source_url\":");
     h = put_cstr(h, source_url);
     h = put_lit(h, ",\"embeddings_data\":[");
-    const size_t head_len = static_cast<size_t>(h - head.data());
-    std::vector<char> tail(string_bound(std::strlen(model_name ? model_name : "")) + 64);
-    char* q = tail.data();
+    head->assign(hb.data(), static_cast<size_t>(h - hb.data()));
+    std::vector<char> tb(string_bound(std::strlen(model_name ? model_name : "")) + 64);
+    char* q = tb.data();
     q = put_lit(q, "],\"model_name\":");
     q = put_cstr(q, model_name);
     q = put_lit(q, ",\"timestamp_ms\":");
     q = std::to_chars(q, q + 24, timestamp_ms).ptr;
     *q++ = '}';
-    const size_t tail_len = static_cast<size_t>(q - tail.data());
-    std::vector<size_t> off(static_cast<size_t>(t) + 1, head_len);
-    for (int k = 0; k < t; ++k) off[static_cast<size_t>(k) + 1] = off[static_cast<size_t>(k)] + part_len[static_cast<size_t>(k)];
-    const int64_t total = static_cast<int64_t>(off[static_cast<size_t>(t)] + tail_len);
+    tail->assign(tb.data(), static_cast<size_t>(q - tb.data()));
+}
+
+int64_t text_with_embeddings(const char* original_id, const char* source_url, const Sentences& sn, const float* embeddings,
+                             int32_t n, int32_t dim, const char* model_name, uint64_t timestamp_ms, int32_t threads, char* out,
+                             int64_t out_cap) {
+    ItemParts ip;
+    format_items(sn, embeddings, n, dim, threads, true, &ip);
+    std::string head, tail;
+    envelope(original_id, source_url, model_name, timestamp_ms, &head, &tail);
+    const int64_t total = static_cast<int64_t>(head.size() + ip.total + tail.size());
     if (out != nullptr && out_cap >= total) {
-        std::memcpy(out, head.data(), head_len);
-        run([&](int k) { std::memcpy(out + off[static_cast<size_t>(k)], parts[static_cast<size_t>(k)].get(), part_len[static_cast<size_t>(k)]); });
-        std::memcpy(out + off[static_cast<size_t>(t)], tail.data(), tail_len);
+        std::memcpy(out, head.data(), head.size());
+        ip.copy_to(out + head.size());
+        std::memcpy(out + head.size() + ip.total, tail.data(), tail.size());
     }
     return total;
 }
@@ -400,6 +423,30 @@ int64_t b200_json_text_with_embeddings_ranges(const char* original_id, const cha
         if (begin[i] < 0 || end[i] < begin[i]) return -1;
     const Sentences sn{nullptr, text, begin, end};
     return text_with_embeddings(original_id, source_url, sn, embeddings, n, dim, model_name, timestamp_ms, threads, out, out_cap);
+}
+
+int64_t b200_json_envelope(const char* original_id, const char* source_url, const char* model_name, uint64_t timestamp_ms,
+                           char* head, int64_t head_cap, int64_t* head_len, char* tail, int64_t tail_cap, int64_t* tail_len) {
+    if (!head_len || !tail_len) return -1;
+    std::string hs, ts;
+    envelope(original_id, source_url, model_name, timestamp_ms, &hs, &ts);
+    *head_len = static_cast<int64_t>(hs.size());
+    *tail_len = static_cast<int64_t>(ts.size());
+    if (head && head_cap >= *head_len) std::memcpy(head, hs.data(), hs.size());
+    if (tail && tail_cap >= *tail_len) std::memcpy(tail, ts.data(), ts.size());
+    return *head_len + *tail_len;
+}
+
+int64_t b200_json_sentence_items_ranges(const char* text, const int64_t* begin, const int64_t* end, const float* embeddings,
+                                        int32_t n, int32_t dim, int32_t first, int32_t threads, char* out, int64_t out_cap) {
+    if (n < 0 || dim < 0 || (n > 0 && (!text || !begin || !end || !embeddings))) return -1;
+    for (int32_t i = 0; i < n; ++i)
+        if (begin[i] < 0 || end[i] < begin[i]) return -1;
+    const Sentences sn{nullptr, text, begin, end};
+    ItemParts ip;
+    format_items(sn, embeddings, n, dim, threads, first != 0, &ip);
+    if (out != nullptr && out_cap >= static_cast<int64_t>(ip.total)) ip.copy_to(out);
+    return static_cast<int64_t>(ip.total);
 }
 
 int64_t b200_json_query_embedding_result(const char* request_id, const float* embedding_or_null, int32_t dim,

@@ -246,6 +246,15 @@ int64_t b200_json_query_embedding_result(const char* request_id, const float* em
                                          int64_t out_cap);
 /* One f32 as serde_json writes it; out24 must hold 24 bytes. Returns the number of characters. */
 int32_t b200_json_format_f32(float value, char* out24);
+/* The same document in pieces, for a caller that formats a long message chunk by chunk (or publishes one message per
+ * chunk under a payload limit): the envelope `{"original_id":..,"source_url":..,"embeddings_data":[` and
+ * `],"model_name":..,"timestamp_ms":..}` (lengths always reported; written when the capacities suffice), and the
+ * comma-separated items of n sentences given as byte ranges (first != 0: no comma in front of the first item). The items
+ * call returns their size and writes them when out_cap suffices: pass n * (17 * dim + 80) + 6 * (text bytes) to be sure. */
+int64_t b200_json_envelope(const char* original_id, const char* source_url, const char* model_name, uint64_t timestamp_ms,
+                           char* head, int64_t head_cap, int64_t* head_len, char* tail, int64_t tail_cap, int64_t* tail_len);
+int64_t b200_json_sentence_items_ranges(const char* text, const int64_t* begin, const int64_t* end, const float* embeddings,
+                                        int32_t n, int32_t dim, int32_t first, int32_t threads, char* out, int64_t out_cap);
 
 /* -- ingest front-end: raw text -> sentences -> token arrays (host only, no GPU involved) ------------------
  * What runs on the host before the embedding call. Errors of these entries are reported through
@@ -325,6 +334,21 @@ int64_t b200_index_exact_fallbacks(const b200_index* ix);
  * one. B200_EMBED_ERR_IO when the file cannot be written / read or is not an index file. */
 int32_t b200_index_save(b200_index* ix, const char* path);
 int32_t b200_index_load(const char* path, int32_t device, b200_index** out);
+
+/* -- raw text in, JSON payload out (f1 -> path -> f3 in one call) ---------------------------------------------------
+ * What process_raw_text_message and the publish of its result do for one RawTextMessage
+ * (preprocessing_service/src/main.rs:28-142): clean and split the text, tokenise, embed, write the
+ * TextWithEmbeddingsMessage JSON - with the three stages overlapped over chunks of `chunk_sentences` sentences (0 = 8192):
+ * the calling thread tokenises chunk c + 1 while a second thread has the GPU embed chunk c and a third formats chunk c - 1
+ * into `out`. Needs a WordPiece b200_ingest handle. out_cap must cover an upper bound that depends on the number of
+ * sentences; when it does not (or out is NULL) the call returns B200_EMBED_ERR_INVALID_ARG with the bound in *out_len
+ * and the sentence count in *n_sentences - allocate and call again. An empty cleaned text is the reference's
+ * "Cleaned text is empty" error. Message of the last failure: b200_pipeline_last_error(). */
+const char* b200_pipeline_last_error(void);
+int32_t b200_pipeline_text_to_json(b200_embed* h, const b200_ingest* t, const char* raw_text, int64_t len,
+                                   const char* original_id, const char* source_url, const char* model_name,
+                                   uint64_t timestamp_ms, int32_t chunk_sentences, uint32_t flags, char* out,
+                                   int64_t out_cap, int64_t* out_len, int64_t* n_sentences);
 
 #ifdef __cplusplus
 }

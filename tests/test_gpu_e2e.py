@@ -365,3 +365,38 @@ def test_graph_replay_is_bit_identical_and_survives_reallocation(pkg, built, mon
         with pytest.raises(pkg.abi.B200EmbedError):
             emb.forward(*bad)
         assert np.array_equal(emb.forward(*small), want_small)
+
+
+def test_pipeline_text_to_json(pkg, built, tmp_path):
+    """b200_pipeline_text_to_json (main.rs:28-142 in one call): with one chunk the document is byte for byte what the
+    separate calls give (split -> packed tokens -> forward_varlen -> JSON); with several overlapped chunks the sentences,
+    the structure and (to the tolerance between two bf16 batch compositions) the vectors are the same."""
+    import json
+    from tokenizers import Tokenizer, models, normalizers, pre_tokenizers, processors
+    shape = pkg.weights.TINY
+    words = "the quick brown fox jumps over lazy dog . ! ? a symbiont reads web pages and embeds sentences ##s ##ing".split()
+    vocab = {w: i for i, w in enumerate(["[PAD]", "[UNK]", "[CLS]", "[SEP]"] + words)}
+    tok = Tokenizer(models.WordPiece(vocab, unk_token="[UNK]"))
+    tok.normalizer = normalizers.BertNormalizer(lowercase=True)
+    tok.pre_tokenizer = pre_tokenizers.BertPreTokenizer()
+    tok.post_processor = processors.TemplateProcessing(single="[CLS] $A [SEP]", special_tokens=[("[CLS]", 2), ("[SEP]", 3)])
+    tok.save(str(tmp_path / "tokenizer.json"))
+    ing = pkg.abi.Ingest(str(tmp_path / "tokenizer.json"))
+    sents = ["The quick brown fox jumps over the lazy dog.", "A symbiont reads web pages!", "Embeds sentences?", "Dogs."]
+    raw = "  ".join(sents[i % 4] for i in range(203)) + " trailing words"
+    with pkg.Embedder.random_init(shape, seed=5) as emb:
+        one, n = pkg.abi.pipeline_text_to_json(emb, ing, raw, "doc-1", "http://x/y", "tiny", 1234, chunk_sentences=100000)
+        cleaned, begin, end = pkg.abi.split_sentences(raw)
+        ids, tt, cu = ing.encode_ranges_packed(cleaned, begin, end, shape.max_position_embeddings)
+        vec = emb.forward_varlen(ids, tt, cu, int(np.diff(cu).max()))
+        want = pkg.abi.json_text_with_embeddings("doc-1", "http://x/y", (cleaned, begin, end), vec, "tiny", 1234)
+        assert n == 204 and one.tobytes() == want
+        many, n2 = pkg.abi.pipeline_text_to_json(emb, ing, raw, "doc-1", "http://x/y", "tiny", 1234, chunk_sentences=32)
+        a, b = json.loads(one.tobytes()), json.loads(many.tobytes())
+        assert n2 == 204 and list(b) == ["original_id", "source_url", "embeddings_data", "model_name", "timestamp_ms"]
+        assert [d["sentence_text"] for d in b["embeddings_data"]] == [d["sentence_text"] for d in a["embeddings_data"]]
+        va = np.array([d["embedding"] for d in a["embeddings_data"]], np.float32)
+        vb = np.array([d["embedding"] for d in b["embeddings_data"]], np.float32)
+        assert np.abs(va - vb).max() <= 4e-3 and cos_rows(va, vb).min() >= 0.9999
+        with pytest.raises(pkg.abi.B200EmbedError, match="Cleaned text is empty"):
+            pkg.abi.pipeline_text_to_json(emb, ing, " \n ", "d", "u", "m", 1)
