@@ -117,3 +117,32 @@ def test_f32_digit_generator_matches_the_cxx_library(tmp_path):
                    check=True, capture_output=True)
     r = subprocess.run([exe, "61"], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and " 0 mismatches" in r.stdout, r.stdout
+
+
+def test_envelope_and_chunked_items_make_the_same_document(abi):
+    """b200_json_envelope + b200_json_sentence_items_ranges (chunked formatting / publishing): head + items of the chunks +
+    tail is byte for byte the document the one-call entry writes."""
+    import ctypes as C
+    lib = abi.load_library()
+    rng = np.random.default_rng(3)
+    sentences = ['One "quoted".', "Two\ttabs?", "three", "Four!"] * 11
+    emb = rng.standard_normal((len(sentences), 64)).astype(np.float32)
+    enc = [s.encode() for s in sentences]
+    text = b"|".join(enc)
+    begin = np.cumsum([0] + [len(e) + 1 for e in enc[:-1]]).astype(np.int64)
+    end = begin + np.array([len(e) for e in enc], dtype=np.int64)
+    whole = abi.json_text_with_embeddings("id", "http://u", (text, begin, end), emb, "model", 99)
+    hl, tl = C.c_int64(0), C.c_int64(0)
+    lib.b200_json_envelope(b"id", b"http://u", b"model", 99, None, 0, C.byref(hl), None, 0, C.byref(tl))
+    head, tail = C.create_string_buffer(hl.value), C.create_string_buffer(tl.value)
+    lib.b200_json_envelope(b"id", b"http://u", b"model", 99, C.cast(head, C.c_void_p), hl.value, C.byref(hl), C.cast(tail, C.c_void_p), tl.value, C.byref(tl))
+    doc = head.raw[:hl.value]
+    for lo, hi in ((0, 17), (17, 18), (18, len(sentences))):
+        b, e, v = np.ascontiguousarray(begin[lo:hi]), np.ascontiguousarray(end[lo:hi]), np.ascontiguousarray(emb[lo:hi])
+        need = lib.b200_json_sentence_items_ranges(C.c_char_p(text), b.ctypes.data, e.ctypes.data, v.ctypes.data, hi - lo, 64, int(lo == 0), 2, None, 0)
+        buf = C.create_string_buffer(need)
+        got = lib.b200_json_sentence_items_ranges(C.c_char_p(text), b.ctypes.data, e.ctypes.data, v.ctypes.data, hi - lo, 64, int(lo == 0), 3,
+                                                  C.cast(buf, C.c_void_p), need)
+        assert got == need
+        doc += buf.raw[:need]
+    assert doc + tail.raw[:tl.value] == whole
