@@ -149,7 +149,7 @@ __global__ void scan_lengths_kernel(const int* __restrict__ lens, int batch, int
 // most one tile per segment is cut short) by one thread each; counts are scanned in shared memory by the single
 // block, which then writes the compacted list. seg_off: [ceil(batch / 128) + 1] scratch (callers size it for segments of 32).
 constexpr int PACK_SEG = 128;  // 4484 tiles for 16 384 corpus-length sentences with 32, 4351 with 128, 4310 without segments
-__device__ __forceinline__ int pack_segment(const int* __restrict__ cu, int b0, int b1, int cap, int* __restrict__ out) {
+__device__ __forceinline__ int pack_segment(const int* cu, int b0, int b1, int cap, int* __restrict__ out) {
     int n = 0, first = b0;
     int base = cu[b0];
     for (int b = b0; b < b1; ++b) {
@@ -164,12 +164,20 @@ __device__ __forceinline__ int pack_segment(const int* __restrict__ cu, int b0, 
     if (out) out[n] = first;
     return n + 1;
 }
-__global__ void pack_tiles_kernel(const int* __restrict__ cu, int batch, int cap, int* __restrict__ seg_off,
+__global__ void pack_tiles_kernel(const int* cu, int batch, int cap, int* __restrict__ seg_off,
                                   int* __restrict__ tile_first, int* __restrict__ n_tiles) {
     __shared__ int warp_tot[32];
     __shared__ int carry;
+    // the sequential walks below read cu twice, one dependent load after the other: for the batch sizes the engine sends
+    // (<= 8192 sentences per call) the block first copies it into shared memory with coalesced loads
+    constexpr int STAGE_MAX = 8192;
+    __shared__ int s_cu[STAGE_MAX + 1];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int nseg = (batch + PACK_SEG - 1) / PACK_SEG;
+    if (batch <= STAGE_MAX) {
+        for (int i = threadIdx.x; i <= batch; i += blockDim.x) s_cu[i] = cu[i];
+        cu = s_cu;
+    }
     if (threadIdx.x == 0) { carry = 0; seg_off[0] = 0; }
     __syncthreads();
     for (int base = 0; base < nseg; base += blockDim.x) {  // count tiles per segment, exclusive scan into seg_off
