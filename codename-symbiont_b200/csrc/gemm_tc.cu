@@ -560,6 +560,40 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
+
+// True when every byte of [ptr, ptr + bytes) is plain device memory of the CURRENT device. The range is walked
+// allocation by allocation (cuMemGetAddressRange gives the extent of the allocation or mapping that holds an address), so
+// a virtual range stitched together from several mappings, one of them another GPU's memory, is refused as well; so is
+// anything the driver cannot describe (IPC / managed / host mappings, ranges with holes).
+bool operand_is_local_device_memory(const void* ptr, size_t bytes) {
+    using range_fn_t = CUresult (*)(CUdeviceptr*, size_t*, CUdeviceptr);
+    static range_fn_t range_fn = [] {
+        void* f = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuMemGetAddressRange", &f, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            f = nullptr;
+        return reinterpret_cast<range_fn_t>(f);
+    }();
+    int dev = -1;
+    if (!ptr || bytes == 0 || !range_fn || cudaGetDevice(&dev) != cudaSuccess) return false;
+    const uintptr_t end = reinterpret_cast<uintptr_t>(ptr) + bytes;
+    uintptr_t cur = reinterpret_cast<uintptr_t>(ptr);
+    for (int pieces = 0; cur < end; ++pieces) {
+        cudaPointerAttributes pa{};
+        CUdeviceptr base = 0;
+        size_t size = 0;
+        if (pieces >= 64 || cudaPointerGetAttributes(&pa, reinterpret_cast<const void*>(cur)) != cudaSuccess ||
+            pa.type != cudaMemoryTypeDevice || pa.device != dev ||
+            range_fn(&base, &size, static_cast<CUdeviceptr>(cur)) != CUDA_SUCCESS || size == 0 ||
+            static_cast<uintptr_t>(base) > cur) {
+            cudaGetLastError();
+            return false;
+        }
+        cur = static_cast<uintptr_t>(base) + size;
+    }
+    return true;
+}
 template <int BLOCK_N, int EPI, typename OutT, int CL = 1, bool PAIR = false, int RING = 2>
 cudaError_t launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms) {
     constexpr bool OUT_F32 = sizeof(OutT) == 4;
@@ -567,15 +601,9 @@ cudaError_t launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms) {
     alignas(64) CUtensorMap ta, tb, tc, tcl, tr, trl;
     if constexpr (CL > 1) {
         // The A tile is multicast inside the cluster. TMA multicast loads here read only this GPU's memory, since on B200 a
-        // TMA multicast load from another GPU's memory hung the GPU: an operand that is not plain device memory of the
-        // current device (a peer allocation, an IPC or managed mapping) is refused before anything is launched.
-        cudaPointerAttributes pa{};
-        int dev = -1;
-        if (cudaGetDevice(&dev) != cudaSuccess || cudaPointerGetAttributes(&pa, a.a) != cudaSuccess ||
-            pa.type != cudaMemoryTypeDevice || pa.device != dev) {
-            cudaGetLastError();
-            return cudaErrorInvalidDevicePointer;
-        }
+        // TMA multicast load from another GPU's memory hung the GPU. The tensor map of a multicast load must therefore
+        // cover this GPU's memory alone: every byte of the operand is checked, not only its first one.
+        if (!operand_is_local_device_memory(a.a, static_cast<size_t>(a.m) * a.k * 2)) return cudaErrorInvalidDevicePointer;
     }
     if (!make_tmap(&ta, a.a, a.m, a.k, BLOCK_K, BLOCK_M / (CL > 1 ? CL : 1), false, CU_TENSOR_MAP_SWIZZLE_128B))
         return cudaErrorInvalidValue;
