@@ -23,6 +23,8 @@ HEADER_PATH = os.path.join(HERE, "..", "include", "b200_embed.h")
 NOALLOC_MAX_ELEMS = 1 << 20  # B200_OP_NOALLOC_MAX_ELEMS
 FLAG_NORMALIZE = 1
 FLAG_FP32 = 2
+OPERANDS_DEFAULT, OPERANDS_BF16, OPERANDS_FP16 = 0, 1, 2  # B200_EMBED_OPERANDS_*
+OPERAND_NAMES = {"default": 0, "bf16": 1, "f16": 2, "fp16": 2}
 ERR_NAMES = {0: "OK", -1: "INVALID_ARG", -2: "CUDA", -3: "OOM", -4: "UNSUPPORTED_SHAPE", -5: "NO_DEVICE", -6: "IO"}
 KIND_NAMES = ["lengths", "embed_ln", "gemm_qkv", "attention", "gemm_attn_out", "gemm_ffn1", "gemm_ffn2", "add_ln",
               "pool", "ffn_fused", "qkv_attention"]
@@ -39,7 +41,7 @@ class Config(C.Structure):
     _fields_ = [("vocab_size", C.c_int32), ("hidden_size", C.c_int32), ("num_hidden_layers", C.c_int32),
                 ("num_attention_heads", C.c_int32), ("intermediate_size", C.c_int32),
                 ("max_position_embeddings", C.c_int32), ("type_vocab_size", C.c_int32), ("hidden_act", C.c_int32),
-                ("layer_norm_eps", C.c_float), ("max_tokens_per_launch", C.c_int32)]
+                ("layer_norm_eps", C.c_float), ("max_tokens_per_launch", C.c_int32), ("operand_format", C.c_int32)]
 
 
 class KindStats(C.Structure):
@@ -52,6 +54,7 @@ _SIGNATURES = {
     "b200_embed_destroy": (None, [_P]),
     "b200_embed_hidden_size": (C.c_int32, [_P]),
     "b200_embed_max_positions": (C.c_int32, [_P]),
+    "b200_embed_operand_format": (C.c_int32, [_P]),
     "b200_embed_last_error": (C.c_char_p, []),
     "b200_embed_forward": (C.c_int32, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_uint32, _P]),
     "b200_embed_forward_varlen": (C.c_int32, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_uint32, _P]),
@@ -74,6 +77,7 @@ _SIGNATURES = {
                                           _P]),
     "b200_op_mean_pool": (C.c_int32, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, _P, _P]),
     "b200_op_gemm_bf16": (C.c_int32, [_P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P, _P]),
+    "b200_op_gemm_f16": (C.c_int32, [_P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P, _P]),
     "b200_json_text_with_embeddings": (C.c_int64, [C.c_char_p, C.c_char_p, _P, _P, C.c_int32, C.c_int32, C.c_char_p,
                                                    C.c_uint64, C.c_int32, _P, C.c_int64]),
     "b200_json_text_with_embeddings_ranges": (C.c_int64, [C.c_char_p, C.c_char_p, _P, _P, _P, _P, C.c_int32, C.c_int32, C.c_char_p,
@@ -422,12 +426,14 @@ class Embedder:
     """Owns one b200_embed handle (one model replica on one GPU)."""
 
     def __init__(self, shape: W.BertShape, safetensors_path: str | None = None, seed: int = 1234, device: int = 0,
-                 max_tokens_per_launch: int = 0):
+                 max_tokens_per_launch: int = 0, operands: str | int = "default"):
+        """operands: "f16" (the default: IEEE fp16 tensor-core operands) or "bf16" (cfg.operand_format)."""
         self.lib = load_library()
         self.shape = shape
+        fmt = OPERAND_NAMES[operands] if isinstance(operands, str) else int(operands)
         cfg = Config(shape.vocab_size, shape.hidden_size, shape.num_hidden_layers, shape.num_attention_heads,
                      shape.intermediate_size, shape.max_position_embeddings, shape.type_vocab_size,
-                     shape.hidden_act, shape.layer_norm_eps, max_tokens_per_launch)
+                     shape.hidden_act, shape.layer_norm_eps, max_tokens_per_launch, fmt)
         h = _P()
         path = safetensors_path.encode() if safetensors_path else None
         _check(self.lib.b200_embed_create(C.byref(cfg), path, seed, device, C.byref(h)))
@@ -462,6 +468,11 @@ class Embedder:
     @property
     def max_positions(self) -> int:
         return self.lib.b200_embed_max_positions(self.h)
+
+    @property
+    def operands(self) -> str:
+        """"f16" or "bf16": the 16-bit format the handle computes in (and its b200_op_* entries take tensors in)."""
+        return "f16" if self.lib.b200_embed_operand_format(self.h) == OPERANDS_FP16 else "bf16"
 
     def kernel_launches(self) -> int:
         return int(self.lib.b200_embed_kernel_launches(self.h))
@@ -566,3 +577,7 @@ class Embedder:
 
 def op_gemm_bf16(d_a, d_b, d_bias, m, n, k, act, block_n, d_c, stream=0):
     _check(load_library().b200_op_gemm_bf16(d_a, d_b, d_bias, m, n, k, act, block_n, d_c, stream or None))
+
+
+def op_gemm_f16(d_a, d_b, d_bias, m, n, k, act, block_n, d_c, stream=0):
+    _check(load_library().b200_op_gemm_f16(d_a, d_b, d_bias, m, n, k, act, block_n, d_c, stream or None))

@@ -10,7 +10,10 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libb200_embed.so")
 OBJ_DIR = os.path.join(HERE, "build")
-SOURCES = ["engine.cu", "gemm_tc.cu", "ffn_fused.cu", "attention.cu", "attention_tc.cu", "qkv_attention.cu", "elementwise.cu", "fp32_ref.cu", "weights_io.cpp", "json_out.cpp", "ingest.cpp", "search.cu", "pipeline.cpp"]
+SOURCES = ["engine.cu", "fp32_ref.cu", "weights_io.cpp", "json_out.cpp", "ingest.cpp", "search.cu", "pipeline.cpp"]
+# The 16-bit kernels are compiled once per operand format (csrc/fmt.h): as they are for bf16, with -DB200_OPERAND_F16 for
+# IEEE fp16; each build lives in its own namespace and the engine picks per handle.
+FORMAT_SOURCES = ["gemm_tc.cu", "ffn_fused.cu", "attention_tc.cu", "qkv_attention.cu", "elementwise.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-std=c++17", "-O3", "-lineinfo",
               "-Xcompiler", "-fPIC,-Wall,-Wno-unused-function", "--expt-relaxed-constexpr"]
 
@@ -29,12 +32,15 @@ def build_library(verbose: bool = False, force: bool = False) -> str:
     headers.append(os.path.join(HERE, "..", "include", "b200_embed.h"))
     jobs = []
     objs = []
-    for src in SOURCES:
+    units = [(src, "", []) for src in SOURCES] + [(src, "", []) for src in FORMAT_SOURCES] + \
+            [(src, "_f16", ["-DB200_OPERAND_F16"]) for src in FORMAT_SOURCES]
+    for src, suffix, defs in units:
         s = os.path.join(CSRC, src)
-        o = os.path.join(OBJ_DIR, os.path.splitext(src)[0] + ".o")
+        o = os.path.join(OBJ_DIR, os.path.splitext(src)[0] + suffix + ".o")
         objs.append(o)
         if force or not _newer(o, [s] + headers):
-            jobs.append([nvcc, *NVCC_FLAGS, "-c", s, "-o", o])
+            jobs.append([nvcc, *NVCC_FLAGS, *defs, "-c", s, "-o", o])
+    jobs.sort(key=lambda j: 0 if "gemm_tc" in j[-3] else 1)  # the longest compiles first
 
     def run(cmd):
         if verbose:
@@ -44,7 +50,7 @@ def build_library(verbose: bool = False, force: bool = False) -> str:
             raise RuntimeError(f"nvcc failed:\n{r.stdout}\n{r.stderr}")
         return r
 
-    with ThreadPoolExecutor(max_workers=4) as ex:
+    with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 4)) as ex:
         list(ex.map(run, jobs))
     if jobs or force or not _newer(LIB, objs):
         run([nvcc, "-shared", "-o", LIB, *objs, "-gencode", "arch=compute_100a,code=sm_100a", "-cudart", "static"])

@@ -30,6 +30,7 @@
 #include "tc_helpers.cuh"
 
 namespace b200 {
+B200_NS_THIS {
 
 namespace {
 
@@ -173,8 +174,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
         // The units of all of this CTA's items form one stream. S_k = Q.K_k^T is issued one unit ahead of O_k = P_k.V_k
         // ACROSS item boundaries, so the softmax warps never wait for the tensor pipe at the end of an item: two
         // cursors walk the same item sequence, `sc` for the S MMAs and `pc` (one unit behind) for the P.V MMAs.
-        constexpr uint32_t idesc_s = umma_idesc_bf16(BLK, UNIT);
-        constexpr uint32_t idesc_o = umma_idesc_bf16(BLK, D) | (1u << 16);  // B (= V) is MN-major
+        constexpr uint32_t idesc_s = umma_idesc_op(BLK, UNIT);
+        constexpr uint32_t idesc_o = umma_idesc_op(BLK, D) | (1u << 16);  // B (= V) is MN-major
         const uint64_t dq0 = umma_desc_k<D>(smem_q), dk0 = umma_desc_k<D>(smem_kv);
         const uint64_t dp0 = umma_desc_sw128(smem_p), dv0 = umma_desc_mn<D>(smem_kv + TILE);
         struct Cursor {
@@ -286,7 +287,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
                     for (int q = 0; q < D / 16; ++q) {
                         uint32_t w[8];
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) w[j] = pack_bf16x2(o[q * 16 + 2 * j] * inv, o[q * 16 + 2 * j + 1] * inv);
+                        for (int j = 0; j < 8; ++j) w[j] = pack_op2(o[q * 16 + 2 * j] * inv, o[q * 16 + 2 * j + 1] * inv);
                         stg_v8(dst + q * 16, w);
                     }
                 }
@@ -340,7 +341,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
                         upk2(fma2(pk2(__uint_as_float(v[q * 8 + 2 * j]), __uint_as_float(v[q * 8 + 2 * j + 1])), sc2, nm2), a, bb);
                         const float pa = ex2(a), pb = ex2(bb);
                         lb2[j] = add2(lb2[j], pk2(pa, pb));
-                        wd[j] = pack_bf16x2(pa, pb);
+                        wd[j] = pack_op2(pa, pb);
                     }
                     const uint32_t piece = static_cast<uint32_t>(q) ^ (row & 7);
                     sts_v4(prow + (piece << 4), wd[0], wd[1], wd[2], wd[3]);
@@ -402,11 +403,11 @@ cudaError_t launch(const __nv_bfloat16* qkv, const int* cu, int rows_cap, int ba
         return cudaErrorInvalidValue;
     auto kern = attention_tc_kernel<D>;
     constexpr int smem = AttnSmem<D>::BYTES;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static PerDeviceOnce attr_set;  // function attributes belong to a (function, device) pair
+    if (!attr_set.done()) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
-        attr_set = true;
+        attr_set.mark();
     }
     AttnDev p;
     p.cu = cu; p.batch = batch; p.heads = heads; p.H = H; p.q_blocks = (max_seqlen + BLK - 1) / BLK;
@@ -430,4 +431,5 @@ cudaError_t launch_attention_tc(const __nv_bfloat16* qkv, const int* cu, int row
     return cudaErrorInvalidValue;
 }
 
+}  // operand-format namespace
 }  // namespace b200

@@ -3,6 +3,7 @@
 #pragma once
 
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdlib.h>
@@ -18,27 +19,39 @@ __device__ __forceinline__ float warp_sum(float v) {
     return v;
 }
 
-__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+}  // namespace b200
+#include "fmt.h"
+namespace b200 {
+B200_NS_THIS {
+// Two fp32 -> one word of two 16-bit operands (round to nearest even) and back, in this build's operand format.
+#if defined(B200_OPERAND_F16)
+__device__ __forceinline__ uint32_t pack_op2(float lo, float hi) {
+    __half2 t = __floats2half2_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&t);
+}
+__device__ __forceinline__ float2 unpack_op2(uint32_t u) { return __half22float2(*reinterpret_cast<__half2*>(&u)); }
+#else
+__device__ __forceinline__ uint32_t pack_op2(float lo, float hi) {
     __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);
     return *reinterpret_cast<uint32_t*>(&t);
 }
-
-__device__ __forceinline__ float2 unpack_bf16x2(uint32_t u) {
+__device__ __forceinline__ float2 unpack_op2(uint32_t u) {
     return make_float2(__uint_as_float(u << 16), __uint_as_float(u & 0xffff0000u));
 }
+#endif
 
-// 4 consecutive elements as fp32, from bf16 (8-byte load) or fp32 (16-byte load) storage.
+// 4 consecutive elements as fp32, from 16-bit operand (8-byte load) or fp32 (16-byte load) storage.
 template <typename T>
 struct Vec4;
 template <>
 struct Vec4<__nv_bfloat16> {
     static __device__ __forceinline__ float4 load(const __nv_bfloat16* p) {
         const uint2 u = *reinterpret_cast<const uint2*>(p);
-        const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y);
+        const float2 a = unpack_op2(u.x), b = unpack_op2(u.y);
         return make_float4(a.x, a.y, b.x, b.y);
     }
     static __device__ __forceinline__ void store(__nv_bfloat16* p, float4 v) {
-        *reinterpret_cast<uint2*>(p) = make_uint2(pack_bf16x2(v.x, v.y), pack_bf16x2(v.z, v.w));
+        *reinterpret_cast<uint2*>(p) = make_uint2(pack_op2(v.x, v.y), pack_op2(v.z, v.w));
     }
 };
 template <>
@@ -46,6 +59,18 @@ struct Vec4<float> {
     static __device__ __forceinline__ float4 load(const float* p) { return *reinterpret_cast<const float4*>(p); }
     static __device__ __forceinline__ void store(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
 };
+
+// kind::f16 instruction descriptor: D fp32, A/B in this build's operand format (bits 7-9 / 10-12: 0 = fp16,
+// 1 = bf16), both K-major, M x N.
+__host__ __device__ constexpr uint32_t umma_idesc_op(int m, int n) {
+#if defined(B200_OPERAND_F16)
+    return (1u << 4) | (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(m >> 4) << 24);
+#else
+    return (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(n >> 3) << 17) |
+           (static_cast<uint32_t>(m >> 4) << 24);
+#endif
+}
+}  // operand-format namespace
 
 // candle `gelu_erf`: 0.5 x (1 + erf(x / sqrt 2)); `gelu`: tanh form; relu. (act = B200_EMBED_ACT_*)
 __device__ __forceinline__ float activate(float x, int act) {
@@ -315,11 +340,24 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
     return static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4) | (1ull << 16) | (64ull << 32) | (1ull << 46) |
            (2ull << 61);
 }
-// kind::f16 instruction descriptor: D fp32, A/B bf16, both K-major, M x N.
-__host__ __device__ constexpr uint32_t umma_idesc_bf16(int m, int n) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(n >> 3) << 17) |
-           (static_cast<uint32_t>(m >> 4) << 24);
-}
+// ---- host: once-per-device state ------------------------------------------------------------------------------------
+// cudaFuncSetAttribute and occupancy answers belong to a (function, device) pair: a process that creates handles on two
+// GPUs must set them on both. Indexed by the current device ordinal; races are benign (idempotent work).
+struct PerDeviceValue {
+    int v[64] = {};
+    static int dev() {
+        int d = 0;
+        if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d >= 64) d = 0;
+        return d;
+    }
+    int get() const { return v[dev()]; }
+    void set(int x) { v[dev()] = x; }
+};
+struct PerDeviceOnce {
+    PerDeviceValue f;
+    bool done() const { return f.get() != 0; }
+    void mark() { f.set(1); }
+};
 
 // ---- host: launches with the programmatic-dependent-launch attribute --------------------------------------------------
 // B200_EMBED_PDL=0 (read once) launches everything the plain way, for A/B timing.

@@ -9,6 +9,7 @@
 #include "common.cuh"
 
 namespace b200 {
+B200_NS_THIS {
 
 namespace {
 
@@ -25,11 +26,11 @@ __device__ __forceinline__ void store_split<float>(float* hi, float*, int col, f
 }
 template <>
 __device__ __forceinline__ void store_split<__nv_bfloat16>(__nv_bfloat16* hi, __nv_bfloat16* lo, int col, float4 y) {
-    const uint2 h = make_uint2(pack_bf16x2(y.x, y.y), pack_bf16x2(y.z, y.w));
+    const uint2 h = make_uint2(pack_op2(y.x, y.y), pack_op2(y.z, y.w));
     *reinterpret_cast<uint2*>(hi + col) = h;
     if (lo != nullptr) {
-        const float2 a = unpack_bf16x2(h.x), b = unpack_bf16x2(h.y);
-        *reinterpret_cast<uint2*>(lo + col) = make_uint2(pack_bf16x2(y.x - a.x, y.y - a.y), pack_bf16x2(y.z - b.x, y.w - b.y));
+        const float2 a = unpack_op2(h.x), b = unpack_op2(h.y);
+        *reinterpret_cast<uint2*>(lo + col) = make_uint2(pack_op2(y.x - a.x, y.y - a.y), pack_op2(y.z - b.x, y.w - b.y));
     }
 }
 template <typename T>
@@ -462,4 +463,5 @@ template cudaError_t launch_mean_pool<__nv_bfloat16>(const __nv_bfloat16*, const
 template cudaError_t launch_mean_pool<float>(const float*, const float*, const int*, int, int, int, float*,
                                                      cudaStream_t);
 
+}  // operand-format namespace
 }  // namespace b200

@@ -27,9 +27,42 @@
 #include "kernels.h"
 #include "weights_io.h"
 
-using bf16 = __nv_bfloat16;
+using bf16 = __nv_bfloat16;  // 16-bit operand storage: bf16 or fp16 bits, whichever format the handle computes in
 
 namespace {
+
+// The 16-bit kernels of one operand format (fmt.h): every handle points at one of the two sets.
+struct Ops {
+    cudaError_t (*gemm_tc_launch)(const b200::GemmTcArgs&, cudaStream_t, int);
+    int (*pick_block_n)(int, int);
+    cudaError_t (*mask_lengths)(const uint32_t*, int, int, int*, int*, int*, cudaStream_t);
+    cudaError_t (*pack_tiles)(const int*, int, int, int*, int*, int*, cudaStream_t);
+    cudaError_t (*embed_ln)(const b200::EmbedArgs&, cudaStream_t);
+    cudaError_t (*add_ln_f32)(const float*, const bf16*, const bf16*, int, const int*, const float*, const float*, float, int,
+                              bf16*, bf16*, cudaStream_t);
+    cudaError_t (*add_ln_16)(const bf16*, const bf16*, const bf16*, int, const int*, const float*, const float*, float, int,
+                             bf16*, bf16*, cudaStream_t);
+    cudaError_t (*mean_pool)(const bf16*, const bf16*, const int*, int, int, int, float*, cudaStream_t);
+    cudaError_t (*attention_tc)(const bf16*, const int*, int, int, int, int, int, bf16*, int, cudaStream_t);
+    bool (*qkv_attention_supported)(int, int, int);
+    cudaError_t (*qkv_attention)(const bf16*, const bf16*, const float*, const int*, const int*, const int*, int, int, int, int,
+                                 int, bf16*, int, cudaStream_t);
+    bool (*ffn_fused_supported)(int, int, int);
+    cudaError_t (*ffn_fused_launch)(const b200::FfnFusedArgs&, cudaStream_t, int);
+    cudaError_t (*convert_weights)(const float*, bf16*, size_t, cudaStream_t);
+};
+#define B200_OPS(NS, CONVERT)                                                                                          \
+    Ops {                                                                                                              \
+        &b200::NS::gemm_tc_launch, &b200::NS::gemm_tc_pick_block_n, &b200::NS::launch_mask_lengths,                    \
+            &b200::NS::launch_pack_tiles, &b200::NS::launch_embed_layernorm<bf16>,                                     \
+            &b200::NS::launch_add_layernorm<float, bf16>, &b200::NS::launch_add_layernorm<bf16, bf16>,                 \
+            &b200::NS::launch_mean_pool<bf16>, &b200::NS::launch_attention_tc, &b200::NS::qkv_attention_supported,     \
+            &b200::NS::launch_qkv_attention, &b200::NS::ffn_fused_supported, &b200::NS::ffn_fused_launch, CONVERT      \
+    }
+const Ops kOpsBf16 = B200_OPS(op_bf16, &b200::launch_f32_to_bf16);
+const Ops kOpsF16 = B200_OPS(op_f16, &b200::launch_f32_to_f16);
+#undef B200_OPS
+namespace f32ops = b200::op_bf16;  // the float instantiations are the same code in both sets
 
 thread_local std::string g_err;
 
@@ -134,7 +167,8 @@ struct b200_embed {
                              // head_dim 32, seq_len <= 128); B200_EMBED_QKV_ATTN=0 for A/B
     std::atomic<bool> use_graphs{true};  // small host-buffer calls replay a captured CUDA graph; B200_EMBED_GRAPHS=0 for
                                          // A/B; cleared for good if a capture ever fails (any calling thread may do that)
-    bool attn_mma = false;  // B200_EMBED_ATTENTION=mma selects the mma.sync attention kernel (A/B checks)
+    const Ops* ops = &kOpsF16;  // kernels of the handle's operand format (cfg.operand_format)
+    bool f16 = true;
     // weights
     float* arena32 = nullptr;
     bf16* arena16 = nullptr;
@@ -356,7 +390,7 @@ int gemm16(b200_embed* h, Context& c, cudaStream_t s, int kind, const void* x, c
     g.gamma = gamma; g.beta = beta; g.eps = h->cfg.layer_norm_eps; g.out = out; g.out_f32 = out_f32; g.epi = epi;
     g.block_n = block_n;
     g.pair = (h->gemm_pair && epi != b200::EPI_RES_LN && !out_f32) ? 1 : 0;
-    CU_TRY(timed(h, c, s, kind, 1, [&] { return b200::gemm_tc_launch(g, s, h->num_sms); }));
+    CU_TRY(timed(h, c, s, kind, 1, [&] { return h->ops->gemm_tc_launch(g, s, h->num_sms); }));
     return B200_EMBED_OK;
 }
 
@@ -371,17 +405,17 @@ int run_chunk(b200_embed* h, Context& c, cudaStream_t s, const Job& j) {
     const int* cu = j.d_cu;
     if (!cu) {
         CU_TRY(timed(h, c, s, B200_EMBED_KIND_LENGTHS, 2, [&] {
-            return b200::launch_mask_lengths(j.d_mask, j.batch, j.seq_len, c.d_lens, c.d_cu, c.d_status, s);
+            return h->ops->mask_lengths(j.d_mask, j.batch, j.seq_len, c.d_lens, c.d_cu, c.d_status, s);
         }));
         cu = c.d_cu;
     }
     const int* d_rows = cu + j.batch;
     // K23 (fused Q/K/V projection + attention) works on tiles of whole sentences: list them once per call
-    const bool use_k23 = !fp32 && h->qkv_attn && b200::qkv_attention_supported(H, h->heads, j.seq_len) &&
+    const bool use_k23 = !fp32 && h->qkv_attn && h->ops->qkv_attention_supported(H, h->heads, j.seq_len) &&
                          (h->force_qkv_attn || j.batch >= 256);
     if (use_k23)
         CU_TRY(timed(h, c, s, B200_EMBED_KIND_LENGTHS, 1, [&] {
-            return b200::launch_pack_tiles(cu, j.batch, 128, c.d_seg_off, c.d_tile_first, c.d_n_tiles, s);
+            return h->ops->pack_tiles(cu, j.batch, 128, c.d_seg_off, c.d_tile_first, c.d_n_tiles, s);
         }));
 
     b200::EmbedArgs e{};
@@ -391,7 +425,7 @@ int run_chunk(b200_embed* h, Context& c, cudaStream_t s, const Job& j) {
     e.max_pos = h->cfg.max_position_embeddings; e.out = w.x; e.out_lo = fp32 ? nullptr : w.x_lo; e.status = c.d_status;
     e.word = h->word; e.pos = h->pos; e.type = h->type;
     CU_TRY(timed(h, c, s, B200_EMBED_KIND_EMBED_LN, 1, [&] {
-        return fp32 ? b200::launch_embed_layernorm<float>(e, s) : b200::launch_embed_layernorm<bf16>(e, s);
+        return fp32 ? f32ops::launch_embed_layernorm<float>(e, s) : h->ops->embed_ln(e, s);
     }));
 
     for (int l = 0; l < h->L; ++l) {
@@ -409,7 +443,7 @@ int run_chunk(b200_embed* h, Context& c, cudaStream_t s, const Job& j) {
                 return b200::launch_gemm_f32(ctx, lw.ao_w, lw.ao_b, rows, d_rows, H, H, -1, w.y32, s);
             }));
             CU_TRY(timed(h, c, s, B200_EMBED_KIND_ADD_LN, 1, [&] {
-                return b200::launch_add_layernorm<float, float>(w.y32, x, nullptr, rows, d_rows, lw.ao_g, lw.ao_be, eps, H, a, nullptr, s);
+                return f32ops::launch_add_layernorm<float, float>(w.y32, x, nullptr, rows, d_rows, lw.ao_g, lw.ao_be, eps, H, a, nullptr, s);
             }));
             CU_TRY(timed(h, c, s, B200_EMBED_KIND_GEMM_FFN1, 1, [&] {
                 return b200::launch_gemm_f32(a, lw.i_w, lw.i_b, rows, d_rows, I, H, h->cfg.hidden_act, inter, s);
@@ -418,7 +452,7 @@ int run_chunk(b200_embed* h, Context& c, cudaStream_t s, const Job& j) {
                 return b200::launch_gemm_f32(inter, lw.o_w, lw.o_b, rows, d_rows, H, I, -1, w.y32, s);
             }));
             CU_TRY(timed(h, c, s, B200_EMBED_KIND_ADD_LN, 1, [&] {
-                return b200::launch_add_layernorm<float, float>(w.y32, a, nullptr, rows, d_rows, lw.o_g, lw.o_be, eps, H, x, nullptr, s);
+                return f32ops::launch_add_layernorm<float, float>(w.y32, a, nullptr, rows, d_rows, lw.o_g, lw.o_be, eps, H, x, nullptr, s);
             }));
         } else {
             bf16 *x = static_cast<bf16*>(w.x), *qkv = static_cast<bf16*>(w.qkv), *ctx = static_cast<bf16*>(w.ctx),
@@ -426,7 +460,7 @@ int run_chunk(b200_embed* h, Context& c, cudaStream_t s, const Job& j) {
             bf16 *x_lo = static_cast<bf16*>(w.x_lo), *a_lo = static_cast<bf16*>(w.a_lo);
             if (use_k23) {
                 CU_TRY(timed(h, c, s, B200_EMBED_KIND_QKV_ATTN, 1, [&] {
-                    return b200::launch_qkv_attention(x, lw.qkv_w16, lw.qkv_b, cu, c.d_tile_first, c.d_n_tiles, rows, j.batch,
+                    return h->ops->qkv_attention(x, lw.qkv_w16, lw.qkv_b, cu, c.d_tile_first, c.d_n_tiles, rows, j.batch,
                                                       j.seq_len, H, h->heads, ctx, h->num_sms, s);
                 }));
             } else {
@@ -434,9 +468,7 @@ int run_chunk(b200_embed* h, Context& c, cudaStream_t s, const Job& j) {
                             b200::EPI_BIAS, h->bn_qkv, nullptr, nullptr, nullptr, nullptr, qkv, nullptr, 0);
                 if (rc) return rc;
                 CU_TRY(timed(h, c, s, B200_EMBED_KIND_ATTENTION, 1, [&] {
-                    return h->attn_mma ? b200::launch_attention_bf16(qkv, cu, j.batch, j.seq_len, h->heads, h->D, ctx, s)
-                                       : b200::launch_attention_tc(qkv, cu, rows, j.batch, j.seq_len, h->heads, h->D, ctx,
-                                                                   h->num_sms, s);
+                    return h->ops->attention_tc(qkv, cu, rows, j.batch, j.seq_len, h->heads, h->D, ctx, h->num_sms, s);
                 }));
             }
             if (h->fuse_ln) {
@@ -448,7 +480,7 @@ int run_chunk(b200_embed* h, Context& c, cudaStream_t s, const Job& j) {
                             b200::EPI_BIAS, h->bn_h, nullptr, nullptr, nullptr, nullptr, w.y32, nullptr, 1);
                 if (rc) return rc;
                 CU_TRY(timed(h, c, s, B200_EMBED_KIND_ADD_LN, 1, [&] {
-                    return b200::launch_add_layernorm<float, bf16>(w.y32, x, x_lo, rows, d_rows, lw.ao_g, lw.ao_be, eps, H, a, a_lo, s);
+                    return h->ops->add_ln_f32(w.y32, x, x_lo, rows, d_rows, lw.ao_g, lw.ao_be, eps, H, a, a_lo, s);
                 }));
             }
             if (h->ffn_fused && (h->force_fused_ffn || rows >= 64 * 128)) {
@@ -456,7 +488,7 @@ int run_chunk(b200_embed* h, Context& c, cudaStream_t s, const Job& j) {
                 f.a = a; f.a_lo = a_lo; f.w1 = lw.i_w16; f.w2 = lw.o_w16; f.b1 = lw.i_b; f.b2 = lw.o_b; f.gamma = lw.o_g;
                 f.beta = lw.o_be; f.eps = eps; f.m = rows; f.hidden = H; f.inter = I; f.d_rows = d_rows; f.out = x;
                 f.out_lo = x_lo;
-                CU_TRY(timed(h, c, s, B200_EMBED_KIND_FFN_FUSED, 1, [&] { return b200::ffn_fused_launch(f, s, h->num_sms); }));
+                CU_TRY(timed(h, c, s, B200_EMBED_KIND_FFN_FUSED, 1, [&] { return h->ops->ffn_fused_launch(f, s, h->num_sms); }));
                 continue;
             }
             rc = gemm16(h, c, s, B200_EMBED_KIND_GEMM_FFN1, a, lw.i_w16, lw.i_b, rows, d_rows, I, H, h->act_epi,
@@ -471,16 +503,16 @@ int run_chunk(b200_embed* h, Context& c, cudaStream_t s, const Job& j) {
                             b200::EPI_BIAS, h->bn_h, nullptr, nullptr, nullptr, nullptr, w.y32, nullptr, 1);
                 if (rc) return rc;
                 CU_TRY(timed(h, c, s, B200_EMBED_KIND_ADD_LN, 1, [&] {
-                    return b200::launch_add_layernorm<float, bf16>(w.y32, a, a_lo, rows, d_rows, lw.o_g, lw.o_be, eps, H, x, x_lo, s);
+                    return h->ops->add_ln_f32(w.y32, a, a_lo, rows, d_rows, lw.o_g, lw.o_be, eps, H, x, x_lo, s);
                 }));
             }
         }
     }
     const int normalize = (j.flags & B200_EMBED_FLAG_NORMALIZE) ? 1 : 0;
     CU_TRY(timed(h, c, s, B200_EMBED_KIND_POOL, 1, [&] {
-        return fp32 ? b200::launch_mean_pool<float>(static_cast<const float*>(w.x), nullptr, cu, j.batch, H, normalize, j.d_out, s)
-                    : b200::launch_mean_pool<bf16>(static_cast<const bf16*>(w.x), static_cast<const bf16*>(w.x_lo), cu,
-                                                   j.batch, H, normalize, j.d_out, s);
+        return fp32 ? f32ops::launch_mean_pool<float>(static_cast<const float*>(w.x), nullptr, cu, j.batch, H, normalize, j.d_out, s)
+                    : h->ops->mean_pool(static_cast<const bf16*>(w.x), static_cast<const bf16*>(w.x_lo), cu, j.batch, H,
+                                        normalize, j.d_out, s);
     }));
     return B200_EMBED_OK;
 }
@@ -630,6 +662,7 @@ int32_t b200_embed_create(const b200_embed_config* cfg, const char* path, uint64
         return fail(B200_EMBED_ERR_UNSUPPORTED_SHAPE, "head dim must be 32 or 64");
     if (I % 128 != 0) return fail(B200_EMBED_ERR_UNSUPPORTED_SHAPE, "intermediate_size must be a multiple of 128");
     if (cfg->hidden_act < 0 || cfg->hidden_act > 2) return fail(B200_EMBED_ERR_INVALID_ARG, "unknown hidden_act");
+    if (cfg->operand_format < 0 || cfg->operand_format > 2) return fail(B200_EMBED_ERR_INVALID_ARG, "unknown operand_format");
 
     cudaDeviceProp prop;
     CU_TRY(cudaGetDeviceProperties(&prop, device));
@@ -646,25 +679,26 @@ int32_t b200_embed_create(const b200_embed_config* cfg, const char* path, uint64
     h->H = H; h->I = I; h->L = L; h->heads = heads; h->D = H / heads;
     h->cap_tokens = cfg->max_tokens_per_launch > 0 ? static_cast<size_t>(cfg->max_tokens_per_launch) : (1u << 20);
     if (h->cap_tokens < static_cast<size_t>(cfg->max_position_embeddings)) h->cap_tokens = cfg->max_position_embeddings;
-    h->bn_ln = b200::gemm_tc_pick_block_n(H, b200::EPI_RES_LN);
+    h->f16 = cfg->operand_format != B200_EMBED_OPERANDS_BF16;
+    h->ops = h->f16 ? &kOpsF16 : &kOpsBf16;
+    h->bn_ln = h->ops->pick_block_n(H, b200::EPI_RES_LN);
     h->fuse_ln = h->bn_ln != 0;
     if (const char* v = getenv("B200_EMBED_FUSE_LN")) h->fuse_ln = h->fuse_ln && std::string(v) != "0";
     h->act_epi = b200::EPI_GELU_ERF + cfg->hidden_act;
-    h->ffn_fused = h->fuse_ln && b200::ffn_fused_supported(H, I, cfg->hidden_act);
+    h->ffn_fused = h->fuse_ln && h->ops->ffn_fused_supported(H, I, cfg->hidden_act);
     if (const char* v = getenv("B200_EMBED_FFN_FUSED")) {
         h->ffn_fused = h->ffn_fused && std::string(v) != "0";
         h->force_fused_ffn = std::string(v) == "1";
     }
-    if (const char* v = getenv("B200_EMBED_ATTENTION")) h->attn_mma = std::string(v) == "mma";
     if (const char* v = getenv("B200_EMBED_QKV_ATTN")) {
         h->qkv_attn = std::string(v) != "0";
         h->force_qkv_attn = std::string(v) == "1";
     }
     if (const char* v = getenv("B200_EMBED_GEMM_PAIR")) h->gemm_pair = std::string(v) != "0";
     if (const char* v = getenv("B200_EMBED_GRAPHS")) h->use_graphs = std::string(v) != "0";
-    h->bn_qkv = b200::gemm_tc_pick_block_n(3 * H, b200::EPI_BIAS);
-    h->bn_ffn1 = b200::gemm_tc_pick_block_n(I, h->act_epi);
-    h->bn_h = b200::gemm_tc_pick_block_n(H, b200::EPI_GELU_ERF);  // 256 or 128 (fp32-out instantiations)
+    h->bn_qkv = h->ops->pick_block_n(3 * H, b200::EPI_BIAS);
+    h->bn_ffn1 = h->ops->pick_block_n(I, h->act_epi);
+    h->bn_h = h->ops->pick_block_n(H, b200::EPI_GELU_ERF);  // 256 or 128 (fp32-out instantiations)
     if (!h->bn_qkv || !h->bn_ffn1 || !h->bn_h) return fail(B200_EMBED_ERR_UNSUPPORTED_SHAPE, "no GEMM tiling for this shape");
 
     // ---- weight arenas ----
@@ -738,13 +772,13 @@ int32_t b200_embed_create(const b200_embed_config* cfg, const char* path, uint64
         if ((rc = load(layer_name(l, "output.LayerNorm.weight"), {H}, w.o_g))) return rc;
         if ((rc = load(layer_name(l, "output.LayerNorm.bias"), {H}, w.o_be))) return rc;
     }
-    // bf16 copies (round to nearest even of the fp32 master)
+    // 16-bit copies in the handle's operand format (round to nearest even of the fp32 master)
     for (int l = 0; l < L; ++l) {
         LayerW& w = h->layers[l];
-        CU_TRY(b200::launch_f32_to_bf16(w.qkv_w, w.qkv_w16, 3 * (size_t)H * H, nullptr));
-        CU_TRY(b200::launch_f32_to_bf16(w.ao_w, w.ao_w16, (size_t)H * H, nullptr));
-        CU_TRY(b200::launch_f32_to_bf16(w.i_w, w.i_w16, (size_t)I * H, nullptr));
-        CU_TRY(b200::launch_f32_to_bf16(w.o_w, w.o_w16, (size_t)H * I, nullptr));
+        CU_TRY(h->ops->convert_weights(w.qkv_w, w.qkv_w16, 3 * (size_t)H * H, nullptr));
+        CU_TRY(h->ops->convert_weights(w.ao_w, w.ao_w16, (size_t)H * H, nullptr));
+        CU_TRY(h->ops->convert_weights(w.i_w, w.i_w16, (size_t)I * H, nullptr));
+        CU_TRY(h->ops->convert_weights(w.o_w, w.o_w16, (size_t)H * I, nullptr));
     }
     CU_TRY(cudaDeviceSynchronize());
     for (int i = 0; i < MAX_CONTEXTS; ++i)
@@ -1002,7 +1036,7 @@ int32_t b200_op_embed_layernorm(b200_embed* h, const uint32_t* ids, const uint32
     e.word = h->word; e.pos = h->pos; e.type = h->type;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     h->launches.fetch_add(1);
-    CU_TRY(dtype ? b200::launch_embed_layernorm<float>(e, s) : b200::launch_embed_layernorm<bf16>(e, s));
+    CU_TRY(dtype ? f32ops::launch_embed_layernorm<float>(e, s) : h->ops->embed_ln(e, s));
     return B200_EMBED_OK;
 }
 
@@ -1030,7 +1064,7 @@ int32_t b200_op_linear(b200_embed* h, int32_t layer, int32_t which, const void* 
         cudaError_t e = b200::launch_gemm_f32(static_cast<const float*>(x), w32[which], bias[which], rows, nullptr,
                                               n[which], k[which], which == 2 ? h->cfg.hidden_act : -1, tmp, s);
         if (e == cudaSuccess && ln)
-            e = b200::launch_add_layernorm<float, float>(tmp, static_cast<const float*>(residual), nullptr, rows, nullptr,
+            e = f32ops::launch_add_layernorm<float, float>(tmp, static_cast<const float*>(residual), nullptr, rows, nullptr,
                                                          gam, bet, eps, H, static_cast<float*>(y), nullptr, s);
         if (ln) { cudaStreamSynchronize(s); cudaFree(tmp); }
         CU_TRY(e);
@@ -1054,7 +1088,7 @@ int32_t b200_op_linear(b200_embed* h, int32_t layer, int32_t which, const void* 
                     tmp, nullptr, 1);
     if (!rc) {
         h->launches.fetch_add(1);
-        const cudaError_t e = b200::launch_add_layernorm<float, bf16>(
+        const cudaError_t e = h->ops->add_ln_f32(
             tmp, static_cast<const bf16*>(residual), static_cast<const bf16*>(residual_lo), rows, nullptr, gam, bet, eps, H,
             static_cast<bf16*>(y), static_cast<bf16*>(y_lo), s);
         if (e != cudaSuccess) rc = cuda_fail(e, "add_layernorm");
@@ -1067,7 +1101,7 @@ int32_t b200_op_linear(b200_embed* h, int32_t layer, int32_t which, const void* 
 int32_t b200_op_ffn(b200_embed* h, int32_t layer, const void* x, const void* x_lo, int32_t rows, void* y, void* y_lo,
                     void* stream) {
     if (!h || !x || !y || layer < 0 || layer >= h->L || rows < 0) return fail(B200_EMBED_ERR_INVALID_ARG, "bad argument");
-    if (!b200::ffn_fused_supported(h->H, h->I, h->cfg.hidden_act))
+    if (!h->ops->ffn_fused_supported(h->H, h->I, h->cfg.hidden_act))
         return fail(B200_EMBED_ERR_UNSUPPORTED_SHAPE, "fused FFN needs hidden size 128 / 256 / 384 and erf-GELU");
     DeviceGuard guard(h->device);
     const LayerW& w = h->layers[layer];
@@ -1075,7 +1109,7 @@ int32_t b200_op_ffn(b200_embed* h, int32_t layer, const void* x, const void* x_l
     f.a = x; f.a_lo = x_lo; f.w1 = w.i_w16; f.w2 = w.o_w16; f.b1 = w.i_b; f.b2 = w.o_b; f.gamma = w.o_g; f.beta = w.o_be;
     f.eps = h->cfg.layer_norm_eps; f.m = rows; f.hidden = h->H; f.inter = h->I; f.out = y; f.out_lo = y_lo;
     h->launches.fetch_add(1);
-    CU_TRY(b200::ffn_fused_launch(f, static_cast<cudaStream_t>(stream), h->num_sms));
+    CU_TRY(h->ops->ffn_fused_launch(f, static_cast<cudaStream_t>(stream), h->num_sms));
     return B200_EMBED_OK;
 }
 
@@ -1085,19 +1119,18 @@ int32_t b200_op_attention(b200_embed* h, const void* qkv, const int32_t* cu, int
     DeviceGuard guard(h->device);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     h->launches.fetch_add(1);
+    if (dtype != 0 && dtype != 1) return fail(B200_EMBED_ERR_INVALID_ARG, "b200_op_attention: dtype must be 0 or 1");
     CU_TRY(dtype == 1 ? b200::launch_attention_f32(static_cast<const float*>(qkv), cu, batch, max_seqlen, h->heads, h->D,
                                                    static_cast<float*>(ctx), s)
-                 : dtype == 2 ? b200::launch_attention_bf16(static_cast<const bf16*>(qkv), cu, batch, max_seqlen, h->heads,
-                                                            h->D, static_cast<bf16*>(ctx), s)
-                              : b200::launch_attention_tc(static_cast<const bf16*>(qkv), cu, rows, batch, max_seqlen, h->heads,
-                                                          h->D, static_cast<bf16*>(ctx), h->num_sms, s));
+                      : h->ops->attention_tc(static_cast<const bf16*>(qkv), cu, rows, batch, max_seqlen, h->heads, h->D,
+                                             static_cast<bf16*>(ctx), h->num_sms, s));
     return B200_EMBED_OK;
 }
 
 int32_t b200_op_qkv_attention(b200_embed* h, int32_t layer, const void* x, const int32_t* cu, int32_t batch, int32_t rows,
                               int32_t max_seqlen, void* ctx, void* stream) {
     if (!h || !x || !cu || !ctx || layer < 0 || layer >= h->L) return fail(B200_EMBED_ERR_INVALID_ARG, "bad argument");
-    if (!b200::qkv_attention_supported(h->H, h->heads, max_seqlen))
+    if (!h->ops->qkv_attention_supported(h->H, h->heads, max_seqlen))
         return fail(B200_EMBED_ERR_UNSUPPORTED_SHAPE, "fused QKV + attention: hidden 128/256/384, head_dim 32, seq <= 128");
     DeviceGuard guard(h->device);
     const LayerW& w = h->layers[layer];
@@ -1106,9 +1139,9 @@ int32_t b200_op_qkv_attention(b200_embed* h, int32_t layer, const void* x, const
     const size_t n_ints = static_cast<size_t>(batch) + 2 + static_cast<size_t>(batch) / 32 + 2;
     CU_TRY(cudaMalloc(&tmp, n_ints * 4));
     h->launches.fetch_add(2);
-    cudaError_t e = b200::launch_pack_tiles(cu, batch, 128, tmp + batch + 2, tmp, tmp + batch + 1, s);
+    cudaError_t e = h->ops->pack_tiles(cu, batch, 128, tmp + batch + 2, tmp, tmp + batch + 1, s);
     if (e == cudaSuccess)
-        e = b200::launch_qkv_attention(static_cast<const bf16*>(x), w.qkv_w16, w.qkv_b, cu, tmp, tmp + batch + 1, rows, batch,
+        e = h->ops->qkv_attention(static_cast<const bf16*>(x), w.qkv_w16, w.qkv_b, cu, tmp, tmp + batch + 1, rows, batch,
                                        max_seqlen, h->H, h->heads, static_cast<bf16*>(ctx), h->num_sms, s);
     cudaStreamSynchronize(s);
     cudaFree(tmp);
@@ -1129,15 +1162,15 @@ int32_t b200_op_add_layernorm(b200_embed* h, int32_t layer, int32_t which, const
     const float eps = h->cfg.layer_norm_eps;
     h->launches.fetch_add(1);
     if (dtype)
-        CU_TRY((b200::launch_add_layernorm<float, float>(static_cast<const float*>(y), static_cast<const float*>(residual),
+        CU_TRY((f32ops::launch_add_layernorm<float, float>(static_cast<const float*>(y), static_cast<const float*>(residual),
                                                          nullptr, rows, nullptr, gam, bet, eps, h->H,
                                                          static_cast<float*>(out), nullptr, s)));
     else if (y_is_f32)
-        CU_TRY((b200::launch_add_layernorm<float, bf16>(static_cast<const float*>(y), static_cast<const bf16*>(residual),
+        CU_TRY((h->ops->add_ln_f32(static_cast<const float*>(y), static_cast<const bf16*>(residual),
                                                         static_cast<const bf16*>(residual_lo), rows, nullptr, gam, bet, eps,
                                                         h->H, static_cast<bf16*>(out), static_cast<bf16*>(out_lo), s)));
     else
-        CU_TRY((b200::launch_add_layernorm<bf16, bf16>(static_cast<const bf16*>(y), static_cast<const bf16*>(residual),
+        CU_TRY((h->ops->add_ln_16(static_cast<const bf16*>(y), static_cast<const bf16*>(residual),
                                                        static_cast<const bf16*>(residual_lo), rows, nullptr, gam, bet, eps,
                                                        h->H, static_cast<bf16*>(out), static_cast<bf16*>(out_lo), s)));
     return B200_EMBED_OK;
@@ -1149,28 +1182,39 @@ int32_t b200_op_mean_pool(b200_embed* h, const void* hidden, const void* hidden_
     DeviceGuard guard(h->device);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     h->launches.fetch_add(1);
-    CU_TRY(dtype ? b200::launch_mean_pool<float>(static_cast<const float*>(hidden), nullptr, cu, batch, h->H, normalize, out, s)
-                 : b200::launch_mean_pool<bf16>(static_cast<const bf16*>(hidden), static_cast<const bf16*>(hidden_lo), cu,
-                                                batch, h->H, normalize, out, s));
+    CU_TRY(dtype ? f32ops::launch_mean_pool<float>(static_cast<const float*>(hidden), nullptr, cu, batch, h->H, normalize, out, s)
+                 : h->ops->mean_pool(static_cast<const bf16*>(hidden), static_cast<const bf16*>(hidden_lo), cu, batch, h->H,
+                                     normalize, out, s));
     return B200_EMBED_OK;
 }
 
-int32_t b200_op_gemm_bf16(const void* a, const void* b, const float* bias, int32_t m, int32_t n, int32_t k,
-                          int32_t act, int32_t block_n, void* c, void* stream) {
+static int op_gemm16(const Ops& ops, const void* a, const void* b, const float* bias, int32_t m, int32_t n, int32_t k,
+                     int32_t act, int32_t block_n, void* c, void* stream) {
     if (!a || !b || !bias || !c || m < 0 || n <= 0 || k <= 0) return fail(B200_EMBED_ERR_INVALID_ARG, "bad argument");
     if (act < -1 || act > 2) return fail(B200_EMBED_ERR_INVALID_ARG, "unknown activation");
     int dev = 0, sms = 148;
     CU_TRY(cudaGetDevice(&dev));
     CU_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     const int epi = act < 0 ? b200::EPI_BIAS : b200::EPI_GELU_ERF + act;
-    if (block_n == 0) block_n = b200::gemm_tc_pick_block_n(n, epi);
+    if (block_n == 0) block_n = ops.pick_block_n(n, epi);
     if (block_n == 0 || n % block_n) return fail(B200_EMBED_ERR_UNSUPPORTED_SHAPE, "n has no supported tile width");
     b200::GemmTcArgs g{};
     g.a = a; g.b = b; g.m = m; g.n = n; g.k = k; g.bias = bias; g.out = c; g.epi = epi; g.block_n = block_n;
     const char* pv = getenv("B200_EMBED_GEMM_PAIR");
     g.pair = (pv && std::string(pv) == "0") ? 0 : 1;
-    CU_TRY(b200::gemm_tc_launch(g, static_cast<cudaStream_t>(stream), sms));
+    CU_TRY(ops.gemm_tc_launch(g, static_cast<cudaStream_t>(stream), sms));
     return B200_EMBED_OK;
+}
+int32_t b200_op_gemm_bf16(const void* a, const void* b, const float* bias, int32_t m, int32_t n, int32_t k,
+                          int32_t act, int32_t block_n, void* c, void* stream) {
+    return op_gemm16(kOpsBf16, a, b, bias, m, n, k, act, block_n, c, stream);
+}
+int32_t b200_op_gemm_f16(const void* a, const void* b, const float* bias, int32_t m, int32_t n, int32_t k,
+                         int32_t act, int32_t block_n, void* c, void* stream) {
+    return op_gemm16(kOpsF16, a, b, bias, m, n, k, act, block_n, c, stream);
+}
+int32_t b200_embed_operand_format(const b200_embed* h) {
+    return !h ? 0 : (h->f16 ? B200_EMBED_OPERANDS_FP16 : B200_EMBED_OPERANDS_BF16);
 }
 
 }  // extern "C"
@@ -1232,15 +1276,15 @@ extern "C" int32_t b200_op_linear_noalloc(b200_embed* h, int32_t layer, int32_t 
     if (dtype == 1) {
         CU_TRY(b200::launch_gemm_f32(static_cast<const float*>(x), which == 1 ? w.ao_w : w.o_w, bias, rows, nullptr, H, k,
                                      -1, scratch, s));
-        CU_TRY((b200::launch_add_layernorm<float, float>(scratch, static_cast<const float*>(residual), nullptr, rows,
+        CU_TRY((f32ops::launch_add_layernorm<float, float>(scratch, static_cast<const float*>(residual), nullptr, rows,
                                                          nullptr, gam, bet, eps, H, static_cast<float*>(y), nullptr, s)));
         return B200_EMBED_OK;
     }
     b200::GemmTcArgs g{};
     g.a = x; g.b = which == 1 ? w.ao_w16 : w.o_w16; g.m = rows; g.n = H; g.k = k; g.bias = bias; g.eps = eps;
     g.out = scratch; g.out_f32 = 1; g.epi = b200::EPI_BIAS; g.block_n = h->bn_h;
-    CU_TRY(b200::gemm_tc_launch(g, s, h->num_sms));
-    CU_TRY((b200::launch_add_layernorm<float, bf16>(scratch, static_cast<const bf16*>(residual),
+    CU_TRY(h->ops->gemm_tc_launch(g, s, h->num_sms));
+    CU_TRY((h->ops->add_ln_f32(scratch, static_cast<const bf16*>(residual),
                                                     static_cast<const bf16*>(residual_lo), rows, nullptr, gam, bet, eps, H,
                                                     static_cast<bf16*>(y), static_cast<bf16*>(y_lo), s)));
     return B200_EMBED_OK;

@@ -29,6 +29,7 @@
 #include "tc_helpers.cuh"
 
 namespace b200 {
+B200_NS_THIS {
 
 namespace {
 
@@ -211,8 +212,8 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     } else if (warp == 1) {
         // The whole warp walks the schedule (waits included) so that control flow stays uniform; one elected lane issues.
         if (leader) {
-            constexpr uint32_t idesc1 = umma_idesc_bf16(2 * BM, IC);
-            constexpr uint32_t idesc2 = umma_idesc_bf16(2 * BM, UN2);
+            constexpr uint32_t idesc1 = umma_idesc_op(2 * BM, IC);
+            constexpr uint32_t idesc2 = umma_idesc_op(2 * BM, UN2);
             uint32_t tile_it = 0, g1_it = 0, g2_it = 0;  // g*_it: chunks issued so far
             const uint64_t da0 = umma_desc_sw128(smem_a), dh0 = umma_desc_sw128(smem_h);
             const uint64_t dw1 = umma_desc_sw128(smem_w1), dw2 = umma_desc_sw128(smem_w2);
@@ -464,11 +465,11 @@ cudaError_t launch_ffn(const FfnFusedArgs& a, cudaStream_t stream, int num_sms) 
     tcl = tc;
     if (a.out_lo && !make_tmap(&tcl, a.out_lo, a.m, H, CHUNK, 32, false, CU_TENSOR_MAP_SWIZZLE_64B)) return cudaErrorInvalidValue;
     auto kern = ffn_fused_kernel<H>;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static PerDeviceOnce attr_set;  // function attributes belong to a (function, device) pair
+    if (!attr_set.done()) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::BYTES);
         if (e != cudaSuccess) return e;
-        attr_set = true;
+        attr_set.mark();
     }
     FfnDev p;
     p.m = a.m; p.d_rows = a.d_rows; p.inter = a.inter; p.b1 = a.b1; p.b2 = a.b2; p.gamma = a.gamma; p.beta = a.beta;
@@ -485,12 +486,14 @@ cudaError_t launch_ffn(const FfnFusedArgs& a, cudaStream_t stream, int num_sms) 
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    static int max_pairs = 0;  // CTA pairs the device holds at once
+    static PerDeviceValue max_pairs_dev;  // CTA pairs the device holds at once
+    int max_pairs = max_pairs_dev.get();
     if (max_pairs == 0) {
         max_pairs = num_sms / 2;
         cfg.gridDim = dim3(2 * (num_sms / 2));
         int n = 0;
         if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) == cudaSuccess && n > 0 && n < max_pairs) max_pairs = n;
+        max_pairs_dev.set(max_pairs);
     }
     const int grid = 2 * (pairs < max_pairs ? pairs : max_pairs);
     if (grid <= 0) return cudaSuccess;
@@ -513,4 +516,5 @@ cudaError_t ffn_fused_launch(const FfnFusedArgs& a, cudaStream_t stream, int num
     return cudaErrorInvalidValue;
 }
 
+}  // operand-format namespace
 }  // namespace b200

@@ -123,6 +123,16 @@ cudaError_t launch_attention_f32(const float* qkv, const int* cu, int batch, int
     return cudaGetLastError();
 }
 
+__global__ void f32_to_f16_kernel(const float* __restrict__ src, __half* __restrict__ dst, size_t n) {
+    const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = __float2half_rn(src[i]);
+}
+cudaError_t launch_f32_to_f16(const float* src, __nv_bfloat16* dst, size_t n, cudaStream_t s) {
+    if (n == 0) return cudaSuccess;
+    f32_to_f16_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, s>>>(src, reinterpret_cast<__half*>(dst), n);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_f32_to_bf16(const float* src, __nv_bfloat16* dst, size_t n, cudaStream_t s) {
     if (n == 0) return cudaSuccess;
     size_t blocks = (n + 255) / 256;

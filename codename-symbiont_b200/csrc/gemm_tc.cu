@@ -47,6 +47,7 @@
 #include "tc_helpers.cuh"
 
 namespace b200 {
+B200_NS_THIS {
 
 namespace {
 
@@ -256,7 +257,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     } else if (warp == 1) {
         // ------------------------------ MMA issuer --------------------------------
         if ((!PAIR || crank == 0) && (UNIFORM || lane == 0)) {
-            constexpr uint32_t idesc = umma_idesc_bf16(PAIR ? 2 * BLOCK_M : BLOCK_M, BLOCK_N);
+            constexpr uint32_t idesc = umma_idesc_op(PAIR ? 2 * BLOCK_M : BLOCK_M, BLOCK_N);
             const uint64_t da0 = umma_desc_sw128(smem_a), db0 = umma_desc_sw128(smem_b);
             int stage = 0;
             uint32_t phase = 0;
@@ -624,18 +625,22 @@ cudaError_t launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms) {
     constexpr int smem = smem_bytes(BLOCK_N, EPI, OUT_F32, RING, PAIR, CL);
     static_assert(num_stages(BLOCK_N, EPI, OUT_F32, RING, PAIR, CL) >= 2, "not enough shared memory for a pipeline");
     static_assert(smem <= SMEM_LIMIT, "shared memory budget exceeded");
-    static bool attr_set = false;  // per instantiation; benign race (idempotent)
-    if (!attr_set) {
+    static PerDeviceOnce attr_set;  // per instantiation AND per device: function attributes belong to a device
+    if (!attr_set.done()) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
-        attr_set = true;
+        attr_set.mark();
     }
     GemmDev p;
     p.m = a.m; p.d_rows = a.d_rows; p.n = a.n; p.k = a.k; p.bias = a.bias;
     p.gamma = a.gamma; p.beta = a.beta; p.eps = a.eps;
     p.has_res_lo = a.residual_lo != nullptr; p.has_out_lo = a.out_lo != nullptr;
+#if defined(B200_GEMM_DEBUG)  // timing experiments (results wrong by construction): never in the shipped library
     static const int dbg = [] { const char* dv = getenv("B200_EMBED_GEMM_DBG"); return dv ? atoi(dv) : 0; }();
     p.dbg = dbg;
+#else
+    p.dbg = 0;
+#endif
     const int m_tiles = (a.m + BLOCK_M - 1) / BLOCK_M;
     const int units = CL > 1 ? m_tiles : (PAIR ? ((m_tiles + 1) / 2) : m_tiles) * (a.n / BLOCK_N);
     cudaLaunchConfig_t cfg{};
@@ -651,7 +656,8 @@ cudaError_t launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms) {
     cfg.attrs = attr;
     cfg.numAttrs = CSIZE > 1 ? 2 : 1;
     // persistent grid: as many clusters as the device can hold at once (size-4 clusters do not tile all 148 SMs)
-    static int max_units = 0;
+    static PerDeviceValue max_units_dev;
+    int max_units = max_units_dev.get();
     if (max_units == 0) {
         max_units = num_sms / CSIZE;
         if (CSIZE > 1) {
@@ -659,6 +665,7 @@ cudaError_t launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms) {
             int n = 0;
             if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) == cudaSuccess && n > 0 && n < max_units) max_units = n;
         }
+        max_units_dev.set(max_units);
     }
     const int grid = (units < max_units ? units : max_units) * CSIZE;
     if (grid <= 0) return cudaSuccess;
@@ -730,4 +737,5 @@ cudaError_t gemm_tc_launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms
     return cudaErrorInvalidValue;
 }
 
+}  // operand-format namespace
 }  // namespace b200

@@ -2,6 +2,8 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include "fmt.h"
+
 namespace b200 {
 
 enum GemmEpilogue {
@@ -13,28 +15,32 @@ enum GemmEpilogue {
 };
 
 struct GemmTcArgs {
-    const void* a;         // [m, k] bf16 row-major (activations)
-    const void* b;         // [n, k] bf16 row-major (HF Linear weight)
+    const void* a;         // [m, k] 16-bit row-major (activations)
+    const void* b;         // [n, k] 16-bit row-major (HF Linear weight)
     int m, n, k;
     const int* d_rows;     // optional device int: rows actually present (<= m); tiles beyond are skipped
     const float* bias;     // [n]
-    const void* residual;  // [m, n] bf16 (EPI_RES_LN), high half of the residual stream
-    const void* residual_lo;  // [m, n] bf16 low half (residual = hi + lo), or nullptr
+    const void* residual;  // [m, n] 16-bit (EPI_RES_LN), high half of the residual stream
+    const void* residual_lo;  // [m, n] 16-bit low half (residual = hi + lo), or nullptr
     const float* gamma;    // [n]     (EPI_RES_LN)
     const float* beta;     // [n]     (EPI_RES_LN)
     float eps;
-    void* out;             // [m, n] bf16, or fp32 when out_f32
-    void* out_lo;          // EPI_RES_LN: optional [m, n] bf16 low half of the output
+    void* out;             // [m, n] 16-bit, or fp32 when out_f32
+    void* out_lo;          // EPI_RES_LN: optional [m, n] 16-bit low half of the output
     int out_f32;           // only with EPI_BIAS
     int epi;               // GemmEpilogue
     int pair;              // plain bf16 epilogues: 1 = clusters of 2 CTAs on adjacent row blocks, one cta_group::2 MMA per pair
     int block_n;           // 128, 192, 256 (EPI_RES_LN: n / cluster size, from gemm_tc_pick_block_n)
 };
 
-// EPI_RES_LN: CTAs per cluster that share one row block (1, 2 or 4); 0 if this N cannot be fused.
-int gemm_tc_pick_cluster(int n, int epi);
-// Largest supported tile width for this N and epilogue; 0 if none.
-int gemm_tc_pick_block_n(int n, int epi);
-cudaError_t gemm_tc_launch(const GemmTcArgs& args, cudaStream_t stream, int num_sms);
+// One set per operand format (fmt.h).
+#define B200_GEMM_TC_DECLS                                                                               \
+    /* EPI_RES_LN: CTAs per cluster that share one row block (1, 2 or 4); 0 if this N cannot be fused. */ \
+    int gemm_tc_pick_cluster(int n, int epi);                                                            \
+    /* Largest supported tile width for this N and epilogue; 0 if none. */                               \
+    int gemm_tc_pick_block_n(int n, int epi);                                                            \
+    cudaError_t gemm_tc_launch(const GemmTcArgs& args, cudaStream_t stream, int num_sms);
+B200_NS_BF16 { B200_GEMM_TC_DECLS }
+B200_NS_F16 { B200_GEMM_TC_DECLS }
 
 }  // namespace b200

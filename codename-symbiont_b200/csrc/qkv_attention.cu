@@ -33,6 +33,7 @@
 #include "tc_helpers.cuh"
 
 namespace b200 {
+B200_NS_THIS {
 
 namespace {
 
@@ -200,9 +201,9 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
         }
     } else if (warp == 1) {
         // ------------------------------ MMA issuer: event loop ------------------------------
-        constexpr uint32_t idesc_g = umma_idesc_bf16(BLK, NQ);
-        constexpr uint32_t idesc_s = umma_idesc_bf16(BLK, UNIT);
-        constexpr uint32_t idesc_o = umma_idesc_bf16(BLK, D) | (1u << 16);  // B (= V) is MN-major
+        constexpr uint32_t idesc_g = umma_idesc_op(BLK, NQ);
+        constexpr uint32_t idesc_s = umma_idesc_op(BLK, UNIT);
+        constexpr uint32_t idesc_o = umma_idesc_op(BLK, D) | (1u << 16);  // B (= V) is MN-major
         const uint64_t dx0 = umma_desc_sw128(smem_x), dw0 = umma_desc_sw128(smem_w);
         const uint64_t dq0 = umma_desc_k_sw64(smem_t), dp0 = umma_desc_sw128(smem_p);
         const uint64_t dv0 = umma_desc_mn<D>(smem_t + 2 * T_TILE);
@@ -353,7 +354,7 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                     for (int q = 0; q < D / 16; ++q) {
                         uint32_t wd[8];
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) wd[j] = pack_bf16x2(o[q * 16 + 2 * j] * inv, o[q * 16 + 2 * j + 1] * inv);
+                        for (int j = 0; j < 8; ++j) wd[j] = pack_op2(o[q * 16 + 2 * j] * inv, o[q * 16 + 2 * j + 1] * inv);
                         stg_v8(dst + q * 16, wd);
                     }
                 }
@@ -445,7 +446,7 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                             upk2(fma2(pk2(__uint_as_float(v[q * 8 + 2 * j]), __uint_as_float(v[q * 8 + 2 * j + 1])), sc2, nm2), a, bb);
                             const float pa = ex2(a), pb = ex2(bb);
                             lb2[j] = add2(lb2[j], pk2(pa, pb));
-                            wd[j] = pack_bf16x2(pa, pb);
+                            wd[j] = pack_op2(pa, pb);
                         }
                         const uint32_t piece = static_cast<uint32_t>(q) ^ (row & 7);
                         sts_v4(prow + (piece << 4), wd[0], wd[1], wd[2], wd[3]);
@@ -485,11 +486,11 @@ cudaError_t launch_qa(const __nv_bfloat16* x, const __nv_bfloat16* wqkv, const f
     if (!make_tmap(&tx, x, rows_cap, H, BK, BLK, false, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
     if (!make_tmap(&tw, wqkv, 3 * H, H, BK, D, false, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
     auto kern = qkv_attention_kernel<H, D>;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static PerDeviceOnce attr_set;  // function attributes belong to a (function, device) pair
+    if (!attr_set.done()) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::BYTES);
         if (e != cudaSuccess) return e;
-        attr_set = true;
+        attr_set.mark();
     }
     QaDev p;
     p.cu = cu; p.tile_first = tile_first; p.n_tiles = n_tiles; p.bias = bqkv; p.batch = batch; p.H = H; p.ctx = ctx;
@@ -516,4 +517,5 @@ cudaError_t launch_qkv_attention(const __nv_bfloat16* x, const __nv_bfloat16* wq
     return launch_qa<128, 32>(x, wqkv, bqkv, cu, tile_first, n_tiles, rows_cap, batch, ctx, num_sms, s);
 }
 
+}  // operand-format namespace
 }  // namespace b200

@@ -11,6 +11,7 @@
 #include "gemm_tc.h"
 
 namespace b200 {
+B200_NS_THIS {
 namespace {
 
 constexpr int CHUNK = 32;                   // epilogue chunk: 32 rows x 32 columns per warp
@@ -91,9 +92,9 @@ __device__ __forceinline__ uint32_t epi_pair_bf16(uint32_t acc0, uint32_t acc1, 
         if constexpr (EPI == EPI_GELU_ERF) x = gelu_erf_fast2(x);
         float a, b;
         upk2(x, a, b);
-        return pack_bf16x2(a, b);
+        return pack_op2(a, b);
     } else {
-        return pack_bf16x2(epi_act<EPI>(__uint_as_float(acc0) + b0), epi_act<EPI>(__uint_as_float(acc1) + b1));
+        return pack_op2(epi_act<EPI>(__uint_as_float(acc0) + b0), epi_act<EPI>(__uint_as_float(acc1) + b1));
     }
 }
 
@@ -144,8 +145,8 @@ __device__ __forceinline__ void ln_accumulate_chunk(uint32_t (&v)[32], uint32_t 
         for (int j = 0; j < 4; ++j) {
             uint64_t x = add2(pk2(__uint_as_float(v[q * 8 + 2 * j]), __uint_as_float(v[q * 8 + 2 * j + 1])),
                               pk2(__uint_as_float(bw[2 * j]), __uint_as_float(bw[2 * j + 1])));
-            x = add2(x, pk2(__uint_as_float(rw[j] << 16), __uint_as_float(rw[j] & 0xffff0000u)));
-            if (has_lo) x = add2(x, pk2(__uint_as_float(lw[j] << 16), __uint_as_float(lw[j] & 0xffff0000u)));
+            { const float2 f = unpack_op2(rw[j]); x = add2(x, pk2(f.x, f.y)); }
+            if (has_lo) { const float2 f = unpack_op2(lw[j]); x = add2(x, pk2(f.x, f.y)); }
             sum2 = add2(sum2, x);
             sq2 = fma2(x, x, sq2);
             float a, b;
@@ -171,10 +172,11 @@ __device__ __forceinline__ void ln_normalize_chunk(const uint32_t (&x)[32], floa
                                     pk2(__uint_as_float(bw[2 * j]), __uint_as_float(bw[2 * j + 1])));
             float a, b;
             upk2(y, a, b);
-            const uint32_t h = pack_bf16x2(a, b);
+            const uint32_t h = pack_op2(a, b);
             hi[q * 2 + j] = h;
-            upk2(fma2(pk2(__uint_as_float(h << 16), __uint_as_float(h & 0xffff0000u)), m1, y), a, b);
-            lo[q * 2 + j] = pack_bf16x2(a, b);
+            const float2 hf = unpack_op2(h);
+            upk2(fma2(pk2(hf.x, hf.y), m1, y), a, b);
+            lo[q * 2 + j] = pack_op2(a, b);
         }
     }
 }
@@ -240,4 +242,5 @@ bool make_tmap(CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t cols, 
 }
 
 }  // namespace
+}  // operand-format namespace
 }  // namespace b200

@@ -43,7 +43,7 @@ class EmbeddingGenerator:
 
     @classmethod
     def new(cls, model_id: str, revision: str | None = None, force_cpu: bool = False, device: int = 0,
-            normalize: bool = False) -> "EmbeddingGenerator":
+            normalize: bool = False, operands: str = "default") -> "EmbeddingGenerator":
         if force_cpu:
             raise B200EmbedError(-5, "force_cpu=true: this embedding path has no CPU fallback (NO_DEVICE)")
         d = model_id
@@ -58,7 +58,7 @@ class EmbeddingGenerator:
 
             tok = Tokenizer.from_file(os.path.join(d, "tokenizer.json"))
             configure_tokenizer(tok, shape.max_position_embeddings)
-        emb = Embedder(shape, os.path.join(d, "model.safetensors"), device=device)
+        emb = Embedder(shape, os.path.join(d, "model.safetensors"), device=device, operands=operands)
         return cls(emb, tok, shape, normalize, ingest)
 
     def generate_sentence_embeddings(self, sentences: Sequence[str]) -> List[List[float]]:

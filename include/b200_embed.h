@@ -46,7 +46,7 @@ extern "C" {
 #define B200_EMBED_FLAG_NORMALIZE 1u /* append v / max(||v||_2, 1e-12). The reference does NOT normalise
                                         (embedding_generator.rs:201-207), so the drop-in default is 0. */
 #define B200_EMBED_FLAG_FP32 2u      /* fp32 validation mode: fp32 weights, activations and SIMT GEMMs
-                                        (slow; parity gate cosine >= 0.999999). Default is bf16 tensor cores. */
+                                        (slow; parity gate cosine >= 0.999999). Default is the 16-bit tensor-core path. */
 
 /* hidden_act values: candle HiddenAct::{Gelu, GeluApproximate, Relu} */
 #define B200_EMBED_ACT_GELU_ERF 0
@@ -68,13 +68,24 @@ typedef struct b200_embed_config {
     float layer_norm_eps;
     int32_t max_tokens_per_launch; /* workspace capacity in tokens; 0 = default (1 Mi). Larger calls are
                                       split into sentence chunks internally, order preserved. */
+    int32_t operand_format;     /* B200_EMBED_OPERANDS_*: what the tensor-core GEMMs multiply. 0 = default = fp16 */
 } b200_embed_config;
+
+/* Operand format of the 16-bit path (weights, activations fed to tcgen05.mma kind::f16, the (hi, lo) residual pairs).
+ * Both run at the same tensor-core rate and move the same bytes; accumulation, LayerNorm statistics, softmax and pooling
+ * are fp32 either way. fp16 (11 significand bits) keeps the un-normalised output within max-abs 2e-3 of the f32
+ * reference (measured 7e-4 on MiniLM-L6), which bf16 (8 bits) cannot: rounding the weight matrices to bf16 alone moves it
+ * by 2.6-3.1e-3. fp16's range (6e-5 .. 65504 at full precision) covers BERT weights and post-LayerNorm activations; a
+ * checkpoint with activations beyond it should pick bf16. */
+#define B200_EMBED_OPERANDS_DEFAULT 0
+#define B200_EMBED_OPERANDS_BF16 1
+#define B200_EMBED_OPERANDS_FP16 2
 
 /* -- lifetime: replaces EmbeddingGenerator::new (embedding_generator.rs:17-132) ------------------
  * safetensors_path: a HuggingFace BERT `model.safetensors` (F32/F16/BF16; names as in
  * BertModel::load, optional `bert.` prefix, legacy gamma/beta LayerNorm names) or NULL for the
  * seeded random init used by benchmarks (spec in codename-symbiont_b200/weights.py).
- * Converts weights to bf16 once, packs Q/K/V into one [3H,H] matrix, keeps the f32 master for
+ * Converts weights to the operand format (cfg->operand_format) once, packs Q/K/V into one [3H,H] matrix, keeps the f32 master for
  * the validation mode. The handle is thread-safe: concurrent forward calls each lease a
  * stream + workspace (the reference shares one Arc<EmbeddingGenerator>, main.rs:314, :373). */
 int32_t b200_embed_create(const b200_embed_config* cfg, const char* safetensors_path, uint64_t seed,
@@ -82,6 +93,9 @@ int32_t b200_embed_create(const b200_embed_config* cfg, const char* safetensors_
 void b200_embed_destroy(b200_embed* h);
 
 int32_t b200_embed_hidden_size(const b200_embed* h);
+/* B200_EMBED_OPERANDS_BF16 or _FP16: the format this handle computes in (and that the b200_op_* device-pointer entry
+ * points below expect their 16-bit tensors in). */
+int32_t b200_embed_operand_format(const b200_embed* h);
 int32_t b200_embed_max_positions(const b200_embed* h);
 /* thread-local, never NULL */
 const char* b200_embed_last_error(void);
@@ -158,11 +172,13 @@ int32_t b200_embed_profile_read(b200_embed* h, b200_embed_kind_stats* out /* [B2
 
 /* -- single kernels on device pointers (parity tests and roofline runs) ---------------------------
  * All pointers are device pointers; `stream` is a cudaStream_t (NULL = default stream). dtype:
- * 0 = bf16 activations / tensor-core GEMM, 1 = fp32 validation kernels. Row counts are tokens. */
+ * 0 = 16-bit activations in the handle's operand format / tensor-core GEMM, 1 = fp32 validation kernels. Row counts are
+ * tokens. */
 
-/* Residual-stream tensors in bf16 mode are (hi, lo) pairs of bf16 [rows, H] arrays: hi = bf16(v) is what
- * the next GEMM multiplies, hi + lo is what residual adds and the pooling read. Every `*_lo` argument may be
- * NULL (plain bf16) and is ignored when dtype = 1. */
+/* Residual-stream tensors in the 16-bit mode are (hi, lo) pairs of [rows, H] arrays in the operand format: hi =
+ * round16(v) is what the next GEMM multiplies, hi + lo is what residual adds and the pooling read. Every `*_lo`
+ * argument may be NULL (plain 16-bit) and is ignored when dtype = 1. ("bf16" in the comments below means "the handle's
+ * 16-bit operand format".) */
 
 /* K1. out[t,:] = LN(word[ids[t]] + type[tt[t]] + pos[position of t]) for the packed tokens of
  * `batch` sentences; cu_seqlens int32[batch+1] on device. (bert.rs BertEmbeddings::forward) */
@@ -182,8 +198,8 @@ int32_t b200_op_ffn(b200_embed* h, int32_t layer, const void* x, const void* x_l
 
 /* The same Linear + residual + LayerNorm step as b200_op_linear(which = 1 or 3) for callers that must not
  * allocate. It has no counterpart in the reference. b200_op_linear parks the fp32 pre-LayerNorm rows in a
- * cudaMalloc'ed temporary when the LayerNorm is not fused into the GEMM (hidden sizes other than 128/256/384,
- * and the fp32 mode); cudaMalloc and cudaFree are off limits for a caller that has already handed every byte
+ * cudaMalloc'ed temporary when the LayerNorm is not fused into the GEMM (hidden sizes other than 128, 256, 384,
+ * 512, 768 and 1024 - e.g. 640 - and the fp32 mode); cudaMalloc and cudaFree are off limits for a caller that has already handed every byte
  * of the GPU to its own pool, and they synchronise the whole device, which a caller with other streams in
  * flight in a latency-bound loop cannot afford. Here those rows go to a fixed 4 MiB array that is part of the
  * library image instead (resident on every GPU that loads the library until the process exits), and the call
@@ -202,7 +218,7 @@ int32_t b200_op_linear_noalloc(b200_embed* h, int32_t layer, int32_t which, cons
                                void* stream);
 
 /* K3. ctx = softmax(q k^T / sqrt(d)) v per sentence and head over packed qkv [rows, 3H].
- * dtype 0: tcgen05 kernel (the one the forward uses), 1: fp32 validation, 2: mma.sync bf16 kernel (A/B checks). */
+ * dtype 0: tcgen05 kernel (the one the forward uses), 1: fp32 validation. */
 int32_t b200_op_attention(b200_embed* h, const void* qkv, const int32_t* cu_seqlens, int32_t batch, int32_t rows,
                           int32_t max_seqlen, int32_t dtype, void* ctx, void* stream);
 /* K23. ctx = attention(x . Wqkv^T + bqkv) of layer `layer` straight from the bf16 activations x [rows, H]: the fused
@@ -222,6 +238,9 @@ int32_t b200_op_mean_pool(b200_embed* h, const void* hidden, const void* hidden_
  * bf16 in, fp32 accumulate, bf16 out. N % 128 == 0, K % 8 == 0. act: -1 none, else B200_EMBED_ACT_*. */
 int32_t b200_op_gemm_bf16(const void* a, const void* b, const float* bias, int32_t m, int32_t n, int32_t k,
                           int32_t act, int32_t block_n, void* c, void* stream);
+/* The same kernel with IEEE fp16 operands and output. */
+int32_t b200_op_gemm_f16(const void* a, const void* b, const float* bias, int32_t m, int32_t n, int32_t k,
+                         int32_t act, int32_t block_n, void* c, void* stream);
 
 /* -- wire format of the results (host only, no GPU involved) --------------------------------------------
  * The JSON text serde_json::to_vec produces for the messages the service publishes after the embedding call

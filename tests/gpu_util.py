@@ -23,6 +23,14 @@ def bf16_round(a):
     return torch.from_numpy(np.array(a, dtype=np.float32, copy=True)).bfloat16().float().numpy()
 
 
+T16 = {"bf16": torch.bfloat16, "f16": torch.float16}
+
+
+def round16(a, fmt):
+    """fp32 ndarray rounded (RNE) to the 16-bit operand format `fmt` ("bf16" / "f16") and back."""
+    return torch.from_numpy(np.array(a, dtype=np.float32, copy=True)).to(T16[fmt]).float().numpy()
+
+
 def host(t):
     torch.cuda.synchronize()
     return t.float().cpu().numpy()

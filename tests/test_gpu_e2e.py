@@ -6,7 +6,8 @@ import threading
 import numpy as np
 import pytest
 
-from conftest import load_golden, cos_rows, BF16_COS, BF16_ABS, FP32_COS
+from conftest import (load_golden, cos_rows, GATE_COS, GATE_ABS, FP32_COS, FP32_ABS, BF16_RAW_ABS, BF16_SHORT_ABS,
+                      CROSS_SCHEDULE_ABS)
 from oracle.oracle import Oracle
 
 pytestmark = pytest.mark.gpu
@@ -16,72 +17,99 @@ def l2n(v):
     return v / np.maximum(np.linalg.norm(v, axis=1, keepdims=True), 1e-12)
 
 
+FMT = "f16"  # operand format of the running parametrisation (set by the fixture below)
+_ORACLE_CACHE = {}
+
+
+@pytest.fixture(scope="module", params=["f16", "bf16"], autouse=True)
+def fmt(request):
+    global FMT
+    FMT = request.param
+    return request.param
+
+
+def cached(tag, fn):
+    """Oracle results do not depend on the operand format: computed once per module run."""
+    if tag not in _ORACLE_CACHE:
+        _ORACLE_CACHE[tag] = fn()
+    return _ORACLE_CACHE[tag]
+
+
 def check(got, want, fp32, want_same_weights=None, lengths=None):
-    """BASELINE.md section 5 gates. fp32 validation mode: cosine >= 0.999999 (+ max-abs 1e-4).
-    bf16 mode: per-vector cosine >= 0.9999 always, and max-abs <= 2e-3
-      (a) on the L2-normalised vectors, which is what the north_star pipeline emits, and
-      (b) on the raw pooled vectors against the oracle run on the SAME bf16-rounded weight matrices the
-          kernels multiply by (`want_same_weights`), which isolates kernel error from weight quantisation;
-          sentences of fewer than 8 tokens are held to 5e-3 there: with little to average over, the bf16
-          rounding of the GEMM inputs alone reaches 3.6e-3 for them (scripts/precision_study.py bylen).
-    Raw vectors against the fp32-weight oracle are held to 6e-3: rounding the weights to bf16 ALONE moves the
-    raw MiniLM output by 2.9e-3 max-abs (scripts/precision_study.py), so 2e-3 is below
-    the floor of any bf16-weight implementation for un-normalised vectors of magnitude ~3."""
+    """BASELINE.md section 5 gates (constants and their reasons in conftest.py).
+    fp32 validation mode: cosine >= 0.999999 (+ max-abs 1e-4).
+    fp16 operands: cosine >= 0.9999 and max-abs <= 2e-3 on the raw pooled vectors against the f32 oracle - the gate as
+    stated.  bf16 operands: the cosine gate; max-abs <= 2e-3 after L2 normalisation and against the oracle on the same
+    bf16-rounded weights (`want_same_weights`); the measured limits BF16_RAW_ABS / BF16_SHORT_ABS otherwise."""
     assert got.shape == want.shape and np.isfinite(got).all()
     c, e = cos_rows(got, want).min(), np.abs(got - want).max()
     if fp32:
-        assert c >= FP32_COS and e <= 1e-4, (c, e)
+        assert c >= FP32_COS and e <= FP32_ABS, (c, e)
         return
-    assert c >= BF16_COS, c
+    assert c >= GATE_COS, c
+    if FMT == "f16":
+        assert e <= GATE_ABS, e
+        return
     en = np.abs(l2n(got) - l2n(want)).max()
-    assert en <= BF16_ABS, en
-    assert e <= 6e-3, e
+    assert en <= GATE_ABS, en
+    assert e <= BF16_RAW_ABS, e
     if want_same_weights is not None:
         e2 = np.abs(got - want_same_weights).max(axis=1)
         short = np.zeros(len(e2), bool) if lengths is None else (np.asarray(lengths) < 8)
-        assert (e2[~short] <= BF16_ABS).all(), e2[~short].max()
-        assert (e2[short] <= 5e-3).all(), e2[short].max()
+        assert (e2[~short] <= GATE_ABS).all(), e2[~short].max()
+        assert (e2[short] <= BF16_SHORT_ABS).all(), e2[short].max()
+
+
+def close_schedules(a, b):
+    """two schedules / batch compositions of the same 16-bit math"""
+    assert np.abs(a - b).max() <= CROSS_SCHEDULE_ABS[FMT], np.abs(a - b).max()
+    assert cos_rows(a, b).min() >= GATE_COS
 
 
 @pytest.fixture(scope="module")
-def tiny(pkg, built):
-    with pkg.Embedder.random_init(pkg.weights.TINY, seed=1234) as emb:
+def tiny(pkg, built, fmt):
+    with pkg.Embedder.random_init(pkg.weights.TINY, seed=1234, operands=fmt) as emb:
         yield emb
 
 
 @pytest.fixture(scope="module")
-def minilm(pkg, built):
-    with pkg.Embedder.random_init(pkg.weights.MINILM_L6, seed=1234) as emb:
+def minilm(pkg, built, fmt):
+    with pkg.Embedder.random_init(pkg.weights.MINILM_L6, seed=1234, operands=fmt) as emb:
         yield emb
 
 
 def oracle_pair(emb, shape):
     """The f32 oracle on the handle's weights, and on those weights with the matrices rounded to bf16."""
-    from gpu_util import bf16_round
+    from gpu_util import round16
     w = emb.export_weights()
-    w16 = {k: bf16_round(v) if (v.ndim == 2 and "embeddings" not in k) else v for k, v in w.items()}
+    w16 = {k: round16(v, "bf16") if (v.ndim == 2 and "embeddings" not in k) else v for k, v in w.items()}
     return Oracle(shape, w, "f32"), Oracle(shape, w16, "f32")
+
+
+def same_weights(o16, tag, ids, tt, mask):
+    """the bf16-weights oracle result (only the bf16 parametrisation needs it)"""
+    return cached(tag + ":w16", lambda: o16.generate(ids, tt, mask, chunk=8)) if FMT == "bf16" else None
 
 
 @pytest.mark.parametrize("fp32", [False, True])
 @pytest.mark.parametrize("name", ["tiny_dense", "tiny_ragged", "tiny_single"])
 def test_golden_tiny(pkg, built, name, fp32):
     g = load_golden(name)
-    with pkg.Embedder.random_init(pkg.weights.TINY, seed=int(g["seed"])) as emb:
+    with pkg.Embedder.random_init(pkg.weights.TINY, seed=int(g["seed"]), operands=FMT) as emb:
         got = emb.forward(g["ids"], g["mask"], g["type_ids"], flags=pkg.FLAG_FP32 if fp32 else 0)
     check(got, g["expected_hf_f64"], fp32)
     check(got, g["expected_oracle_f32"], fp32)
 
 
 @pytest.fixture(scope="module")
-def minilm_fused(pkg, built):
+def minilm_fused(pkg, built, fmt):
     """Same weights, with the fused kernels (K23, K2f) forced on for every call size: by default calls this small
     take the unfused schedule (the switches are read when the handle is created)."""
     old = {k: os.environ.get(k) for k in ("B200_EMBED_FFN_FUSED", "B200_EMBED_QKV_ATTN")}
     os.environ["B200_EMBED_FFN_FUSED"] = "1"
     os.environ["B200_EMBED_QKV_ATTN"] = "1"
     try:
-        emb = pkg.Embedder.random_init(pkg.weights.MINILM_L6, seed=1234)
+        emb = pkg.Embedder.random_init(pkg.weights.MINILM_L6, seed=1234, operands=fmt)
     finally:  # the switches are read at create: restore at once so that no other handle inherits them
         for k, v in old.items():
             if v is None:
@@ -105,12 +133,10 @@ def test_fused_schedule_golden_and_ragged(pkg, minilm, minilm_fused):
     lengths = np.array([2, 2, 7, 31, 32, 33, 63, 64, 65, 100, 127, 128, 128, 5, 90, 17, 64, 3])
     ids, mask, tt = pkg.synth.padded_batch(shape.vocab_size, lengths, 128, seed=9)
     o, o16 = oracle_pair(minilm, shape)
-    want = o.generate(ids, tt, mask, chunk=8)
+    want = cached("fused_ragged", lambda: o.generate(ids, tt, mask, chunk=8))
     got = minilm_fused.forward(ids, mask, tt)
-    check(got, want, False, o16.generate(ids, tt, mask, chunk=8), lengths)
-    other = minilm.forward(ids, mask, tt)
-    assert np.abs(got - other).max() <= 4e-3  # two bf16 schedules of the same math
-    assert cos_rows(got, other).min() >= 0.9999
+    check(got, want, False, same_weights(o16, "fused_ragged", ids, tt, mask), lengths)
+    close_schedules(got, minilm.forward(ids, mask, tt))
 
 
 def test_auto_schedule_switches_to_fused_kernels(pkg, minilm):
@@ -124,8 +150,7 @@ def test_auto_schedule_switches_to_fused_kernels(pkg, minilm):
     assert minilm.kernel_launches() - n0 == 2 + 1 + 1 + shape.num_hidden_layers * 3 + 1
     small = np.concatenate([minilm.forward(ids[i:i + 40], mask[i:i + 40], tt[i:i + 40]) for i in range(0, 320, 40)])
     assert np.isfinite(big).all()
-    assert np.abs(big - small).max() <= 4e-3
-    assert cos_rows(big, small).min() >= 0.9999
+    close_schedules(big, small)
 
 
 @pytest.mark.parametrize("fp32", [False, True])
@@ -141,11 +166,11 @@ def test_config1_b32_s128_vs_oracle(pkg, minilm):
     shape = pkg.weights.MINILM_L6
     ids, mask, tt = pkg.synth.padded_batch(shape.vocab_size, pkg.synth.lengths_dense(32, 128), 128, seed=42)
     o, o16 = oracle_pair(minilm, shape)
-    want = o.generate(ids, tt, mask, chunk=8)
-    check(minilm.forward(ids, mask, tt), want, False, o16.generate(ids, tt, mask, chunk=8))
+    want = cached("c1", lambda: o.generate(ids, tt, mask, chunk=8))
+    check(minilm.forward(ids, mask, tt), want, False, same_weights(o16, "c1", ids, tt, mask))
     check(minilm.forward(ids, mask, tt, flags=pkg.FLAG_FP32), want, True)
     got_n = minilm.forward(ids, mask, tt, flags=pkg.FLAG_NORMALIZE)  # the north_star output
-    assert np.abs(got_n - o.l2_normalize(want)).max() <= BF16_ABS
+    assert np.abs(got_n - o.l2_normalize(want)).max() <= GATE_ABS
 
 
 def test_config3_ragged_8_512_vs_oracle(pkg, minilm):
@@ -154,14 +179,14 @@ def test_config3_ragged_8_512_vs_oracle(pkg, minilm):
     lengths = np.concatenate([pkg.synth.lengths_loguniform(10, 8, 512, seed=7), [8, 512, 8, 512, 2, 511]])
     ids, mask, tt = pkg.synth.padded_batch(shape.vocab_size, lengths, 512, seed=42)
     o, o16 = oracle_pair(minilm, shape)
-    want = o.generate(ids, tt, mask, chunk=8)  # reference schedule
+    want = cached("c3", lambda: o.generate(ids, tt, mask, chunk=8))  # reference schedule
     got = minilm.forward(ids, mask, tt)
-    check(got, want, False, o16.generate(ids, tt, mask, chunk=8), lengths)
+    check(got, want, False, same_weights(o16, "c3", ids, tt, mask), lengths)
     pi, pt, cu = pkg.synth.pack(ids, mask, tt)
     got_v = minilm.forward_varlen(pi, pt, cu, 512)
     # The padded call is scheduled by its bound batch * seq_len (8192 tokens: fused FFN), the packed one by its real
     # token count (unfused): two bf16 schedules of the same math.
-    assert np.abs(got - got_v).max() <= 4e-3 and cos_rows(got, got_v).min() >= 0.9999
+    close_schedules(got, got_v)
     # Calls that take the same schedule run the same kernels on the same packed layout: bit-identical.
     p4 = pkg.synth.pack(ids[:4], mask[:4], tt[:4])
     assert np.array_equal(minilm.forward(ids[:4], mask[:4], tt[:4]), minilm.forward_varlen(p4[0], p4[1], p4[2], 512))
@@ -174,10 +199,10 @@ def test_config4_shape_bert_base_two_layers(pkg, built):
     shape = pkg.weights.BertShape(30522, 768, 2, 12, 3072, 512, 2)
     lengths = np.concatenate([pkg.synth.lengths_uniform(20, 4, 256, seed=5), [256, 255, 129, 128]])
     ids, mask, tt = pkg.synth.padded_batch(shape.vocab_size, lengths, 256, seed=42)
-    with pkg.Embedder.random_init(shape, seed=77) as emb:
+    with pkg.Embedder.random_init(shape, seed=77, operands=FMT) as emb:
         o, o16 = oracle_pair(emb, shape)
-        want = o.generate(ids, tt, mask, chunk=8)
-        check(emb.forward(ids, mask, tt), want, False, o16.generate(ids, tt, mask, chunk=8), lengths)
+        want = cached("c4x2", lambda: o.generate(ids, tt, mask, chunk=8))
+        check(emb.forward(ids, mask, tt), want, False, same_weights(o16, "c4x2", ids, tt, mask), lengths)
         check(emb.forward(ids, mask, tt, flags=pkg.FLAG_FP32), want, True)
 
 
@@ -212,8 +237,8 @@ def test_chunked_launches_match_single_launch(pkg):
     shape = pkg.weights.TINY
     lengths = pkg.synth.lengths_uniform(37, 2, 64, seed=1)
     ids, mask, tt = pkg.synth.padded_batch(shape.vocab_size, lengths, 64)
-    with pkg.Embedder.random_init(shape, seed=1234) as a, \
-            pkg.Embedder.random_init(shape, seed=1234, max_tokens_per_launch=5 * 64) as b:
+    with pkg.Embedder.random_init(shape, seed=1234, operands=FMT) as a, \
+            pkg.Embedder.random_init(shape, seed=1234, max_tokens_per_launch=5 * 64, operands=FMT) as b:
         ra, rb = a.forward(ids, mask, tt), b.forward(ids, mask, tt)
         pi, pt, cu = pkg.synth.pack(ids, mask, tt)
         rc = b.forward_varlen(pi, pt, cu, 64)
@@ -240,9 +265,9 @@ def test_permutation_and_padding_invariance_at_scale(pkg, minilm):
     perm = np.random.default_rng(0).permutation(len(lengths))
     for other, ref in ((minilm.forward(ids[perm], mask[perm], tt[perm]), base[perm]),
                        (minilm.forward(wide(ids), wide(mask), wide(tt)), base)):
-        assert np.abs(other - ref).max() <= 4e-3 and cos_rows(other, ref).min() >= 0.9999
+        close_schedules(other, ref)
     sub = np.arange(0, 1024, 97)
-    want = Oracle(shape, minilm.export_weights(), "f32").generate(ids[sub], tt[sub], mask[sub])
+    want = cached("perm_sub", lambda: Oracle(shape, minilm.export_weights(), "f32").generate(ids[sub], tt[sub], mask[sub]))
     check(base[sub], want, False)
 
 
@@ -305,7 +330,7 @@ def test_embedding_generator_end_to_end_text(pkg, built, tmp_path):
     json.dump(cfg, open(tmp_path / "config.json", "w"))
     w = pkg.weights.init_weights(shape, 5)
     pkg.weights.save_safetensors(str(tmp_path / "model.safetensors"), w)
-    gen = pkg.EmbeddingGenerator.new(str(tmp_path))
+    gen = pkg.EmbeddingGenerator.new(str(tmp_path), operands=FMT)
     try:
         assert gen.generate_sentence_embeddings([]) == []
         sents = ["The quick brown fox jumps over the lazy dog.", "A symbiont reads web pages!", "Embeds sentences?"] * 4
@@ -326,8 +351,7 @@ def test_embedding_generator_end_to_end_text(pkg, built, tmp_path):
         assert split == sents + ["trailing words"] and vecs.shape == (len(sents) + 1, shape.hidden_size)
         # process_raw_text goes through the packed entries (encode_packed -> forward_varlen): same values as the padded
         # call up to the bf16 schedule (the same sentences in a different batch composition)
-        assert np.abs(vecs[:len(sents)] - np.array(out, np.float32)).max() <= 4e-3
-        assert cos_rows(vecs[:len(sents)], np.array(out, np.float32)).min() >= 0.9999
+        close_schedules(vecs[:len(sents)], np.array(out, np.float32))
         with pytest.raises(ValueError, match="Cleaned text is empty for id: doc7"):
             gen.process_raw_text(" \n\t ", "doc7")
     finally:
@@ -344,13 +368,13 @@ def test_graph_replay_is_bit_identical_and_survives_reallocation(pkg, built, mon
     other = pkg.synth.padded_batch(shape.vocab_size, [9, 2, 30], 32, seed=2)
     big = pkg.synth.padded_batch(shape.vocab_size, [128] * 96, 128, seed=3)
     monkeypatch.setenv("B200_EMBED_GRAPHS", "0")
-    with pkg.Embedder.random_init(shape, seed=11) as plain:
+    with pkg.Embedder.random_init(shape, seed=11, operands=FMT) as plain:
         want_small, want_other, want_big = plain.forward(*small), plain.forward(*other), plain.forward(*big)
         n0 = plain.kernel_launches()
         plain.forward(*small)
         per_call = plain.kernel_launches() - n0
     monkeypatch.delenv("B200_EMBED_GRAPHS")
-    with pkg.Embedder.random_init(shape, seed=11) as emb:
+    with pkg.Embedder.random_init(shape, seed=11, operands=FMT) as emb:
         for _ in range(4):  # plain, capture + launch, replay, replay
             assert np.array_equal(emb.forward(*small), want_small)
             assert np.array_equal(emb.forward(*other), want_other)  # two shapes interleaved
@@ -384,7 +408,7 @@ def test_pipeline_text_to_json(pkg, built, tmp_path):
     ing = pkg.abi.Ingest(str(tmp_path / "tokenizer.json"))
     sents = ["The quick brown fox jumps over the lazy dog.", "A symbiont reads web pages!", "Embeds sentences?", "Dogs."]
     raw = "  ".join(sents[i % 4] for i in range(203)) + " trailing words"
-    with pkg.Embedder.random_init(shape, seed=5) as emb:
+    with pkg.Embedder.random_init(shape, seed=5, operands=FMT) as emb:
         one, n = pkg.abi.pipeline_text_to_json(emb, ing, raw, "doc-1", "http://x/y", "tiny", 1234, chunk_sentences=100000)
         cleaned, begin, end = pkg.abi.split_sentences(raw)
         ids, tt, cu = ing.encode_ranges_packed(cleaned, begin, end, shape.max_position_embeddings)
@@ -397,6 +421,6 @@ def test_pipeline_text_to_json(pkg, built, tmp_path):
         assert [d["sentence_text"] for d in b["embeddings_data"]] == [d["sentence_text"] for d in a["embeddings_data"]]
         va = np.array([d["embedding"] for d in a["embeddings_data"]], np.float32)
         vb = np.array([d["embedding"] for d in b["embeddings_data"]], np.float32)
-        assert np.abs(va - vb).max() <= 4e-3 and cos_rows(va, vb).min() >= 0.9999
+        close_schedules(va, vb)
         with pytest.raises(pkg.abi.B200EmbedError, match="Cleaned text is empty"):
             pkg.abi.pipeline_text_to_json(emb, ing, " \n ", "d", "u", "m", 1)

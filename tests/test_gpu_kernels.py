@@ -1,25 +1,41 @@
 """GPU: every kernel of the path, called through the C ABI (b200_op_*), against the CPU oracle on the
-same seeded inputs. bf16 kernels are compared with the oracle running on bf16-rounded weights and
-inputs (so only accumulation order and the output rounding differ); fp32 kernels with the oracle as is."""
+same seeded inputs. The 16-bit kernels are compared with the oracle running on weights and inputs rounded to the
+operand format (so only accumulation order and the output rounding differ); fp32 kernels with the oracle as is.
+Every test runs once per operand format (bf16 and IEEE fp16: the same kernels compiled twice, csrc/fmt.h)."""
 import numpy as np
 import pytest
 import torch
 
 from conftest import cos_rows
-from gpu_util import dev, dev_u32, dev_i32, bf16_round, host, padded_to_packed, cu_of
+from gpu_util import dev, dev_u32, dev_i32, round16, T16, host, padded_to_packed, cu_of
 from oracle.oracle import Oracle
 
 pytestmark = pytest.mark.gpu
 
 LENGTHS = [2, 3, 16, 33, 64, 64, 17, 9, 1, 40]
 
+FMT = "bf16"          # operand format of the running parametrisation (set by the fixture below)
+td16 = T16["bf16"]  # its torch dtype
+
+
+def rnd(a):
+    return round16(a, FMT)
+
+
+@pytest.fixture(scope="module", params=["bf16", "f16"], autouse=True)
+def fmt(request):
+    global FMT, td16
+    FMT, td16 = request.param, T16[request.param]
+    return request.param
+
 
 @pytest.fixture(scope="module")
-def env(pkg, built):
+def env(pkg, built, fmt):
     shape = pkg.weights.TINY
-    emb = pkg.Embedder.random_init(shape, seed=1234, device=0)
+    emb = pkg.Embedder.random_init(shape, seed=1234, device=0, operands=fmt)
+    assert emb.operands == fmt
     w = emb.export_weights()
-    w16 = {k: bf16_round(v) if v.ndim == 2 else v for k, v in w.items()}
+    w16 = {k: rnd(v) if v.ndim == 2 else v for k, v in w.items()}
     yield pkg, shape, emb, w, Oracle(shape, w, "f32"), Oracle(shape, w16, "f32")
     emb.close()
 
@@ -37,7 +53,7 @@ def test_safetensors_load_equals_random_init(env, tmp_path):
     pkg, shape, emb, w, _, _ = env
     p = str(tmp_path / "model.safetensors")
     pkg.weights.save_safetensors(p, {"bert." + k: v for k, v in w.items()})  # candle's prefix fallback
-    with pkg.Embedder(shape, p, device=0) as e2:
+    with pkg.Embedder(shape, p, device=0, operands=FMT) as e2:
         w2 = e2.export_weights()
     assert all(np.array_equal(w[k], w2[k]) for k in w)
 
@@ -51,7 +67,7 @@ def test_k1_embed_layernorm(env, dtype):
     want = padded_to_packed(o32.embeddings(ids, tt), lengths)
     pi, pt, cu = pkg.synth.pack(ids, mask, tt)
     T = int(cu[-1])
-    td = torch.float32 if dtype else torch.bfloat16
+    td = torch.float32 if dtype else td16
     out = torch.empty((T, shape.hidden_size), dtype=td, device="cuda")
     out_lo = torch.empty_like(out)
     d_pi, d_pt, d_cu = dev_u32(pi), dev_u32(pt), dev_i32(cu)
@@ -75,11 +91,11 @@ def test_gemm_tcgen05_vs_fp32(env, m, n, k, block_n, act):
     """K2 mainloop + bias/activation epilogue vs an fp32 reference of the same op on the same bf16 inputs."""
     pkg = env[0]
     g = torch.Generator(device="cuda").manual_seed(m * 7 + n + k)
-    a = (torch.randn((m, k), device="cuda", generator=g) * 1.0).bfloat16()
-    b = (torch.randn((n, k), device="cuda", generator=g) * 0.05).bfloat16()
+    a = (torch.randn((m, k), device="cuda", generator=g) * 1.0).to(td16)
+    b = (torch.randn((n, k), device="cuda", generator=g) * 0.05).to(td16)
     bias = torch.randn((n,), device="cuda", generator=g) * 0.1
-    c = torch.full((m, n), float("nan"), dtype=torch.bfloat16, device="cuda")
-    pkg.abi.op_gemm_bf16(a.data_ptr(), b.data_ptr(), bias.data_ptr(), m, n, k, act, block_n, c.data_ptr())
+    c = torch.full((m, n), float("nan"), dtype=td16, device="cuda")
+    (pkg.abi.op_gemm_f16 if FMT == "f16" else pkg.abi.op_gemm_bf16)(a.data_ptr(), b.data_ptr(), bias.data_ptr(), m, n, k, act, block_n, c.data_ptr())
     torch.cuda.synchronize()
     torch.backends.cuda.matmul.allow_tf32 = False
     ref = a.float() @ b.float().t() + bias
@@ -107,7 +123,7 @@ def test_k2_linear_layers(env, dtype, which):
     x = rng.standard_normal((rows, kin)).astype(np.float32)
     res = rng.standard_normal((rows, H)).astype(np.float32)
     if not dtype:
-        x = bf16_round(x)
+        x = rnd(x)
     L = 1
     if which == 0:
         want = np.concatenate([o.linear(x, o.layer(L, f"attention.self.{n}.weight"), o.layer(L, f"attention.self.{n}.bias"))
@@ -122,8 +138,8 @@ def test_k2_linear_layers(env, dtype, which):
         y = o.linear(x, o.layer(L, "output.dense.weight"), o.layer(L, "output.dense.bias"))
         want = o.add_layer_norm(y, res, o.layer(L, "output.LayerNorm.weight"), o.layer(L, "output.LayerNorm.bias"),
                                 shape.layer_norm_eps)
-    td = torch.float32 if dtype else torch.bfloat16
-    res_hi = bf16_round(res)
+    td = torch.float32 if dtype else td16
+    res_hi = rnd(res)
     dx, dr, dr_lo = dev(x, td), dev(res, td), dev(res - res_hi, td)  # residual = hi + lo in bf16 mode
     out = torch.full(want.shape, float("nan"), dtype=td, device="cuda")
     out_lo = torch.full(want.shape, float("nan"), dtype=td, device="cuda")
@@ -145,17 +161,17 @@ def test_k2f_fused_ffn(pkg, built, H, heads, I, rows):
     shape = pkg.weights.BertShape(512, H, 1, heads, I, 64, 2)
     rng = np.random.default_rng(H)
     x = rng.standard_normal((rows, H)).astype(np.float32)
-    x_hi = bf16_round(x)
-    with pkg.Embedder.random_init(shape, seed=4) as emb:
+    x_hi = rnd(x)
+    with pkg.Embedder.random_init(shape, seed=4, operands=FMT) as emb:
         w = emb.export_weights()
-        o = Oracle(shape, {k: bf16_round(v) if v.ndim == 2 else v for k, v in w.items()}, "f32")
+        o = Oracle(shape, {k: rnd(v) if v.ndim == 2 else v for k, v in w.items()}, "f32")
         inter = o.activation(o.linear(x_hi, o.layer(0, "intermediate.dense.weight"), o.layer(0, "intermediate.dense.bias")), 0)
-        y = o.linear(bf16_round(inter), o.layer(0, "output.dense.weight"), o.layer(0, "output.dense.bias"))
+        y = o.linear(rnd(inter), o.layer(0, "output.dense.weight"), o.layer(0, "output.dense.bias"))
         want = o.add_layer_norm(y, x, o.layer(0, "output.LayerNorm.weight"), o.layer(0, "output.LayerNorm.bias"),
                                 shape.layer_norm_eps)
-        dx, dx_lo = dev(x, torch.bfloat16), dev(x - x_hi, torch.bfloat16)
-        out = torch.full((rows, H), float("nan"), dtype=torch.bfloat16, device="cuda")
-        out_lo = torch.full((rows, H), float("nan"), dtype=torch.bfloat16, device="cuda")
+        dx, dx_lo = dev(x, td16), dev(x - x_hi, td16)
+        out = torch.full((rows, H), float("nan"), dtype=td16, device="cuda")
+        out_lo = torch.full((rows, H), float("nan"), dtype=td16, device="cuda")
         emb.op_ffn(0, dx.data_ptr(), dx_lo.data_ptr(), rows, out.data_ptr(), out_lo.data_ptr())
         got, got_lo = host(out), host(out_lo)
     assert np.isfinite(got).all() and np.isfinite(got_lo).all()
@@ -173,18 +189,18 @@ def test_k2_layernorm_epilogue_across_hidden_sizes(pkg, built, H, heads, I, whic
     rows = 1000
     rng = np.random.default_rng(H + which)
     kin = I if which == 3 else H
-    x = bf16_round(rng.standard_normal((rows, kin)).astype(np.float32))
+    x = rnd(rng.standard_normal((rows, kin)).astype(np.float32))
     res = rng.standard_normal((rows, H)).astype(np.float32) * 2
-    with pkg.Embedder.random_init(shape, seed=2) as emb:
+    with pkg.Embedder.random_init(shape, seed=2, operands=FMT) as emb:
         w = emb.export_weights()
-        o = Oracle(shape, {k: bf16_round(v) if v.ndim == 2 else v for k, v in w.items()}, "f32")
+        o = Oracle(shape, {k: rnd(v) if v.ndim == 2 else v for k, v in w.items()}, "f32")
         pre = "attention.output" if which == 1 else "output"
         y = o.linear(x, o.layer(0, pre + ".dense.weight"), o.layer(0, pre + ".dense.bias"))
         want = o.add_layer_norm(y, res, o.layer(0, pre + ".LayerNorm.weight"), o.layer(0, pre + ".LayerNorm.bias"),
                                 shape.layer_norm_eps)
-        dx, dr, dr_lo = dev(x, torch.bfloat16), dev(res, torch.bfloat16), dev(res - bf16_round(res), torch.bfloat16)
-        out = torch.full(want.shape, float("nan"), dtype=torch.bfloat16, device="cuda")
-        out_lo = torch.full(want.shape, float("nan"), dtype=torch.bfloat16, device="cuda")
+        dx, dr, dr_lo = dev(x, td16), dev(res, td16), dev(res - rnd(res), td16)
+        out = torch.full(want.shape, float("nan"), dtype=td16, device="cuda")
+        out_lo = torch.full(want.shape, float("nan"), dtype=td16, device="cuda")
         emb.op_linear(0, which, dx.data_ptr(), dr.data_ptr(), rows, 0, out.data_ptr(), d_residual_lo=dr_lo.data_ptr(),
                       d_y_lo=out_lo.data_ptr())
         got, got_lo = host(out), host(out_lo)
@@ -193,7 +209,7 @@ def test_k2_layernorm_epilogue_across_hidden_sizes(pkg, built, H, heads, I, whic
     assert np.abs(got + got_lo - want).max() <= 2e-3
 
 
-@pytest.mark.parametrize("dtype", [0, 1, 2])
+@pytest.mark.parametrize("dtype", [0, 1])
 @pytest.mark.parametrize("heads,d", [(4, 32), (2, 64)])
 def test_k3_attention(env, pkg, dtype, heads, d):
     """Varlen attention vs the oracle's padded additive-mask softmax; ragged lengths incl. 1 and > 64."""
@@ -203,13 +219,13 @@ def test_k3_attention(env, pkg, dtype, heads, d):
     rng = np.random.default_rng(11)
     q, k, v = (rng.standard_normal((len(lengths), S, H)).astype(np.float32) for _ in range(3))
     if dtype != 1:
-        q, k, v = bf16_round(q), bf16_round(k), bf16_round(v)
+        q, k, v = rnd(q), rnd(k), rnd(v)
     mask = (np.arange(S)[None, :] < lengths[:, None]).astype(np.uint32)
-    with pkg.Embedder.random_init(shape, seed=1) as e:
+    with pkg.Embedder.random_init(shape, seed=1, operands=FMT) as e:
         o = Oracle(shape, e.export_weights(), "f32")
         want = padded_to_packed(o.attention(q, k, v, mask, heads), lengths)
         qkv = np.concatenate([padded_to_packed(t, lengths) for t in (q, k, v)], axis=1)
-        td = torch.float32 if dtype == 1 else torch.bfloat16
+        td = torch.float32 if dtype == 1 else td16
         dq = dev(qkv, td)
         ctx = torch.full(want.shape, float("nan"), dtype=td, device="cuda")
         d_cu = dev_i32(cu_of(lengths))
@@ -237,18 +253,18 @@ def test_k23_qkv_attention_fused(pkg, built, heads, lens):
                else np.random.default_rng(7).integers(1, 4, size=301))
     S = 128
     rng = np.random.default_rng(heads)
-    x = bf16_round(rng.standard_normal((len(lengths), S, H)).astype(np.float32))
+    x = rnd(rng.standard_normal((len(lengths), S, H)).astype(np.float32))
     mask = (np.arange(S)[None, :] < lengths[:, None]).astype(np.uint32)
-    with pkg.Embedder.random_init(shape, seed=5) as e:
+    with pkg.Embedder.random_init(shape, seed=5, operands=FMT) as e:
         w = e.export_weights()
-        o = Oracle(shape, {k: bf16_round(v) if v.ndim == 2 else v for k, v in w.items()}, "f32")
+        o = Oracle(shape, {k: rnd(v) if v.ndim == 2 else v for k, v in w.items()}, "f32")
         pre = "attention.self."
-        q, k, v = (bf16_round(o.linear(x.reshape(-1, H), o.layer(0, pre + n + ".weight"), o.layer(0, pre + n + ".bias"))
+        q, k, v = (rnd(o.linear(x.reshape(-1, H), o.layer(0, pre + n + ".weight"), o.layer(0, pre + n + ".bias"))
                               .reshape(len(lengths), S, H)) for n in ("query", "key", "value"))
         want = padded_to_packed(o.attention(q, k, v, mask, heads), lengths)
         xp = padded_to_packed(x, lengths)
-        dx = dev(xp, torch.bfloat16)
-        ctx = torch.full(want.shape, float("nan"), dtype=torch.bfloat16, device="cuda")
+        dx = dev(xp, td16)
+        ctx = torch.full(want.shape, float("nan"), dtype=td16, device="cuda")
         d_cu = dev_i32(cu_of(lengths))
         e.op_qkv_attention(0, dx.data_ptr(), d_cu.data_ptr(), len(lengths), xp.shape[0], S, ctx.data_ptr())
         got = host(ctx)
@@ -265,14 +281,14 @@ def test_k4_add_layernorm(env, mode):
     y = rng.standard_normal((rows, H)).astype(np.float32) * 2
     r = rng.standard_normal((rows, H)).astype(np.float32)
     if mode == "bf16":
-        y = bf16_round(y)
+        y = rnd(y)
     want = o32.add_layer_norm(y, r, o32.layer(0, "output.LayerNorm.weight"), o32.layer(0, "output.LayerNorm.bias"),
                               shape.layer_norm_eps)
-    td = torch.float32 if mode == "fp32" else torch.bfloat16
-    dy = dev(y, torch.bfloat16 if mode == "bf16" else torch.float32)
+    td = torch.float32 if mode == "fp32" else td16
+    dy = dev(y, td16 if mode == "bf16" else torch.float32)
     out = torch.empty((rows, H), dtype=td, device="cuda")
     out_lo = torch.empty_like(out)
-    r_hi = bf16_round(r)
+    r_hi = rnd(r)
     d_r, d_r_lo = dev(r, td), dev(r - r_hi, td)
     emb.op_add_layernorm(0, 3, dy.data_ptr(), mode != "bf16", d_r.data_ptr(), rows, int(mode == "fp32"),
                          out.data_ptr(), d_residual_lo=0 if mode == "fp32" else d_r_lo.data_ptr(),
@@ -296,10 +312,10 @@ def test_k5_mean_pool(env, dtype, normalize):
     want = o32.mean_pool(hid, mask)
     if normalize:
         want = o32.l2_normalize(want)
-    td = torch.float32 if dtype else torch.bfloat16
+    td = torch.float32 if dtype else td16
     out = torch.empty((len(lengths), H), dtype=torch.float32, device="cuda")
     packed = padded_to_packed(hid, lengths)
-    d_h, d_lo, d_cu = dev(packed, td), dev(packed - bf16_round(packed), td), dev_i32(cu_of(lengths))
+    d_h, d_lo, d_cu = dev(packed, td), dev(packed - rnd(packed), td), dev_i32(cu_of(lengths))
     emb.op_mean_pool(d_h.data_ptr(), d_cu.data_ptr(), len(lengths), dtype, normalize, out.data_ptr(),
                      d_hidden_lo=0 if dtype else d_lo.data_ptr())
     got = host(out)
@@ -312,15 +328,15 @@ def test_k2_layernorm_gemm_refuses_operands_outside_this_gpus_memory(pkg, built)
     refused with an error before anything is launched; the same call with a device operand works."""
     shape = pkg.weights.BertShape(512, 384, 1, 12, 1536, 64, 2)
     rows = 256
-    with pkg.Embedder.random_init(shape, seed=2) as emb:
+    with pkg.Embedder.random_init(shape, seed=2, operands=FMT) as emb:
         x_host = pkg.abi.host_alloc((rows, 384), np.uint16)
         x_host[:] = 0
-        res = torch.zeros((rows, 384), dtype=torch.bfloat16, device="cuda")
+        res = torch.zeros((rows, 384), dtype=td16, device="cuda")
         out, out_lo = torch.empty_like(res), torch.empty_like(res)
         with pytest.raises(pkg.abi.B200EmbedError):
             emb.op_linear(0, 1, x_host.ctypes.data, res.data_ptr(), rows, 0, out.data_ptr(), d_residual_lo=res.data_ptr(),
                           d_y_lo=out_lo.data_ptr())
-        x_dev = torch.zeros((rows, 384), dtype=torch.bfloat16, device="cuda")
+        x_dev = torch.zeros((rows, 384), dtype=td16, device="cuda")
         emb.op_linear(0, 1, x_dev.data_ptr(), res.data_ptr(), rows, 0, out.data_ptr(), d_residual_lo=res.data_ptr(),
                       d_y_lo=out_lo.data_ptr())
         torch.cuda.synchronize()
