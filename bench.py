@@ -20,6 +20,11 @@ plumbing). One JSON line is printed by rank 0:
             cannot be built in this image) on the host cores, in the reference's own schedule
             (chunks of 8 sentences, each padded to max_position_embeddings, embedding_generator.rs:146,:75)
 
+  parity    rows of the timed c2-sized calls (dense, and a ragged 8..128 variant of the same batch size) against the f32
+            oracle on the same ids and weights, for both operand formats of the 16-bit path
+  workloads short runs of the other BASELINE configs (c3 ragged 8..512, c4 BERT-base 8192 x 256, c5 corpus lengths) and of
+            c2 in the other operand format, same timing method
+
 --impl reference times that same CPU path as the reference arm (rank 0 only).
 """
 from __future__ import annotations
@@ -122,9 +127,23 @@ def make_lengths(pkg, batch, seq, ragged, seed):
     return pkg.synth.lengths_dense(batch, seq)
 
 
+def algorithmic_bytes(shape, lengths, kind):
+    """SURVEY.md section 8(d) bytes of one pass of an HBM-bound kind: single 16-bit activations, no (hi, lo) pair, no
+    fp32 table rows - what an ideal implementation would have to move. None where the survey states no figure."""
+    H = shape.hidden_size
+    T, B = float(np.sum(lengths)), len(lengths)
+    if kind == "embed_ln":
+        return (4 * H + 12) * T
+    if kind in ("add_ln", "gemm_attn_out"):
+        return 6 * H * T
+    if kind == "pool":
+        return 2 * H * T + 4 * T + 4 * H * B
+    return None
+
+
 def kernel_work(shape, lengths, kind):
-    """Algorithmic (FLOPs, HBM bytes) of ONE launch of a kernel kind for this batch. The kernel's
-    roofline is whichever of the two takes longer at the measured peaks."""
+    """(FLOPs, HBM bytes the kernel actually has to move in this design) of ONE launch of a kernel kind for this batch
+    (DESIGN.md section 5). The kernel's roofline is whichever of the two takes longer at the measured peaks."""
     H, I = shape.hidden_size, shape.intermediate_size
     T = float(np.sum(lengths))
     s2 = float(np.sum(np.asarray(lengths, dtype=np.float64) ** 2))
@@ -154,17 +173,48 @@ def kernel_work(shape, lengths, kind):
     raise KeyError(kind)
 
 
-def cpu_reference_path(pkg, shape, n_sentences, s, schedule, seed=42):
+def cpu_reference_path(pkg, shape, n_sentences, s, schedule, seed=42, native=False):
     """The reference's CPU path via the oracle port. schedule "reference": chunks of 8 padded to P
-    (embedding_generator.rs:146, :75); "fair": one batch padded to s."""
+    (embedding_generator.rs:146, :75); "fair": one batch padded to s. native: the build for the TIMED legs
+    (-march=native -ffp-contract=fast, compiled on this host) instead of the portable one the parity tests use."""
     from oracle.oracle import Oracle
     w = pkg.weights.init_weights(shape, 1234)
-    o = Oracle(shape, w, "f32")
+    o = Oracle(shape, w, "f32", native=native)
     o.use_all_cores()
     pad = shape.max_position_embeddings if schedule == "reference" else s
     ids, mask, tt = pkg.synth.padded_batch(shape.vocab_size, pkg.synth.lengths_dense(n_sentences, s), pad, seed=seed)
     chunk = 8 if schedule == "reference" else n_sentences
     return o, (ids, tt, mask, chunk)
+
+
+def hf_torch_cpu_c1(pkg, shape):
+    """BASELINE.md section 4, third line: HuggingFace BertModel on torch-CPU for c1 (32 x 128, f32) - an independent
+    calibration of how fast a tuned CPU GEMM stack runs the same math (not the reference, not a target)."""
+    try:
+        import torch
+        from transformers import BertConfig, BertModel
+        torch.set_num_threads(len(os.sched_getaffinity(0)))
+        cfg = BertConfig(vocab_size=shape.vocab_size, hidden_size=shape.hidden_size, num_hidden_layers=shape.num_hidden_layers,
+                         num_attention_heads=shape.num_attention_heads, intermediate_size=shape.intermediate_size,
+                         max_position_embeddings=shape.max_position_embeddings, type_vocab_size=shape.type_vocab_size,
+                         layer_norm_eps=shape.layer_norm_eps, hidden_act="gelu", attn_implementation="eager")
+        model = BertModel(cfg, add_pooling_layer=False).eval()
+        ids, mask, tt = pkg.synth.padded_batch(shape.vocab_size, pkg.synth.lengths_dense(32, 128), 128, seed=42)
+        ti, tm, ty = (torch.from_numpy(a.astype(np.int64)) for a in (ids, mask, tt))
+        with torch.no_grad():
+            def once():
+                h = model(input_ids=ti, attention_mask=tm, token_type_ids=ty).last_hidden_state
+                m = tm[:, :, None].float()
+                return (h * m).sum(1) / (m.sum(1) + 1e-9)
+            once()
+            t0 = time.perf_counter()
+            for _ in range(3):
+                once()
+            dt = (time.perf_counter() - t0) / 3
+        return {"value": 32 / dt, "unit": UNIT, "ms_per_batch": 1e3 * dt, "threads": torch.get_num_threads(),
+                "what": "transformers BertModel (eager, f32) + the pooling formula on torch-CPU, MiniLM-L6 shape, 32 x 128"}
+    except Exception as e:  # the baseline line is informative only
+        return {"unavailable": f"{type(e).__name__}: {e}"[:200]}
 
 
 def run_reference(args, pkg, rank):
@@ -173,7 +223,7 @@ def run_reference(args, pkg, rank):
     shape_key, batch, seq, ragged = WORKLOADS[args.workload]
     shape = pkg.weights.SHAPES[shape_key]
     n = 8  # one reference chunk per step: a bounded sample of the workload
-    o, (ids, tt, mask, chunk) = cpu_reference_path(pkg, shape, n, seq, "reference")
+    o, (ids, tt, mask, chunk) = cpu_reference_path(pkg, shape, n, seq, "reference", native=True)
     for _ in range(max(args.warmup, 1)):
         o.generate(ids, tt, mask, chunk=chunk)
     t0 = time.perf_counter()
@@ -183,7 +233,7 @@ def run_reference(args, pkg, rank):
     v = n * args.steps / dt
     sample = (f"{n} sentences of {seq} tokens per step, reference schedule: one chunk of 8 padded to "
               f"max_position_embeddings={shape.max_position_embeddings} (embedding_generator.rs:146,:75), f32, "
-              "C oracle port of the candle CPU path (the Rust reference cannot be built here)")
+              "C oracle port of the candle CPU path built -O3 -march=native (the Rust reference cannot be built here)")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
@@ -194,104 +244,205 @@ def run_reference(args, pkg, rank):
     }), flush=True)
 
 
+class Dist:
+    """torch.distributed plumbing of the bench: barrier and max over ranks (NCCL); nothing on the data path."""
+
+    def __init__(self, world, local_rank):
+        import torch
+        self.torch, self.world = torch, world
+        if world > 1:
+            import torch.distributed as dist
+            self.dist = dist
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier(self):
+        self.torch.cuda.synchronize()
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def max(self, x: float) -> float:
+        if self.world == 1:
+            return x
+        t = self.torch.tensor([x], dtype=self.torch.float64, device="cuda")
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def close(self):
+        if self.world > 1:
+            self.dist.destroy_process_group()
+
+
+def workload_label(name, shape_key, batch, seq, ragged, operands):
+    return (f"{name}: {shape_key} random-init {operands}, batch {batch} x seq {seq} per GPU"
+            + (" corpus lengths clip(LogNormal(ln 24, 0.6), 4, 128)" if ragged == "corpus"
+               else " ragged log-uniform 8..seq packed varlen" if ragged else " dense"))
+
+
+class Workload:
+    """One BASELINE config on this rank's GPU: synthetic tokenised batch, a handle, and the two timed legs."""
+
+    def __init__(self, pkg, name, operands, rank, local_rank, batch_override=0, normalize=False, emb=None):
+        import torch
+        self.pkg, self.torch, self.name, self.operands = pkg, torch, name, operands
+        self.shape_key, self.batch, self.seq, self.ragged = WORKLOADS[name]
+        if batch_override:
+            self.batch = batch_override
+        self.shape = pkg.weights.SHAPES[self.shape_key]
+        self.H = self.shape.hidden_size
+        self.lengths = make_lengths(pkg, self.batch, self.seq, self.ragged, seed=7 + rank)
+        self.ids, self.mask, self.tt = pkg.synth.padded_batch(self.shape.vocab_size, self.lengths, self.seq, seed=42 + rank)
+        self.flags = pkg.FLAG_NORMALIZE if normalize else 0
+        self.owns = emb is None
+        self.emb = emb or pkg.Embedder.random_init(self.shape, seed=1234, device=local_rank, operands=operands)
+        as_dev = lambda a: torch.from_numpy(a.view(np.int32)).cuda()
+        self.d_ids, self.d_mask, self.d_tt = as_dev(self.ids), as_dev(self.mask), as_dev(self.tt)
+        self.d_out = torch.empty((self.batch, self.H), dtype=torch.float32, device="cuda")
+        self.stream = torch.cuda.Stream()
+        self.local_rank = local_rank
+        uniq, cnt = np.unique(self.lengths, return_counts=True)
+        self.flops_per_step = float(sum(self.shape.flops_per_sentence(int(s)) * int(c) for s, c in zip(uniq, cnt)))
+
+    def label(self):
+        return workload_label(self.name, self.shape_key, self.batch, self.seq, self.ragged, self.operands)
+
+    def step_device(self, stream=None):
+        self.emb.forward_device(self.d_ids.data_ptr(), self.d_mask.data_ptr(), self.d_tt.data_ptr(), self.batch, self.seq,
+                                self.d_out.data_ptr(), flags=self.flags, stream=stream.cuda_stream if stream else 0)
+
+    def device_leg(self, dist, steps, warmup):
+        """inputs resident in HBM, CUDA events on the launching stream, max over ranks"""
+        torch = self.torch
+        with torch.cuda.stream(self.stream):
+            for _ in range(warmup):
+                self.step_device(self.stream)
+        dist.barrier()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n0 = self.emb.kernel_launches()
+        with ClockSampler(self.local_rank) as clocks:
+            with torch.cuda.stream(self.stream):
+                ev0.record(self.stream)
+                for _ in range(steps):
+                    self.step_device(self.stream)
+                ev1.record(self.stream)
+            dist.barrier()
+        launches = self.emb.kernel_launches() - n0
+        dev_ms = dist.max(ev0.elapsed_time(ev1))
+        return dev_ms, launches, clocks.summary()
+
+    def e2e_leg(self, dist, steps, warmup):
+        """public host API (b200_embed_submit / wait), pinned buffers, H2D + D2H inside the timed region"""
+        pkg, emb, nbuf = self.pkg, self.emb, 2
+        pin = [[pkg.abi.host_alloc(a.shape, np.uint32) for a in (self.ids, self.mask, self.tt)] +
+               [pkg.abi.host_alloc((self.batch, self.H), np.float32)] for _ in range(nbuf)]
+        for b in pin:
+            b[0][:], b[1][:], b[2][:] = self.ids, self.mask, self.tt
+
+        def run(n):
+            tickets = [None] * nbuf
+            for i in range(n):
+                k = i % nbuf
+                if tickets[k] is not None:
+                    emb.wait(tickets[k])  # result of step i - nbuf is on the host
+                tickets[k] = emb.submit(pin[k][0], pin[k][1], pin[k][2], pin[k][3], flags=self.flags)
+            for t in tickets:
+                if t is not None:
+                    emb.wait(t)
+
+        run(warmup)
+        dist.barrier()
+        t0 = time.perf_counter()
+        run(steps)
+        self.torch.cuda.synchronize()
+        e2e_s = dist.max(time.perf_counter() - t0)
+        dist.barrier()
+        host_out = pin[0][3].copy()
+        for b in pin:
+            for a in b:
+                pkg.abi.host_free(a)
+        return e2e_s, host_out
+
+    def summary(self, dist, steps, warmup, pk):
+        """a short run for the `workloads` section: both legs, no per-kernel breakdown"""
+        dev_ms, launches, clocks = self.device_leg(dist, steps, warmup)
+        e2e_s, _ = self.e2e_leg(dist, steps, min(warmup, 2))
+        w = dist.world
+        tf = self.flops_per_step * steps / (dev_ms * 1e-3) / 1e12
+        return {"workload": self.label(), "value": w * self.batch * steps / (dev_ms * 1e-3), "unit": UNIT,
+                "ms_per_step": dev_ms / steps, "steps": steps, "warmup": warmup,
+                "e2e": w * self.batch * steps / e2e_s, "tokens_per_step_per_gpu": int(np.sum(self.lengths)),
+                "model_tflops_per_gpu": round(tf, 1), "model_frac_of_sustained_bf16_peak": round(tf / pk["tf_sustained"], 4),
+                "gpu_launches": int(launches), "sm_mhz": clocks["sm_mhz"], "reasons": clocks["reasons"]}
+
+    def close(self):
+        if self.owns:
+            self.emb.close()
+
+
+def parity_stats(got, want):
+    l2 = lambda v: v / np.maximum(np.linalg.norm(v, axis=1, keepdims=True), 1e-12)
+    cos = (got.astype(np.float64) * want).sum(1) / (np.linalg.norm(got, axis=1) * np.linalg.norm(want, axis=1))
+    return {"n": int(len(got)), "cos_min": float(cos.min()), "max_abs_raw": float(np.abs(got - want).max()),
+            "max_abs_l2": float(np.abs(l2(got) - l2(want)).max())}
+
+
+def parity_section(pkg, wl_by_operands):
+    """Rows of c2-SIZED calls (the fused schedule at full occupancy) against the f32 oracle on the same ids and weights:
+    16 sentences of the dense batch the bench times, and 16 of a ragged 8..128 variant of the same batch size (shortest,
+    longest and a spread in between). BASELINE.md section 5 gate: cosine >= 0.9999 and max-abs <= 2e-3 on raw vectors."""
+    from oracle.oracle import Oracle
+    any_wl = next(iter(wl_by_operands.values()))
+    shape, B, S = any_wl.shape, any_wl.batch, any_wl.seq
+    o = Oracle(shape, pkg.weights.init_weights(shape, 1234), "f32")
+    o.use_all_cores()
+    rows_d = np.arange(16)
+    want_d = o.generate(any_wl.ids[rows_d], any_wl.tt[rows_d], any_wl.mask[rows_d], chunk=16)
+    lengths = pkg.synth.lengths_uniform(B, 8, S, seed=11)
+    ids, mask, tt = pkg.synth.padded_batch(shape.vocab_size, lengths, S, seed=43)
+    order = np.argsort(lengths, kind="stable")
+    rows_r = np.unique(np.concatenate([order[:4], order[-4:], order[np.linspace(0, B - 1, 10).astype(int)]]))[:16]
+    want_r = o.generate(ids[rows_r], tt[rows_r], mask[rows_r], chunk=len(rows_r))
+    out = {"vs": "f32 C oracle (port of the candle CPU path), same weights and ids; rows taken from calls of "
+                 f"{B} x {S} (fused K23 + K2f schedule)", "gate": {"cos_min": 0.9999, "max_abs_raw": 2e-3}}
+    for operands, wl in wl_by_operands.items():
+        wl.step_device()
+        dense = wl.d_out[:16].cpu().numpy()
+        ragged = wl.emb.forward(ids, mask, tt)[rows_r]
+        both = parity_stats(np.concatenate([dense, ragged]), np.concatenate([want_d, want_r]))
+        both["dense"], both["ragged_8_128"] = parity_stats(dense, want_d), parity_stats(ragged, want_r)
+        both["meets_gate"] = bool(both["cos_min"] >= 0.9999 and both["max_abs_raw"] <= 2e-3)
+        out[operands] = both
+    return out
+
+
 def run_b200(args, pkg, rank, world, local_rank):
     import torch
-    import torch.distributed as dist
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback "
                          "(use --impl reference for the CPU arm)")
     torch.cuda.set_device(local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-
-    def barrier():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def max_over_ranks(x: float) -> float:
-        if world == 1:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    shape_key, batch, seq, ragged = WORKLOADS[args.workload]
-    if args.batch:
-        batch = args.batch
-    shape = pkg.weights.SHAPES[shape_key]
-    H = shape.hidden_size
-    lengths = make_lengths(pkg, batch, seq, ragged, seed=7 + rank)
-    ids, mask, tt = pkg.synth.padded_batch(shape.vocab_size, lengths, seq, seed=42 + rank)
-    flags = pkg.FLAG_NORMALIZE if args.normalize else 0
-    emb = pkg.Embedder.random_init(shape, seed=1234, device=local_rank)
+    dist = Dist(world, local_rank)
+    pk = peaks()
+    wl = Workload(pkg, args.workload, args.operands, rank, local_rank, args.batch, args.normalize)
+    shape, batch, seq, H, lengths, emb = wl.shape, wl.batch, wl.seq, wl.H, wl.lengths, wl.emb
 
     # ---- leg 1: inputs resident in HBM, CUDA events on the launching stream --------------------
-    as_dev = lambda a: torch.from_numpy(a.view(np.int32)).cuda()
-    d_ids, d_mask, d_tt = as_dev(ids), as_dev(mask), as_dev(tt)
-    d_out = torch.empty((batch, H), dtype=torch.float32, device="cuda")
-    stream = torch.cuda.Stream()
-
-    def step_device():
-        emb.forward_device(d_ids.data_ptr(), d_mask.data_ptr(), d_tt.data_ptr(), batch, seq, d_out.data_ptr(),
-                           flags=flags, stream=stream.cuda_stream)
-
-    with torch.cuda.stream(stream):
-        for _ in range(args.warmup):
-            step_device()
-    barrier()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    n0 = emb.kernel_launches()
-    with ClockSampler(local_rank) as clocks:
-        with torch.cuda.stream(stream):
-            ev0.record(stream)
-            for _ in range(args.steps):
-                step_device()
-            ev1.record(stream)
-        barrier()
-    launches = emb.kernel_launches() - n0
-    dev_ms = max_over_ranks(ev0.elapsed_time(ev1))
+    dev_ms, launches, clocks = wl.device_leg(dist, args.steps, args.warmup)
     value = world * batch * args.steps / (dev_ms * 1e-3)
-
     # ---- leg 2: public host API, pinned buffers, H2D + D2H inside the timed region ---------------
-    nbuf = 2
-    pin = [[pkg.abi.host_alloc(a.shape, np.uint32) for a in (ids, mask, tt)] + [pkg.abi.host_alloc((batch, H), np.float32)]
-           for _ in range(nbuf)]
-    for b in pin:
-        b[0][:], b[1][:], b[2][:] = ids, mask, tt
-
-    def e2e_steps(n):
-        tickets = [None] * nbuf
-        for i in range(n):
-            k = i % nbuf
-            if tickets[k] is not None:
-                emb.wait(tickets[k])  # result of step i - nbuf is on the host
-            tickets[k] = emb.submit(pin[k][0], pin[k][1], pin[k][2], pin[k][3], flags=flags)
-        for t in tickets:
-            if t is not None:
-                emb.wait(t)
-
-    e2e_steps(args.warmup)
-    barrier()
-    t0 = time.perf_counter()
-    e2e_steps(args.steps)
-    torch.cuda.synchronize()
-    e2e_s = max_over_ranks(time.perf_counter() - t0)
-    barrier()
+    e2e_s, host_out = wl.e2e_leg(dist, args.steps, args.warmup)
     e2e_value = world * batch * args.steps / e2e_s
-    e2e_check = float(np.abs(pin[0][3] - d_out.cpu().numpy()).max())
+    e2e_check = float(np.abs(host_out - wl.d_out.cpu().numpy()).max())
 
     # ---- per-kernel timing (outside the timed regions): CUDA events around every launch ----------
     emb.profile(True)
     emb.profile_read(reset=True)
     prof_steps = 3
     for _ in range(prof_steps):
-        emb.forward_device(d_ids.data_ptr(), d_mask.data_ptr(), d_tt.data_ptr(), batch, seq, d_out.data_ptr(), flags=flags)
+        wl.step_device()
     stats = emb.profile_read(reset=True)
     emb.profile(False)
-    pk = peaks()
     kernels, total_ms = {}, sum(v["total_ms"] for v in stats.values()) / prof_steps
     per_layer = {"gemm_qkv", "attention", "gemm_attn_out", "gemm_ffn1", "gemm_ffn2", "ffn_fused", "qkv_attention"}
     for kind, v in stats.items():
@@ -312,68 +463,96 @@ def run_b200(args, pkg, rank, world, local_rank):
         kernels[kind] = {"ms_per_launch": round(ms, 4), "launches_per_step": v["launches"] // prof_steps,
                          "share_of_step": round(step_ms / total_ms, 4), "bound": bound,
                          "achieved": round(ach, 2), "peak": peak, "unit": unit, "frac": round(ach / peak, 4)}
+        if bound == "hbm":  # both conventions: bytes this design moves (frac) and SURVEY 8(d)'s algorithmic bytes
+            kernels[kind]["bytes_moved_per_pass"] = int(nbytes)
+            ab = algorithmic_bytes(shape, lengths, kind)
+            if ab is not None:
+                kernels[kind]["bytes_algorithmic_per_pass"] = int(ab)
+                kernels[kind]["frac_algorithmic"] = round(ab * passes / (step_ms * 1e-3) / 1e9 / pk["hbm_gbs"], 4)
     top = max(kernels, key=lambda k: kernels[k]["share_of_step"])
-    traffic = None
+    traffic_all = {}
     tp = os.path.join(ROOT, "profiles", "traffic.json")  # dram bytes per launch from the committed ncu capture
     if os.path.exists(tp):
-        traffic = json.load(open(tp)).get(f"{args.workload}:{top}")
+        traffic_all = json.load(open(tp))
+    for kind in kernels:
+        t = traffic_all.get(f"{args.workload}:{kind}")
+        if t is not None:
+            kernels[kind]["traffic"] = t
     roofline = {"kernel": top, "bound": kernels[top]["bound"], "achieved": kernels[top]["achieved"],
                 "peak": kernels[top]["peak"], "unit": kernels[top]["unit"], "frac": kernels[top]["frac"],
-                "traffic": traffic, "peak_source": pk["source"] + ", sustained figure (kernel timed inside a long step)",
+                "traffic": traffic_all.get(f"{args.workload}:{top}"),
+                "peak_source": pk["source"] + ", sustained figure (kernel timed inside a long step)",
                 "ms_per_launch": kernels[top]["ms_per_launch"], "share_of_step": kernels[top]["share_of_step"]}
-    uniq, cnt = np.unique(lengths, return_counts=True)
-    flops_per_step = float(sum(shape.flops_per_sentence(int(s)) * int(c) for s, c in zip(uniq, cnt)))
-    model_tflops = flops_per_step * args.steps / (dev_ms * 1e-3) / 1e12  # per GPU
+    model_tflops = wl.flops_per_step * args.steps / (dev_ms * 1e-3) / 1e12  # per GPU
+
+    # ---- the other configs and the other operand format (short runs, every N) ------------------------
+    workloads, parity = {}, None
+    other = "f16" if args.operands == "bf16" else "bf16"
+    if not args.no_workloads:
+        wl_other = Workload(pkg, args.workload, other, rank, local_rank, args.batch, args.normalize)
+        workloads[f"{args.workload}_{other}"] = wl_other.summary(dist, 5, 3, pk)
+        if rank == 0 and world == 1 and args.workload == "c2":
+            parity = parity_section(pkg, {args.operands: wl, other: wl_other})
+        wl_other.close()
+        for name, st, wu in (("c3", 5, 3), ("c5", 5, 3), ("c4", 3, 3)):
+            if name == args.workload:
+                continue
+            share = emb if WORKLOADS[name][0] == wl.shape_key else None  # same model shape: same handle
+            w2 = Workload(pkg, name, args.operands, rank, local_rank, 0, args.normalize, emb=share)
+            workloads[name] = w2.summary(dist, st, wu, pk)
+            w2.close()
+            del w2
+            torch.cuda.empty_cache()
 
     # ---- CPU baseline (rank 0, N = 1 only) ---------------------------------------------------------
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         n = 16
-        o, (ci, ct, cm, chunk) = cpu_reference_path(pkg, shape, n, seq, "reference")
+        o, (ci, ct, cm, chunk) = cpu_reference_path(pkg, shape, n, seq, "reference", native=True)
         o.generate(ci[:8], ct[:8], cm[:8], chunk=chunk)
         t0 = time.perf_counter()
-        ref_out = o.generate(ci, ct, cm, chunk=chunk)
+        o.generate(ci, ct, cm, chunk=chunk)
         dt = time.perf_counter() - t0
-        o2, (fi, ft, fm, fchunk) = cpu_reference_path(pkg, shape, 32, seq, "fair")
+        o2, (fi, ft, fm, fchunk) = cpu_reference_path(pkg, shape, 32, seq, "fair", native=True)
+        o2.generate(fi, ft, fm, chunk=fchunk)
         t0 = time.perf_counter()
         o2.generate(fi, ft, fm, chunk=fchunk)
         dt_fair = time.perf_counter() - t0
         cpu = {"value": n / dt, "unit": UNIT, "cores": o.threads, "kind": "port",
                "sample": (f"{n} sentences of {seq} tokens, reference schedule (chunks of 8, padded to "
-                          f"P={shape.max_position_embeddings}, f32), C oracle port of the candle CPU path"),
-               "fair_pad_to_seq_b32": 32 / dt_fair}
-        del ref_out
+                          f"P={shape.max_position_embeddings}, f32), C oracle port of the candle CPU path, built -O3 "
+                          "-march=native on this host"),
+               "fair_pad_to_seq_b32": 32 / dt_fair,
+               "hf_torch_cpu_c1": hf_torch_cpu_c1(pkg, pkg.weights.SHAPES["minilm-l6"])}
 
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": f"{args.workload}: {shape_key} random-init bf16, batch {batch} x seq {seq} per GPU"
-                                   + (" corpus lengths clip(LogNormal(ln 24, 0.6), 4, 128)" if ragged == "corpus"
-                                      else " ragged log-uniform 8..seq packed varlen" if ragged else " dense"),
+            "dtype": args.operands, "data": "synthetic",
+            "config": {"workload": wl.label(),
+                       "operands": (f"{args.operands} tensor-core operands (tcgen05.mma kind::f16), fp32 accumulation; the "
+                                    f"other 16-bit format ({other}) runs the same kernels at the same rate: workloads.{args.workload}_{other}"),
                        "tokens_per_step_per_gpu": int(np.sum(lengths)), "normalize": bool(args.normalize),
                        "parallelism": f"replica per GPU x{world}, sentence batches sharded, no data-path collective",
                        "l2": "activations per step (>= 4 GB at c2) exceed the 126 MB L2; no explicit flush"},
-            "clocks": clocks.summary(),
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(3 * ids.nbytes),
+            "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(3 * wl.ids.nbytes),
                     "d2h_bytes_per_step": int(batch * H * 4), "ms_per_step": 1e3 * e2e_s / args.steps,
                     "api": "b200_embed_submit/b200_embed_wait, 2 requests in flight, pinned host buffers",
                     "max_abs_vs_device_leg": e2e_check},
             "gpu_launches": int(launches),
             "roofline": roofline,
             "cpu_baseline": cpu,
+            "parity": parity,
             "kernels": kernels,
             "model_tflops_per_gpu": round(model_tflops, 1),
             "model_frac_of_sustained_bf16_peak": round(model_tflops / pk["tf_sustained"], 4),
+            "workloads": workloads,
         }
         print(json.dumps(line), flush=True)
-    for b in pin:
-        for a in b:
-            pkg.abi.host_free(a)
-    emb.close()
-    if world > 1:
-        dist.destroy_process_group()
+    wl.close()
+    dist.close()
 
 
 def main():
@@ -386,6 +565,9 @@ def main():
     ap.add_argument("--batch", type=int, default=0, help="override sentences per GPU per step")
     ap.add_argument("--normalize", action="store_true", help="append the L2 normalisation (north_star option)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-workloads", action="store_true", help="skip the short runs of the other configs and the parity section")
+    ap.add_argument("--operands", default="bf16", choices=["bf16", "f16"],
+                    help="16-bit operand format of the headline run (BASELINE names bf16; the library default is f16)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -56,12 +56,30 @@ def _u32(a):
     return np.ascontiguousarray(a, dtype=np.uint32)
 
 
+def build_native() -> str:
+    """liboracle_f32_native.so: the same source built for THIS host (-march=native, contraction allowed), used only for
+    the timed CPU-baseline legs of bench.py so that the baseline is not artificially slow. Rebuilt on every call: a
+    library built for another machine's instruction set must not travel."""
+    out = os.path.join(_HERE, "_native", "liboracle_f32_native.so")
+    os.makedirs(os.path.dirname(out), exist_ok=True)
+    subprocess.run(["gcc", "-O3", "-march=native", "-fopenmp", "-fPIC", "-shared", "-fno-fast-math", "-ffp-contract=fast",
+                    "-o", out, os.path.join(_HERE, "bert_oracle.c"), "-lm"], check=True)
+    return out
+
+
 class Oracle:
     """The reference path on the CPU. `precision` is "f32" (candle's DTYPE) or "f64"."""
 
-    def __init__(self, shape, weights: dict, precision: str = "f32"):
+    _native_path = None
+
+    def __init__(self, shape, weights: dict, precision: str = "f32", native: bool = False):
         build()
-        self.lib = C.CDLL(os.path.join(_HERE, f"liboracle_{precision}.so"))
+        if native and precision == "f32":
+            if Oracle._native_path is None:
+                Oracle._native_path = build_native()
+            self.lib = C.CDLL(Oracle._native_path)
+        else:
+            self.lib = C.CDLL(os.path.join(_HERE, f"liboracle_{precision}.so"))
         self.real = np.float32 if precision == "f32" else np.float64
         assert self.lib.oracle_real_bytes() == np.dtype(self.real).itemsize
         self.shape = shape
