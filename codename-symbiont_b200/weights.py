@@ -135,17 +135,31 @@ def init_weights(shape: BertShape, seed: int = 1234) -> dict:
 _ST_DTYPES = {"F32": np.float32, "F16": np.float16, "F64": np.float64, "I64": np.int64, "I32": np.int32}
 
 
-def save_safetensors(path: str, tensors: dict, metadata: dict | None = None) -> None:
+def to_bf16_bits(a: np.ndarray) -> np.ndarray:
+    """f32 -> bf16 bit patterns (uint16), round to nearest even."""
+    u = np.ascontiguousarray(a, dtype=np.float32).view(np.uint32).astype(np.uint64)
+    return ((u + 0x7FFF + ((u >> 16) & 1)) >> 16).astype(np.uint16)
+
+
+def save_safetensors(path: str, tensors: dict, metadata: dict | None = None, store_as: str | None = None) -> None:
+    """store_as: None keeps each array's dtype (F32 / F16 / F64); "F16" / "BF16" converts every tensor on the way out
+    (checkpoints are published in all three)."""
     header, off = {}, 0
     if metadata:
         header["__metadata__"] = {k: str(v) for k, v in metadata.items()}
     blobs = []
     for name, arr in tensors.items():
         arr = np.ascontiguousarray(arr)
-        dt = {np.dtype(np.float32): "F32", np.dtype(np.float16): "F16", np.dtype(np.float64): "F64"}[arr.dtype]
-        nb = arr.nbytes
+        if store_as == "BF16":
+            dt, raw = "BF16", to_bf16_bits(arr).tobytes()
+        else:
+            if store_as == "F16":
+                arr = arr.astype(np.float16)
+            dt = {np.dtype(np.float32): "F32", np.dtype(np.float16): "F16", np.dtype(np.float64): "F64"}[arr.dtype]
+            raw = arr.tobytes()
+        nb = len(raw)
         header[name] = {"dtype": dt, "shape": list(arr.shape), "data_offsets": [off, off + nb]}
-        blobs.append(arr.tobytes())
+        blobs.append(raw)
         off += nb
     hj = json.dumps(header, separators=(",", ":")).encode()
     hj += b" " * ((8 - len(hj) % 8) % 8)
