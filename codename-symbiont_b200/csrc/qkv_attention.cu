@@ -15,14 +15,16 @@
 // and each does everything the head needs outside the tensor pipe:
 //   warp 0      TMA producer: the x tile once per sentence; per head KB blocks of Wqkv rows {h*d.., H + h*d.., 2H + h*d..}
 //               x 64 columns (three 4 KB boxes = one 96-row K-major B operand) through a small ring
-//   warp 1      MMA issuer, fixed schedule per pair of heads (whole warp walks it, one elected lane issues):
-//                 projection  ACC[g & 1] = x . Wqkv_h^T      128 x 96 x H per head g, two heads ahead
-//                 group 0/1   S = Q . K_u^T (128 x 64 x d) and O_u = P_u . V_u (128 x d x 64) per unit u of 64 keys
-//   warp 2      TMEM allocator (512 columns: 2 x 128 ACC, 2 x 64 S, 2 x 2 x 32 O)
+//   warp 1      MMA issuer of the projections  ACC[g & 1] = x . Wqkv_h^T  (128 x 96 x H per head g, up to two heads ahead;
+//               the whole warp walks the loop, one elected lane issues)
+//   warps 2, 3  MMA issuers of group 0 / 1: S = Q . K_u^T (128 x 64 x d) and O_u = P_u . V_u (128 x d x 64) per unit u of
+//               64 keys. Three issuers, each blocking on its own dependencies only: one issuer with a fixed schedule kept the
+//               groups in lockstep (softmax warps spent 27 % of their samples waiting for S / O / ACC, profiles/r02a).
+//               Warp 2 is also the TMEM allocator (512 columns: 2 x 128 ACC, 2 x 64 S, 2 x 2 x 32 O)
 //   warps 4-7 / 8-11  group 0 / 1, thread = token row = TMEM lane. Per head: convert ACC + bias -> bf16 Q / K / V tiles
 //               in shared memory, in the layouts K3 gets from TMA (64-byte rows, SWIZZLE_64B; V consumed MN-major as
-//               stored); then per unit the softmax of attention_tc.cu (unit read once into registers, P as bf16 into a
-//               128B-swizzled K-major tile, online softmax, ctx rows stored as whole 32-byte sectors). A group has one
+//               stored); then per unit the softmax of attention_tc.cu (unit read once into registers, P as 16-bit pairs into
+//               tensor memory - the P.V MMA reads its A operand there -, online softmax, ctx rows stored as whole 32-byte sectors). A group has one
 //               S and one P buffer: the previous unit's P.V is retired (which also proves P free) between the row
 //               maximum and the exponentials of the next unit.
 #include <cuda.h>
@@ -54,15 +56,17 @@ struct QaCfg {
     static constexpr int W_BLK = 3 * W_SUB;          // [3D x 64]: one K-major B operand block
     static constexpr int WS = KB % 3 == 0 ? 3 : 2;   // W ring slots (KB % WS == 0: slots are compile-time in the k loop)
     static constexpr int T_TILE = BLK * D * 2;       // one Q / K / V tile
-    static constexpr int P_UNIT = BLK * UNIT * 2;    // one K-major 128 x 64 bf16 tile
     static constexpr int OFF_X = 0;
     static constexpr int OFF_W = KB * X_BLK;
     static constexpr int OFF_T = OFF_W + WS * W_BLK;   // per group: Q, K, V
-    static constexpr int OFF_P = OFF_T + 2 * 3 * T_TILE;
-    static constexpr int OFF_AUX = OFF_P + 2 * P_UNIT;  // per group: one P unit
+    static constexpr int OFF_AUX = OFF_T + 2 * 3 * T_TILE;
     static constexpr int OFF_BIAS = OFF_AUX + 512;     // bqkv [3H] fp32
     static constexpr int BYTES = OFF_BIAS + 3 * H * 4;
-    static constexpr int ACC_COL = 0, ACC_STRIDE = 128, S_COL = 256, O_COL = 384;  // S: + group * 64; O: + group * 64 + (unit & 1) * 32
+    // tensor memory: ACC[2] (q | k | v of the head being projected), per group S (one unit of 64 keys), O (two units), and P:
+    // the probabilities as 16-bit pairs, one 32-bit column per two keys, which the P.V MMA reads straight from tensor
+    // memory (A operand in TMEM) - they never go through shared memory
+    static constexpr int ACC_COL = 0, ACC_STRIDE = NQ, S_COL = 2 * NQ, O_COL = S_COL + 2 * UNIT, P_COL = O_COL + 4 * D;
+    static_assert(P_COL + 2 * (UNIT / 2) <= 512, "tensor memory budget");
     static_assert(HEADS % 2 == 0, "the two groups take alternate heads");
     static_assert(D == 32, "the q / k / v tiles use 64-byte rows");
     static_assert(KB % WS == 0 && H % BK == 0 && H % D == 0, "shape");
@@ -86,12 +90,12 @@ __global__ void __launch_bounds__(QA_THREADS, 1)
 qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w, const QaDev p) {
     using C = QaCfg<H, D>;
     constexpr int KB = C::KB, HEADS = C::HEADS, NQ = C::NQ, W_SUB = C::W_SUB, W_BLK = C::W_BLK, WS = C::WS;
-    constexpr int T_TILE = C::T_TILE, P_UNIT = C::P_UNIT;
+    constexpr int T_TILE = C::T_TILE;
 
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     const uint32_t base = smem_u32(smem_raw);
     if ((base & 1023u) != 0) __trap();
-    const uint32_t smem_x = base + C::OFF_X, smem_w = base + C::OFF_W, smem_t = base + C::OFF_T, smem_p = base + C::OFF_P;
+    const uint32_t smem_x = base + C::OFF_X, smem_w = base + C::OFF_W, smem_t = base + C::OFF_T;
     const uint32_t aux = base + C::OFF_AUX;
     const uint32_t bar_x_full = aux, bar_x_empty = aux + 8;
     const uint32_t bar_w_full = aux + 16, bar_w_empty = aux + 48;        // WS each
@@ -200,61 +204,56 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
             }
         }
     } else if (warp == 1) {
-        // ------------------------------ MMA issuer: event loop ------------------------------
+        // ------------------------------ MMA issuer 1 of 3: the projections ------------------------------
+        // ACC[g & 1] = x . Wqkv_h^T (128 x 96 x H) for head after head, as far ahead as the two accumulators allow. The
+        // three issuers (this warp and one per group) block on their own dependencies only: with a single issuing warp
+        // walking a fixed schedule the two groups ran in lockstep and each waited for the other's softmax.
         constexpr uint32_t idesc_g = umma_idesc_op(BLK, NQ);
+        const uint64_t dx0 = umma_desc_sw128(smem_x), dw0 = umma_desc_sw128(smem_w);
+        Walk wp = walk_init();
+        uint32_t pit = 0, gg = 0, wb = 0;  // tiles entered, heads projected, W blocks consumed
+        while (wp.b < n_items) {
+            int a, b;
+            if (!take(wp, a, b)) continue;
+            mbar_wait(bar_x_full, pit & 1);
+            ++pit;
+            for (int ph = 0; ph < HEADS; ++ph, ++gg) {
+                const uint32_t ab = gg & 1;
+                mbar_wait(bar_acc_empty + 8 * ab, ((gg >> 1) & 1) ^ 1);  // the group has drained this accumulator
+                tc_fence_after_sync();
+#pragma unroll
+                for (int kb = 0; kb < KB; ++kb, ++wb) {
+                    const uint32_t sl = kb % WS;
+                    mbar_wait(bar_w_full + 8 * sl, (wb / WS) & 1);
+                    tc_fence_after_sync();
+                    if (elect_one()) {
+                        const uint64_t da = dx0 + ((kb * X_BLK) >> 4), db = dw0 + ((sl * W_BLK) >> 4);
+#pragma unroll
+                        for (int k = 0; k < BK / 16; ++k)
+                            umma_bf16(tmem_base + C::ACC_COL + ab * C::ACC_STRIDE, da + 2 * k, db + 2 * k, idesc_g,
+                                      (kb > 0 || k > 0) ? 1u : 0u);
+                        umma_commit(bar_w_empty + 8 * sl);
+                        if (kb == KB - 1) {
+                            umma_commit(bar_acc_full + 8 * ab);
+                            if (ph == HEADS - 1) umma_commit(bar_x_empty);  // the x tile has been read for the last time
+                        }
+                    }
+                    __syncwarp();
+                }
+            }
+        }
+    } else if (warp == 2 || warp == 3) {
+        // ------------------------------ MMA issuers 2, 3 of 3: one per group ------------------------------
+        // Per head of the group: S = Q . K_u^T (128 x 64 x d) and O_u = P_u . V_u (128 x d x 64) per unit u of 64 keys,
+        // in the order S(u0), S(u1), P.V(u0), P.V(u1): S(u1) only needs the softmax warps to have read S(u0).
+        const int G = warp - 2;
         constexpr uint32_t idesc_s = umma_idesc_op(BLK, UNIT);
         constexpr uint32_t idesc_o = umma_idesc_op(BLK, D) | (1u << 16);  // B (= V) is MN-major
-        const uint64_t dx0 = umma_desc_sw128(smem_x), dw0 = umma_desc_sw128(smem_w);
-        const uint64_t dq0 = umma_desc_k_sw64(smem_t), dp0 = umma_desc_sw128(smem_p);
+        const uint64_t dq0 = umma_desc_k_sw64(smem_t);
         const uint64_t dv0 = umma_desc_mn<D>(smem_t + 2 * T_TILE);
-        // A fixed schedule (the two groups do the same work at the same pace, so an event loop buys nothing and a polling
-        // one was measured 2x slower: its own instructions became the bottleneck). Per PAIR of heads (h for group 0,
-        // h + 1 for group 1):   S(u0) x2 | projection of head h + 2 | S(u1) x2 | P.V(u0) x2 | projection of head h + 3 |
-        // P.V(u1) x2 - the projections run on the tensor pipe while the groups are busy with their softmax.
-        Walk wp = walk_init();
-        int ph = HEADS;                 // projection cursor: head within its sentence (HEADS: needs the next sentence)
-        uint32_t pit = 0, gg = 0, wb = 0;  // sentences entered, heads projected, W blocks consumed
-        auto proj_head = [&]() -> bool {
-            if (ph == HEADS) {
-                int a, b;
-                bool ok = false;
-                while (wp.b < n_items) {
-                    if (take(wp, a, b)) { ok = true; break; }
-                }
-                if (!ok) return false;
-                mbar_wait(bar_x_full, pit & 1);
-                ++pit;
-                ph = 0;
-            }
-            const uint32_t ab = gg & 1;
-            mbar_wait(bar_acc_empty + 8 * ab, ((gg >> 1) & 1) ^ 1);  // the group has drained this accumulator
-            tc_fence_after_sync();
-#pragma unroll
-            for (int kb = 0; kb < KB; ++kb, ++wb) {
-                const uint32_t sl = kb % WS;
-                mbar_wait(bar_w_full + 8 * sl, (wb / WS) & 1);
-                tc_fence_after_sync();
-                if (elect_one()) {
-                    const uint64_t da = dx0 + ((kb * X_BLK) >> 4), db = dw0 + ((sl * W_BLK) >> 4);
-#pragma unroll
-                    for (int k = 0; k < BK / 16; ++k)
-                        umma_bf16(tmem_base + C::ACC_COL + ab * C::ACC_STRIDE, da + 2 * k, db + 2 * k, idesc_g,
-                                  (kb > 0 || k > 0) ? 1u : 0u);
-                    umma_commit(bar_w_empty + 8 * sl);
-                    if (kb == KB - 1) {
-                        umma_commit(bar_acc_full + 8 * ab);
-                        if (ph == HEADS - 1) umma_commit(bar_x_empty);  // the x tile has been read for the last time
-                    }
-                }
-                __syncwarp();
-            }
-            ++ph;
-            ++gg;
-            return true;
-        };
-        uint32_t hc = 0;          // head pairs completed (both groups advance together)
-        uint32_t us = 0, uo = 0;  // S / P.V units issued per group (the same for both)
-        auto issue_s = [&](int G, int u, bool first) {
+        uint32_t hc = 0;          // heads of this group completed
+        uint32_t us = 0, uo = 0;  // S / P.V units issued
+        auto issue_s = [&](int u, bool first) {
             if (first) mbar_wait(bar_t_full + 8 * G, hc & 1);       // this head's Q / K / V are staged
             mbar_wait(bar_s_empty + 8 * G, (us & 1) ^ 1);           // the group has read the previous S
             tc_fence_after_sync();
@@ -267,50 +266,36 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                 umma_commit(bar_s_full + 8 * G);
             }
             __syncwarp();
+            ++us;
         };
-        auto issue_pv = [&](int G, int u, bool last) {
+        auto issue_pv = [&](int u, bool last) {
             const uint32_t ob = uo & 1;
-            mbar_wait(bar_p_full + 8 * G, uo & 1);                                  // P_u is in shared memory
+            mbar_wait(bar_p_full + 8 * G, uo & 1);                                  // P_u is in tensor memory
             mbar_wait(bar_o_empty + 8 * (2 * G + ob), ((uo >> 1) & 1) ^ 1);         // the O buffer has been read
             tc_fence_after_sync();
             if (elect_one()) {
-                const uint64_t dp = dp0 + ((G * P_UNIT) >> 4);
+                const uint32_t tp = tmem_base + C::P_COL + G * (UNIT / 2);
                 const uint64_t dv = dv0 + ((G * 3 * T_TILE + u * (UNIT * D * 2)) >> 4);
 #pragma unroll
-                for (int k = 0; k < UNIT / 16; ++k)  // P: 32 B per 16 keys; V: 16 rows of D*2 B
-                    umma_bf16(tmem_base + C::O_COL + G * 64 + ob * D, dp + 2 * k, dv + ((k * 16 * D * 2) >> 4), idesc_o,
-                              k > 0 ? 1u : 0u);
+                for (int k = 0; k < UNIT / 16; ++k)  // P: 8 columns per 16 keys; V: 16 rows of D*2 B
+                    umma_ts(tmem_base + C::O_COL + G * 64 + ob * D, tp + 8 * k, dv + ((k * 16 * D * 2) >> 4), idesc_o,
+                            k > 0 ? 1u : 0u);
                 umma_commit(bar_o_full + 8 * (2 * G + ob));
                 if (last) umma_commit(bar_t_empty + 8 * G);  // this head's tiles are consumed
             }
             __syncwarp();
+            ++uo;
         };
-        bool more = proj_head();
-        if (more) more = proj_head();
         Walk w = walk_init();
         while (w.b < n_items) {
             int start, len;
             if (!take(w, start, len)) continue;
             const int nunits = (len + UNIT - 1) / UNIT;
-            for (int h = 0; h < HEADS; h += 2, ++hc) {
-                issue_s(0, 0, true);
-                issue_s(1, 0, true);
-                ++us;
-                if (more) more = proj_head();
-                if (nunits > 1) {
-                    issue_s(0, 1, false);
-                    issue_s(1, 1, false);
-                    ++us;
-                }
-                issue_pv(0, 0, nunits == 1);
-                issue_pv(1, 0, nunits == 1);
-                ++uo;
-                if (more) more = proj_head();
-                if (nunits > 1) {
-                    issue_pv(0, 1, true);
-                    issue_pv(1, 1, true);
-                    ++uo;
-                }
+            for (int h = G; h < HEADS; h += 2, ++hc) {
+                issue_s(0, true);
+                if (nunits > 1) issue_s(1, false);
+                issue_pv(0, nunits == 1);
+                if (nunits > 1) issue_pv(1, true);
             }
         }
     } else if (warp >= QA_GROUP_WARP0) {
@@ -319,7 +304,7 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
         const int quad = warp & 3;
         const int row = quad * 32 + lane;  // token row inside the item = TMEM lane
         const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
-        const uint32_t tile = smem_t + G * 3 * T_TILE, ptile = smem_p + G * P_UNIT;
+        const uint32_t tile = smem_t + G * 3 * T_TILE;
         uint32_t hc = 0;  // heads done by this group
         uint32_t ug = 0;  // units done by this group (O buffer ug & 1)
         float o[D];       // running output of the head being retired
@@ -436,21 +421,19 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                     if (pend.valid) retire_pending();  // also: the previous P.V is done, the P buffer is free
                     const uint64_t sc2 = pk2(p.scale_log2, p.scale_log2), nm2 = pk2(-m_use, -m_use);
                     uint64_t lb2[4] = {0, 0, 0, 0};
-                    const uint32_t prow = ptile + row * 128;
+                    uint32_t pw[UNIT / 2];  // this row's probabilities, two keys per word
 #pragma unroll
                     for (int q = 0; q < UNIT / 8; ++q) {
-                        uint32_t wd[4];
 #pragma unroll
                         for (int j = 0; j < 4; ++j) {
                             float a, bb;
                             upk2(fma2(pk2(__uint_as_float(v[q * 8 + 2 * j]), __uint_as_float(v[q * 8 + 2 * j + 1])), sc2, nm2), a, bb);
                             const float pa = ex2(a), pb = ex2(bb);
                             lb2[j] = add2(lb2[j], pk2(pa, pb));
-                            wd[j] = pack_op2(pa, pb);
+                            pw[q * 4 + j] = pack_op2(pa, pb);
                         }
-                        const uint32_t piece = static_cast<uint32_t>(q) ^ (row & 7);
-                        sts_v4(prow + (piece << 4), wd[0], wd[1], wd[2], wd[3]);
                     }
+                    tmem_st_32x32(t_lane + C::P_COL + G * (UNIT / 2), pw);
                     float lb;
                     {
                         float a0, a1, a2, a3;
@@ -458,7 +441,8 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                         upk2(add2(lb2[2], lb2[3]), a2, a3);
                         lb = (a0 + a1) + (a2 + a3);
                     }
-                    fence_proxy_async_smem();
+                    tmem_st_wait();
+                    tc_fence_before_sync();
                     mbar_arrive(bar_p_full + 8 * G);
                     l = fmaf(l, corr, lb);
                     pend.valid = true; pend.last = u == nunits - 1; pend.ur = ug; pend.corr = corr; pend.l = l;
