@@ -25,8 +25,12 @@ def _newer(target: str, deps) -> bool:
     return all(os.path.getmtime(d) <= t for d in deps)
 
 
-def build_library(verbose: bool = False, force: bool = False) -> str:
+def build_library(verbose: bool = False, force: bool = False, suffix: str = "", extra_flags=()) -> str:
+    """suffix / extra_flags: an experimental variant next to the shipped library (libb200_embed<suffix>.so, objects in
+    build<suffix>/), loaded with B200_EMBED_LIB=... for same-box A/B timing (scripts/k23_ab.py)."""
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    LIB = os.path.join(HERE, f"libb200_embed{suffix}.so")
+    OBJ_DIR = os.path.join(HERE, "build" + suffix)
     os.makedirs(OBJ_DIR, exist_ok=True)
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh"))]
     headers.append(os.path.join(HERE, "..", "include", "b200_embed.h"))
@@ -39,7 +43,7 @@ def build_library(verbose: bool = False, force: bool = False) -> str:
         o = os.path.join(OBJ_DIR, os.path.splitext(src)[0] + suffix + ".o")
         objs.append(o)
         if force or not _newer(o, [s] + headers):
-            jobs.append([nvcc, *NVCC_FLAGS, *defs, "-c", s, "-o", o])
+            jobs.append([nvcc, *NVCC_FLAGS, *defs, *extra_flags, "-c", s, "-o", o])
     jobs.sort(key=lambda j: 0 if "gemm_tc" in j[-3] else 1)  # the longest compiles first
 
     def run(cmd):
@@ -58,4 +62,10 @@ def build_library(verbose: bool = False, force: bool = False) -> str:
 
 
 if __name__ == "__main__":
-    print(build_library(verbose=True, force="--force" in sys.argv))
+    import argparse
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--force", action="store_true")
+    ap.add_argument("--suffix", default="")
+    ap.add_argument("--flags", default="", help="extra nvcc flags of a variant build, e.g. '-DQA_POLY_PAIRS=0'")
+    a = ap.parse_args()
+    print(build_library(verbose=True, force=a.force, suffix=a.suffix, extra_flags=a.flags.split()))
