@@ -44,6 +44,17 @@ class Config(C.Structure):
                 ("layer_norm_eps", C.c_float), ("max_tokens_per_launch", C.c_int32), ("operand_format", C.c_int32)]
 
 
+CORPUS_MAX_GPUS = 16  # B200_CORPUS_MAX_GPUS
+
+
+class CorpusStats(C.Structure):
+    _fields_ = [("sentences", C.c_int64), ("tokens", C.c_int64), ("micro_batches", C.c_int64),
+                ("tokenizer_threads", C.c_int32), ("gpus", C.c_int32), ("tokenize_busy_s", C.c_double), ("plan_s", C.c_double),
+                ("gather_s", C.c_double), ("gpu_wait_s", C.c_double), ("scatter_s", C.c_double),
+                ("per_gpu_active_s", C.c_double * CORPUS_MAX_GPUS), ("per_gpu_sentences", C.c_int64 * CORPUS_MAX_GPUS),
+                ("per_gpu_tokens", C.c_int64 * CORPUS_MAX_GPUS), ("per_gpu_batches", C.c_int64 * CORPUS_MAX_GPUS)]
+
+
 class KindStats(C.Structure):
     _fields_ = [("total_ms", C.c_double), ("launches", C.c_int64)]
 
@@ -60,6 +71,15 @@ _SIGNATURES = {
     "b200_embed_forward_varlen": (C.c_int32, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_uint32, _P]),
     "b200_embed_submit": (C.c_int32, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_uint32, _P, C.POINTER(C.c_int64)]),
     "b200_embed_wait": (C.c_int32, [_P, C.c_int64]),
+    "b200_embed_submit_varlen": (C.c_int32, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_uint32, _P, C.POINTER(C.c_int64)]),
+    "b200_corpus_last_error": (C.c_char_p, []),
+    "b200_corpus_create": (C.c_int32, [C.POINTER(Config), C.c_char_p, C.c_uint64, _P, C.c_int32, _P, C.c_int32, C.c_int32, C.c_int32,
+                                       C.POINTER(_P)]),
+    "b200_corpus_destroy": (None, [_P]),
+    "b200_corpus_submit": (C.c_int32, [_P, _P, _P, _P, C.c_int64, C.c_uint32, _P, C.POINTER(C.c_int64)]),
+    "b200_corpus_wait": (C.c_int32, [_P, C.c_int64]),
+    "b200_corpus_stats_read": (C.c_int32, [_P, C.POINTER(CorpusStats), C.c_int32]),
+    "b200_corpus_plan": (C.c_int64, [_P, C.c_int64, C.c_int32, C.c_int32, C.c_int64, _P, _P, C.c_int64]),
     "b200_embed_forward_device": (C.c_int32, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_uint32, _P, _P]),
     "b200_embed_host_alloc": (C.c_int32, [C.c_size_t, C.POINTER(_P)]),
     "b200_embed_host_free": (None, [_P]),
@@ -121,7 +141,7 @@ def declared_symbols() -> list:
     with open(HEADER_PATH) as f:
         text = f.read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
-    return sorted(set(re.findall(r"\b(b200_(?:embed|op|json|ingest|index|pipeline)_[a-z0-9_]+)\s*\(", text)))
+    return sorted(set(re.findall(r"\b(b200_(?:embed|op|json|ingest|index|pipeline|corpus)_[a-z0-9_]+)\s*\(", text)))
 
 
 def load_library():
@@ -217,11 +237,11 @@ def _check_ingest(rc: int):
         raise B200EmbedError(int(rc), load_library().b200_ingest_last_error().decode(errors="replace"))
 
 
-def split_sentences(raw_text: str):
+def split_sentences(raw_text):
     """process_raw_text_message's splitter (preprocessing_service/src/main.rs:28-63) -> (cleaned: bytes, begin, end);
     sentence i is cleaned[begin[i]:end[i]]. An empty cleaned text raises like the reference's Err("Cleaned text is empty")."""
     lib = load_library()
-    raw = raw_text.encode("utf-8")
+    raw = raw_text if isinstance(raw_text, (bytes, bytearray)) else raw_text.encode("utf-8")
     cleaned = np.empty(max(len(raw), 1), dtype=np.uint8)
     clen = C.c_int64(0)
     cap = len(raw) // 16 + 16  # a guess; the call returns the full count, so a second call fixes an underestimate
@@ -516,6 +536,17 @@ class Embedder:
     def wait(self, ticket: int) -> None:
         _check(self.lib.b200_embed_wait(self.h, ticket))
 
+    def submit_varlen(self, ids_packed, type_ids_packed, cu_seqlens, max_seqlen: int, out: np.ndarray, flags: int = 0) -> int:
+        """Packed form of submit: buffers must stay alive (and should be pinned) until wait(ticket)."""
+        for a in (ids_packed, type_ids_packed):
+            assert a.dtype == np.uint32 and a.flags.c_contiguous
+        assert cu_seqlens.dtype == np.int32 and out.dtype == np.float32 and out.flags.c_contiguous
+        t = C.c_int64()
+        _check(self.lib.b200_embed_submit_varlen(self.h, ids_packed.ctypes.data, type_ids_packed.ctypes.data, cu_seqlens.ctypes.data,
+                                                 len(cu_seqlens) - 1, int(cu_seqlens[-1]), max_seqlen, flags, out.ctypes.data,
+                                                 C.byref(t)))
+        return t.value
+
     # -- device-buffer entry point --------------------------------------------------------------
     def forward_device(self, d_ids: int, d_mask: int, d_type_ids: int, batch: int, seq_len: int, d_out: int,
                        flags: int = 0, stream: int = 0) -> None:
@@ -573,6 +604,85 @@ class Embedder:
     def op_mean_pool(self, d_hidden, d_cu, batch, dtype, normalize, d_out, d_hidden_lo=0, stream=0):
         _check(self.lib.b200_op_mean_pool(self.h, d_hidden, d_hidden_lo or None, d_cu, batch, dtype, int(normalize), d_out,
                                           stream or None))
+
+
+def corpus_plan(lengths, max_len: int, max_batch_sentences: int, max_batch_tokens: int):
+    """b200_corpus_plan: -> (order [n] int32: the sentences by ascending token count, batch_begin [nb + 1] int64)."""
+    lengths = np.ascontiguousarray(lengths, dtype=np.int32)
+    n = len(lengths)
+    order = np.empty(n, dtype=np.int32)
+    begins = np.empty(n + 2, dtype=np.int64)
+    nb = load_library().b200_corpus_plan(lengths.ctypes.data, n, max_len, max_batch_sentences, max_batch_tokens,
+                                         order.ctypes.data, begins.ctypes.data, len(begins))
+    if nb < 0:
+        raise B200EmbedError(int(nb), load_library().b200_corpus_last_error().decode())
+    return order, begins[:nb + 1].copy()
+
+
+class Corpus:
+    """Owns one b200_corpus handle: shards of sentences in, embeddings out in input order, over all the listed GPUs."""
+
+    def __init__(self, shape: W.BertShape, ingest: "Ingest", devices, safetensors_path: str | None = None, seed: int = 1234,
+                 tokenizer_threads: int = 0, max_batch_sentences: int = 0, max_batch_tokens: int = 0, operands: str = "default"):
+        self.lib = load_library()
+        self.shape, self.ingest = shape, ingest  # the tokenizer must outlive the corpus handle
+        cfg = Config(shape.vocab_size, shape.hidden_size, shape.num_hidden_layers, shape.num_attention_heads,
+                     shape.intermediate_size, shape.max_position_embeddings, shape.type_vocab_size,
+                     shape.hidden_act, shape.layer_norm_eps, 0, OPERAND_NAMES[operands])
+        dev = np.ascontiguousarray(list(devices), dtype=np.int32)
+        h = _P()
+        rc = self.lib.b200_corpus_create(C.byref(cfg), safetensors_path.encode() if safetensors_path else None, seed, dev.ctypes.data,
+                                         len(dev), ingest._h, tokenizer_threads, max_batch_sentences, max_batch_tokens, C.byref(h))
+        if rc != 0:
+            raise B200EmbedError(rc, self.lib.b200_corpus_last_error().decode())
+        self.h, self._keep = h, {}
+
+    def submit(self, text: bytes, begin, end, out: np.ndarray, flags: int = 0) -> int:
+        """Shard = sentences text[begin[i]:end[i]]; out [n, hidden] f32. Everything is kept alive until wait(ticket)."""
+        begin = np.ascontiguousarray(begin, dtype=np.int64)
+        end = np.ascontiguousarray(end, dtype=np.int64)
+        assert out.dtype == np.float32 and out.flags.c_contiguous and out.shape == (len(begin), self.shape.hidden_size)
+        t = C.c_int64()
+        rc = self.lib.b200_corpus_submit(self.h, C.c_char_p(text), begin.ctypes.data, end.ctypes.data, len(begin), flags,
+                                         out.ctypes.data, C.byref(t))
+        if rc != 0:
+            raise B200EmbedError(rc, self.lib.b200_corpus_last_error().decode())
+        self._keep[t.value] = (text, begin, end, out)
+        return t.value
+
+    def wait(self, ticket: int) -> np.ndarray:
+        rc = self.lib.b200_corpus_wait(self.h, ticket)
+        kept = self._keep.pop(ticket, None)
+        if rc != 0:
+            raise B200EmbedError(rc, self.lib.b200_corpus_last_error().decode())
+        return kept[3] if kept else None
+
+    def stats(self, reset: bool = False) -> dict:
+        st = CorpusStats()
+        self.lib.b200_corpus_stats_read(self.h, C.byref(st), int(reset))
+        g = st.gpus
+        d = {k: getattr(st, k) for k in ("sentences", "tokens", "micro_batches", "tokenizer_threads", "gpus", "tokenize_busy_s",
+                                         "plan_s", "gather_s", "gpu_wait_s", "scatter_s")}
+        for k in ("per_gpu_active_s", "per_gpu_sentences", "per_gpu_tokens", "per_gpu_batches"):
+            d[k] = list(getattr(st, k))[:g]
+        return d
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.b200_corpus_destroy(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 def op_gemm_bf16(d_a, d_b, d_bias, m, n, k, act, block_n, d_c, stream=0):

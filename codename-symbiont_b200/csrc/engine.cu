@@ -863,8 +863,9 @@ int32_t b200_embed_wait(b200_embed* h, int64_t ticket) {
     return rc;
 }
 
-int32_t b200_embed_forward_varlen(b200_embed* h, const uint32_t* ids, const uint32_t* tt, const int32_t* cu,
-                                  int32_t batch, int32_t total, int32_t max_seqlen, uint32_t flags, float* out) {
+// Validates a packed request on the host; B200_EMBED_OK with batch == 0 means "nothing to do".
+static int validate_varlen(const b200_embed* h, const uint32_t* ids, const uint32_t* tt, const int32_t* cu, int32_t batch,
+                           int32_t total, int32_t max_seqlen, const float* out) {
     if (!h) return fail(B200_EMBED_ERR_INVALID_ARG, "null handle");
     if (batch < 0 || total < 0) return fail(B200_EMBED_ERR_INVALID_ARG, "negative batch or total_tokens");
     if (batch == 0) return B200_EMBED_OK;
@@ -875,45 +876,84 @@ int32_t b200_embed_forward_varlen(b200_embed* h, const uint32_t* ids, const uint
         const int len = cu[b + 1] - cu[b];
         if (len < 0 || len > max_seqlen) return fail(B200_EMBED_ERR_INVALID_ARG, "cu_seqlens not monotone or a sentence longer than max_seqlen");
     }
+    return B200_EMBED_OK;
+}
+
+// Enqueues a packed host-buffer request on context c (H2D, kernels, D2H, status copy); no sync.
+static int enqueue_packed_host(b200_embed* h, Context* c, const uint32_t* ids, const uint32_t* tt, const int32_t* cu,
+                               int32_t batch, int32_t max_seqlen, uint32_t flags, float* out) {
+    cudaStream_t s = c->stream;
+    CU_TRY(cudaStreamWaitEvent(s, c->done, 0));
+    CU_TRY(cudaMemsetAsync(c->d_status, 0, sizeof(int), s));
+    std::vector<int32_t> local;
+    int b0 = 0;
+    while (b0 < batch) {
+        int b1 = b0 + 1;  // at least one sentence per chunk
+        while (b1 < batch && static_cast<size_t>(cu[b1 + 1] - cu[b0]) <= h->cap_tokens) ++b1;
+        const int nb = b1 - b0, ntok = cu[b1] - cu[b0];
+        local.resize(nb + 1);
+        for (int i = 0; i <= nb; ++i) local[i] = cu[b0 + i] - cu[b0];
+        int r = ensure_input_bufs(*c, (size_t)ntok + 1);
+        if (!r) r = ensure_buf(&c->d_out, &c->out_cap, (size_t)nb * h->H);
+        if (!r) r = ensure_batch_bufs(*c, (size_t)nb);
+        if (r) return r;
+        if (ntok > 0) {
+            CU_TRY(cudaMemcpyAsync(c->d_ids, ids + cu[b0], (size_t)ntok * 4, cudaMemcpyHostToDevice, s));
+            CU_TRY(cudaMemcpyAsync(c->d_tt, tt + cu[b0], (size_t)ntok * 4, cudaMemcpyHostToDevice, s));
+        }
+        // `local` is pageable: this copy is staged before the call returns, so reuse is safe
+        CU_TRY(cudaMemcpyAsync(c->d_cu, local.data(), (size_t)(nb + 1) * 4, cudaMemcpyHostToDevice, s));
+        Job j{c->d_ids, nullptr, c->d_tt, c->d_cu, nb, max_seqlen, ntok, flags, c->d_out};
+        if ((r = run_chunk(h, *c, s, j))) return r;
+        CU_TRY(cudaMemcpyAsync(out + (size_t)b0 * h->H, c->d_out, (size_t)nb * h->H * 4, cudaMemcpyDeviceToHost, s));
+        b0 = b1;
+    }
+    CU_TRY(cudaMemcpyAsync(c->h_status, c->d_status, sizeof(int), cudaMemcpyDeviceToHost, s));
+    CU_TRY(cudaEventRecord(c->done, s));
+    return B200_EMBED_OK;
+}
+
+int32_t b200_embed_forward_varlen(b200_embed* h, const uint32_t* ids, const uint32_t* tt, const int32_t* cu,
+                                  int32_t batch, int32_t total, int32_t max_seqlen, uint32_t flags, float* out) {
+    int rc = validate_varlen(h, ids, tt, cu, batch, total, max_seqlen, out);
+    if (rc || batch == 0) return rc;
     DeviceGuard guard(h->device);
     if (!guard.ok) return fail(B200_EMBED_ERR_CUDA, "cudaSetDevice failed");
     Context* c = lease(h, true);
-    cudaStream_t s = c->stream;
-    int rc = B200_EMBED_OK;
-    auto body = [&]() -> int {
-        CU_TRY(cudaStreamWaitEvent(s, c->done, 0));
-        CU_TRY(cudaMemsetAsync(c->d_status, 0, sizeof(int), s));
-        std::vector<int32_t> local;
-        int b0 = 0;
-        while (b0 < batch) {
-            int b1 = b0 + 1;  // at least one sentence per chunk
-            while (b1 < batch && static_cast<size_t>(cu[b1 + 1] - cu[b0]) <= h->cap_tokens) ++b1;
-            const int nb = b1 - b0, ntok = cu[b1] - cu[b0];
-            local.resize(nb + 1);
-            for (int i = 0; i <= nb; ++i) local[i] = cu[b0 + i] - cu[b0];
-            int r = ensure_input_bufs(*c, (size_t)ntok + 1);
-            if (!r) r = ensure_buf(&c->d_out, &c->out_cap, (size_t)nb * h->H);
-            if (!r) r = ensure_batch_bufs(*c, (size_t)nb);
-            if (r) return r;
-            if (ntok > 0) {
-                CU_TRY(cudaMemcpyAsync(c->d_ids, ids + cu[b0], (size_t)ntok * 4, cudaMemcpyHostToDevice, s));
-                CU_TRY(cudaMemcpyAsync(c->d_tt, tt + cu[b0], (size_t)ntok * 4, cudaMemcpyHostToDevice, s));
-            }
-            // `local` is pageable: this copy is staged before the call returns, so reuse is safe
-            CU_TRY(cudaMemcpyAsync(c->d_cu, local.data(), (size_t)(nb + 1) * 4, cudaMemcpyHostToDevice, s));
-            Job j{c->d_ids, nullptr, c->d_tt, c->d_cu, nb, max_seqlen, ntok, flags, c->d_out};
-            if ((r = run_chunk(h, *c, s, j))) return r;
-            CU_TRY(cudaMemcpyAsync(out + (size_t)b0 * h->H, c->d_out, (size_t)nb * h->H * 4, cudaMemcpyDeviceToHost, s));
-            b0 = b1;
-        }
-        CU_TRY(cudaMemcpyAsync(c->h_status, c->d_status, sizeof(int), cudaMemcpyDeviceToHost, s));
-        CU_TRY(cudaEventRecord(c->done, s));
-        return B200_EMBED_OK;
-    };
-    rc = body();
+    rc = enqueue_packed_host(h, c, ids, tt, cu, batch, max_seqlen, flags, out);
     const int rc2 = finish(h, *c);
     release(h, c);
     return rc ? rc : rc2;
+}
+
+int32_t b200_embed_submit_varlen(b200_embed* h, const uint32_t* ids, const uint32_t* tt, const int32_t* cu, int32_t batch,
+                                 int32_t total, int32_t max_seqlen, uint32_t flags, float* out, int64_t* ticket) {
+    if (!ticket) return fail(B200_EMBED_ERR_INVALID_ARG, "null ticket pointer");
+    *ticket = 0;
+    int rc = validate_varlen(h, ids, tt, cu, batch, total, max_seqlen, out);
+    if (rc) return rc;
+    DeviceGuard guard(h->device);
+    if (!guard.ok) return fail(B200_EMBED_ERR_CUDA, "cudaSetDevice failed");
+    int idx = -1;
+    Context* c = lease(h, false, &idx);
+    if (!c) return fail(B200_EMBED_ERR_INVALID_ARG, "too many requests in flight (max 4): call b200_embed_wait first");
+    if (batch > 0) {
+        rc = enqueue_packed_host(h, c, ids, tt, cu, batch, max_seqlen, flags, out);
+        if (rc) {
+            cudaStreamSynchronize(c->stream);
+            collect_profile(h, *c);
+            release(h, c);
+            return rc;
+        }
+    } else {
+        *c->h_status = 0;
+    }
+    {
+        std::lock_guard<std::mutex> lk(h->mu);
+        *ticket = h->next_ticket++;
+        h->ticket_of[idx] = *ticket;
+    }
+    return B200_EMBED_OK;
 }
 
 int32_t b200_embed_forward_device(b200_embed* h, const uint32_t* d_ids, const uint32_t* d_mask, const uint32_t* d_tt,

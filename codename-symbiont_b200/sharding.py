@@ -11,36 +11,37 @@ from __future__ import annotations
 import numpy as np
 
 
-def plan_shards(lengths, world: int, token_budget: int, window: int = 65536, shape=None):
+def plan_shards(lengths, world: int, token_budget: int, window: int = 65536, shape=None, max_batch_sentences: int = 1 << 30):
     """-> list over ranks of lists of index arrays (micro-batches of original sentence indices).
 
-    Sentences are sorted by length inside windows of `window` sentences (short with short: fewer wasted
-    128-row tile rows, similar cost per micro-batch), cut at `token_budget` real tokens, then dealt greedily to
-    the rank with the least accumulated cost (longest-processing-time rule)."""
+    A STATIC plan, for callers that run one process per GPU (torchrun) and cannot share a queue: sentences are sorted by
+    length inside windows of `window` sentences and cut at `token_budget` real tokens (the native planner,
+    b200_corpus_plan: short with short, so fewer wasted 128-row tile rows and similar cost per micro-batch), then dealt
+    greedily to the rank with the least accumulated cost (longest-processing-time rule). The one-process driver
+    (b200_corpus_*) needs no dealing: its GPU workers pull micro-batches from one queue. Vectorised: 10 M sentences plan in
+    about a second."""
+    from .abi import corpus_plan
     lengths = np.asarray(lengths, dtype=np.int64)
     n = len(lengths)
-    if shape is not None:
-        cost = np.array([shape.flops_per_sentence(int(s)) for s in np.unique(lengths)])
-        cost = dict(zip(np.unique(lengths).tolist(), cost.tolist()))
-        cost_of = np.vectorize(cost.get, otypes=[np.float64])
+    if shape is not None:  # F(s) per distinct length, looked up through a table
+        table = np.zeros(int(lengths.max()) + 1 if n else 1)
+        for s in np.unique(lengths):
+            table[int(s)] = shape.flops_per_sentence(int(s))
+        sent_cost = table[lengths]
     else:
-        cost_of = lambda s: s.astype(np.float64)
-    batches = []
+        sent_cost = lengths.astype(np.float64)
+    batches, costs = [], []
+    max_len = int(lengths.max()) if n else 1
     for lo in range(0, n, window):
-        idx = np.arange(lo, min(n, lo + window))
-        idx = idx[np.argsort(lengths[idx], kind="stable")]
-        start, tok = 0, 0
-        for k, i in enumerate(idx):
-            if tok + lengths[i] > token_budget and k > start:
-                batches.append(idx[start:k])
-                start, tok = k, 0
-            tok += lengths[i]
-        if start < len(idx):
-            batches.append(idx[start:])
-    costs = [float(cost_of(lengths[b]).sum()) for b in batches]
+        hi = min(n, lo + window)
+        order, begins = corpus_plan(lengths[lo:hi], max(max_len, 1), max_batch_sentences, max(token_budget, max_len))
+        csum = np.concatenate([[0.0], np.cumsum(sent_cost[lo:hi][order])])
+        for k in range(len(begins) - 1):
+            batches.append(order[begins[k]:begins[k + 1]].astype(np.int64) + lo)
+            costs.append(csum[begins[k + 1]] - csum[begins[k]])
     load = np.zeros(world)
     out = [[] for _ in range(world)]
-    for k in np.argsort(costs)[::-1]:
+    for k in np.argsort(costs, kind="stable")[::-1]:
         r = int(np.argmin(load))
         out[r].append(batches[k])
         load[r] += costs[k]
@@ -64,8 +65,14 @@ def scatter_back(n: int, hidden: int, parts):
 def imbalance(plan, lengths, shape=None) -> float:
     """max rank cost / mean rank cost (1.0 = perfect)."""
     lengths = np.asarray(lengths, dtype=np.int64)
-    f = (lambda s: shape.flops_per_sentence(int(s))) if shape is not None else float
-    loads = [sum(sum(f(s) for s in lengths[b]) for b in rank) for rank in plan]
+    if shape is not None:
+        table = np.zeros(int(lengths.max()) + 1)
+        for s in np.unique(lengths):
+            table[int(s)] = shape.flops_per_sentence(int(s))
+        cost = table[lengths]
+    else:
+        cost = lengths.astype(np.float64)
+    loads = [sum(float(cost[b].sum()) for b in rank) for rank in plan]
     return max(loads) / (sum(loads) / len(loads))
 
 

@@ -124,6 +124,12 @@ int32_t b200_embed_submit(b200_embed* h, const uint32_t* input_ids, const uint32
                           const uint32_t* token_type_ids, int32_t batch, int32_t seq_len, uint32_t flags,
                           float* out, int64_t* ticket);
 int32_t b200_embed_wait(b200_embed* h, int64_t ticket);
+/* The same for packed input (the form b200_ingest_encode_packed produces): b200_embed_forward_varlen split into submit and
+ * b200_embed_wait. cu_seqlens is read before the call returns; ids_packed, type_ids_packed and out must stay valid (and,
+ * for overlap, pinned) until the wait. The corpus driver below keeps two of these in flight per GPU. */
+int32_t b200_embed_submit_varlen(b200_embed* h, const uint32_t* ids_packed, const uint32_t* type_ids_packed,
+                                 const int32_t* cu_seqlens, int32_t batch, int32_t total_tokens, int32_t max_seqlen,
+                                 uint32_t flags, float* out, int64_t* ticket);
 
 /* Same computation with all four buffers already resident in device memory (replaces the
  * candle-on-CUDA tensors of :189-198 when the caller keeps data on the GPU). Enqueues on `stream`
@@ -368,6 +374,47 @@ int32_t b200_pipeline_text_to_json(b200_embed* h, const b200_ingest* t, const ch
                                    const char* original_id, const char* source_url, const char* model_name,
                                    uint64_t timestamp_ms, int32_t chunk_sentences, uint32_t flags, char* out,
                                    int64_t out_cap, int64_t* out_len, int64_t* n_sentences);
+
+/* -- corpus ingest over all GPUs of one box (BASELINE config 5) --------------------------------------------------------------
+ * The multi-GPU form of the service's ingest loop, which spawns one task per incoming message onto one shared generator
+ * (preprocessing_service/src/main.rs:355-393) and tokenises inside the embedding call (embedding_generator.rs:146-164): one
+ * process, one model replica + one host worker thread per GPU, a pool of tokeniser threads, no data-path collective (each
+ * GPU reads host memory and its own HBM only). A SHARD is the sentences of one message or a window of a corpus, given as
+ * byte ranges of one UTF-8 text (what b200_ingest_split_sentences produces). b200_corpus_submit returns a ticket at once;
+ * the shard is tokenised in chunks by the pool, its sentences are ordered by token count and cut into micro-batches
+ * (<= max_batch_sentences sentences, <= max_batch_tokens tokens) that the GPU workers take from one queue on demand, two
+ * requests in flight per GPU (b200_embed_submit_varlen) over pinned staging buffers; finished rows are scattered back by
+ * sentence index, so out[i] belongs to sentence i whatever GPU computed it. text / begin / end / out must stay valid until
+ * b200_corpus_wait(ticket) returns; any number of shards may be in flight, from any threads. Needs a b200_ingest
+ * tokenizer (borrowed, must outlive the corpus handle). Errors: b200_corpus_last_error(). */
+#define B200_CORPUS_MAX_GPUS 16
+typedef struct b200_corpus b200_corpus;
+typedef struct b200_corpus_stats {
+    int64_t sentences, tokens, micro_batches;
+    int32_t tokenizer_threads, gpus;
+    double tokenize_busy_s; /* summed over the tokeniser threads */
+    double plan_s;          /* length sort + micro-batch cut */
+    double gather_s, gpu_wait_s, scatter_s; /* summed over the GPU worker threads: staging copies, blocked in wait, result copies */
+    double per_gpu_active_s[B200_CORPUS_MAX_GPUS]; /* first submit .. last retire since the last reset */
+    int64_t per_gpu_sentences[B200_CORPUS_MAX_GPUS], per_gpu_tokens[B200_CORPUS_MAX_GPUS], per_gpu_batches[B200_CORPUS_MAX_GPUS];
+} b200_corpus_stats;
+const char* b200_corpus_last_error(void);
+/* devices: the CUDA ordinals to use (1 .. 16). tokenizer_threads 0 = host cores minus one per GPU. max_batch_sentences 0 =
+ * 16384, max_batch_tokens 0 = 512 Ki (pinned staging per GPU: 2 x (8 B per token + (4 * hidden + 4) B per sentence)). */
+int32_t b200_corpus_create(const b200_embed_config* cfg, const char* safetensors_path, uint64_t seed, const int32_t* devices,
+                           int32_t n_devices, const b200_ingest* tokenizer, int32_t tokenizer_threads,
+                           int32_t max_batch_sentences, int32_t max_batch_tokens, b200_corpus** out);
+void b200_corpus_destroy(b200_corpus* c);
+int32_t b200_corpus_submit(b200_corpus* c, const char* text, const int64_t* begin, const int64_t* end, int64_t n, uint32_t flags,
+                           float* out /* [n, hidden] f32, host */, int64_t* ticket);
+int32_t b200_corpus_wait(b200_corpus* c, int64_t ticket);
+int32_t b200_corpus_stats_read(b200_corpus* c, b200_corpus_stats* out, int32_t reset);
+/* The planner on its own (host arithmetic, no GPU): order[n] = the sentences by ascending token count (stable), cut into
+ * micro-batches of at most max_batch_sentences sentences and max_batch_tokens tokens; micro-batch k is
+ * order[batch_begin[k] .. batch_begin[k + 1]). Returns the number of micro-batches (batch_begin is written when
+ * batch_begin_cap >= that + 1); negative on bad arguments. */
+int64_t b200_corpus_plan(const int32_t* lengths, int64_t n, int32_t max_len, int32_t max_batch_sentences,
+                         int64_t max_batch_tokens, int32_t* order, int64_t* batch_begin, int64_t batch_begin_cap);
 
 #ifdef __cplusplus
 }

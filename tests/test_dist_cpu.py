@@ -120,3 +120,24 @@ def test_merge_topk_padding_and_order(pkg):
     ids_b = np.array([[7, 9, 8]]); sc_b = np.array([[0.9, 0.5, 0.1]], np.float32)
     ids, sc = pkg.sharding.merge_topk([ids_a, ids_b], [sc_a, sc_b], 6)
     assert ids[0].tolist() == [4, 7, 2, 9, 8, -1] and np.isneginf(sc[0, 5]) and sc[0, :5].tolist() == pytest.approx([0.9, 0.9, 0.5, 0.5, 0.1])
+
+
+def test_native_corpus_planner_properties(pkg, built):
+    """b200_corpus_plan (the planner of the one-process multi-GPU driver): a permutation, ascending token counts, stable for
+    equal lengths, every micro-batch inside both budgets, nothing lost at the budget edges."""
+    rng = np.random.default_rng(0)
+    for n, max_s, max_t in [(0, 4, 100), (1, 4, 100), (1000, 64, 900), (70000, 16384, 512 * 1024), (5000, 1 << 30, 128)]:
+        lengths = rng.integers(1, 129, size=n).astype(np.int32)
+        order, begins = pkg.abi.corpus_plan(lengths, 128, max_s, max_t)
+        assert sorted(order.tolist()) == list(range(n))
+        ls = lengths[order]
+        assert np.all(np.diff(ls) >= 0)
+        for l in np.unique(ls):
+            idx = order[ls == l]
+            assert np.all(np.diff(idx) > 0)  # stable
+        assert begins[0] == 0 and begins[-1] == n and (n == 0 or np.all(np.diff(begins) > 0))
+        for a, b in zip(begins[:-1], begins[1:]):
+            assert b - a <= max_s and ls[a:b].sum() <= max(max_t, 128)
+        # greedy cuts: a batch could not have taken the next sentence as well
+        for a, b in zip(begins[:-2], begins[1:-1]):
+            assert b - a == max_s or ls[a:b].sum() + ls[b] > max_t
