@@ -129,6 +129,8 @@ _SIGNATURES = {
     "b200_ingest_vocab_size": (C.c_int32, [_P]),
     "b200_ingest_pad_id": (C.c_int32, [_P]),
     "b200_ingest_split_sentences": (C.c_int64, [_P, C.c_int64, _P, C.c_int64, C.POINTER(C.c_int64), _P, _P, C.c_int64]),
+    "b200_ingest_split_sentences_threads": (C.c_int64, [_P, C.c_int64, _P, C.c_int64, C.POINTER(C.c_int64), _P, _P, C.c_int64,
+                                                        C.c_int32]),
     "b200_ingest_encode_packed": (C.c_int64, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, _P, _P, C.c_int64, _P]),
     "b200_ingest_encode": (C.c_int32, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, _P, _P, _P, _P]),
 }
@@ -237,7 +239,7 @@ def _check_ingest(rc: int):
         raise B200EmbedError(int(rc), load_library().b200_ingest_last_error().decode(errors="replace"))
 
 
-def split_sentences(raw_text):
+def split_sentences(raw_text, threads: int = 0):
     """process_raw_text_message's splitter (preprocessing_service/src/main.rs:28-63) -> (cleaned: bytes, begin, end);
     sentence i is cleaned[begin[i]:end[i]]. An empty cleaned text raises like the reference's Err("Cleaned text is empty")."""
     lib = load_library()
@@ -248,8 +250,8 @@ def split_sentences(raw_text):
     while True:
         begin = np.empty(cap, dtype=np.int64)
         end = np.empty(cap, dtype=np.int64)
-        n = lib.b200_ingest_split_sentences(raw, len(raw), cleaned.ctypes.data, len(cleaned), C.byref(clen), begin.ctypes.data,
-                                            end.ctypes.data, cap)
+        n = lib.b200_ingest_split_sentences_threads(raw, len(raw), cleaned.ctypes.data, len(cleaned), C.byref(clen),
+                                                    begin.ctypes.data, end.ctypes.data, cap, threads)
         if n <= cap:
             break
         cap = int(n)

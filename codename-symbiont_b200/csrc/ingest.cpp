@@ -679,13 +679,19 @@ static void clean_chunk(const unsigned char* p, const unsigned char* e, char* ou
 
 int64_t b200_ingest_split_sentences(const char* raw_text, int64_t len, char* cleaned, int64_t cleaned_cap,
                                     int64_t* cleaned_len, int64_t* begin, int64_t* end, int64_t max_sentences) {
+    return b200_ingest_split_sentences_threads(raw_text, len, cleaned, cleaned_cap, cleaned_len, begin, end, max_sentences, 0);
+}
+
+int64_t b200_ingest_split_sentences_threads(const char* raw_text, int64_t len, char* cleaned, int64_t cleaned_cap,
+                                            int64_t* cleaned_len, int64_t* begin, int64_t* end, int64_t max_sentences,
+                                            int32_t threads) {
     if (!raw_text || len < 0 || !cleaned || cleaned_cap < len || !cleaned_len || max_sentences < 0 ||
         (max_sentences > 0 && (!begin || !end)))
         return fail(B200_EMBED_ERR_INVALID_ARG, "split_sentences: bad pointer or capacity (cleaned_cap must be >= len)");
     const unsigned char* base = reinterpret_cast<const unsigned char*>(raw_text);
     // split_whitespace().collect().join(" ") and the cuts after '.', '?', '!' in one pass; a long text is processed in
     // chunks (cut at ASCII whitespace) on several threads - the result does not depend on the chunking
-    int nt = static_cast<int>(std::thread::hardware_concurrency());
+    int nt = threads > 0 ? threads : static_cast<int>(std::thread::hardware_concurrency());
     if (nt < 1) nt = 1;
     if (static_cast<int64_t>(nt) > len / (256 * 1024)) nt = static_cast<int>(len / (256 * 1024));
     if (nt < 1) nt = 1;

@@ -306,6 +306,11 @@ int32_t b200_ingest_pad_id(const b200_ingest* t);
  * reference answers "Cleaned text is empty for id: .."). Negative on bad arguments. */
 int64_t b200_ingest_split_sentences(const char* raw_text, int64_t len, char* cleaned, int64_t cleaned_cap,
                                     int64_t* cleaned_len, int64_t* begin, int64_t* end, int64_t max_sentences);
+/* The same with the number of worker threads given (0 = every host core, what the call above uses): a driver that splits
+ * several texts side by side passes 1 so that the calls do not each start a thread per core. */
+int64_t b200_ingest_split_sentences_threads(const char* raw_text, int64_t len, char* cleaned, int64_t cleaned_cap,
+                                            int64_t* cleaned_len, int64_t* begin, int64_t* end, int64_t max_sentences,
+                                            int32_t threads);
 
 /* tokenizer.encode_batch(inputs, true) (embedding_generator.rs:160-187): sentence i is text[begin[i], end[i]) in
  * UTF-8; row i of ids / mask / type_ids ([n, seq_len] u32, row-major) receives [CLS] tokens [SEP] then padding,
