@@ -8,6 +8,7 @@
 // of chunk c - 1 straight into the caller's buffer; every stage is internally multi-threaded where it is CPU work. Host
 // only: everything below goes through the C ABI of the other files.
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -34,36 +35,51 @@ int fail(int code, const std::string& msg) {
 // Pinned staging buffers for the embeddings of a chunk, kept for the life of the process: pinning memory costs about as
 // much per megabyte as copying it several times, so a service that converts message after message must not pay it per call.
 struct PinnedPool {
+    static constexpr size_t kMaxIdleBytes = size_t(1) << 30;  // idle buffers kept at most; the smallest go first beyond that
     std::mutex mu;
-    std::vector<std::pair<void*, size_t>> free_list;
+    std::vector<std::pair<void*, size_t>> free_list, in_use;
     void* acquire(size_t bytes) {
         {
             std::lock_guard<std::mutex> lk(mu);
-            for (size_t i = 0; i < free_list.size(); ++i)
-                if (free_list[i].second >= bytes) {
-                    void* p = free_list[i].first;
-                    sizes_push(p, free_list[i].second);
-                    free_list.erase(free_list.begin() + static_cast<long>(i));
-                    return p;
-                }
+            size_t best = free_list.size();
+            for (size_t i = 0; i < free_list.size(); ++i)  // best fit: the smallest idle buffer that is large enough
+                if (free_list[i].second >= bytes && (best == free_list.size() || free_list[i].second < free_list[best].second)) best = i;
+            if (best < free_list.size()) {
+                in_use.push_back(free_list[best]);
+                void* p = free_list[best].first;
+                free_list.erase(free_list.begin() + static_cast<long>(best));
+                return p;
+            }
         }
         void* p = nullptr;
         if (b200_embed_host_alloc(bytes, &p) != B200_EMBED_OK) return nullptr;
         std::lock_guard<std::mutex> lk(mu);
-        sizes_push(p, bytes);
+        in_use.emplace_back(p, bytes);
         return p;
     }
     void release(void* p) {
-        std::lock_guard<std::mutex> lk(mu);
-        for (size_t i = 0; i < in_use.size(); ++i)
-            if (in_use[i].first == p) {
-                free_list.push_back(in_use[i]);
-                in_use.erase(in_use.begin() + static_cast<long>(i));
-                return;
+        std::vector<void*> drop;
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            for (size_t i = 0; i < in_use.size(); ++i)
+                if (in_use[i].first == p) {
+                    free_list.push_back(in_use[i]);
+                    in_use.erase(in_use.begin() + static_cast<long>(i));
+                    break;
+                }
+            size_t idle = 0;
+            for (auto& f : free_list) idle += f.second;
+            while (idle > kMaxIdleBytes && !free_list.empty()) {  // a grown chunk size leaves small buffers behind: unpin them
+                size_t k = 0;
+                for (size_t i = 1; i < free_list.size(); ++i)
+                    if (free_list[i].second < free_list[k].second) k = i;
+                idle -= free_list[k].second;
+                drop.push_back(free_list[k].first);
+                free_list.erase(free_list.begin() + static_cast<long>(k));
             }
+        }
+        for (void* d : drop) b200_embed_host_free(d);
     }
-    std::vector<std::pair<void*, size_t>> in_use;
-    void sizes_push(void* p, size_t n) { in_use.emplace_back(p, n); }  // caller holds mu
 };
 PinnedPool g_pool;
 
@@ -81,7 +97,7 @@ extern "C" {
 
 const char* b200_pipeline_last_error(void) { return g_pipe_err.c_str(); }
 
-int32_t b200_pipeline_text_to_json(b200_embed* h, const b200_ingest* t, const char* raw_text, int64_t len,
+static int32_t pipeline_text_to_json_impl(b200_embed* h, const b200_ingest* t, const char* raw_text, int64_t len,
                                    const char* original_id, const char* source_url, const char* model_name,
                                    uint64_t timestamp_ms, int32_t chunk_sentences, uint32_t flags, char* out, int64_t out_cap,
                                    int64_t* out_len, int64_t* n_sentences) {
@@ -136,14 +152,16 @@ int32_t b200_pipeline_text_to_json(b200_embed* h, const b200_ingest* t, const ch
     std::vector<Chunk> chunks(static_cast<size_t>(nchunks));
     std::mutex mu;
     std::condition_variable cv;
-    int tokenised = 0, embedded = 0, formatted = 0, rc = B200_EMBED_OK;
+    int tokenised = 0, embedded = 0, formatted = 0;
+    std::atomic<int> rc{B200_EMBED_OK};  // written under mu, read by the stage loops without it
     std::string err;
     auto set_error = [&](int code, const char* msg) {
         std::lock_guard<std::mutex> lk(mu);
-        if (rc == B200_EMBED_OK) { rc = code; err = msg; }
+        if (rc.load() == B200_EMBED_OK) { err = msg; rc.store(code); }
         cv.notify_all();
     };
     std::thread gpu([&] {
+      try {
         for (int c = 0; c < nchunks; ++c) {
             {
                 std::unique_lock<std::mutex> lk(mu);
@@ -163,9 +181,13 @@ int32_t b200_pipeline_text_to_json(b200_embed* h, const b200_ingest* t, const ch
             }
             cv.notify_all();
         }
+      } catch (const std::exception& e) { set_error(B200_EMBED_ERR_OOM, e.what()); }
     });
     int64_t at = hl;  // write position in `out` (only the JSON thread moves it)
-    std::thread json([&] {
+    std::thread json;
+    try {
+    json = std::thread([&] {
+      try {
         for (int c = 0; c < nchunks; ++c) {
             {
                 std::unique_lock<std::mutex> lk(mu);
@@ -185,7 +207,15 @@ int32_t b200_pipeline_text_to_json(b200_embed* h, const b200_ingest* t, const ch
             cv.notify_all();
             if (trace) std::fprintf(stderr, "[pipeline] chunk %d formatted %.1f ms\n", c, now_ms());
         }
+      } catch (const std::exception& e) { set_error(B200_EMBED_ERR_OOM, e.what()); }
     });
+    } catch (const std::exception& e) {  // the second thread could not be started: stop the first, report
+        set_error(B200_EMBED_ERR_OOM, e.what());
+        gpu.join();
+        for (int i = 0; i < NBUF; ++i) g_pool.release(ebuf[i]);
+        return fail(rc.load(), err);
+    }
+    try {
     for (int c = 0; c < nchunks; ++c) {  // this thread tokenises, at most two chunks ahead of the GPU
         {
             std::unique_lock<std::mutex> lk(mu);
@@ -218,6 +248,7 @@ int32_t b200_pipeline_text_to_json(b200_embed* h, const b200_ingest* t, const ch
         }
         cv.notify_all();
     }
+    } catch (const std::exception& e) { set_error(B200_EMBED_ERR_OOM, e.what()); }
     gpu.join();
     json.join();
     for (int i = 0; i < NBUF; ++i) g_pool.release(ebuf[i]);
@@ -225,6 +256,18 @@ int32_t b200_pipeline_text_to_json(b200_embed* h, const b200_ingest* t, const ch
     std::memmove(out + at, out + out_cap - tl, static_cast<size_t>(tl));
     *out_len = at + tl;
     return B200_EMBED_OK;
+}
+
+int32_t b200_pipeline_text_to_json(b200_embed* h, const b200_ingest* t, const char* raw_text, int64_t len,
+                                   const char* original_id, const char* source_url, const char* model_name,
+                                   uint64_t timestamp_ms, int32_t chunk_sentences, uint32_t flags, char* out, int64_t out_cap,
+                                   int64_t* out_len, int64_t* n_sentences) {
+    try {  // nothing may leave through the C boundary (allocation failures of the buffers set up before the stages start)
+        return pipeline_text_to_json_impl(h, t, raw_text, len, original_id, source_url, model_name, timestamp_ms, chunk_sentences,
+                                          flags, out, out_cap, out_len, n_sentences);
+    } catch (const std::exception& e) {
+        return fail(B200_EMBED_ERR_OOM, std::string("pipeline: ") + e.what());
+    }
 }
 
 }  // extern "C"

@@ -75,8 +75,10 @@ __global__ void normalize_rows_kernel(float* __restrict__ v, int64_t n, int dim)
         s = fmaf(x.x, x.x, s); s = fmaf(x.y, x.y, s); s = fmaf(x.z, x.z, s); s = fmaf(x.w, x.w, s);
     }
     s = warp_sum(s);
+    // Qdrant's cosine_preprocess tests the SQUARED length (is_length_zero_or_normalized): below f32::EPSILON, or within
+    // 1e-6 of 1, leaves the vector as it is
+    if (s < 1.1920929e-07f || fabsf(s - 1.0f) <= 1e-6f) return;
     const float len = sqrtf(s);
-    if (len < 1.1920929e-07f || fabsf(len - 1.0f) < 1e-6f) return;  // zero or already normalised: unchanged
     for (int j = lane; j < n4; j += 32) {
         float4 x = p[j];
         x.x /= len; x.y /= len; x.z /= len; x.w /= len;
@@ -457,31 +459,43 @@ int ensure_capacity(b200_index* ix, int64_t want) {
     if (want <= ix->cap) return B200_EMBED_OK;
     int64_t cap = ix->cap > 0 ? ix->cap : 4096;
     while (cap < want) cap *= 2;
-    float* nv = nullptr;
-    IX_TRY(cudaMalloc(&nv, static_cast<size_t>(cap) * ix->dim * sizeof(float)));
-    if (ix->n > 0) IX_TRY(cudaMemcpyAsync(nv, ix->vecs, static_cast<size_t>(ix->n) * ix->dim * sizeof(float), cudaMemcpyDeviceToDevice, ix->stream));
-    IX_TRY(cudaStreamSynchronize(ix->stream));
-    if (ix->vecs) cudaFree(ix->vecs);
-    ix->vecs = nv;
-    if (ix->vecs16) {  // the bf16 copy grows with the matrix
-        __nv_bfloat16* n16 = nullptr;
-        IX_TRY(cudaMalloc(&n16, static_cast<size_t>(cap) * ix->dim * sizeof(__nv_bfloat16)));
-        if (ix->n > 0) IX_TRY(cudaMemcpy(n16, ix->vecs16, static_cast<size_t>(ix->n) * ix->dim * sizeof(__nv_bfloat16), cudaMemcpyDeviceToDevice));
-        cudaFree(ix->vecs16);
-        ix->vecs16 = n16;
-    }
-    if (ix->d_scores) cudaFree(ix->d_scores);
-    ix->d_scores = nullptr;
-    IX_TRY(cudaMalloc(&ix->d_scores, static_cast<size_t>(cap) * QT_MAX * sizeof(float)));
-    // first level keeps at most K_MAX of every SEL_CHUNK candidates
-    const int64_t cand = level_blocks(cap) * K_MAX;
+    // Every new buffer is allocated (and the rows copied) before any old one is touched: a failed allocation leaves the
+    // index exactly as it was, still answering searches.
+    const int64_t cand = level_blocks(cap) * K_MAX;  // the first level keeps at most K_MAX of every SEL_CHUNK candidates
+    float *nv = nullptr, *nsc = nullptr, *ncsc[2] = {nullptr, nullptr};
+    __nv_bfloat16* n16 = nullptr;
+    int64_t* ncid[2] = {nullptr, nullptr};
+    auto undo = [&](cudaError_t e, const char* what) {
+        for (void* p : {static_cast<void*>(nv), static_cast<void*>(nsc), static_cast<void*>(n16), static_cast<void*>(ncsc[0]),
+                        static_cast<void*>(ncsc[1]), static_cast<void*>(ncid[0]), static_cast<void*>(ncid[1])})
+            if (p) cudaFree(p);
+        cudaGetLastError();
+        return fail(e == cudaErrorMemoryAllocation ? B200_EMBED_ERR_OOM : B200_EMBED_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+    };
+    cudaError_t e;
+    if ((e = cudaMalloc(&nv, static_cast<size_t>(cap) * ix->dim * sizeof(float))) != cudaSuccess) return undo(e, "index rows");
+    if (ix->vecs16 && (e = cudaMalloc(&n16, static_cast<size_t>(cap) * ix->dim * sizeof(__nv_bfloat16))) != cudaSuccess) return undo(e, "bf16 rows");
+    if ((e = cudaMalloc(&nsc, static_cast<size_t>(cap) * QT_MAX * sizeof(float))) != cudaSuccess) return undo(e, "scores");
     for (int i = 0; i < 2; ++i) {
-        if (ix->d_csc[i]) cudaFree(ix->d_csc[i]);
-        if (ix->d_cid[i]) cudaFree(ix->d_cid[i]);
-        ix->d_csc[i] = nullptr; ix->d_cid[i] = nullptr;
-        IX_TRY(cudaMalloc(&ix->d_csc[i], static_cast<size_t>(cand) * QT_MAX * sizeof(float)));
-        IX_TRY(cudaMalloc(&ix->d_cid[i], static_cast<size_t>(cand) * QT_MAX * sizeof(int64_t)));
+        if ((e = cudaMalloc(&ncsc[i], static_cast<size_t>(cand) * QT_MAX * sizeof(float))) != cudaSuccess) return undo(e, "candidate scores");
+        if ((e = cudaMalloc(&ncid[i], static_cast<size_t>(cand) * QT_MAX * sizeof(int64_t))) != cudaSuccess) return undo(e, "candidate ids");
     }
+    if (ix->n > 0) {
+        if ((e = cudaMemcpyAsync(nv, ix->vecs, static_cast<size_t>(ix->n) * ix->dim * sizeof(float), cudaMemcpyDeviceToDevice, ix->stream)) != cudaSuccess)
+            return undo(e, "copy rows");
+        if (n16 && (e = cudaMemcpyAsync(n16, ix->vecs16, static_cast<size_t>(ix->n) * ix->dim * sizeof(__nv_bfloat16), cudaMemcpyDeviceToDevice,
+                                        ix->stream)) != cudaSuccess)
+            return undo(e, "copy bf16 rows");
+    }
+    if ((e = cudaStreamSynchronize(ix->stream)) != cudaSuccess) return undo(e, "copy rows");
+    for (void* p : {static_cast<void*>(ix->vecs), static_cast<void*>(ix->vecs16), static_cast<void*>(ix->d_scores),
+                    static_cast<void*>(ix->d_csc[0]), static_cast<void*>(ix->d_csc[1]), static_cast<void*>(ix->d_cid[0]),
+                    static_cast<void*>(ix->d_cid[1])})
+        if (p) cudaFree(p);
+    ix->vecs = nv;
+    ix->vecs16 = n16;
+    ix->d_scores = nsc;
+    for (int i = 0; i < 2; ++i) { ix->d_csc[i] = ncsc[i]; ix->d_cid[i] = ncid[i]; }
     ix->cand_cap = cand;
     ix->cap = cap;
     return B200_EMBED_OK;

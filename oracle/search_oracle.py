@@ -5,7 +5,8 @@ CPU restatement of what the consumer's search returns for a collection created w
 :319-403 results in descending score order). The arithmetic lives in the Qdrant server, which is not part of the
 reference tree (the service only holds the client crate `qdrant-client`, vector_memory_service/Cargo.toml); restated
 from its published source (lib/segment/src/spaces/simple.rs): cosine_preprocess divides a vector by its f32 length
-unless the length is < f32::EPSILON or within 1e-6 of 1, on insert and on the query; the score is the dot product.
+unless its SQUARED length (is_length_zero_or_normalized) is < f32::EPSILON or within 1e-6 of 1, on insert and on the query;
+the score is the dot product.
 Qdrant answers exactly (full scan) below its indexing threshold and approximately (HNSW) above it; the restatement is
 the exact answer. The reference holds no fixture for it: "parity unpinned" for the search row.
 Scores are accumulated in float64 here, so that the checker does not depend on a summation order; ties (equal
@@ -16,8 +17,9 @@ import numpy as np
 
 def cosine_preprocess(v: np.ndarray) -> np.ndarray:
     v = np.asarray(v, dtype=np.float32)
-    length = np.sqrt(np.sum(v.astype(np.float64) ** 2, axis=-1, keepdims=True)).astype(np.float32)
-    keep = (length < np.finfo(np.float32).eps) | (np.abs(length - np.float32(1.0)) < np.float32(1e-6))
+    sq = np.sum(v.astype(np.float64) ** 2, axis=-1, keepdims=True).astype(np.float32)
+    length = np.sqrt(sq.astype(np.float64)).astype(np.float32)
+    keep = (sq < np.finfo(np.float32).eps) | (np.abs(sq - np.float32(1.0)) <= np.float32(1e-6))
     with np.errstate(divide="ignore", invalid="ignore"):
         out = (v / length).astype(np.float32)
     return np.where(keep, v, out)
