@@ -28,6 +28,7 @@
 #include <vector>
 
 #include "../../include/b200_embed.h"
+#include "ingest_unigram.h"
 #include "bert_unicode_tables.h"
 
 namespace {
@@ -326,6 +327,11 @@ struct Added { std::string content; int32_t id; };
 }  // namespace
 
 struct b200_ingest {
+    int kind = 0;  // 0 WordPiece (BERT pipeline), 1 Unigram (SentencePiece / XLM-R pipeline, ingest_unigram.h)
+    b200::unigram::Model uni;
+    b200::unigram::Precompiled pre;
+    bool has_pre = false, collapse_spaces = false, ws_split = false, meta_prepend = true;
+    std::string meta = "\xE2\x96\x81";  // Metaspace replacement (U+2581)
     Vocab whole;  // every vocabulary entry: looked up for the first piece of a word
     Vocab cont;   // entries that start with the continuation prefix, stored without it
     std::vector<Added> added;  // matched on the raw text before normalisation, leftmost-longest
@@ -342,6 +348,112 @@ struct b200_ingest {
 namespace {
 
 enum : uint8_t { A_APPEND = 0, A_SKIP = 1, A_BOUNDARY = 2, A_ISOLATE = 3 };
+
+// The Unigram model, its normalizer and its pre-tokenizer out of tokenizer.json (the shapes an XLM-R / SentencePiece
+// conversion produces; anything else is refused by name).
+bool load_unigram(const JVal& root, const JVal& model, b200_ingest* t, std::string* err) {
+    const JVal* vocab = model.find("vocab");
+    if (!vocab || vocab->type != JVal::ARR || vocab->arr.empty()) { *err = "tokenizer.json: Unigram model without a vocab list"; return false; }
+    if (model.is_true("byte_fallback", false)) { *err = "tokenizer.json: Unigram byte_fallback is not supported"; return false; }
+    const JVal* unk = model.find("unk_id");
+    if (!unk || unk->type != JVal::NUM) { *err = "tokenizer.json: Unigram model without unk_id"; return false; }
+    std::vector<std::pair<std::string, int32_t>> keys;
+    keys.reserve(vocab->arr.size());
+    t->uni.score.resize(vocab->arr.size());
+    double mn = 0;
+    for (size_t i = 0; i < vocab->arr.size(); ++i) {
+        const JVal& e = vocab->arr[i];
+        if (e.type != JVal::ARR || e.arr.size() != 2 || e.arr[0].type != JVal::STR || e.arr[1].type != JVal::NUM) {
+            *err = "tokenizer.json: Unigram vocab entry is not [piece, score]";
+            return false;
+        }
+        keys.emplace_back(e.arr[0].s, static_cast<int32_t>(i));
+        t->uni.score[i] = e.arr[1].n;
+        if (i == 0 || e.arr[1].n < mn) mn = e.arr[1].n;
+    }
+    t->uni.min_score = mn;
+    t->uni.unk_id = static_cast<int32_t>(unk->n);
+    if (t->uni.unk_id < 0 || static_cast<size_t>(t->uni.unk_id) >= vocab->arr.size()) { *err = "tokenizer.json: unk_id out of range"; return false; }
+    t->unk_id = t->uni.unk_id;
+    t->uni.build(keys);
+
+    auto one_normalizer = [&](const JVal& nz) -> bool {
+        const JVal* ty = nz.find("type");
+        if (!ty || ty->type != JVal::STR) { *err = "tokenizer.json: normalizer without a type"; return false; }
+        if (ty->s == "Precompiled") {
+            const JVal* cm = nz.find("precompiled_charsmap");
+            std::string blob;
+            if (!cm || cm->type != JVal::STR || !b200::unigram::base64_decode(cm->s, &blob) || !t->pre.load(blob)) {
+                *err = "tokenizer.json: bad precompiled_charsmap";
+                return false;
+            }
+            if (t->collapse_spaces) { *err = "tokenizer.json: Precompiled after Replace is not supported"; return false; }
+            t->has_pre = true;
+            return true;
+        }
+        if (ty->s == "Replace") {
+            const JVal* pat = nz.find("pattern");
+            const JVal* rx = pat ? pat->find("Regex") : nullptr;
+            const JVal* content = nz.find("content");
+            if (!rx || rx->type != JVal::STR || rx->s != " {2,}" || !content || content->type != JVal::STR || content->s != " ") {
+                *err = "tokenizer.json: the only Replace normalizer supported is Regex \" {2,}\" -> \" \"";
+                return false;
+            }
+            t->collapse_spaces = true;
+            return true;
+        }
+        *err = "tokenizer.json: normalizer " + ty->s + " is not supported with a Unigram model";
+        return false;
+    };
+    if (const JVal* nz = root.find("normalizer")) {
+        if (nz->type == JVal::OBJ) {
+            const JVal* ty = nz->find("type");
+            if (ty && ty->type == JVal::STR && ty->s == "Sequence") {
+                const JVal* list = nz->find("normalizers");
+                if (!list || list->type != JVal::ARR) { *err = "tokenizer.json: bad normalizer Sequence"; return false; }
+                for (const JVal& one : list->arr)
+                    if (!one_normalizer(one)) return false;
+            } else if (!one_normalizer(*nz)) return false;
+        } else if (nz->type != JVal::NUL) { *err = "tokenizer.json: bad normalizer"; return false; }
+    }
+    bool have_meta = false;
+    auto one_pretok = [&](const JVal& pt) -> bool {
+        const JVal* ty = pt.find("type");
+        if (!ty || ty->type != JVal::STR) { *err = "tokenizer.json: pre_tokenizer without a type"; return false; }
+        if (ty->s == "WhitespaceSplit") {
+            if (have_meta) { *err = "tokenizer.json: WhitespaceSplit after Metaspace is not supported"; return false; }
+            t->ws_split = true;
+            return true;
+        }
+        if (ty->s == "Metaspace") {
+            if (const JVal* r = pt.find("replacement")) if (r->type == JVal::STR && !r->s.empty()) t->meta = r->s;
+            if (const JVal* sp = pt.find("split")) if (sp->type == JVal::BOOL && !sp->b) { *err = "tokenizer.json: Metaspace split = false is not supported"; return false; }
+            t->meta_prepend = pt.is_true("add_prefix_space", true);  // the older spelling
+            if (const JVal* ps = pt.find("prepend_scheme")) {
+                if (ps->type == JVal::STR && ps->s == "always") t->meta_prepend = true;
+                else if (ps->type == JVal::STR && ps->s == "never") t->meta_prepend = false;
+                else { *err = "tokenizer.json: Metaspace prepend_scheme must be always or never"; return false; }
+            }
+            have_meta = true;
+            return true;
+        }
+        *err = "tokenizer.json: pre_tokenizer " + ty->s + " is not supported with a Unigram model";
+        return false;
+    };
+    const JVal* pt = root.find("pre_tokenizer");
+    if (!pt || pt->type != JVal::OBJ) { *err = "tokenizer.json: a Unigram model needs a Metaspace pre_tokenizer"; return false; }
+    {
+        const JVal* ty = pt->find("type");
+        if (ty && ty->type == JVal::STR && ty->s == "Sequence") {
+            const JVal* list = pt->find("pretokenizers");
+            if (!list || list->type != JVal::ARR) { *err = "tokenizer.json: bad pre_tokenizer Sequence"; return false; }
+            for (const JVal& one : list->arr)
+                if (!one_pretok(one)) return false;
+        } else if (!one_pretok(*pt)) return false;
+    }
+    if (!have_meta) { *err = "tokenizer.json: a Unigram model needs a Metaspace pre_tokenizer"; return false; }
+    return true;
+}
 
 bool load_tokenizer(const char* path, b200_ingest* t, std::string* err) {
     std::string text;
@@ -360,16 +472,23 @@ bool load_tokenizer(const char* path, b200_ingest* t, std::string* err) {
     if (!model || model->type != JVal::OBJ) { *err = "tokenizer.json: no model object"; return false; }
     const JVal* mtype = model->find("type");
     const JVal* vocab = model->find("vocab");
+    const bool is_unigram = (mtype && mtype->type == JVal::STR && mtype->s == "Unigram") ||
+                            (!mtype && vocab && vocab->type == JVal::ARR);
+    int32_t max_id = -1;
+    if (is_unigram) {
+        if (!load_unigram(root, *model, t, err)) return false;
+        t->kind = 1;
+        max_id = static_cast<int32_t>(t->uni.score.size()) - 1;
+    } else {
     // old files carry no "type"; a WordPiece model is the one whose vocab is an object and that has no merges
     if ((mtype && mtype->type == JVal::STR && mtype->s != "WordPiece") || !vocab || vocab->type != JVal::OBJ || model->find("merges")) {
-        *err = "tokenizer.json: only a WordPiece model is supported (got " + (mtype && mtype->type == JVal::STR ? mtype->s : std::string("an untyped model")) + ")";
+        *err = "tokenizer.json: only WordPiece and Unigram models are supported (got " + (mtype && mtype->type == JVal::STR ? mtype->s : std::string("an untyped model")) + ")";
         return false;
     }
     std::string prefix = "##", unk = "[UNK]";
     if (const JVal* v = model->find("continuing_subword_prefix")) if (v->type == JVal::STR) prefix = v->s;
     if (const JVal* v = model->find("unk_token")) if (v->type == JVal::STR) unk = v->s;
     if (const JVal* v = model->find("max_input_chars_per_word")) if (v->type == JVal::NUM) t->max_chars = static_cast<int>(v->n);
-    int32_t max_id = -1;
     for (const auto& kv : vocab->obj) {
         if (kv.second.type != JVal::NUM) { *err = "tokenizer.json: vocab id is not a number"; return false; }
         const int32_t id = static_cast<int32_t>(kv.second.n);
@@ -383,6 +502,7 @@ bool load_tokenizer(const char* path, b200_ingest* t, std::string* err) {
     t->cont.finish();
     t->unk_id = t->whole.find(unk.data(), unk.size());
     if (t->unk_id < 0) { *err = "tokenizer.json: unk_token " + unk + " is not in the vocabulary"; return false; }
+    }  // WordPiece model
 
     if (const JVal* at = root.find("added_tokens")) {
         if (at->type == JVal::ARR)
@@ -402,12 +522,15 @@ bool load_tokenizer(const char* path, b200_ingest* t, std::string* err) {
     t->vocab_size = max_id + 1;
     auto token_to_id = [&](const std::string& s) -> int32_t {  // added vocabulary first, then the model's
         for (const Added& a : t->added) if (a.content == s) return a.id;
+        if (t->kind == 1) return t->uni.find(reinterpret_cast<const unsigned char*>(s.data()), s.size());
         return t->whole.find(s.data(), s.size());
     };
     const int32_t pad = token_to_id("[PAD]");  // embedding_generator.rs:76-82
     t->pad_id = pad >= 0 ? pad : 0;
 
-    if (const JVal* nz = root.find("normalizer")) {
+    if (t->kind == 1) {
+        // normalizer and pre-tokenizer were read by load_unigram
+    } else if (const JVal* nz = root.find("normalizer")) {
         if (nz->type == JVal::OBJ) {
             const JVal* ty = nz->find("type");
             if (!ty || ty->type != JVal::STR || ty->s != "BertNormalizer") { *err = "tokenizer.json: only BertNormalizer is supported"; return false; }
@@ -420,7 +543,8 @@ bool load_tokenizer(const char* path, b200_ingest* t, std::string* err) {
         } else if (nz->type != JVal::NUL) { *err = "tokenizer.json: bad normalizer"; return false; }
         else { t->clean_text = t->handle_chinese = t->lowercase = false; }
     } else { t->clean_text = t->handle_chinese = t->lowercase = false; }
-    if (const JVal* pt = root.find("pre_tokenizer")) {
+    if (t->kind == 1) {
+    } else if (const JVal* pt = root.find("pre_tokenizer")) {
         const JVal* ty = pt->find("type");
         if (!ty || ty->type != JVal::STR || ty->s != "BertPreTokenizer") { *err = "tokenizer.json: only BertPreTokenizer is supported"; return false; }
     } else { *err = "tokenizer.json: no pre_tokenizer"; return false; }
@@ -474,6 +598,8 @@ bool load_tokenizer(const char* path, b200_ingest* t, std::string* err) {
 }
 
 struct Scratch {
+    std::string norm, piece;   // Unigram: the normalised segment, the current pre-token with its Metaspace prefix
+    std::vector<b200::unigram::Model::Node> lattice;
     std::string word;          // the current pre-token, normalised, UTF-8
     int word_chars = 0;
     std::vector<int32_t> toks; // the sentence's tokens before the template
@@ -529,7 +655,68 @@ inline void feed_char(const b200_ingest& t, Scratch& sc, uint32_t c, uint8_t kla
 
 // BertNormalizer + BertPreTokenizer + WordPiece over text[b, e), which holds no added token. Stops feeding once
 // `budget` tokens exist: truncation keeps the first ones only.
+// Unigram pipeline for one text segment between added tokens: Precompiled + Replace, WhitespaceSplit, Metaspace, Viterbi.
+void encode_piece_unigram(const b200_ingest& t, Scratch& sc, const unsigned char* b, const unsigned char* e, size_t budget) {
+    if (b >= e) return;
+    sc.norm.clear();
+    if (t.has_pre) t.pre.normalize(b, e, sc.norm);
+    else sc.norm.assign(reinterpret_cast<const char*>(b), static_cast<size_t>(e - b));
+    if (t.collapse_spaces) {  // Replace(Regex " {2,}", " ")
+        size_t w = 0;
+        for (size_t i = 0; i < sc.norm.size(); ++i) {
+            if (sc.norm[i] == ' ' && w > 0 && sc.norm[w - 1] == ' ') continue;
+            sc.norm[w++] = sc.norm[i];
+        }
+        sc.norm.resize(w);
+    }
+    const unsigned char* p = reinterpret_cast<const unsigned char*>(sc.norm.data());
+    const unsigned char* end = p + sc.norm.size();
+    const std::string& rep = t.meta;
+    // one pre-token of the first stage (a whitespace-free run, or the whole segment) through Metaspace and the model
+    auto metaspace = [&](const unsigned char* wb, const unsigned char* we) {
+        sc.piece.clear();
+        for (const unsigned char* q = wb; q < we; ++q) {
+            if (*q == ' ') sc.piece += rep; else sc.piece.push_back(static_cast<char>(*q));
+        }
+        if (t.meta_prepend && sc.piece.compare(0, rep.size(), rep) != 0) sc.piece.insert(0, rep);
+        // split, delimiter merged with what follows: a piece starts at every occurrence of the replacement
+        const unsigned char* s0 = reinterpret_cast<const unsigned char*>(sc.piece.data());
+        const size_t n = sc.piece.size();
+        size_t start = 0;
+        for (size_t i = 0; i <= n && sc.toks.size() < budget;) {
+            const bool at_rep = i + rep.size() <= n && !std::memcmp(s0 + i, rep.data(), rep.size());
+            if (i == n || (at_rep && i > start)) {
+                if (i > start) t.uni.encode(s0 + start, i - start, sc.lattice, sc.toks);
+                start = i;
+                if (i == n) break;
+            }
+            i += at_rep ? rep.size() : 1;
+        }
+    };
+    if (!t.ws_split) {
+        metaspace(p, end);
+        return;
+    }
+    while (p < end && sc.toks.size() < budget) {
+        int len;
+        // skip whitespace, then take the run up to the next whitespace character (char::is_whitespace)
+        while (p < end) {
+            const uint32_t c = utf8_next(p, end, &len);
+            if (!rust_is_whitespace(c)) break;
+            p += len;
+        }
+        const unsigned char* wb = p;
+        while (p < end) {
+            const uint32_t c = utf8_next(p, end, &len);
+            if (rust_is_whitespace(c)) break;
+            p += len;
+        }
+        if (p > wb) metaspace(wb, p);
+    }
+}
+
 void encode_piece(const b200_ingest& t, Scratch& sc, const unsigned char* b, const unsigned char* e, size_t budget) {
+    if (t.kind == 1) { encode_piece_unigram(t, sc, b, e, budget); return; }
     const CharTable& ct = char_table();
     std::string tmp;
     const unsigned char* p = b;

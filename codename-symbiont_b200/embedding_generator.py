@@ -5,10 +5,11 @@ points, same argument meaning, same error behaviour, with the tensor work behind
     EmbeddingGenerator.new(model_dir, revision, force_cpu)          (:17)
     generator.generate_sentence_embeddings(sentences) -> [[f32]]    (:134)
 
-What is unchanged from the reference: the tokenizer's behaviour (a BERT WordPiece tokenizer.json goes through the
-native b200_ingest_* entries, checked bit-exactly against the `tokenizers` library in tests/test_ingest.py; any other
-tokenizer.json goes through the `tokenizers` library itself, the Python binding of the Rust core the reference
-links), Fixed right padding to `max_position_embeddings` with `[PAD]`
+What is unchanged from the reference: the tokenizer's behaviour (a BERT WordPiece tokenizer.json, and the Unigram /
+SentencePiece tokenizer.json of XLM-R checkpoints such as the service's deployed model, go through the native
+b200_ingest_* entries, checked bit-exactly against the `tokenizers` library in tests/test_ingest.py and
+tests/test_ingest_unigram.py; any other tokenizer.json goes through the `tokenizers` library itself, the Python binding
+of the Rust core the reference links), Fixed right padding to `max_position_embeddings` with `[PAD]`
 (:75-91), LongestFirst truncation to the same length (:93-99), `encode_batch(inputs, true)` (:160-164),
 the length check (:172-177), the flattening of ids / attention mask / type ids (:179-187), the order of
 the results and "empty in => empty out" (:135-137). What changes: lines :189-214 (three candle tensors,
@@ -37,7 +38,7 @@ class EmbeddingGenerator:
     def __init__(self, embedder: Embedder, tokenizer, shape: W.BertShape, normalize: bool = False, ingest: Ingest | None = None):
         self.model = embedder
         self.tokenizer = tokenizer  # the `tokenizers` library object, used only when `ingest` is None
-        self.ingest = ingest        # native WordPiece front-end (b200_ingest_*), None for a non-WordPiece tokenizer.json
+        self.ingest = ingest        # native front-end (b200_ingest_*: WordPiece or Unigram), None for any other tokenizer.json
         self.config = shape
         self.normalize = normalize
 
@@ -54,7 +55,7 @@ class EmbeddingGenerator:
         except B200EmbedError as e:
             if e.code != ERR_UNSUPPORTED:
                 raise
-            from tokenizers import Tokenizer  # e.g. the Unigram tokenizer of an XLM-R checkpoint
+            from tokenizers import Tokenizer  # e.g. a BPE tokenizer
 
             tok = Tokenizer.from_file(os.path.join(d, "tokenizer.json"))
             configure_tokenizer(tok, shape.max_position_embeddings)

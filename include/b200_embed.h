@@ -287,12 +287,16 @@ int64_t b200_json_sentence_items_ranges(const char* text, const int64_t* begin, 
 typedef struct b200_ingest b200_ingest;
 const char* b200_ingest_last_error(void);
 
-/* Loads a HuggingFace tokenizer.json holding a BERT WordPiece pipeline (BertNormalizer, BertPreTokenizer, WordPiece,
- * BertProcessing or TemplateProcessing). Replaces Tokenizer::from_file plus the padding / truncation set-up of
- * preprocessing_service/src/embedding_generator.rs:73-99: padding is Fixed(seq_len) on the right with the id of
- * "[PAD]" (0 when the vocabulary has none), type id 0; truncation is LongestFirst to seq_len (seq_len is passed to
- * b200_ingest_encode). B200_EMBED_ERR_IO when the file cannot be read, B200_EMBED_ERR_UNSUPPORTED_SHAPE for any other
- * tokenizer (Unigram / BPE models, other normalizers, added tokens with lstrip / rstrip / single_word / normalized). */
+/* Loads a HuggingFace tokenizer.json. Two pipelines are understood:
+ *   - BERT WordPiece (BertNormalizer, BertPreTokenizer, WordPiece, BertProcessing or TemplateProcessing): the BASELINE models;
+ *   - Unigram / SentencePiece as XLM-R ships it (normalizer Precompiled charsmap [+ Replace " {2,}" -> " "], pre-tokenizer
+ *     [WhitespaceSplit +] Metaspace, model Unigram with unk_id, TemplateProcessing "<s> $A </s>"): the tokenizer of the model
+ *     the service deploys, paraphrase-multilingual-mpnet-base-v2 (preprocessing_service/src/main.rs:305).
+ * Replaces Tokenizer::from_file plus the padding / truncation set-up of preprocessing_service/src/embedding_generator.rs:73-99:
+ * padding is Fixed(seq_len) on the right with the id of "[PAD]" (0 when the vocabulary has none - the XLM-R case, exactly as
+ * the reference falls back), type id 0; truncation is LongestFirst to seq_len (seq_len is passed to b200_ingest_encode).
+ * B200_EMBED_ERR_IO when the file cannot be read, B200_EMBED_ERR_UNSUPPORTED_SHAPE for any other tokenizer (BPE models,
+ * byte fallback, other normalizers / pre-tokenizers, added tokens with lstrip / rstrip / single_word / normalized). */
 int32_t b200_ingest_create(const char* tokenizer_json_path, b200_ingest** out);
 void b200_ingest_destroy(b200_ingest* t);
 int32_t b200_ingest_vocab_size(const b200_ingest* t); /* largest id + 1, added tokens included */
