@@ -107,6 +107,11 @@ _SIGNATURES = {
     "b200_json_envelope": (C.c_int64, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_uint64, _P, C.c_int64, C.POINTER(C.c_int64), _P, C.c_int64,
                                        C.POINTER(C.c_int64)]),
     "b200_json_sentence_items_ranges": (C.c_int64, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P, C.c_int64]),
+    "b200_jsongpu_last_error": (C.c_char_p, []),
+    "b200_jsongpu_create": (C.c_int32, [C.c_int32, C.POINTER(_P)]),
+    "b200_jsongpu_destroy": (None, [_P]),
+    "b200_jsongpu_sentence_items": (C.c_int64, [_P, _P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, _P, C.c_int64]),
+    "b200_jsongpu_sentence_items_host": (C.c_int64, [_P, _P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, _P, C.c_int64]),
     "b200_pipeline_last_error": (C.c_char_p, []),
     "b200_pipeline_text_to_json": (C.c_int32, [_P, _P, _P, C.c_int64, C.c_char_p, C.c_char_p, C.c_char_p, C.c_uint64, C.c_int32, C.c_uint32,
                                                _P, C.c_int64, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
@@ -143,7 +148,7 @@ def declared_symbols() -> list:
     with open(HEADER_PATH) as f:
         text = f.read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
-    return sorted(set(re.findall(r"\b(b200_(?:embed|op|json|ingest|index|pipeline|corpus)_[a-z0-9_]+)\s*\(", text)))
+    return sorted(set(re.findall(r"\b(b200_(?:embed|op|json|jsongpu|ingest|index|pipeline|corpus)_[a-z0-9_]+)\s*\(", text)))
 
 
 def load_library():
@@ -606,6 +611,73 @@ class Embedder:
     def op_mean_pool(self, d_hidden, d_cu, batch, dtype, normalize, d_out, d_hidden_lo=0, stream=0):
         _check(self.lib.b200_op_mean_pool(self.h, d_hidden, d_hidden_lo or None, d_cu, batch, dtype, int(normalize), d_out,
                                           stream or None))
+
+
+def json_sentence_items_ranges(text: bytes, begin, end, embeddings: np.ndarray, first: bool = True, threads: int = 0) -> np.ndarray:
+    """b200_json_sentence_items_ranges (host): the comma-separated items of the sentences text[begin[i]:end[i]]."""
+    lib = load_library()
+    begin = np.ascontiguousarray(begin, dtype=np.int64)
+    end = np.ascontiguousarray(end, dtype=np.int64)
+    emb = np.ascontiguousarray(embeddings, dtype=np.float32)
+    n, dim = emb.shape
+    cap = n * (dim * 17 + 80) + int((end - begin).sum()) * 6 + 64
+    out = np.empty(cap, dtype=np.uint8)
+    got = lib.b200_json_sentence_items_ranges(C.c_char_p(text), begin.ctypes.data, end.ctypes.data, emb.ctypes.data, n, dim, int(first),
+                                              threads, out.ctypes.data, cap)
+    if got < 0:
+        raise B200EmbedError(int(got), "b200_json_sentence_items_ranges failed")
+    return out[:got]
+
+
+class JsonGpu:
+    """b200_jsongpu_*: the JSON items of sentences formatted on the GPU from device-resident embeddings."""
+
+    def __init__(self, device: int = 0):
+        self.lib = load_library()
+        h = _P()
+        rc = self.lib.b200_jsongpu_create(device, C.byref(h))
+        if rc != 0:
+            raise B200EmbedError(rc, self.lib.b200_jsongpu_last_error().decode())
+        self.h = h
+
+    def sentence_items(self, text: bytes, begin, end, d_embeddings: int, n: int, dim: int, first: bool = True, out: np.ndarray | None = None):
+        """-> uint8 array holding the items (a view of `out` when given and large enough; `out` should be pinned)."""
+        begin = np.ascontiguousarray(begin, dtype=np.int64)
+        end = np.ascontiguousarray(end, dtype=np.int64)
+        cap = n * (dim * 17 + 48) + int((end - begin).sum()) * 6 + 64
+        if out is None or out.size < cap:
+            out = np.empty(cap, dtype=np.uint8)
+        got = self.lib.b200_jsongpu_sentence_items(self.h, C.c_char_p(text), begin.ctypes.data, end.ctypes.data, d_embeddings, n, dim,
+                                                   int(first), out.ctypes.data, out.size)
+        if got < 0:
+            raise B200EmbedError(int(got), self.lib.b200_jsongpu_last_error().decode())
+        return out[:got]
+
+    def sentence_items_host(self, text: bytes, begin, end, embeddings: np.ndarray, first: bool = True, out: np.ndarray | None = None):
+        """The same from host embeddings ([n, dim] f32, pinned for speed): uploaded, formatted, the text copied back."""
+        begin = np.ascontiguousarray(begin, dtype=np.int64)
+        end = np.ascontiguousarray(end, dtype=np.int64)
+        assert embeddings.dtype == np.float32 and embeddings.flags.c_contiguous
+        n, dim = embeddings.shape
+        cap = n * (dim * 17 + 48) + int((end - begin).sum()) * 6 + 64
+        if out is None or out.size < cap:
+            out = np.empty(cap, dtype=np.uint8)
+        got = self.lib.b200_jsongpu_sentence_items_host(self.h, C.c_char_p(text), begin.ctypes.data, end.ctypes.data, embeddings.ctypes.data,
+                                                        n, dim, int(first), out.ctypes.data, out.size)
+        if got < 0:
+            raise B200EmbedError(int(got), self.lib.b200_jsongpu_last_error().decode())
+        return out[:got]
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.b200_jsongpu_destroy(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
 
 
 def corpus_plan(lengths, max_len: int, max_batch_sentences: int, max_batch_tokens: int):

@@ -10,7 +10,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libb200_embed.so")
 OBJ_DIR = os.path.join(HERE, "build")
-SOURCES = ["engine.cu", "fp32_ref.cu", "weights_io.cpp", "json_out.cpp", "ingest.cpp", "search.cu", "pipeline.cpp", "corpus.cpp"]
+SOURCES = ["engine.cu", "fp32_ref.cu", "weights_io.cpp", "json_out.cpp", "ingest.cpp", "search.cu", "pipeline.cpp", "corpus.cpp", "json_gpu.cu"]
 # The 16-bit kernels are compiled once per operand format (csrc/fmt.h): as they are for bf16, with -DB200_OPERAND_F16 for
 # IEEE fp16; each build lives in its own namespace and the engine picks per handle.
 FORMAT_SOURCES = ["gemm_tc.cu", "ffn_fused.cu", "attention_tc.cu", "qkv_attention.cu", "elementwise.cu"]

@@ -19,6 +19,7 @@
 #include <vector>
 
 #include "../../include/b200_embed.h"
+#include "pow10_table.h"
 
 namespace {
 
@@ -50,85 +51,7 @@ inline int shortest_digits(float v, char* digits, int* kk) {
 // even. Checked against the library for every finite float (scripts/probes/f32_digits_check.cpp: all 2^31 - 2^23
 // positive values). About 3x faster than std::to_chars + re-layout here.
 constexpr int kPow10Min = -31, kPow10Max = 45;
-const uint64_t kPow10_64[kPow10Max - kPow10Min + 1] = {
-    0x81CEB32C4B43FCF5ULL,
-    0xA2425FF75E14FC32ULL,
-    0xCAD2F7F5359A3B3FULL,
-    0xFD87B5F28300CA0EULL,
-    0x9E74D1B791E07E49ULL,
-    0xC612062576589DDBULL,
-    0xF79687AED3EEC552ULL,
-    0x9ABE14CD44753B53ULL,
-    0xC16D9A0095928A28ULL,
-    0xF1C90080BAF72CB2ULL,
-    0x971DA05074DA7BEFULL,
-    0xBCE5086492111AEBULL,
-    0xEC1E4A7DB69561A6ULL,
-    0x9392EE8E921D5D08ULL,
-    0xB877AA3236A4B44AULL,
-    0xE69594BEC44DE15CULL,
-    0x901D7CF73AB0ACDAULL,
-    0xB424DC35095CD810ULL,
-    0xE12E13424BB40E14ULL,
-    0x8CBCCC096F5088CCULL,
-    0xAFEBFF0BCB24AAFFULL,
-    0xDBE6FECEBDEDD5BFULL,
-    0x89705F4136B4A598ULL,
-    0xABCC77118461CEFDULL,
-    0xD6BF94D5E57A42BDULL,
-    0x8637BD05AF6C69B6ULL,
-    0xA7C5AC471B478424ULL,
-    0xD1B71758E219652CULL,
-    0x83126E978D4FDF3CULL,
-    0xA3D70A3D70A3D70BULL,
-    0xCCCCCCCCCCCCCCCDULL,
-    0x8000000000000000ULL,
-    0xA000000000000000ULL,
-    0xC800000000000000ULL,
-    0xFA00000000000000ULL,
-    0x9C40000000000000ULL,
-    0xC350000000000000ULL,
-    0xF424000000000000ULL,
-    0x9896800000000000ULL,
-    0xBEBC200000000000ULL,
-    0xEE6B280000000000ULL,
-    0x9502F90000000000ULL,
-    0xBA43B74000000000ULL,
-    0xE8D4A51000000000ULL,
-    0x9184E72A00000000ULL,
-    0xB5E620F480000000ULL,
-    0xE35FA931A0000000ULL,
-    0x8E1BC9BF04000000ULL,
-    0xB1A2BC2EC5000000ULL,
-    0xDE0B6B3A76400000ULL,
-    0x8AC7230489E80000ULL,
-    0xAD78EBC5AC620001ULL,
-    0xD8D726B7177A8001ULL,
-    0x878678326EAC9001ULL,
-    0xA968163F0A57B401ULL,
-    0xD3C21BCECCEDA101ULL,
-    0x84595161401484A1ULL,
-    0xA56FA5B99019A5C9ULL,
-    0xCECB8F27F4200F3BULL,
-    0x813F3978F8940985ULL,
-    0xA18F07D736B90BE6ULL,
-    0xC9F2C9CD04674EDFULL,
-    0xFC6F7C4045812297ULL,
-    0x9DC5ADA82B70B59EULL,
-    0xC5371912364CE306ULL,
-    0xF684DF56C3E01BC7ULL,
-    0x9A130B963A6C115DULL,
-    0xC097CE7BC90715B4ULL,
-    0xF0BDC21ABB48DB21ULL,
-    0x96769950B50D88F5ULL,
-    0xBC143FA4E250EB32ULL,
-    0xEB194F8E1AE525FEULL,
-    0x92EFD1B8D0CF37BFULL,
-    0xB7ABC627050305AEULL,
-    0xE596B7B0C643C71AULL,
-    0x8F7E32CE7BEA5C70ULL,
-    0xB35DBF821AE4F38CULL
-};
+const uint64_t kPow10_64[kPow10Max - kPow10Min + 1] = {B200_POW10_64_VALUES};
 inline int floor_log10_pow2(int e) { return (e * 1262611) >> 22; }
 inline int floor_log10_three_quarters_pow2(int e) { return (e * 1262611 - 524031) >> 22; }
 inline int floor_log2_pow10(int e) { return (e * 1741647) >> 19; }

@@ -281,6 +281,25 @@ int64_t b200_json_envelope(const char* original_id, const char* source_url, cons
 int64_t b200_json_sentence_items_ranges(const char* text, const int64_t* begin, const int64_t* end, const float* embeddings,
                                         int32_t n, int32_t dim, int32_t first, int32_t threads, char* out, int64_t out_cap);
 
+/* The items of n sentences formatted ON THE GPU, from embeddings still in device memory (e.g. the output of
+ * b200_embed_forward_device): byte for byte what b200_json_sentence_items_ranges writes, so only the finished text (about
+ * 4.5 KB per 384-d sentence) crosses PCIe and no host core formats a float. The sentence texts are escaped on the host
+ * (a few hundred bytes per sentence). `out` is a host buffer (pinned memory makes the copy faster); the call returns the
+ * size of the items and writes them when out_cap suffices - call with out = NULL to size it. One handle per GPU; calls on
+ * one handle are serialised. CUDA only: without a device use the host entry above. Errors: b200_jsongpu_last_error(). */
+typedef struct b200_jsongpu b200_jsongpu;
+const char* b200_jsongpu_last_error(void);
+int32_t b200_jsongpu_create(int32_t device, b200_jsongpu** out);
+void b200_jsongpu_destroy(b200_jsongpu* g);
+int64_t b200_jsongpu_sentence_items(b200_jsongpu* g, const char* text, const int64_t* begin, const int64_t* end,
+                                    const float* device_embeddings, int32_t n, int32_t dim, int32_t first, char* out,
+                                    int64_t out_cap);
+/* The same for embeddings that are already back on the host (they are uploaded first, 4 bytes per value against the ~12 of
+ * their text): for callers of the host-buffer entry points that want the formatting off their cores. */
+int64_t b200_jsongpu_sentence_items_host(b200_jsongpu* g, const char* text, const int64_t* begin, const int64_t* end,
+                                         const float* host_embeddings, int32_t n, int32_t dim, int32_t first, char* out,
+                                         int64_t out_cap);
+
 /* -- ingest front-end: raw text -> sentences -> token arrays (host only, no GPU involved) ------------------
  * What runs on the host before the embedding call. Errors of these entries are reported through
  * b200_ingest_last_error() (calling thread), with the same B200_EMBED_ERR_* codes. */

@@ -69,6 +69,7 @@ def main():
     ap.add_argument("--operands", default="bf16")
     ap.add_argument("--json", action="store_true", help="format the TextWithEmbeddingsMessage payload of every shard as well")
     ap.add_argument("--json-threads", type=int, default=4)
+    ap.add_argument("--json-gpu", action="store_true", help="with --json: format on the GPUs (b200_jsongpu_*, one handle per GPU) instead of host threads")
     ap.add_argument("--check", type=int, default=0, help="compare the first N sentences with a direct single-GPU call, in order")
     ap.add_argument("--start-shard", type=int, default=0)
     ap.add_argument("--progress", default="")
@@ -119,7 +120,13 @@ def main():
         corpus.stats(reset=True)
 
     # ---- the timed ingest --------------------------------------------------------------------------------------------------
-    outs = [np.empty((args.shard, H), np.float32) for _ in range(inflight)]
+    outs = [(pkg.abi.host_alloc if args.json_gpu else np.empty)((args.shard, H), np.float32) for _ in range(inflight)]
+    if args.json_gpu:
+        import queue
+        args.json_threads = ngpu
+        jg_free = queue.Queue()
+        for g in range(ngpu):  # (formatter of GPU g, its pinned text buffer)
+            jg_free.put((pkg.abi.JsonGpu(g), pkg.abi.host_alloc((args.shard * (H * 17 + 48) + int(raw_bytes) * 6 + 4096,), np.uint8)))
     pre_split = [pkg.abi.split_sentences(b[0]) for b in base] if args.no_split else None
     json_pool = ThreadPoolExecutor(max_workers=args.json_threads) if args.json else None
     json_bytes, json_busy, lock = [0], [0.0], threading.Lock()
@@ -132,8 +139,15 @@ def main():
 
     def format_json(slot, cleaned, begin, end, n, shard):
         t = time.perf_counter()
-        doc = pkg.abi.json_text_with_embeddings(f"doc-{shard}", "http://corpus/synthetic", (cleaned, begin, end), outs[slot][:n],
-                                                "all-MiniLM-L6-v2", 1700000000000 + shard, threads=1, as_array=True)
+        if args.json_gpu:  # the items on a GPU; the envelope (a few hundred bytes) is the host's
+            jg, buf = jg_free.get()
+            try:
+                doc = jg.sentence_items_host(cleaned, begin, end, outs[slot][:n], out=buf)
+            finally:
+                jg_free.put((jg, buf))
+        else:
+            doc = pkg.abi.json_text_with_embeddings(f"doc-{shard}", "http://corpus/synthetic", (cleaned, begin, end), outs[slot][:n],
+                                                    "all-MiniLM-L6-v2", 1700000000000 + shard, threads=1, as_array=True)
         with lock:
             json_bytes[0] += len(doc)
             json_busy[0] += time.perf_counter() - t
@@ -219,7 +233,8 @@ def main():
         "split_threads": args.split_threads,
     })
     if args.json:
-        result["json"] = {"bytes": json_bytes[0], "busy_s_sum_over_threads": round(json_busy[0], 3), "threads": args.json_threads}
+        result["json"] = {"bytes": json_bytes[0], "busy_s_sum_over_threads": round(json_busy[0], 3), "threads": args.json_threads,
+                          "where": "GPUs (b200_jsongpu_sentence_items_host, one formatter per GPU)" if args.json_gpu else "host threads"}
     print(json.dumps(result), flush=True)
 
 

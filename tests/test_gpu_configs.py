@@ -168,3 +168,39 @@ def test_two_devices_in_one_process(pkg, built):
         rb2 = b.forward(ids[:8], mask[:8], tt[:8])  # unfused schedule on device 1
         ra2 = a.forward(ids[:8], mask[:8], tt[:8])
     assert np.array_equal(ra, rb) and np.array_equal(ra2, rb2)
+
+
+def test_embedding_generator_with_the_deployed_models_tokenizer_kind(pkg, built, tmp_path):
+    """The host mirror of EmbeddingGenerator on a model directory of the deployed model's KIND (main.rs:305): an XLM-R style
+    Unigram tokenizer.json (tests/golden/xlmr_like_tokenizer.json), 514 positions, one token type, eps 1e-5. The native
+    front-end takes the tokenizer (no fallback to the `tokenizers` library), ids equal the library's, vectors match the
+    oracle on those ids."""
+    import json
+    import shutil
+    from tokenizers import Tokenizer
+    from conftest import GOLDEN
+    import os
+    shape = pkg.weights.BertShape(6001, 128, 2, 4, 512, 514, 1, pkg.weights.ACT_GELU_ERF, 1e-5)
+    shutil.copy(os.path.join(GOLDEN, "xlmr_like_tokenizer.json"), tmp_path / "tokenizer.json")
+    cfg = dict(vocab_size=shape.vocab_size, hidden_size=shape.hidden_size, num_hidden_layers=shape.num_hidden_layers,
+               num_attention_heads=shape.num_attention_heads, intermediate_size=shape.intermediate_size, hidden_act="gelu",
+               max_position_embeddings=514, type_vocab_size=1, layer_norm_eps=1e-5, model_type="xlm-roberta")
+    json.dump(cfg, open(tmp_path / "config.json", "w"))
+    w = pkg.weights.init_weights(shape, 9)
+    pkg.weights.save_safetensors(str(tmp_path / "model.safetensors"), w)
+    sents = ["The quick brown fox jumps over the lazy dog.", "Naïve café déjà vu ｆｕｌｌ width",
+             "Привет мир!", "日本語のテキスト", "word " * 700, "a"]
+    gen = pkg.EmbeddingGenerator.new(str(tmp_path))
+    try:
+        assert gen.ingest is not None and gen.tokenizer is None
+        out = np.array(gen.generate_sentence_embeddings(sents), np.float32)
+        lib = Tokenizer.from_file(str(tmp_path / "tokenizer.json"))
+        from codename_symbiont_b200.embedding_generator import configure_tokenizer, tokenize_fixed
+        configure_tokenizer(lib, 514)
+        ids, mask, tt = tokenize_fixed(lib, sents, 514)
+        got_ids, got_mask, _, _ = gen.ingest.encode(sents, 514)
+        assert np.array_equal(ids, got_ids) and np.array_equal(mask, got_mask) and mask[4].sum() == 514
+        want = Oracle(shape, w, "f32").generate(ids, tt, mask, chunk=8)
+        gate(out, want, "f16")
+    finally:
+        gen.close()
