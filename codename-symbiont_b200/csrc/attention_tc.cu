@@ -9,11 +9,11 @@
 //   warp 0     TMA producer: Q tile once per item, K and V tiles per 128-key block (2-stage rings), straight from
 //              the packed qkv [tokens, 3H] activations (box D x 128 rows; D*2-byte swizzle)
 //   warp 1     one thread issues tcgen05.mma: S_u = Q.K_u^T (128 x 64, fp32 in TMEM, double-buffered) one unit
-//              ahead of the softmax, then O_u = P_u.V_u (128 x D, double-buffered) as soon as P_u is in smem
-//   warp 2     TMEM allocator (256 columns: 2 x 64 S + 2 x D O)
+//              ahead of the softmax, then O_u = P_u.V_u (128 x D, double-buffered) as soon as P_u is written
+//   warp 2     TMEM allocator (2 x 64 S + 2 x D O + 2 x 32 P columns: 256 for d = 32, 512 for d = 64)
 //   warps 4-7  softmax: thread r owns query row r (= TMEM lane r). One tcgen05.ld brings the unit's 64 scores
 //              into registers (read once: row max, p = exp2(s*scale - max) and the row sum all work from there),
-//              P goes as bf16 into a 128B-swizzled K-major smem tile (the A operand of the second MMA), and the
+//              P goes as 16-bit pairs into tensor memory (the A operand of the second MMA is read there), and the
 //              previous unit's O_u is folded into the running output while this unit's P.V runs. Running max /
 //              sum / output live in registers (online softmax, fp32).
 // Keys past the sentence end get p = 0, which is exactly what the reference's additive f32::MIN mask yields.
@@ -53,11 +53,9 @@ struct AttnDev {
 template <int D>
 struct AttnSmem {
     static constexpr int TILE = BLK * D * 2;         // one Q / K / V tile
-    static constexpr int P_UNIT = BLK * UNIT * 2;     // one K-major 128 x 64 bf16 tile (16 KB)
     static constexpr int OFF_Q = 0;                   // 2 stages
     static constexpr int OFF_KV = 2 * TILE;           // 2 stages x (K, V)
-    static constexpr int OFF_P = OFF_KV + 4 * TILE;   // 2 units
-    static constexpr int OFF_AUX = OFF_P + 2 * P_UNIT;
+    static constexpr int OFF_AUX = OFF_KV + 4 * TILE;
     static constexpr int BYTES = OFF_AUX + 256;
 };
 
@@ -66,13 +64,16 @@ __global__ void __launch_bounds__(ATT_THREADS, D == 32 ? 2 : 1)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev p) {
     using L = AttnSmem<D>;
     constexpr int TILE = L::TILE;
-    constexpr uint32_t TMEM_COLS = 256;
-    constexpr int O_COL = 2 * UNIT;  // O buffers start after the two S buffers
+    // tensor memory: 2 x 64 S | 2 x D O | 2 x 32 P. The probabilities are written there as 16-bit pairs (one 32-bit column per
+    // two keys) and the P.V MMA reads its A operand from tensor memory: P never goes through shared memory, whose operand
+    // fetch (128 B per clock) paces these small MMAs.
+    constexpr int O_COL = 2 * UNIT, P_COL = O_COL + 2 * D;
+    constexpr uint32_t TMEM_COLS = P_COL + UNIT <= 256 ? 256 : 512;
 
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     const uint32_t base = smem_u32(smem_raw);
     if ((base & 1023u) != 0) __trap();
-    const uint32_t smem_q = base + L::OFF_Q, smem_kv = base + L::OFF_KV, smem_p = base + L::OFF_P;
+    const uint32_t smem_q = base + L::OFF_Q, smem_kv = base + L::OFF_KV;
     const uint32_t aux = base + L::OFF_AUX;
     const uint32_t bar_q_full = aux, bar_q_empty = aux + 16, bar_kv_full = aux + 32, bar_kv_empty = aux + 48;
     const uint32_t bar_s_full = aux + 64, bar_s_empty = aux + 80, bar_p_full = aux + 96, bar_o_full = aux + 112,
@@ -177,7 +178,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
         constexpr uint32_t idesc_s = umma_idesc_op(BLK, UNIT);
         constexpr uint32_t idesc_o = umma_idesc_op(BLK, D) | (1u << 16);  // B (= V) is MN-major
         const uint64_t dq0 = umma_desc_k<D>(smem_q), dk0 = umma_desc_k<D>(smem_kv);
-        const uint64_t dp0 = umma_desc_sw128(smem_p), dv0 = umma_desc_mn<D>(smem_kv + TILE);
+        const uint64_t dv0 = umma_desc_mn<D>(smem_kv + TILE);
         struct Cursor {
             Walk w;
             bool valid;        // points at a unit
@@ -219,15 +220,15 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
         };
         auto issue_pv = [&](const Cursor& c) {
             const uint32_t kvi = c.kv_it + (c.u >> 1), s = kvi & 1, ob = uo & 1;
-            mbar_wait(bar_p_full + 8 * ob, (uo >> 1) & 1);         // P_u is in shared memory
+            mbar_wait(bar_p_full + 8 * ob, (uo >> 1) & 1);         // P_u is in tensor memory
             mbar_wait(bar_o_empty + 8 * ob, ((uo >> 1) & 1) ^ 1);  // the O buffer has been read
             tc_fence_after_sync();
             if (elect_one()) {
-                const uint64_t dp = dp0 + ((ob * L::P_UNIT) >> 4);
+                const uint32_t tp = tmem_base + P_COL + ob * (UNIT / 2);
                 const uint64_t dv = dv0 + ((s * 2 * TILE + (c.u & 1) * (UNIT * D * 2)) >> 4);
 #pragma unroll
-                for (int k = 0; k < UNIT / 16; ++k)  // P: 32 B per 16 keys; V: 16 rows of D*2 B
-                    umma_bf16(tmem_base + O_COL + ob * D, dp + 2 * k, dv + ((k * 16 * D * 2) >> 4), idesc_o, k > 0 ? 1u : 0u);
+                for (int k = 0; k < UNIT / 16; ++k)  // P: 8 columns per 16 keys; V: 16 rows of D*2 B
+                    umma_ts(tmem_base + O_COL + ob * D, tp + 8 * k, dv + ((k * 16 * D * 2) >> 4), idesc_o, k > 0 ? 1u : 0u);
                 umma_commit(bar_o_full + 8 * ob);
                 if ((c.u & 1) == 1 || c.u == c.nunits - 1) umma_commit(bar_kv_empty + 8 * s);  // block fully consumed
             }
@@ -331,21 +332,19 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
                 // four packed chains
                 const uint64_t sc2 = pk2(p.scale_log2, p.scale_log2), nm2 = pk2(-m_new, -m_new);
                 uint64_t lb2[4] = {0, 0, 0, 0};
-                const uint32_t prow = smem_p + sb * L::P_UNIT + row * 128;
+                uint32_t pw[UNIT / 2];  // this row's probabilities, two keys per word
 #pragma unroll
                 for (int q = 0; q < UNIT / 8; ++q) {
-                    uint32_t wd[4];
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
                         float a, bb;
                         upk2(fma2(pk2(__uint_as_float(v[q * 8 + 2 * j]), __uint_as_float(v[q * 8 + 2 * j + 1])), sc2, nm2), a, bb);
                         const float pa = ex2(a), pb = ex2(bb);
                         lb2[j] = add2(lb2[j], pk2(pa, pb));
-                        wd[j] = pack_op2(pa, pb);
+                        pw[q * 4 + j] = pack_op2(pa, pb);
                     }
-                    const uint32_t piece = static_cast<uint32_t>(q) ^ (row & 7);
-                    sts_v4(prow + (piece << 4), wd[0], wd[1], wd[2], wd[3]);
                 }
+                tmem_st_32x32(t_lane + P_COL + sb * (UNIT / 2), pw);
                 float lb;
                 {
                     float a0, a1, a2, a3;
@@ -353,7 +352,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
                     upk2(add2(lb2[2], lb2[3]), a2, a3);
                     lb = (a0 + a1) + (a2 + a3);
                 }
-                fence_proxy_async_smem();
+                tmem_st_wait();
+                tc_fence_before_sync();
                 mbar_arrive(bar_p_full + 8 * sb);
                 l = fmaf(l, corr, lb);
                 // while P_u . V_u runs, fold the previous unit of the stream in (and finalise its item if it ended there)
