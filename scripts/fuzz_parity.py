@@ -1,6 +1,6 @@
 """GPU: randomised end-to-end parity sweep. Every trial draws a batch (size, padded length, length distribution), runs it
 through (a) the fused schedule forced on (K23 + K2f), (b) the unfused schedule, (c) whatever the engine picks by itself,
-and - for small trials - the f32 C oracle; reports the worst differences. Usage: python scripts/fuzz_parity.py [trials] [seed]"""
+and - for small trials - the f32 C oracle; reports the worst differences. Usage: python scripts/fuzz_parity.py [trials] [seed] [f16|bf16]"""
 import importlib, os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
@@ -10,6 +10,7 @@ from oracle.oracle import Oracle
 
 trials = int(sys.argv[1]) if len(sys.argv) > 1 else 150
 seed = int(sys.argv[2]) if len(sys.argv) > 2 else 0
+operands = sys.argv[3] if len(sys.argv) > 3 else "f16"
 shape = pkg.weights.MINILM_L6
 rng = np.random.default_rng(seed)
 
@@ -17,7 +18,7 @@ def make(env):
     old = {k: os.environ.get(k) for k in env}
     os.environ.update(env)
     try:
-        return pkg.Embedder.random_init(shape, seed=77)
+        return pkg.Embedder.random_init(shape, seed=77, operands=operands)
     finally:
         for k, v in old.items():
             os.environ.pop(k, None) if v is None else os.environ.__setitem__(k, v)
@@ -53,5 +54,5 @@ for t in range(trials):
         want = oracle.generate(ids, tt, mask, chunk=8)
         for x in (a, b):
             worst["orc"] = max(worst["orc"], float(np.abs(x - want).max())); worst["orc_cos"] = min(worst["orc_cos"], float(cos(x, want).min()))
-print(f"{trials} trials in {time.time() - t0:.0f}s: max |fused - unfused| {worst['fp']:.2e}, auto equals one of them within {worst['fa']:.1e}, "
+print(f"operands {operands}: {trials} trials in {time.time() - t0:.0f}s: max |fused - unfused| {worst['fp']:.2e}, auto equals one of them within {worst['fa']:.1e}, "
       f"min cosine between schedules {worst['cos']:.7f}; vs f32 oracle: max abs {worst['orc']:.2e}, min cosine {worst['orc_cos']:.7f}")
