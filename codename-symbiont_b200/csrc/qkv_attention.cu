@@ -29,6 +29,9 @@
 //               maximum and the exponentials of the next unit.
 #include <cuda.h>
 #include <cudaTypedefs.h>
+#ifdef QA_TIMELINE
+#include <cstdio>
+#endif
 
 #include "common.cuh"
 #include "kernels.h"
@@ -54,7 +57,9 @@ struct QaCfg {
     static constexpr int NQ = 3 * D;                 // accumulator columns per head: q | k | v
     static constexpr int W_SUB = D * BK * 2;         // one [D x 64] box of Wqkv rows
     static constexpr int W_BLK = 3 * W_SUB;          // [3D x 64]: one K-major B operand block
-    static constexpr int WS = KB % 3 == 0 ? 3 : 2;   // W ring slots (KB % WS == 0: slots are compile-time in the k loop)
+    // W ring slots (KB % WS == 0: slots are compile-time in the k loop). A ring holding the whole head (6 slots at H = 384)
+    // was measured slower: 0.703 vs 0.644 ms per launch at c2
+    static constexpr int WS = KB % 3 == 0 ? 3 : 2;
     static constexpr int T_TILE = BLK * D * 2;       // one Q / K / V tile
     static constexpr int OFF_X = 0;
     static constexpr int OFF_W = KB * X_BLK;
@@ -85,6 +90,18 @@ struct QaDev {
     __nv_bfloat16* ctx;
 };
 
+// -DQA_TIMELINE: cycles per phase of one thread per role (block 0), printed at kernel end - a measuring build only
+#ifdef QA_TIMELINE
+#define TL_DECL uint32_t tl[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}; uint32_t tl_last = static_cast<uint32_t>(clock())
+#define TL(i) do { const uint32_t now_ = static_cast<uint32_t>(clock()); tl[i] += now_ - tl_last; tl_last = now_; } while (0)
+#define TL_PRINT(name) do { if (blockIdx.x == 0 && lane == 0) printf("TL %s w%d: %u %u %u %u %u %u %u %u %u %u %u %u\n", name, warp, \
+    tl[0], tl[1], tl[2], tl[3], tl[4], tl[5], tl[6], tl[7], tl[8], tl[9], tl[10], tl[11]); } while (0)
+#else
+#define TL_DECL
+#define TL(i)
+#define TL_PRINT(name)
+#endif
+
 template <int H, int D>
 __global__ void __launch_bounds__(QA_THREADS, 1)
 qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w, const QaDev p) {
@@ -98,7 +115,7 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
     const uint32_t smem_x = base + C::OFF_X, smem_w = base + C::OFF_W, smem_t = base + C::OFF_T;
     const uint32_t aux = base + C::OFF_AUX;
     const uint32_t bar_x_full = aux, bar_x_empty = aux + 8;
-    const uint32_t bar_w_full = aux + 16, bar_w_empty = aux + 48;        // WS each
+    const uint32_t bar_w_full = aux + 272, bar_w_empty = aux + 336;      // WS (<= 8) each
     // two of each from here on, index = ACC buffer / group
     const uint32_t bar_acc_full = aux + 80, bar_acc_empty = aux + 96;
     const uint32_t bar_t_full = aux + 112, bar_t_empty = aux + 128;      // Q / K / V tiles of the group's head
@@ -212,19 +229,25 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
         const uint64_t dx0 = umma_desc_sw128(smem_x), dw0 = umma_desc_sw128(smem_w);
         Walk wp = walk_init();
         uint32_t pit = 0, gg = 0, wb = 0;  // tiles entered, heads projected, W blocks consumed
+        TL_DECL;
         while (wp.b < n_items) {
             int a, b;
             if (!take(wp, a, b)) continue;
+            TL(0);
             mbar_wait(bar_x_full, pit & 1);
+            TL(1);
             ++pit;
             for (int ph = 0; ph < HEADS; ++ph, ++gg) {
                 const uint32_t ab = gg & 1;
                 mbar_wait(bar_acc_empty + 8 * ab, ((gg >> 1) & 1) ^ 1);  // the group has drained this accumulator
+                TL(2);
                 tc_fence_after_sync();
 #pragma unroll
                 for (int kb = 0; kb < KB; ++kb, ++wb) {
                     const uint32_t sl = kb % WS;
+                    TL(0);
                     mbar_wait(bar_w_full + 8 * sl, (wb / WS) & 1);
+                    TL(3);
                     tc_fence_after_sync();
                     if (elect_one()) {
                         const uint64_t da = dx0 + ((kb * X_BLK) >> 4), db = dw0 + ((sl * W_BLK) >> 4);
@@ -242,6 +265,8 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                 }
             }
         }
+        TL(0);
+        TL_PRINT("proj: issue x_full acc_empty w_full");
     } else if (warp == 2 || warp == 3) {
         // ------------------------------ MMA issuers 2, 3 of 3: one per group ------------------------------
         // Per head of the group: S = Q . K_u^T (128 x 64 x d) and O_u = P_u . V_u (128 x d x 64) per unit u of 64 keys,
@@ -253,9 +278,13 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
         const uint64_t dv0 = umma_desc_mn<D>(smem_t + 2 * T_TILE);
         uint32_t hc = 0;          // heads of this group completed
         uint32_t us = 0, uo = 0;  // S / P.V units issued
+        TL_DECL;
         auto issue_s = [&](int u, bool first) {
+            TL(0);
             if (first) mbar_wait(bar_t_full + 8 * G, hc & 1);       // this head's Q / K / V are staged
+            TL(1);
             mbar_wait(bar_s_empty + 8 * G, (us & 1) ^ 1);           // the group has read the previous S
+            TL(2);
             tc_fence_after_sync();
             if (elect_one()) {
                 const uint64_t dq = dq0 + ((G * 3 * T_TILE) >> 4);
@@ -270,8 +299,11 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
         };
         auto issue_pv = [&](int u, bool last) {
             const uint32_t ob = uo & 1;
+            TL(0);
             mbar_wait(bar_p_full + 8 * G, uo & 1);                                  // P_u is in tensor memory
+            TL(3);
             mbar_wait(bar_o_empty + 8 * (2 * G + ob), ((uo >> 1) & 1) ^ 1);         // the O buffer has been read
+            TL(4);
             tc_fence_after_sync();
             if (elect_one()) {
                 const uint32_t tp = tmem_base + C::P_COL + G * (UNIT / 2);
@@ -298,6 +330,8 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                 if (nunits > 1) issue_pv(1, true);
             }
         }
+        TL(0);
+        TL_PRINT("grp issuer: issue t_full s_empty p_full o_empty");
     } else if (warp >= QA_GROUP_WARP0) {
         // ------------------------------ groups: convert + softmax of alternate heads ------------------------------
         const int G = (warp - QA_GROUP_WARP0) >> 2;
@@ -318,9 +352,12 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
             float corr, l;
             int start, len, h;
         } pend{false, false, 0, 0.f, 0.f, 0, 0, 0};
+        TL_DECL;
         auto retire_pending = [&]() {
             const uint32_t ob = pend.ur & 1;
+            TL(7);
             mbar_wait(bar_o_full + 8 * (2 * G + ob), (pend.ur >> 1) & 1);
+            TL(8);
             tc_fence_after_sync();
             {
                 uint32_t v[32];
@@ -345,6 +382,7 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                 }
             }
             pend.valid = false;
+            TL(9);
         };
         Walk w = walk_init();
         while (w.b < n_items) {
@@ -364,7 +402,9 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
             }
             for (int h = G; h < HEADS; h += 2, ++hc) {
                 // ---- convert: ACC[G] + bias -> Q / K / V tiles ----
+                TL(11);
                 mbar_wait(bar_acc_full + 8 * G, hc & 1);
+                TL(0);
                 tc_fence_after_sync();
                 {
                     uint32_t words[3][16];
@@ -383,18 +423,23 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                     }
                     tc_fence_before_sync();
                     mbar_arrive(bar_acc_empty + 8 * G);  // the accumulator is in registers
+                    TL(1);
                     mbar_wait(bar_t_empty + 8 * G, (hc & 1) ^ 1);  // the group's previous head has finished with the tiles
+                    TL(2);
 #pragma unroll
                     for (int j = 0; j < 3; ++j) stage_words_bf16(tile + j * T_TILE, row, words[j]);
                     fence_proxy_async_smem();
                     mbar_arrive(bar_t_full + 8 * G);
+                    TL(3);
                 }
                 // ---- softmax ----
                 float m = -INFINITY, l = 0.f;  // the first unit's corr is exp2(-inf) = 0: the previous head's output vanishes
                 for (int u = 0; u < nunits; ++u, ++ug) {
                     // this unit's keys u*64 + j, j in [jlo, jhi), belong to the row's sentence
                     const int jlo = min(max(klo - u * UNIT, 0), UNIT), jhi = min(max(khi - u * UNIT, 0), UNIT);
+                    TL(11);
                     mbar_wait(bar_s_full + 8 * G, ug & 1);
+                    TL(4);
                     tc_fence_after_sync();
                     uint32_t v[UNIT];
                     tmem_ld_32x32(t_lane + C::S_COL + G * UNIT, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
@@ -402,6 +447,7 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                     tmem_ld_wait();
                     tc_fence_before_sync();
                     mbar_arrive(bar_s_empty + 8 * G);  // S is in registers: the MMA warp may overwrite the buffer
+                    TL(5);
                     if (jlo > 0 || jhi < UNIT) {  // keys of other sentences / past the end -> -inf (exp2 then gives exactly 0)
                         const uint32_t span = static_cast<uint32_t>(jhi - jlo);
 #pragma unroll
@@ -418,6 +464,7 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                     const float m_use = m_new == -INFINITY ? 0.f : m_new;
                     const float corr = ex2(m - m_use);
                     m = m_new;
+                    TL(6);
                     if (pend.valid) retire_pending();  // also: the previous P.V is done, the P buffer is free
                     const uint64_t sc2 = pk2(p.scale_log2, p.scale_log2), nm2 = pk2(-m_use, -m_use);
                     uint64_t lb2[4] = {0, 0, 0, 0};
@@ -444,6 +491,7 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                     tmem_st_wait();
                     tc_fence_before_sync();
                     mbar_arrive(bar_p_full + 8 * G);
+                    TL(10);
                     l = fmaf(l, corr, lb);
                     pend.valid = true; pend.last = u == nunits - 1; pend.ur = ug; pend.corr = corr; pend.l = l;
                     pend.start = start; pend.len = len; pend.h = h;
@@ -451,6 +499,8 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
             }
         }
         if (pend.valid) retire_pending();
+        TL(11);
+        TL_PRINT("softmax: acc_full cvt t_empty stage s_full ldS max [7] o_full retire exp+stP other");
     }
 
     tc_fence_before_sync();
