@@ -11,22 +11,26 @@
 // Work item = a TILE of up to 128 token rows holding whole sentences (one sentence of 65..128 tokens, or several short
 // ones packed by pack_tiles_kernel; attention is then block-diagonal: every row only sees the keys of its own
 // sentence). A persistent CTA (one per SM) keeps the tile's activations x[128, H] resident in shared memory (rows past
-// the tile's tokens belong to the next tile or are zero-filled: they are computed and never used) and walks its heads. Two GROUPS of four warps take alternate heads (even / odd; the head count is even)
-// and each does everything the head needs outside the tensor pipe:
+// the tile's tokens belong to the next tile or are zero-filled: they are computed and never used) and walks its heads.
+// Five warpgroups (640 threads; setmaxnreg moves registers from the control and output warps to the softmax groups):
 //   warp 0      TMA producer: the x tile once per sentence; per head KB blocks of Wqkv rows {h*d.., H + h*d.., 2H + h*d..}
 //               x 64 columns (three 4 KB boxes = one 96-row K-major B operand) through a small ring
-//   warp 1      MMA issuer of the projections  ACC[g & 1] = x . Wqkv_h^T  (128 x 96 x H per head g, up to two heads ahead;
+//   warp 1      MMA issuer of the projections  ACC[h & 1] = x . Wqkv_h^T  (128 x 96 x H per head h, up to two heads ahead;
 //               the whole warp walks the loop, one elected lane issues)
 //   warps 2, 3  MMA issuers of group 0 / 1: S = Q . K_u^T (128 x 64 x d) and O_u = P_u . V_u (128 x d x 64) per unit u of
 //               64 keys. Three issuers, each blocking on its own dependencies only: one issuer with a fixed schedule kept the
 //               groups in lockstep (softmax warps spent 27 % of their samples waiting for S / O / ACC, profiles/r02a).
-//               Warp 2 is also the TMEM allocator (512 columns: 2 x 128 ACC, 2 x 64 S, 2 x 2 x 32 O)
-//   warps 4-7 / 8-11  group 0 / 1, thread = token row = TMEM lane. Per head: convert ACC + bias -> bf16 Q / K / V tiles
-//               in shared memory, in the layouts K3 gets from TMA (64-byte rows, SWIZZLE_64B; V consumed MN-major as
-//               stored); then per unit the softmax of attention_tc.cu (unit read once into registers, P as 16-bit pairs into
-//               tensor memory - the P.V MMA reads its A operand there -, online softmax, ctx rows stored as whole 32-byte sectors). A group has one
-//               S and one P buffer: the previous unit's P.V is retired (which also proves P free) between the row
-//               maximum and the exponentials of the next unit.
+//               Warp 2 is also the TMEM allocator (512 columns: 2 x 96 ACC, 2 x 64 S, 2 x 2 x 32 O, 2 x 32 P)
+//   warps 4-7 / 8-11  softmax group 0 / 1 (even / odd heads), thread = token row = TMEM lane. Per unit the softmax of
+//               attention_tc.cu: S read once into registers, P written as 16-bit pairs into tensor memory (the P.V MMA reads its
+//               A operand there). Nothing else: a unit's P.V goes to its own O buffer, and the head's rescaling factor and
+//               row sum are handed to the output warps through shared memory
+//   warps 12-15 convert: ACC + bias -> 16-bit Q / K / V tiles of the head's group in shared memory, in the layouts K3
+//               gets from TMA (64-byte rows, SWIZZLE_64B; V consumed MN-major as stored), head after head
+//   warps 16-19 output: ctx rows = (O_0 * corr + O_1) / l of finished heads, stored as whole 32-byte sectors
+// With convert and output inside the softmax warps (12 warps, 168 registers) a head took a group 7.5 k cycles of which 1.8 k
+// were these two; as separate warps under a 128-register launch bound they spilled (0.91 ms) - setmaxnreg is what makes
+// the split pay: 13.83 vs 14.14 ms per c2 step in a same-box A/B.
 #include <cuda.h>
 #include <cudaTypedefs.h>
 #ifdef QA_TIMELINE
@@ -42,13 +46,29 @@ B200_NS_THIS {
 
 namespace {
 
-constexpr int QA_THREADS = 384;
+constexpr int QA_THREADS = 640;    // five warpgroups: control, softmax 0, softmax 1, convert, output
 constexpr int QA_GROUP_WARP0 = 4;  // group 0: warps 4-7, group 1: warps 8-11
+constexpr int QA_CONVERT_WARP0 = 12, QA_OUTPUT_WARP0 = 16;
 constexpr int QA_GROUP = 128;      // threads per group
+// registers per thread after the roles have split (setmaxnreg; 640 threads start at 96, the sum over the five warpgroups
+// must stay <= 5 * 96)
+constexpr int QA_REGS_CONTROL = 80, QA_REGS_SOFTMAX = 112, QA_REGS_CONVERT = 104, QA_REGS_OUTPUT = 72;
+static_assert(QA_REGS_CONTROL + 2 * QA_REGS_SOFTMAX + QA_REGS_CONVERT + QA_REGS_OUTPUT <= 5 * 96, "register budget");
 constexpr int BLK = 128;           // token rows per item
 constexpr int UNIT = 64;           // keys per softmax unit
 constexpr int BK = 64;             // bf16 per 128-byte swizzle row
 constexpr int X_BLK = BLK * BK * 2;
+
+// Two measured options, both off (same-box A/B at c2, kernel alone: 0.626 ms as shipped): QA_VBUFS = 2 stages a head's V
+// into a second tile so that the next head's Q / K / V are ready before the current head's last P.V has finished, and
+// QA_LOOKAHEAD = 1 then issues the next head's first S ahead of that P.V (0.636 / 0.672 ms: the tensor pipe executes in
+// issue order and the chain a group waits on is not shortened by queueing more behind the projections).
+#ifndef QA_LOOKAHEAD
+#define QA_LOOKAHEAD 0
+#endif
+#ifndef QA_VBUFS
+#define QA_VBUFS 1
+#endif
 
 template <int H, int D>
 struct QaCfg {
@@ -63,10 +83,12 @@ struct QaCfg {
     static constexpr int T_TILE = BLK * D * 2;       // one Q / K / V tile
     static constexpr int OFF_X = 0;
     static constexpr int OFF_W = KB * X_BLK;
-    static constexpr int OFF_T = OFF_W + WS * W_BLK;   // per group: Q, K, V
-    static constexpr int OFF_AUX = OFF_T + 2 * 3 * T_TILE;
+    static constexpr int OFF_T = OFF_W + WS * W_BLK;   // per group: Q, K, V of even heads, V of odd heads (of the group's heads)
+    static constexpr int G_TILES = 2 + QA_VBUFS;
+    static constexpr int OFF_AUX = OFF_T + 2 * G_TILES * T_TILE;
     static constexpr int OFF_BIAS = OFF_AUX + 512;     // bqkv [3H] fp32
-    static constexpr int BYTES = OFF_BIAS + 3 * H * 4;
+    static constexpr int OFF_ROWS = OFF_BIAS + 3 * H * 4;  // per group: corr[128], l[128] of the head being finished
+    static constexpr int BYTES = OFF_ROWS + 2 * 2 * BLK * 4;
     // tensor memory: ACC[2] (q | k | v of the head being projected), per group S (one unit of 64 keys), O (two units), and P:
     // the probabilities as 16-bit pairs, one 32-bit column per two keys, which the P.V MMA reads straight from tensor
     // memory (A operand in TMEM) - they never go through shared memory
@@ -115,12 +137,16 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
     const uint32_t smem_x = base + C::OFF_X, smem_w = base + C::OFF_W, smem_t = base + C::OFF_T;
     const uint32_t aux = base + C::OFF_AUX;
     const uint32_t bar_x_full = aux, bar_x_empty = aux + 8;
-    const uint32_t bar_w_full = aux + 272, bar_w_empty = aux + 336;      // WS (<= 8) each
+    const uint32_t bar_w_full = aux + 16, bar_w_empty = aux + 48;        // WS each
     // two of each from here on, index = ACC buffer / group
     const uint32_t bar_acc_full = aux + 80, bar_acc_empty = aux + 96;
-    const uint32_t bar_t_full = aux + 112, bar_t_empty = aux + 128;      // Q / K / V tiles of the group's head
+    const uint32_t bar_t_full = aux + 112;                               // Q / K / V tiles of the group's head are staged
+    const uint32_t bar_qk_empty = aux + 128;                             // [group]: the head's last S has read Q and K
+    const uint32_t bar_v_empty = aux + 272;                              // [group][head & 1]: the head's last P.V has read V
     const uint32_t bar_s_full = aux + 144, bar_s_empty = aux + 160, bar_p_full = aux + 176;
-    const uint32_t bar_o_full = aux + 192, bar_o_empty = aux + 224;      // [group][unit & 1]
+    const uint32_t bar_o_full = aux + 192;                               // [group][unit]: P.V of that unit has completed
+    const uint32_t bar_o_empty = aux + 224;                              // [group]: the output warps have read the head's O
+    const uint32_t bar_c_full = aux + 240;                               // [group]: the head's corr / l are in shared memory
     const uint32_t tmem_slot = aux + 256;
     volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + C::OFF_AUX + 256);
 
@@ -136,15 +162,14 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
             mbar_init(bar_acc_full + 8 * s, 1);
             mbar_init(bar_acc_empty + 8 * s, QA_GROUP);
             mbar_init(bar_t_full + 8 * s, QA_GROUP);
-            mbar_init(bar_t_empty + 8 * s, 1);
+            mbar_init(bar_qk_empty + 8 * s, 1);
             mbar_init(bar_s_full + 8 * s, 1);
             mbar_init(bar_s_empty + 8 * s, QA_GROUP);
             mbar_init(bar_p_full + 8 * s, QA_GROUP);
-        }
-        for (int s = 0; s < 4; ++s) {
-            mbar_init(bar_o_full + 8 * s, 1);
             mbar_init(bar_o_empty + 8 * s, QA_GROUP);
+            mbar_init(bar_c_full + 8 * s, QA_GROUP);
         }
+        for (int s = 0; s < 4; ++s) { mbar_init(bar_o_full + 8 * s, 1); mbar_init(bar_v_empty + 8 * s, 1); }
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc(tmem_slot, 512);
@@ -155,6 +180,10 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
     __syncthreads();
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot_ptr;
+
+    // The roles split the register file: 640 threads start with 96 registers each; the control warps and the output
+    // warps hand registers to the two softmax groups (a whole warpgroup executes the same setmaxnreg).
+    // (each setmaxnreg sits at the head of its role's branch below: ptxas budgets the code that follows it)
 
     // Work items are TILES: runs of whole sentences that together have at most 128 tokens (built on the device by
     // pack_tiles_kernel; a sentence of 65..128 tokens is a tile of its own, short ones share one). Every role walks the
@@ -190,6 +219,8 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
         return take2(w, start, len, f, l);
     };
 
+    if (warp < QA_GROUP_WARP0) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(QA_REGS_CONTROL));
     if (warp == 0) {
         // ------------------------------ TMA producer ------------------------------
         uint32_t it = 0, wb = 0;  // sentences taken, W blocks loaded (ring slot wb % WS)
@@ -239,7 +270,7 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
             ++pit;
             for (int ph = 0; ph < HEADS; ++ph, ++gg) {
                 const uint32_t ab = gg & 1;
-                mbar_wait(bar_acc_empty + 8 * ab, ((gg >> 1) & 1) ^ 1);  // the group has drained this accumulator
+                mbar_wait(bar_acc_empty + 8 * ab, ((gg >> 1) & 1) ^ 1);  // the convert warps have drained this accumulator
                 TL(2);
                 tc_fence_after_sync();
 #pragma unroll
@@ -267,123 +298,126 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
         }
         TL(0);
         TL_PRINT("proj: issue x_full acc_empty w_full");
-    } else if (warp == 2 || warp == 3) {
+    } else {
         // ------------------------------ MMA issuers 2, 3 of 3: one per group ------------------------------
         // Per head of the group: S = Q . K_u^T (128 x 64 x d) and O_u = P_u . V_u (128 x d x 64) per unit u of 64 keys,
         // in the order S(u0), S(u1), P.V(u0), P.V(u1): S(u1) only needs the softmax warps to have read S(u0).
         const int G = warp - 2;
         constexpr uint32_t idesc_s = umma_idesc_op(BLK, UNIT);
         constexpr uint32_t idesc_o = umma_idesc_op(BLK, D) | (1u << 16);  // B (= V) is MN-major
-        const uint64_t dq0 = umma_desc_k_sw64(smem_t);
-        const uint64_t dv0 = umma_desc_mn<D>(smem_t + 2 * T_TILE);
-        uint32_t hc = 0;          // heads of this group completed
+        const uint64_t dq0 = umma_desc_k_sw64(smem_t + G * C::G_TILES * T_TILE);
+        const uint64_t dv0 = umma_desc_mn<D>(smem_t + G * C::G_TILES * T_TILE + 2 * T_TILE);
+        uint32_t hc = 0;          // heads of this group completed (P.V side)
         uint32_t us = 0, uo = 0;  // S / P.V units issued
         TL_DECL;
-        auto issue_s = [&](int u, bool first) {
+        // S of head number hn (of this group; hn = hc or hc + 1: the first unit of the next head is issued ahead)
+        auto issue_s = [&](int u, bool first, bool last, uint32_t hn) {
             TL(0);
-            if (first) mbar_wait(bar_t_full + 8 * G, hc & 1);       // this head's Q / K / V are staged
+            if (first) mbar_wait(bar_t_full + 8 * G, hn & 1);       // this head's Q / K / V are staged
             TL(1);
             mbar_wait(bar_s_empty + 8 * G, (us & 1) ^ 1);           // the group has read the previous S
             TL(2);
             tc_fence_after_sync();
             if (elect_one()) {
-                const uint64_t dq = dq0 + ((G * 3 * T_TILE) >> 4);
-                const uint64_t dk = dq0 + ((G * 3 * T_TILE + T_TILE + u * (UNIT * D * 2)) >> 4);
+                const uint64_t dk = dq0 + ((T_TILE + u * (UNIT * D * 2)) >> 4);
 #pragma unroll
                 for (int k = 0; k < D / 16; ++k)
-                    umma_bf16(tmem_base + C::S_COL + G * UNIT, dq + 2 * k, dk + 2 * k, idesc_s, k > 0 ? 1u : 0u);
+                    umma_bf16(tmem_base + C::S_COL + G * UNIT, dq0 + 2 * k, dk + 2 * k, idesc_s, k > 0 ? 1u : 0u);
                 umma_commit(bar_s_full + 8 * G);
+                if (last) umma_commit(bar_qk_empty + 8 * G);  // Q and K may be restaged for the next head
             }
             __syncwarp();
             ++us;
         };
         auto issue_pv = [&](int u, bool last) {
-            const uint32_t ob = uo & 1;
             TL(0);
-            mbar_wait(bar_p_full + 8 * G, uo & 1);                                  // P_u is in tensor memory
+            mbar_wait(bar_p_full + 8 * G, uo & 1);                          // P_u is in tensor memory
             TL(3);
-            mbar_wait(bar_o_empty + 8 * (2 * G + ob), ((uo >> 1) & 1) ^ 1);         // the O buffer has been read
+            if (u == 0) mbar_wait(bar_o_empty + 8 * G, (hc & 1) ^ 1);       // the previous head's O has been read
             TL(4);
             tc_fence_after_sync();
             if (elect_one()) {
                 const uint32_t tp = tmem_base + C::P_COL + G * (UNIT / 2);
-                const uint64_t dv = dv0 + ((G * 3 * T_TILE + u * (UNIT * D * 2)) >> 4);
+                const uint64_t dv = dv0 + (((hc % QA_VBUFS) * T_TILE + u * (UNIT * D * 2)) >> 4);
 #pragma unroll
                 for (int k = 0; k < UNIT / 16; ++k)  // P: 8 columns per 16 keys; V: 16 rows of D*2 B
-                    umma_ts(tmem_base + C::O_COL + G * 64 + ob * D, tp + 8 * k, dv + ((k * 16 * D * 2) >> 4), idesc_o,
+                    umma_ts(tmem_base + C::O_COL + G * 64 + u * D, tp + 8 * k, dv + ((k * 16 * D * 2) >> 4), idesc_o,
                             k > 0 ? 1u : 0u);
-                umma_commit(bar_o_full + 8 * (2 * G + ob));
-                if (last) umma_commit(bar_t_empty + 8 * G);  // this head's tiles are consumed
+                umma_commit(bar_o_full + 8 * (2 * G + u));
+                if (last) umma_commit(bar_v_empty + 8 * (2 * G + (hc % QA_VBUFS)));  // this head's V buffer is consumed
             }
             __syncwarp();
             ++uo;
         };
-        Walk w = walk_init();
-        while (w.b < n_items) {
-            int start, len;
-            if (!take(w, start, len)) continue;
-            const int nunits = (len + UNIT - 1) / UNIT;
-            for (int h = G; h < HEADS; h += 2, ++hc) {
-                issue_s(0, true);
-                if (nunits > 1) issue_s(1, false);
-                issue_pv(0, nunits == 1);
-                if (nunits > 1) issue_pv(1, true);
+        // the group's heads over all tiles, one after the other, with the unit count of their tile
+        struct HeadIt { Walk w; int h, nunits; bool valid; };
+        auto next_head = [&](HeadIt& it) {
+            it.h += 2;
+            if (it.h < HEADS) return;
+            it.valid = false;
+            while (it.w.b < n_items) {
+                int start, len;
+                if (!take(it.w, start, len)) continue;
+                it.nunits = (len + UNIT - 1) / UNIT;
+                it.h = G;
+                it.valid = true;
+                return;
             }
+        };
+        HeadIt cur{walk_init(), HEADS, 0, false};
+        next_head(cur);
+        // order per head k: [S(k, u0) was issued during head k - 1], S(k, u1), P.V(k, u0), then S(k + 1, u0) and
+        // P.V(k, last) in the order their inputs arrive: the next head's first scores are computed while the softmax warps
+        // work on this head's last unit, without holding that unit's P.V back when the next head's tiles are late
+        auto ready = [&](uint32_t bar, uint32_t parity) { return __shfl_sync(0xffffffffu, mbar_test(bar, parity) ? 1 : 0, 0) != 0; };
+#if QA_LOOKAHEAD
+        if (cur.valid) issue_s(0, true, cur.nunits == 1, 0);
+#endif
+        while (cur.valid) {
+            HeadIt nxt = cur;
+            next_head(nxt);
+#if !QA_LOOKAHEAD
+            issue_s(0, true, cur.nunits == 1, hc);
+            nxt.valid = false;
+#endif
+            if (cur.nunits > 1) {
+                issue_s(1, false, true, hc);
+                issue_pv(0, false);
+            }
+            bool s_pending = nxt.valid, pv_pending = true;
+            while (s_pending || pv_pending) {
+                if (pv_pending && (!s_pending || ready(bar_p_full + 8 * G, uo & 1))) {
+                    issue_pv(cur.nunits - 1, true);
+                    pv_pending = false;
+                } else if (s_pending && (!pv_pending || (ready(bar_t_full + 8 * G, (hc + 1) & 1) &&
+                                                         ready(bar_s_empty + 8 * G, (us & 1) ^ 1)))) {
+                    issue_s(0, true, nxt.nunits == 1, hc + 1);
+                    s_pending = false;
+                }
+            }
+            ++hc;
+#if !QA_LOOKAHEAD
+            nxt = cur;
+            next_head(nxt);
+#endif
+            cur = nxt;
         }
         TL(0);
         TL_PRINT("grp issuer: issue t_full s_empty p_full o_empty");
-    } else if (warp >= QA_GROUP_WARP0) {
-        // ------------------------------ groups: convert + softmax of alternate heads ------------------------------
+    }
+    } else if (warp < QA_CONVERT_WARP0) {
+        // ------------------------------ softmax groups: alternate heads ------------------------------
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(QA_REGS_SOFTMAX));
         const int G = (warp - QA_GROUP_WARP0) >> 2;
         const int quad = warp & 3;
         const int row = quad * 32 + lane;  // token row inside the item = TMEM lane
         const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
-        const uint32_t tile = smem_t + G * 3 * T_TILE;
-        uint32_t hc = 0;  // heads done by this group
-        uint32_t ug = 0;  // units done by this group (O buffer ug & 1)
-        float o[D];       // running output of the head being retired
-#pragma unroll
-        for (int j = 0; j < D; ++j) o[j] = 0.f;
-        // the group's previous unit: folded in (and its head finalised if it ended there) between the row maximum and
-        // the exponentials of the next unit - its P.V has had that long to finish, and P is free again once it has
-        struct Pending {
-            bool valid, last;
-            uint32_t ur;
-            float corr, l;
-            int start, len, h;
-        } pend{false, false, 0, 0.f, 0.f, 0, 0, 0};
+        const uint32_t my_rows = base + C::OFF_ROWS + G * (2 * BLK * 4) + row * 4;  // corr; l at + BLK * 4
+        uint32_t hc = 0;   // heads done by this group
+        uint32_t h2 = 0;   // ... of which had two units
+        uint32_t ug = 0;   // units done by this group
+        uint32_t prev_bar = 0, prev_par = 0;  // the barrier that says the previous unit's P.V has read P (0: no previous unit)
         TL_DECL;
-        auto retire_pending = [&]() {
-            const uint32_t ob = pend.ur & 1;
-            TL(7);
-            mbar_wait(bar_o_full + 8 * (2 * G + ob), (pend.ur >> 1) & 1);
-            TL(8);
-            tc_fence_after_sync();
-            {
-                uint32_t v[32];
-                tmem_ld_32x32(t_lane + C::O_COL + G * 64 + ob * D, v);
-                tmem_ld_wait();
-#pragma unroll
-                for (int j = 0; j < 32; ++j) o[j] = fmaf(o[j], pend.corr, __uint_as_float(v[j]));
-            }
-            tc_fence_before_sync();
-            mbar_arrive(bar_o_empty + 8 * (2 * G + ob));
-            if (pend.last) {
-                const float inv = 1.0f / pend.l;
-                if (row < pend.len) {
-                    __nv_bfloat16* dst = p.ctx + static_cast<size_t>(pend.start + row) * p.H + pend.h * D;
-#pragma unroll
-                    for (int q = 0; q < D / 16; ++q) {
-                        uint32_t wd[8];
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) wd[j] = pack_op2(o[q * 16 + 2 * j] * inv, o[q * 16 + 2 * j + 1] * inv);
-                        stg_v8(dst + q * 16, wd);
-                    }
-                }
-            }
-            pend.valid = false;
-            TL(9);
-        };
         Walk w = walk_init();
         while (w.b < n_items) {
             int start, len, first, last;
@@ -401,39 +435,7 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                 khi = __ldg(p.cu + b) - start;
             }
             for (int h = G; h < HEADS; h += 2, ++hc) {
-                // ---- convert: ACC[G] + bias -> Q / K / V tiles ----
-                TL(11);
-                mbar_wait(bar_acc_full + 8 * G, hc & 1);
-                TL(0);
-                tc_fence_after_sync();
-                {
-                    uint32_t words[3][16];
-#pragma unroll
-                    for (int j = 0; j < 3; ++j) {  // q, k, v
-                        uint32_t v[32];
-                        tmem_ld_32x32(t_lane + C::ACC_COL + G * C::ACC_STRIDE + j * D, v);
-                        const uint32_t bs = smem_bias + (j * H + h * D) * 4;
-                        tmem_ld_wait();
-#pragma unroll
-                        for (int q = 0; q < 8; ++q) {
-                            const uint4 b = lds_v4(bs + q * 16);
-                            words[j][q * 2 + 0] = epi_pair_bf16<EPI_BIAS>(v[q * 4 + 0], v[q * 4 + 1], __uint_as_float(b.x), __uint_as_float(b.y));
-                            words[j][q * 2 + 1] = epi_pair_bf16<EPI_BIAS>(v[q * 4 + 2], v[q * 4 + 3], __uint_as_float(b.z), __uint_as_float(b.w));
-                        }
-                    }
-                    tc_fence_before_sync();
-                    mbar_arrive(bar_acc_empty + 8 * G);  // the accumulator is in registers
-                    TL(1);
-                    mbar_wait(bar_t_empty + 8 * G, (hc & 1) ^ 1);  // the group's previous head has finished with the tiles
-                    TL(2);
-#pragma unroll
-                    for (int j = 0; j < 3; ++j) stage_words_bf16(tile + j * T_TILE, row, words[j]);
-                    fence_proxy_async_smem();
-                    mbar_arrive(bar_t_full + 8 * G);
-                    TL(3);
-                }
-                // ---- softmax ----
-                float m = -INFINITY, l = 0.f;  // the first unit's corr is exp2(-inf) = 0: the previous head's output vanishes
+                float m = -INFINITY, l = 0.f;
                 for (int u = 0; u < nunits; ++u, ++ug) {
                     // this unit's keys u*64 + j, j in [jlo, jhi), belong to the row's sentence
                     const int jlo = min(max(klo - u * UNIT, 0), UNIT), jhi = min(max(khi - u * UNIT, 0), UNIT);
@@ -462,10 +464,9 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                     // a row with no key yet (its sentence lies in the other unit, or the row is past the tile's tokens)
                     // keeps m = -inf; 0 stands in for it below so that exp2 sees -inf, not inf - inf
                     const float m_use = m_new == -INFINITY ? 0.f : m_new;
-                    const float corr = ex2(m - m_use);
+                    const float corr = ex2(m - m_use);  // unit 0: exp2(-inf) = 0
                     m = m_new;
                     TL(6);
-                    if (pend.valid) retire_pending();  // also: the previous P.V is done, the P buffer is free
                     const uint64_t sc2 = pk2(p.scale_log2, p.scale_log2), nm2 = pk2(-m_use, -m_use);
                     uint64_t lb2[4] = {0, 0, 0, 0};
                     uint32_t pw[UNIT / 2];  // this row's probabilities, two keys per word
@@ -480,6 +481,10 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                             pw[q * 4 + j] = pack_op2(pa, pb);
                         }
                     }
+                    TL(7);
+                    if (prev_bar != 0) mbar_wait(prev_bar, prev_par);  // the previous unit's P.V has read the P buffer
+                    TL(8);
+                    tc_fence_after_sync();
                     tmem_st_32x32(t_lane + C::P_COL + G * (UNIT / 2), pw);
                     float lb;
                     {
@@ -488,19 +493,135 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                         upk2(add2(lb2[2], lb2[3]), a2, a3);
                         lb = (a0 + a1) + (a2 + a3);
                     }
+                    l = fmaf(l, corr, lb);
                     tmem_st_wait();
                     tc_fence_before_sync();
                     mbar_arrive(bar_p_full + 8 * G);
+                    prev_bar = bar_o_full + 8 * (2 * G + u);
+                    prev_par = (u == 0 ? hc : h2) & 1;
                     TL(10);
-                    l = fmaf(l, corr, lb);
-                    pend.valid = true; pend.last = u == nunits - 1; pend.ur = ug; pend.corr = corr; pend.l = l;
-                    pend.start = start; pend.len = len; pend.h = h;
+                    if (u == nunits - 1) {
+                        // hand the head to the output warps: out = (O_0 * corr + O_1) / l (one unit: O_0 / l)
+                        mbar_wait(bar_o_empty + 8 * G, (hc & 1) ^ 1);  // they have read the previous head's pair
+                        asm volatile("st.shared.f32 [%0], %1;" ::"r"(my_rows), "f"(corr) : "memory");
+                        asm volatile("st.shared.f32 [%0], %1;" ::"r"(my_rows + BLK * 4), "f"(l) : "memory");
+                        mbar_arrive(bar_c_full + 8 * G);
+                        TL(9);
+                    }
                 }
+                if (nunits > 1) ++h2;
             }
         }
-        if (pend.valid) retire_pending();
         TL(11);
-        TL_PRINT("softmax: acc_full cvt t_empty stage s_full ldS max [7] o_full retire exp+stP other");
+        TL_PRINT("softmax: - - - - s_full ldS max exp o_full(P free) handoff stP other");
+    } else if (warp < QA_OUTPUT_WARP0) {
+        // ------------------------------ convert warps: ACC + bias -> Q / K / V tiles, head after head ------------------------------
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(QA_REGS_CONVERT));
+        const int quad = warp & 3;
+        const int row = quad * 32 + lane;
+        const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
+        uint32_t gh = 0;  // heads converted; head gh belongs to group gh & 1 and is that group's head number gh >> 1
+        TL_DECL;
+        Walk w = walk_init();
+        while (w.b < n_items) {
+            int start, len;
+            if (!take(w, start, len)) continue;
+            for (int h = 0; h < HEADS; ++h, ++gh) {
+                const uint32_t G = gh & 1, hcg = gh >> 1;
+                const uint32_t tile = smem_t + G * C::G_TILES * T_TILE;
+                TL(11);
+                mbar_wait(bar_acc_full + 8 * G, hcg & 1);
+                TL(0);
+                tc_fence_after_sync();
+                uint32_t words[3][16];
+#pragma unroll
+                for (int j = 0; j < 3; ++j) {  // q, k, v
+                    uint32_t v[32];
+                    tmem_ld_32x32(t_lane + C::ACC_COL + G * C::ACC_STRIDE + j * D, v);
+                    const uint32_t bs = smem_bias + (j * H + h * D) * 4;
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) {
+                        const uint4 b = lds_v4(bs + q * 16);
+                        words[j][q * 2 + 0] = epi_pair_bf16<EPI_BIAS>(v[q * 4 + 0], v[q * 4 + 1], __uint_as_float(b.x), __uint_as_float(b.y));
+                        words[j][q * 2 + 1] = epi_pair_bf16<EPI_BIAS>(v[q * 4 + 2], v[q * 4 + 3], __uint_as_float(b.z), __uint_as_float(b.w));
+                    }
+                }
+                tc_fence_before_sync();
+                mbar_arrive(bar_acc_empty + 8 * G);  // the accumulator is in registers
+                TL(1);
+                // Q and K: the previous head's last S has read them; V alternates between two tiles, this one was read by the
+                // head before the previous one - so the tiles are staged while the previous head's softmax is still running
+                mbar_wait(bar_qk_empty + 8 * G, (hcg & 1) ^ 1);
+                mbar_wait(bar_v_empty + 8 * (2 * G + (hcg % QA_VBUFS)), ((hcg / QA_VBUFS) & 1) ^ 1);
+                TL(2);
+                stage_words_bf16(tile, row, words[0]);
+                stage_words_bf16(tile + T_TILE, row, words[1]);
+                stage_words_bf16(tile + (2 + (hcg % QA_VBUFS)) * T_TILE, row, words[2]);
+                fence_proxy_async_smem();
+                mbar_arrive(bar_t_full + 8 * G);
+                TL(3);
+            }
+        }
+        TL(11);
+        TL_PRINT("convert: acc_full cvt qkv_empty stage");
+    } else {
+        // ------------------------------ output warps: ctx rows of finished heads ------------------------------
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(QA_REGS_OUTPUT));
+        const int quad = warp & 3;
+        const int row = quad * 32 + lane;
+        const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
+        uint32_t gh = 0;   // heads written
+        uint32_t h2 = 0;   // two-unit heads per group before this tile
+        TL_DECL;
+        Walk w = walk_init();
+        while (w.b < n_items) {
+            int start, len;
+            if (!take(w, start, len)) continue;
+            const int nunits = (len + UNIT - 1) / UNIT;
+            for (int h = 0; h < HEADS; ++h, ++gh) {
+                const uint32_t G = gh & 1, hcg = gh >> 1;
+                const uint32_t rows_g = base + C::OFF_ROWS + G * (2 * BLK * 4) + row * 4;
+                TL(11);
+                mbar_wait(bar_c_full + 8 * G, hcg & 1);
+                TL(0);
+                float corr, l;
+                asm volatile("ld.shared.f32 %0, [%1];" : "=f"(corr) : "r"(rows_g) : "memory");
+                asm volatile("ld.shared.f32 %0, [%1];" : "=f"(l) : "r"(rows_g + BLK * 4) : "memory");
+                // the last unit's P.V is complete, and with it the first's (one issuing thread, in order)
+                mbar_wait(bar_o_full + 8 * (2 * G + (nunits - 1)), (nunits == 1 ? hcg : h2 + (h >> 1)) & 1);
+                TL(1);
+                tc_fence_after_sync();
+                const float inv = 1.0f / l;
+                const float c0 = nunits > 1 ? corr * inv : inv;
+                __nv_bfloat16* dst = p.ctx + static_cast<size_t>(start + row) * p.H + h * D;
+                const uint32_t to = t_lane + C::O_COL + G * 64;
+#pragma unroll
+                for (int q = 0; q < D / 16; ++q) {
+                    uint32_t a[16], b[16];
+                    tmem_ld_32x16(to + q * 16, a);
+                    if (nunits > 1) tmem_ld_32x16(to + D + q * 16, b);
+                    tmem_ld_wait();
+                    uint32_t wd[8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        float o0 = __uint_as_float(a[2 * j]) * c0, o1 = __uint_as_float(a[2 * j + 1]) * c0;
+                        if (nunits > 1) {
+                            o0 = fmaf(__uint_as_float(b[2 * j]), inv, o0);
+                            o1 = fmaf(__uint_as_float(b[2 * j + 1]), inv, o1);
+                        }
+                        wd[j] = pack_op2(o0, o1);
+                    }
+                    if (row < len) stg_v8(dst + q * 16, wd);
+                }
+                tc_fence_before_sync();
+                mbar_arrive(bar_o_empty + 8 * G);
+                TL(2);
+            }
+            if (nunits > 1) h2 += HEADS / 2;
+        }
+        TL(11);
+        TL_PRINT("output: c_full o_full write");
     }
 
     tc_fence_before_sync();
