@@ -321,10 +321,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
                         if (j >= nvalid) v[j] = 0xff800000u;  // -inf
                 }
                 // four independent chains for the row max (a single 64-deep FMNMX chain is pure latency)
-                float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-#pragma unroll
-                for (int j = 0; j < UNIT; ++j) mx4[j & 3] = fmaxf(mx4[j & 3], __uint_as_float(v[j]));
-                const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+                const float mx = row_max(v);
                 const float m_new = fmaxf(m, mx * p.scale_log2);
                 const float corr = ex2(m - m_new);
                 m = m_new;

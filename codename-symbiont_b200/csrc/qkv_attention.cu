@@ -66,6 +66,9 @@ constexpr int X_BLK = BLK * BK * 2;
 #ifndef QA_LOOKAHEAD
 #define QA_LOOKAHEAD 0
 #endif
+#ifndef QA_JOINT
+#define QA_JOINT 0
+#endif
 #ifndef QA_VBUFS
 #define QA_VBUFS 1
 #endif
@@ -76,10 +79,11 @@ struct QaCfg {
     static constexpr int HEADS = H / D;
     static constexpr int NQ = 3 * D;                 // accumulator columns per head: q | k | v
     static constexpr int W_SUB = D * BK * 2;         // one [D x 64] box of Wqkv rows
-    static constexpr int W_BLK = 3 * W_SUB;          // [3D x 64]: one K-major B operand block
+    static constexpr int PASS_HEADS = QA_JOINT ? 2 : 1;   // heads per projection pass (one accumulator of PASS_HEADS * NQ columns)
+    static constexpr int W_BLK = PASS_HEADS * 3 * W_SUB;  // [PASS_HEADS * 3D x 64]: one K-major B operand block
     // W ring slots (KB % WS == 0: slots are compile-time in the k loop). A ring holding the whole head (6 slots at H = 384)
     // was measured slower: 0.703 vs 0.644 ms per launch at c2
-    static constexpr int WS = KB % 3 == 0 ? 3 : 2;
+    static constexpr int WS = QA_JOINT ? 2 : (KB % 3 == 0 ? 3 : 2);
     static constexpr int T_TILE = BLK * D * 2;       // one Q / K / V tile
     static constexpr int OFF_X = 0;
     static constexpr int OFF_W = KB * X_BLK;
@@ -160,7 +164,7 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
         for (int s = 0; s < WS; ++s) { mbar_init(bar_w_full + 8 * s, 1); mbar_init(bar_w_empty + 8 * s, 1); }
         for (int s = 0; s < 2; ++s) {
             mbar_init(bar_acc_full + 8 * s, 1);
-            mbar_init(bar_acc_empty + 8 * s, QA_GROUP);
+            mbar_init(bar_acc_empty + 8 * s, C::PASS_HEADS * QA_GROUP);
             mbar_init(bar_t_full + 8 * s, QA_GROUP);
             mbar_init(bar_qk_empty + 8 * s, 1);
             mbar_init(bar_s_full + 8 * s, 1);
@@ -236,7 +240,7 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
             }
             __syncwarp();
             ++it;
-            for (int h = 0; h < HEADS; ++h) {
+            for (int h = 0; h < HEADS; h += C::PASS_HEADS) {
 #pragma unroll
                 for (int kb = 0; kb < KB; ++kb, ++wb) {
                     const uint32_t s = kb % WS;
@@ -244,8 +248,11 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                     if (elect_one()) {
                         mbar_arrive_expect_tx(bar_w_full + 8 * s, W_BLK);
 #pragma unroll
-                        for (int j = 0; j < 3; ++j)  // q, k, v rows of this head
-                            tma_load_2d(smem_w + s * W_BLK + j * W_SUB, &tmap_w, kb * BK, j * H + h * D, bar_w_full + 8 * s);
+                        for (int hh = 0; hh < C::PASS_HEADS; ++hh)
+#pragma unroll
+                            for (int j = 0; j < 3; ++j)  // q, k, v rows of this head
+                                tma_load_2d(smem_w + s * W_BLK + (hh * 3 + j) * W_SUB, &tmap_w, kb * BK, j * H + (h + hh) * D,
+                                            bar_w_full + 8 * s);
                     }
                     __syncwarp();
                 }
@@ -256,7 +263,7 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
         // ACC[g & 1] = x . Wqkv_h^T (128 x 96 x H) for head after head, as far ahead as the two accumulators allow. The
         // three issuers (this warp and one per group) block on their own dependencies only: with a single issuing warp
         // walking a fixed schedule the two groups ran in lockstep and each waited for the other's softmax.
-        constexpr uint32_t idesc_g = umma_idesc_op(BLK, NQ);
+        constexpr uint32_t idesc_g = umma_idesc_op(BLK, C::PASS_HEADS * NQ);
         const uint64_t dx0 = umma_desc_sw128(smem_x), dw0 = umma_desc_sw128(smem_w);
         Walk wp = walk_init();
         uint32_t pit = 0, gg = 0, wb = 0;  // tiles entered, heads projected, W blocks consumed
@@ -268,9 +275,10 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
             mbar_wait(bar_x_full, pit & 1);
             TL(1);
             ++pit;
-            for (int ph = 0; ph < HEADS; ++ph, ++gg) {
-                const uint32_t ab = gg & 1;
-                mbar_wait(bar_acc_empty + 8 * ab, ((gg >> 1) & 1) ^ 1);  // the convert warps have drained this accumulator
+            for (int ph = 0; ph < HEADS; ph += C::PASS_HEADS, ++gg) {
+                // one head per pass: accumulators alternate; two heads per pass: one accumulator of 2 * NQ columns
+                const uint32_t ab = QA_JOINT ? 0u : (gg & 1);
+                mbar_wait(bar_acc_empty + 8 * ab, ((QA_JOINT ? gg : gg >> 1) & 1) ^ 1);  // the convert warps have drained it
                 TL(2);
                 tc_fence_after_sync();
 #pragma unroll
@@ -289,7 +297,7 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                         umma_commit(bar_w_empty + 8 * sl);
                         if (kb == KB - 1) {
                             umma_commit(bar_acc_full + 8 * ab);
-                            if (ph == HEADS - 1) umma_commit(bar_x_empty);  // the x tile has been read for the last time
+                            if (ph == HEADS - C::PASS_HEADS) umma_commit(bar_x_empty);  // the x tile has been read for the last time
                         }
                     }
                     __syncwarp();
@@ -456,10 +464,7 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                         for (int j = 0; j < UNIT; ++j)
                             if (static_cast<uint32_t>(j - jlo) >= span) v[j] = 0xff800000u;
                     }
-                    float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-#pragma unroll
-                    for (int j = 0; j < UNIT; ++j) mx4[j & 3] = fmaxf(mx4[j & 3], __uint_as_float(v[j]));
-                    const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+                    const float mx = row_max(v);
                     const float m_new = fmaxf(m, mx * p.scale_log2);
                     // a row with no key yet (its sentence lies in the other unit, or the row is past the tile's tokens)
                     // keeps m = -inf; 0 stands in for it below so that exp2 sees -inf, not inf - inf
@@ -530,7 +535,8 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                 const uint32_t G = gh & 1, hcg = gh >> 1;
                 const uint32_t tile = smem_t + G * C::G_TILES * T_TILE;
                 TL(11);
-                mbar_wait(bar_acc_full + 8 * G, hcg & 1);
+                const uint32_t ab = QA_JOINT ? 0u : G;
+                mbar_wait(bar_acc_full + 8 * ab, hcg & 1);  // (two heads per pass: pass number = the group's head number)
                 TL(0);
                 tc_fence_after_sync();
                 uint32_t words[3][16];
@@ -548,7 +554,7 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                     }
                 }
                 tc_fence_before_sync();
-                mbar_arrive(bar_acc_empty + 8 * G);  // the accumulator is in registers
+                mbar_arrive(bar_acc_empty + 8 * ab);  // the accumulator is in registers
                 TL(1);
                 // Q and K: the previous head's last S has read them; V alternates between two tiles, this one was read by the
                 // head before the previous one - so the tiles are staged while the previous head's softmax is still running

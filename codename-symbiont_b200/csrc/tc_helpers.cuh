@@ -206,6 +206,26 @@ __device__ __forceinline__ uint64_t umma_desc_k(uint32_t a) {
     return D == 32 ? umma_desc_k_sw64(a) : umma_desc_sw128(a);
 }
 
+// max of three in one instruction (FMNMX3)
+__device__ __forceinline__ float fmax3(float a, float b, float c) {
+    float r;
+    asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+    return r;
+}
+// row maximum of n fp32 bit patterns (n % 8 == 0): four chains of three-input maxima
+template <int N>
+__device__ __forceinline__ float row_max(const uint32_t (&v)[N]) {
+    static_assert(N % 8 == 0, "eight values per round");
+    float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
+#pragma unroll
+    for (int j = 0; j < N; j += 8) {
+        m0 = fmax3(m0, __uint_as_float(v[j]), __uint_as_float(v[j + 1]));
+        m1 = fmax3(m1, __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
+        m2 = fmax3(m2, __uint_as_float(v[j + 4]), __uint_as_float(v[j + 5]));
+        m3 = fmax3(m3, __uint_as_float(v[j + 6]), __uint_as_float(v[j + 7]));
+    }
+    return fmaxf(fmax3(m0, m1, m2), m3);
+}
 __device__ __forceinline__ float ex2(float x) {
     float y;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
