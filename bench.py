@@ -150,24 +150,24 @@ def kernel_work(shape, lengths, kind):
     B = len(lengths)
     if kind == "gemm_qkv":  # x (hi) in, qkv out, bf16
         return 2 * T * 3 * H * H, (2 * H + 6 * H) * T
-    if kind == "gemm_attn_out":  # ctx + (hi, lo) residual in, (hi, lo) out
-        return 2 * T * H * H, (2 * H + 4 * H + 4 * H) * T
+    if kind == "gemm_attn_out":  # ctx + (hi, lo) residual in, (hi, lo) out; a (hi, lo) element is 2 + 1 bytes
+        return 2 * T * H * H, (2 * H + 3 * H + 3 * H) * T
     if kind == "gemm_ffn1":
         return 2 * T * I * H, (2 * H + 2 * I) * T
     if kind == "gemm_ffn2":
-        return 2 * T * I * H, (2 * I + 4 * H + 4 * H) * T
+        return 2 * T * I * H, (2 * I + 3 * H + 3 * H) * T
     if kind == "ffn_fused":  # (hi, lo) in, (hi, lo) out; the intermediate stays on chip
-        return 4 * T * I * H, (4 * H + 4 * H) * T
+        return 4 * T * I * H, (3 * H + 3 * H) * T
     if kind == "qkv_attention":  # x (hi) in, ctx out; q, k, v stay on chip
         return 2 * T * 3 * H * H + 4 * H * s2, (2 * H + 2 * H) * T
     if kind == "attention":  # qkv in, ctx out
         return 4 * H * s2, (6 * H + 2 * H) * T
-    if kind == "embed_ln":  # fp32 word row in, (hi, lo) bf16 rows out, ids + type ids + mask
-        return 0.0, (8 * H + 12) * T
+    if kind == "embed_ln":  # fp32 word row in, (hi, lo) rows out, ids + type ids + mask
+        return 0.0, (7 * H + 12) * T
     if kind == "add_ln":  # fp32 GEMM output + (hi, lo) residual in, (hi, lo) out
-        return 0.0, 12 * H * T
+        return 0.0, 10 * H * T
     if kind == "pool":  # (hi, lo) rows in, f32 [B,H] out
-        return 0.0, 4 * H * T + 4 * T + 4 * H * B
+        return 0.0, 3 * H * T + 4 * T + 4 * H * B
     if kind == "lengths":
         return 0.0, 4.0 * B * (T / max(B, 1)) + 8 * B
     raise KeyError(kind)

@@ -72,6 +72,29 @@ __host__ __device__ constexpr uint32_t umma_idesc_op(int m, int n) {
 }
 }  // operand-format namespace
 
+// ---- the low half of the residual stream -----------------------------------------------------------------------------
+// An activation that feeds a residual add is kept as hi (the 16-bit value the next GEMM multiplies) plus lo = y - hi
+// rounded to an 8-bit e5m2 float (fp16's exponent range, 2 mantissa bits): 3 bytes per element instead of 4. |y - hi| is
+// at most half an ulp of hi, so hi + lo carries 3 more bits than hi alone (14 with fp16 operands); measured through the
+// whole model that is as good as a 16-bit lo (6.8e-4 vs 6.6e-4 max-abs on 2-4-token sentences,
+// scripts/precision_study_f16.py variants). The same format in both operand builds.
+__device__ __forceinline__ uint32_t pack_lo8x4(float a, float b, float c, float d) {  // byte i = value i
+    uint16_t w0, w1;
+    asm("cvt.rn.satfinite.e5m2x2.f32 %0, %1, %2;" : "=h"(w0) : "f"(b), "f"(a));
+    asm("cvt.rn.satfinite.e5m2x2.f32 %0, %1, %2;" : "=h"(w1) : "f"(d), "f"(c));
+    return static_cast<uint32_t>(w0) | (static_cast<uint32_t>(w1) << 16);
+}
+// two e5m2 bytes (the low 16 bits of h) -> two floats; exact
+__device__ __forceinline__ float2 unpack_lo8x2(uint32_t h) {
+    uint32_t f;
+    asm("cvt.rn.f16x2.e5m2x2 %0, %1;" : "=r"(f) : "h"(static_cast<uint16_t>(h)));
+    return __half22float2(*reinterpret_cast<__half2*>(&f));
+}
+__device__ __forceinline__ float4 unpack_lo8x4(uint32_t w) {
+    const float2 a = unpack_lo8x2(w), b = unpack_lo8x2(w >> 16);
+    return make_float4(a.x, a.y, b.x, b.y);
+}
+
 // candle `gelu_erf`: 0.5 x (1 + erf(x / sqrt 2)); `gelu`: tanh form; relu. (act = B200_EMBED_ACT_*)
 __device__ __forceinline__ float activate(float x, int act) {
     if (act == 0) return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f));

@@ -15,29 +15,30 @@ namespace {
 
 constexpr int MAX_CHUNKS = 8;  // hidden <= 1024: 32 lanes x 4 elements x 8 chunks
 
-// bf16 activations that feed a residual add are kept as a (hi, lo) pair of bf16 tensors: hi = bf16(y) is what
-// the next GEMM multiplies, hi + lo (16 mantissa bits) is what the residual add and the pooling read. Rounding
-// the residual stream to bf16 alone would cost 8e-3 max-abs on short sentences (scripts/precision_study.py).
+// 16-bit activations that feed a residual add are kept as a (hi, lo) pair: hi = the 16-bit value the next GEMM
+// multiplies, lo = y - hi as an 8-bit e5m2 float (common.cuh); hi + lo is what the residual add and the pooling read.
+// Rounding the residual stream to 16 bits alone would cost 8e-3 (bf16) / 2.9e-3 (fp16) max-abs on short sentences
+// (scripts/precision_study.py, precision_study_f16.py).
 template <typename T>
-__device__ __forceinline__ void store_split(T* hi, T* lo, int col, float4 y);
+__device__ __forceinline__ void store_split(T* hi, uint8_t* lo, int col, float4 y);
 template <>
-__device__ __forceinline__ void store_split<float>(float* hi, float*, int col, float4 y) {
+__device__ __forceinline__ void store_split<float>(float* hi, uint8_t*, int col, float4 y) {
     Vec4<float>::store(hi + col, y);
 }
 template <>
-__device__ __forceinline__ void store_split<__nv_bfloat16>(__nv_bfloat16* hi, __nv_bfloat16* lo, int col, float4 y) {
+__device__ __forceinline__ void store_split<__nv_bfloat16>(__nv_bfloat16* hi, uint8_t* lo, int col, float4 y) {
     const uint2 h = make_uint2(pack_op2(y.x, y.y), pack_op2(y.z, y.w));
     *reinterpret_cast<uint2*>(hi + col) = h;
     if (lo != nullptr) {
         const float2 a = unpack_op2(h.x), b = unpack_op2(h.y);
-        *reinterpret_cast<uint2*>(lo + col) = make_uint2(pack_op2(y.x - a.x, y.y - a.y), pack_op2(y.z - b.x, y.w - b.y));
+        *reinterpret_cast<uint32_t*>(lo + col) = pack_lo8x4(y.x - a.x, y.y - a.y, y.z - b.x, y.w - b.y);
     }
 }
 template <typename T>
-__device__ __forceinline__ float4 load_split(const T* hi, const T* lo, size_t off) {
+__device__ __forceinline__ float4 load_split(const T* hi, const uint8_t* lo, size_t off) {
     float4 a = Vec4<T>::load(hi + off);
     if (lo != nullptr) {
-        const float4 b = Vec4<T>::load(lo + off);
+        const float4 b = unpack_lo8x4(*reinterpret_cast<const uint32_t*>(lo + off));
         a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
     }
     return a;
@@ -48,7 +49,7 @@ template <typename T, int NC>
 __device__ __forceinline__ void warp_layernorm_store(float4 (&v)[NC], int nchunk, int H, int lane,
                                                      const float* __restrict__ gamma,
                                                      const float* __restrict__ beta, float eps, T* out_row,
-                                                     T* out_lo_row) {
+                                                     uint8_t* out_lo_row) {
     float s = 0.f;
 #pragma unroll
     for (int i = 0; i < NC; ++i)
@@ -229,7 +230,7 @@ embed_layernorm_kernel(const uint32_t* __restrict__ ids, const uint32_t* __restr
                        const float* __restrict__ word, const float* __restrict__ pos,
                        const float* __restrict__ type, const float* __restrict__ gamma,
                        const float* __restrict__ beta, float eps, int H, int vocab,
-                       int type_vocab, int max_pos, T* __restrict__ out, T* __restrict__ out_lo,
+                       int type_vocab, int max_pos, T* __restrict__ out, uint8_t* __restrict__ out_lo,
                        int* __restrict__ status) {
     pdl_trigger();
     pdl_wait();
@@ -299,10 +300,10 @@ embed_layernorm_kernel(const uint32_t* __restrict__ ids, const uint32_t* __restr
 // ---- K4 -------------------------------------------------------------------------------------------
 template <typename TY, typename T>
 __global__ void add_layernorm_kernel(const TY* __restrict__ y, const T* __restrict__ residual,
-                                     const T* __restrict__ residual_lo, int rows_cap,
+                                     const uint8_t* __restrict__ residual_lo, int rows_cap,
                                      const int* __restrict__ d_rows, const float* __restrict__ gamma,
                                      const float* __restrict__ beta, float eps, int H, T* __restrict__ out,
-                                     T* __restrict__ out_lo) {
+                                     uint8_t* __restrict__ out_lo) {
     const long long r = static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     int rows = rows_cap;
@@ -324,7 +325,7 @@ __global__ void add_layernorm_kernel(const TY* __restrict__ y, const T* __restri
 // One block per sentence: thread (g, c) sums rows g, g+G, ... of 4 columns; groups are combined in
 // shared memory; the divisor is len + 1e-9 in fp32 exactly as the reference; optional L2 norm.
 template <typename T>
-__global__ void mean_pool_kernel(const T* __restrict__ hidden, const T* __restrict__ hidden_lo,
+__global__ void mean_pool_kernel(const T* __restrict__ hidden, const uint8_t* __restrict__ hidden_lo,
                                  const int* __restrict__ cu, int H, int normalize, float* __restrict__ out) {
     extern __shared__ float4 part[];  // [G][H/4]
     __shared__ float red[32];
@@ -405,7 +406,7 @@ cudaError_t launch_embed_layernorm(const EmbedArgs& a, cudaStream_t s) {
 #define B200_EMBED_LAUNCH(PAD, TOK, NCH)                                                                                   \
     launch_err = launch_pdl(embed_layernorm_kernel<T, PAD, TOK, NCH>, dim3(grid), dim3(256), 0, s,                       \
         a.ids, a.type_ids, a.cu, a.batch, a.seq_len, a.total_tokens, a.word, a.pos, a.type, a.gamma, a.beta, a.eps, a.H,  \
-        a.vocab, a.type_vocab, a.max_pos, static_cast<T*>(a.out), static_cast<T*>(a.out_lo), a.status)
+        a.vocab, a.type_vocab, a.max_pos, static_cast<T*>(a.out), static_cast<uint8_t*>(a.out_lo), a.status)
 #define B200_EMBED_PICK(PAD)                                    \
     switch (nch) {                                              \
         case 1: B200_EMBED_LAUNCH(PAD, 2, 1); break;            \
@@ -426,28 +427,28 @@ template cudaError_t launch_embed_layernorm<__nv_bfloat16>(const EmbedArgs&, cud
 template cudaError_t launch_embed_layernorm<float>(const EmbedArgs&, cudaStream_t);
 
 template <typename TY, typename T>
-cudaError_t launch_add_layernorm(const TY* y, const T* residual, const T* residual_lo, int rows_cap,
+cudaError_t launch_add_layernorm(const TY* y, const T* residual, const uint8_t* residual_lo, int rows_cap,
                                  const int* d_rows, const float* gamma, const float* beta, float eps, int H, T* out,
-                                 T* out_lo, cudaStream_t s) {
+                                 uint8_t* out_lo, cudaStream_t s) {
     if (rows_cap <= 0) return cudaSuccess;
     add_layernorm_kernel<TY, T><<<(rows_cap + 7) / 8, 256, 0, s>>>(y, residual, residual_lo, rows_cap, d_rows, gamma,
                                                                   beta, eps, H, out, out_lo);
     return cudaGetLastError();
 }
 template cudaError_t launch_add_layernorm<__nv_bfloat16, __nv_bfloat16>(const __nv_bfloat16*, const __nv_bfloat16*,
-                                                                        const __nv_bfloat16*, int, const int*,
+                                                                        const uint8_t*, int, const int*,
                                                                         const float*, const float*, float, int,
-                                                                        __nv_bfloat16*, __nv_bfloat16*, cudaStream_t);
+                                                                        __nv_bfloat16*, uint8_t*, cudaStream_t);
 template cudaError_t launch_add_layernorm<float, __nv_bfloat16>(const float*, const __nv_bfloat16*,
-                                                                const __nv_bfloat16*, int, const int*, const float*,
+                                                                const uint8_t*, int, const int*, const float*,
                                                                 const float*, float, int, __nv_bfloat16*,
-                                                                __nv_bfloat16*, cudaStream_t);
-template cudaError_t launch_add_layernorm<float, float>(const float*, const float*, const float*, int, const int*,
-                                                        const float*, const float*, float, int, float*, float*,
+                                                                uint8_t*, cudaStream_t);
+template cudaError_t launch_add_layernorm<float, float>(const float*, const float*, const uint8_t*, int, const int*,
+                                                        const float*, const float*, float, int, float*, uint8_t*,
                                                         cudaStream_t);
 
 template <typename T>
-cudaError_t launch_mean_pool(const T* hidden, const T* hidden_lo, const int* cu, int batch, int H, int normalize,
+cudaError_t launch_mean_pool(const T* hidden, const uint8_t* hidden_lo, const int* cu, int batch, int H, int normalize,
                              float* out, cudaStream_t s) {
     if (batch <= 0) return cudaSuccess;
     const int cols4 = H / 4;
@@ -458,9 +459,9 @@ cudaError_t launch_mean_pool(const T* hidden, const T* hidden_lo, const int* cu,
     return launch_pdl(mean_pool_kernel<T>, dim3(batch), dim3(threads), G * cols4 * sizeof(float4), s, hidden, hidden_lo, cu, H,
                       normalize, out);
 }
-template cudaError_t launch_mean_pool<__nv_bfloat16>(const __nv_bfloat16*, const __nv_bfloat16*, const int*, int, int,
+template cudaError_t launch_mean_pool<__nv_bfloat16>(const __nv_bfloat16*, const uint8_t*, const int*, int, int,
                                                      int, float*, cudaStream_t);
-template cudaError_t launch_mean_pool<float>(const float*, const float*, const int*, int, int, int, float*,
+template cudaError_t launch_mean_pool<float>(const float*, const uint8_t*, const int*, int, int, int, float*,
                                                      cudaStream_t);
 
 }  // operand-format namespace

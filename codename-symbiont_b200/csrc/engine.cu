@@ -38,11 +38,11 @@ struct Ops {
     cudaError_t (*mask_lengths)(const uint32_t*, int, int, int*, int*, int*, cudaStream_t);
     cudaError_t (*pack_tiles)(const int*, int, int, int*, int*, int*, cudaStream_t);
     cudaError_t (*embed_ln)(const b200::EmbedArgs&, cudaStream_t);
-    cudaError_t (*add_ln_f32)(const float*, const bf16*, const bf16*, int, const int*, const float*, const float*, float, int,
-                              bf16*, bf16*, cudaStream_t);
-    cudaError_t (*add_ln_16)(const bf16*, const bf16*, const bf16*, int, const int*, const float*, const float*, float, int,
-                             bf16*, bf16*, cudaStream_t);
-    cudaError_t (*mean_pool)(const bf16*, const bf16*, const int*, int, int, int, float*, cudaStream_t);
+    cudaError_t (*add_ln_f32)(const float*, const bf16*, const uint8_t*, int, const int*, const float*, const float*, float, int,
+                              bf16*, uint8_t*, cudaStream_t);
+    cudaError_t (*add_ln_16)(const bf16*, const bf16*, const uint8_t*, int, const int*, const float*, const float*, float, int,
+                             bf16*, uint8_t*, cudaStream_t);
+    cudaError_t (*mean_pool)(const bf16*, const uint8_t*, const int*, int, int, int, float*, cudaStream_t);
     cudaError_t (*attention_tc)(const bf16*, const int*, int, int, int, int, int, bf16*, int, cudaStream_t);
     bool (*qkv_attention_supported)(int, int, int);
     cudaError_t (*qkv_attention)(const bf16*, const bf16*, const float*, const int*, const int*, const int*, int, int, int, int,
@@ -95,7 +95,7 @@ struct LayerW {
 struct Workspace {
     size_t cap = 0;  // rows (tokens)
     void *x = nullptr, *qkv = nullptr, *ctx = nullptr, *a = nullptr, *inter = nullptr;
-    void *x_lo = nullptr, *a_lo = nullptr;  // bf16 mode: low halves of the residual stream (x = hi + lo)
+    void *x_lo = nullptr, *a_lo = nullptr;  // 16-bit mode: low halves of the residual stream (x = hi + lo), one e5m2 byte per element
     float* y32 = nullptr;  // pre-LayerNorm fp32 rows when the LN is not fused into the GEMM
     void release() {
         for (void* p : {x, qkv, ctx, a, inter, x_lo, a_lo, static_cast<void*>(y32)})
@@ -270,8 +270,8 @@ int ensure_workspace(b200_embed* h, Workspace& w, size_t rows, size_t elt, cudaS
     CU_TRY(cudaMalloc(&w.a, rows * H * elt));
     CU_TRY(cudaMalloc(&w.inter, rows * I * elt));
     if (elt == 2) {
-        CU_TRY(cudaMalloc(&w.x_lo, rows * H * elt));
-        CU_TRY(cudaMalloc(&w.a_lo, rows * H * elt));
+        CU_TRY(cudaMalloc(&w.x_lo, rows * H));
+        CU_TRY(cudaMalloc(&w.a_lo, rows * H));
     }
     if (elt == 4 || !h->fuse_ln) CU_TRY(cudaMalloc(&w.y32, rows * H * sizeof(float)));
     // Rows past the real token count are read (never used) by 128-row tiles; keep them finite. The memsets
@@ -281,8 +281,8 @@ int ensure_workspace(b200_embed* h, Workspace& w, size_t rows, size_t elt, cudaS
     CU_TRY(cudaMemsetAsync(w.ctx, 0, rows * H * elt, s));
     CU_TRY(cudaMemsetAsync(w.a, 0, rows * H * elt, s));
     CU_TRY(cudaMemsetAsync(w.inter, 0, rows * I * elt, s));
-    if (w.x_lo) CU_TRY(cudaMemsetAsync(w.x_lo, 0, rows * H * elt, s));
-    if (w.a_lo) CU_TRY(cudaMemsetAsync(w.a_lo, 0, rows * H * elt, s));
+    if (w.x_lo) CU_TRY(cudaMemsetAsync(w.x_lo, 0, rows * H, s));
+    if (w.a_lo) CU_TRY(cudaMemsetAsync(w.a_lo, 0, rows * H, s));
     w.cap = rows;
     return B200_EMBED_OK;
 }
@@ -457,7 +457,7 @@ int run_chunk(b200_embed* h, Context& c, cudaStream_t s, const Job& j) {
         } else {
             bf16 *x = static_cast<bf16*>(w.x), *qkv = static_cast<bf16*>(w.qkv), *ctx = static_cast<bf16*>(w.ctx),
                  *a = static_cast<bf16*>(w.a), *inter = static_cast<bf16*>(w.inter);
-            bf16 *x_lo = static_cast<bf16*>(w.x_lo), *a_lo = static_cast<bf16*>(w.a_lo);
+            uint8_t *x_lo = static_cast<uint8_t*>(w.x_lo), *a_lo = static_cast<uint8_t*>(w.a_lo);
             if (use_k23) {
                 CU_TRY(timed(h, c, s, B200_EMBED_KIND_QKV_ATTN, 1, [&] {
                     return h->ops->qkv_attention(x, lw.qkv_w16, lw.qkv_b, cu, c.d_tile_first, c.d_n_tiles, rows, j.batch,
@@ -511,7 +511,7 @@ int run_chunk(b200_embed* h, Context& c, cudaStream_t s, const Job& j) {
     const int normalize = (j.flags & B200_EMBED_FLAG_NORMALIZE) ? 1 : 0;
     CU_TRY(timed(h, c, s, B200_EMBED_KIND_POOL, 1, [&] {
         return fp32 ? f32ops::launch_mean_pool<float>(static_cast<const float*>(w.x), nullptr, cu, j.batch, H, normalize, j.d_out, s)
-                    : h->ops->mean_pool(static_cast<const bf16*>(w.x), static_cast<const bf16*>(w.x_lo), cu, j.batch, H,
+                    : h->ops->mean_pool(static_cast<const bf16*>(w.x), static_cast<const uint8_t*>(w.x_lo), cu, j.batch, H,
                                         normalize, j.d_out, s);
     }));
     return B200_EMBED_OK;
@@ -1129,8 +1129,8 @@ int32_t b200_op_linear(b200_embed* h, int32_t layer, int32_t which, const void* 
     if (!rc) {
         h->launches.fetch_add(1);
         const cudaError_t e = h->ops->add_ln_f32(
-            tmp, static_cast<const bf16*>(residual), static_cast<const bf16*>(residual_lo), rows, nullptr, gam, bet, eps, H,
-            static_cast<bf16*>(y), static_cast<bf16*>(y_lo), s);
+            tmp, static_cast<const bf16*>(residual), static_cast<const uint8_t*>(residual_lo), rows, nullptr, gam, bet, eps, H,
+            static_cast<bf16*>(y), static_cast<uint8_t*>(y_lo), s);
         if (e != cudaSuccess) rc = cuda_fail(e, "add_layernorm");
     }
     cudaStreamSynchronize(s);
@@ -1207,12 +1207,12 @@ int32_t b200_op_add_layernorm(b200_embed* h, int32_t layer, int32_t which, const
                                                          static_cast<float*>(out), nullptr, s)));
     else if (y_is_f32)
         CU_TRY((h->ops->add_ln_f32(static_cast<const float*>(y), static_cast<const bf16*>(residual),
-                                                        static_cast<const bf16*>(residual_lo), rows, nullptr, gam, bet, eps,
-                                                        h->H, static_cast<bf16*>(out), static_cast<bf16*>(out_lo), s)));
+                                                        static_cast<const uint8_t*>(residual_lo), rows, nullptr, gam, bet, eps,
+                                                        h->H, static_cast<bf16*>(out), static_cast<uint8_t*>(out_lo), s)));
     else
         CU_TRY((h->ops->add_ln_16(static_cast<const bf16*>(y), static_cast<const bf16*>(residual),
-                                                       static_cast<const bf16*>(residual_lo), rows, nullptr, gam, bet, eps,
-                                                       h->H, static_cast<bf16*>(out), static_cast<bf16*>(out_lo), s)));
+                                                       static_cast<const uint8_t*>(residual_lo), rows, nullptr, gam, bet, eps,
+                                                       h->H, static_cast<bf16*>(out), static_cast<uint8_t*>(out_lo), s)));
     return B200_EMBED_OK;
 }
 
@@ -1223,7 +1223,7 @@ int32_t b200_op_mean_pool(b200_embed* h, const void* hidden, const void* hidden_
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     h->launches.fetch_add(1);
     CU_TRY(dtype ? f32ops::launch_mean_pool<float>(static_cast<const float*>(hidden), nullptr, cu, batch, h->H, normalize, out, s)
-                 : h->ops->mean_pool(static_cast<const bf16*>(hidden), static_cast<const bf16*>(hidden_lo), cu, batch, h->H,
+                 : h->ops->mean_pool(static_cast<const bf16*>(hidden), static_cast<const uint8_t*>(hidden_lo), cu, batch, h->H,
                                      normalize, out, s));
     return B200_EMBED_OK;
 }
@@ -1325,7 +1325,7 @@ extern "C" int32_t b200_op_linear_noalloc(b200_embed* h, int32_t layer, int32_t 
     g.out = scratch; g.out_f32 = 1; g.epi = b200::EPI_BIAS; g.block_n = h->bn_h;
     CU_TRY(h->ops->gemm_tc_launch(g, s, h->num_sms));
     CU_TRY((h->ops->add_ln_f32(scratch, static_cast<const bf16*>(residual),
-                                                    static_cast<const bf16*>(residual_lo), rows, nullptr, gam, bet, eps, H,
-                                                    static_cast<bf16*>(y), static_cast<bf16*>(y_lo), s)));
+                                                    static_cast<const uint8_t*>(residual_lo), rows, nullptr, gam, bet, eps, H,
+                                                    static_cast<bf16*>(y), static_cast<uint8_t*>(y_lo), s)));
     return B200_EMBED_OK;
 }

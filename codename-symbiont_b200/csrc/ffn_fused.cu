@@ -293,7 +293,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             if (lane == 0) {
                 const uint32_t s = ld_issued % LO_SLOTS;
                 const uint32_t bar = bar_res + 8 * (4 * ew + s);
-                mbar_arrive_expect_tx(bar, CHUNK_BF16);
+                mbar_arrive_expect_tx(bar, CHUNK_BF16 / 2);  // 32 x 32 e5m2 bytes in the first half of the slot
                 tma_load_2d(my_smem + s * CHUNK_BF16, &tmap_r_lo, half * HALF + c * CHUNK, tile * BM + quad * 32, bar);
             }
             ++ld_issued;
@@ -365,15 +365,12 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 #pragma unroll
                 for (int c = 0; c < NCH; ++c) {
                     const int col0 = half * HALF + c * CHUNK;
-                    uint32_t hi_addr[4], lo_addr[4];
-                    // a tile: k-block col0 / 64, 128-byte rows, SWIZZLE_128B; lo slot: 64-byte rows, SWIZZLE_64B
+                    uint32_t hi_addr[4], lo_addr[2];
+                    // a tile: k-block col0 / 64, 128-byte rows, SWIZZLE_128B; lo slot: 32-byte rows, SWIZZLE_32B
                     const uint32_t arow = smem_a + (col0 / BK) * BLK16 + row_in_tile * 128;
-                    const uint32_t lrow = my_smem + (ld_used % LO_SLOTS) * CHUNK_BF16 + lane * 64;
 #pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        hi_addr[q] = arow + ((((col0 % BK) / 8 + q) ^ (row_in_tile & 7)) << 4);
-                        lo_addr[q] = lrow + ((q ^ ((lane >> 1) & 3)) << 4);
-                    }
+                    for (int q = 0; q < 4; ++q) hi_addr[q] = arow + ((((col0 % BK) / 8 + q) ^ (row_in_tile & 7)) << 4);
+                    lo8_piece_addrs(my_smem + (ld_used % LO_SLOTS) * CHUNK_BF16, lane, lo_addr);
                     if (p.has_lo) {
                         mbar_wait(bar_res + 8 * (4 * ew + (ld_used % LO_SLOTS)), (ld_used / LO_SLOTS) & 1);
                         ++ld_used;
@@ -415,13 +412,13 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                         if (lane == 0) mbar_arrive_cluster(l_out_empty);
                     }
                     const int col0 = half * HALF + c * CHUNK;
-                    uint32_t hi[16], lo[16];
+                    uint32_t hi[16], lo[8];
                     ln_normalize_chunk(x[c & 1], mean, rstd, const_s + (H + col0) * 4, const_s + (2 * H + col0) * 4, hi, lo);
                     const uint32_t buf_hi = my_smem, buf_lo = my_smem + CHUNK_BF16;
                     if (lane == 0) tma_store_wait_read<0>();
                     __syncwarp();
                     stage_words_bf16(buf_hi, lane, hi);
-                    if (p.has_lo) stage_words_bf16(buf_lo, lane, lo);
+                    if (p.has_lo) stage_words_lo8(buf_lo, lane, lo);
                     fence_proxy_async_smem();
                     __syncwarp();
                     if (lane == 0) {
@@ -458,12 +455,12 @@ cudaError_t launch_ffn(const FfnFusedArgs& a, cudaStream_t stream, int num_sms) 
     if (!make_tmap(&tw2, a.w2, H, a.inter, BK, C::UN2 / 2, false, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
     if (!make_tmap(&tr, a.a, a.m, H, CHUNK, 32, false, CU_TENSOR_MAP_SWIZZLE_64B)) return cudaErrorInvalidValue;
     trl = tr;
-    if (a.a_lo && !make_tmap(&trl, a.a_lo, a.m, H, CHUNK, 32, false, CU_TENSOR_MAP_SWIZZLE_64B)) return cudaErrorInvalidValue;
+    if (a.a_lo && !make_tmap_lo8(&trl, a.a_lo, a.m, H, CHUNK, 32)) return cudaErrorInvalidValue;
     tlp = ta;
-    if (a.a_lo && !make_tmap(&tlp, a.a_lo, a.m, H, BK, BM, false, CU_TENSOR_MAP_SWIZZLE_128B)) return cudaErrorInvalidValue;
+    if (a.a_lo && !make_tmap_es(&tlp, a.a_lo, a.m, H, BK, BM, 1, CU_TENSOR_MAP_SWIZZLE_NONE)) return cudaErrorInvalidValue;  // L2 prefetch only
     if (!make_tmap(&tc, a.out, a.m, H, CHUNK, 32, false, CU_TENSOR_MAP_SWIZZLE_64B)) return cudaErrorInvalidValue;
     tcl = tc;
-    if (a.out_lo && !make_tmap(&tcl, a.out_lo, a.m, H, CHUNK, 32, false, CU_TENSOR_MAP_SWIZZLE_64B)) return cudaErrorInvalidValue;
+    if (a.out_lo && !make_tmap_lo8(&tcl, a.out_lo, a.m, H, CHUNK, 32)) return cudaErrorInvalidValue;
     auto kern = ffn_fused_kernel<H>;
     static PerDeviceOnce attr_set;  // function attributes belong to a (function, device) pair
     if (!attr_set.done()) {

@@ -332,7 +332,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             ++st_it;
         };
 
-        // residual ring (EPI_RES_LN): stage s of this warp = my_smem + s * 4 KB: [hi 2 KB][lo 2 KB]. Chunks are numbered
+        // residual ring (EPI_RES_LN): stage s of this warp = my_smem + s * 4 KB: [hi 2 KB][lo 1 KB, e5m2 bytes, then 1 KB unused]. Chunks are numbered
         // g = tile * NCH + c over the CTA's whole tile sequence and loaded RING chunks ahead of their use.
         uint32_t ld_used = 0;
         auto issue_residual = [&](uint32_t g) {
@@ -343,7 +343,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 const uint32_t bar = bar_res + 8 * (RING * ew + s);
                 const uint32_t dst = my_smem + s * (2 * CHUNK_BF16);
                 const int col0 = n_tile * BLOCK_N + half * HALF_N + c * CHUNK, row0 = m_tile * BLOCK_M + quad * 32;
-                mbar_arrive_expect_tx(bar, p.has_res_lo ? 2 * CHUNK_BF16 : CHUNK_BF16);
+                mbar_arrive_expect_tx(bar, p.has_res_lo ? CHUNK_BF16 + CHUNK_BF16 / 2 : CHUNK_BF16);  // lo: one byte per element
                 tma_load_2d(dst, &tmap_r, col0, row0, bar);
                 if (p.has_res_lo) tma_load_2d(dst + CHUNK_BF16, &tmap_r_lo, col0, row0, bar);
             }
@@ -447,12 +447,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     const uint32_t s = ld_used % RING;
                     mbar_wait(bar_res + 8 * (RING * ew + s), (ld_used / RING) & 1);
                     const uint32_t rbuf = my_smem + s * (2 * CHUNK_BF16) + lane * 64;
-                    uint32_t hi_addr[4], lo_addr[4];
+                    uint32_t hi_addr[4], lo_addr[2];
 #pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        hi_addr[q] = rbuf + ((q ^ ((lane >> 1) & 3)) << 4);
-                        lo_addr[q] = hi_addr[q] + CHUNK_BF16;
-                    }
+                    for (int q = 0; q < 4; ++q) hi_addr[q] = rbuf + ((q ^ ((lane >> 1) & 3)) << 4);
+                    lo8_piece_addrs(my_smem + s * (2 * CHUNK_BF16) + CHUNK_BF16, lane, lo_addr);
                     tmem_ld_wait();
                     ln_accumulate_chunk(v, ln_const + (lcol + c * CHUNK) * 4, hi_addr, lo_addr, p.has_res_lo != 0, sum2, sq2);
                     __syncwarp();  // every lane has read this ring stage: refill it with the chunk RING ahead
@@ -515,7 +513,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 // pass 2: normalise, scale, shift, store (hi, lo)
                 auto pass2_chunk = [&](int c, const uint32_t (&x)[32]) {
                     const int col0 = col_base + c * CHUNK;
-                    uint32_t hi[16], lo[16];
+                    uint32_t hi[16], lo[8];
                     ln_normalize_chunk(x, mean, rstd, ln_const + (BLOCK_N + lcol + c * CHUNK) * 4,
                                        ln_const + (2 * BLOCK_N + lcol + c * CHUNK) * 4, hi, lo);
                     if (p.dbg & 1) return;
@@ -524,7 +522,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     stage_end(&tmap_c, buf, col0, row0);
                     if (p.has_out_lo) {
                         buf = stage_begin();
-                        stage_words_bf16(buf, lane, lo);
+                        stage_words_lo8(buf, lane, lo);
                         stage_end(&tmap_c_lo, buf, col0, row0);
                     }
                 };
@@ -613,12 +611,12 @@ cudaError_t launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms) {
     const CUtensorMapSwizzle csw = OUT_F32 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
     if (!make_tmap(&tc, a.out, a.m, a.n, CHUNK, 32, OUT_F32, csw)) return cudaErrorInvalidValue;
     tcl = tc; tr = tc; trl = tc;
-    if (a.out_lo && !make_tmap(&tcl, a.out_lo, a.m, a.n, CHUNK, 32, false, csw)) return cudaErrorInvalidValue;
+    if (a.out_lo && !make_tmap_lo8(&tcl, a.out_lo, a.m, a.n, CHUNK, 32)) return cudaErrorInvalidValue;
     if (EPI == EPI_RES_LN) {
         if (!a.residual) return cudaErrorInvalidValue;
         if (!make_tmap(&tr, a.residual, a.m, a.n, CHUNK, 32, false, csw)) return cudaErrorInvalidValue;
         trl = tr;
-        if (a.residual_lo && !make_tmap(&trl, a.residual_lo, a.m, a.n, CHUNK, 32, false, csw))
+        if (a.residual_lo && !make_tmap_lo8(&trl, a.residual_lo, a.m, a.n, CHUNK, 32))
             return cudaErrorInvalidValue;
     }
     auto kern = gemm_tc_kernel<BLOCK_N, EPI, OutT, CL, PAIR, RING>;

@@ -21,12 +21,12 @@ struct GemmTcArgs {
     const int* d_rows;     // optional device int: rows actually present (<= m); tiles beyond are skipped
     const float* bias;     // [n]
     const void* residual;  // [m, n] 16-bit (EPI_RES_LN), high half of the residual stream
-    const void* residual_lo;  // [m, n] 16-bit low half (residual = hi + lo), or nullptr
+    const void* residual_lo;  // [m, n] bytes: low half (residual = hi + lo, lo an e5m2 byte per element), or nullptr
     const float* gamma;    // [n]     (EPI_RES_LN)
     const float* beta;     // [n]     (EPI_RES_LN)
     float eps;
     void* out;             // [m, n] 16-bit, or fp32 when out_f32
-    void* out_lo;          // EPI_RES_LN: optional [m, n] 16-bit low half of the output
+    void* out_lo;          // EPI_RES_LN: optional [m, n] bytes, low half of the output
     int out_f32;           // only with EPI_BIAS
     int epi;               // GemmEpilogue
     int pair;              // plain bf16 epilogues: 1 = clusters of 2 CTAs on adjacent row blocks, one cta_group::2 MMA per pair

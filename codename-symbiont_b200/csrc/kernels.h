@@ -20,14 +20,14 @@ struct EmbedArgs {
     float eps;
     int H, vocab, type_vocab, max_pos;
     void* out;                 // packed [tokens, H] in T
-    void* out_lo;              // 16-bit mode: low half of the (hi, lo) pair, or nullptr
+    void* out_lo;              // 16-bit mode: low half of the (hi, lo) pair (one e5m2 byte per element), or nullptr
     int* status;               // |= 2 on id / type id / position out of range
 };
 
 // K2f (ffn_fused.cu): x' = LayerNorm(gelu(a.W1^T + b1).W2^T + b2 + a) in one kernel; hidden 128 / 256 / 384, erf-GELU.
 struct FfnFusedArgs {
     const void* a;       // [m, hidden] 16-bit: GEMM operand and high half of the residual
-    const void* a_lo;    // [m, hidden] 16-bit low half of the residual, or nullptr
+    const void* a_lo;    // [m, hidden] bytes: low half of the residual (e5m2), or nullptr
     const void* w1;      // [inter, hidden] 16-bit (intermediate.dense.weight)
     const void* w2;      // [hidden, inter] 16-bit (output.dense.weight)
     const float *b1, *b2, *gamma, *beta;
@@ -35,7 +35,7 @@ struct FfnFusedArgs {
     int m, hidden, inter;
     const int* d_rows;   // optional device-side row count
     void* out;           // [m, hidden] 16-bit (hi)
-    void* out_lo;        // [m, hidden] 16-bit (lo) or nullptr
+    void* out_lo;        // [m, hidden] bytes (lo) or nullptr
 };
 
 // Everything below exists once per operand format; T = __nv_bfloat16 stands for "16-bit operand of this namespace".
@@ -46,11 +46,11 @@ struct FfnFusedArgs {
     template <typename T>                                                                                               \
     cudaError_t launch_embed_layernorm(const EmbedArgs& a, cudaStream_t s);                                             \
     template <typename TY, typename T>                                                                                  \
-    cudaError_t launch_add_layernorm(const TY* y, const T* residual, const T* residual_lo, int rows_cap,                \
+    cudaError_t launch_add_layernorm(const TY* y, const T* residual, const uint8_t* residual_lo, int rows_cap,          \
                                      const int* d_rows, const float* gamma, const float* beta, float eps, int H,        \
-                                     T* out, T* out_lo, cudaStream_t s);                                                \
+                                     T* out, uint8_t* out_lo, cudaStream_t s);                                          \
     template <typename T>                                                                                               \
-    cudaError_t launch_mean_pool(const T* hidden, const T* hidden_lo, const int* cu, int batch, int H, int normalize,   \
+    cudaError_t launch_mean_pool(const T* hidden, const uint8_t* hidden_lo, const int* cu, int batch, int H, int normalize, \
                                  float* out, cudaStream_t s);                                                           \
     /* K3 on tcgen05 (attention_tc.cu): varlen flash attention over packed qkv [tokens, 3H]; head_dim 32 or 64; qkv    \
        has rows_cap rows (TMA bound), persistent grid. */                                                               \

@@ -128,25 +128,30 @@ __device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
 
 // ---- residual + LayerNorm epilogue arithmetic on one 32-column chunk of this thread's row (packed fp32 pairs) ----
 // Pass 1: x = acc + bias + residual_hi (+ residual_lo), accumulated into (sum, sum of squares) pairs; x replaces acc
-// in v. bias_s: shared address of the chunk's 32 bias floats; hi_addr / lo_addr: shared addresses of the four 16-byte
-// pieces (8 bf16 each) of this thread's row of the residual chunk, whatever layout they sit in.
+// in v. bias_s: shared address of the chunk's 32 bias floats; hi_addr: shared addresses of the four 16-byte pieces (8
+// 16-bit values each) of this thread's row of the residual chunk, lo_addr: of the two 16-byte pieces (16 e5m2 bytes each)
+// of its low halves, whatever layout they sit in.
 __device__ __forceinline__ void ln_accumulate_chunk(uint32_t (&v)[32], uint32_t bias_s, const uint32_t (&hi_addr)[4],
-                                                    const uint32_t (&lo_addr)[4], bool has_lo, uint64_t& sum2,
+                                                    const uint32_t (&lo_addr)[2], bool has_lo, uint64_t& sum2,
                                                     uint64_t& sq2) {
+    uint32_t lw[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // four low halves per word
+    if (has_lo) {
+        const uint4 l0 = lds_v4(lo_addr[0]), l1 = lds_v4(lo_addr[1]);
+        lw[0] = l0.x; lw[1] = l0.y; lw[2] = l0.z; lw[3] = l0.w;
+        lw[4] = l1.x; lw[5] = l1.y; lw[6] = l1.z; lw[7] = l1.w;
+    }
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
         const uint4 r = lds_v4(hi_addr[q]);
-        uint4 l = make_uint4(0, 0, 0, 0);
-        if (has_lo) l = lds_v4(lo_addr[q]);
         const uint4 b0 = lds_v4(bias_s + q * 32), b1 = lds_v4(bias_s + q * 32 + 16);
-        const uint32_t rw[4] = {r.x, r.y, r.z, r.w}, lw[4] = {l.x, l.y, l.z, l.w};
+        const uint32_t rw[4] = {r.x, r.y, r.z, r.w};
         const uint32_t bw[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             uint64_t x = add2(pk2(__uint_as_float(v[q * 8 + 2 * j]), __uint_as_float(v[q * 8 + 2 * j + 1])),
                               pk2(__uint_as_float(bw[2 * j]), __uint_as_float(bw[2 * j + 1])));
             { const float2 f = unpack_op2(rw[j]); x = add2(x, pk2(f.x, f.y)); }
-            if (has_lo) { const float2 f = unpack_op2(lw[j]); x = add2(x, pk2(f.x, f.y)); }
+            if (has_lo) { const float2 f = unpack_lo8x2(lw[2 * q + (j >> 1)] >> ((j & 1) * 16)); x = add2(x, pk2(f.x, f.y)); }
             sum2 = add2(sum2, x);
             sq2 = fma2(x, x, sq2);
             float a, b;
@@ -156,15 +161,16 @@ __device__ __forceinline__ void ln_accumulate_chunk(uint32_t (&v)[32], uint32_t 
         }
     }
 }
-// Pass 2: y = (x - mean) * rstd * gamma + beta -> hi = bf16(y) and lo = bf16(y - hi), two values per word.
-// gamma_s / beta_s: shared addresses of the chunk's 32 floats.
+// Pass 2: y = (x - mean) * rstd * gamma + beta -> hi = 16-bit(y), two values per word, and lo = e5m2(y - hi), four per
+// word. gamma_s / beta_s: shared addresses of the chunk's 32 floats.
 __device__ __forceinline__ void ln_normalize_chunk(const uint32_t (&x)[32], float mean, float rstd, uint32_t gamma_s,
-                                                   uint32_t beta_s, uint32_t (&hi)[16], uint32_t (&lo)[16]) {
+                                                   uint32_t beta_s, uint32_t (&hi)[16], uint32_t (&lo)[8]) {
     const uint64_t r2 = pk2(rstd, rstd), nm2 = pk2(-mean * rstd, -mean * rstd), m1 = pk2(-1.0f, -1.0f);
 #pragma unroll
     for (int q = 0; q < 8; ++q) {
         const uint4 g = lds_v4(gamma_s + q * 16), be = lds_v4(beta_s + q * 16);
         const uint32_t gw[4] = {g.x, g.y, g.z, g.w}, bw[4] = {be.x, be.y, be.z, be.w};
+        float d[4];
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
             const uint64_t t = fma2(pk2(__uint_as_float(x[q * 4 + 2 * j]), __uint_as_float(x[q * 4 + 2 * j + 1])), r2, nm2);
@@ -175,9 +181,9 @@ __device__ __forceinline__ void ln_normalize_chunk(const uint32_t (&x)[32], floa
             const uint32_t h = pack_op2(a, b);
             hi[q * 2 + j] = h;
             const float2 hf = unpack_op2(h);
-            upk2(fma2(pk2(hf.x, hf.y), m1, y), a, b);
-            lo[q * 2 + j] = pack_op2(a, b);
+            upk2(fma2(pk2(hf.x, hf.y), m1, y), d[2 * j], d[2 * j + 1]);
         }
+        lo[q] = pack_lo8x4(d[0], d[1], d[2], d[3]);
     }
 }
 // one staged 32 x 32 bf16 chunk (SWIZZLE_64B rows of 64 bytes): this lane's 16 words
@@ -186,6 +192,21 @@ __device__ __forceinline__ void stage_words_bf16(uint32_t buf, int r, const uint
     const int sw = (r >> 1) & 3;
 #pragma unroll
     for (int q = 0; q < 4; ++q) sts_v4(row + ((q ^ sw) << 4), w[q * 4], w[q * 4 + 1], w[q * 4 + 2], w[q * 4 + 3]);
+}
+
+// one staged 32 x 32 chunk of low halves (SWIZZLE_32B rows of 32 bytes; the buffer is 256-byte aligned): this lane's 8 words
+__device__ __forceinline__ void stage_words_lo8(uint32_t buf, int r, const uint32_t (&w)[8]) {
+    const uint32_t row = buf + r * 32;
+    const int sw = (r >> 2) & 1;
+#pragma unroll
+    for (int q = 0; q < 2; ++q) sts_v4(row + ((q ^ sw) << 4), w[q * 4], w[q * 4 + 1], w[q * 4 + 2], w[q * 4 + 3]);
+}
+// shared addresses of this lane's two 16-byte pieces of such a chunk
+__device__ __forceinline__ void lo8_piece_addrs(uint32_t buf, int r, uint32_t (&addr)[2]) {
+    const uint32_t row = buf + r * 32;
+    const int sw = (r >> 2) & 1;
+    addr[0] = row + (sw << 4);
+    addr[1] = row + ((1 ^ sw) << 4);
 }
 
 // ---- attention operand descriptors (attention_tc.cu, qkv_attention.cu) ----
@@ -245,20 +266,28 @@ PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
     return fn;
 }
 
-// Row-major [rows, cols] matrix of 2- or 4-byte elements; box = box_cols x box_rows.
-bool make_tmap(CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t cols, uint32_t box_cols, uint32_t box_rows,
-               bool f32, CUtensorMapSwizzle swizzle) {
+// Row-major [rows, cols] matrix of es-byte elements (1: bytes, 2: 16-bit operands, 4: fp32); box = box_cols x box_rows.
+bool make_tmap_es(CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t cols, uint32_t box_cols, uint32_t box_rows,
+                  int es, CUtensorMapSwizzle swizzle) {
     auto fn = get_encode_fn();
     if (!fn) return false;
-    const uint64_t es = f32 ? 4 : 2;
     cuuint64_t dims[2] = {cols, rows};
-    cuuint64_t strides[1] = {cols * es};
+    cuuint64_t strides[1] = {cols * static_cast<uint64_t>(es)};
     cuuint32_t box[2] = {box_cols, box_rows};
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = fn(map, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
-                    const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle,
+    const CUtensorMapDataType dt = es == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
+                                           : (es == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_UINT8);
+    CUresult r = fn(map, dt, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle,
                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     return r == CUDA_SUCCESS;
+}
+bool make_tmap(CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t cols, uint32_t box_cols, uint32_t box_rows,
+               bool f32, CUtensorMapSwizzle swizzle) {
+    return make_tmap_es(map, ptr, rows, cols, box_cols, box_rows, f32 ? 4 : 2, swizzle);
+}
+// the low halves of a [rows, cols] activation: one byte per element, boxes of 32 x 32 bytes, SWIZZLE_32B
+bool make_tmap_lo8(CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t cols, uint32_t box_cols, uint32_t box_rows) {
+    return make_tmap_es(map, ptr, rows, cols, box_cols, box_rows, 1, CU_TENSOR_MAP_SWIZZLE_32B);
 }
 
 }  // namespace

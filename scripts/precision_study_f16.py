@@ -15,6 +15,12 @@ def rnd(x, fmt):
         hi = x.bfloat16().float(); return hi + (x - hi).bfloat16().float()
     if fmt == "f16x2":
         hi = x.half().float(); return hi + (x - hi).half().float()
+    if fmt == "f16+e5m2":  # fp16 hi, the remainder as an 8-bit e5m2 float
+        hi = x.half().float(); return hi + (x - hi).to(torch.float8_e5m2).float()
+    if fmt == "bf16+e5m2":
+        hi = x.bfloat16().float(); return hi + (x - hi).to(torch.float8_e5m2).float()
+    if fmt == "f16+e4m3s":  # remainder scaled by 2^12 into e4m3
+        hi = x.half().float(); return hi + ((x - hi) * 4096).to(torch.float8_e4m3fn).float() / 4096
     raise ValueError(fmt)
 
 def forward(shape, w, ids, mask, tt, op, resid, final=None):
@@ -70,7 +76,7 @@ def main():
         cos = ((got * ref).sum(1) / np.linalg.norm(got, axis=1) / np.linalg.norm(ref, axis=1)).min()
         err = np.abs(got - ref)
         print(f"{name:52s} cos {cos:.7f} max-abs {err.max():.2e} | by len " + " ".join(f"{n}:{err[i].max():.1e}" for i, n in enumerate(lengths)))
-main()
+if len(sys.argv) <= 2: main()
 
 def variants():
     """which LayerNorm outputs need the low half when the operands are fp16"""
@@ -115,6 +121,9 @@ def variants():
                        ("f16 op; x f16,   a f16,   final f32", ("f16", "f16", "f16", "f32")),
                        ("f16 op; x f16x2, a f16,   final f16x2", ("f16", "f16x2", "f16", "f16x2")),
                        ("f16 op; x f16,   a f16x2, final f16x2", ("f16", "f16", "f16x2", "f16x2")),
+                       ("f16 op; x, a, final f16+e5m2", ("f16", "f16+e5m2", "f16+e5m2", "f16+e5m2")),
+                       ("f16 op; x, a, final f16+e4m3s", ("f16", "f16+e4m3s", "f16+e4m3s", "f16+e4m3s")),
+                       ("bf16 op; x, a, final bf16+e5m2", ("bf16", "bf16+e5m2", "bf16+e5m2", "bf16+e5m2")),
                        ("bf16 op; x bf16x2, a bf16x2 [r1]", ("bf16", "bf16x2", "bf16x2", "bf16x2"))]:
         got = run(*args)
         err = np.abs(got - ref).max(1)

@@ -31,6 +31,32 @@ def round16(a, fmt):
     return torch.from_numpy(np.array(a, dtype=np.float32, copy=True)).to(T16[fmt]).float().numpy()
 
 
+LO8 = torch.float8_e5m2  # the low half of a (hi, lo) activation: one e5m2 byte per element (csrc/common.cuh)
+
+
+def dev_lo8(a):
+    """fp32 remainders (x - hi) as the library's low-half bytes"""
+    return dev(a, LO8)
+
+
+def nan_lo8(shape):
+    """a low-half output buffer filled with NaN bytes (0x7f), so that unwritten elements show"""
+    return torch.full(shape, 0x7F, dtype=torch.uint8, device="cuda").view(LO8)
+
+
+def split_lo8(x, fmt):
+    """an fp32 array as a (hi, lo) pair in operand format fmt: (hi + lo as the library reads it back, hi as a device
+    tensor, the low-half bytes as a device tensor). hi must be uploaded as it is: rounding hi + lo to 16 bits again can
+    land on the neighbour when lo is exactly half an ulp."""
+    hi = round16(x, fmt)
+    lo = torch.from_numpy(np.ascontiguousarray(x - hi)).to(LO8)
+    return hi + lo.float().numpy(), dev(hi, T16[fmt]), lo.cuda().contiguous()
+
+
+# what hi + lo can be off by, relative to |y|: lo keeps 3 significant bits of a remainder of at most half an ulp of hi
+LO8_REL = {"f16": 2.0 ** -14, "bf16": 2.0 ** -11}
+
+
 def host(t):
     torch.cuda.synchronize()
     return t.float().cpu().numpy()
