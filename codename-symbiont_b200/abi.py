@@ -580,6 +580,8 @@ class Embedder:
         return {n: {"total_ms": arr[i].total_ms, "launches": int(arr[i].launches)} for i, n in enumerate(KIND_NAMES)}
 
     # -- single kernels (device pointers) -------------------------------------------------------
+    # every *_lo argument is the low half of a (hi, lo) activation: rows x H BYTES, one e5m2 float per element
+    # (torch.float8_e5m2 has the same encoding); 0 = none
     def op_embed_layernorm(self, d_ids, d_tt, d_cu, batch, total, dtype, d_out, d_out_lo=0, stream=0):
         _check(self.lib.b200_op_embed_layernorm(self.h, d_ids, d_tt, d_cu, batch, total, dtype, d_out, d_out_lo or None,
                                                 stream or None))

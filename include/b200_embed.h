@@ -181,10 +181,11 @@ int32_t b200_embed_profile_read(b200_embed* h, b200_embed_kind_stats* out /* [B2
  * 0 = 16-bit activations in the handle's operand format / tensor-core GEMM, 1 = fp32 validation kernels. Row counts are
  * tokens. */
 
-/* Residual-stream tensors in the 16-bit mode are (hi, lo) pairs of [rows, H] arrays in the operand format: hi =
- * round16(v) is what the next GEMM multiplies, hi + lo is what residual adds and the pooling read. Every `*_lo`
- * argument may be NULL (plain 16-bit) and is ignored when dtype = 1. ("bf16" in the comments below means "the handle's
- * 16-bit operand format".) */
+/* Residual-stream tensors in the 16-bit mode are (hi, lo) pairs of [rows, H] arrays: hi = round16(v), in the operand
+ * format, is what the next GEMM multiplies; lo = v - hi as ONE BYTE per element (an e5m2 float: fp16's exponent range,
+ * 2 mantissa bits, round to nearest even, saturating), so hi + lo is what residual adds and the pooling read at 3 bytes
+ * per element. Every `*_lo` argument points to rows x H bytes, may be NULL (plain 16-bit) and is ignored when dtype = 1.
+ * ("bf16" in the comments below means "the handle's 16-bit operand format".) */
 
 /* K1. out[t,:] = LN(word[ids[t]] + type[tt[t]] + pos[position of t]) for the packed tokens of
  * `batch` sentences; cu_seqlens int32[batch+1] on device. (bert.rs BertEmbeddings::forward) */
@@ -198,7 +199,7 @@ int32_t b200_op_linear(b200_embed* h, int32_t layer, int32_t which, const void* 
                        const void* residual_lo, int32_t rows, int32_t dtype, void* y, void* y_lo, void* stream);
 /* K2f. y = LayerNorm(gelu(x . Wi^T + bi) . Wo^T + bo + x) with the feed-forward weights of `layer`, in one kernel
  * (bf16 tensor cores; hidden size 128 / 256 / 384 with erf-GELU, else B200_EMBED_ERR_UNSUPPORTED_SHAPE).
- * x / x_lo and y / y_lo are (hi, lo) bf16 pairs as above. (bert.rs BertIntermediate::forward + BertOutput::forward) */
+ * x / x_lo and y / y_lo are (hi, lo) pairs as above. (bert.rs BertIntermediate::forward + BertOutput::forward) */
 int32_t b200_op_ffn(b200_embed* h, int32_t layer, const void* x, const void* x_lo, int32_t rows, void* y, void* y_lo,
                     void* stream);
 
