@@ -223,8 +223,13 @@ __global__ void pack_tiles_kernel(const int* cu, int batch, int cap, int* __rest
 // the row is written packed at cu[b] + j. Packed: slots are tokens, sentence found by binary search in cu.
 // The work per token is a chain of dependent loads (bounds -> id -> three table rows) followed by a short reduction:
 // all TOK tokens' loads are issued before any of them is consumed, which is what keeps enough bytes in flight.
+// five blocks per SM (51 registers; the 54 the compiler takes on its own allow four): 0.374 -> 0.337 ms at c2, six and
+// eight blocks spill a little and give 0.345
+#ifndef EMBED_MIN_BLOCKS
+#define EMBED_MIN_BLOCKS 5
+#endif
 template <typename T, bool PADDED, int TOK, int NCH>  // NCH: 128-column chunks a token needs (H <= 128 NCH)
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, EMBED_MIN_BLOCKS)
 embed_layernorm_kernel(const uint32_t* __restrict__ ids, const uint32_t* __restrict__ type_ids,
                        const int* __restrict__ cu, int batch, int seq_len, int total_tokens,
                        const float* __restrict__ word, const float* __restrict__ pos,

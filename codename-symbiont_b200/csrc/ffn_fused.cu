@@ -116,18 +116,12 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     float2* ln_part = reinterpret_cast<float2*>(aux_ptr + 1024);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    int rows = p.m;
-    if (p.d_rows != nullptr) {
-        const int r = *p.d_rows;
-        rows = r < rows ? r : rows;
-    }
-    const int num_tiles = (rows + BM - 1) / BM;
+    pdl_trigger();
     const int NC = p.inter / IC;  // chunks per tile
     // Pair `pr` owns row tiles 2 pr (leader) and 2 pr + 1 (peer). With an odd tile count the last peer tile is out of
     // range: its loads are zero-filled and its stores clipped, and it keeps its side of every handshake.
     const uint32_t crank = cluster_ctarank();
     const bool leader = crank == 0;
-    const int num_pairs = (num_tiles + 1) / 2;
     const int pair0 = static_cast<int>(blockIdx.x) / 2, pair_step = static_cast<int>(gridDim.x) / 2;
     // "full" barriers and the barriers the MMA thread waits on live in the leader CTA
     const uint32_t l_a_full = map_to_cta(bar_a_full, 0), l_w1_full = map_to_cta(bar_w1_full, 0),
@@ -154,6 +148,14 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     cluster_sync_all();  // the peer's barriers exist before anything arrives on them
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot_ptr;
+    pdl_wait();  // nothing above reads or writes global memory; the predecessor's output (and the row count) from here on
+    int rows = p.m;
+    if (p.d_rows != nullptr) {
+        const int r = *p.d_rows;
+        rows = r < rows ? r : rows;
+    }
+    const int num_tiles = (rows + BM - 1) / BM;
+    const int num_pairs = (num_tiles + 1) / 2;
 
     // Both the producer and the MMA thread walk the tensor-pipe schedule of a tile in the same order:
     //   G1(0), [G1(1), G2(0)], [G1(2), G2(1)], ..., [G1(NC-1), G2(NC-2)], G2(NC-1)
@@ -476,13 +478,14 @@ cudaError_t launch_ffn(const FfnFusedArgs& a, cudaStream_t stream, int num_sms) 
     cfg.blockDim = dim3(FF_THREADS);
     cfg.dynamicSmemBytes = C::BYTES;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
+    pdl_attribute(&attr[1]);
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = 2;
     static PerDeviceValue max_pairs_dev;  // CTA pairs the device holds at once
     int max_pairs = max_pairs_dev.get();
     if (max_pairs == 0) {

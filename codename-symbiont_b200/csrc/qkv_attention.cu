@@ -155,6 +155,7 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
     volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + C::OFF_AUX + 256);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    pdl_trigger();
 
     if (threadIdx.x == 0) {
         prefetch_tmap(&tmap_x);
@@ -178,12 +179,13 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
     }
     if (warp == 2) tmem_alloc(tmem_slot, 512);
     const uint32_t smem_bias = base + C::OFF_BIAS;
-    for (int i = threadIdx.x; i < 3 * H; i += QA_THREADS)
+    for (int i = threadIdx.x; i < 3 * H; i += QA_THREADS)  // (weights: written at create time, not by the predecessor)
         asm volatile("st.shared.f32 [%0], %1;" ::"r"(smem_bias + i * 4), "f"(__ldg(p.bias + i)) : "memory");
     tc_fence_before_sync();
     __syncthreads();
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot_ptr;
+    pdl_wait();  // the tile list, cu and x of the predecessor kernels from here on
 
     // The roles split the register file: 640 threads start with 96 registers each; the control warps and the output
     // warps hand registers to the two softmax groups (a whole warpgroup executes the same setmaxnreg).
@@ -668,8 +670,7 @@ cudaError_t launch_qa(const __nv_bfloat16* x, const __nv_bfloat16* wqkv, const f
     p.scale_log2 = 1.4426950408889634f / sqrtf(static_cast<float>(D));
     const int grid = batch < num_sms ? batch : num_sms;
     if (grid <= 0) return cudaSuccess;
-    kern<<<grid, QA_THREADS, C::BYTES, s>>>(tx, tw, p);
-    return cudaGetLastError();
+    return launch_pdl(kern, dim3(grid), dim3(QA_THREADS), C::BYTES, s, tx, tw, p);
 }
 
 }  // namespace
