@@ -142,7 +142,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     constexpr bool UNIFORM = PAIR;
     constexpr int CSIZE = CL > 1 ? CL : (PAIR ? 2 : 1);        // CTAs per cluster
     constexpr uint16_t CMASK = static_cast<uint16_t>((1u << CSIZE) - 1);
-    constexpr int A_SLICE_ROWS = BLOCK_M / (CL > 1 ? CL : 1);  // rows of the A tile this CTA loads (and multicasts)
+    // rows of the A tile this CTA loads (and multicasts); a cluster of 3 splits the tile between its first two CTAs
+    constexpr int A_LOADERS = CL == 3 ? 2 : (CL > 1 ? CL : 1);
+    constexpr int A_SLICE_ROWS = BLOCK_M / A_LOADERS;
     constexpr int B_SLICE_ROWS = BLOCK_N / (PAIR ? 2 : 1);     // rows of the W tile this CTA loads
 
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -242,10 +244,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                                         leader_full + 8 * stage);
                     } else {
                         mbar_arrive_expect_tx(bar_full + 8 * stage, A_STAGE_BYTES + B_STAGE_BYTES);
-                        if constexpr (CL > 1)  // my slice of the A tile, delivered to every CTA of the cluster
-                            tma_load_2d_multicast(sa + crank * (A_SLICE_ROWS * BLOCK_K * 2), &tmap_a, kb * BLOCK_K,
-                                                  m_tile * BLOCK_M + crank * A_SLICE_ROWS, bar_full + 8 * stage, CMASK);
-                        else
+                        if constexpr (CL > 1) {  // my slice of the A tile, delivered to every CTA of the cluster
+                            if (crank < A_LOADERS)
+                                tma_load_2d_multicast(sa + crank * (A_SLICE_ROWS * BLOCK_K * 2), &tmap_a, kb * BLOCK_K,
+                                                      m_tile * BLOCK_M + crank * A_SLICE_ROWS, bar_full + 8 * stage, CMASK);
+                        } else
                             tma_load_2d(sa, &tmap_a, kb * BLOCK_K, m_tile * BLOCK_M, bar_full + 8 * stage);
                         tma_load_2d(sb, &tmap_b, kb * BLOCK_K, n_tile * BLOCK_N, bar_full + 8 * stage);
                     }
@@ -604,7 +607,7 @@ cudaError_t launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms) {
         // cover this GPU's memory alone: every byte of the operand is checked, not only its first one.
         if (!operand_is_local_device_memory(a.a, static_cast<size_t>(a.m) * a.k * 2)) return cudaErrorInvalidDevicePointer;
     }
-    if (!make_tmap(&ta, a.a, a.m, a.k, BLOCK_K, BLOCK_M / (CL > 1 ? CL : 1), false, CU_TENSOR_MAP_SWIZZLE_128B))
+    if (!make_tmap(&ta, a.a, a.m, a.k, BLOCK_K, BLOCK_M / (CL == 3 ? 2 : (CL > 1 ? CL : 1)), false, CU_TENSOR_MAP_SWIZZLE_128B))
         return cudaErrorInvalidValue;
     if (!make_tmap(&tb, a.b, a.n, a.k, BLOCK_K, BLOCK_N / (PAIR ? 2 : 1), false, CU_TENSOR_MAP_SWIZZLE_128B))
         return cudaErrorInvalidValue;
@@ -697,6 +700,9 @@ cudaError_t gemm_tc_launch(const GemmTcArgs& a, cudaStream_t stream, int num_sms
     // TMA needs 16-byte row pitches: k % 8 (bf16 operands) and n % 8 (bf16 output rows)
     if (a.k % 8 != 0 || a.n % a.block_n != 0) return cudaErrorInvalidValue;
     if (a.epi == EPI_RES_LN) {  // a CTA, or a cluster of 2 / 4 CTAs, owns whole rows
+        // N = 768 with a long K (BERT-base FFN2): 3 x 256 columns instead of 4 x 192 (experiment, B200_EMBED_LN_CL3=1)
+        static const bool cl3 = getenv("B200_EMBED_LN_CL3") != nullptr;
+        if (cl3 && a.n == 768 && a.k >= 1536) return launch<256, EPI_RES_LN, __nv_bfloat16, 3, false, 1>(a, stream, num_sms);
         const int cl = a.n / a.block_n;
         if (a.block_n == 128 && cl == 1) return launch<128, EPI_RES_LN, __nv_bfloat16, 1>(a, stream, num_sms);
         if (a.block_n == 256 && cl == 1) return launch<256, EPI_RES_LN, __nv_bfloat16, 1>(a, stream, num_sms);
