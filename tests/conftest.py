@@ -61,4 +61,5 @@ BF16_SHORT_ABS = 5e-3      # (b) for sentences of fewer than 8 tokens (little to
 F16_DEEP_SHORT_ABS = 2.5e-3
 BF16_DEEP_RAW_ABS = 2.5e-2
 # two schedules (fused / unfused kernels, different batch compositions) of the same 16-bit math against each other
-CROSS_SCHEDULE_ABS = {"bf16": 4e-3, "f16": 1e-3}
+# (scripts/fuzz_parity.py over 4500 random calls: worst 4.2e-3 in bf16, 5.8e-4 in fp16)
+CROSS_SCHEDULE_ABS = {"bf16": 5e-3, "f16": 1e-3}
