@@ -9,13 +9,16 @@
 //   warp 0     TMA producer: Q tile once per item, K and V tiles per 128-key block (2-stage rings), straight from
 //              the packed qkv [tokens, 3H] activations (box D x 128 rows; D*2-byte swizzle)
 //   warp 1     one thread issues tcgen05.mma: S_u = Q.K_u^T (128 x 64, fp32 in TMEM, double-buffered) one unit
-//              ahead of the softmax, then O_u = P_u.V_u (128 x D, double-buffered) as soon as P_u is written
+//              ahead of the softmax, then O += P_u.V_u (128 x D, one accumulator per item, two items' worth) as soon
+//              as P_u is written
 //   warp 2     TMEM allocator (2 x 64 S + 2 x D O + 2 x 32 P columns: 256 for d = 32, 512 for d = 64)
 //   warps 4-7  softmax: thread r owns query row r (= TMEM lane r). One tcgen05.ld brings the unit's 64 scores
 //              into registers (read once: row max, p = exp2(s*scale - max) and the row sum all work from there),
-//              P goes as 16-bit pairs into tensor memory (the A operand of the second MMA is read there), and the
-//              previous unit's O_u is folded into the running output while this unit's P.V runs. Running max /
-//              sum / output live in registers (online softmax, fp32).
+//              P goes as 16-bit pairs into tensor memory (the A operand of the second MMA is read there). The units of an
+//              item accumulate in one tensor-memory accumulator: a unit's exponentials use the maximum the row had
+//              before it unless the new one is more than 2^8 above (then the accumulator is rescaled in place), so
+//              there is no per-unit read-back of O; running max / sum live in registers (fp32), the item's rows are
+//              written out during the next item's first unit.
 // Keys past the sentence end get p = 0, which is exactly what the reference's additive f32::MIN mask yields.
 // Rows of the 128-row tiles that lie past the sentence end belong to the next sentence (or are zero-filled
 // by TMA past the last token); they are computed and never stored.
@@ -183,7 +186,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
             Walk w;
             bool valid;        // points at a unit
             int nunits, u;     // units of the current item, current unit (keys [u*64, u*64+64): block u/2, half u&1)
-            uint32_t q_it, kv_it;  // ring positions of the current item's Q tile and first K/V block
+            uint32_t q_it, kv_it;  // ring positions of the current item's Q tile and first K/V block; q_it is also the
+                                   // item's number in this CTA's stream (O buffer q_it & 1)
         };
         auto advance = [&](Cursor& c) {
             if (c.valid && c.u + 1 < c.nunits) { ++c.u; return true; }
@@ -219,17 +223,19 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
             ++us;
         };
         auto issue_pv = [&](const Cursor& c) {
-            const uint32_t kvi = c.kv_it + (c.u >> 1), s = kvi & 1, ob = uo & 1;
-            mbar_wait(bar_p_full + 8 * ob, (uo >> 1) & 1);         // P_u is in tensor memory
-            mbar_wait(bar_o_empty + 8 * ob, ((uo >> 1) & 1) ^ 1);  // the O buffer has been read
+            const uint32_t kvi = c.kv_it + (c.u >> 1), s = kvi & 1, pb = uo & 1, ob = c.q_it & 1;
+            mbar_wait(bar_p_full + 8 * pb, (uo >> 1) & 1);         // P_u is in tensor memory (and O rescaled if it had to be)
+            // the item's first unit overwrites its O buffer: the item two back has been finalised out of it
+            if (c.u == 0) mbar_wait(bar_o_empty + 8 * ob, ((c.q_it >> 1) & 1) ^ 1);
             tc_fence_after_sync();
             if (elect_one()) {
-                const uint32_t tp = tmem_base + P_COL + ob * (UNIT / 2);
+                const uint32_t tp = tmem_base + P_COL + pb * (UNIT / 2);
                 const uint64_t dv = dv0 + ((s * 2 * TILE + (c.u & 1) * (UNIT * D * 2)) >> 4);
 #pragma unroll
                 for (int k = 0; k < UNIT / 16; ++k)  // P: 8 columns per 16 keys; V: 16 rows of D*2 B
-                    umma_ts(tmem_base + O_COL + ob * D, tp + 8 * k, dv + ((k * 16 * D * 2) >> 4), idesc_o, k > 0 ? 1u : 0u);
-                umma_commit(bar_o_full + 8 * ob);
+                    umma_ts(tmem_base + O_COL + ob * D, tp + 8 * k, dv + ((k * 16 * D * 2) >> 4), idesc_o,
+                            (c.u > 0 || k > 0) ? 1u : 0u);  // the units of an item accumulate in tensor memory
+                umma_commit(bar_o_full + 8 * pb);  // "P.V of this unit has completed" (P buffer free, O readable)
                 if ((c.u & 1) == 1 || c.u == c.nunits - 1) umma_commit(bar_kv_empty + 8 * s);  // block fully consumed
             }
             __syncwarp();
@@ -249,50 +255,49 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
         const int quad = warp & 3;
         const int row = quad * 32 + lane;  // query row inside the item = TMEM lane
         const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
-        uint32_t uc = 0;  // units processed so far by this CTA (buffer uc & 1, phase (uc >> 1) & 1)
-        float o[D];       // running output of the item being retired
-#pragma unroll
-        for (int j = 0; j < D; ++j) o[j] = 0.f;
+        uint32_t uc = 0;  // units processed so far by this CTA (S / P buffer uc & 1, phase (uc >> 1) & 1)
+        uint32_t ic = 0;  // items started (O buffer ic & 1)
 
-        // The previous unit of the stream, whose P.V is still running while this unit's softmax is computed. It is folded
-        // into the running output afterwards; if it was its item's last unit the item is finalised then - i.e. during
-        // the NEXT item's first unit, so the end of an item never waits for the tensor pipe.
+        // The units of an item accumulate in ONE tensor-memory accumulator (P.V with the accumulate flag), so there is no
+        // running output in registers and nothing to fold in per unit. For that the exponentials of a unit use the
+        // maximum the row had BEFORE it as long as the new maximum is not more than 2^8 above it (p <= 256 then: fine in
+        // 16 bits, the row sum is fp32; softmax is shift-invariant, so this is exact arithmetic, not an approximation).
+        // Only when some row of the warp jumps further the accumulator is rescaled in place - tcgen05.ld, multiply,
+        // tcgen05.st - after the previous unit's P.V has completed.
+        constexpr float LAZY = 8.0f;
+        // The previous item, whose last P.V may still be running: finalised during the next item's first unit.
         struct Pending {
-            bool valid, last;
-            uint32_t ur;   // stream index of the unit
-            float corr;    // rescale of the running output before this unit's O is added
-            float l;       // row sum of the item after this unit
+            bool valid;
+            uint32_t ur, ob;  // stream index of its last unit, its O buffer
+            float l;
             int start, len, qb, h;
-        } pend{false, false, 0, 0.f, 0.f, 0, 0, 0, 0};
-        auto retire_pending = [&]() {
-            const uint32_t ob = pend.ur & 1;
-            mbar_wait(bar_o_full + 8 * ob, (pend.ur >> 1) & 1);
+        } pend{false, 0, 0, 0.f, 0, 0, 0, 0};
+        auto finalise_pending = [&]() {
+            mbar_wait(bar_o_full + 8 * (pend.ur & 1), (pend.ur >> 1) & 1);  // the item's last P.V has completed
             tc_fence_after_sync();
+            // O / l. Each lane owns one row of D 16-bit values (64 or 128 contiguous bytes of ctx): whole 32-byte sectors
+            // straight from registers.
+            const float inv = 1.0f / pend.l;
+            const bool live = pend.qb * BLK + row < pend.len;
+            __nv_bfloat16* dst = p.ctx + static_cast<size_t>(pend.start + pend.qb * BLK + row) * p.H + pend.h * D;
 #pragma unroll
             for (int c = 0; c < D / 32; ++c) {
                 uint32_t v[32];
-                tmem_ld_32x32(t_lane + O_COL + ob * D + c * 32, v);
+                tmem_ld_32x32(t_lane + O_COL + pend.ob * D + c * 32, v);
                 tmem_ld_wait();
+                if (live) {
 #pragma unroll
-                for (int j = 0; j < 32; ++j) o[c * 32 + j] = fmaf(o[c * 32 + j], pend.corr, __uint_as_float(v[j]));
-            }
-            tc_fence_before_sync();
-            mbar_arrive(bar_o_empty + 8 * ob);
-            if (pend.last) {
-                // finalise: O / l. Each lane owns one row of D bf16 (64 or 128 contiguous bytes of ctx): whole 32-byte
-                // sectors straight from registers.
-                const float inv = 1.0f / pend.l;
-                if (pend.qb * BLK + row < pend.len) {
-                    __nv_bfloat16* dst = p.ctx + static_cast<size_t>(pend.start + pend.qb * BLK + row) * p.H + pend.h * D;
-#pragma unroll
-                    for (int q = 0; q < D / 16; ++q) {
+                    for (int q = 0; q < 2; ++q) {
                         uint32_t w[8];
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) w[j] = pack_op2(o[q * 16 + 2 * j] * inv, o[q * 16 + 2 * j + 1] * inv);
-                        stg_v8(dst + q * 16, w);
+                        for (int j = 0; j < 8; ++j)
+                            w[j] = pack_op2(__uint_as_float(v[q * 16 + 2 * j]) * inv, __uint_as_float(v[q * 16 + 2 * j + 1]) * inv);
+                        stg_v8(dst + c * 32 + q * 16, w);
                     }
                 }
             }
+            tc_fence_before_sync();
+            mbar_arrive(bar_o_empty + 8 * pend.ob);
             pend.valid = false;
         };
 
@@ -300,8 +305,9 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
         while (w.i < items) {
             int b, qb, h, start, len;
             if (!take(w, b, qb, h, start, len)) continue;
-            float m = -INFINITY, l = 0.f;  // the first unit's corr is exp2(-inf) = 0: the previous item's output vanishes
+            float m = -INFINITY, l = 0.f;
             const int nunits = (len + UNIT - 1) / UNIT;
+            const uint32_t ob = ic & 1;
             for (int u = 0; u < nunits; ++u, ++uc) {
                 const uint32_t sb = uc & 1;
                 const int nvalid = min(UNIT, len - u * UNIT);  // keys of this unit inside the sentence
@@ -320,14 +326,31 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
                     for (int j = 0; j < UNIT; ++j)
                         if (j >= nvalid) v[j] = 0xff800000u;  // -inf
                 }
-                // four independent chains for the row max (a single 64-deep FMNMX chain is pure latency)
-                const float mx = row_max(v);
-                const float m_new = fmaxf(m, mx * p.scale_log2);
-                const float corr = ex2(m - m_new);
-                m = m_new;
-                // p = exp2(s*scale - m) (packed-pair FMA), rounded to bf16 into the swizzled K-major tile; row sum in
-                // four packed chains
-                const uint64_t sc2 = pk2(p.scale_log2, p.scale_log2), nm2 = pk2(-m_new, -m_new);
+                const float m_new = fmaxf(m, row_max(v) * p.scale_log2);
+                if (u == 0) {
+                    m = m_new;  // every unit has at least one key of the sentence: m is finite from here on
+                } else if (__any_sync(0xffffffffu, m_new > m + LAZY)) {
+                    // rare: rescale this warp's rows of the accumulator (rows that did not jump: factor 1)
+                    const bool jump = m_new > m + LAZY;
+                    const float corr = jump ? ex2(m - m_new) : 1.0f;
+                    if (jump) m = m_new;
+                    l *= corr;
+                    mbar_wait(bar_o_full + 8 * ((uc - 1) & 1), ((uc - 1) >> 1) & 1);  // the previous unit's P.V has completed
+                    tc_fence_after_sync();
+#pragma unroll
+                    for (int c = 0; c < D / 32; ++c) {
+                        uint32_t o[32];
+                        tmem_ld_32x32(t_lane + O_COL + ob * D + c * 32, o);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) o[j] = __float_as_uint(__uint_as_float(o[j]) * corr);
+                        tmem_st_32x32(t_lane + O_COL + ob * D + c * 32, o);
+                    }
+                    tmem_st_wait();
+                    tc_fence_before_sync();
+                }
+                // p = exp2(s*scale - m) (packed-pair FMA), rounded to 16 bits, two keys per word; row sum in four packed chains
+                const uint64_t sc2 = pk2(p.scale_log2, p.scale_log2), nm2 = pk2(-m, -m);
                 uint64_t lb2[4] = {0, 0, 0, 0};
                 uint32_t pw[UNIT / 2];  // this row's probabilities, two keys per word
 #pragma unroll
@@ -341,6 +364,9 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
                         pw[q * 4 + j] = pack_op2(pa, pb);
                     }
                 }
+                // the P buffer was last read by the P.V of the unit two back
+                mbar_wait(bar_o_full + 8 * sb, ((uc >> 1) & 1) ^ 1);
+                tc_fence_after_sync();
                 tmem_st_32x32(t_lane + P_COL + sb * (UNIT / 2), pw);
                 float lb;
                 {
@@ -349,17 +375,18 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
                     upk2(add2(lb2[2], lb2[3]), a2, a3);
                     lb = (a0 + a1) + (a2 + a3);
                 }
+                l += lb;
                 tmem_st_wait();
                 tc_fence_before_sync();
                 mbar_arrive(bar_p_full + 8 * sb);
-                l = fmaf(l, corr, lb);
-                // while P_u . V_u runs, fold the previous unit of the stream in (and finalise its item if it ended there)
-                if (pend.valid) retire_pending();
-                pend.valid = true; pend.last = u == nunits - 1; pend.ur = uc; pend.corr = corr; pend.l = l;
-                pend.start = start; pend.len = len; pend.qb = qb; pend.h = h;
+                // while P_u . V_u runs: the previous item's rows go out
+                if (pend.valid) finalise_pending();
             }
+            pend.valid = true; pend.ur = uc - 1; pend.ob = ob; pend.l = l;
+            pend.start = start; pend.len = len; pend.qb = qb; pend.h = h;
+            ++ic;
         }
-        if (pend.valid) retire_pending();
+        if (pend.valid) finalise_pending();
     }
 
     tc_fence_before_sync();

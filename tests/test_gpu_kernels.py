@@ -238,6 +238,42 @@ def test_k3_attention(env, pkg, dtype, heads, d):
     assert cos_rows(got, want).min() >= (0.999999 if dtype == 1 else 0.9998)
 
 
+@pytest.mark.parametrize("heads,d", [(4, 32), (2, 64)])
+def test_k3_attention_rescales_when_the_row_maximum_jumps(env, pkg, heads, d):
+    """K3 keeps an item's output in one tensor-memory accumulator and lets a unit of 64 keys reuse the row maximum of the
+    units before it unless the new maximum is more than 2^8 above; then the accumulator is rescaled in place. Keys whose
+    scores grow from unit to unit (and keys that jump only for some rows and some heads) take that path in every unit;
+    compared with the oracle's softmax like the plain test."""
+    shape = pkg.weights.BertShape(512, heads * d, 1, heads, 512, 512, 2)
+    lengths = np.array([512, 300, 129, 65, 511, 64, 200])
+    S, H = 512, heads * d
+    rng = np.random.default_rng(23)
+    q, k, v = (rng.standard_normal((len(lengths), S, H)).astype(np.float32) for _ in range(3))
+    # the keys of unit u are scaled by 1 + 0.9 u (scores of later units dominate more and more), one key per unit is an
+    # outlier aligned with a few query rows only, and one head is left alone
+    unit = np.arange(S) // 64
+    k *= (1.0 + 0.9 * unit)[None, :, None]
+    for b in range(len(lengths)):
+        for u in range(1, 8):
+            j = u * 64 + 7 * b % 64
+            rows = rng.integers(0, S, size=9)
+            k[b, j, :H - d] = 3.0 * q[b, rows[0], :H - d]
+    q, k, v = rnd(q), rnd(k), rnd(v)
+    mask = (np.arange(S)[None, :] < lengths[:, None]).astype(np.uint32)
+    with pkg.Embedder.random_init(shape, seed=1, operands=FMT) as e:
+        o = Oracle(shape, e.export_weights(), "f32")
+        want = padded_to_packed(o.attention(q, k, v, mask, heads), lengths)
+        qkv = np.concatenate([padded_to_packed(t, lengths) for t in (q, k, v)], axis=1)
+        dq = dev(qkv, td16)
+        ctx = torch.full(want.shape, float("nan"), dtype=td16, device="cuda")
+        d_cu = dev_i32(cu_of(lengths))
+        e.op_attention(dq.data_ptr(), d_cu.data_ptr(), len(lengths), qkv.shape[0], int(lengths.max()), 0, ctx.data_ptr())
+        got = host(ctx)
+    assert np.isfinite(got).all()
+    assert np.abs(got - want).max() <= 0.03, np.abs(got - want).max()
+    assert cos_rows(got, want).min() >= 0.9998
+
+
 @pytest.mark.parametrize("lens", ["mixed", "tiny"])
 @pytest.mark.parametrize("heads", [4, 8, 12])
 def test_k23_qkv_attention_fused(pkg, built, heads, lens):
