@@ -3,7 +3,7 @@
 #   gpu_profile.sh list                 launch list: device time of every kernel of a short bench run
 #   gpu_profile.sh full [regex] [skip] [count]   ncu --set full of the kernels matching regex
 mkdir -p gpurun_out
-CMD="python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-workloads"
+CMD="python bench.py --workload ${WL:-c2} --steps 2 --warmup 1 --no-cpu-baseline --no-workloads"
 $CMD > gpurun_out/plain.log 2>&1 || { echo "plain run failed"; tail -5 gpurun_out/plain.log; exit 1; }
 if [ "$1" = "list" ]; then
   ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1
