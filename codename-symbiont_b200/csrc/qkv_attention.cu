@@ -62,7 +62,9 @@ constexpr int X_BLK = BLK * BK * 2;
 // Two measured options, both off (same-box A/B at c2, kernel alone: 0.626 ms as shipped): QA_VBUFS = 2 stages a head's V
 // into a second tile so that the next head's Q / K / V are ready before the current head's last P.V has finished, and
 // QA_LOOKAHEAD = 1 then issues the next head's first S ahead of that P.V (0.636 / 0.672 ms: the tensor pipe executes in
-// issue order and the chain a group waits on is not shortened by queueing more behind the projections).
+// issue order and the chain a group waits on is not shortened by queueing more behind the projections). QA_JOINT = 1
+// projects both groups' heads in one N = 192 chain into one accumulator (x read from shared memory once per head pair):
+// 0.655 ms, 13.92 vs 13.77 ms per step.
 #ifndef QA_LOOKAHEAD
 #define QA_LOOKAHEAD 0
 #endif
