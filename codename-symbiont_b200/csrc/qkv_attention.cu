@@ -59,15 +59,12 @@ constexpr int UNIT = 64;           // keys per softmax unit
 constexpr int BK = 64;             // bf16 per 128-byte swizzle row
 constexpr int X_BLK = BLK * BK * 2;
 
-// Two measured options, both off (same-box A/B at c2, kernel alone: 0.626 ms as shipped): QA_VBUFS = 2 stages a head's V
-// into a second tile so that the next head's Q / K / V are ready before the current head's last P.V has finished, and
-// QA_LOOKAHEAD = 1 then issues the next head's first S ahead of that P.V (0.636 / 0.672 ms: the tensor pipe executes in
-// issue order and the chain a group waits on is not shortened by queueing more behind the projections). QA_JOINT = 1
-// projects both groups' heads in one N = 192 chain into one accumulator (x read from shared memory once per head pair):
-// 0.655 ms, 13.92 vs 13.77 ms per step.
-#ifndef QA_LOOKAHEAD
-#define QA_LOOKAHEAD 0
-#endif
+// Measured options, off (same-box A/B at c2, kernel alone: 0.626 ms as shipped): a second V tile per group (QA_VBUFS = 2)
+// so that the next head's Q / K / V are staged before the current head's last P.V has finished: 0.636 ms, and with the next
+// head's first S then issued ahead of that P.V 0.624-0.672 ms (that issue order is no longer in the source): the tensor pipe
+// executes in issue order and the chain a group waits on is not shortened by queueing more behind the projections.
+// QA_JOINT = 1 projects both groups' heads in one N = 192 chain into one accumulator (x read from shared memory once per
+// head pair): 0.655 ms, 13.92 vs 13.77 ms per step.
 #ifndef QA_JOINT
 #define QA_JOINT 0
 #endif
@@ -94,7 +91,12 @@ struct QaCfg {
     static constexpr int OFF_AUX = OFF_T + 2 * G_TILES * T_TILE;
     static constexpr int OFF_BIAS = OFF_AUX + 512;     // bqkv [3H] fp32
     static constexpr int OFF_ROWS = OFF_BIAS + 3 * H * 4;  // per group: corr[128], l[128] of the head being finished
-    static constexpr int BYTES = OFF_ROWS + 2 * 2 * BLK * 4;
+    // score-bias tiles of a packed tile (see the convert warps): [128 rows x 32 columns] 16-bit, Q side and K side, in the
+    // layout of the Q / K tiles (64-byte rows, SWIZZLE_64B)
+    static constexpr int OFF_BIASQ = (OFF_ROWS + 2 * 2 * BLK * 4 + 1023) / 1024 * 1024;
+    static constexpr int OFF_BIASK = OFF_BIASQ + T_TILE;
+    static constexpr int BYTES = OFF_BIASK + T_TILE;
+    static constexpr int MAX_PACKED = 31;  // sentences per tile the score-bias columns can tell apart
     // tensor memory: ACC[2] (q | k | v of the head being projected), per group S (one unit of 64 keys), O (two units), and P:
     // the probabilities as 16-bit pairs, one 32-bit column per two keys, which the P.V MMA reads straight from tensor
     // memory (A operand in TMEM) - they never go through shared memory
@@ -153,6 +155,7 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
     const uint32_t bar_o_full = aux + 192;                               // [group][unit]: P.V of that unit has completed
     const uint32_t bar_o_empty = aux + 224;                              // [group]: the output warps have read the head's O
     const uint32_t bar_c_full = aux + 240;                               // [group]: the head's corr / l are in shared memory
+    const uint32_t bar_sb_full = aux + 304, bar_sb_empty = aux + 312;    // the tile's score-bias tiles are written / have been read
     const uint32_t tmem_slot = aux + 256;
     volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + C::OFF_AUX + 256);
 
@@ -177,6 +180,8 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
             mbar_init(bar_c_full + 8 * s, QA_GROUP);
         }
         for (int s = 0; s < 4; ++s) { mbar_init(bar_o_full + 8 * s, 1); mbar_init(bar_v_empty + 8 * s, 1); }
+        mbar_init(bar_sb_full, QA_GROUP);
+        mbar_init(bar_sb_empty, 2);  // one commit per group issuer
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc(tmem_slot, 512);
@@ -319,13 +324,18 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
         constexpr uint32_t idesc_o = umma_idesc_op(BLK, D) | (1u << 16);  // B (= V) is MN-major
         const uint64_t dq0 = umma_desc_k_sw64(smem_t + G * C::G_TILES * T_TILE);
         const uint64_t dv0 = umma_desc_mn<D>(smem_t + G * C::G_TILES * T_TILE + 2 * T_TILE);
-        uint32_t hc = 0;          // heads of this group completed (P.V side)
+        const uint64_t dbq0 = umma_desc_k_sw64(base + C::OFF_BIASQ), dbk0 = umma_desc_k_sw64(base + C::OFF_BIASK);
+        uint32_t hc = 0;          // heads of this group completed
         uint32_t us = 0, uo = 0;  // S / P.V units issued
+        uint32_t nb = 0;          // packed tiles (with score-bias tiles) seen
         TL_DECL;
-        // S of head number hn (of this group; hn = hc or hc + 1: the first unit of the next head is issued ahead)
-        auto issue_s = [&](int u, bool first, bool last, uint32_t hn) {
+        // S of unit u. `packed`: the tile holds several sentences and the convert warps have written its score-bias tiles:
+        // two more k-steps add 0 to the scores of a row's own sentence and -30000 to all others (keys past the tile's
+        // tokens included), so the softmax warps need no masking at all.
+        auto issue_s = [&](int u, bool first, bool last, bool packed, bool sb_wait, bool sb_release) {
             TL(0);
-            if (first) mbar_wait(bar_t_full + 8 * G, hn & 1);       // this head's Q / K / V are staged
+            if (first) mbar_wait(bar_t_full + 8 * G, hc & 1);       // this head's Q / K / V are staged
+            if (sb_wait) mbar_wait(bar_sb_full, nb & 1);            // this tile's score-bias tiles are written
             TL(1);
             mbar_wait(bar_s_empty + 8 * G, (us & 1) ^ 1);           // the group has read the previous S
             TL(2);
@@ -335,8 +345,15 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
 #pragma unroll
                 for (int k = 0; k < D / 16; ++k)
                     umma_bf16(tmem_base + C::S_COL + G * UNIT, dq0 + 2 * k, dk + 2 * k, idesc_s, k > 0 ? 1u : 0u);
+                if (packed) {
+                    const uint64_t dbk = dbk0 + ((u * (UNIT * 64)) >> 4);
+#pragma unroll
+                    for (int k = 0; k < 2; ++k)
+                        umma_bf16(tmem_base + C::S_COL + G * UNIT, dbq0 + 2 * k, dbk + 2 * k, idesc_s, 1u);
+                }
                 umma_commit(bar_s_full + 8 * G);
                 if (last) umma_commit(bar_qk_empty + 8 * G);  // Q and K may be restaged for the next head
+                if (sb_release) umma_commit(bar_sb_empty);    // this group's last S of the tile
             }
             __syncwarp();
             ++us;
@@ -361,58 +378,22 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
             __syncwarp();
             ++uo;
         };
-        // the group's heads over all tiles, one after the other, with the unit count of their tile
-        struct HeadIt { Walk w; int h, nunits; bool valid; };
-        auto next_head = [&](HeadIt& it) {
-            it.h += 2;
-            if (it.h < HEADS) return;
-            it.valid = false;
-            while (it.w.b < n_items) {
-                int start, len;
-                if (!take(it.w, start, len)) continue;
-                it.nunits = (len + UNIT - 1) / UNIT;
-                it.h = G;
-                it.valid = true;
-                return;
-            }
-        };
-        HeadIt cur{walk_init(), HEADS, 0, false};
-        next_head(cur);
-        // order per head k: [S(k, u0) was issued during head k - 1], S(k, u1), P.V(k, u0), then S(k + 1, u0) and
-        // P.V(k, last) in the order their inputs arrive: the next head's first scores are computed while the softmax warps
-        // work on this head's last unit, without holding that unit's P.V back when the next head's tiles are late
-        auto ready = [&](uint32_t bar, uint32_t parity) { return __shfl_sync(0xffffffffu, mbar_test(bar, parity) ? 1 : 0, 0) != 0; };
-#if QA_LOOKAHEAD
-        if (cur.valid) issue_s(0, true, cur.nunits == 1, 0);
-#endif
-        while (cur.valid) {
-            HeadIt nxt = cur;
-            next_head(nxt);
-#if !QA_LOOKAHEAD
-            issue_s(0, true, cur.nunits == 1, hc);
-            nxt.valid = false;
-#endif
-            if (cur.nunits > 1) {
-                issue_s(1, false, true, hc);
-                issue_pv(0, false);
-            }
-            bool s_pending = nxt.valid, pv_pending = true;
-            while (s_pending || pv_pending) {
-                if (pv_pending && (!s_pending || ready(bar_p_full + 8 * G, uo & 1))) {
-                    issue_pv(cur.nunits - 1, true);
-                    pv_pending = false;
-                } else if (s_pending && (!pv_pending || (ready(bar_t_full + 8 * G, (hc + 1) & 1) &&
-                                                         ready(bar_s_empty + 8 * G, (us & 1) ^ 1)))) {
-                    issue_s(0, true, nxt.nunits == 1, hc + 1);
-                    s_pending = false;
+        Walk w = walk_init();
+        while (w.b < n_items) {
+            int start, len, first, last;
+            if (!take2(w, start, len, first, last)) continue;
+            const int nunits = (len + UNIT - 1) / UNIT;
+            const bool packed = last - first > 1 && last - first <= C::MAX_PACKED;
+            for (int h = G; h < HEADS; h += 2, ++hc) {
+                const bool tfirst = h == G, tlast = h + 2 >= HEADS;
+                issue_s(0, true, nunits == 1, packed, packed && tfirst, packed && tlast && nunits == 1);
+                if (nunits > 1) {
+                    issue_s(1, false, true, packed, false, packed && tlast);
+                    issue_pv(0, false);
                 }
+                issue_pv(nunits - 1, true);
             }
-            ++hc;
-#if !QA_LOOKAHEAD
-            nxt = cur;
-            next_head(nxt);
-#endif
-            cur = nxt;
+            if (packed) ++nb;
         }
         TL(0);
         TL_PRINT("grp issuer: issue t_full s_empty p_full o_empty");
@@ -436,8 +417,10 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
             if (!take2(w, start, len, first, last)) continue;
             const int nunits = (len + UNIT - 1) / UNIT;
             // keys [klo, khi) of the tile are this row's own sentence (rows past the tile's tokens: none)
+            // (tiles of up to 31 sentences are masked by the S MMA itself - see the convert warps - and need none of this)
+            const bool packed = last - first > 1 && last - first <= C::MAX_PACKED;
             int klo = 0, khi = row < len ? len : 0;
-            if (last - first > 1 && row < len) {  // several sentences share the tile: find mine
+            if (!packed && last - first > 1 && row < len) {  // more sentences than that share the tile: find mine
                 int a = first, b = last;          // cu[a] - start <= row < cu[b] - start
                 while (b - a > 1) {
                     const int mid = (a + b) >> 1;
@@ -473,7 +456,7 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                     const uint32_t k0 = u == 0 ? km[0][0] : km[1][0], k1 = u == 0 ? km[0][1] : km[1][1];
                     // (a mask test is one instruction per key; comparing j with the range bounds took two: 0.412 -> 0.362 ms per
                     // launch on corpus-length tiles)
-                    if ((k0 & k1) != 0xffffffffu) {  // keys of other sentences / past the end -> -inf (exp2 then gives exactly 0)
+                    if (!packed && (k0 & k1) != 0xffffffffu) {  // keys of other sentences / past the end -> -inf (exp2 then gives exactly 0)
 #pragma unroll
                         for (int j = 0; j < UNIT; ++j)
                             if (((j < 32 ? k0 : k1) & (1u << (j & 31))) == 0) v[j] = 0xff800000u;
@@ -540,11 +523,43 @@ qkv_attention_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
         const int row = quad * 32 + lane;
         const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
         uint32_t gh = 0;  // heads converted; head gh belongs to group gh & 1 and is that group's head number gh >> 1
+        uint32_t nb = 0;  // packed tiles seen
         TL_DECL;
         Walk w = walk_init();
         while (w.b < n_items) {
-            int start, len;
-            if (!take(w, start, len)) continue;
+            int start, len, first, last;
+            if (!take2(w, start, len, first, last)) continue;
+            if (last - first > 1 && last - first <= C::MAX_PACKED) {
+                // Several sentences share the tile: attention is block-diagonal. Instead of masking 64 scores per row and
+                // unit in registers, the mask rides on the tensor pipe: 32 extra columns of the S contraction hold, on the Q
+                // side, a one-hot row "my sentence is number c of this tile" and, on the K side, 0 in the column of the key's
+                // own sentence and -30000 everywhere else (keys past the tile's tokens: -30000 in every column). Their
+                // product adds 0 to the scores inside a sentence and -30000 (x log2 e / sqrt d, far below any score) to all
+                // others, whose exponentials are then exactly 0. Written once per tile, read by the S MMAs of all heads.
+                int sid = C::MAX_PACKED;  // rows past the tile's tokens: a sentence nobody has
+                if (row < len) {
+                    int a = first, b = last;  // cu[a] - start <= row < cu[b] - start
+                    while (b - a > 1) {
+                        const int mid = (a + b) >> 1;
+                        if (__ldg(p.cu + mid) - start <= row) a = mid; else b = mid;
+                    }
+                    sid = a - first;
+                }
+                uint32_t wq[16], wk[16];
+                const uint32_t neg2 = pack_op2(-30000.0f, -30000.0f);
+#pragma unroll
+                for (int c = 0; c < 16; ++c) {
+                    const bool mine = c == (sid >> 1);
+                    wq[c] = mine ? ((sid & 1) ? pack_op2(0.0f, 1.0f) : pack_op2(1.0f, 0.0f)) : 0u;
+                    wk[c] = (mine && row < len) ? ((sid & 1) ? pack_op2(-30000.0f, 0.0f) : pack_op2(0.0f, -30000.0f)) : neg2;
+                }
+                mbar_wait(bar_sb_empty, (nb & 1) ^ 1);  // the previous packed tile's last S MMAs (both groups) have read them
+                stage_words_bf16(base + C::OFF_BIASQ, row, wq);
+                stage_words_bf16(base + C::OFF_BIASK, row, wk);
+                fence_proxy_async_smem();
+                mbar_arrive(bar_sb_full);
+                ++nb;
+            }
             for (int h = 0; h < HEADS; ++h, ++gh) {
                 const uint32_t G = gh & 1, hcg = gh >> 1;
                 const uint32_t tile = smem_t + G * C::G_TILES * T_TILE;
