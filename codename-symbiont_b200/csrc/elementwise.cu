@@ -166,17 +166,17 @@ __device__ __forceinline__ int pack_segment(const int* cu, int b0, int b1, int c
     if (out) out[n] = first;
     return n + 1;
 }
-__global__ void pack_tiles_kernel(const int* cu, int batch, int cap, int* __restrict__ seg_off,
+__global__ void pack_tiles_kernel(const int* cu, int batch, int cap, int stage_max, int* __restrict__ seg_off,
                                   int* __restrict__ tile_first, int* __restrict__ n_tiles) {
     __shared__ int warp_tot[32];
     __shared__ int carry;
-    // the sequential walks below read cu twice, one dependent load after the other: for the batch sizes the engine sends
-    // (<= 8192 sentences per call) the block first copies it into shared memory with coalesced loads
-    constexpr int STAGE_MAX = 8192;
-    __shared__ int s_cu[STAGE_MAX + 1];
+    // the sequential walks below read cu twice, one dependent load after the other: for the batch sizes the callers send
+    // (the engine <= 8192 sentences per launch, the corpus driver <= 16384) the block first copies it into shared memory
+    // with coalesced loads; `stage_max` = the capacity of the dynamic shared array (0: read global memory)
+    extern __shared__ int s_cu[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int nseg = (batch + PACK_SEG - 1) / PACK_SEG;
-    if (batch <= STAGE_MAX) {
+    if (batch <= stage_max) {
         for (int i = threadIdx.x; i <= batch; i += blockDim.x) s_cu[i] = cu[i];
         cu = s_cu;
     }
@@ -394,7 +394,19 @@ cudaError_t launch_mask_lengths(const uint32_t* mask, int batch, int seq_len, in
 cudaError_t launch_pack_tiles(const int* cu, int batch, int cap, int* seg_off, int* tile_first, int* n_tiles,
                               cudaStream_t s) {
     if (batch <= 0) return cudaSuccess;
-    pack_tiles_kernel<<<1, 1024, 0, s>>>(cu, batch, cap, seg_off, tile_first, n_tiles);
+    constexpr int STAGE_LIMIT = 32768;  // sentences whose cu fits the staging array (128 KB of dynamic shared memory)
+    const int stage_max = batch <= STAGE_LIMIT ? batch : 0;
+    const size_t smem = stage_max ? (static_cast<size_t>(stage_max) + 1) * sizeof(int) : 0;
+    if (smem > 48 * 1024) {
+        static PerDeviceOnce attr_set;  // function attributes belong to a (function, device) pair
+        if (!attr_set.done()) {
+            cudaError_t e = cudaFuncSetAttribute(pack_tiles_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                 (STAGE_LIMIT + 1) * static_cast<int>(sizeof(int)));
+            if (e != cudaSuccess) return e;
+            attr_set.mark();
+        }
+    }
+    pack_tiles_kernel<<<1, 1024, smem, s>>>(cu, batch, cap, stage_max, seg_off, tile_first, n_tiles);
     return cudaGetLastError();
 }
 
