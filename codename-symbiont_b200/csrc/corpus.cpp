@@ -141,6 +141,38 @@ void plan_lengths(const int32_t* len, int64_t n, int32_t max_len, int32_t max_se
     begins.push_back(n);
 }
 
+// The engine's fused attention (K23) works on tiles of 128 token rows that hold WHOLE consecutive sentences, packed
+// greedily in the order they are sent. Sorted by length that order fills the tiles to 83 % (corpus length law; 84 % in
+// random order); sending a micro-batch tile by tile - best-fit-decreasing bin packing into 128-token bins, then the bins one
+// after the other - fills them to 99 % (96 % after the packing kernel's 128-sentence segments). `sentences`: ascending by
+// length on entry. Only the order inside the micro-batch changes; results are scattered back by sentence index as before.
+void order_by_tiles(std::vector<int32_t>& sentences, const int32_t* len, int cap) {
+    const size_t n = sentences.size();
+    std::vector<std::vector<int32_t>> by_room(static_cast<size_t>(cap) + 1);  // open bins by remaining room
+    std::vector<std::vector<int32_t>> bins;
+    bins.reserve(n / 3 + 1);
+    for (size_t k = n; k-- > 0;) {  // longest first
+        const int32_t i = sentences[k];
+        const int l = std::min(std::max(static_cast<int>(len[static_cast<size_t>(i)]), 1), cap);
+        int room = l;
+        while (room <= cap && by_room[static_cast<size_t>(room)].empty()) ++room;  // the fullest bin it still fits
+        int32_t b;
+        if (room <= cap) {
+            b = by_room[static_cast<size_t>(room)].back();
+            by_room[static_cast<size_t>(room)].pop_back();
+        } else {
+            b = static_cast<int32_t>(bins.size());
+            bins.emplace_back();
+            room = cap;
+        }
+        bins[static_cast<size_t>(b)].push_back(i);
+        if (room - l > 0) by_room[static_cast<size_t>(room - l)].push_back(b);
+    }
+    size_t at = 0;
+    for (const auto& bin : bins)
+        for (int32_t i : bin) sentences[at++] = i;
+}
+
 // All chunks of the shard are tokenised: order its sentences by token count and cut the micro-batches.
 void plan_shard(b200_corpus* c, Shard* sh) {
     const int64_t n = sh->n;
@@ -162,6 +194,7 @@ void plan_shard(b200_corpus* c, Shard* sh) {
             mb->tokens += len[static_cast<size_t>(i)];
             mb->max_len = std::max(mb->max_len, len[static_cast<size_t>(i)]);
         }
+        if (mb->max_len <= 128) order_by_tiles(mb->sentences, len.data(), 128);  // the shape K23 takes
         made.push_back(std::move(mb));
     }
     sh->batches_left.store(static_cast<int>(made.size()));
