@@ -80,6 +80,7 @@ _SIGNATURES = {
     "b200_corpus_wait": (C.c_int32, [_P, C.c_int64]),
     "b200_corpus_stats_read": (C.c_int32, [_P, C.POINTER(CorpusStats), C.c_int32]),
     "b200_corpus_plan": (C.c_int64, [_P, C.c_int64, C.c_int32, C.c_int32, C.c_int64, _P, _P, C.c_int64]),
+    "b200_corpus_plan_packed": (C.c_int64, [_P, C.c_int64, C.c_int32, C.c_int32, C.c_int64, _P, _P, C.c_int64]),
     "b200_embed_forward_device": (C.c_int32, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_uint32, _P, _P]),
     "b200_embed_host_alloc": (C.c_int32, [C.c_size_t, C.POINTER(_P)]),
     "b200_embed_host_free": (None, [_P]),
@@ -690,6 +691,20 @@ def corpus_plan(lengths, max_len: int, max_batch_sentences: int, max_batch_token
     begins = np.empty(n + 2, dtype=np.int64)
     nb = load_library().b200_corpus_plan(lengths.ctypes.data, n, max_len, max_batch_sentences, max_batch_tokens,
                                          order.ctypes.data, begins.ctypes.data, len(begins))
+    if nb < 0:
+        raise B200EmbedError(int(nb), load_library().b200_corpus_last_error().decode())
+    return order, begins[:nb + 1].copy()
+
+
+def corpus_plan_packed(lengths, max_len: int, max_batch_sentences: int, max_batch_tokens: int):
+    """b200_corpus_plan_packed, the plan b200_corpus_submit makes: -> (order [n] int32, batch_begin [nb + 1] int64); short
+    sentences in input-order micro-batches, tile by tile inside each."""
+    lengths = np.ascontiguousarray(lengths, dtype=np.int32)
+    n = len(lengths)
+    order = np.empty(n, dtype=np.int32)
+    begins = np.empty(n + 2, dtype=np.int64)
+    nb = load_library().b200_corpus_plan_packed(lengths.ctypes.data, n, max_len, max_batch_sentences, max_batch_tokens,
+                                                order.ctypes.data, begins.ctypes.data, len(begins))
     if nb < 0:
         raise B200EmbedError(int(nb), load_library().b200_corpus_last_error().decode())
     return order, begins[:nb + 1].copy()

@@ -173,31 +173,24 @@ void order_by_tiles(std::vector<int32_t>& sentences, const int32_t* len, int cap
         for (int32_t i : bin) sentences[at++] = i;
 }
 
-// All chunks of the shard are tokenised: order its sentences by token count and cut the micro-batches.
-void plan_shard(b200_corpus* c, Shard* sh) {
-    const int64_t n = sh->n;
-    std::vector<int32_t> len(static_cast<size_t>(n));
-    for (int64_t i = 0; i < n; ++i) {
-        const Chunk& ch = sh->chunks[static_cast<size_t>(i / CHUNK_SENTENCES)];
-        const int k = static_cast<int>(i % CHUNK_SENTENCES);
-        len[static_cast<size_t>(i)] = ch.cu[static_cast<size_t>(k) + 1] - ch.cu[static_cast<size_t>(k)];
-    }
-    std::vector<int32_t> order;
-    std::vector<int64_t> begins;
-    plan_lengths(len.data(), n, c->max_len, c->max_batch_sentences, c->max_batch_tokens, order, begins);
+// The plan the corpus driver uses (also exported as b200_corpus_plan_packed): plan_lengths, then the sentences of at most
+// 128 tokens recut in input order and every micro-batch of such sentences put into tile order.
+void plan_packed(const int32_t* len, int64_t n, int32_t max_len, int32_t max_sentences, int64_t max_tokens,
+                 std::vector<int32_t>& order, std::vector<int64_t>& begins) {
+    plan_lengths(len, n, max_len, max_sentences, max_tokens, order, begins);
     // Sentences of at most 128 tokens go through K23, whose tiles want long and short sentences side by side (order_by_tiles
     // below): they are cut into micro-batches in INPUT order - a length-sorted micro-batch holds nothing short enough to fill
     // the gaps its long sentences leave (89 % full tiles instead of 99 %). Longer sentences keep the length order.
     {
         int64_t n_short = 0;
-        while (n_short < n && len[static_cast<size_t>(order[static_cast<size_t>(n_short)])] <= 128) ++n_short;
+        while (n_short < n && len[order[static_cast<size_t>(n_short)]] <= 128) ++n_short;
         if (n_short > 0) {
             std::sort(order.begin(), order.begin() + n_short);  // back to input order
             std::vector<int64_t> cut;
             int64_t tokens = 0, sentences = 0;
             for (int64_t k = 0; k < n_short; ++k) {
-                const int l = len[static_cast<size_t>(order[static_cast<size_t>(k)])];
-                if (k == 0 || sentences >= c->max_batch_sentences || tokens + l > c->max_batch_tokens) {
+                const int l = len[order[static_cast<size_t>(k)]];
+                if (k == 0 || sentences >= max_sentences || tokens + l > max_tokens) {
                     cut.push_back(k);
                     tokens = 0;
                     sentences = 0;
@@ -214,6 +207,30 @@ void plan_shard(b200_corpus* c, Shard* sh) {
             begins.swap(cut);
         }
     }
+    for (size_t b = 0; b + 1 < begins.size(); ++b) {
+        int32_t longest = 0;
+        for (int64_t k = begins[b]; k < begins[b + 1]; ++k) longest = std::max(longest, len[order[static_cast<size_t>(k)]]);
+        if (longest <= 128) {  // the shape K23 takes
+            std::vector<int32_t> part(order.begin() + begins[b], order.begin() + begins[b + 1]);
+            std::sort(part.begin(), part.end(), [&](int32_t x, int32_t y) { return len[x] != len[y] ? len[x] < len[y] : x < y; });
+            order_by_tiles(part, len, 128);
+            std::copy(part.begin(), part.end(), order.begin() + begins[b]);
+        }
+    }
+}
+
+// All chunks of the shard are tokenised: order its sentences by token count and cut the micro-batches.
+void plan_shard(b200_corpus* c, Shard* sh) {
+    const int64_t n = sh->n;
+    std::vector<int32_t> len(static_cast<size_t>(n));
+    for (int64_t i = 0; i < n; ++i) {
+        const Chunk& ch = sh->chunks[static_cast<size_t>(i / CHUNK_SENTENCES)];
+        const int k = static_cast<int>(i % CHUNK_SENTENCES);
+        len[static_cast<size_t>(i)] = ch.cu[static_cast<size_t>(k) + 1] - ch.cu[static_cast<size_t>(k)];
+    }
+    std::vector<int32_t> order;
+    std::vector<int64_t> begins;
+    plan_packed(len.data(), n, c->max_len, c->max_batch_sentences, c->max_batch_tokens, order, begins);
     std::vector<std::unique_ptr<MicroBatch>> made;
     for (size_t b = 0; b + 1 < begins.size(); ++b) {
         std::unique_ptr<MicroBatch> mb(new MicroBatch());
@@ -223,7 +240,6 @@ void plan_shard(b200_corpus* c, Shard* sh) {
             mb->tokens += len[static_cast<size_t>(i)];
             mb->max_len = std::max(mb->max_len, len[static_cast<size_t>(i)]);
         }
-        if (mb->max_len <= 128) order_by_tiles(mb->sentences, len.data(), 128);  // the shape K23 takes
         made.push_back(std::move(mb));
     }
     sh->batches_left.store(static_cast<int>(made.size()));
@@ -536,6 +552,24 @@ int64_t b200_corpus_plan(const int32_t* lengths, int64_t n, int32_t max_len, int
         return nb;
     } catch (const std::exception& e) {
         return fail(B200_EMBED_ERR_OOM, std::string("corpus_plan: ") + e.what());
+    }
+}
+
+int64_t b200_corpus_plan_packed(const int32_t* lengths, int64_t n, int32_t max_len, int32_t max_batch_sentences,
+                                int64_t max_batch_tokens, int32_t* order, int64_t* batch_begin, int64_t batch_begin_cap) {
+    if (n < 0 || (n > 0 && (!lengths || !order)) || max_len <= 0 || max_batch_sentences <= 0 || max_batch_tokens <= 0)
+        return fail(B200_EMBED_ERR_INVALID_ARG, "corpus_plan_packed: bad argument");
+    if (n > INT32_MAX) return fail(B200_EMBED_ERR_INVALID_ARG, "corpus_plan_packed: more than 2^31 sentences");
+    try {
+        std::vector<int32_t> ord;
+        std::vector<int64_t> begins;
+        plan_packed(lengths, n, max_len, max_batch_sentences, max_batch_tokens, ord, begins);
+        if (n > 0) std::memcpy(order, ord.data(), static_cast<size_t>(n) * sizeof(int32_t));
+        const int64_t nb = static_cast<int64_t>(begins.size()) - 1;
+        if (batch_begin && batch_begin_cap >= nb + 1) std::memcpy(batch_begin, begins.data(), static_cast<size_t>(nb + 1) * sizeof(int64_t));
+        return nb;
+    } catch (const std::exception& e) {
+        return fail(B200_EMBED_ERR_OOM, std::string("corpus_plan_packed: ") + e.what());
     }
 }
 

@@ -444,6 +444,12 @@ int32_t b200_corpus_stats_read(b200_corpus* c, b200_corpus_stats* out, int32_t r
  * batch_begin_cap >= that + 1); negative on bad arguments. */
 int64_t b200_corpus_plan(const int32_t* lengths, int64_t n, int32_t max_len, int32_t max_batch_sentences,
                          int64_t max_batch_tokens, int32_t* order, int64_t* batch_begin, int64_t batch_begin_cap);
+/* The plan b200_corpus_submit itself makes, same arguments and results: sentences longer than 128 tokens as above; those
+ * of at most 128 tokens (the shape the fused QKV + attention kernel takes) cut into micro-batches in INPUT order and,
+ * inside each micro-batch, ordered tile by tile - best-fit-decreasing packing into 128-token tiles, the tiles one after the
+ * other - so that the kernel's tiles of whole consecutive sentences come out full. */
+int64_t b200_corpus_plan_packed(const int32_t* lengths, int64_t n, int32_t max_len, int32_t max_batch_sentences,
+                                int64_t max_batch_tokens, int32_t* order, int64_t* batch_begin, int64_t batch_begin_cap);
 
 #ifdef __cplusplus
 }

@@ -141,3 +141,49 @@ def test_native_corpus_planner_properties(pkg, built):
         # greedy cuts: a batch could not have taken the next sentence as well
         for a, b in zip(begins[:-2], begins[1:-1]):
             assert b - a == max_s or ls[a:b].sum() + ls[b] > max_t
+
+
+def _greedy_tiles(lengths, seg=128, cap=128):
+    """tiles the engine's packing kernel makes of sentences sent in this order (csrc/elementwise.cu pack_tiles_kernel)"""
+    n = 0
+    for s0 in range(0, len(lengths), seg):
+        base = cnt = 0
+        for l in lengths[s0:s0 + seg]:
+            if base + l > cap and cnt > 0:
+                n, base, cnt = n + 1, 0, 0
+            base, cnt = base + l, cnt + 1
+        n += 1
+    return n
+
+
+def test_native_corpus_planner_packs_tiles(pkg, built):
+    """b200_corpus_plan_packed (what b200_corpus_submit plans): a permutation inside the budgets; sentences of at most 128
+    tokens stay in input-order micro-batches (as sets) and come out tile by tile - the packing kernel's greedy tiles are
+    nearly full, far fuller than from the length order; longer sentences keep the ascending order of b200_corpus_plan."""
+    rng = np.random.default_rng(3)
+    lengths = np.clip(np.rint(rng.lognormal(np.log(24), 0.6, size=70000)), 4, 128).astype(np.int32)
+    max_s, max_t = 16384, 512 * 1024
+    order, begins = pkg.abi.corpus_plan_packed(lengths, 512, max_s, max_t)
+    assert sorted(order.tolist()) == list(range(len(lengths)))
+    assert begins[0] == 0 and begins[-1] == len(lengths) and np.all(np.diff(begins) > 0)
+    tiles = 0
+    for k, (a, b) in enumerate(zip(begins[:-1], begins[1:])):
+        ls = lengths[order[a:b]]
+        assert b - a <= max_s and ls.sum() <= max_t
+        # input-order cut: micro-batch k is the k-th run of consecutive sentences
+        assert sorted(order[a:b].tolist()) == list(range(a, b))
+        tiles += _greedy_tiles(ls.tolist())
+    ideal = lengths.sum() / 128
+    by_length, _ = pkg.abi.corpus_plan(lengths, 512, max_s, max_t)
+    assert tiles <= 1.06 * ideal, (tiles, ideal)  # 128-sentence segments cost a few per cent
+    assert tiles <= 0.87 * _greedy_tiles(lengths[by_length].tolist())
+    # mixed corpus: the long sentences follow, ascending, in micro-batches of their own
+    lengths2 = np.concatenate([lengths[:5000], rng.integers(129, 513, size=800).astype(np.int32)])
+    rng.shuffle(lengths2)
+    order2, begins2 = pkg.abi.corpus_plan_packed(lengths2, 512, max_s, max_t)
+    assert sorted(order2.tolist()) == list(range(len(lengths2)))
+    ls2 = lengths2[order2]
+    n_short = int((lengths2 <= 128).sum())
+    assert np.all(ls2[:n_short] <= 128) and np.all(np.diff(ls2[n_short:]) >= 0) and n_short in begins2.tolist()
+    for a, b in zip(begins2[:-1], begins2[1:]):
+        assert b - a <= max_s and ls2[a:b].sum() <= max_t
