@@ -11,7 +11,7 @@ for fused in ("0", "1"):
     for operands in ("f16", "bf16"):
         for shape, lengths, S in ((pkg.weights.BertShape(512, 384, 1, 12, 1536, 128, 2), [2, 7, 33, 64, 65, 100, 128, 128, 5, 3], 128),
                                   (pkg.weights.BertShape(512, 768, 1, 12, 3072, 256, 2), [2, 200, 129, 64], 256),
-                                  (pkg.weights.TINY, [1, 2, 17, 64], 64)):
+                                  (pkg.weights.TINY, [2, 3, 17, 64], 64)):
             ids, mask, tt = pkg.synth.padded_batch(shape.vocab_size, lengths, S, seed=1)
             with pkg.Embedder.random_init(shape, seed=3, operands=operands) as emb:
                 out = emb.forward(ids, mask, tt)
