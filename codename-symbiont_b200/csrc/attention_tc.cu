@@ -53,6 +53,11 @@ struct AttnDev {
     __nv_bfloat16* ctx;
 };
 
+// CTAs per SM at head_dim 64 (2: one O accumulator per CTA and registers moved to the softmax warps by setmaxnreg)
+#ifndef K3_CTAS_D64
+#define K3_CTAS_D64 2
+#endif
+
 template <int D>
 struct AttnSmem {
     static constexpr int TILE = BLK * D * 2;         // one Q / K / V tile
@@ -63,14 +68,17 @@ struct AttnSmem {
 };
 
 template <int D>
-__global__ void __launch_bounds__(ATT_THREADS, D == 32 ? 2 : 1)
+__global__ void __launch_bounds__(ATT_THREADS, K3_CTAS_D64 == 2 || D == 32 ? 2 : 1)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev p) {
     using L = AttnSmem<D>;
     constexpr int TILE = L::TILE;
     // tensor memory: 2 x 64 S | 2 x D O | 2 x 32 P. The probabilities are written there as 16-bit pairs (one 32-bit column per
     // two keys) and the P.V MMA reads its A operand from tensor memory: P never goes through shared memory, whose operand
     // fetch (128 B per clock) paces these small MMAs.
-    constexpr int O_COL = 2 * UNIT, P_COL = O_COL + 2 * D;
+    // d = 64 with two CTAs per SM: one O accumulator (the next item's first P.V waits for this item's rows to be written,
+    // which happens right after that item's first P is in place), so that each CTA fits 256 of the SM's 512 columns
+    constexpr int OB = (D == 64 && K3_CTAS_D64 == 2) ? 1 : 2;
+    constexpr int O_COL = 2 * UNIT, P_COL = O_COL + OB * D;
     constexpr uint32_t TMEM_COLS = P_COL + UNIT <= 256 ? 256 : 512;
 
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -147,6 +155,11 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
     // The producer and MMA warps walk their loops as whole warps (uniform control flow) and elect one lane to issue:
     // under `if (lane == 0)` every single-thread instruction gets wrapped in a divergence-safe ELECT loop and the issue
     // rate of that one thread becomes the bottleneck.
+    // d = 64, two CTAs per SM: they start at 128 registers per thread; the four single-thread-role warps hand theirs to the
+    // softmax warps (each setmaxnreg at the head of its warpgroup's branch: ptxas budgets the code that follows it)
+    constexpr bool REGSPLIT = D == 64 && K3_CTAS_D64 == 2;
+    if (warp < SM_WARP0) {
+    if constexpr (REGSPLIT) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(40));
     if (warp == PRODUCER_WARP) {
         uint32_t q_it = 0, kv_it = 0;
         Walk w = walk_init();
@@ -223,10 +236,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
             ++us;
         };
         auto issue_pv = [&](const Cursor& c) {
-            const uint32_t kvi = c.kv_it + (c.u >> 1), s = kvi & 1, pb = uo & 1, ob = c.q_it & 1;
+            const uint32_t kvi = c.kv_it + (c.u >> 1), s = kvi & 1, pb = uo & 1, ob = c.q_it % OB;
             mbar_wait(bar_p_full + 8 * pb, (uo >> 1) & 1);         // P_u is in tensor memory (and O rescaled if it had to be)
             // the item's first unit overwrites its O buffer: the item two back has been finalised out of it
-            if (c.u == 0) mbar_wait(bar_o_empty + 8 * ob, ((c.q_it >> 1) & 1) ^ 1);
+            if (c.u == 0) mbar_wait(bar_o_empty + 8 * ob, ((c.q_it / OB) & 1) ^ 1);
             tc_fence_after_sync();
             if (elect_one()) {
                 const uint32_t tp = tmem_base + P_COL + pb * (UNIT / 2);
@@ -251,7 +264,9 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
             }
             issue_pv(pc);
         }
-    } else if (warp >= SM_WARP0) {
+    }
+    } else {
+        if constexpr (REGSPLIT) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(216));
         const int quad = warp & 3;
         const int row = quad * 32 + lane;  // query row inside the item = TMEM lane
         const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
@@ -307,7 +322,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
             if (!take(w, b, qb, h, start, len)) continue;
             float m = -INFINITY, l = 0.f;
             const int nunits = (len + UNIT - 1) / UNIT;
-            const uint32_t ob = ic & 1;
+            const uint32_t ob = ic % OB;
             for (int u = 0; u < nunits; ++u, ++uc) {
                 const uint32_t sb = uc & 1;
                 const int nvalid = min(UNIT, len - u * UNIT);  // keys of this unit inside the sentence
@@ -439,7 +454,7 @@ cudaError_t launch(const __nv_bfloat16* qkv, const int* cu, int rows_cap, int ba
     p.ctx = ctx;
     const long long items = static_cast<long long>(batch) * heads * p.q_blocks;
     if (items <= 0) return cudaSuccess;
-    const int ctas = num_sms * (D == 32 ? 2 : 1);
+    const int ctas = num_sms * ((D == 32 || K3_CTAS_D64 == 2) ? 2 : 1);
     const int grid = static_cast<int>(items < ctas ? items : ctas);
     return launch_pdl(kern, dim3(grid), dim3(ATT_THREADS), smem, s, map, p);
 }
