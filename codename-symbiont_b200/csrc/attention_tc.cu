@@ -57,6 +57,10 @@ struct AttnDev {
 #ifndef K3_CTAS_D64
 #define K3_CTAS_D64 2
 #endif
+// CTAs per SM at head_dim 32 (3: one S, one P and one O buffer per CTA - 128 tensor-memory columns - and the register split)
+#ifndef K3_CTAS_D32
+#define K3_CTAS_D32 3
+#endif
 
 template <int D>
 struct AttnSmem {
@@ -68,7 +72,7 @@ struct AttnSmem {
 };
 
 template <int D>
-__global__ void __launch_bounds__(ATT_THREADS, K3_CTAS_D64 == 2 || D == 32 ? 2 : 1)
+__global__ void __launch_bounds__(ATT_THREADS, D == 32 ? K3_CTAS_D32 : K3_CTAS_D64)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev p) {
     using L = AttnSmem<D>;
     constexpr int TILE = L::TILE;
@@ -77,9 +81,13 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
     // fetch (128 B per clock) paces these small MMAs.
     // d = 64 with two CTAs per SM: one O accumulator (the next item's first P.V waits for this item's rows to be written,
     // which happens right after that item's first P is in place), so that each CTA fits 256 of the SM's 512 columns
-    constexpr int OB = (D == 64 && K3_CTAS_D64 == 2) ? 1 : 2;
-    constexpr int O_COL = 2 * UNIT, P_COL = O_COL + OB * D;
-    constexpr uint32_t TMEM_COLS = P_COL + UNIT <= 256 ? 256 : 512;
+    constexpr int OB = ((D == 64 && K3_CTAS_D64 == 2) || (D == 32 && K3_CTAS_D32 == 3)) ? 1 : 2;
+    // d = 32 with three CTAs per SM: S and P single-buffered as well (S of the next unit is issued once the softmax warps
+    // have the current one in registers, P is rewritten once the previous unit's P.V has completed - both long before they
+    // are needed), 64 + 32 + 32 = 128 columns per CTA
+    constexpr int NB = (D == 32 && K3_CTAS_D32 == 3) ? 1 : 2;
+    constexpr int O_COL = NB * UNIT, P_COL = O_COL + OB * D;
+    constexpr uint32_t TMEM_COLS = P_COL + NB * (UNIT / 2) <= 128 ? 128 : (P_COL + NB * (UNIT / 2) <= 256 ? 256 : 512);
 
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     const uint32_t base = smem_u32(smem_raw);
@@ -157,9 +165,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
     // rate of that one thread becomes the bottleneck.
     // d = 64, two CTAs per SM: they start at 128 registers per thread; the four single-thread-role warps hand theirs to the
     // softmax warps (each setmaxnreg at the head of its warpgroup's branch: ptxas budgets the code that follows it)
-    constexpr bool REGSPLIT = D == 64 && K3_CTAS_D64 == 2;
+    constexpr bool REGSPLIT = (D == 64 && K3_CTAS_D64 == 2) || (D == 32 && K3_CTAS_D32 == 3);
+    constexpr int REGS_CONTROL = D == 64 ? 40 : 32, REGS_SOFTMAX = D == 64 ? 216 : 128;  // 2 x 128 / 2 x 80 per thread pair at launch
     if (warp < SM_WARP0) {
-    if constexpr (REGSPLIT) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(40));
+    if constexpr (REGSPLIT) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(REGS_CONTROL));
     if (warp == PRODUCER_WARP) {
         uint32_t q_it = 0, kv_it = 0;
         Walk w = walk_init();
@@ -221,23 +230,23 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
             const uint32_t qs = c.q_it & 1, kvi = c.kv_it + (c.u >> 1), s = kvi & 1;
             if (c.u == 0) mbar_wait(bar_q_full + 8 * qs, (c.q_it >> 1) & 1);       // first touch of this item's Q
             if ((c.u & 1) == 0) mbar_wait(bar_kv_full + 8 * s, (kvi >> 1) & 1);    // first touch of this K/V block
-            mbar_wait(bar_s_empty + 8 * (us & 1), ((us >> 1) & 1) ^ 1);            // softmax drained this S buffer
+            mbar_wait(bar_s_empty + 8 * (us % NB), ((us / NB) & 1) ^ 1);           // softmax drained this S buffer
             tc_fence_after_sync();
             if (elect_one()) {
                 const uint64_t dq = dq0 + ((qs * TILE) >> 4);
                 const uint64_t dk = dk0 + ((s * 2 * TILE + (c.u & 1) * (UNIT * D * 2)) >> 4);
 #pragma unroll
                 for (int k = 0; k < D / 16; ++k)
-                    umma_bf16(tmem_base + (us & 1) * UNIT, dq + 2 * k, dk + 2 * k, idesc_s, k > 0 ? 1u : 0u);
-                umma_commit(bar_s_full + 8 * (us & 1));
+                    umma_bf16(tmem_base + (us % NB) * UNIT, dq + 2 * k, dk + 2 * k, idesc_s, k > 0 ? 1u : 0u);
+                umma_commit(bar_s_full + 8 * (us % NB));
                 if (c.u == c.nunits - 1) umma_commit(bar_q_empty + 8 * qs);  // Q is only read by the S MMAs
             }
             __syncwarp();
             ++us;
         };
         auto issue_pv = [&](const Cursor& c) {
-            const uint32_t kvi = c.kv_it + (c.u >> 1), s = kvi & 1, pb = uo & 1, ob = c.q_it % OB;
-            mbar_wait(bar_p_full + 8 * pb, (uo >> 1) & 1);         // P_u is in tensor memory (and O rescaled if it had to be)
+            const uint32_t kvi = c.kv_it + (c.u >> 1), s = kvi & 1, pb = uo % NB, ob = c.q_it % OB;
+            mbar_wait(bar_p_full + 8 * pb, (uo / NB) & 1);         // P_u is in tensor memory (and O rescaled if it had to be)
             // the item's first unit overwrites its O buffer: the item two back has been finalised out of it
             if (c.u == 0) mbar_wait(bar_o_empty + 8 * ob, ((c.q_it / OB) & 1) ^ 1);
             tc_fence_after_sync();
@@ -266,7 +275,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
         }
     }
     } else {
-        if constexpr (REGSPLIT) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(216));
+        if constexpr (REGSPLIT) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(REGS_SOFTMAX));
         const int quad = warp & 3;
         const int row = quad * 32 + lane;  // query row inside the item = TMEM lane
         const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
@@ -288,7 +297,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
             int start, len, qb, h;
         } pend{false, 0, 0, 0.f, 0, 0, 0, 0};
         auto finalise_pending = [&]() {
-            mbar_wait(bar_o_full + 8 * (pend.ur & 1), (pend.ur >> 1) & 1);  // the item's last P.V has completed
+            mbar_wait(bar_o_full + 8 * (pend.ur % NB), (pend.ur / NB) & 1);  // the item's last P.V has completed
             tc_fence_after_sync();
             // O / l. Each lane owns one row of D 16-bit values (64 or 128 contiguous bytes of ctx): whole 32-byte sectors
             // straight from registers.
@@ -324,9 +333,9 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
             const int nunits = (len + UNIT - 1) / UNIT;
             const uint32_t ob = ic % OB;
             for (int u = 0; u < nunits; ++u, ++uc) {
-                const uint32_t sb = uc & 1;
+                const uint32_t sb = uc % NB;
                 const int nvalid = min(UNIT, len - u * UNIT);  // keys of this unit inside the sentence
-                mbar_wait(bar_s_full + 8 * sb, (uc >> 1) & 1);
+                mbar_wait(bar_s_full + 8 * sb, (uc / NB) & 1);
                 tc_fence_after_sync();
                 uint32_t v[UNIT];
                 tmem_ld_32x32(t_lane + sb * UNIT, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
@@ -350,7 +359,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
                     const float corr = jump ? ex2(m - m_new) : 1.0f;
                     if (jump) m = m_new;
                     l *= corr;
-                    mbar_wait(bar_o_full + 8 * ((uc - 1) & 1), ((uc - 1) >> 1) & 1);  // the previous unit's P.V has completed
+                    mbar_wait(bar_o_full + 8 * ((uc - 1) % NB), ((uc - 1) / NB) & 1);  // the previous unit's P.V has completed
                     tc_fence_after_sync();
 #pragma unroll
                     for (int c = 0; c < D / 32; ++c) {
@@ -379,9 +388,12 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnDev 
                         pw[q * 4 + j] = pack_op2(pa, pb);
                     }
                 }
-                // the P buffer was last read by the P.V of the unit two back
-                mbar_wait(bar_o_full + 8 * sb, ((uc >> 1) & 1) ^ 1);
+                // the P buffer was last read by the P.V of the unit NB back
+                mbar_wait(bar_o_full + 8 * sb, ((uc / NB) & 1) ^ 1);
                 tc_fence_after_sync();
+                // (single P buffer: the previous item's rows go out here, while no later P.V can complete - its barrier
+                // would otherwise run a phase ahead of the wait in finalise_pending)
+                if (NB == 1 && pend.valid) finalise_pending();
                 tmem_st_32x32(t_lane + P_COL + sb * (UNIT / 2), pw);
                 float lb;
                 {
@@ -454,7 +466,7 @@ cudaError_t launch(const __nv_bfloat16* qkv, const int* cu, int rows_cap, int ba
     p.ctx = ctx;
     const long long items = static_cast<long long>(batch) * heads * p.q_blocks;
     if (items <= 0) return cudaSuccess;
-    const int ctas = num_sms * ((D == 32 || K3_CTAS_D64 == 2) ? 2 : 1);
+    const int ctas = num_sms * (D == 32 ? K3_CTAS_D32 : K3_CTAS_D64);
     const int grid = static_cast<int>(items < ctas ? items : ctas);
     return launch_pdl(kern, dim3(grid), dim3(ATT_THREADS), smem, s, map, p);
 }
