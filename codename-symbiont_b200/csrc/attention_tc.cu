@@ -1,17 +1,16 @@
 // K3 (tcgen05): varlen self-attention on the 5th-generation tensor cores.
 //
 // Replaces candle bert.rs BertSelfAttention::forward after the Q/K/V projections (scores = q.k^T/sqrt(d)
-// + (1-mask)*f32::MIN, softmax, .v, head merge; called from embedding_generator.rs:198). See attention.cu
-// for the mma.sync variant of the same math; this kernel is the one the forward uses.
+// + (1-mask)*f32::MIN, softmax, .v, head merge; called from embedding_generator.rs:198)
+// (the mma.sync variant of round 1 is gone); this kernel is the one the forward uses when K23 does not apply.
 //
-// Work item = (sentence, head, block of 128 query rows). A persistent CTA (2 per SM for d = 32) walks items; per
+// Work item = (sentence, head, block of 128 query rows). A persistent CTA (3 per SM for d = 32, 2 for d = 64) walks items; per
 // item it walks the sentence's keys in UNITS of 64 keys, two units in flight:
 //   warp 0     TMA producer: Q tile once per item, K and V tiles per 128-key block (2-stage rings), straight from
 //              the packed qkv [tokens, 3H] activations (box D x 128 rows; D*2-byte swizzle)
-//   warp 1     one thread issues tcgen05.mma: S_u = Q.K_u^T (128 x 64, fp32 in TMEM, double-buffered) one unit
-//              ahead of the softmax, then O += P_u.V_u (128 x D, one accumulator per item, two items' worth) as soon
-//              as P_u is written
-//   warp 2     TMEM allocator (2 x 64 S + 2 x D O + 2 x 32 P columns: 256 for d = 32, 512 for d = 64)
+//   warp 1     one thread issues tcgen05.mma: S_u = Q.K_u^T (128 x 64, fp32 in TMEM) one unit ahead of the softmax, then
+//              O += P_u.V_u (128 x D, one accumulator per item) as soon as P_u is written
+//   warp 2     TMEM allocator (S 64 + O 32 + P 32 = 128 columns at d = 32, 2 x 64 S + 64 O + 2 x 32 P = 256 at d = 64)
 //   warps 4-7  softmax: thread r owns query row r (= TMEM lane r). One tcgen05.ld brings the unit's 64 scores
 //              into registers (read once: row max, p = exp2(s*scale - max) and the row sum all work from there),
 //              P goes as 16-bit pairs into tensor memory (the A operand of the second MMA is read there). The units of an
